@@ -1,0 +1,145 @@
+"""Pin the oracle (oracle/) against fixtures produced by the unmodified reference
+(oracle/gen_golden.py).  CPU only."""
+import os
+import re
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import vq_ref, vqvae_ref as R
+
+
+def _load(golden_dir, name):
+    return np.load(os.path.join(golden_dir, name), allow_pickle=False)
+
+
+def _check_summary(g, prefix, t, rtol, atol=0.0):
+    a = t.detach().cpu().numpy().astype(np.float64)
+    if prefix + '/full' in g:
+        ref = g[prefix + '/full'].astype(np.float64)
+        err = np.linalg.norm(a - ref) / max(np.linalg.norm(ref), 1e-30)
+        assert err <= rtol or np.abs(a - ref).max() <= atol, (prefix, err)
+    else:
+        norm = float(g[prefix + '/norm'])
+        assert abs(np.sqrt((a ** 2).sum()) - norm) <= rtol * norm, prefix
+        stride = max(1, a.size // 32)
+        s = a.reshape(-1)[::stride][:32]
+        ref = g[prefix + '/samples'].astype(np.float64)
+        assert np.abs(s - ref).max() <= rtol * max(np.abs(ref).max(), norm / np.sqrt(a.size)) + atol, prefix
+
+
+@pytest.mark.parametrize('tag', ['init', 'spread'])
+def test_vq_c1_against_reference(golden_dir, tag):
+    g = _load(golden_dir, 'vq_c1.npz')
+    rng = np.random.RandomState(int(g[tag + '/seed']))
+    z = rng.standard_normal((16, 128, 64)).astype(np.float32)
+    if tag == 'init':
+        cb = rng.uniform(-1 / 512, 1 / 512, (512, 64)).astype(np.float32)
+    else:
+        cb = rng.standard_normal((512, 64)).astype(np.float32)
+    gout = rng.standard_normal((16, 128, 64)).astype(np.float32)
+    ref_idx = g[tag + '/indices'].astype(np.int64)
+    idx = vq_ref.vq_indices(z, cb)
+    assert idx.dtype == np.int64 and idx.shape == (16, 128)
+    n_mis, n_viol = vq_ref.index_parity(idx, ref_idx, z, cb)
+    assert n_viol == 0 and n_mis <= 4, (n_mis, n_viol)
+    codes, flat = vq_ref.vq_st_forward(z, cb)
+    assert flat.shape == (2048,) and codes.shape == z.shape
+    assert np.array_equal(codes.reshape(-1, 64), cb[flat])
+    gi, gc = vq_ref.vq_st_backward(gout, ref_idx.reshape(-1), cb.shape)
+    assert bool(g[tag + '/grad_inputs_equal_gout']) and np.array_equal(gi, gout)
+    ref_gc = g[tag + '/grad_codebook']
+    assert np.abs(gc - ref_gc).max() <= 1e-5 * np.abs(ref_gc).max()
+
+
+def test_vq_ties_lowest_index(golden_dir):
+    g = _load(golden_dir, 'vq_c1.npz')
+    rng = np.random.RandomState(int(g['ties/seed']))
+    cb = rng.standard_normal((8, 4)).astype(np.float32)
+    cb[5] = cb[2]
+    cb[7] = cb[0]
+    z = np.concatenate([cb, rng.standard_normal((8, 4)).astype(np.float32)], 0)
+    idx = vq_ref.vq_indices(z, cb)
+    assert np.array_equal(idx, g['ties/indices'].astype(np.int64))
+    assert idx[5] == 2 and idx[7] == 0
+    assert bool(g['vq_backward_raises'])
+
+
+@pytest.mark.parametrize('tag,codebook', [('spread_t32', 'spread'), ('init_t30', 'init')])
+@pytest.mark.parametrize('dtype,rtol', [(torch.float64, 2e-6), (torch.float32, 1e-4)])
+def test_train_step_against_reference(golden_dir, tag, codebook, dtype, rtol):
+    """fwd/bwd of the oracle vs the reference modules evaluated in fp64 (fixture of record)."""
+    g = _load(golden_dir, 'vqvae_step_%s.npz' % tag)
+    input_dim, dim, k, batch, frames, seed, steps = [int(v) for v in g['meta']]
+    p, b = R.make_state(input_dim, dim, k, seed, codebook=codebook, dtype=dtype)
+    mel = R.make_mel(batch, 80, frames, seed + 100, dtype=dtype)
+    ref_idx = torch.from_numpy(g['indices'].astype(np.int64))
+    r = R.step_grads(p, b, mel, beta=1.0)
+    n_mis, n_viol = vq_ref.index_parity(
+        r['indices'].numpy(), ref_idx.numpy(),
+        r['z_e_x'].permute(0, 2, 3, 1).contiguous().numpy(), p['codebook.embedding.weight'].numpy())
+    assert n_viol == 0
+    if n_mis:   # re-run teacher-forced so the remaining comparisons are apples to apples
+        r = R.step_grads(p, b, mel, beta=1.0, indices=ref_idx)
+    assert r['x_tilde'].shape == g['x_tilde'].shape
+    for name in ('x_tilde', 'z_e_x'):
+        ref = g[name].astype(np.float64)
+        err = np.linalg.norm(r[name].double().numpy() - ref) / np.linalg.norm(ref)
+        assert err < max(rtol, 1e-6), (name, err)
+    got = np.array([r['loss_recons'].item(), r['loss_vq'].item(), r['loss_commit'].item(), r['loss'].item()])
+    assert np.allclose(got, g['losses'], rtol=max(rtol, 1e-6))
+    for name in p:
+        _check_summary(g, 'grad/' + name, r['grads'][name], rtol=rtol,
+                       atol=1e-9 if dtype == torch.float64 else 1e-6)
+    for name in R.bn_names():
+        for s in ('running_mean', 'running_var'):
+            ref = g['buf1/%s.%s' % (name, s)]
+            assert np.allclose(r['buffers'][name + '.' + s].double().numpy(), ref, rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize('tag,codebook', [('spread_t32', 'spread'), ('init_t30', 'init')])
+def test_train_loop_against_reference(golden_dir, tag, codebook):
+    """the verbatim fp32 train_vqvae loop: weights after `steps` Adam updates and the printed loss."""
+    g = _load(golden_dir, 'vqvae_step_%s.npz' % tag)
+    input_dim, dim, k, batch, frames, seed, steps = [int(v) for v in g['meta']]
+    p, b = R.make_state(input_dim, dim, k, seed, codebook=codebook)
+    mels = [R.make_mel(batch, 80, frames, seed + 100 + i) for i in range(steps)]
+    p2, b2, log = R.train_steps(p, b, mels, beta=1.0, lr=1e-3)
+    for name in p2:
+        _check_summary(g, 'after/' + name, p2[name], rtol=2e-4, atol=2e-6)
+    for name in R.bn_names():
+        assert int(b2[name + '.num_batches_tracked']) == int(g['bufN/%s.num_batches_tracked' % name]) == steps
+        assert np.allclose(b2[name + '.running_var'].numpy(), g['bufN/%s.running_var' % name], rtol=1e-4, atol=1e-6)
+    printed = [float(v) for v in re.findall(r'Loss: ([0-9.]+)', str(g['train_stdout']))]
+    assert len(printed) == steps
+    for pr, lg in zip(printed, log):
+        assert abs(pr - (lg['loss_recons'].item() + lg['loss_vq'].item())) < 5e-4 * max(1.0, pr)
+
+
+def test_eval_encode_decode_against_reference(golden_dir):
+    g = _load(golden_dir, 'vqvae_eval.npz')
+    input_dim, dim, k, batch, frames, seed = [int(v) for v in g['meta']]
+    p, b = R.make_state(input_dim, dim, k, seed, codebook='spread')
+    rng = np.random.RandomState(seed + 1)
+    for n in R.bn_names():
+        b[n + '.running_mean'] = torch.tensor(0.1 * rng.standard_normal(dim).astype(np.float32))
+        b[n + '.running_var'] = torch.tensor(rng.uniform(0.5, 1.5, dim).astype(np.float32))
+    x = R.make_mel(batch, 80, frames, seed + 2).unsqueeze(1)
+    with torch.no_grad():
+        lat = R.encode(p, b, x)
+        xt = R.decode(p, b, lat)
+    assert lat.dtype == torch.int64 and tuple(lat.shape) == g['latents'].shape
+    assert np.array_equal(lat.numpy(), g['latents'].astype(np.int64))
+    assert tuple(xt.shape) == (1, 1, 80, 4 * (frames // 4))
+    assert np.abs(xt.numpy() - g['x_tilde']).max() < 1e-5
+
+
+def test_ema_extension_self_consistent():
+    """EMA is not in the reference (parity unpinned): only structural checks."""
+    rng = np.random.RandomState(5)
+    z = rng.standard_normal((100, 8)).astype(np.float32)
+    idx = rng.randint(0, 16, size=100)
+    n, m, e, counts, sums = vq_ref.ema_update(z, idx, np.ones(16, np.float32), np.zeros((16, 8), np.float32))
+    assert counts.sum() == 100 and np.allclose(sums.sum(0), z.sum(0), atol=1e-4)
+    assert n.shape == (16,) and m.shape == (16, 8) and e.shape == (16, 8)
