@@ -217,6 +217,24 @@ def gen_eval(ref_models):
     print('vqvae_eval.npz', lat.shape, xt.shape)
 
 
+def gen_adam():
+    """Known-answer vectors for torch.optim.Adam as the reference constructs it (main.py:124)."""
+    out = {}
+    rng = np.random.RandomState(41)
+    shapes = [(64,), (64, 16), (5,)]
+    ps = [torch.nn.Parameter(torch.tensor(rng.standard_normal(s).astype(np.float32))) for s in shapes]
+    opt = torch.optim.Adam(ps, lr=1e-3)
+    for step in range(3):
+        for i, prm in enumerate(ps):
+            scale = [1.0, 1e-4, 1e-8][i]          # includes the eps-dominated regime
+            prm.grad = torch.tensor((scale * rng.standard_normal(prm.shape)).astype(np.float32))
+        opt.step()
+    for i, prm in enumerate(ps):
+        out['p%d' % i] = prm.detach().numpy().copy()
+    np.savez_compressed(os.path.join(OUT, 'adam_kat.npz'), **out)
+    print('adam_kat.npz')
+
+
 def main():
     torch.manual_seed(1)
     torch.set_num_threads(1)          # fixed summation order for the fixtures
@@ -226,6 +244,7 @@ def main():
     gen_step(ref_models, ref_train, ref_test, 'spread_t32', 'spread', 32, 21)
     gen_step(ref_models, ref_train, ref_test, 'init_t30', 'init', 30, 22)
     gen_eval(ref_models)
+    gen_adam()
 
 
 if __name__ == '__main__':
