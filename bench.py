@@ -1,0 +1,241 @@
+#!/usr/bin/env python
+"""Benchmark of the VQ-VAE train step (BASELINE.json config 2) on N B200s of one node.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--mode fp32|bf16]
+
+Prints ONE JSON line (rank 0).  `value` = mel-frames/s of the whole job with inputs resident in HBM;
+`e2e` = the same step driven from pinned HOST buffers (H2D of the mel batch + D2H of the losses inside the
+timed region); `roofline` = the dominant kernel timed alone with CUDA events; `cpu_baseline` = the oracle
+port of the reference's CPU path on this box's host cores (bounded sample).
+`--impl reference` times the reference's CPU algorithm (oracle port; /root/reference is not on the GPU box).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+B_PER_GPU, N_MELS, FRAMES = 32, 80, 256          # BASELINE.json configs[1]
+DIM, K_CODES = 64, 512
+TRAIN_GFLOP = 76.84                              # SURVEY.md §8d, per 32x256 step
+
+
+def peaks():
+    p = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return dict(hbm=d['hbm_gbs'], tf_burst=d['bf16_tflops'], tf_sust=d.get('bf16_tflops_sustained', d['bf16_tflops']),
+                    src='measured')
+    return dict(hbm=6650.0, tf_burst=1590.0, tf_sust=1400.0, src='fallback')
+
+
+class ClockSampler(object):
+    Q = 'clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,' \
+        'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap'
+
+    def __init__(self, index):
+        self.samples, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(['nvidia-smi', '-i', str(index), '--query-gpu=' + self.Q,
+                                          '--format=csv,noheader,nounits', '-lms', '100'],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.samples.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return dict(sm_mhz=None, sm_max_mhz=None, reasons=['nvidia-smi unavailable'])
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        for s in self.samples:
+            f = [x.strip() for x in s.split(',')]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx = float(f[1])
+            except ValueError:
+                continue
+            for n, v in zip(names, f[2:6]):
+                if v.lower().startswith('active'):
+                    reasons.add(n)
+        sm.sort()
+        return dict(sm_mhz=sm[len(sm) // 2] if sm else None, sm_max_mhz=mx, reasons=sorted(reasons), samples=len(sm))
+
+
+def cpu_reference_run(steps, warmup, batch):
+    """The reference's CPU path (oracle port, all host threads) on a bounded sample of the workload."""
+    from oracle import vqvae_ref as R
+    torch.set_num_threads(os.cpu_count() or 1)
+    p, b = R.make_state(1, DIM, K_CODES, 1, codebook='spread')
+    mels = [R.make_mel(batch, N_MELS, FRAMES, 100 + i) for i in range(2)]
+    state = R.adam_init(p)
+    times = []
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        r = R.step_grads(p, b, mels[i % 2], 1.0)
+        p = R.adam_step(p, r['grads'], state, 1e-3)
+        b = r['buffers']
+        dt = time.perf_counter() - t0
+        if i >= warmup:
+            times.append(dt)
+    ms = 1e3 * sum(times) / len(times)
+    return dict(value=batch * FRAMES / (ms / 1e3), ms_per_step=ms, cores=torch.get_num_threads(),
+                sample='%d steps of fwd+bwd+Adam on a %dx%dx%d mel batch (fp32, oracle port of the reference CPU path)'
+                       % (steps, batch, N_MELS, FRAMES))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=20)
+    ap.add_argument('--warmup', type=int, default=5)
+    ap.add_argument('--impl', default='ours')
+    ap.add_argument('--mode', default=os.environ.get('NSG_BENCH_MODE', 'fp32'))
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    args = ap.parse_args()
+    rank = int(os.environ.get('RANK', '0'))
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    config = dict(workload='vqvae_train_step VQVAE(1,64,512) batch %dx%dx%d per GPU, Adam lr 1e-3, beta 1.0'
+                           % (B_PER_GPU, N_MELS, FRAMES), parallelism='dp%d' % world, global_batch=B_PER_GPU * world)
+
+    if args.impl == 'reference':
+        if rank != 0:
+            return
+        steps, warm = max(1, min(args.steps, 3)), max(1, min(args.warmup, 1))
+        r = cpu_reference_run(steps, warm, 8)
+        out = dict(metric='vqvae_train_mel_frames_per_sec', value=r['value'], unit='mel-frames/s', n_gpus=args.gpus,
+                   steps=steps, warmup=warm, ms_per_step=r['ms_per_step'], higher_is_better=True, scaling='weak',
+                   vs_baseline=None, dtype='f32', data='synthetic', config=config, impl='reference',
+                   cpu_baseline=dict(value=r['value'], unit='mel-frames/s', cores=r['cores'], kind='port',
+                                     sample=r['sample']),
+                   e2e=dict(value=r['value'], unit='mel-frames/s', h2d_bytes_per_step=0, d2h_bytes_per_step=0))
+        print(json.dumps(out))
+        return
+
+    import torch.distributed as dist
+    import neural_sound_generation_b200 as nsg
+    from neural_sound_generation_b200 import ops
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+    torch.manual_seed(1)                                           # main.py:43 default
+    model = nsg.VQVAE(1, DIM, K_CODES)
+    with torch.no_grad():
+        model.codebook.embedding.weight.normal_()                  # trained-like codebook
+    model = model.to(dev)
+    if args.mode == 'bf16':
+        model.act_dtype, model.conv_impl, model.vq_mode = torch.bfloat16, 1, 1
+    model.train()
+    opt = nsg.optim.Adam(model, lr=1e-3)
+    opt.grad_scale = 1.0 / world
+    flat = model.flatten_parameters()
+    g = torch.Generator(device='cpu').manual_seed(1 + rank)
+    n_in = 8
+    host = [torch.rand(B_PER_GPU, N_MELS, FRAMES, generator=g).pin_memory() for _ in range(n_in)]
+    devin = [h.to(dev) for h in host]
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)       # > 126 MB L2
+
+    def step(c):
+        opt.zero_grad()
+        losses, _ = model.loss_and_grads(c, beta=1.0)
+        if world > 1:
+            dist.all_reduce(flat['grads'])                          # NCCL over NVLink; averaged via grad_scale
+        opt.step()
+        return losses
+
+    def sync():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        evs = []
+        for i in range(steps):
+            flush.zero_()
+            s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s.record()
+            fn(i)
+            e.record()
+            evs.append((s, e))
+        sync()
+        ms = sum(s.elapsed_time(e) for s, e in evs)
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.item() / steps
+
+    for i in range(max(3, args.warmup)):
+        step(devin[i % n_in])
+    sync()
+    sampler = ClockSampler(local) if rank == 0 else None
+    l0 = ops.launch_count
+    ms = timed(lambda i: step(devin[i % n_in]), args.steps)
+    launches = (ops.launch_count - l0) // args.steps
+    clocks = sampler.stop() if sampler else None
+
+    # end to end: pinned host mel batch -> device, step, losses -> host, every step
+    def e2e_step(i):
+        c = host[i % n_in].to(dev, non_blocking=True)
+        return step(c).tolist()
+    e2e_step(0)
+    sync()
+    ms_e2e = timed(e2e_step, args.steps)
+    frames = B_PER_GPU * FRAMES * world
+    value = frames / (ms / 1e3)
+
+    # dominant kernel alone: 3x3 ResBlock convolution forward (implicit GEMM 40960 x 64 x 576, 3.02 GFLOP)
+    pk = peaks()
+    eng = model.engine()
+    x = torch.randn(B_PER_GPU, 20, 64, DIM, device=dev).to(model.act_dtype)
+    w = dict(model.named_parameters())['encoder.4.block.1.weight'].detach()
+    bias = dict(model.named_parameters())['encoder.4.block.1.bias'].detach()
+    for _ in range(3):
+        eng._conv_fwd(x, w, bias, 3, 1, 1, False, ops.prologue(ops.PRO_RELU))
+    kms = timed(lambda i: eng._conv_fwd(x, w, bias, 3, 1, 1, False, ops.prologue(ops.PRO_RELU)), 20)
+    kflop = 2.0 * x.numel() // DIM * DIM * DIM * 9
+    achieved = kflop / (kms / 1e3) / 1e12
+    roof = dict(bound='tensor', achieved=achieved, peak=pk['tf_burst'], unit='TFLOP/s', frac=achieved / pk['tf_burst'],
+                traffic=None, kernel='conv3x3 64->64 fwd (%s)' % ('tcgen05 bf16' if model.conv_impl else 'CUDA-core fp32'),
+                peak_source=pk['src'], step_frac_of_tensor_peak=TRAIN_GFLOP * world / (ms / 1e3) / 1e3 / (pk['tf_sust'] * world))
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    cpu = None
+    if not args.no_cpu_baseline and world == 1:
+        r = cpu_reference_run(2, 1, 8)
+        cpu = dict(value=r['value'], unit='mel-frames/s', cores=r['cores'], kind='port', sample=r['sample'])
+    out = dict(metric='vqvae_train_mel_frames_per_sec', value=value, unit='mel-frames/s', n_gpus=world,
+               steps=args.steps, warmup=max(3, args.warmup), ms_per_step=ms, higher_is_better=True, scaling='weak',
+               vs_baseline=None, dtype='bf16' if args.mode == 'bf16' else 'f32', data='synthetic',
+               config=dict(config, l2='256 MiB flush between timed steps; 8 rotating input batches',
+                           mode=args.mode, bn='local batch statistics per rank' if world > 1 else 'batch statistics'),
+               e2e=dict(value=frames / (ms_e2e / 1e3), unit='mel-frames/s', ms_per_step=ms_e2e,
+                        h2d_bytes_per_step=B_PER_GPU * N_MELS * FRAMES * 4, d2h_bytes_per_step=24),
+               gpu_launches=launches, clocks=clocks, roofline=roof, cpu_baseline=cpu)
+    print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == '__main__':
+    main()

@@ -1,0 +1,178 @@
+/* nsg_b200 -- C ABI of the B200-native VQ-VAE hot path.
+ *
+ * Drop-in boundary for dendisuhubdy/neural_sound_generation.  The reference has no FFI layer of
+ * its own (its hot path is Python calling ATen); each entry point below names the reference call
+ * site it replaces (paths relative to /root/reference).  INTEGRATION.md shows the ctypes binding a
+ * maintainer adds on the reference side.
+ *
+ * Conventions
+ *  - extern "C", plain pointers and sizes only.  Every pointer is a DEVICE pointer owned by the
+ *    caller (the PyTorch caching allocator in the shipped host layer); the library allocates nothing.
+ *  - every call takes the cudaStream_t to launch on (as void*), never synchronises, never touches
+ *    the host heap after the first call: all entry points are CUDA-graph capturable.
+ *  - return value: 0 = OK, negative = error (NSG_E_*); text via nsg_last_error() (thread local).
+ *  - there is NO CPU path: a missing device, a non-sm_100 device or a null pointer is an error.
+ *  - activations are NHWC ("pixel-major": (N, H, W, C) with C contiguous).  `dtype` selects the
+ *    activation storage type: NSG_F32 or NSG_BF16.  Parameters, statistics, losses and optimiser
+ *    state are always fp32 (sums in fp64).
+ */
+#ifndef NSG_B200_H_
+#define NSG_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NSG_OK 0
+#define NSG_E_INVALID (-1)     /* bad argument / unsupported shape */
+#define NSG_E_CUDA (-2)        /* CUDA runtime error, see nsg_last_error() */
+#define NSG_E_UNSUPPORTED (-3) /* valid request this build cannot serve (e.g. tensor-core path shape) */
+
+#define NSG_F32 0
+#define NSG_BF16 1
+
+/* operand transform applied while an activation tensor is being read ("prologue") */
+#define NSG_PRO_NONE 0
+#define NSG_PRO_RELU 1        /* max(x, 0)                           ResBlock leading ReLU, models.py:149 */
+#define NSG_PRO_AFFINE_RELU 2 /* max(scale[c]*x + shift[c], 0)       BatchNorm2d + ReLU, models.py:151-152,166-167,180-181 */
+#define NSG_PRO_AFFINE 3      /* scale[c]*x + shift[c]               BatchNorm2d alone */
+
+/* gradient mask applied in a dgrad epilogue */
+#define NSG_MASK_NONE 0
+#define NSG_MASK_POS 1    /* keep where mask_src > 0                         (ReLU backward) */
+#define NSG_MASK_AFFINE 2 /* keep where mscale[c]*mask_src + mshift[c] > 0   (BN+ReLU backward) */
+
+/* per-channel statistics accumulated by an epilogue into double stats[2*C] (caller zeroes them) */
+#define NSG_STATS_NONE 0
+#define NSG_STATS_MOMENTS 1 /* sum v, sum v^2            -> BatchNorm forward statistics           */
+#define NSG_STATS_BNBWD 2   /* sum g, sum g*xhat         -> BatchNorm backward reductions           */
+
+const char* nsg_version(void);
+const char* nsg_last_error(void);
+/* 1 when the current device is sm_100 (B200); fills name (<= 127 chars) when not null. */
+int nsg_device_ok(char* name, int name_len);
+
+/* ---------------------------------------------------------------- convolution (models.py:150,153,165,168,179,182)
+ * One implicit-GEMM-over-taps entry point serves nn.Conv2d forward, nn.ConvTranspose2d forward and both
+ * data gradients (ATen convolution_backward in the reference path):
+ *     out[n, oh, ow, co] = bias[co] + sum_{kh,kw,ci} pro(in[n, ih, iw, ci]) * w[kh*k+kw + ci*w_cin_stride + co*w_cout_stride]
+ *   gather 0 ("conv"):        ih = oh*stride - pad + kh                      (Conv2d fwd, ConvTranspose2d dgrad)
+ *   gather 1 ("transposed"):  ih = (oh + pad - kh)/stride when divisible     (ConvTranspose2d fwd, Conv2d dgrad)
+ * out-of-range taps contribute 0 (zero padding is applied AFTER the prologue, as in the reference where the
+ * activation precedes the padded convolution).  `w` is the reference's parameter tensor untouched (OIHW for
+ * Conv2d, (Cin,Cout,KH,KW) for ConvTranspose2d); the two strides say which of its axes the GEMM contracts.
+ * cin / cout are the channel counts of `in` / `out`.
+ */
+typedef struct {
+  int batch, in_h, in_w, cin;   /* tensor being read  */
+  int out_h, out_w, cout;       /* tensor being written (for wgrad: the un-gathered operand Q) */
+  int ksize, stride, pad;
+  int gather;                   /* 0 conv-like, 1 transposed-like */
+  long long w_cin_stride;       /* elements between consecutive GEMM-input channels in w  */
+  long long w_cout_stride;      /* elements between consecutive GEMM-output channels in w */
+  int dtype;                    /* NSG_F32 / NSG_BF16: storage type of in/out/add/mask/xhat tensors */
+} nsg_conv_geom;
+
+typedef struct {
+  int mode;                 /* NSG_PRO_* */
+  const float* scale;       /* [channels] when affine */
+  const float* shift;
+} nsg_prologue;
+
+typedef struct {
+  const float* bias;        /* [cout] or null */
+  const void* add_src;      /* same shape as out, added before masking, or null */
+  int mask_mode;            /* NSG_MASK_* */
+  const void* mask_src;     /* same shape as out */
+  const float* mscale;      /* [cout] for NSG_MASK_AFFINE */
+  const float* mshift;
+  int stats_mode;           /* NSG_STATS_* */
+  double* stats;            /* [2*cout], accumulated (+=) */
+  const void* xhat_src;     /* NSG_STATS_BNBWD: pre-BN tensor h, same shape as out */
+  const float* mean;        /* [cout] */
+  const float* invstd;      /* [cout] */
+  int tanh_out;             /* 1: out = tanh(v)  (models.py:183) */
+} nsg_epilogue;
+
+/* impl: 0 = fp32 CUDA-core kernel (any shape), 1 = tcgen05 bf16 tensor-core kernel (cin = cout = 64, bf16) */
+int nsg_conv_gemm(const nsg_conv_geom* g, const void* in, const float* w, const nsg_prologue* pro,
+                  const nsg_epilogue* epi, void* out, int impl, void* stream);
+
+/* weight gradient:  dw[t + a*w_cin_stride + b*w_cout_stride] += sum_m proP(P[gather0(m, t), a]) * proQ(Q[m, b])
+ * with m over Q's pixels and the conv-like gather into P (geometry fields: in_* = P, out_* = Q).
+ *   Conv2d:           P = x,  Q = dy  (a = ci, b = co)      ConvTranspose2d:  P = dy, Q = x  (a = co, b = ci)
+ * dw is ACCUMULATED with float atomics; q_colsum (nullable, [cout]) += sum_m proQ(Q[m, b]) (= dbias for Conv2d). */
+int nsg_conv_wgrad(const nsg_conv_geom* g, const void* p, const nsg_prologue* pro_p, const void* q,
+                   const nsg_prologue* pro_q, float* dw, float* q_colsum, int impl, void* stream);
+
+/* ---------------------------------------------------------------- batch norm (nn.BatchNorm2d, models.py:151,154,166,180) */
+/* stats (sum, sumsq over `count` elements per channel) -> mean, invstd, scale = gamma*invstd,
+ * shift = beta - mean*scale; running stats updated with momentum (unbiased variance), as torch does. */
+int nsg_bn_finalize(const double* stats, int channels, double count, const float* gamma, const float* beta,
+                    float eps, float momentum, float* running_mean, float* running_var,
+                    long long* num_batches_tracked, float* mean, float* invstd, float* scale, float* shift,
+                    void* stream);
+/* eval mode: scale/shift from running statistics */
+int nsg_bn_eval_coeffs(int channels, const float* gamma, const float* beta, const float* running_mean,
+                       const float* running_var, float eps, float* scale, float* shift, void* stream);
+/* y = [relu](scale*h + shift) [+ relu(res)]: ResBlock output  relu(x) + BN(h)  (models.py:158) */
+int nsg_bn_apply(const void* h, const float* scale, const float* shift, const void* res, int res_relu,
+                 int relu_out, void* y, long long pixels, int channels, int dtype, void* stream);
+/* sums for BN backward: stats[c] += sum g, stats[C+c] += sum g*xhat   (g optionally ReLU-masked by bn(h) > 0) */
+int nsg_bn_bwd_reduce(const void* g, const void* h, const float* mean, const float* invstd, const float* scale,
+                      const float* shift, int relu_mask, double* stats, long long pixels, int channels,
+                      int dtype, void* stream);
+/* dh = gamma*invstd*(g - sum_g/M - xhat*sum_gx/M); dgamma += sum_gx; dbeta += sum_g;  dbias_prev += sum dh */
+int nsg_bn_bwd_apply(const void* g, const void* h, const float* mean, const float* invstd, const float* gamma,
+                     const float* scale, const float* shift, int relu_mask, const double* stats, double count,
+                     void* dh, float* dgamma, float* dbeta, long long pixels, int channels, int dtype,
+                     void* stream);
+/* dx = (g1 + g2) * (x > 0)   (ResBlock input gradient: skip + conv path through the in-place ReLU) */
+int nsg_relu_bwd_add(const void* g1, const void* g2, const void* x, void* dx, long long n, int dtype,
+                     void* stream);
+/* out[c] += sum over pixels of g[p, c]   (bias gradients) */
+int nsg_colsum(const void* g, float* out, long long pixels, int channels, int dtype, void* stream);
+
+/* ---------------------------------------------------------------- vector quantisation (vector_quantization.py) */
+/* vq / vq_st forward (vector_quantization.py:6-23, 34-44) fused with the two VQ loss terms' common value
+ * (train.py:131,133).  z (N,D) activations [dtype], codebook (K,D) fp32.
+ *   indices : int64 [N]  argmin_k |z-e_k|^2, lowest index on ties            (required)
+ *   codes   : [N,D] [dtype] = codebook[indices]                              (nullable)
+ *   sqerr   : double[1] += sum (z - e)^2                                     (nullable)
+ * mode 0 = exact fp32 CUDA-core search; 1 = tcgen05 split-bf16 tensor-core search (sm_100a). */
+int nsg_vq_forward(const void* z, const float* codebook, long long n, int k, int d, int dtype, int mode,
+                   long long* indices, void* codes, double* sqerr, void* stream);
+/* index_add_ / codebook gradient (vector_quantization.py:58-61; autograd of models.py:137-138) and the EMA
+ * extension's statistics: table[idx[n], :] += alpha * (rows[n,:] - (sub ? sub[n,:] : 0)); counts[idx[n]] += 1. */
+int nsg_scatter_add(const void* rows, const void* sub, const long long* indices, long long n, int k, int d,
+                    float alpha, float* table, float* counts, int dtype, void* stream);
+/* out[n,:] = table[indices[n],:]: nn.Embedding lookup / index_select (models.py:137-138, 194); out-of-range -> 0 */
+int nsg_gather_rows(const float* table, const long long* indices, long long n, int k, int d, void* out, int dtype,
+                    void* stream);
+/* encoder-side gradient at the bottleneck: dz = g_st + coef*(z - zq)   (vq_st backward clone + commitment term);
+ * g_st and zq are nullable (treated as 0). */
+int nsg_vq_backward_inputs(const void* g_st, const void* z, const void* zq, float coef, void* dz, long long n,
+                           int dtype, void* stream);
+
+/* ---------------------------------------------------------------- losses (train.py:118-134) */
+/* recon = mean over (B,H,W) of (pad(x_tilde) - c)^2 where x_tilde has width wt <= w and is zero padded;
+ * loss_sum[0] += sum of squares;  dpre (nullable) = d loss_recons / d (pre-tanh), i.e.
+ * 2*(x_tilde - c)/(B*H*W) * (1 - x_tilde^2), shape (B,H,wt). x_tilde, c, dpre are fp32. */
+int nsg_recon_loss(const float* x_tilde, const float* c, int batch, int h, int w, int wt, double* loss_sum,
+                   float* dpre, void* stream);
+
+/* out = g * (1 - y^2): gradient through the decoder's final nn.Tanh (models.py:183), fp32 */
+int nsg_tanh_bwd(const float* g, const float* y, float* out, long long n, void* stream);
+
+/* ---------------------------------------------------------------- optimiser (torch.optim.Adam, main.py:124) */
+/* one Adam step over a flat fp32 buffer.  step_count is a device scalar (incremented by the kernel grid's
+ * first block AFTER use, so graphs replay correctly).  grad_scale multiplies grads (DP averaging). */
+int nsg_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, long long n, float lr,
+                  float beta1, float beta2, float eps, float grad_scale, long long* step_count, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NSG_B200_H_ */

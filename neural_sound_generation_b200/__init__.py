@@ -1,0 +1,16 @@
+"""neural_sound_generation_b200 -- B200-native (sm_100a) VQ-VAE hot path.
+
+Drop-in for the VQ-VAE path of dendisuhubdy/neural_sound_generation: the modules below keep the
+reference's names and call signatures (``vector_quantization.vq / vq_st``, ``models.VQEmbedding /
+ResBlock / VQVAE / weights_init / to_scalar``, ``train.train_vqvae``, ``test.test_vqvae``) and run on
+hand-written CUDA kernels behind the C ABI in ``include/nsg_b200.h``.  There is no CPU fallback.
+"""
+from . import _cabi  # noqa: F401  (does not load the library until first use)
+from .vector_quantization import vq, vq_st  # noqa: F401
+from .models import VQEmbedding, ResBlock, VQVAE, weights_init, to_scalar  # noqa: F401
+from .train import train_vqvae  # noqa: F401
+from .test import test_vqvae  # noqa: F401
+from . import optim  # noqa: F401
+
+VectorQuantizer = VQEmbedding   # alias for the name BASELINE.json's north_star uses
+__version__ = '0.1'

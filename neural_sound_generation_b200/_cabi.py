@@ -1,0 +1,124 @@
+"""ctypes binding of libnsg_b200.so (C ABI declared in include/nsg_b200.h).
+
+There is no CPU or PyTorch fallback: if the shared library is missing or the
+device is not a B200 the import / first call fails loudly.
+"""
+import ctypes as C
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, 'libnsg_b200.so')
+
+F32, BF16 = 0, 1
+PRO_NONE, PRO_RELU, PRO_AFFINE_RELU, PRO_AFFINE = 0, 1, 2, 3
+MASK_NONE, MASK_POS, MASK_AFFINE = 0, 1, 2
+STATS_NONE, STATS_MOMENTS, STATS_BNBWD = 0, 1, 2
+
+EXPORTS = [
+    'nsg_version', 'nsg_last_error', 'nsg_device_ok', 'nsg_conv_gemm', 'nsg_conv_wgrad', 'nsg_bn_finalize',
+    'nsg_bn_eval_coeffs', 'nsg_bn_apply', 'nsg_bn_bwd_reduce', 'nsg_bn_bwd_apply', 'nsg_relu_bwd_add',
+    'nsg_colsum', 'nsg_vq_forward', 'nsg_scatter_add', 'nsg_vq_backward_inputs', 'nsg_recon_loss',
+    'nsg_adam_step', 'nsg_tanh_bwd', 'nsg_gather_rows',
+]
+
+
+class ConvGeom(C.Structure):
+    _fields_ = [('batch', C.c_int), ('in_h', C.c_int), ('in_w', C.c_int), ('cin', C.c_int),
+                ('out_h', C.c_int), ('out_w', C.c_int), ('cout', C.c_int),
+                ('ksize', C.c_int), ('stride', C.c_int), ('pad', C.c_int), ('gather', C.c_int),
+                ('w_cin_stride', C.c_longlong), ('w_cout_stride', C.c_longlong), ('dtype', C.c_int)]
+
+
+class Prologue(C.Structure):
+    _fields_ = [('mode', C.c_int), ('scale', C.c_void_p), ('shift', C.c_void_p)]
+
+
+class Epilogue(C.Structure):
+    _fields_ = [('bias', C.c_void_p), ('add_src', C.c_void_p), ('mask_mode', C.c_int), ('mask_src', C.c_void_p),
+                ('mscale', C.c_void_p), ('mshift', C.c_void_p), ('stats_mode', C.c_int), ('stats', C.c_void_p),
+                ('xhat_src', C.c_void_p), ('mean', C.c_void_p), ('invstd', C.c_void_p), ('tanh_out', C.c_int)]
+
+
+class NsgError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def load():
+    """Load the shared library (once).  Raises if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            'neural_sound_generation_b200: %s not found. Build it with `python -c "import __graft_entry__ as g; '
+            'g.build()"` or `make -C neural_sound_generation_b200/csrc`. There is no CPU fallback.' % LIB_PATH)
+    lib = C.CDLL(LIB_PATH)
+    vp, i, ll, f, d = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_double
+    lib.nsg_version.restype = C.c_char_p
+    lib.nsg_last_error.restype = C.c_char_p
+    lib.nsg_device_ok.argtypes = [C.c_char_p, i]
+    lib.nsg_conv_gemm.argtypes = [C.POINTER(ConvGeom), vp, vp, C.POINTER(Prologue), C.POINTER(Epilogue), vp, i, vp]
+    lib.nsg_conv_wgrad.argtypes = [C.POINTER(ConvGeom), vp, C.POINTER(Prologue), vp, C.POINTER(Prologue), vp, vp,
+                                   i, vp]
+    lib.nsg_bn_finalize.argtypes = [vp, i, d, vp, vp, f, f, vp, vp, vp, vp, vp, vp, vp, vp]
+    lib.nsg_bn_eval_coeffs.argtypes = [i, vp, vp, vp, vp, f, vp, vp, vp]
+    lib.nsg_bn_apply.argtypes = [vp, vp, vp, vp, i, i, vp, ll, i, i, vp]
+    lib.nsg_bn_bwd_reduce.argtypes = [vp, vp, vp, vp, vp, vp, i, vp, ll, i, i, vp]
+    lib.nsg_bn_bwd_apply.argtypes = [vp, vp, vp, vp, vp, vp, vp, i, vp, d, vp, vp, vp, ll, i, i, vp]
+    lib.nsg_relu_bwd_add.argtypes = [vp, vp, vp, vp, ll, i, vp]
+    lib.nsg_colsum.argtypes = [vp, vp, ll, i, i, vp]
+    lib.nsg_vq_forward.argtypes = [vp, vp, ll, i, i, i, i, vp, vp, vp, vp]
+    lib.nsg_scatter_add.argtypes = [vp, vp, vp, ll, i, i, f, vp, vp, i, vp]
+    lib.nsg_vq_backward_inputs.argtypes = [vp, vp, vp, f, vp, ll, i, vp]
+    lib.nsg_recon_loss.argtypes = [vp, vp, i, i, i, i, vp, vp, vp]
+    lib.nsg_gather_rows.argtypes = [vp, vp, ll, i, i, vp, i, vp]
+    lib.nsg_tanh_bwd.argtypes = [vp, vp, vp, ll, vp]
+    lib.nsg_adam_step.argtypes = [vp, vp, vp, vp, ll, f, f, f, f, f, vp, vp]
+    for name in EXPORTS:
+        fn = getattr(lib, name)
+        if name not in ('nsg_version', 'nsg_last_error'):
+            fn.restype = i
+    _lib = lib
+    return lib
+
+
+def check(rc, what):
+    if rc != 0:
+        raise NsgError('%s failed (%d): %s' % (what, rc, load().nsg_last_error().decode()))
+
+
+_device_checked = False
+
+
+def require_device():
+    """Fail loudly unless a CUDA device of compute capability 10.x is current."""
+    global _device_checked
+    if _device_checked:
+        return
+    if not torch.cuda.is_available():
+        raise NsgError('neural_sound_generation_b200 needs a CUDA device (B200, sm_100a); there is no CPU path')
+    name = C.create_string_buffer(128)
+    if load().nsg_device_ok(name, 128) != 1:
+        raise NsgError(load().nsg_last_error().decode())
+    _device_checked = True
+
+
+def stream_ptr():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+
+
+def dtype_code(t):
+    if t.dtype == torch.float32:
+        return F32
+    if t.dtype == torch.bfloat16:
+        return BF16
+    raise NsgError('unsupported activation dtype %s (float32 / bfloat16 only)' % t.dtype)

@@ -1,0 +1,108 @@
+// C-ABI plumbing: error text, device check, dispatch between the CUDA-core and tcgen05 kernels.
+#include <cstring>
+
+#include "common.cuh"
+
+namespace nsg {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int cuda_fail(cudaError_t e, const char* what) {
+  set_error("%s: CUDA error %d (%s)", what, (int)e, cudaGetErrorString(e));
+  return NSG_E_CUDA;
+}
+
+int num_sms() {
+  static int cached = 0;
+  if (cached == 0) {
+    int dev = 0, n = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess &&
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n > 0)
+      cached = n;
+    else
+      cached = 148;
+  }
+  return cached;
+}
+
+int conv_gemm_simt(const nsg_conv_geom* cg, const void* in, const float* w, const nsg_prologue* pro,
+                   const nsg_epilogue* epi, void* out, cudaStream_t stream);
+int conv_wgrad_simt(const nsg_conv_geom* cg, const void* p, const nsg_prologue* pro_p, const void* q,
+                    const nsg_prologue* pro_q, float* dw, float* q_colsum, cudaStream_t stream);
+int conv_gemm_tc(const nsg_conv_geom* cg, const void* in, const float* w, const nsg_prologue* pro,
+                 const nsg_epilogue* epi, void* out, cudaStream_t stream);
+int conv_wgrad_tc(const nsg_conv_geom* cg, const void* p, const nsg_prologue* pro_p, const void* q,
+                  const nsg_prologue* pro_q, float* dw, float* q_colsum, cudaStream_t stream);
+
+}  // namespace nsg
+
+using namespace nsg;
+
+extern "C" {
+
+const char* nsg_version(void) { return "nsg_b200 0.1 (sm_100a)"; }
+const char* nsg_last_error(void) { return g_err; }
+
+int nsg_device_ok(char* name, int name_len) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) {
+    cuda_fail(e, "cudaGetDevice");
+    return 0;
+  }
+  cudaDeviceProp prop;
+  e = cudaGetDeviceProperties(&prop, dev);
+  if (e != cudaSuccess) {
+    cuda_fail(e, "cudaGetDeviceProperties");
+    return 0;
+  }
+  if (name && name_len > 0) {
+    strncpy(name, prop.name, (size_t)name_len - 1);
+    name[name_len - 1] = 0;
+  }
+  if (prop.major != 10) {
+    set_error("device '%s' is sm_%d%d; this library contains sm_100a code only", prop.name, prop.major, prop.minor);
+    return 0;
+  }
+  return 1;
+}
+
+static int check_geom(const nsg_conv_geom* g) {
+  NSG_REQUIRE(g, "conv: null geometry");
+  NSG_REQUIRE(g->batch > 0 && g->in_h > 0 && g->in_w > 0 && g->cin > 0 && g->out_h > 0 && g->out_w > 0 &&
+                  g->cout > 0,
+              "conv: non-positive dimension");
+  NSG_REQUIRE(g->gather == 0 || g->gather == 1, "conv: gather must be 0 or 1");
+  return NSG_OK;
+}
+
+int nsg_conv_gemm(const nsg_conv_geom* g, const void* in, const float* w, const nsg_prologue* pro,
+                  const nsg_epilogue* epi, void* out, int impl, void* stream) {
+  int rc = check_geom(g);
+  if (rc) return rc;
+  NSG_REQUIRE(in && w && out, "conv_gemm: null pointer");
+  if (impl == 0) return conv_gemm_simt(g, in, w, pro, epi, out, (cudaStream_t)stream);
+  if (impl == 1) return conv_gemm_tc(g, in, w, pro, epi, out, (cudaStream_t)stream);
+  set_error("conv_gemm: unknown impl %d", impl);
+  return NSG_E_INVALID;
+}
+
+int nsg_conv_wgrad(const nsg_conv_geom* g, const void* p, const nsg_prologue* pro_p, const void* q,
+                   const nsg_prologue* pro_q, float* dw, float* q_colsum, int impl, void* stream) {
+  int rc = check_geom(g);
+  if (rc) return rc;
+  NSG_REQUIRE(p && q && dw, "conv_wgrad: null pointer");
+  if (impl == 0) return conv_wgrad_simt(g, p, pro_p, q, pro_q, dw, q_colsum, (cudaStream_t)stream);
+  if (impl == 1) return conv_wgrad_tc(g, p, pro_p, q, pro_q, dw, q_colsum, (cudaStream_t)stream);
+  set_error("conv_wgrad: unknown impl %d", impl);
+  return NSG_E_INVALID;
+}
+
+}  // extern "C"

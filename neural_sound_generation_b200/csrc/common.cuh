@@ -1,0 +1,106 @@
+// Shared helpers for the nsg_b200 kernels (sm_100a only).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <cstdarg>
+#include <cstdio>
+
+#include "../../include/nsg_b200.h"
+
+namespace nsg {
+
+// ---- error plumbing (thread local text, integer codes across the ABI)
+void set_error(const char* fmt, ...);
+int cuda_fail(cudaError_t e, const char* what);
+
+#define NSG_REQUIRE(cond, ...)      \
+  do {                              \
+    if (!(cond)) {                  \
+      nsg::set_error(__VA_ARGS__);  \
+      return NSG_E_INVALID;         \
+    }                               \
+  } while (0)
+
+#define NSG_CHECK_LAUNCH(what)                                   \
+  do {                                                           \
+    cudaError_t e__ = cudaPeekAtLastError();                     \
+    if (e__ != cudaSuccess) return nsg::cuda_fail(e__, what);    \
+  } while (0)
+
+int num_sms();
+
+// ---- activation storage types: float or bf16, always computed in fp32
+template <typename T>
+struct Act;
+template <>
+struct Act<float> {
+  static __device__ __forceinline__ float ld(const float* p) { return __ldg(p); }
+  static __device__ __forceinline__ float4 ld4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
+  static __device__ __forceinline__ void st(float* p, float v) { *p = v; }
+  static __device__ __forceinline__ void st4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
+};
+template <>
+struct Act<__nv_bfloat16> {
+  static __device__ __forceinline__ float ld(const __nv_bfloat16* p) {
+    return __bfloat162float(__ldg(p));
+  }
+  static __device__ __forceinline__ float4 ld4(const __nv_bfloat16* p) {
+    uint2 r = __ldg(reinterpret_cast<const uint2*>(p));
+    float4 v;
+    v.x = __uint_as_float(r.x << 16);
+    v.y = __uint_as_float(r.x & 0xffff0000u);
+    v.z = __uint_as_float(r.y << 16);
+    v.w = __uint_as_float(r.y & 0xffff0000u);
+    return v;
+  }
+  static __device__ __forceinline__ void st(__nv_bfloat16* p, float v) { *p = __float2bfloat16_rn(v); }
+  static __device__ __forceinline__ void st4(__nv_bfloat16* p, float4 v) {
+    __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y);
+    __nv_bfloat162 b = __floats2bfloat162_rn(v.z, v.w);
+    uint2 r;
+    r.x = *reinterpret_cast<uint32_t*>(&a);
+    r.y = *reinterpret_cast<uint32_t*>(&b);
+    *reinterpret_cast<uint2*>(p) = r;
+  }
+};
+
+// prologue transform (NSG_PRO_*) on one value of channel c
+struct Pro {
+  int mode;
+  const float* scale;
+  const float* shift;
+};
+__device__ __forceinline__ float pro_apply(int mode, float x, float sc, float sh) {
+  if (mode == NSG_PRO_RELU) return fmaxf(x, 0.f);
+  if (mode == NSG_PRO_AFFINE_RELU) return fmaxf(fmaf(sc, x, sh), 0.f);
+  if (mode == NSG_PRO_AFFINE) return fmaf(sc, x, sh);
+  return x;
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ double warp_sum_d(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+#define NSG_DISPATCH_DTYPE(dtype, ...)                 \
+  [&]() -> int {                                       \
+    if ((dtype) == NSG_F32) {                          \
+      using T = float;                                 \
+      return __VA_ARGS__();                            \
+    } else if ((dtype) == NSG_BF16) {                  \
+      using T = __nv_bfloat16;                         \
+      return __VA_ARGS__();                            \
+    }                                                  \
+    nsg::set_error("unknown dtype %d", (int)(dtype));  \
+    return NSG_E_INVALID;                              \
+  }()
+
+}  // namespace nsg

@@ -1,0 +1,244 @@
+"""Tensor-level wrappers over the C ABI (one Python function per entry point).
+
+Every function takes CUDA tensors that are already laid out as the ABI wants
+(NHWC activations, fp32 parameters) and launches on the current stream.  No
+function here computes anything in PyTorch.
+"""
+import ctypes as C
+
+import torch
+
+from . import _cabi as A
+from ._cabi import (F32, BF16, PRO_NONE, PRO_RELU, PRO_AFFINE_RELU, PRO_AFFINE, MASK_NONE, MASK_POS,  # noqa: F401
+                    MASK_AFFINE, STATS_NONE, STATS_MOMENTS, STATS_BNBWD)
+
+# number of kernel launches issued through this module (bench.py reports it as gpu_launches)
+launch_count = 0
+
+
+def _cuda(*ts):
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise A.NsgError('nsg_b200 ops need CUDA tensors (got %s); there is no CPU path' % t.device)
+
+
+def _contig(t, what):
+    if t is not None and not t.is_contiguous():
+        raise A.NsgError('%s must be contiguous' % what)
+
+
+def conv_geom(batch, in_h, in_w, cin, out_h, out_w, cout, ksize, stride, pad, gather, w_cin_stride,
+              w_cout_stride, dtype):
+    return A.ConvGeom(batch, in_h, in_w, cin, out_h, out_w, cout, ksize, stride, pad, gather, w_cin_stride,
+                      w_cout_stride, dtype)
+
+
+def prologue(mode=PRO_NONE, scale=None, shift=None):
+    return A.Prologue(mode, A.ptr(scale), A.ptr(shift))
+
+
+def conv_gemm(geom, x, w, out, pro=None, bias=None, add_src=None, mask_mode=MASK_NONE, mask_src=None,
+              mscale=None, mshift=None, stats_mode=STATS_NONE, stats=None, xhat_src=None, mean=None, invstd=None,
+              tanh_out=False, impl=0):
+    global launch_count
+    A.require_device()
+    _cuda(x, w, out, bias, add_src, mask_src, stats, xhat_src)
+    _contig(x, 'conv input')
+    _contig(out, 'conv output')
+    _contig(w, 'conv weight')
+    epi = A.Epilogue(A.ptr(bias), A.ptr(add_src), mask_mode, A.ptr(mask_src), A.ptr(mscale), A.ptr(mshift),
+                     stats_mode, A.ptr(stats), A.ptr(xhat_src), A.ptr(mean), A.ptr(invstd), int(bool(tanh_out)))
+    p = pro if pro is not None else prologue()
+    rc = A.load().nsg_conv_gemm(C.byref(geom), A.ptr(x), A.ptr(w), C.byref(p), C.byref(epi), A.ptr(out), impl,
+                                A.stream_ptr())
+    A.check(rc, 'nsg_conv_gemm')
+    launch_count += (geom.stride * geom.stride) if geom.gather == 1 else 1
+    return out
+
+
+def conv_wgrad(geom, p, q, dw, pro_p=None, pro_q=None, q_colsum=None, impl=0):
+    global launch_count
+    A.require_device()
+    _cuda(p, q, dw, q_colsum)
+    _contig(p, 'wgrad P')
+    _contig(q, 'wgrad Q')
+    _contig(dw, 'wgrad dw')
+    pp = pro_p if pro_p is not None else prologue()
+    pq = pro_q if pro_q is not None else prologue()
+    rc = A.load().nsg_conv_wgrad(C.byref(geom), A.ptr(p), C.byref(pp), A.ptr(q), C.byref(pq), A.ptr(dw),
+                                 A.ptr(q_colsum), impl, A.stream_ptr())
+    A.check(rc, 'nsg_conv_wgrad')
+    launch_count += 1
+
+
+def bn_finalize(stats, count, gamma, beta, eps, momentum, running_mean, running_var, nbt, mean, invstd, scale,
+                shift):
+    global launch_count
+    A.require_device()
+    _cuda(stats, gamma, beta, mean)
+    rc = A.load().nsg_bn_finalize(A.ptr(stats), gamma.numel(), float(count), A.ptr(gamma), A.ptr(beta), eps,
+                                  momentum, A.ptr(running_mean), A.ptr(running_var), A.ptr(nbt), A.ptr(mean),
+                                  A.ptr(invstd), A.ptr(scale), A.ptr(shift), A.stream_ptr())
+    A.check(rc, 'nsg_bn_finalize')
+    launch_count += 1
+
+
+def bn_eval_coeffs(gamma, beta, running_mean, running_var, eps, scale, shift):
+    global launch_count
+    A.require_device()
+    _cuda(gamma, beta, running_mean, running_var, scale, shift)
+    rc = A.load().nsg_bn_eval_coeffs(gamma.numel(), A.ptr(gamma), A.ptr(beta), A.ptr(running_mean),
+                                     A.ptr(running_var), eps, A.ptr(scale), A.ptr(shift), A.stream_ptr())
+    A.check(rc, 'nsg_bn_eval_coeffs')
+    launch_count += 1
+
+
+def bn_apply(h, scale, shift, y, res=None, res_relu=False, relu_out=False):
+    global launch_count
+    A.require_device()
+    _cuda(h, scale, shift, y, res)
+    c = h.shape[-1]
+    rc = A.load().nsg_bn_apply(A.ptr(h), A.ptr(scale), A.ptr(shift), A.ptr(res), int(res_relu), int(relu_out),
+                               A.ptr(y), h.numel() // c, c, A.dtype_code(h), A.stream_ptr())
+    A.check(rc, 'nsg_bn_apply')
+    launch_count += 1
+    return y
+
+
+def bn_bwd_reduce(g, h, mean, invstd, stats, scale=None, shift=None, relu_mask=False):
+    global launch_count
+    A.require_device()
+    _cuda(g, h, mean, invstd, stats)
+    c = h.shape[-1]
+    rc = A.load().nsg_bn_bwd_reduce(A.ptr(g), A.ptr(h), A.ptr(mean), A.ptr(invstd), A.ptr(scale), A.ptr(shift),
+                                    int(relu_mask), A.ptr(stats), h.numel() // c, c, A.dtype_code(h),
+                                    A.stream_ptr())
+    A.check(rc, 'nsg_bn_bwd_reduce')
+    launch_count += 1
+
+
+def bn_bwd_apply(g, h, mean, invstd, gamma, stats, count, dh, dgamma=None, dbeta=None, scale=None, shift=None,
+                 relu_mask=False):
+    global launch_count
+    A.require_device()
+    _cuda(g, h, mean, invstd, gamma, stats, dh)
+    c = h.shape[-1]
+    rc = A.load().nsg_bn_bwd_apply(A.ptr(g), A.ptr(h), A.ptr(mean), A.ptr(invstd), A.ptr(gamma), A.ptr(scale),
+                                   A.ptr(shift), int(relu_mask), A.ptr(stats), float(count), A.ptr(dh),
+                                   A.ptr(dgamma), A.ptr(dbeta), h.numel() // c, c, A.dtype_code(h),
+                                   A.stream_ptr())
+    A.check(rc, 'nsg_bn_bwd_apply')
+    launch_count += 1
+    return dh
+
+
+def relu_bwd_add(g1, g2, x, dx):
+    global launch_count
+    A.require_device()
+    _cuda(g1, g2, x, dx)
+    rc = A.load().nsg_relu_bwd_add(A.ptr(g1), A.ptr(g2), A.ptr(x), A.ptr(dx), x.numel(), A.dtype_code(x),
+                                   A.stream_ptr())
+    A.check(rc, 'nsg_relu_bwd_add')
+    launch_count += 1
+    return dx
+
+
+def colsum(g, out):
+    global launch_count
+    A.require_device()
+    _cuda(g, out)
+    c = g.shape[-1]
+    rc = A.load().nsg_colsum(A.ptr(g), A.ptr(out), g.numel() // c, c, A.dtype_code(g), A.stream_ptr())
+    A.check(rc, 'nsg_colsum')
+    launch_count += 1
+
+
+def vq_forward(z, codebook, indices, codes=None, sqerr=None, mode=0):
+    """z (..., D) contiguous activations; codebook (K, D) fp32; indices int64 (N,)."""
+    global launch_count
+    A.require_device()
+    _cuda(z, codebook, indices, codes, sqerr)
+    _contig(z, 'vq input')
+    _contig(codebook, 'codebook')
+    k, d = codebook.shape
+    n = z.numel() // d
+    if codebook.dtype != torch.float32:
+        raise A.NsgError('codebook must be float32')
+    rc = A.load().nsg_vq_forward(A.ptr(z), A.ptr(codebook), n, k, d, A.dtype_code(z), mode, A.ptr(indices),
+                                 A.ptr(codes), A.ptr(sqerr), A.stream_ptr())
+    A.check(rc, 'nsg_vq_forward')
+    launch_count += 1
+
+
+def scatter_add(rows, indices, table, alpha=1.0, sub=None, counts=None):
+    global launch_count
+    A.require_device()
+    _cuda(rows, indices, table, sub, counts)
+    _contig(rows, 'scatter rows')
+    k, d = table.shape
+    n = rows.numel() // d
+    rc = A.load().nsg_scatter_add(A.ptr(rows), A.ptr(sub), A.ptr(indices), n, k, d, float(alpha), A.ptr(table),
+                                  A.ptr(counts), A.dtype_code(rows), A.stream_ptr())
+    A.check(rc, 'nsg_scatter_add')
+    launch_count += 1
+
+
+def vq_backward_inputs(g_st, z, zq, coef, dz):
+    global launch_count
+    A.require_device()
+    _cuda(g_st, z, zq, dz)
+    rc = A.load().nsg_vq_backward_inputs(A.ptr(g_st), A.ptr(z), A.ptr(zq), float(coef), A.ptr(dz), z.numel(),
+                                         A.dtype_code(z), A.stream_ptr())
+    A.check(rc, 'nsg_vq_backward_inputs')
+    launch_count += 1
+    return dz
+
+
+def recon_loss(x_tilde, c, loss_sum, dpre=None):
+    """x_tilde (B, H, Wt) fp32, c (B, H, W) fp32, W >= Wt (right zero pad, train.py:118-120)."""
+    global launch_count
+    A.require_device()
+    _cuda(x_tilde, c, loss_sum, dpre)
+    _contig(x_tilde, 'x_tilde')
+    _contig(c, 'target mel')
+    b, h, w = c.shape
+    wt = x_tilde.shape[-1]
+    rc = A.load().nsg_recon_loss(A.ptr(x_tilde), A.ptr(c), b, h, w, wt, A.ptr(loss_sum), A.ptr(dpre),
+                                 A.stream_ptr())
+    A.check(rc, 'nsg_recon_loss')
+    launch_count += 1
+
+
+def adam_step(params, grads, exp_avg, exp_avg_sq, step_count, lr, beta1=0.9, beta2=0.999, eps=1e-8,
+              grad_scale=1.0):
+    global launch_count
+    A.require_device()
+    _cuda(params, grads, exp_avg, exp_avg_sq, step_count)
+    rc = A.load().nsg_adam_step(A.ptr(params), A.ptr(grads), A.ptr(exp_avg), A.ptr(exp_avg_sq), params.numel(),
+                                lr, beta1, beta2, eps, grad_scale, A.ptr(step_count), A.stream_ptr())
+    A.check(rc, 'nsg_adam_step')
+    launch_count += 2
+
+
+def tanh_bwd(g, y, out):
+    global launch_count
+    A.require_device()
+    _cuda(g, y, out)
+    rc = A.load().nsg_tanh_bwd(A.ptr(g), A.ptr(y), A.ptr(out), y.numel(), A.stream_ptr())
+    A.check(rc, 'nsg_tanh_bwd')
+    launch_count += 1
+    return out
+
+
+def gather_rows(table, indices, out):
+    """out (N, D) [fp32/bf16] = table (K, D) fp32 rows selected by int64 indices (N,)."""
+    global launch_count
+    A.require_device()
+    _cuda(table, indices, out)
+    _contig(table, 'gather table')
+    k, d = table.shape
+    rc = A.load().nsg_gather_rows(A.ptr(table), A.ptr(indices), indices.numel(), k, d, A.ptr(out),
+                                  A.dtype_code(out), A.stream_ptr())
+    A.check(rc, 'nsg_gather_rows')
+    launch_count += 1
+    return out

@@ -1,0 +1,76 @@
+"""CPU-side checks: the C-ABI library loads and exports every symbol include/nsg_b200.h declares, the
+drop-in modules keep the reference's state_dict layout, and the product path refuses to run without CUDA."""
+import os
+import re
+
+import pytest
+import torch
+
+import neural_sound_generation_b200 as nsg
+from neural_sound_generation_b200 import _cabi
+from oracle import vqvae_ref as R
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_declared_symbol():
+    header = open(os.path.join(ROOT, 'include', 'nsg_b200.h')).read()
+    declared = set(re.findall(r'\b(nsg_[a-z0-9_]+)\s*\(', header))
+    declared -= {'nsg_conv_geom', 'nsg_prologue', 'nsg_epilogue'}
+    lib = _cabi.load()
+    for name in sorted(declared):
+        assert hasattr(lib, name), 'libnsg_b200.so does not export %s' % name
+    assert set(_cabi.EXPORTS) == declared
+    assert b'sm_100a' in lib.nsg_version()
+
+
+def test_state_dict_layout_matches_reference():
+    m = nsg.VQVAE(1, 64, 512)
+    sd = m.state_dict()
+    shapes = R.param_shapes(1, 64, 512)
+    params = dict(m.named_parameters())
+    assert list(params.keys()) == list(shapes.keys())
+    for k, s in shapes.items():
+        assert tuple(params[k].shape) == tuple(s), k
+    for n in R.bn_names():
+        for suffix in ('running_mean', 'running_var', 'num_batches_tracked'):
+            assert n + '.' + suffix in sd
+    assert len(sd) == 45 + 30
+    assert sum(p.numel() for p in m.parameters()) == 331713
+    # checkpoints written from oracle/reference state load strictly
+    p, b = R.make_state(1, 64, 512, 3)
+    full = dict(p)
+    full.update(b)
+    m.load_state_dict(full, strict=True)
+
+
+def test_codebook_init_range_and_conv_init():
+    torch.manual_seed(0)
+    m = nsg.VQVAE(1, 64, 512)
+    w = m.codebook.embedding.weight
+    assert w.abs().max().item() <= 1.0 / 512 + 1e-9          # models.py:125
+    assert m.encoder[0].bias.abs().max().item() == 0.0         # weights_init, models.py:25-32
+    assert m.decoder[3].bias.abs().max().item() == 0.0
+    assert nsg.VectorQuantizer is nsg.VQEmbedding
+
+
+def test_no_cpu_fallback():
+    with pytest.raises(_cabi.NsgError):
+        nsg.vq(torch.zeros(4, 8), torch.zeros(3, 8))
+    with pytest.raises(_cabi.NsgError):
+        nsg.vq_st(torch.zeros(4, 8), torch.zeros(3, 8))
+    if not torch.cuda.is_available():
+        m = nsg.VQVAE(1, 8, 16)
+        with pytest.raises(_cabi.NsgError):
+            m(torch.zeros(1, 1, 8, 8))
+        with pytest.raises(_cabi.NsgError):
+            _cabi.require_device()
+
+
+def test_product_does_not_import_oracle():
+    pkg = os.path.join(ROOT, 'neural_sound_generation_b200')
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith(('.py', '.cu', '.cuh', '.h')):
+                src = open(os.path.join(dirpath, f)).read()
+                assert 'oracle' not in src.replace('oracle of record', ''), os.path.join(dirpath, f)

@@ -1,0 +1,375 @@
+"""Op-level parity of the C-ABI kernels (called through ctypes) against CPU fp64 restatements.
+
+Run on the B200 box: python -m pytest tests -m gpu
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+from helpers import relerr, nhwc, nchw
+
+pytestmark = pytest.mark.gpu
+
+if torch.cuda.is_available():
+    import neural_sound_generation_b200 as nsg
+    from neural_sound_generation_b200 import ops
+    from oracle import vq_ref
+
+
+def _skip_if_tc_missing(fn):
+    """mode=1 (tcgen05) paths raise NSG_E_UNSUPPORTED for shapes/builds they do not cover."""
+    try:
+        return fn()
+    except nsg._cabi.NsgError as e:
+        if '(-3)' in str(e):
+            pytest.skip(str(e))
+        raise
+
+DEV = 'cuda'
+TOL = {torch.float32: 2e-5, torch.bfloat16: 1.5e-2}
+
+
+def _rand(rng, *shape):
+    return torch.tensor(rng.standard_normal(shape).astype(np.float32))
+
+
+def _pro_ref(x, mode, scale, shift):
+    if mode == ops.PRO_RELU:
+        return F.relu(x)
+    if mode == ops.PRO_AFFINE_RELU:
+        return F.relu(x * scale[None, :, None, None] + shift[None, :, None, None])
+    if mode == ops.PRO_AFFINE:
+        return x * scale[None, :, None, None] + shift[None, :, None, None]
+    return x
+
+
+CONV_CASES = [
+    # (cin, cout, k, s, p, transposed, H, W, B, pro)
+    (1, 64, 4, 2, 1, False, 16, 12, 2, 0),
+    (64, 64, 4, 2, 1, False, 12, 10, 2, 2),
+    (64, 64, 3, 1, 1, False, 7, 9, 3, 1),
+    (64, 64, 1, 1, 0, False, 5, 6, 2, 2),
+    (64, 64, 4, 2, 1, True, 5, 7, 2, 1),
+    (64, 1, 4, 2, 1, True, 6, 5, 2, 2),
+    (3, 20, 4, 2, 1, False, 9, 11, 1, 0),      # generic (non-multiple-of-4) channel counts
+    (20, 3, 4, 2, 1, True, 4, 5, 1, 3),
+    (32, 48, 3, 1, 1, False, 6, 6, 1, 0),
+]
+
+
+@pytest.mark.parametrize('case', CONV_CASES)
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
+def test_conv_forward_dgrad_wgrad(case, dtype):
+    cin, cout, k, s, p, transposed, H, W, B, pro = case
+    rng = np.random.RandomState(hash(case) % 2 ** 31)
+    x = _rand(rng, B, cin, H, W)
+    w = _rand(rng, *((cin, cout, k, k) if transposed else (cout, cin, k, k))) * 0.2
+    bias = _rand(rng, cout)
+    scale = 1.0 + 0.2 * _rand(rng, cin)
+    shift = 0.3 * _rand(rng, cin)
+    if dtype == torch.bfloat16:      # both sides see the same (rounded) activations
+        x = x.bfloat16().float()
+    xd = x.double().requires_grad_(True)
+    wd = w.double().requires_grad_(True)
+    xin = _pro_ref(xd, pro, scale.double(), shift.double())
+    if transposed:
+        yref = F.conv_transpose2d(xin, wd, bias.double(), s, p)
+    else:
+        yref = F.conv2d(xin, wd, bias.double(), s, p)
+    OH, OW = yref.shape[2:]
+    eng = nsg.engine.Engine(cin, 64, 8, act_dtype=dtype)
+    xg = nhwc(x).to(DEV).to(dtype)
+    wg, bg = w.to(DEV), bias.to(DEV)
+    prol = ops.prologue(pro, scale.to(DEV), shift.to(DEV)) if pro else None
+    stats = torch.zeros(2 * cout, dtype=torch.float64, device=DEV)
+    y = eng._conv_fwd(xg, wg, bg, k, s, p, transposed, prol, stats=stats)
+    torch.cuda.synchronize()
+    assert tuple(y.shape) == (B, OH, OW, cout)
+    err = relerr(nchw(y.float()), yref)
+    assert err < TOL[dtype], ('fwd', err)
+    # statistics epilogue: sum and sum of squares per output channel (computed before rounding to storage)
+    sref = torch.cat([yref.sum((0, 2, 3)), (yref ** 2).sum((0, 2, 3))])
+    assert relerr(stats, sref) < (1e-4 if dtype == torch.float32 else 2e-2)
+    # dgrad + wgrad against autograd of the fp64 restatement
+    gy = _rand(rng, *yref.shape)
+    if dtype == torch.bfloat16:
+        gy = gy.bfloat16().float()
+    yref.backward(gy.double())
+    # gradient wrt the (post-prologue) conv input
+    xin2 = _pro_ref(x.double(), pro, scale.double(), shift.double()).detach().requires_grad_(True)
+    y2 = (F.conv_transpose2d(xin2, w.double(), None, s, p) if transposed else F.conv2d(xin2, w.double(), None, s, p))
+    y2.backward(gy.double())
+    gyg = nhwc(gy).to(DEV).to(dtype)
+    dx = eng._conv_dgrad(gyg, wg, k, s, p, transposed, (H, W))
+    torch.cuda.synchronize()
+    assert relerr(nchw(dx.float()), xin2.grad) < TOL[dtype], 'dgrad'
+    dw = torch.zeros_like(wg)
+    db = torch.zeros(cout, device=DEV)
+    eng._conv_wgrad(xg, gyg, dw, k, s, p, transposed, prol, dbias=db)
+    torch.cuda.synchronize()
+    assert relerr(dw, wd.grad) < TOL[dtype], 'wgrad'
+    assert relerr(db, gy.double().sum((0, 2, 3))) < TOL[dtype], 'dbias'
+
+
+def test_conv_epilogue_mask_add_bnbwd_stats():
+    rng = np.random.RandomState(7)
+    B, C, H, W = 2, 64, 6, 5
+    gy = _rand(rng, B, C, H, W)
+    w = _rand(rng, C, C, 3, 3) * 0.1
+    add = _rand(rng, B, C, H, W)
+    h = _rand(rng, B, C, H, W)
+    scale, shift = 1 + 0.2 * _rand(rng, C), 0.3 * _rand(rng, C)
+    mean, invstd = 0.1 * _rand(rng, C), 1 + 0.1 * _rand(rng, C).abs()
+    # reference: dgrad of conv3x3, + add, masked by affine(h) > 0, sums of g and g*xhat
+    xin = torch.zeros(B, C, H, W, dtype=torch.float64, requires_grad=True)
+    F.conv2d(xin, w.double(), None, 1, 1).backward(gy.double())
+    g = xin.grad + add.double()
+    mask = (h.double() * scale.double()[None, :, None, None] + shift.double()[None, :, None, None]) > 0
+    g = g * mask
+    xhat = (h.double() - mean.double()[None, :, None, None]) * invstd.double()[None, :, None, None]
+    sref = torch.cat([g.sum((0, 2, 3)), (g * xhat).sum((0, 2, 3))])
+    eng = nsg.engine.Engine(1, C, 8)
+    stats = torch.zeros(2 * C, dtype=torch.float64, device=DEV)
+    hg = nhwc(h).to(DEV)
+    out = eng._conv_dgrad(nhwc(gy).to(DEV), w.to(DEV), 3, 1, 1, False, (H, W), add_src=nhwc(add).to(DEV),
+                          mask_mode=ops.MASK_AFFINE, mask_src=hg, mscale=scale.to(DEV), mshift=shift.to(DEV),
+                          stats_mode=ops.STATS_BNBWD, stats=stats, xhat_src=hg, mean=mean.to(DEV),
+                          invstd=invstd.to(DEV))
+    torch.cuda.synchronize()
+    assert relerr(nchw(out), g) < 2e-5
+    assert relerr(stats, sref) < 1e-4
+    # MASK_POS
+    out2 = eng._conv_dgrad(nhwc(gy).to(DEV), w.to(DEV), 3, 1, 1, False, (H, W), mask_mode=ops.MASK_POS, mask_src=hg)
+    assert relerr(nchw(out2), xin.grad * (h.double() > 0)) < 2e-5
+
+
+def test_tanh_epilogue_and_recon_loss():
+    rng = np.random.RandomState(8)
+    B, C, H, W = 2, 64, 5, 4
+    x = _rand(rng, B, C, H, W)
+    w = _rand(rng, C, 1, 4, 4) * 0.1
+    b = _rand(rng, 1)
+    eng = nsg.engine.Engine(1, C, 8)
+    y = eng._conv_fwd(nhwc(x).to(DEV), w.to(DEV), b.to(DEV), 4, 2, 1, True, None, tanh_out=True)
+    ref = torch.tanh(F.conv_transpose2d(x.double(), w.double(), b.double(), 2, 1))
+    assert relerr(nchw(y), ref) < 2e-5
+    # reconstruction loss with right zero padding (train.py:118-129) and its gradient through tanh
+    Wt, Wc = 2 * W, 2 * W + 3
+    xt = ref[:, 0].float().contiguous()                       # (B, 2H, 2W)
+    c = torch.tensor(rng.uniform(0, 1, (B, 2 * H, Wc)).astype(np.float32))
+    xt64 = xt.double().requires_grad_(True)
+    pre = torch.atanh(xt64.detach().clamp(-0.999999, 0.999999)).requires_grad_(True)
+    loss = F.mse_loss(F.pad(torch.tanh(pre), (0, Wc - Wt)), c.double())
+    loss.backward()
+    sums = torch.zeros(1, dtype=torch.float64, device=DEV)
+    dpre = torch.empty(B, 2 * H, Wt, device=DEV)
+    ops.recon_loss(torch.tanh(pre).detach().float().to(DEV), c.to(DEV), sums, dpre)
+    torch.cuda.synchronize()
+    assert abs(sums.item() / c.numel() - loss.item()) < 1e-6 * max(1.0, loss.item())
+    assert relerr(dpre, pre.grad) < 1e-5
+    g = _rand(rng, B, 2 * H, Wt)
+    out = torch.empty_like(dpre)
+    ops.tanh_bwd(g.to(DEV), xt.to(DEV), out)
+    assert relerr(out, g.double() * (1 - xt.double() ** 2)) < 1e-6
+
+
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize('C', [64, 20, 1])
+def test_batchnorm_kernels(dtype, C):
+    rng = np.random.RandomState(9 + C)
+    B, H, W = 3, 7, 5
+    h = _rand(rng, B, C, H, W) * 1.5 + 0.3
+    res = _rand(rng, B, C, H, W)
+    g = _rand(rng, B, C, H, W)
+    if dtype == torch.bfloat16:
+        h, res, g = h.bfloat16().float(), res.bfloat16().float(), g.bfloat16().float()
+    gamma, beta = 1 + 0.2 * _rand(rng, C), 0.1 * _rand(rng, C)
+    rm, rv = 0.1 * _rand(rng, C), 1 + 0.1 * _rand(rng, C).abs()
+    n = B * H * W
+    hd = h.double().requires_grad_(True)
+    gd, bd = gamma.double().requires_grad_(True), beta.double().requires_grad_(True)
+    rm_ref, rv_ref = rm.double().clone(), rv.double().clone()
+    yref = F.batch_norm(hd, rm_ref, rv_ref, gd, bd, True, 0.1, 1e-5)
+    out_ref = F.relu(res.double()) + yref
+    out_ref.backward(g.double())
+    # forward: stats -> finalize -> apply
+    hg = nhwc(h).to(DEV).to(dtype)
+    stats = torch.cat([h.double().sum((0, 2, 3)), (h.double() ** 2).sum((0, 2, 3))]).to(DEV)
+    coef = torch.empty(4, C, device=DEV)
+    rmg, rvg = rm.to(DEV), rv.to(DEV)
+    nbt = torch.zeros((), dtype=torch.int64, device=DEV)
+    ops.bn_finalize(stats, n, gamma.to(DEV), beta.to(DEV), 1e-5, 0.1, rmg, rvg, nbt, coef[0], coef[1], coef[2], coef[3])
+    y = torch.empty_like(hg)
+    ops.bn_apply(hg, coef[2], coef[3], y, res=nhwc(res).to(DEV).to(dtype), res_relu=True)
+    torch.cuda.synchronize()
+    assert int(nbt) == 1
+    assert relerr(rmg, rm_ref) < 1e-5 and relerr(rvg, rv_ref) < 1e-5
+    assert relerr(nchw(y.float()), out_ref) < TOL[dtype]
+    # backward: reduce -> apply
+    bst = torch.zeros(2 * C, dtype=torch.float64, device=DEV)
+    gg = nhwc(g).to(DEV).to(dtype)
+    ops.bn_bwd_reduce(gg, hg, coef[0], coef[1], bst)
+    dh = torch.empty_like(hg)
+    dgam, dbet = torch.zeros(C, device=DEV), torch.zeros(C, device=DEV)
+    ops.bn_bwd_apply(gg, hg, coef[0], coef[1], gamma.to(DEV), bst, n, dh, dgamma=dgam, dbeta=dbet)
+    torch.cuda.synchronize()
+    assert relerr(nchw(dh.float()), hd.grad) < (2e-4 if dtype == torch.float32 else 3e-2)
+    assert relerr(dgam, gd.grad) < 1e-4 and relerr(dbet, bd.grad) < 1e-4
+    # eval coefficients, relu mask variant, colsum, relu_bwd_add
+    sc, sh = torch.empty(C, device=DEV), torch.empty(C, device=DEV)
+    ops.bn_eval_coeffs(gamma.to(DEV), beta.to(DEV), rm.to(DEV), rv.to(DEV), 1e-5, sc, sh)
+    isd = 1 / torch.sqrt(rv.double() + 1e-5)
+    assert relerr(sc, gamma.double() * isd) < 1e-6 and relerr(sh, beta.double() - rm.double() * gamma.double() * isd) < 1e-5
+    cs = torch.zeros(C, device=DEV)
+    ops.colsum(gg, cs)
+    assert relerr(cs, g.double().sum((0, 2, 3))) < 1e-5
+    dx = torch.empty_like(hg)
+    ops.relu_bwd_add(gg, hg, nhwc(res).to(DEV).to(dtype), dx)
+    assert relerr(nchw(dx.float()), (g.double() + h.double()) * (res.double() > 0)) < TOL[dtype]
+    bst2 = torch.zeros(2 * C, dtype=torch.float64, device=DEV)
+    ops.bn_bwd_reduce(gg, hg, coef[0], coef[1], bst2, scale=coef[2], shift=coef[3], relu_mask=True)
+    m = (yref.detach() > 0).double()
+    xhat = (h.double() - h.double().mean((0, 2, 3), keepdim=True)) / torch.sqrt(
+        h.double().var((0, 2, 3), unbiased=False, keepdim=True) + 1e-5)
+    ref2 = torch.cat([(g.double() * m).sum((0, 2, 3)), (g.double() * m * xhat).sum((0, 2, 3))])
+    assert relerr(bst2, ref2) < (1e-4 if dtype == torch.float32 else 5e-2)
+
+
+# ------------------------------------------------------------------------------------ vector quantisation
+def _vq_case(tag, golden_dir):
+    g = np.load(os.path.join(golden_dir, 'vq_c1.npz'))
+    rng = np.random.RandomState(int(g[tag + '/seed']))
+    z = rng.standard_normal((16, 128, 64)).astype(np.float32)
+    cb = (rng.uniform(-1 / 512, 1 / 512, (512, 64)) if tag == 'init' else rng.standard_normal((512, 64))).astype(np.float32)
+    gout = rng.standard_normal((16, 128, 64)).astype(np.float32)
+    return g, z, cb, gout
+
+
+@pytest.mark.parametrize('tag', ['init', 'spread'])
+@pytest.mark.parametrize('mode', [0, 1])
+def test_vq_c1_golden(golden_dir, tag, mode):
+    """Config C1 against the reference's own outputs (tests/golden/vq_c1.npz)."""
+    g, z, cb, gout = _vq_case(tag, golden_dir)
+    nsg.vector_quantization.DEFAULT_MODE = mode
+    try:
+        zt = torch.tensor(z, device=DEV, requires_grad=True)
+        cbt = torch.tensor(cb, device=DEV, requires_grad=True)
+        idx = _skip_if_tc_missing(lambda: nsg.vq(zt, cbt))
+        assert idx.dtype == torch.int64 and tuple(idx.shape) == (16, 128) and not idx.requires_grad
+        codes, flat = nsg.vq_st(zt, cbt)
+        assert tuple(flat.shape) == (2048,) and codes.shape == zt.shape and torch.equal(idx.view(-1), flat)
+        ref_idx = g[tag + '/indices'].astype(np.int64)
+        n_mis, n_viol = vq_ref.index_parity(idx.cpu().numpy(), ref_idx, z, cb)
+        assert n_viol == 0, (n_mis, n_viol)
+        assert n_mis <= 8
+        assert torch.equal(codes.detach().view(-1, 64), cbt.detach()[flat])       # bit-exact gather
+        codes.backward(torch.tensor(gout, device=DEV))
+        assert torch.equal(zt.grad.cpu(), torch.tensor(gout))                     # straight-through clone
+        if n_mis == 0:
+            ref_gc = g[tag + '/grad_codebook']
+            assert np.abs(cbt.grad.cpu().numpy() - ref_gc).max() <= 1e-5 * np.abs(ref_gc).max()
+        gi, gc = vq_ref.vq_st_backward(gout, flat.cpu().numpy(), cb.shape)
+        assert np.abs(cbt.grad.cpu().numpy() - gc).max() <= 1e-5 * np.abs(gc).max()
+    finally:
+        nsg.vector_quantization.DEFAULT_MODE = 0
+
+
+@pytest.mark.parametrize('mode', [0, 1])
+def test_vq_ties_and_errors(golden_dir, mode):
+    g = np.load(os.path.join(golden_dir, 'vq_c1.npz'))
+    rng = np.random.RandomState(int(g['ties/seed']))
+    cb = rng.standard_normal((8, 4)).astype(np.float32)
+    cb[5] = cb[2]
+    cb[7] = cb[0]
+    z = np.concatenate([cb, rng.standard_normal((8, 4)).astype(np.float32)], 0)
+    nsg.vector_quantization.DEFAULT_MODE = mode
+    try:
+        idx = _skip_if_tc_missing(lambda: nsg.vq(torch.tensor(z, device=DEV), torch.tensor(cb, device=DEV)))
+    finally:
+        nsg.vector_quantization.DEFAULT_MODE = 0
+    assert np.array_equal(idx.cpu().numpy(), g['ties/indices'].astype(np.int64))
+    with pytest.raises(RuntimeError, match='VectorQuantization'):
+        nsg.vector_quantization.VectorQuantization.backward(None, None)
+    assert str(g['vq_backward_message']).startswith('Trying to call `.grad()`')
+    with pytest.raises(RuntimeError):
+        nsg.vq(torch.zeros(4, 6, device=DEV).t(), torch.zeros(3, 4, device=DEV))   # non-contiguous like .view
+
+
+@pytest.mark.parametrize('n,k,d', [(1, 1, 1), (5, 3, 1), (100, 17, 7), (333, 512, 64), (4096, 1024, 128), (257, 640, 256)])
+@pytest.mark.parametrize('mode', [0, 1])
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
+def test_vq_shapes_vs_oracle(n, k, d, mode, dtype):
+    rng = np.random.RandomState(n + k + d)
+    z = rng.standard_normal((n, d)).astype(np.float32)
+    cb = rng.standard_normal((k, d)).astype(np.float32)
+    zt = torch.tensor(z, device=DEV).to(dtype)
+    z_used = zt.float().cpu().numpy()
+    idx = torch.empty(n, dtype=torch.int64, device=DEV)
+    codes = torch.empty_like(zt)
+    sq = torch.zeros(1, dtype=torch.float64, device=DEV)
+    _skip_if_tc_missing(lambda: ops.vq_forward(zt, torch.tensor(cb, device=DEV), idx, codes, sq, mode=mode))
+    torch.cuda.synchronize()
+    ref = vq_ref.vq_indices(z_used, cb)
+    n_mis, n_viol = vq_ref.index_parity(idx.cpu().numpy(), ref, z_used, cb)
+    assert n_viol == 0, (n_mis, n_viol)
+    got = idx.cpu().numpy()
+    assert np.array_equal(codes.float().cpu().numpy(), torch.tensor(cb[got]).to(dtype).float().numpy())
+    want = ((z_used.astype(np.float64) - cb[got].astype(np.float64)) ** 2).sum()
+    assert abs(sq.item() - want) <= (1e-5 if dtype == torch.float32 else 1e-5) * want + 1e-9
+
+
+def test_scatter_add_gather_and_bottleneck_grad():
+    rng = np.random.RandomState(21)
+    n, k, d = 1000, 37, 64
+    rows, sub = _rand(rng, n, d), _rand(rng, n, d)
+    idx = torch.tensor(rng.randint(0, k, n))
+    table = torch.zeros(k, d, device=DEV)
+    counts = torch.zeros(k, device=DEV)
+    ops.scatter_add(rows.to(DEV), idx.to(DEV), table, alpha=0.5, sub=sub.to(DEV), counts=counts)
+    ref = torch.zeros(k, d, dtype=torch.float64).index_add_(0, idx, 0.5 * (rows.double() - sub.double()))
+    assert relerr(table, ref) < 1e-5
+    assert torch.equal(counts.cpu(), torch.bincount(idx, minlength=k).float())
+    # EMA extension statistics agree with the (unpinned) oracle restatement
+    _, _, _, c_ref, s_ref = vq_ref.ema_update(rows.numpy(), idx.numpy(), np.ones(k, np.float32), np.zeros((k, d), np.float32))
+    t2 = torch.zeros(k, d, device=DEV)
+    ops.scatter_add(rows.to(DEV), idx.to(DEV), t2)
+    assert relerr(t2, s_ref) < 1e-5 and np.array_equal(counts.cpu().numpy(), c_ref)
+    out = torch.empty(n, d, device=DEV)
+    ops.gather_rows(table, idx.to(DEV), out)
+    assert torch.equal(out, table[idx.to(DEV)])
+    dz = torch.empty(n, d, device=DEV)
+    ops.vq_backward_inputs(rows.to(DEV), sub.to(DEV), out, 0.25, dz)
+    assert relerr(dz, rows.double() + 0.25 * (sub.double() - out.double().cpu())) < 1e-6
+    # odd widths take the scalar path
+    t3 = torch.zeros(5, 3, device=DEV)
+    r3 = _rand(rng, 11, 3)
+    i3 = torch.tensor(rng.randint(0, 5, 11))
+    ops.scatter_add(r3.to(DEV), i3.to(DEV), t3)
+    assert relerr(t3, torch.zeros(5, 3, dtype=torch.float64).index_add_(0, i3, r3.double())) < 1e-6
+
+
+def test_adam_known_answer(golden_dir):
+    """torch.optim.Adam KAT recorded from the reference's optimizer (tests/golden/adam_kat.npz)."""
+    g = np.load(os.path.join(golden_dir, 'adam_kat.npz'))
+    rng = np.random.RandomState(41)
+    shapes = [(64,), (64, 16), (5,)]
+    ps = [rng.standard_normal(s).astype(np.float32) for s in shapes]
+    sizes = [p.size for p in ps]
+    flat = torch.tensor(np.concatenate([p.reshape(-1) for p in ps]), device=DEV)
+    m, v = torch.zeros_like(flat), torch.zeros_like(flat)
+    step = torch.zeros((), dtype=torch.int64, device=DEV)
+    for _ in range(3):
+        gs = []
+        for i in range(3):
+            scale = [1.0, 1e-4, 1e-8][i]
+            gs.append((scale * rng.standard_normal(shapes[i])).astype(np.float32).reshape(-1))
+        ops.adam_step(flat, torch.tensor(np.concatenate(gs), device=DEV), m, v, step, 1e-3)
+    assert int(step) == 3
+    out = flat.cpu().numpy()
+    o = 0
+    for i, s in enumerate(sizes):
+        assert np.allclose(out[o:o + s].reshape(shapes[i]), g['p%d' % i], rtol=2e-6, atol=2e-7), i
+        o += s
