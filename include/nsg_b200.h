@@ -141,9 +141,12 @@ int nsg_colsum(const void* g, float* out, long long pixels, int channels, int dt
  *   indices : int64 [N]  argmin_k |z-e_k|^2, lowest index on ties            (required)
  *   codes   : [N,D] [dtype] = codebook[indices]                              (nullable)
  *   sqerr   : double[1] += sum (z - e)^2                                     (nullable)
- * mode 0 = exact fp32 CUDA-core search; 1 = tcgen05 split-bf16 tensor-core search (sm_100a). */
+ * mode 0 = exact fp32 CUDA-core search; 1 = tcgen05 split-bf16 tensor-core search with exact fp32 re-scoring of
+ * the two best candidates (D == 64, K <= 8192).  mode 1 needs a caller-owned scratch buffer `ws` of
+ * nsg_vq_workspace_bytes(k, d, 1) bytes (negative = shape not served by that mode); mode 0 needs none. */
+long long nsg_vq_workspace_bytes(int k, int d, int mode);
 int nsg_vq_forward(const void* z, const float* codebook, long long n, int k, int d, int dtype, int mode,
-                   long long* indices, void* codes, double* sqerr, void* stream);
+                   long long* indices, void* codes, double* sqerr, void* ws, long long ws_bytes, void* stream);
 /* index_add_ / codebook gradient (vector_quantization.py:58-61; autograd of models.py:137-138) and the EMA
  * extension's statistics: table[idx[n], :] += alpha * (rows[n,:] - (sub ? sub[n,:] : 0)); counts[idx[n]] += 1. */
 int nsg_scatter_add(const void* rows, const void* sub, const long long* indices, long long n, int k, int d,

@@ -20,7 +20,7 @@ EXPORTS = [
     'nsg_version', 'nsg_last_error', 'nsg_device_ok', 'nsg_conv_gemm', 'nsg_conv_wgrad', 'nsg_bn_finalize',
     'nsg_bn_eval_coeffs', 'nsg_bn_apply', 'nsg_bn_bwd_reduce', 'nsg_bn_bwd_apply', 'nsg_relu_bwd_add',
     'nsg_colsum', 'nsg_vq_forward', 'nsg_scatter_add', 'nsg_vq_backward_inputs', 'nsg_recon_loss',
-    'nsg_adam_step', 'nsg_tanh_bwd', 'nsg_gather_rows',
+    'nsg_adam_step', 'nsg_tanh_bwd', 'nsg_gather_rows', 'nsg_vq_workspace_bytes',
 ]
 
 
@@ -72,7 +72,8 @@ def load():
     lib.nsg_bn_bwd_apply.argtypes = [vp, vp, vp, vp, vp, vp, vp, i, vp, d, vp, vp, vp, ll, i, i, vp]
     lib.nsg_relu_bwd_add.argtypes = [vp, vp, vp, vp, ll, i, vp]
     lib.nsg_colsum.argtypes = [vp, vp, ll, i, i, vp]
-    lib.nsg_vq_forward.argtypes = [vp, vp, ll, i, i, i, i, vp, vp, vp, vp]
+    lib.nsg_vq_forward.argtypes = [vp, vp, ll, i, i, i, i, vp, vp, vp, vp, ll, vp]
+    lib.nsg_vq_workspace_bytes.argtypes = [i, i, i]
     lib.nsg_scatter_add.argtypes = [vp, vp, vp, ll, i, i, f, vp, vp, i, vp]
     lib.nsg_vq_backward_inputs.argtypes = [vp, vp, vp, f, vp, ll, i, vp]
     lib.nsg_recon_loss.argtypes = [vp, vp, i, i, i, i, vp, vp, vp]
@@ -82,7 +83,7 @@ def load():
     for name in EXPORTS:
         fn = getattr(lib, name)
         if name not in ('nsg_version', 'nsg_last_error'):
-            fn.restype = i
+            fn.restype = ll if name == 'nsg_vq_workspace_bytes' else i
     _lib = lib
     return lib
 

@@ -11,8 +11,4 @@ int conv_wgrad_tc(const nsg_conv_geom*, const void*, const nsg_prologue*, const 
   set_error("conv_wgrad: tensor-core implementation not built");
   return NSG_E_UNSUPPORTED;
 }
-int vq_forward_tc(const void*, const float*, long long, int, int, int, long long*, void*, double*, cudaStream_t) {
-  set_error("vq_forward: tensor-core implementation not built");
-  return NSG_E_UNSUPPORTED;
-}
 }  // namespace nsg

@@ -218,7 +218,8 @@ int vq_forward_simt(const void* z, const float* codebook, long long n, int k, in
 }
 
 int vq_forward_tc(const void* z, const float* codebook, long long n, int k, int d, int dtype, long long* indices,
-                  void* codes, double* sqerr, cudaStream_t stream);
+                  void* codes, double* sqerr, void* ws, long long ws_bytes, cudaStream_t stream);
+long long vq_tc_workspace_bytes(int k, int d);
 
 }  // namespace nsg
 
@@ -226,13 +227,19 @@ using namespace nsg;
 
 extern "C" {
 
+long long nsg_vq_workspace_bytes(int k, int d, int mode) {
+  if (mode == 0) return 0;
+  return vq_tc_workspace_bytes(k, d);
+}
+
 int nsg_vq_forward(const void* z, const float* codebook, long long n, int k, int d, int dtype, int mode,
-                   long long* indices, void* codes, double* sqerr, void* stream) {
+                   long long* indices, void* codes, double* sqerr, void* ws, long long ws_bytes, void* stream) {
   NSG_REQUIRE(z && codebook && indices, "vq_forward: null pointer");
   NSG_REQUIRE(n >= 0 && k >= 1 && d >= 1, "vq_forward: bad sizes n=%lld k=%d d=%d", n, k, d);
   if (n == 0) return NSG_OK;
   if (mode == 0) return vq_forward_simt(z, codebook, n, k, d, dtype, indices, codes, sqerr, (cudaStream_t)stream);
-  if (mode == 1) return vq_forward_tc(z, codebook, n, k, d, dtype, indices, codes, sqerr, (cudaStream_t)stream);
+  if (mode == 1)
+    return vq_forward_tc(z, codebook, n, k, d, dtype, indices, codes, sqerr, ws, ws_bytes, (cudaStream_t)stream);
   set_error("vq_forward: unknown mode %d", mode);
   return NSG_E_INVALID;
 }

@@ -246,5 +246,6 @@ class Engine(object):
         n = z_e.numel() // z_e.shape[-1]
         idx = torch.empty((n,), dtype=torch.int64, device=z_e.device)
         codes = torch.empty_like(z_e) if want_codes else None
-        ops.vq_forward(z_e, codebook, idx, codes, sqerr, mode=self.vq_mode)
+        mode = self.vq_mode if ops.vq_mode_serves(codebook.shape[0], codebook.shape[1], self.vq_mode) else 0
+        ops.vq_forward(z_e, codebook, idx, codes, sqerr, mode=mode)
         return idx, codes

@@ -153,6 +153,10 @@ def colsum(g, out):
     launch_count += 1
 
 
+def vq_mode_serves(k, d, mode):
+    return mode == 0 or A.load().nsg_vq_workspace_bytes(k, d, mode) >= 0
+
+
 def vq_forward(z, codebook, indices, codes=None, sqerr=None, mode=0):
     """z (..., D) contiguous activations; codebook (K, D) fp32; indices int64 (N,)."""
     global launch_count
@@ -164,10 +168,16 @@ def vq_forward(z, codebook, indices, codes=None, sqerr=None, mode=0):
     n = z.numel() // d
     if codebook.dtype != torch.float32:
         raise A.NsgError('codebook must be float32')
+    ws, ws_bytes = None, 0
+    if mode != 0:
+        ws_bytes = A.load().nsg_vq_workspace_bytes(k, d, mode)
+        if ws_bytes < 0:
+            raise A.NsgError('nsg_vq_forward failed (-3): mode %d does not serve K=%d, D=%d' % (mode, k, d))
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=z.device)
     rc = A.load().nsg_vq_forward(A.ptr(z), A.ptr(codebook), n, k, d, A.dtype_code(z), mode, A.ptr(indices),
-                                 A.ptr(codes), A.ptr(sqerr), A.stream_ptr())
+                                 A.ptr(codes), A.ptr(sqerr), A.ptr(ws), ws_bytes, A.stream_ptr())
     A.check(rc, 'nsg_vq_forward')
-    launch_count += 1
+    launch_count += 1 if mode == 0 else 2
 
 
 def scatter_add(rows, indices, table, alpha=1.0, sub=None, counts=None):

@@ -83,7 +83,8 @@ def test_conv_forward_dgrad_wgrad(case, dtype):
     eng = nsg.engine.Engine(cin, 64, 8, act_dtype=dtype)
     xg = nhwc(x).to(DEV).to(dtype)
     wg, bg = w.to(DEV), bias.to(DEV)
-    prol = ops.prologue(pro, scale.to(DEV), shift.to(DEV)) if pro else None
+    scale_g, shift_g = scale.to(DEV), shift.to(DEV)      # keep alive: the prologue struct holds raw pointers
+    prol = ops.prologue(pro, scale_g, shift_g) if pro else None
     stats = torch.zeros(2 * cout, dtype=torch.float64, device=DEV)
     y = eng._conv_fwd(xg, wg, bg, k, s, p, transposed, prol, stats=stats)
     torch.cuda.synchronize()
