@@ -159,9 +159,12 @@ def gen_step(ref_models, ref_train, ref_test, tag, codebook, frames, seed, batch
         out['z_e_x' + sfx] = z_e_x.detach().float().numpy()
         out['indices' + sfx] = latents.numpy().astype(np.int16)
         out['losses' + sfx] = np.array([lr_.item(), lv.item(), lc.item(), loss.item()], dtype=np.float64)
+        # fp64 gradients are the fixture of record ('grad/'); the reference's own fp32 gradients are kept too
+        # ('grad32/'): a pre-activation that sits within rounding of a ReLU threshold makes the two differ by a
+        # discrete O(1/pixels) step, and an fp32 implementation may land on either side (a tie, like equal distances).
+        for name, prm in model.named_parameters():
+            put(out, ('grad/' if dt == torch.float64 else 'grad32/') + name, prm.grad)
         if dt == torch.float64:
-            for name, prm in model.named_parameters():
-                put(out, 'grad/' + name, prm.grad)
             for name, buf in model.named_buffers():
                 if 'num_batches' not in name:
                     out['buf1/' + name] = buf.detach().float().numpy().copy()
