@@ -129,6 +129,8 @@ def gen_step(ref_models, ref_train, ref_test, tag, codebook, frames, seed, batch
     params, buffers = R.make_state(1, dim, k, seed, codebook=codebook)
     mels = [R.make_mel(batch, 80, frames, seed + 100 + i) for i in range(steps)]
     out['meta'] = np.array([1, dim, k, batch, frames, seed, steps], dtype=np.int64)
+    out['relu_margin'] = np.float64(R.relu_margins(params, buffers, mels[0]))
+    print(tag, 'relu margin', out['relu_margin'])
     # ---- single fwd/bwd (train.py:115-135 evaluated by the reference modules themselves), twice:
     # fp32 as the reference runs, and the same unmodified modules cast to fp64.  The fp64 run is the
     # fixture of record for tensors and gradients: on this tiny batch the reference's own fp32
@@ -244,8 +246,10 @@ def main():
     os.makedirs(OUT, exist_ok=True)
     ref_vq, ref_models, ref_train, ref_test = import_reference()
     gen_vq(ref_vq)
-    gen_step(ref_models, ref_train, ref_test, 'spread_t32', 'spread', 32, 21)
-    gen_step(ref_models, ref_train, ref_test, 'init_t30', 'init', 30, 22)
+    # seeds chosen (search over 200 seeds each) for the largest ReLU margin of the first batch, see
+    # oracle.vqvae_ref.relu_margins: >= 1.8e-5 relative, i.e. ~20x fp32 rounding of a pre-activation
+    gen_step(ref_models, ref_train, ref_test, 'spread_t32', 'spread', 32, 163)
+    gen_step(ref_models, ref_train, ref_test, 'init_t30', 'init', 30, 38)
     gen_eval(ref_models)
     gen_adam()
 
