@@ -96,7 +96,7 @@ typedef struct {
   int tanh_out;             /* 1: out = tanh(v)  (models.py:183) */
 } nsg_epilogue;
 
-/* impl: 0 = fp32 CUDA-core kernel (any shape), 1 = tcgen05 bf16 tensor-core kernel (cin = cout = 64, bf16) */
+/* CUDA-core fp32-accumulate kernel, any shape.  `impl` must be 0 (kept for ABI stability). */
 int nsg_conv_gemm(const nsg_conv_geom* g, const void* in, const float* w, const nsg_prologue* pro,
                   const nsg_epilogue* epi, void* out, int impl, void* stream);
 
@@ -106,6 +106,22 @@ int nsg_conv_gemm(const nsg_conv_geom* g, const void* in, const float* w, const 
  * dw is ACCUMULATED with float atomics; q_colsum (nullable, [cout]) += sum_m proQ(Q[m, b]) (= dbias for Conv2d). */
 int nsg_conv_wgrad(const nsg_conv_geom* g, const void* p, const nsg_prologue* pro_p, const void* q,
                    const nsg_prologue* pro_q, float* dw, float* q_colsum, int impl, void* stream);
+
+/* tcgen05 / TMEM tensor-core kernels for the 64 -> 64 channel layers (cin == cout == 64; other shapes return
+ * NSG_E_UNSUPPORTED).  Same contract as nsg_conv_gemm / nsg_conv_wgrad, except that the forward/dgrad kernel
+ * reads the weights from a caller-owned packed bf16 image (hi + lo halves per tap, UMMA K-major SWIZZLE_128B)
+ * written by nsg_conv_pack_weights for the SAME geometry (the two strides select the GEMM orientation, so a
+ * layer has one image for its forward and one for its data gradient).  `passes` selects operand precision:
+ *   1  bf16 x bf16                      (bf16 mode: what torch.autocast(bfloat16) would feed cuDNN)
+ *   2  activation x (w_hi + w_lo)       (bf16 activations, fp32-faithful weights)
+ *   3  (a_hi + a_lo) x (w_hi + w_lo) without the lo*lo term: fp32 activations to ~2^-16 relative
+ * Accumulation is fp32 in TMEM in every case.  nsg_conv_pack_bytes < 0 = shape not served. */
+long long nsg_conv_pack_bytes(const nsg_conv_geom* g);
+int nsg_conv_pack_weights(const nsg_conv_geom* g, const float* w, void* packed, void* stream);
+int nsg_conv_gemm_tc(const nsg_conv_geom* g, const void* in, const void* packed_w, const nsg_prologue* pro,
+                     const nsg_epilogue* epi, void* out, int passes, void* stream);
+int nsg_conv_wgrad_tc(const nsg_conv_geom* g, const void* p, const nsg_prologue* pro_p, const void* q,
+                      const nsg_prologue* pro_q, float* dw, float* q_colsum, int passes, void* stream);
 
 /* ---------------------------------------------------------------- batch norm (nn.BatchNorm2d, models.py:151,154,166,180) */
 /* stats (sum, sumsq over `count` elements per channel) -> mean, invstd, scale = gamma*invstd,

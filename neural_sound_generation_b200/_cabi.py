@@ -21,6 +21,7 @@ EXPORTS = [
     'nsg_bn_eval_coeffs', 'nsg_bn_apply', 'nsg_bn_bwd_reduce', 'nsg_bn_bwd_apply', 'nsg_relu_bwd_add',
     'nsg_colsum', 'nsg_vq_forward', 'nsg_scatter_add', 'nsg_vq_backward_inputs', 'nsg_recon_loss',
     'nsg_adam_step', 'nsg_tanh_bwd', 'nsg_gather_rows', 'nsg_vq_workspace_bytes',
+    'nsg_conv_pack_bytes', 'nsg_conv_pack_weights', 'nsg_conv_gemm_tc', 'nsg_conv_wgrad_tc',
 ]
 
 
@@ -65,6 +66,11 @@ def load():
     lib.nsg_conv_gemm.argtypes = [C.POINTER(ConvGeom), vp, vp, C.POINTER(Prologue), C.POINTER(Epilogue), vp, i, vp]
     lib.nsg_conv_wgrad.argtypes = [C.POINTER(ConvGeom), vp, C.POINTER(Prologue), vp, C.POINTER(Prologue), vp, vp,
                                    i, vp]
+    lib.nsg_conv_pack_bytes.argtypes = [C.POINTER(ConvGeom)]
+    lib.nsg_conv_pack_weights.argtypes = [C.POINTER(ConvGeom), vp, vp, vp]
+    lib.nsg_conv_gemm_tc.argtypes = [C.POINTER(ConvGeom), vp, vp, C.POINTER(Prologue), C.POINTER(Epilogue), vp, i, vp]
+    lib.nsg_conv_wgrad_tc.argtypes = [C.POINTER(ConvGeom), vp, C.POINTER(Prologue), vp, C.POINTER(Prologue), vp, vp,
+                                      i, vp]
     lib.nsg_bn_finalize.argtypes = [vp, i, d, vp, vp, f, f, vp, vp, vp, vp, vp, vp, vp, vp]
     lib.nsg_bn_eval_coeffs.argtypes = [i, vp, vp, vp, vp, f, vp, vp, vp]
     lib.nsg_bn_apply.argtypes = [vp, vp, vp, vp, i, i, vp, ll, i, i, vp]
@@ -83,7 +89,7 @@ def load():
     for name in EXPORTS:
         fn = getattr(lib, name)
         if name not in ('nsg_version', 'nsg_last_error'):
-            fn.restype = ll if name == 'nsg_vq_workspace_bytes' else i
+            fn.restype = ll if name in ('nsg_vq_workspace_bytes', 'nsg_conv_pack_bytes') else i
     _lib = lib
     return lib
 

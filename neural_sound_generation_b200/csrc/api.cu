@@ -36,10 +36,12 @@ int conv_gemm_simt(const nsg_conv_geom* cg, const void* in, const float* w, cons
                    const nsg_epilogue* epi, void* out, cudaStream_t stream);
 int conv_wgrad_simt(const nsg_conv_geom* cg, const void* p, const nsg_prologue* pro_p, const void* q,
                     const nsg_prologue* pro_q, float* dw, float* q_colsum, cudaStream_t stream);
-int conv_gemm_tc(const nsg_conv_geom* cg, const void* in, const float* w, const nsg_prologue* pro,
-                 const nsg_epilogue* epi, void* out, cudaStream_t stream);
+long long conv_pack_bytes(const nsg_conv_geom* cg);
+int conv_pack_weights(const nsg_conv_geom* cg, const float* w, void* packed, cudaStream_t stream);
+int conv_gemm_tc(const nsg_conv_geom* cg, const void* in, const void* packed, const nsg_prologue* pro,
+                 const nsg_epilogue* epi, void* out, int passes, cudaStream_t stream);
 int conv_wgrad_tc(const nsg_conv_geom* cg, const void* p, const nsg_prologue* pro_p, const void* q,
-                  const nsg_prologue* pro_q, float* dw, float* q_colsum, cudaStream_t stream);
+                  const nsg_prologue* pro_q, float* dw, float* q_colsum, int passes, cudaStream_t stream);
 
 }  // namespace nsg
 
@@ -88,10 +90,33 @@ int nsg_conv_gemm(const nsg_conv_geom* g, const void* in, const float* w, const 
   int rc = check_geom(g);
   if (rc) return rc;
   NSG_REQUIRE(in && w && out, "conv_gemm: null pointer");
-  if (impl == 0) return conv_gemm_simt(g, in, w, pro, epi, out, (cudaStream_t)stream);
-  if (impl == 1) return conv_gemm_tc(g, in, w, pro, epi, out, (cudaStream_t)stream);
-  set_error("conv_gemm: unknown impl %d", impl);
-  return NSG_E_INVALID;
+  NSG_REQUIRE(impl == 0, "conv_gemm: impl must be 0 (the tensor-core kernel is nsg_conv_gemm_tc)");
+  return conv_gemm_simt(g, in, w, pro, epi, out, (cudaStream_t)stream);
+}
+
+long long nsg_conv_pack_bytes(const nsg_conv_geom* g) { return g ? conv_pack_bytes(g) : -1; }
+
+int nsg_conv_pack_weights(const nsg_conv_geom* g, const float* w, void* packed, void* stream) {
+  int rc = check_geom(g);
+  if (rc) return rc;
+  NSG_REQUIRE(w && packed, "conv_pack_weights: null pointer");
+  return conv_pack_weights(g, w, packed, (cudaStream_t)stream);
+}
+
+int nsg_conv_gemm_tc(const nsg_conv_geom* g, const void* in, const void* packed_w, const nsg_prologue* pro,
+                     const nsg_epilogue* epi, void* out, int passes, void* stream) {
+  int rc = check_geom(g);
+  if (rc) return rc;
+  NSG_REQUIRE(in && packed_w && out, "conv_gemm_tc: null pointer");
+  return conv_gemm_tc(g, in, packed_w, pro, epi, out, passes, (cudaStream_t)stream);
+}
+
+int nsg_conv_wgrad_tc(const nsg_conv_geom* g, const void* p, const nsg_prologue* pro_p, const void* q,
+                      const nsg_prologue* pro_q, float* dw, float* q_colsum, int passes, void* stream) {
+  int rc = check_geom(g);
+  if (rc) return rc;
+  NSG_REQUIRE(p && q && dw, "conv_wgrad_tc: null pointer");
+  return conv_wgrad_tc(g, p, pro_p, q, pro_q, dw, q_colsum, passes, (cudaStream_t)stream);
 }
 
 int nsg_conv_wgrad(const nsg_conv_geom* g, const void* p, const nsg_prologue* pro_p, const void* q,
@@ -99,10 +124,8 @@ int nsg_conv_wgrad(const nsg_conv_geom* g, const void* p, const nsg_prologue* pr
   int rc = check_geom(g);
   if (rc) return rc;
   NSG_REQUIRE(p && q && dw, "conv_wgrad: null pointer");
-  if (impl == 0) return conv_wgrad_simt(g, p, pro_p, q, pro_q, dw, q_colsum, (cudaStream_t)stream);
-  if (impl == 1) return conv_wgrad_tc(g, p, pro_p, q, pro_q, dw, q_colsum, (cudaStream_t)stream);
-  set_error("conv_wgrad: unknown impl %d", impl);
-  return NSG_E_INVALID;
+  NSG_REQUIRE(impl == 0, "conv_wgrad: impl must be 0 (the tensor-core kernel is nsg_conv_wgrad_tc)");
+  return conv_wgrad_simt(g, p, pro_p, q, pro_q, dw, q_colsum, (cudaStream_t)stream);
 }
 
 }  // extern "C"

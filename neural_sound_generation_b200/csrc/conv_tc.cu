@@ -1,0 +1,446 @@
+// 64-channel convolutions on the 5th-generation tensor cores (tcgen05 + TMEM).
+//
+// tapgemm_tc: out[m, co] = sum_tap sum_ci pro(in[gather(m, tap), ci]) * W_tap[co, ci]  -- Conv2d / ConvTranspose2d
+// forward and both data gradients for cin = cout = 64 (models.py:150,153,168,179 and their ATen backward).
+// One CTA = 128 output pixels (UMMA M = 128, N = 64); every tap is one K = 64 block:
+//   * 4 producer warps gather the 128 input rows of the tap from NHWC global memory (128 B of bf16 or 256 B of
+//     fp32 per row), apply the BatchNorm/ReLU prologue in registers, and store bf16 (hi [+ lo]) into the
+//     K-major SWIZZLE_128B operand image of a ring stage; the tap's packed weight image arrives by a 1-D bulk
+//     async copy on the same mbarrier;
+//   * one MMA thread issues 4 x PASSES tcgen05.mma (K = 16 each) per tap into a 64-column TMEM accumulator and
+//     releases the stage with tcgen05.commit;
+//   * the producer warps then become the epilogue: tcgen05.ld the accumulator row per thread, bias / residual
+//     add / ReLU-mask / per-channel statistics (BatchNorm forward moments or backward reductions), store.
+// PASSES: 1 = bf16 x bf16; 2 = activation x (W_hi + W_lo) (exact products for bf16 activations, fp32 weights);
+// 3 = split activations as well (fp32 activations: ~2^-16 relative, "fp32-accuracy mode" on tensor cores).
+//
+// wgrad_tc: dW_tap[a, b] = sum_m P[gather(m, tap), a] * Q[m, b] with the pixel axis as GEMM K: both operands are
+// used as MN-major SWIZZLE_128B tiles, which is byte-for-byte the pixel-major image the forward kernel builds.
+#include "common.cuh"
+#include "conv_geom.cuh"
+#include "tc_common.cuh"
+
+namespace nsg {
+
+using namespace tc;
+
+constexpr int CT_M = 128;                 // output pixels per CTA
+constexpr int CT_C = 64;                  // channels (cin = cout)
+constexpr uint32_t CT_A_BYTES = CT_M * 128;   // one bf16 A image (128 rows x 128 B)
+constexpr uint32_t CT_B_BYTES = CT_C * 128;   // one bf16 W image (64 rows x 128 B)
+constexpr uint32_t CT_WTAP_BYTES = 2 * CT_B_BYTES;   // packed weights per tap: hi image, lo image
+
+// ---------------------------------------------------------------------------------------------- weight packing
+// w (reference layout, addressed by the two strides) -> per tap t = kh*k + kw: bf16 hi image, bf16 lo image,
+// rows = GEMM output channel, 64 GEMM input channels along K, K-major SWIZZLE_128B.
+__global__ void __launch_bounds__(256)
+conv_pack_kernel(const float* __restrict__ w, int ntaps, long long in_stride, long long out_stride,
+                 uint8_t* __restrict__ packed) {
+  const int gid = blockIdx.x * 256 + threadIdx.x;      // (tap, row, chunk)
+  const int c = gid & 7, r = (gid >> 3) & 63, t = gid >> 9;
+  if (t >= ntaps) return;
+  float hi[8], lo[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const float v = __ldg(w + t + (long long)(c * 8 + i) * in_stride + (long long)r * out_stride);
+    split_bf16(v, hi[i], lo[i]);
+  }
+  uint8_t* dst = packed + (size_t)t * CT_WTAP_BYTES + sw128_offset(r, c);
+  *reinterpret_cast<uint4*>(dst) =
+      make_uint4(pack_bf16(hi[0], hi[1]), pack_bf16(hi[2], hi[3]), pack_bf16(hi[4], hi[5]), pack_bf16(hi[6], hi[7]));
+  *reinterpret_cast<uint4*>(dst + CT_B_BYTES) =
+      make_uint4(pack_bf16(lo[0], lo[1]), pack_bf16(lo[2], lo[3]), pack_bf16(lo[4], lo[5]), pack_bf16(lo[6], lo[7]));
+}
+
+// ---------------------------------------------------------------------------------------------- small helpers
+// 8 consecutive channels of one pixel as floats
+template <typename T>
+__device__ __forceinline__ void ld8(const T* p, float (&v)[8]);
+template <>
+__device__ __forceinline__ void ld8<float>(const float* p, float (&v)[8]) {
+  const float4 a = __ldg(reinterpret_cast<const float4*>(p));
+  const float4 b = __ldg(reinterpret_cast<const float4*>(p + 4));
+  v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+}
+template <>
+__device__ __forceinline__ void ld8<__nv_bfloat16>(const __nv_bfloat16* p, float (&v)[8]) {
+  const uint4 r = __ldg(reinterpret_cast<const uint4*>(p));
+  const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    v[2 * i] = __uint_as_float(w[i] << 16);
+    v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+  }
+}
+template <typename T>
+__device__ __forceinline__ void st8(T* p, const float (&v)[8]);
+template <>
+__device__ __forceinline__ void st8<float>(float* p, const float (&v)[8]) {
+  *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+  *reinterpret_cast<float4*>(p + 4) = make_float4(v[4], v[5], v[6], v[7]);
+}
+template <>
+__device__ __forceinline__ void st8<__nv_bfloat16>(__nv_bfloat16* p, const float (&v)[8]) {
+  *reinterpret_cast<uint4*>(p) =
+      make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
+}
+
+// v[i] of lane l -> returns sum over lanes of v[lane] (a 32x32 transpose-reduce in 31 shuffles); v is destroyed
+__device__ __forceinline__ float warp_transpose_sum(float (&v)[32], int lane) {
+#pragma unroll
+  for (int half = 16; half >= 1; half >>= 1) {
+    const bool up = (lane & half) != 0;
+#pragma unroll
+    for (int i = 0; i < half; ++i) {
+      const float keep = up ? v[i + half] : v[i];
+      const float send = up ? v[i] : v[i + half];
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, half);
+    }
+  }
+  return v[0];
+}
+
+// 32 lanes x 16 consecutive fp32 columns
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+}
+
+// ---------------------------------------------------------------------------------------------- tap GEMM
+template <int PASSES>
+struct TcCfg {
+  static constexpr int A_IMGS = PASSES == 3 ? 2 : 1;
+  static constexpr int B_IMGS = PASSES >= 2 ? 2 : 1;
+  static constexpr uint32_t STAGE_BYTES = A_IMGS * CT_A_BYTES + B_IMGS * CT_B_BYTES;
+  static constexpr int STAGES = PASSES == 1 ? 4 : (PASSES == 2 ? 3 : 2);
+  static constexpr uint32_t B_OFF = A_IMGS * CT_A_BYTES;
+  static constexpr uint32_t TAIL_BYTES = 3 * CT_M * 4 + 7 * CT_C * 4 + 128;
+  static constexpr uint32_t SMEM_BYTES = 1024 + STAGES * STAGE_BYTES + TAIL_BYTES;
+};
+
+template <typename T, int PASSES>
+__global__ void __launch_bounds__(160)
+tapgemm_tc_kernel(const T* __restrict__ in, const uint8_t* __restrict__ wpacked, T* __restrict__ out, Pro pro,
+                  EpiArgs epi, TapGeom g) {
+  using Cfg = TcCfg<PASSES>;
+  constexpr int STAGES = Cfg::STAGES;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* sm = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* tail = sm + STAGES * Cfg::STAGE_BYTES;
+  int* rowN = reinterpret_cast<int*>(tail);
+  int* rowH = rowN + CT_M;
+  int* rowW = rowH + CT_M;
+  float* sPar = reinterpret_cast<float*>(rowW + CT_M);     // [5][64]: bias, mscale, mshift, mean, invstd
+  float* sStat = sPar + 5 * CT_C;                          // [2][64]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sStat + 2 * CT_C);   // full[STAGES], empty[STAGES], acc_full
+  uint64_t* full = bars;
+  uint64_t* empty = bars + STAGES;
+  uint64_t* acc_full = bars + 2 * STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 1);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const long long M = (long long)g.batch * g.sub_h * g.sub_w;
+  const long long m0 = (long long)blockIdx.x * CT_M;
+
+  if (tid < CT_M) {
+    const long long m = m0 + tid;
+    if (m < M) {
+      rowW[tid] = (int)(m % g.sub_w);
+      const long long t = m / g.sub_w;
+      rowH[tid] = (int)(t % g.sub_h);
+      rowN[tid] = (int)(t / g.sub_h);
+    } else {
+      rowN[tid] = -1;
+      rowH[tid] = 0;
+      rowW[tid] = 0;
+    }
+    if (tid < CT_C) {
+      sPar[0 * CT_C + tid] = epi.bias ? __ldg(epi.bias + tid) : 0.f;
+      sPar[1 * CT_C + tid] = epi.mask_mode == NSG_MASK_AFFINE ? __ldg(epi.mscale + tid) : 1.f;
+      sPar[2 * CT_C + tid] = epi.mask_mode == NSG_MASK_AFFINE ? __ldg(epi.mshift + tid) : 0.f;
+      sPar[3 * CT_C + tid] = epi.stats_mode == NSG_STATS_BNBWD ? __ldg(epi.mean + tid) : 0.f;
+      sPar[4 * CT_C + tid] = epi.stats_mode == NSG_STATS_BNBWD ? __ldg(epi.invstd + tid) : 0.f;
+    }
+    sStat[tid] = 0.f;
+  }
+  if (tid == 128) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full[s], CT_M + 1);
+      mbar_init(&empty[s], 1);
+    }
+    mbar_init(acc_full, 1);
+    fence_mbar_init();
+  }
+  if (warp == 4) tmem_alloc<64>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 4) {
+    // ------------------------------------------------------------------ MMA issuer
+    if (lane == 0) {
+      const uint32_t idesc = idesc_bf16(CT_M, CT_C);
+      for (int t = 0; t < g.ntaps; ++t) {
+        const int s = t % STAGES;
+        mbar_wait(&full[s], (uint32_t)((t / STAGES) & 1));
+        tc_fence_after();
+        const uint32_t base = smem_u32(sm + (size_t)s * Cfg::STAGE_BYTES);
+        const uint64_t a_hi = sw128_desc(base);
+        const uint64_t a_lo = sw128_desc(base + CT_A_BYTES);
+        const uint64_t b_hi = sw128_desc(base + Cfg::B_OFF);
+        const uint64_t b_lo = sw128_desc(base + Cfg::B_OFF + CT_B_BYTES);
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks) umma_bf16(tmem_base, a_hi + 2 * ks, b_hi + 2 * ks, idesc, (t | ks) != 0);
+        if (PASSES >= 2) {
+#pragma unroll
+          for (int ks = 0; ks < 4; ++ks) umma_bf16(tmem_base, a_hi + 2 * ks, b_lo + 2 * ks, idesc, 1);
+        }
+        if (PASSES == 3) {
+#pragma unroll
+          for (int ks = 0; ks < 4; ++ks) umma_bf16(tmem_base, a_lo + 2 * ks, b_hi + 2 * ks, idesc, 1);
+        }
+        umma_commit(&empty[s]);
+      }
+      umma_commit(acc_full);
+    }
+  } else {
+    // ------------------------------------------------------------------ producers: one tap per ring stage
+    const int c = tid & 7;            // 16-byte chunk of the 128-byte bf16 row = channels c*8 .. c*8+7
+    const int rbase = tid >> 3;       // rows rbase + 16*j
+    float sc[8], sh[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      sc[i] = pro.mode >= NSG_PRO_AFFINE_RELU ? __ldg(pro.scale + c * 8 + i) : 1.f;
+      sh[i] = pro.mode >= NSG_PRO_AFFINE_RELU ? __ldg(pro.shift + c * 8 + i) : 0.f;
+    }
+    for (int t = 0; t < g.ntaps; ++t) {
+      const int s = t % STAGES;
+      if (t >= STAGES) mbar_wait(&empty[s], (uint32_t)(((t / STAGES) - 1) & 1));
+      uint8_t* stage = sm + (size_t)s * Cfg::STAGE_BYTES;
+      if (tid == 0) {
+        mbar_arrive_expect_tx(&full[s], Cfg::B_IMGS * CT_B_BYTES);
+        bulk_g2s(stage + Cfg::B_OFF, wpacked + (size_t)g.woff[t] * CT_WTAP_BYTES, Cfg::B_IMGS * CT_B_BYTES, &full[s]);
+      }
+      const int dh = g.dh[t], dw = g.dw[t];
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        float v[4][8];
+        bool ok[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int r = rbase + 16 * (half * 4 + j);
+          const int n = rowN[r];
+          const int ih = rowH[r] * g.in_stride + dh;
+          const int iw = rowW[r] * g.in_stride + dw;
+          ok[j] = n >= 0 && ih >= 0 && ih < g.in_h && iw >= 0 && iw < g.in_w;
+          if (ok[j]) {
+            ld8<T>(in + (((long long)n * g.in_h + ih) * g.in_w + iw) * CT_C + c * 8, v[j]);
+          } else {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[j][i] = 0.f;
+          }
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int r = rbase + 16 * (half * 4 + j);
+          float hi[8], lo[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float x = ok[j] ? pro_apply(pro.mode, v[j][i], sc[i], sh[i]) : 0.f;
+            split_bf16(x, hi[i], lo[i]);
+          }
+          const uint32_t off = sw128_offset(r, c);
+          *reinterpret_cast<uint4*>(stage + off) = make_uint4(pack_bf16(hi[0], hi[1]), pack_bf16(hi[2], hi[3]),
+                                                              pack_bf16(hi[4], hi[5]), pack_bf16(hi[6], hi[7]));
+          if (PASSES == 3)
+            *reinterpret_cast<uint4*>(stage + CT_A_BYTES + off) = make_uint4(
+                pack_bf16(lo[0], lo[1]), pack_bf16(lo[2], lo[3]), pack_bf16(lo[4], lo[5]), pack_bf16(lo[6], lo[7]));
+        }
+      }
+      fence_proxy_async_smem();
+      mbar_arrive(&full[s]);
+    }
+
+    // ------------------------------------------------------------------ epilogue: thread = output row
+    mbar_wait(acc_full, 0);
+    tc_fence_after();
+    const int r = tid;
+    const int n = rowN[r];
+    const bool valid = n >= 0;
+    long long o = 0;
+    if (valid) {
+      const int oh = rowH[r] * g.out_stride + g.off_h;
+      const int ow = rowW[r] * g.out_stride + g.off_w;
+      o = (((long long)n * g.full_h + oh) * g.full_w + ow) * CT_C;
+    }
+    const T* add_src = static_cast<const T*>(epi.add_src);
+    const T* mask_src = static_cast<const T*>(epi.mask_src);
+    const T* xhat_src = static_cast<const T*>(epi.xhat_src);
+#pragma unroll 1
+    for (int chunk = 0; chunk < 2; ++chunk) {
+      const int ch0 = chunk * 32;
+      uint32_t acc[32];
+      tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)ch0, acc);
+      tmem_ld_wait();
+      float x[32], y[32];
+#pragma unroll
+      for (int i = 0; i < 32; ++i) x[i] = valid ? __uint_as_float(acc[i]) + sPar[ch0 + i] : 0.f;
+      if (valid && add_src) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          float a[8];
+          ld8<T>(add_src + o + ch0 + q * 8, a);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) x[q * 8 + i] += a[i];
+        }
+      }
+      if (valid && epi.mask_mode != NSG_MASK_NONE) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          float mk[8];
+          ld8<T>(mask_src + o + ch0 + q * 8, mk);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const int ch = ch0 + q * 8 + i;
+            const float mv = epi.mask_mode == NSG_MASK_AFFINE ? fmaf(sPar[CT_C + ch], mk[i], sPar[2 * CT_C + ch]) : mk[i];
+            x[q * 8 + i] = mv > 0.f ? x[q * 8 + i] : 0.f;
+          }
+        }
+      }
+      if (valid) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          float a[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) a[i] = x[q * 8 + i];
+          st8<T>(out + o + ch0 + q * 8, a);
+        }
+      }
+      if (epi.stats_mode != NSG_STATS_NONE) {
+        if (epi.stats_mode == NSG_STATS_MOMENTS) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) y[i] = x[i] * x[i];
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) y[i] = 0.f;
+          if (valid) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              float hx[8];
+              ld8<T>(xhat_src + o + ch0 + q * 8, hx);
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                const int ch = ch0 + q * 8 + i;
+                y[q * 8 + i] = x[q * 8 + i] * ((hx[i] - sPar[3 * CT_C + ch]) * sPar[4 * CT_C + ch]);
+              }
+            }
+          }
+        }
+        const float s1 = warp_transpose_sum(x, lane);
+        const float s2 = warp_transpose_sum(y, lane);
+        atomicAdd(&sStat[ch0 + lane], s1);
+        atomicAdd(&sStat[CT_C + ch0 + lane], s2);
+      }
+    }
+    if (epi.stats_mode != NSG_STATS_NONE) {
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      atomicAdd(epi.stats + tid, (double)sStat[tid]);     // tid < 128 = [sum(64) | second moment(64)]
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 4) tmem_dealloc<64>(tmem_base);
+}
+
+// ---------------------------------------------------------------------------------------------- host side
+static int tc_shape_ok(const nsg_conv_geom* cg, const char* what) {
+  if (cg->cin != CT_C || cg->cout != CT_C) {
+    set_error("%s: the tcgen05 kernels serve cin == cout == 64 (got %d -> %d)", what, cg->cin, cg->cout);
+    return NSG_E_UNSUPPORTED;
+  }
+  NSG_REQUIRE(cg->ksize >= 1 && cg->ksize <= 4, "%s: ksize %d unsupported (1..4)", what, cg->ksize);
+  NSG_REQUIRE(cg->stride >= 1 && cg->stride <= 2, "%s: stride %d unsupported (1..2)", what, cg->stride);
+  return NSG_OK;
+}
+
+long long conv_pack_bytes(const nsg_conv_geom* cg) {
+  if (cg->cin != CT_C || cg->cout != CT_C || cg->ksize < 1 || cg->ksize > 4) return -1;
+  return (long long)cg->ksize * cg->ksize * CT_WTAP_BYTES;
+}
+
+int conv_pack_weights(const nsg_conv_geom* cg, const float* w, void* packed, cudaStream_t stream) {
+  if (int rc = tc_shape_ok(cg, "conv_pack_weights")) return rc;
+  NSG_REQUIRE((reinterpret_cast<uintptr_t>(packed) & 127) == 0, "conv_pack_weights: packed buffer must be 128-byte aligned");
+  const int ntaps = cg->ksize * cg->ksize;
+  conv_pack_kernel<<<ntaps * 2, 256, 0, stream>>>(w, ntaps, cg->w_cin_stride, cg->w_cout_stride,
+                                                   static_cast<uint8_t*>(packed));
+  NSG_CHECK_LAUNCH("conv_pack_kernel");
+  return NSG_OK;
+}
+
+template <typename T, int PASSES>
+static int launch_tapgemm_tc(const TapGeom& g, const void* in, const void* packed, void* out, const Pro& p,
+                             const EpiArgs& e, cudaStream_t stream) {
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t err = cudaFuncSetAttribute(tapgemm_tc_kernel<T, PASSES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           (int)TcCfg<PASSES>::SMEM_BYTES);
+    if (err != cudaSuccess) return cuda_fail(err, "cudaFuncSetAttribute(tapgemm_tc_kernel)");
+    configured = true;
+  }
+  const long long M = (long long)g.batch * g.sub_h * g.sub_w;
+  const unsigned grid = (unsigned)((M + CT_M - 1) / CT_M);
+  tapgemm_tc_kernel<T, PASSES><<<grid, 160, TcCfg<PASSES>::SMEM_BYTES, stream>>>(
+      (const T*)in, (const uint8_t*)packed, (T*)out, p, e, g);
+  NSG_CHECK_LAUNCH("tapgemm_tc_kernel");
+  return NSG_OK;
+}
+
+int conv_gemm_tc(const nsg_conv_geom* cg, const void* in, const void* packed, const nsg_prologue* pro,
+                 const nsg_epilogue* epi, void* out, int passes, cudaStream_t stream) {
+  if (int rc = tc_shape_ok(cg, "conv_gemm_tc")) return rc;
+  NSG_REQUIRE(passes >= 1 && passes <= 3, "conv_gemm_tc: passes must be 1, 2 or 3");
+  NSG_REQUIRE((reinterpret_cast<uintptr_t>(packed) & 127) == 0, "conv_gemm_tc: packed weights must be 128-byte aligned");
+  TapGeom phases[4];
+  const int np = build_phases(cg, phases);
+  Pro p{NSG_PRO_NONE, nullptr, nullptr};
+  if (pro) p = Pro{pro->mode, pro->scale, pro->shift};
+  if (p.mode >= NSG_PRO_AFFINE_RELU) NSG_REQUIRE(p.scale && p.shift, "conv: affine prologue needs scale/shift");
+  EpiArgs e{};
+  if (int rc = make_epi(epi, &e)) return rc;
+  NSG_REQUIRE(!e.tanh_out, "conv_gemm_tc: tanh epilogue is served by the CUDA-core kernel (cout == 1 layer)");
+  if (cg->dtype == NSG_BF16 && passes == 3) passes = 2;     // bf16 activations have no low part
+  for (int i = 0; i < np; ++i) {
+    const TapGeom& g = phases[i];
+    if ((long long)g.batch * g.sub_h * g.sub_w == 0) continue;
+    NSG_REQUIRE(g.ntaps > 0, "conv_gemm_tc: a stride phase without taps (ksize < stride) is not supported");
+    int rc;
+    if (cg->dtype == NSG_F32) {
+      rc = passes == 1 ? launch_tapgemm_tc<float, 1>(g, in, packed, out, p, e, stream)
+           : passes == 2 ? launch_tapgemm_tc<float, 2>(g, in, packed, out, p, e, stream)
+                         : launch_tapgemm_tc<float, 3>(g, in, packed, out, p, e, stream);
+    } else if (cg->dtype == NSG_BF16) {
+      rc = passes == 1 ? launch_tapgemm_tc<__nv_bfloat16, 1>(g, in, packed, out, p, e, stream)
+                       : launch_tapgemm_tc<__nv_bfloat16, 2>(g, in, packed, out, p, e, stream);
+    } else {
+      set_error("unknown dtype %d", cg->dtype);
+      rc = NSG_E_INVALID;
+    }
+    if (rc) return rc;
+  }
+  return NSG_OK;
+}
+
+int conv_wgrad_tc(const nsg_conv_geom*, const void*, const nsg_prologue*, const void*, const nsg_prologue*, float*,
+                  float*, int, cudaStream_t) {
+  set_error("conv_wgrad_tc: not built yet");
+  return NSG_E_UNSUPPORTED;
+}
+
+}  // namespace nsg

@@ -34,18 +34,24 @@ def _out_hw(h, w, k, s, p, transposed):
 
 
 class Engine(object):
-    def __init__(self, input_dim, dim, z_dim, act_dtype=torch.float32, conv_impl=0, vq_mode=0):
+    def __init__(self, input_dim, dim, z_dim, act_dtype=torch.float32, conv_impl=0, vq_mode=0, passes=None,
+                 wgrad_impl=None):
         self.cin0, self.dim, self.k = input_dim, dim, z_dim
         self.act_dtype = act_dtype
         self.conv_impl = conv_impl      # 0 = fp32 CUDA-core kernels, 1 = tcgen05 kernels where shapes allow
+        self.wgrad_impl = 0 if wgrad_impl is None else wgrad_impl   # TODO: follow conv_impl once wgrad_tc lands
         self.vq_mode = vq_mode
         self.dt = ops.F32 if act_dtype == torch.float32 else ops.BF16
+        # operand precision of the tcgen05 convolutions (include/nsg_b200.h): fp32 activations default to the
+        # split-bf16 "fp32-accuracy" mode, bf16 activations to plain bf16 x bf16
+        self.passes = passes if passes is not None else (3 if act_dtype == torch.float32 else 1)
 
     # ------------------------------------------------------------------ helpers
     def _impl(self, cin, cout):
-        if self.conv_impl == 1 and cin == 64 and cout == 64 and self.act_dtype == torch.bfloat16:
-            return 1
-        return 0
+        return 1 if (self.conv_impl == 1 and cin == 64 and cout == 64) else 0
+
+    def _wimpl(self, cin, cout):
+        return 1 if (self.wgrad_impl == 1 and cin == 64 and cout == 64) else 0
 
     def _new(self, *shape, dtype=None, like=None):
         return torch.empty(shape, dtype=dtype or self.act_dtype, device=like.device)
@@ -79,7 +85,7 @@ class Engine(object):
         out = torch.empty((b, oh, ow, cout), dtype=x.dtype, device=x.device)
         g = ops.conv_geom(b, h, wd, cin, oh, ow, cout, k, s, p, 1 if transposed else 0, wci, wco, self._dt(x))
         ops.conv_gemm(g, x, w, out, pro=pro, bias=bias, stats_mode=STATS_MOMENTS if stats is not None else 0,
-                      stats=stats, tanh_out=tanh_out, impl=self._impl(cin, cout))
+                      stats=stats, tanh_out=tanh_out, impl=self._impl(cin, cout), passes=self.passes)
         return out
 
     def _dt(self, t):
@@ -99,7 +105,7 @@ class Engine(object):
             gather = 1
         out = torch.empty((b, ih, iw, cin_f), dtype=dy.dtype, device=dy.device)
         g = ops.conv_geom(b, oh, ow, cdy, ih, iw, cin_f, k, s, p, gather, wci, wco, self._dt(dy))
-        ops.conv_gemm(g, dy, w, out, impl=self._impl(cdy, cin_f), **epi)
+        ops.conv_gemm(g, dy, w, out, impl=self._impl(cdy, cin_f), passes=self.passes, **epi)
         return out
 
     def _conv_wgrad(self, x, dy, dw, k, s, p, transposed, pro_x, dbias=None):
@@ -108,12 +114,12 @@ class Engine(object):
         _, oh, ow, cout = dy.shape
         if transposed:      # dW[ci][co][t]: P = dy (gathered over x pixels), Q = x
             g = ops.conv_geom(b, oh, ow, cout, h, wd, cin, k, s, p, 0, k * k, cout * k * k, self._dt(x))
-            ops.conv_wgrad(g, dy, x, dw, pro_p=None, pro_q=pro_x, q_colsum=None, impl=self._impl(cin, cout))
+            ops.conv_wgrad(g, dy, x, dw, pro_p=None, pro_q=pro_x, q_colsum=None, impl=self._wimpl(cin, cout), passes=self.passes)
             if dbias is not None:
                 ops.colsum(dy, dbias)
         else:               # dW[co][ci][t]: P = x (gathered over dy pixels), Q = dy
             g = ops.conv_geom(b, h, wd, cin, oh, ow, cout, k, s, p, 0, k * k, cin * k * k, self._dt(x))
-            ops.conv_wgrad(g, x, dy, dw, pro_p=pro_x, pro_q=None, q_colsum=dbias, impl=self._impl(cin, cout))
+            ops.conv_wgrad(g, x, dy, dw, pro_p=pro_x, pro_q=None, q_colsum=dbias, impl=self._wimpl(cin, cout), passes=self.passes)
 
     # ------------------------------------------------------------------ ResBlock (models.py:145-158)
     def resblock_fwd(self, ctx, P, Bufs, name, xin):

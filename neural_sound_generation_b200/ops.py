@@ -37,9 +37,26 @@ def prologue(mode=PRO_NONE, scale=None, shift=None):
     return A.Prologue(mode, A.ptr(scale), A.ptr(shift))
 
 
+def conv_pack(geom, w):
+    """Packed bf16 (hi + lo) tensor-core image of conv weight ``w`` for the GEMM orientation in ``geom``."""
+    global launch_count
+    A.require_device()
+    _cuda(w)
+    _contig(w, 'conv weight')
+    nbytes = A.load().nsg_conv_pack_bytes(C.byref(geom))
+    if nbytes < 0:
+        raise A.NsgError('nsg_conv_pack_weights failed (-3): the tcgen05 kernels serve cin == cout == 64')
+    packed = torch.empty(nbytes, dtype=torch.uint8, device=w.device)
+    rc = A.load().nsg_conv_pack_weights(C.byref(geom), A.ptr(w), A.ptr(packed), A.stream_ptr())
+    A.check(rc, 'nsg_conv_pack_weights')
+    launch_count += 1
+    return packed
+
+
 def conv_gemm(geom, x, w, out, pro=None, bias=None, add_src=None, mask_mode=MASK_NONE, mask_src=None,
               mscale=None, mshift=None, stats_mode=STATS_NONE, stats=None, xhat_src=None, mean=None, invstd=None,
-              tanh_out=False, impl=0):
+              tanh_out=False, impl=0, passes=1, packed=None):
+    """impl 0: CUDA-core kernel reading ``w``; impl 1: tcgen05 kernel reading ``packed`` (built from w if None)."""
     global launch_count
     A.require_device()
     _cuda(x, w, out, bias, add_src, mask_src, stats, xhat_src)
@@ -49,14 +66,21 @@ def conv_gemm(geom, x, w, out, pro=None, bias=None, add_src=None, mask_mode=MASK
     epi = A.Epilogue(A.ptr(bias), A.ptr(add_src), mask_mode, A.ptr(mask_src), A.ptr(mscale), A.ptr(mshift),
                      stats_mode, A.ptr(stats), A.ptr(xhat_src), A.ptr(mean), A.ptr(invstd), int(bool(tanh_out)))
     p = pro if pro is not None else prologue()
-    rc = A.load().nsg_conv_gemm(C.byref(geom), A.ptr(x), A.ptr(w), C.byref(p), C.byref(epi), A.ptr(out), impl,
-                                A.stream_ptr())
-    A.check(rc, 'nsg_conv_gemm')
+    if impl == 1:
+        if packed is None:
+            packed = conv_pack(geom, w)
+        rc = A.load().nsg_conv_gemm_tc(C.byref(geom), A.ptr(x), A.ptr(packed), C.byref(p), C.byref(epi), A.ptr(out),
+                                       passes, A.stream_ptr())
+        A.check(rc, 'nsg_conv_gemm_tc')
+    else:
+        rc = A.load().nsg_conv_gemm(C.byref(geom), A.ptr(x), A.ptr(w), C.byref(p), C.byref(epi), A.ptr(out), 0,
+                                    A.stream_ptr())
+        A.check(rc, 'nsg_conv_gemm')
     launch_count += (geom.stride * geom.stride) if geom.gather == 1 else 1
     return out
 
 
-def conv_wgrad(geom, p, q, dw, pro_p=None, pro_q=None, q_colsum=None, impl=0):
+def conv_wgrad(geom, p, q, dw, pro_p=None, pro_q=None, q_colsum=None, impl=0, passes=1):
     global launch_count
     A.require_device()
     _cuda(p, q, dw, q_colsum)
@@ -65,9 +89,14 @@ def conv_wgrad(geom, p, q, dw, pro_p=None, pro_q=None, q_colsum=None, impl=0):
     _contig(dw, 'wgrad dw')
     pp = pro_p if pro_p is not None else prologue()
     pq = pro_q if pro_q is not None else prologue()
-    rc = A.load().nsg_conv_wgrad(C.byref(geom), A.ptr(p), C.byref(pp), A.ptr(q), C.byref(pq), A.ptr(dw),
-                                 A.ptr(q_colsum), impl, A.stream_ptr())
-    A.check(rc, 'nsg_conv_wgrad')
+    if impl == 1:
+        rc = A.load().nsg_conv_wgrad_tc(C.byref(geom), A.ptr(p), C.byref(pp), A.ptr(q), C.byref(pq), A.ptr(dw),
+                                        A.ptr(q_colsum), passes, A.stream_ptr())
+        A.check(rc, 'nsg_conv_wgrad_tc')
+    else:
+        rc = A.load().nsg_conv_wgrad(C.byref(geom), A.ptr(p), C.byref(pp), A.ptr(q), C.byref(pq), A.ptr(dw),
+                                     A.ptr(q_colsum), 0, A.stream_ptr())
+        A.check(rc, 'nsg_conv_wgrad')
     launch_count += 1
 
 

@@ -60,10 +60,17 @@ CONV_CASES = [
 ]
 
 
+TC_TOL = {torch.float32: 5e-5, torch.bfloat16: 1.5e-2}     # tcgen05: split-bf16 (3 passes) / plain bf16 operands
+
+
 @pytest.mark.parametrize('case', CONV_CASES)
 @pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
-def test_conv_forward_dgrad_wgrad(case, dtype):
+@pytest.mark.parametrize('impl', [0, 1])
+def test_conv_forward_dgrad_wgrad(case, dtype, impl):
     cin, cout, k, s, p, transposed, H, W, B, pro = case
+    if impl == 1 and not (cin == 64 and cout == 64):
+        pytest.skip('tcgen05 convolutions serve the 64 -> 64 channel layers')
+    TOL = TC_TOL if impl == 1 else globals()['TOL']
     rng = np.random.RandomState(hash(case) % 2 ** 31)
     x = _rand(rng, B, cin, H, W)
     w = _rand(rng, *((cin, cout, k, k) if transposed else (cout, cin, k, k))) * 0.2
@@ -80,7 +87,7 @@ def test_conv_forward_dgrad_wgrad(case, dtype):
     else:
         yref = F.conv2d(xin, wd, bias.double(), s, p)
     OH, OW = yref.shape[2:]
-    eng = nsg.engine.Engine(cin, 64, 8, act_dtype=dtype)
+    eng = nsg.engine.Engine(cin, 64, 8, act_dtype=dtype, conv_impl=impl)
     xg = nhwc(x).to(DEV).to(dtype)
     wg, bg = w.to(DEV), bias.to(DEV)
     scale_g, shift_g = scale.to(DEV), shift.to(DEV)      # keep alive: the prologue struct holds raw pointers
@@ -115,7 +122,8 @@ def test_conv_forward_dgrad_wgrad(case, dtype):
     assert relerr(db, gy.double().sum((0, 2, 3))) < TOL[dtype], 'dbias'
 
 
-def test_conv_epilogue_mask_add_bnbwd_stats():
+@pytest.mark.parametrize('impl', [0, 1])
+def test_conv_epilogue_mask_add_bnbwd_stats(impl):
     rng = np.random.RandomState(7)
     B, C, H, W = 2, 64, 6, 5
     gy = _rand(rng, B, C, H, W)
@@ -132,7 +140,7 @@ def test_conv_epilogue_mask_add_bnbwd_stats():
     g = g * mask
     xhat = (h.double() - mean.double()[None, :, None, None]) * invstd.double()[None, :, None, None]
     sref = torch.cat([g.sum((0, 2, 3)), (g * xhat).sum((0, 2, 3))])
-    eng = nsg.engine.Engine(1, C, 8)
+    eng = nsg.engine.Engine(1, C, 8, conv_impl=impl)
     stats = torch.zeros(2 * C, dtype=torch.float64, device=DEV)
     hg = nhwc(h).to(DEV)
     out = eng._conv_dgrad(nhwc(gy).to(DEV), w.to(DEV), 3, 1, 1, False, (H, W), add_src=nhwc(add).to(DEV),
@@ -140,11 +148,11 @@ def test_conv_epilogue_mask_add_bnbwd_stats():
                           stats_mode=ops.STATS_BNBWD, stats=stats, xhat_src=hg, mean=mean.to(DEV),
                           invstd=invstd.to(DEV))
     torch.cuda.synchronize()
-    assert relerr(nchw(out), g) < 2e-5
+    assert relerr(nchw(out), g) < (5e-5 if impl else 2e-5)
     assert relerr(stats, sref) < 1e-4
     # MASK_POS
     out2 = eng._conv_dgrad(nhwc(gy).to(DEV), w.to(DEV), 3, 1, 1, False, (H, W), mask_mode=ops.MASK_POS, mask_src=hg)
-    assert relerr(nchw(out2), xin.grad * (h.double() > 0)) < 2e-5
+    assert relerr(nchw(out2), xin.grad * (h.double() > 0)) < (5e-5 if impl else 2e-5)
 
 
 def test_tanh_epilogue_and_recon_loss():
