@@ -437,10 +437,292 @@ int conv_gemm_tc(const nsg_conv_geom* cg, const void* in, const void* packed, co
   return NSG_OK;
 }
 
-int conv_wgrad_tc(const nsg_conv_geom*, const void*, const nsg_prologue*, const void*, const nsg_prologue*, float*,
-                  float*, int, cudaStream_t) {
-  set_error("conv_wgrad_tc: not built yet");
-  return NSG_E_UNSUPPORTED;
+// ---------------------------------------------------------------------------------------------- weight gradient
+// D_pair[a, b] (+)= P_pair^T (128 x pixels) * Q (pixels x 64): pixels are the GEMM K axis, so the pixel-major
+// NHWC tiles are MN-major operands: canonical layout ((8,8,m),(8,k)):((1,8,LBO),(64,SBO)) in elements, i.e. one
+// 128-byte row per pixel, 1024-byte groups of 8 pixels (SBO), and the second 64 channels of a 128-row A operand
+// LBO bytes away -- which is where the NEXT TAP's tile lives: two taps share one M = 128 instruction.
+struct WgradTcGeom {
+  int batch, p_h, p_w, q_h, q_w;
+  int ksize, stride, pad;
+  int tap0, ntaps;               // taps of this launch's blockIdx.y group: tap0 + blockIdx.y * ntaps_per_group
+  int taps_per_group, nslots;    // nslots = even number of operand slots per stage (>= taps_per_group)
+  long long w_a_stride, w_b_stride;
+  int pix_per_cta;
+};
+
+// instruction descriptor, kind::f16: D = f32, A = B = bf16, both MN-major
+__device__ __host__ constexpr uint32_t idesc_bf16_mn(uint32_t m, uint32_t n) {
+  return idesc_bf16(m, n) | (1u << 15) | (1u << 16);
+}
+// MN-major SWIZZLE_128B descriptor: LBO = bytes between 64-element blocks along M/N, SBO = 1024 (8-pixel groups)
+__device__ __forceinline__ uint64_t sw128_desc_mn(uint32_t smem_addr, uint32_t lbo_bytes) {
+  return (uint64_t)((smem_addr >> 4) & 0x3FFFu) | ((uint64_t)((lbo_bytes >> 4) & 0x3FFFu) << 16) | (64ull << 32) |
+         (1ull << 46) | (2ull << 61);
+}
+
+template <typename T, bool SPLIT, int TMEM_COLS>
+__global__ void __launch_bounds__(160, 1)
+wgrad_tc_kernel(const T* __restrict__ P, const T* __restrict__ Q, float* __restrict__ dw,
+                float* __restrict__ q_colsum, Pro proP, Pro proQ, WgradTcGeom g) {
+  constexpr int KP = SPLIT ? 32 : 64;                 // pixels per stage
+  constexpr uint32_t SLOT = KP * 128;                 // one bf16 tile: KP pixels x 64 channels
+  constexpr int STAGES = 2;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* sm = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int NS = g.nslots;
+  const uint32_t half_bytes = (uint32_t)(NS + 1) * SLOT;                 // P slots + Q, one precision half
+  const uint32_t stage_bytes = half_bytes * (SPLIT ? 2 : 1);
+  uint8_t* tail = sm + STAGES * stage_bytes;
+  float* sCol = reinterpret_cast<float*>(tail);                          // [64]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(tail + 256);              // full[2], empty[2], acc_full
+  uint64_t* full = bars;
+  uint64_t* empty = bars + STAGES;
+  uint64_t* acc_full = bars + 2 * STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 1);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tap_base = g.tap0 + blockIdx.y * g.taps_per_group;
+  const int ntaps = min(g.taps_per_group, g.ntaps - blockIdx.y * g.taps_per_group);
+  const long long Mtot = (long long)g.batch * g.q_h * g.q_w;
+  const long long mbeg = (long long)blockIdx.x * g.pix_per_cta;
+  const long long mend = min(Mtot, mbeg + (long long)g.pix_per_cta);
+  const int nstages = mend > mbeg ? (int)((mend - mbeg + KP - 1) / KP) : 0;
+
+  if (tid < CT_C) sCol[tid] = 0.f;
+  if (tid == 128) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full[s], 128);
+      mbar_init(&empty[s], 1);
+    }
+    mbar_init(acc_full, 1);
+    fence_mbar_init();
+  }
+  if (warp == 4) tmem_alloc<TMEM_COLS>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  if (nstages == 0) {           // whole CTA leaves together (no barrier below is needed)
+    if (warp == 4) tmem_dealloc<TMEM_COLS>(tmem_base);
+    return;
+  }
+
+  if (warp == 4) {
+    // ------------------------------------------------------------------ MMA issuer
+    if (lane == 0) {
+      const uint32_t idesc = idesc_bf16_mn(128, CT_C);
+      const int npairs = NS / 2;
+      for (int it = 0; it < nstages; ++it) {
+        const int s = it & 1;
+        mbar_wait(&full[s], (uint32_t)((it >> 1) & 1));
+        tc_fence_after();
+        const uint32_t base = smem_u32(sm + (size_t)s * stage_bytes);
+        for (int j = 0; j < npairs; ++j) {
+          const uint32_t d = tmem_base + (uint32_t)j * CT_C;
+#pragma unroll
+          for (int ks = 0; ks < KP / 16; ++ks) {
+            const uint64_t a_hi = sw128_desc_mn(base + (uint32_t)(2 * j) * SLOT + ks * 2048, SLOT);
+            const uint64_t b_hi = sw128_desc_mn(base + (uint32_t)NS * SLOT + ks * 2048, SLOT);
+            umma_bf16(d, a_hi, b_hi, idesc, (it | ks) != 0);
+            if (SPLIT) {
+              const uint64_t a_lo = sw128_desc_mn(base + half_bytes + (uint32_t)(2 * j) * SLOT + ks * 2048, SLOT);
+              const uint64_t b_lo = sw128_desc_mn(base + half_bytes + (uint32_t)NS * SLOT + ks * 2048, SLOT);
+              umma_bf16(d, a_hi, b_lo, idesc, 1);
+              umma_bf16(d, a_lo, b_hi, idesc, 1);
+            }
+          }
+        }
+        umma_commit(&empty[s]);
+      }
+      umma_commit(acc_full);
+    }
+  } else {
+    // ------------------------------------------------------------------ producers
+    const int c = tid & 7;
+    const int prow = tid >> 3;      // pixel rows prow + 16*j of the stage
+    float scP[8], shP[8], scQ[8], shQ[8], colsum[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      scP[i] = proP.mode >= NSG_PRO_AFFINE_RELU ? __ldg(proP.scale + c * 8 + i) : 1.f;
+      shP[i] = proP.mode >= NSG_PRO_AFFINE_RELU ? __ldg(proP.shift + c * 8 + i) : 0.f;
+      scQ[i] = proQ.mode >= NSG_PRO_AFFINE_RELU ? __ldg(proQ.scale + c * 8 + i) : 1.f;
+      shQ[i] = proQ.mode >= NSG_PRO_AFFINE_RELU ? __ldg(proQ.shift + c * 8 + i) : 0.f;
+      colsum[i] = 0.f;
+    }
+    for (int it = 0; it < nstages; ++it) {
+      const int s = it & 1;
+      if (it >= STAGES) mbar_wait(&empty[s], (uint32_t)(((it >> 1) - 1) & 1));
+      uint8_t* stage = sm + (size_t)s * stage_bytes;
+#pragma unroll 1
+      for (int j = 0; j < KP / 16; ++j) {
+        const int pr = prow + 16 * j;
+        const long long m = mbeg + (long long)it * KP + pr;
+        const bool mv = m < mend;
+        int ow = 0, oh = 0, n = 0;
+        if (mv) {
+          ow = (int)(m % g.q_w);
+          const long long t = m / g.q_w;
+          oh = (int)(t % g.q_h);
+          n = (int)(t / g.q_h);
+        }
+        const uint32_t off = sw128_offset(pr, c);
+        // Q tile
+        {
+          float v[8], hi[8], lo[8];
+          if (mv) {
+            ld8<T>(Q + m * CT_C + c * 8, v);
+          } else {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[i] = 0.f;
+          }
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float x = mv ? pro_apply(proQ.mode, v[i], scQ[i], shQ[i]) : 0.f;
+            colsum[i] += x;
+            split_bf16(x, hi[i], lo[i]);
+          }
+          uint8_t* dst = stage + (uint32_t)NS * SLOT + off;
+          *reinterpret_cast<uint4*>(dst) = make_uint4(pack_bf16(hi[0], hi[1]), pack_bf16(hi[2], hi[3]),
+                                                      pack_bf16(hi[4], hi[5]), pack_bf16(hi[6], hi[7]));
+          if (SPLIT)
+            *reinterpret_cast<uint4*>(dst + half_bytes) = make_uint4(
+                pack_bf16(lo[0], lo[1]), pack_bf16(lo[2], lo[3]), pack_bf16(lo[4], lo[5]), pack_bf16(lo[6], lo[7]));
+        }
+        // P tiles, one per tap
+#pragma unroll 2
+        for (int tl = 0; tl < ntaps; ++tl) {
+          const int tap = tap_base + tl;
+          const int ih = oh * g.stride - g.pad + tap / g.ksize;
+          const int iw = ow * g.stride - g.pad + tap % g.ksize;
+          const bool ok = mv && ih >= 0 && ih < g.p_h && iw >= 0 && iw < g.p_w;
+          float v[8], hi[8], lo[8];
+          if (ok) {
+            ld8<T>(P + (((long long)n * g.p_h + ih) * g.p_w + iw) * CT_C + c * 8, v);
+          } else {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[i] = 0.f;
+          }
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float x = ok ? pro_apply(proP.mode, v[i], scP[i], shP[i]) : 0.f;
+            split_bf16(x, hi[i], lo[i]);
+          }
+          uint8_t* dst = stage + (uint32_t)tl * SLOT + off;
+          *reinterpret_cast<uint4*>(dst) = make_uint4(pack_bf16(hi[0], hi[1]), pack_bf16(hi[2], hi[3]),
+                                                      pack_bf16(hi[4], hi[5]), pack_bf16(hi[6], hi[7]));
+          if (SPLIT)
+            *reinterpret_cast<uint4*>(dst + half_bytes) = make_uint4(
+                pack_bf16(lo[0], lo[1]), pack_bf16(lo[2], lo[3]), pack_bf16(lo[4], lo[5]), pack_bf16(lo[6], lo[7]));
+        }
+        if (ntaps < NS) {       // the odd slot out: keep it finite (its TMEM lanes are never read)
+          uint8_t* dst = stage + (uint32_t)ntaps * SLOT + off;
+          *reinterpret_cast<uint4*>(dst) = make_uint4(0u, 0u, 0u, 0u);
+          if (SPLIT) *reinterpret_cast<uint4*>(dst + half_bytes) = make_uint4(0u, 0u, 0u, 0u);
+        }
+      }
+      fence_proxy_async_smem();
+      mbar_arrive(&full[s]);
+    }
+    if (q_colsum && blockIdx.y == 0) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) atomicAdd(&sCol[c * 8 + i], colsum[i]);
+    }
+
+    // ------------------------------------------------------------------ epilogue: thread = (slot parity, channel a)
+    mbar_wait(acc_full, 0);
+    tc_fence_after();
+    const int a = tid & 63, sp = tid >> 6;
+    for (int j = 0; j < NS / 2; ++j) {
+      const int tl = 2 * j + sp;
+#pragma unroll 1
+      for (int chunk = 0; chunk < 2; ++chunk) {
+        uint32_t acc[32];
+        tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(j * CT_C + chunk * 32), acc);
+        tmem_ld_wait();
+        if (tl < ntaps) {
+          float* dst = dw + (tap_base + tl) + (long long)a * g.w_a_stride + (long long)(chunk * 32) * g.w_b_stride;
+#pragma unroll
+          for (int i = 0; i < 32; ++i) atomicAdd(dst + (long long)i * g.w_b_stride, __uint_as_float(acc[i]));
+        }
+      }
+    }
+    if (q_colsum && blockIdx.y == 0) {
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (tid < CT_C) atomicAdd(q_colsum + tid, sCol[tid]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 4) tmem_dealloc<TMEM_COLS>(tmem_base);
+}
+
+template <typename T, bool SPLIT, int TMEM_COLS>
+static int launch_wgrad_tc(const WgradTcGeom& g, unsigned gx, unsigned gy, size_t smem, const void* p, const void* q,
+                           float* dw, float* q_colsum, const Pro& pp, const Pro& pq, cudaStream_t stream) {
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t err = cudaFuncSetAttribute(wgrad_tc_kernel<T, SPLIT, TMEM_COLS>,
+                                           cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    if (err != cudaSuccess) return cuda_fail(err, "cudaFuncSetAttribute(wgrad_tc_kernel)");
+    configured = true;
+  }
+  wgrad_tc_kernel<T, SPLIT, TMEM_COLS><<<dim3(gx, gy), 160, smem, stream>>>((const T*)p, (const T*)q, dw, q_colsum,
+                                                                            pp, pq, g);
+  NSG_CHECK_LAUNCH("wgrad_tc_kernel");
+  return NSG_OK;
+}
+
+template <typename T, bool SPLIT>
+static int dispatch_wgrad_cols(int cols, const WgradTcGeom& g, unsigned gx, unsigned gy, size_t smem, const void* p,
+                               const void* q, float* dw, float* q_colsum, const Pro& pp, const Pro& pq,
+                               cudaStream_t stream) {
+  if (cols <= 64) return launch_wgrad_tc<T, SPLIT, 64>(g, gx, gy, smem, p, q, dw, q_colsum, pp, pq, stream);
+  if (cols <= 256) return launch_wgrad_tc<T, SPLIT, 256>(g, gx, gy, smem, p, q, dw, q_colsum, pp, pq, stream);
+  return launch_wgrad_tc<T, SPLIT, 512>(g, gx, gy, smem, p, q, dw, q_colsum, pp, pq, stream);
+}
+
+int conv_wgrad_tc(const nsg_conv_geom* cg, const void* p, const nsg_prologue* pro_p, const void* q,
+                  const nsg_prologue* pro_q, float* dw, float* q_colsum, int passes, cudaStream_t stream) {
+  if (int rc = tc_shape_ok(cg, "conv_wgrad_tc")) return rc;
+  NSG_REQUIRE(passes >= 1 && passes <= 3, "conv_wgrad_tc: passes must be 1, 2 or 3");
+  const bool split = passes >= 2;
+  const int kp = split ? 32 : 64;
+  WgradTcGeom g{};
+  g.batch = cg->batch; g.p_h = cg->in_h; g.p_w = cg->in_w; g.q_h = cg->out_h; g.q_w = cg->out_w;
+  g.ksize = cg->ksize; g.stride = cg->stride; g.pad = cg->pad;
+  g.w_a_stride = cg->w_cin_stride; g.w_b_stride = cg->w_cout_stride;
+  const int taps = cg->ksize * cg->ksize;
+  g.tap0 = 0; g.ntaps = taps;
+  g.taps_per_group = taps <= 10 ? taps : 8;
+  g.nslots = (g.taps_per_group + 1) / 2 * 2;
+  const unsigned groups = (unsigned)((taps + g.taps_per_group - 1) / g.taps_per_group);
+  const long long M = (long long)g.batch * g.q_h * g.q_w;
+  if (M == 0) return NSG_OK;
+  long long nctas = num_sms() / (long long)groups;
+  if (nctas < 1) nctas = 1;
+  long long ppc = (M + nctas - 1) / nctas;
+  ppc = (ppc + kp - 1) / kp * kp;
+  if (ppc < 2 * kp) ppc = 2 * kp;
+  g.pix_per_cta = (int)ppc;
+  const unsigned gx = (unsigned)((M + ppc - 1) / ppc);
+  const size_t slot = (size_t)kp * 128;
+  const size_t smem = 1024 + 2 * (size_t)(g.nslots + 1) * slot * (split ? 2 : 1) + 512;
+  Pro pp{NSG_PRO_NONE, nullptr, nullptr}, pq{NSG_PRO_NONE, nullptr, nullptr};
+  if (pro_p) pp = Pro{pro_p->mode, pro_p->scale, pro_p->shift};
+  if (pro_q) pq = Pro{pro_q->mode, pro_q->scale, pro_q->shift};
+  if (pp.mode >= NSG_PRO_AFFINE_RELU) NSG_REQUIRE(pp.scale && pp.shift, "wgrad: affine prologue needs scale/shift");
+  if (pq.mode >= NSG_PRO_AFFINE_RELU) NSG_REQUIRE(pq.scale && pq.shift, "wgrad: affine prologue needs scale/shift");
+  const int cols = g.nslots / 2 * CT_C;
+  if (cg->dtype == NSG_F32) {
+    return split ? dispatch_wgrad_cols<float, true>(cols, g, gx, groups, smem, p, q, dw, q_colsum, pp, pq, stream)
+                 : dispatch_wgrad_cols<float, false>(cols, g, gx, groups, smem, p, q, dw, q_colsum, pp, pq, stream);
+  } else if (cg->dtype == NSG_BF16) {
+    return split ? dispatch_wgrad_cols<__nv_bfloat16, true>(cols, g, gx, groups, smem, p, q, dw, q_colsum, pp, pq, stream)
+                 : dispatch_wgrad_cols<__nv_bfloat16, false>(cols, g, gx, groups, smem, p, q, dw, q_colsum, pp, pq, stream);
+  }
+  set_error("unknown dtype %d", cg->dtype);
+  return NSG_E_INVALID;
 }
 
 }  // namespace nsg

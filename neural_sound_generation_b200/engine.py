@@ -39,7 +39,7 @@ class Engine(object):
         self.cin0, self.dim, self.k = input_dim, dim, z_dim
         self.act_dtype = act_dtype
         self.conv_impl = conv_impl      # 0 = fp32 CUDA-core kernels, 1 = tcgen05 kernels where shapes allow
-        self.wgrad_impl = 0 if wgrad_impl is None else wgrad_impl   # TODO: follow conv_impl once wgrad_tc lands
+        self.wgrad_impl = conv_impl if wgrad_impl is None else wgrad_impl
         self.vq_mode = vq_mode
         self.dt = ops.F32 if act_dtype == torch.float32 else ops.BF16
         # operand precision of the tcgen05 convolutions (include/nsg_b200.h): fp32 activations default to the
