@@ -141,8 +141,10 @@ def main():
     with torch.no_grad():
         model.codebook.embedding.weight.normal_()                  # trained-like codebook
     model = model.to(dev)
-    if args.mode == 'bf16':
+    if args.mode == 'bf16':        # bf16 activations, tcgen05 convolutions (bf16 x bf16), tcgen05 split-bf16 VQ search
         model.act_dtype, model.conv_impl, model.vq_mode = torch.bfloat16, 1, 1
+    elif args.mode == 'tc32':      # fp32 activations, tcgen05 convolutions with split-bf16 operands (3 passes)
+        model.act_dtype, model.conv_impl, model.vq_mode = torch.float32, 1, 1
     model.train()
     opt = nsg.optim.Adam(model, lr=1e-3)
     opt.grad_scale = 1.0 / world
@@ -153,13 +155,9 @@ def main():
     devin = [h.to(dev) for h in host]
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)       # > 126 MB L2
 
-    def step(c):
-        opt.zero_grad()
-        losses, _ = model.loss_and_grads(c, beta=1.0)
-        if world > 1:
-            dist.all_reduce(flat['grads'])                          # NCCL over NVLink; averaged via grad_scale
-        opt.step()
-        return losses
+    # the public train-step object: the train_vqvae loop body as one CUDA graph (train.py uses the same class)
+    hook = (lambda gflat: dist.all_reduce(gflat)) if world > 1 else None   # NCCL over NVLink; averaged via grad_scale
+    graphed = nsg.GraphedTrainStep(model, opt, (B_PER_GPU, 1, N_MELS, FRAMES), beta=1.0, grad_hook=hook)
 
     def sync():
         torch.cuda.synchronize()
@@ -184,18 +182,20 @@ def main():
         return t.item() / steps
 
     for i in range(max(3, args.warmup)):
-        step(devin[i % n_in])
+        graphed(devin[i % n_in])
     sync()
     sampler = ClockSampler(local) if rank == 0 else None
     l0 = ops.launch_count
-    ms = timed(lambda i: step(devin[i % n_in]), args.steps)
-    launches = (ops.launch_count - l0) // args.steps
+    model.loss_and_grads(devin[0], beta=1.0)          # count the launches of one (eager) step, outside the timing
+    opt.step()
+    launches = ops.launch_count - l0 + 1              # + zero_grad memset
+    sync()
+    ms = timed(lambda i: graphed(devin[i % n_in]), args.steps)
     clocks = sampler.stop() if sampler else None
 
-    # end to end: pinned host mel batch -> device, step, losses -> host, every step
+    # end to end: pinned host mel batch -> device, graph replay, losses -> host, every step
     def e2e_step(i):
-        c = host[i % n_in].to(dev, non_blocking=True)
-        return step(c).tolist()
+        return graphed(host[i % n_in]).tolist()
     e2e_step(0)
     sync()
     ms_e2e = timed(e2e_step, args.steps)

@@ -420,6 +420,11 @@ wgrad_simt_kernel(const T* __restrict__ P, const T* __restrict__ Q, float* __res
 }
 
 // ------------------------------------------------------------------------------------------------
+int conv_gemm_c1(const nsg_conv_geom* cg, const void* in, const float* w, const Pro& pro, const EpiArgs& e, void* out,
+                 cudaStream_t stream);
+int conv_wgrad_c1(const nsg_conv_geom* cg, const void* p, const Pro& pp, const void* q, const Pro& pq, float* dw,
+                  float* q_colsum, cudaStream_t stream);
+
 int conv_gemm_simt(const nsg_conv_geom* cg, const void* in, const float* w, const nsg_prologue* pro,
                    const nsg_epilogue* epi, void* out, cudaStream_t stream) {
   NSG_REQUIRE(cg->ksize >= 1 && cg->ksize <= 4, "conv: ksize %d unsupported (1..4)", cg->ksize);
@@ -431,6 +436,10 @@ int conv_gemm_simt(const nsg_conv_geom* cg, const void* in, const float* w, cons
   if (p.mode >= NSG_PRO_AFFINE_RELU) NSG_REQUIRE(p.scale && p.shift, "conv: affine prologue needs scale/shift");
   EpiArgs e{};
   if (int rc = make_epi(epi, &e)) return rc;
+  {   // the single-channel ends of the network have their own streaming kernels (conv_c1.cu)
+    const int served = conv_gemm_c1(cg, in, w, p, e, out, stream);
+    if (served != 0) return served < 0 ? served : NSG_OK;
+  }
   const bool vec = (cg->cin % 16 == 0);
   return NSG_DISPATCH_DTYPE(cg->dtype, [&]() -> int {
     for (int i = 0; i < np; ++i) {
@@ -470,6 +479,10 @@ int conv_wgrad_simt(const nsg_conv_geom* cg, const void* p, const nsg_prologue* 
   Pro pp{NSG_PRO_NONE, nullptr, nullptr}, pq{NSG_PRO_NONE, nullptr, nullptr};
   if (pro_p) pp = Pro{pro_p->mode, pro_p->scale, pro_p->shift};
   if (pro_q) pq = Pro{pro_q->mode, pro_q->scale, pro_q->shift};
+  {
+    const int served = conv_wgrad_c1(cg, p, pp, q, pq, dw, q_colsum, stream);
+    if (served != 0) return served < 0 ? served : NSG_OK;
+  }
   const bool vec = (g.ca % 4 == 0);
   return NSG_DISPATCH_DTYPE(cg->dtype, [&]() -> int {
     dim3 grid(a_tiles, b_tiles, zc);

@@ -85,6 +85,36 @@ __device__ __forceinline__ void st8<__nv_bfloat16>(__nv_bfloat16* p, const float
       make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
 }
 
+// 8 channels of one pixel as loaded (kept raw in registers while the load is in flight)
+template <typename T>
+struct Raw8;
+template <>
+struct Raw8<float> {
+  float4 a, b;
+  __device__ __forceinline__ void load(const float* p) {
+    a = __ldg(reinterpret_cast<const float4*>(p));
+    b = __ldg(reinterpret_cast<const float4*>(p + 4));
+  }
+  __device__ __forceinline__ void zero() { a = b = make_float4(0.f, 0.f, 0.f, 0.f); }
+  __device__ __forceinline__ void unpack(float (&v)[8]) const {
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+  }
+};
+template <>
+struct Raw8<__nv_bfloat16> {
+  uint4 a;
+  __device__ __forceinline__ void load(const __nv_bfloat16* p) { a = __ldg(reinterpret_cast<const uint4*>(p)); }
+  __device__ __forceinline__ void zero() { a = make_uint4(0u, 0u, 0u, 0u); }
+  __device__ __forceinline__ void unpack(float (&v)[8]) const {
+    const uint32_t w[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      v[2 * i] = __uint_as_float(w[i] << 16);
+      v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+    }
+  }
+};
+
 // v[i] of lane l -> returns sum over lanes of v[lane] (a 32x32 transpose-reduce in 31 shuffles); v is destroyed
 __device__ __forceinline__ float warp_transpose_sum(float (&v)[32], int lane) {
 #pragma unroll
@@ -211,60 +241,75 @@ tapgemm_tc_kernel(const T* __restrict__ in, const uint8_t* __restrict__ wpacked,
     }
   } else {
     // ------------------------------------------------------------------ producers: one tap per ring stage
-    const int c = tid & 7;            // 16-byte chunk of the 128-byte bf16 row = channels c*8 .. c*8+7
-    const int rbase = tid >> 3;       // rows rbase + 16*j
+    // Each thread owns the 16-byte channel chunk c of rows rbase + 16*j.  All 8 row loads of a tap are issued
+    // back to back, and the loads of tap t+1 are in flight while tap t is transformed and stored.
+    const int c = tid & 7;            // channels c*8 .. c*8+7
+    const int rbase = tid >> 3;
     float sc[8], sh[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       sc[i] = pro.mode >= NSG_PRO_AFFINE_RELU ? __ldg(pro.scale + c * 8 + i) : 1.f;
       sh[i] = pro.mode >= NSG_PRO_AFFINE_RELU ? __ldg(pro.shift + c * 8 + i) : 0.f;
     }
+    int rowPix[8], rowHs[8], rowWs[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int r = rbase + 16 * j;
+      const int n = rowN[r];
+      rowPix[j] = n < 0 ? -1 : n * g.in_h * g.in_w;
+      rowHs[j] = rowH[r] * g.in_stride;
+      rowWs[j] = rowW[r] * g.in_stride;
+    }
+    const T* inc = in + c * 8;
+    auto issue = [&](int t, Raw8<T> (&dst)[8]) -> unsigned {
+      const int dh = g.dh[t], dw = g.dw[t];
+      unsigned mask = 0;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int ih = rowHs[j] + dh, iw = rowWs[j] + dw;
+        const bool ok = rowPix[j] >= 0 && ih >= 0 && ih < g.in_h && iw >= 0 && iw < g.in_w;
+        if (ok) {
+          dst[j].load(inc + (long long)(rowPix[j] + ih * g.in_w + iw) * CT_C);
+          mask |= 1u << j;
+        } else {
+          dst[j].zero();
+        }
+      }
+      return mask;
+    };
+    Raw8<T> cur[8], nxt[8];
+    unsigned okc = issue(0, cur), okn = 0;
     for (int t = 0; t < g.ntaps; ++t) {
       const int s = t % STAGES;
+      if (t + 1 < g.ntaps) okn = issue(t + 1, nxt);
       if (t >= STAGES) mbar_wait(&empty[s], (uint32_t)(((t / STAGES) - 1) & 1));
       uint8_t* stage = sm + (size_t)s * Cfg::STAGE_BYTES;
       if (tid == 0) {
         mbar_arrive_expect_tx(&full[s], Cfg::B_IMGS * CT_B_BYTES);
         bulk_g2s(stage + Cfg::B_OFF, wpacked + (size_t)g.woff[t] * CT_WTAP_BYTES, Cfg::B_IMGS * CT_B_BYTES, &full[s]);
       }
-      const int dh = g.dh[t], dw = g.dw[t];
 #pragma unroll
-      for (int half = 0; half < 2; ++half) {
-        float v[4][8];
-        bool ok[4];
+      for (int j = 0; j < 8; ++j) {
+        float v[8], hi[8], lo[8];
+        cur[j].unpack(v);
+        const bool ok = (okc >> j) & 1u;
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const int r = rbase + 16 * (half * 4 + j);
-          const int n = rowN[r];
-          const int ih = rowH[r] * g.in_stride + dh;
-          const int iw = rowW[r] * g.in_stride + dw;
-          ok[j] = n >= 0 && ih >= 0 && ih < g.in_h && iw >= 0 && iw < g.in_w;
-          if (ok[j]) {
-            ld8<T>(in + (((long long)n * g.in_h + ih) * g.in_w + iw) * CT_C + c * 8, v[j]);
-          } else {
-#pragma unroll
-            for (int i = 0; i < 8; ++i) v[j][i] = 0.f;
-          }
+        for (int i = 0; i < 8; ++i) {
+          const float x = ok ? pro_apply(pro.mode, v[i], sc[i], sh[i]) : 0.f;
+          split_bf16(x, hi[i], lo[i]);
         }
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const int r = rbase + 16 * (half * 4 + j);
-          float hi[8], lo[8];
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const float x = ok[j] ? pro_apply(pro.mode, v[j][i], sc[i], sh[i]) : 0.f;
-            split_bf16(x, hi[i], lo[i]);
-          }
-          const uint32_t off = sw128_offset(r, c);
-          *reinterpret_cast<uint4*>(stage + off) = make_uint4(pack_bf16(hi[0], hi[1]), pack_bf16(hi[2], hi[3]),
-                                                              pack_bf16(hi[4], hi[5]), pack_bf16(hi[6], hi[7]));
-          if (PASSES == 3)
-            *reinterpret_cast<uint4*>(stage + CT_A_BYTES + off) = make_uint4(
-                pack_bf16(lo[0], lo[1]), pack_bf16(lo[2], lo[3]), pack_bf16(lo[4], lo[5]), pack_bf16(lo[6], lo[7]));
-        }
+        const uint32_t off = sw128_offset(rbase + 16 * j, c);
+        *reinterpret_cast<uint4*>(stage + off) = make_uint4(pack_bf16(hi[0], hi[1]), pack_bf16(hi[2], hi[3]),
+                                                            pack_bf16(hi[4], hi[5]), pack_bf16(hi[6], hi[7]));
+        if (PASSES == 3)
+          *reinterpret_cast<uint4*>(stage + CT_A_BYTES + off) = make_uint4(
+              pack_bf16(lo[0], lo[1]), pack_bf16(lo[2], lo[3]), pack_bf16(lo[4], lo[5]), pack_bf16(lo[6], lo[7]));
       }
       fence_proxy_async_smem();
       mbar_arrive(&full[s]);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) cur[j] = nxt[j];
+      okc = okn;
     }
 
     // ------------------------------------------------------------------ epilogue: thread = output row
@@ -567,15 +612,28 @@ wgrad_tc_kernel(const T* __restrict__ P, const T* __restrict__ Q, float* __restr
           n = (int)(t / g.q_h);
         }
         const uint32_t off = sw128_offset(pr, c);
-        // Q tile
+        // issue the Q load and every tap's P load before touching any of them
+        Raw8<T> rq, rp[10];
+        unsigned okp = 0;
+        if (mv) rq.load(Q + m * CT_C + c * 8); else rq.zero();
+        const int ih0 = oh * g.stride - g.pad, iw0 = ow * g.stride - g.pad;
+#pragma unroll
+        for (int tl = 0; tl < 10; ++tl) {
+          if (tl < ntaps) {
+            const int tap = tap_base + tl;
+            const int ih = ih0 + tap / g.ksize, iw = iw0 + tap % g.ksize;
+            const bool ok = mv && ih >= 0 && ih < g.p_h && iw >= 0 && iw < g.p_w;
+            if (ok) {
+              rp[tl].load(P + (((long long)n * g.p_h + ih) * g.p_w + iw) * CT_C + c * 8);
+              okp |= 1u << tl;
+            } else {
+              rp[tl].zero();
+            }
+          }
+        }
         {
           float v[8], hi[8], lo[8];
-          if (mv) {
-            ld8<T>(Q + m * CT_C + c * 8, v);
-          } else {
-#pragma unroll
-            for (int i = 0; i < 8; ++i) v[i] = 0.f;
-          }
+          rq.unpack(v);
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
             const float x = mv ? pro_apply(proQ.mode, v[i], scQ[i], shQ[i]) : 0.f;
@@ -589,31 +647,24 @@ wgrad_tc_kernel(const T* __restrict__ P, const T* __restrict__ Q, float* __restr
             *reinterpret_cast<uint4*>(dst + half_bytes) = make_uint4(
                 pack_bf16(lo[0], lo[1]), pack_bf16(lo[2], lo[3]), pack_bf16(lo[4], lo[5]), pack_bf16(lo[6], lo[7]));
         }
-        // P tiles, one per tap
-#pragma unroll 2
-        for (int tl = 0; tl < ntaps; ++tl) {
-          const int tap = tap_base + tl;
-          const int ih = oh * g.stride - g.pad + tap / g.ksize;
-          const int iw = ow * g.stride - g.pad + tap % g.ksize;
-          const bool ok = mv && ih >= 0 && ih < g.p_h && iw >= 0 && iw < g.p_w;
-          float v[8], hi[8], lo[8];
-          if (ok) {
-            ld8<T>(P + (((long long)n * g.p_h + ih) * g.p_w + iw) * CT_C + c * 8, v);
-          } else {
 #pragma unroll
-            for (int i = 0; i < 8; ++i) v[i] = 0.f;
-          }
+        for (int tl = 0; tl < 10; ++tl) {
+          if (tl < ntaps) {
+            float v[8], hi[8], lo[8];
+            rp[tl].unpack(v);
+            const bool ok = (okp >> tl) & 1u;
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const float x = ok ? pro_apply(proP.mode, v[i], scP[i], shP[i]) : 0.f;
-            split_bf16(x, hi[i], lo[i]);
+            for (int i = 0; i < 8; ++i) {
+              const float x = ok ? pro_apply(proP.mode, v[i], scP[i], shP[i]) : 0.f;
+              split_bf16(x, hi[i], lo[i]);
+            }
+            uint8_t* dst = stage + (uint32_t)tl * SLOT + off;
+            *reinterpret_cast<uint4*>(dst) = make_uint4(pack_bf16(hi[0], hi[1]), pack_bf16(hi[2], hi[3]),
+                                                        pack_bf16(hi[4], hi[5]), pack_bf16(hi[6], hi[7]));
+            if (SPLIT)
+              *reinterpret_cast<uint4*>(dst + half_bytes) = make_uint4(
+                  pack_bf16(lo[0], lo[1]), pack_bf16(lo[2], lo[3]), pack_bf16(lo[4], lo[5]), pack_bf16(lo[6], lo[7]));
           }
-          uint8_t* dst = stage + (uint32_t)tl * SLOT + off;
-          *reinterpret_cast<uint4*>(dst) = make_uint4(pack_bf16(hi[0], hi[1]), pack_bf16(hi[2], hi[3]),
-                                                      pack_bf16(hi[4], hi[5]), pack_bf16(hi[6], hi[7]));
-          if (SPLIT)
-            *reinterpret_cast<uint4*>(dst + half_bytes) = make_uint4(
-                pack_bf16(lo[0], lo[1]), pack_bf16(lo[2], lo[3]), pack_bf16(lo[4], lo[5]), pack_bf16(lo[6], lo[7]));
         }
         if (ntaps < NS) {       // the odd slot out: keep it finite (its TMEM lanes are never read)
           uint8_t* dst = stage + (uint32_t)ntaps * SLOT + off;

@@ -1,0 +1,59 @@
+"""The train_vqvae loop body (train.py:109-136) captured once as a CUDA graph and replayed per batch.
+
+The step is ~100 kernel launches of a few microseconds each; driven from Python it is launch-bound,
+so the whole iteration -- zero_grad, forward, the three loss terms, backward, [gradient all-reduce], Adam --
+is recorded on a capture stream and replayed with one ``cudaGraphLaunch``.  Every entry point of the C ABI is
+capturable (no host synchronisation, no allocation: buffers come from the graph's private torch pool).
+"""
+import torch
+
+from . import optim as _optim
+
+
+class GraphedTrainStep(object):
+    """``step = GraphedTrainStep(model, optimizer, (B, n_mels, T), beta); losses = step(c)``.
+
+    ``c`` may live on the host (pinned for an asynchronous copy) or on the device; it is copied into the
+    graph's static input buffer.  Returns the static float64 device tensor [loss_recons, loss_vq, loss_commit]
+    (valid until the next call).  ``grad_hook(flat_grads)`` (optional) is captured between backward and the
+    optimizer step -- bench.py passes the NCCL all-reduce there.
+    """
+
+    def __init__(self, model, optimizer, batch_shape, beta=1.0, grad_hook=None):
+        if not isinstance(optimizer, _optim.Adam):
+            raise TypeError('GraphedTrainStep needs neural_sound_generation_b200.optim.Adam (device-side step count)')
+        self.model, self.optimizer, self.beta = model, optimizer, float(beta)
+        flat = model.flatten_parameters()
+        dev = flat['params'].device
+        self.c = torch.zeros(tuple(batch_shape), dtype=torch.float32, device=dev)
+        # one eager iteration configures every kernel variant (cudaFuncSetAttribute is not capturable); the
+        # model / optimizer state it touches is restored afterwards
+        saved = [t.clone() for t in self._state()]
+        self._body(grad_hook)
+        torch.cuda.synchronize(dev)
+        for t, s in zip(self._state(), saved):
+            t.copy_(s)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.losses, self.outputs = self._body(grad_hook)
+        torch.cuda.synchronize(dev)
+        for t, s in zip(self._state(), saved):
+            t.copy_(s)
+
+    def _state(self):
+        f = self.model._flat
+        o = self.optimizer
+        return [f['params'], o.exp_avg, o.exp_avg_sq, o.step_count] + [b for _, b in self.model.named_buffers()]
+
+    def _body(self, grad_hook):
+        self.optimizer.zero_grad()
+        losses, outs = self.model.loss_and_grads(self.c, beta=self.beta)
+        if grad_hook is not None:
+            grad_hook(self.model._flat['grads'])
+        self.optimizer.step()
+        return losses, outs
+
+    def __call__(self, c):
+        self.c.copy_(c.reshape(self.c.shape), non_blocking=True)
+        self.graph.replay()
+        return self.losses

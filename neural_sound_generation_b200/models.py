@@ -289,9 +289,9 @@ class VQVAE(nn.Module):
         ops.vq_backward_inputs(g_st, z_e, z_q, 2.0 * beta / n_lat, dz)   # ST clone + beta * d commit / d z_e
         ops.scatter_add(z_q, idx, G['codebook.embedding.weight'], alpha=2.0 / n_lat, sub=z_e)  # d loss_vq / d e
         eng.encoder_bwd(ectx, P, G, dz)
-        scale = torch.tensor([1.0 / (b * h * w), 1.0 / z_e.numel()], dtype=torch.float64, device=x.device)
-        means = sums * scale
-        losses = torch.stack([means[0], means[1], means[1]])
+        # (python-scalar multiplies keep this CUDA-graph capturable: no host tensor is created)
+        l_rec, l_vq = sums[0] * (1.0 / (b * h * w)), sums[1] * (1.0 / z_e.numel())
+        losses = torch.stack([l_rec, l_vq, l_vq])
         return losses, (_nchw_view(xt32), _nchw_view(z_e), _nchw_view(z_q), idx)
 
 

@@ -11,19 +11,30 @@ import torch.nn.functional as F
 from tqdm import tqdm
 
 from .models import to_scalar, VQVAE  # noqa: F401
+from . import optim as _optim
+from .graph import GraphedTrainStep
 
 
 def train_vqvae(args, model, optimizer, train_loader, device, epoch):
     model.train()
     train_loss = 0
     fused = isinstance(model, VQVAE)
+    # the whole iteration replays as one CUDA graph per batch shape (opt out: args.cuda_graph = False)
+    graphed = fused and isinstance(optimizer, _optim.Adam) and getattr(args, 'cuda_graph', True)
     if args.dataset == 'ljspeech':
         for batch_idx, (x, y, c, g, input_lengths) in tqdm(enumerate(train_loader)):
             optimizer.zero_grad()
             # Prepare data (x, y, input_lengths are moved by the reference but never used: train.py:111-114)
             c = c.to(device, non_blocking=True) if c is not None else None
             c = c.unsqueeze(1)
-            if fused:
+            if graphed:
+                key = (tuple(c.shape), float(args.beta), id(optimizer))
+                cache = model.__dict__.setdefault('_graphed_steps', {})
+                if key not in cache:
+                    cache[key] = GraphedTrainStep(model, optimizer, c.shape, args.beta)
+                lv = cache[key](c).tolist()
+                train_loss = lv[0] + lv[1]
+            elif fused:
                 losses, _ = model.loss_and_grads(c, beta=args.beta)
                 optimizer.step()
                 lv = losses.tolist()                                   # one host sync (reference: two .item())
