@@ -123,6 +123,46 @@ int nsg_conv_gemm_tc(const nsg_conv_geom* g, const void* in, const void* packed_
 int nsg_conv_wgrad_tc(const nsg_conv_geom* g, const void* p, const nsg_prologue* pro_p, const void* q,
                       const nsg_prologue* pro_q, float* dw, float* q_colsum, int passes, void* stream);
 
+/* TMA-fed persistent tcgen05 kernels (bf16 tensors, cin == cout == 64; the production path of the bf16 train step).
+ * They read OPERAND-READY activations -- the BatchNorm/ReLU that precedes a convolution in models.py:148-183 has
+ * already been applied by nsg_bn_act64 / an epilogue mask -- so there is no prologue argument: the tensor core
+ * consumes exactly what the TMA unit wrote (zero padding = the unit's out-of-bounds fill).
+ *   nsg_conv_pack_many     bf16 K-major SWIZZLE_128B weight images (k*k * 8192 bytes each, 128-byte aligned) of up
+ *                          to 24 (layer, orientation) pairs in one launch; strides as in nsg_conv_geom
+ *   nsg_conv_gemm_tma      same contract as nsg_conv_gemm_tc with passes = 1 and no prologue
+ *   nsg_conv_wgrad_tma     dw_packed[t][a][b] (fp32, k*k*64*64, 16-byte aligned) += sum_m P[gather0(m,t),a]*Q[m,b];
+ *                          q_colsum (nullable) as in nsg_conv_wgrad
+ *   nsg_wgrad_unpack_many  dw[t + a*w_cin_stride + b*w_cout_stride] += dw_packed[t][a][b] for up to 24 layers */
+int nsg_conv_pack_many(int n, const float* const* w, void* const* packed, const int* ntaps,
+                       const long long* w_cin_stride, const long long* w_cout_stride, void* stream);
+int nsg_conv_gemm_tma(const nsg_conv_geom* g, const void* in, const void* packed_w, const nsg_epilogue* epi, void* out,
+                      void* stream);
+int nsg_conv_wgrad_tma(const nsg_conv_geom* g, const void* p, const void* q, float* dw_packed, float* q_colsum,
+                       void* stream);
+int nsg_wgrad_unpack_many(int n, const float* const* dw_packed, float* const* dw, const int* ntaps,
+                          const long long* w_cin_stride, const long long* w_cout_stride, void* stream);
+
+/* Streaming companions for bf16 tensors with 64 channels (fused_elem.cu), `pixels` = N*H*W:
+ *   nsg_bn_act64   out = [relu]([res +] BN(h)); train (stats != null: [sum | sumsq] over `count` elements, as
+ *                  accumulated by a NSG_STATS_MOMENTS epilogue): batch statistics, running statistics updated as
+ *                  torch does; eval (stats == null): running statistics.  mean/invstd/scale/shift (nullable) are
+ *                  published for the backward pass.                         nn.BatchNorm2d + ReLU, models.py:151-158
+ *   nsg_bn_bwd64   dh = gamma*invstd*(g - sum_g/M - xhat*sum_gx/M) from stats = [sum g | sum g*xhat]
+ *                  (NSG_STATS_BNBWD); dgamma += sum_gx; dbeta += sum_g; dbias_prev (nullable) += column sums of dh
+ *   nsg_relu64     out = max(x, 0)
+ *   nsg_vq_bwd_stats64  dz = g_st + coef*(z - zq)  (vq_st backward clone + commitment term, vector_quantization.py:50-52,
+ *                  train.py:133) with the NSG_STATS_BNBWD reductions of the BatchNorm that produced z fused (stats nullable) */
+int nsg_bn_act64(const void* h, const void* res, void* out, const double* stats, double count, const float* gamma,
+                 const float* beta, float eps, float momentum, float* running_mean, float* running_var,
+                 long long* num_batches_tracked, float* mean, float* invstd, float* scale, float* shift, int relu_out,
+                 long long pixels, void* stream);
+int nsg_bn_bwd64(const void* g, const void* h, void* dh, const double* stats, double count, const float* mean,
+                 const float* invstd, const float* gamma, float* dgamma, float* dbeta, float* dbias_prev,
+                 long long pixels, void* stream);
+int nsg_relu64(const void* x, void* out, long long n, void* stream);
+int nsg_vq_bwd_stats64(const void* g_st, const void* z, const void* zq, float coef, void* dz, const void* h,
+                       const float* mean, const float* invstd, double* stats, long long pixels, void* stream);
+
 /* ---------------------------------------------------------------- batch norm (nn.BatchNorm2d, models.py:151,154,166,180) */
 /* stats (sum, sumsq over `count` elements per channel) -> mean, invstd, scale = gamma*invstd,
  * shift = beta - mean*scale; running stats updated with momentum (unbiased variance), as torch does. */

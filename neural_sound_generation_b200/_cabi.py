@@ -22,6 +22,8 @@ EXPORTS = [
     'nsg_colsum', 'nsg_vq_forward', 'nsg_scatter_add', 'nsg_vq_backward_inputs', 'nsg_recon_loss',
     'nsg_adam_step', 'nsg_tanh_bwd', 'nsg_gather_rows', 'nsg_vq_workspace_bytes',
     'nsg_conv_pack_bytes', 'nsg_conv_pack_weights', 'nsg_conv_gemm_tc', 'nsg_conv_wgrad_tc',
+    'nsg_conv_pack_many', 'nsg_conv_gemm_tma', 'nsg_conv_wgrad_tma', 'nsg_wgrad_unpack_many',
+    'nsg_bn_act64', 'nsg_bn_bwd64', 'nsg_relu64', 'nsg_vq_bwd_stats64',
 ]
 
 
@@ -71,6 +73,14 @@ def load():
     lib.nsg_conv_gemm_tc.argtypes = [C.POINTER(ConvGeom), vp, vp, C.POINTER(Prologue), C.POINTER(Epilogue), vp, i, vp]
     lib.nsg_conv_wgrad_tc.argtypes = [C.POINTER(ConvGeom), vp, C.POINTER(Prologue), vp, C.POINTER(Prologue), vp, vp,
                                       i, vp]
+    lib.nsg_conv_pack_many.argtypes = [i, vp, vp, vp, vp, vp, vp]
+    lib.nsg_conv_gemm_tma.argtypes = [C.POINTER(ConvGeom), vp, vp, C.POINTER(Epilogue), vp, vp]
+    lib.nsg_conv_wgrad_tma.argtypes = [C.POINTER(ConvGeom), vp, vp, vp, vp, vp]
+    lib.nsg_wgrad_unpack_many.argtypes = [i, vp, vp, vp, vp, vp, vp]
+    lib.nsg_bn_act64.argtypes = [vp, vp, vp, vp, d, vp, vp, f, f, vp, vp, vp, vp, vp, vp, vp, i, ll, vp]
+    lib.nsg_bn_bwd64.argtypes = [vp, vp, vp, vp, d, vp, vp, vp, vp, vp, vp, ll, vp]
+    lib.nsg_relu64.argtypes = [vp, vp, ll, vp]
+    lib.nsg_vq_bwd_stats64.argtypes = [vp, vp, vp, f, vp, vp, vp, vp, vp, ll, vp]
     lib.nsg_bn_finalize.argtypes = [vp, i, d, vp, vp, f, f, vp, vp, vp, vp, vp, vp, vp, vp]
     lib.nsg_bn_eval_coeffs.argtypes = [i, vp, vp, vp, vp, f, vp, vp, vp]
     lib.nsg_bn_apply.argtypes = [vp, vp, vp, vp, i, i, vp, ll, i, i, vp]

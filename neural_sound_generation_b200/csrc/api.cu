@@ -43,6 +43,15 @@ int conv_gemm_tc(const nsg_conv_geom* cg, const void* in, const void* packed, co
 int conv_wgrad_tc(const nsg_conv_geom* cg, const void* p, const nsg_prologue* pro_p, const void* q,
                   const nsg_prologue* pro_q, float* dw, float* q_colsum, int passes, cudaStream_t stream);
 
+int conv_gemm_tma(const nsg_conv_geom* cg, const void* in, const void* packed, const nsg_epilogue* epi, void* out,
+                  cudaStream_t stream);
+int conv_pack_many(int n, const float* const* w, void* const* dst, const int* ntaps, const long long* in_stride,
+                   const long long* out_stride, cudaStream_t stream);
+int conv_wgrad_tma(const nsg_conv_geom* cg, const void* p, const void* q, float* dwp, float* q_colsum,
+                   cudaStream_t stream);
+int wgrad_unpack_many(int n, const float* const* src, float* const* dw, const int* ntaps, const long long* a_stride,
+                      const long long* b_stride, cudaStream_t stream);
+
 }  // namespace nsg
 
 using namespace nsg;
@@ -126,6 +135,34 @@ int nsg_conv_wgrad(const nsg_conv_geom* g, const void* p, const nsg_prologue* pr
   NSG_REQUIRE(p && q && dw, "conv_wgrad: null pointer");
   NSG_REQUIRE(impl == 0, "conv_wgrad: impl must be 0 (the tensor-core kernel is nsg_conv_wgrad_tc)");
   return conv_wgrad_simt(g, p, pro_p, q, pro_q, dw, q_colsum, (cudaStream_t)stream);
+}
+
+int nsg_conv_gemm_tma(const nsg_conv_geom* g, const void* in, const void* packed_w, const nsg_epilogue* epi, void* out,
+                      void* stream) {
+  int rc = check_geom(g);
+  if (rc) return rc;
+  NSG_REQUIRE(in && packed_w && out, "conv_gemm_tma: null pointer");
+  return conv_gemm_tma(g, in, packed_w, epi, out, (cudaStream_t)stream);
+}
+
+int nsg_conv_pack_many(int n, const float* const* w, void* const* packed, const int* ntaps,
+                       const long long* w_cin_stride, const long long* w_cout_stride, void* stream) {
+  NSG_REQUIRE(n == 0 || (w && packed && ntaps && w_cin_stride && w_cout_stride), "conv_pack_many: null pointer");
+  return conv_pack_many(n, w, packed, ntaps, w_cin_stride, w_cout_stride, (cudaStream_t)stream);
+}
+
+int nsg_conv_wgrad_tma(const nsg_conv_geom* g, const void* p, const void* q, float* dw_packed, float* q_colsum,
+                       void* stream) {
+  int rc = check_geom(g);
+  if (rc) return rc;
+  NSG_REQUIRE(p && q && dw_packed, "conv_wgrad_tma: null pointer");
+  return conv_wgrad_tma(g, p, q, dw_packed, q_colsum, (cudaStream_t)stream);
+}
+
+int nsg_wgrad_unpack_many(int n, const float* const* dw_packed, float* const* dw, const int* ntaps,
+                          const long long* w_cin_stride, const long long* w_cout_stride, void* stream) {
+  NSG_REQUIRE(n == 0 || (dw_packed && dw && ntaps && w_cin_stride && w_cout_stride), "wgrad_unpack_many: null pointer");
+  return wgrad_unpack_many(n, dw_packed, dw, ntaps, w_cin_stride, w_cout_stride, (cudaStream_t)stream);
 }
 
 }  // extern "C"

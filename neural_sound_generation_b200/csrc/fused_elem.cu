@@ -1,0 +1,300 @@
+// Streaming companions of the TMA convolution kernels for bf16 NHWC tensors with 64 channels: they produce the
+// OPERAND-READY activations the tensor-core kernels read (models.py:148-183):
+//   bn_act        v = [relu]( [res +] gamma*(h - mean)*invstd + beta ), BatchNorm2d statistics finalised in-kernel
+//                 from the (sum, sum of squares) the convolution epilogue accumulated (train) or from the running
+//                 statistics (eval); block 0 also publishes mean / invstd / scale / shift and updates the running
+//                 statistics exactly as torch does (momentum, unbiased variance, num_batches_tracked)
+//   bn_bwd        dh = gamma*invstd*(g - sum_g/M - xhat*sum_gx/M); dgamma += sum_gx; dbeta += sum_g;
+//                 dbias_prev += column sums of dh (the gradient of the bias of the convolution that feeds the BN)
+//   relu          out = max(x, 0)
+//   vq_bwd_stats  dz = g_st + coef*(z - zq) with the BatchNorm-backward reductions of the following layer fused
+// One thread owns 8 consecutive channels (16-byte accesses) of a grid-strided set of pixels, so per-channel
+// coefficients live in registers and per-channel reductions need two shuffles, one shared-memory and one global atomic.
+#include "common.cuh"
+
+namespace nsg {
+
+constexpr int FE_C = 64;
+
+__device__ __forceinline__ void fe_ld8(const __nv_bfloat16* p, float (&v)[8]) {
+  const uint4 r = __ldg(reinterpret_cast<const uint4*>(p));
+  const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    v[2 * i] = __uint_as_float(w[i] << 16);
+    v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+  }
+}
+__device__ __forceinline__ uint32_t fe_pack(float a, float b) {
+  __nv_bfloat162 t = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&t);
+}
+__device__ __forceinline__ void fe_st8(__nv_bfloat16* p, const float (&v)[8]) {
+  *reinterpret_cast<uint4*>(p) =
+      make_uint4(fe_pack(v[0], v[1]), fe_pack(v[2], v[3]), fe_pack(v[4], v[5]), fe_pack(v[6], v[7]));
+}
+// sum over the 32 pixel lanes of a CTA for each of the thread's 8 channels; result added to dst[c0 + i] by one thread
+template <typename OutT>
+__device__ __forceinline__ void fe_channel_reduce(float (&s)[8], float* sred, OutT* dst, int c0) {
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    s[i] += __shfl_xor_sync(0xffffffffu, s[i], 8);
+    s[i] += __shfl_xor_sync(0xffffffffu, s[i], 16);
+  }
+  const int tid = threadIdx.x;
+  if (tid < FE_C) sred[tid] = 0.f;
+  __syncthreads();
+  if ((tid & 31) < 8) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) atomicAdd(&sred[c0 + i], s[i]);
+  }
+  __syncthreads();
+  if (tid < FE_C) atomicAdd(dst + tid, (OutT)sred[tid]);
+  __syncthreads();
+}
+
+struct BnActArgs {
+  const __nv_bfloat16* h;
+  const __nv_bfloat16* res;
+  __nv_bfloat16* out;
+  const double* stats;           // train: [sum(64) | sumsq(64)]; null = eval (running statistics)
+  double count;
+  const float* gamma;
+  const float* beta;
+  float eps, momentum;
+  float* running_mean;
+  float* running_var;
+  long long* nbt;
+  float* mean;                   // published coefficients (nullable)
+  float* invstd;
+  float* scale;
+  float* shift;
+  int relu_out;
+  long long pixels;
+};
+
+__global__ void __launch_bounds__(256) bn_act_kernel(const BnActArgs a) {
+  __shared__ float sSc[FE_C], sSh[FE_C];
+  const int tid = threadIdx.x;
+  if (tid < FE_C) {
+    float mu, is;
+    if (a.stats) {
+      const double m = a.stats[tid] / a.count;
+      double var = a.stats[FE_C + tid] / a.count - m * m;
+      if (var < 0.0) var = 0.0;
+      mu = (float)m;
+      is = (float)(1.0 / sqrt(var + (double)a.eps));
+      if (blockIdx.x == 0 && a.running_mean) {
+        const double unbiased = a.count > 1.0 ? var * a.count / (a.count - 1.0) : var;
+        a.running_mean[tid] = (1.f - a.momentum) * a.running_mean[tid] + a.momentum * mu;
+        a.running_var[tid] = (1.f - a.momentum) * a.running_var[tid] + a.momentum * (float)unbiased;
+        if (tid == 0 && a.nbt) *a.nbt += 1;
+      }
+    } else {
+      mu = a.running_mean[tid];
+      is = 1.0f / sqrtf(a.running_var[tid] + a.eps);
+    }
+    const float sc = a.gamma[tid] * is;
+    const float sh = a.beta[tid] - mu * sc;
+    sSc[tid] = sc;
+    sSh[tid] = sh;
+    if (blockIdx.x == 0 && a.mean) {
+      a.mean[tid] = mu;
+      a.invstd[tid] = is;
+      a.scale[tid] = sc;
+      a.shift[tid] = sh;
+    }
+  }
+  __syncthreads();
+  const int c0 = (tid & 7) * 8;
+  float sc[8], sh[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    sc[i] = sSc[c0 + i];
+    sh[i] = sSh[c0 + i];
+  }
+  for (long long p = (long long)blockIdx.x * 32 + (tid >> 3); p < a.pixels; p += (long long)gridDim.x * 32) {
+    const long long o = p * FE_C + c0;
+    float v[8], r[8];
+    fe_ld8(a.h + o, v);
+    if (a.res) fe_ld8(a.res + o, r);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      float x = fmaf(sc[i], v[i], sh[i]);
+      if (a.res) x += r[i];
+      v[i] = a.relu_out ? fmaxf(x, 0.f) : x;
+    }
+    fe_st8(a.out + o, v);
+  }
+}
+
+struct BnBwdArgs {
+  const __nv_bfloat16* g;
+  const __nv_bfloat16* h;
+  __nv_bfloat16* dh;
+  const double* stats;           // [sum g (64) | sum g*xhat (64)]
+  double count;
+  const float* mean;
+  const float* invstd;
+  const float* gamma;
+  float* dgamma;
+  float* dbeta;
+  float* dbias_prev;             // nullable
+  long long pixels;
+};
+
+__global__ void __launch_bounds__(256) bn_bwd_kernel(const BnBwdArgs a) {
+  __shared__ float sred[FE_C];
+  const int tid = threadIdx.x;
+  if (blockIdx.x == 0 && tid < FE_C) {
+    if (a.dbeta) a.dbeta[tid] += (float)a.stats[tid];
+    if (a.dgamma) a.dgamma[tid] += (float)a.stats[FE_C + tid];
+  }
+  const int c0 = (tid & 7) * 8;
+  const float inv_count = (float)(1.0 / a.count);
+  float mu[8], is[8], k0[8], sg[8], sgx[8], col[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    mu[i] = __ldg(a.mean + c0 + i);
+    is[i] = __ldg(a.invstd + c0 + i);
+    k0[i] = __ldg(a.gamma + c0 + i) * is[i];
+    sg[i] = (float)a.stats[c0 + i] * inv_count;
+    sgx[i] = (float)a.stats[FE_C + c0 + i] * inv_count;
+    col[i] = 0.f;
+  }
+  for (long long p = (long long)blockIdx.x * 32 + (tid >> 3); p < a.pixels; p += (long long)gridDim.x * 32) {
+    const long long o = p * FE_C + c0;
+    float gv[8], hv[8];
+    fe_ld8(a.g + o, gv);
+    fe_ld8(a.h + o, hv);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float xhat = (hv[i] - mu[i]) * is[i];
+      gv[i] = k0[i] * (gv[i] - sg[i] - xhat * sgx[i]);
+      col[i] += gv[i];
+    }
+    fe_st8(a.dh + o, gv);
+  }
+  if (a.dbias_prev) fe_channel_reduce<float>(col, sred, a.dbias_prev, c0);
+}
+
+__global__ void __launch_bounds__(256)
+relu_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ out, long long nvec) {
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < nvec; i += (long long)gridDim.x * 256) {
+    float v[8];
+    fe_ld8(x + i * 8, v);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = fmaxf(v[j], 0.f);
+    fe_st8(out + i * 8, v);
+  }
+}
+
+// dz = g_st + coef*(z - zq);  stats[c] += sum dz, stats[64 + c] += sum dz * (h - mean)*invstd
+__global__ void __launch_bounds__(256)
+vq_bwd_stats_kernel(const __nv_bfloat16* __restrict__ g_st, const __nv_bfloat16* __restrict__ z,
+                    const __nv_bfloat16* __restrict__ zq, float coef, __nv_bfloat16* __restrict__ dz,
+                    const __nv_bfloat16* __restrict__ h, const float* __restrict__ mean,
+                    const float* __restrict__ invstd, double* __restrict__ stats, long long pixels) {
+  __shared__ float sred[FE_C];
+  const int tid = threadIdx.x;
+  const int c0 = (tid & 7) * 8;
+  float mu[8], is[8], s1[8], s2[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    mu[i] = stats ? __ldg(mean + c0 + i) : 0.f;
+    is[i] = stats ? __ldg(invstd + c0 + i) : 0.f;
+    s1[i] = s2[i] = 0.f;
+  }
+  for (long long p = (long long)blockIdx.x * 32 + (tid >> 3); p < pixels; p += (long long)gridDim.x * 32) {
+    const long long o = p * FE_C + c0;
+    float gv[8], zv[8], qv[8], hv[8];
+    fe_ld8(z + o, zv);
+    fe_ld8(zq + o, qv);
+    if (g_st) fe_ld8(g_st + o, gv);
+    if (stats) fe_ld8(h + o, hv);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float d = (g_st ? gv[i] : 0.f) + coef * (zv[i] - qv[i]);
+      gv[i] = d;
+      if (stats) {
+        s1[i] += d;
+        s2[i] = fmaf(d, (hv[i] - mu[i]) * is[i], s2[i]);
+      }
+    }
+    fe_st8(dz + o, gv);
+  }
+  if (stats) {
+    fe_channel_reduce<double>(s1, sred, stats, c0);
+    fe_channel_reduce<double>(s2, sred, stats + FE_C, c0);
+  }
+}
+
+static inline int fe_grid(long long pixels) {
+  long long blocks = (pixels + 31) / 32;
+  const long long cap = (long long)num_sms() * 8;
+  if (blocks > cap) blocks = cap;
+  return blocks < 1 ? 1 : (int)blocks;
+}
+
+}  // namespace nsg
+
+using namespace nsg;
+
+extern "C" {
+
+int nsg_bn_act64(const void* h, const void* res, void* out, const double* stats, double count, const float* gamma,
+                 const float* beta, float eps, float momentum, float* running_mean, float* running_var,
+                 long long* num_batches_tracked, float* mean, float* invstd, float* scale, float* shift, int relu_out,
+                 long long pixels, void* stream) {
+  NSG_REQUIRE(h && out && gamma && beta, "bn_act64: null tensor");
+  NSG_REQUIRE(stats || (running_mean && running_var), "bn_act64: eval mode needs the running statistics");
+  NSG_REQUIRE(!stats || count > 0, "bn_act64: count must be positive");
+  if (pixels == 0) return NSG_OK;
+  BnActArgs a{static_cast<const __nv_bfloat16*>(h), static_cast<const __nv_bfloat16*>(res),
+              static_cast<__nv_bfloat16*>(out), stats, count, gamma, beta, eps, momentum,
+              stats ? running_mean : running_mean, stats ? running_var : running_var, num_batches_tracked,
+              mean, invstd, scale, shift, relu_out, pixels};
+  bn_act_kernel<<<fe_grid(pixels), 256, 0, static_cast<cudaStream_t>(stream)>>>(a);
+  NSG_CHECK_LAUNCH("bn_act_kernel");
+  return NSG_OK;
+}
+
+int nsg_bn_bwd64(const void* g, const void* h, void* dh, const double* stats, double count, const float* mean,
+                 const float* invstd, const float* gamma, float* dgamma, float* dbeta, float* dbias_prev,
+                 long long pixels, void* stream) {
+  NSG_REQUIRE(g && h && dh && stats && mean && invstd && gamma, "bn_bwd64: null tensor");
+  NSG_REQUIRE(count > 0, "bn_bwd64: count must be positive");
+  if (pixels == 0) return NSG_OK;
+  BnBwdArgs a{static_cast<const __nv_bfloat16*>(g), static_cast<const __nv_bfloat16*>(h),
+              static_cast<__nv_bfloat16*>(dh), stats, count, mean, invstd, gamma, dgamma, dbeta, dbias_prev, pixels};
+  bn_bwd_kernel<<<fe_grid(pixels), 256, 0, static_cast<cudaStream_t>(stream)>>>(a);
+  NSG_CHECK_LAUNCH("bn_bwd_kernel");
+  return NSG_OK;
+}
+
+int nsg_relu64(const void* x, void* out, long long n, void* stream) {
+  NSG_REQUIRE(x && out && n % 8 == 0, "relu64: null tensor or element count not a multiple of 8");
+  if (n == 0) return NSG_OK;
+  long long blocks = (n / 8 + 255) / 256;
+  const long long cap = (long long)num_sms() * 8;
+  if (blocks > cap) blocks = cap;
+  relu_kernel<<<(int)blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(out), n / 8);
+  NSG_CHECK_LAUNCH("relu_kernel");
+  return NSG_OK;
+}
+
+int nsg_vq_bwd_stats64(const void* g_st, const void* z, const void* zq, float coef, void* dz, const void* h,
+                       const float* mean, const float* invstd, double* stats, long long pixels, void* stream) {
+  NSG_REQUIRE(z && zq && dz, "vq_bwd_stats64: null tensor");
+  NSG_REQUIRE(!stats || (h && mean && invstd), "vq_bwd_stats64: statistics need h, mean and invstd");
+  if (pixels == 0) return NSG_OK;
+  vq_bwd_stats_kernel<<<fe_grid(pixels), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(g_st), static_cast<const __nv_bfloat16*>(z),
+      static_cast<const __nv_bfloat16*>(zq), coef, static_cast<__nv_bfloat16*>(dz),
+      static_cast<const __nv_bfloat16*>(h), mean, invstd, stats, pixels);
+  NSG_CHECK_LAUNCH("vq_bwd_stats_kernel");
+  return NSG_OK;
+}
+
+}  // extern "C"

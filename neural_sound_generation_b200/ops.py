@@ -281,3 +281,138 @@ def gather_rows(table, indices, out):
     A.check(rc, 'nsg_gather_rows')
     launch_count += 1
     return out
+
+
+# ---------------------------------------------------------------------------------------------- TMA-fed bf16 path
+def _bf16(*ts):
+    for t in ts:
+        if t is not None and t.dtype != torch.bfloat16:
+            raise A.NsgError('the TMA kernels take bfloat16 tensors (got %s)' % t.dtype)
+
+
+def _ptr_array(ts):
+    return (C.c_void_p * len(ts))(*[t.data_ptr() for t in ts])
+
+
+def conv_pack_many(items):
+    """items: list of (w fp32, packed uint8 view of k*k*8192 bytes, ntaps, w_cin_stride, w_cout_stride); one launch."""
+    global launch_count
+    A.require_device()
+    if not items:
+        return
+    n = len(items)
+    rc = A.load().nsg_conv_pack_many(
+        n, _ptr_array([it[0] for it in items]), _ptr_array([it[1] for it in items]),
+        (C.c_int * n)(*[it[2] for it in items]), (C.c_longlong * n)(*[it[3] for it in items]),
+        (C.c_longlong * n)(*[it[4] for it in items]), A.stream_ptr())
+    A.check(rc, 'nsg_conv_pack_many')
+    launch_count += 1
+
+
+def conv_pack_tma(geom, w):
+    """bf16 weight image (k*k*8192 bytes) of ``w`` for the GEMM orientation in ``geom``."""
+    _cuda(w)
+    _contig(w, 'conv weight')
+    ntaps = geom.ksize * geom.ksize
+    packed = torch.empty(ntaps * 8192, dtype=torch.uint8, device=w.device)
+    conv_pack_many([(w, packed, ntaps, geom.w_cin_stride, geom.w_cout_stride)])
+    return packed
+
+
+def conv_gemm_tma(geom, x, packed, out, bias=None, add_src=None, mask_mode=MASK_NONE, mask_src=None, mscale=None,
+                  mshift=None, stats_mode=STATS_NONE, stats=None, xhat_src=None, mean=None, invstd=None):
+    global launch_count
+    A.require_device()
+    _cuda(x, packed, out, bias, add_src, mask_src, stats, xhat_src)
+    _bf16(x, out, add_src, mask_src, xhat_src)
+    _contig(x, 'conv input')
+    _contig(out, 'conv output')
+    epi = A.Epilogue(A.ptr(bias), A.ptr(add_src), mask_mode, A.ptr(mask_src), A.ptr(mscale), A.ptr(mshift),
+                     stats_mode, A.ptr(stats), A.ptr(xhat_src), A.ptr(mean), A.ptr(invstd), 0)
+    rc = A.load().nsg_conv_gemm_tma(C.byref(geom), A.ptr(x), A.ptr(packed), C.byref(epi), A.ptr(out), A.stream_ptr())
+    A.check(rc, 'nsg_conv_gemm_tma')
+    launch_count += 1
+    return out
+
+
+def conv_wgrad_tma(geom, p, q, dw_packed, q_colsum=None):
+    global launch_count
+    A.require_device()
+    _cuda(p, q, dw_packed, q_colsum)
+    _bf16(p, q)
+    _contig(p, 'wgrad P')
+    _contig(q, 'wgrad Q')
+    rc = A.load().nsg_conv_wgrad_tma(C.byref(geom), A.ptr(p), A.ptr(q), A.ptr(dw_packed), A.ptr(q_colsum),
+                                     A.stream_ptr())
+    A.check(rc, 'nsg_conv_wgrad_tma')
+    launch_count += 1
+
+
+def wgrad_unpack_many(items):
+    """items: list of (dw_packed fp32 [k*k,64,64], dw fp32 parameter-layout gradient, ntaps, w_cin_stride, w_cout_stride)."""
+    global launch_count
+    A.require_device()
+    if not items:
+        return
+    n = len(items)
+    rc = A.load().nsg_wgrad_unpack_many(
+        n, _ptr_array([it[0] for it in items]), _ptr_array([it[1] for it in items]),
+        (C.c_int * n)(*[it[2] for it in items]), (C.c_longlong * n)(*[it[3] for it in items]),
+        (C.c_longlong * n)(*[it[4] for it in items]), A.stream_ptr())
+    A.check(rc, 'nsg_wgrad_unpack_many')
+    launch_count += 1
+
+
+def bn_act64(h, out, gamma, beta, stats=None, count=1.0, res=None, relu_out=True, eps=1e-5, momentum=0.1,
+             running_mean=None, running_var=None, nbt=None, coef=None):
+    """coef: optional (mean, invstd, scale, shift) fp32 [64] tensors to publish."""
+    global launch_count
+    A.require_device()
+    _cuda(h, out, gamma, beta, stats, res, running_mean, running_var)
+    _bf16(h, out, res)
+    if h.shape[-1] != 64:
+        raise A.NsgError('bn_act64 serves 64-channel tensors')
+    cf = coef if coef is not None else (None, None, None, None)
+    rc = A.load().nsg_bn_act64(A.ptr(h), A.ptr(res), A.ptr(out), A.ptr(stats), float(count), A.ptr(gamma),
+                               A.ptr(beta), eps, momentum, A.ptr(running_mean), A.ptr(running_var), A.ptr(nbt),
+                               A.ptr(cf[0]), A.ptr(cf[1]), A.ptr(cf[2]), A.ptr(cf[3]), int(bool(relu_out)),
+                               h.numel() // 64, A.stream_ptr())
+    A.check(rc, 'nsg_bn_act64')
+    launch_count += 1
+    return out
+
+
+def bn_bwd64(g, h, dh, stats, count, mean, invstd, gamma, dgamma=None, dbeta=None, dbias_prev=None):
+    global launch_count
+    A.require_device()
+    _cuda(g, h, dh, stats, mean, invstd, gamma)
+    _bf16(g, h, dh)
+    rc = A.load().nsg_bn_bwd64(A.ptr(g), A.ptr(h), A.ptr(dh), A.ptr(stats), float(count), A.ptr(mean),
+                               A.ptr(invstd), A.ptr(gamma), A.ptr(dgamma), A.ptr(dbeta), A.ptr(dbias_prev),
+                               h.numel() // 64, A.stream_ptr())
+    A.check(rc, 'nsg_bn_bwd64')
+    launch_count += 1
+    return dh
+
+
+def relu64(x, out):
+    global launch_count
+    A.require_device()
+    _cuda(x, out)
+    _bf16(x, out)
+    rc = A.load().nsg_relu64(A.ptr(x), A.ptr(out), x.numel(), A.stream_ptr())
+    A.check(rc, 'nsg_relu64')
+    launch_count += 1
+    return out
+
+
+def vq_bwd_stats64(g_st, z, zq, coef, dz, h=None, mean=None, invstd=None, stats=None):
+    global launch_count
+    A.require_device()
+    _cuda(g_st, z, zq, dz, h, stats)
+    _bf16(g_st, z, zq, dz, h)
+    rc = A.load().nsg_vq_bwd_stats64(A.ptr(g_st), A.ptr(z), A.ptr(zq), float(coef), A.ptr(dz), A.ptr(h),
+                                     A.ptr(mean), A.ptr(invstd), A.ptr(stats), z.numel() // 64, A.stream_ptr())
+    A.check(rc, 'nsg_vq_bwd_stats64')
+    launch_count += 1
+    return dz

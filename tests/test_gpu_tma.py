@@ -1,0 +1,231 @@
+"""Op-level parity of the TMA-fed tcgen05 convolution kernels and their streaming companions (bf16, 64 channels),
+called through the C ABI, against CPU fp64 restatements fed the SAME bf16-rounded operands (SURVEY.md H7 form (ii)).
+
+Run on the B200 box: python -m pytest tests -m gpu
+"""
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+from helpers import relerr, nhwc, nchw
+
+pytestmark = pytest.mark.gpu
+
+if torch.cuda.is_available():
+    import neural_sound_generation_b200 as nsg  # noqa: F401
+    from neural_sound_generation_b200 import ops
+
+DEV = 'cuda'
+BF = torch.bfloat16
+OUT_TOL = 4e-3       # bf16 storage of the result: 2^-9 relative per element
+ACC_TOL = 2e-4       # fp32-accumulated quantities (statistics, weight gradients)
+
+
+def _rand(rng, *shape):
+    return torch.tensor(rng.standard_normal(shape).astype(np.float32))
+
+
+def _r16(t):
+    return t.bfloat16().float()
+
+
+def _geoms(B, H, W, k, s, p, transposed):
+    """(fwd geom, dgrad geom, wgrad geom, OH, OW) for a 64 -> 64 layer, as engine.Engine builds them."""
+    C = 64
+    if transposed:
+        OH, OW = (H - 1) * s - 2 * p + k, (W - 1) * s - 2 * p + k
+        fwd = ops.conv_geom(B, H, W, C, OH, OW, C, k, s, p, 1, C * k * k, k * k, ops.BF16)
+        dgr = ops.conv_geom(B, OH, OW, C, H, W, C, k, s, p, 0, k * k, C * k * k, ops.BF16)
+        wgr = ops.conv_geom(B, OH, OW, C, H, W, C, k, s, p, 0, k * k, C * k * k, ops.BF16)
+    else:
+        OH, OW = (H + 2 * p - k) // s + 1, (W + 2 * p - k) // s + 1
+        fwd = ops.conv_geom(B, H, W, C, OH, OW, C, k, s, p, 0, k * k, C * k * k, ops.BF16)
+        dgr = ops.conv_geom(B, OH, OW, C, H, W, C, k, s, p, 1, C * k * k, k * k, ops.BF16)
+        wgr = ops.conv_geom(B, H, W, C, OH, OW, C, k, s, p, 0, k * k, C * k * k, ops.BF16)
+    return fwd, dgr, wgr, OH, OW
+
+
+TMA_CASES = [
+    # (k, s, p, transposed, H, W, B)
+    (3, 1, 1, False, 7, 9, 3),
+    (3, 1, 1, False, 20, 64, 2),
+    (1, 1, 0, False, 5, 6, 2),
+    (1, 1, 0, False, 20, 64, 1),
+    (4, 2, 1, False, 12, 10, 2),
+    (4, 2, 1, False, 40, 128, 1),
+    (4, 2, 1, False, 9, 7, 1),         # odd input extents: ragged parity views
+    (4, 2, 1, True, 5, 7, 2),
+    (4, 2, 1, True, 20, 64, 1),
+    (3, 1, 1, False, 20, 215, 1),      # inference width (config 5)
+]
+
+
+@pytest.mark.parametrize('case', TMA_CASES)
+def test_conv_tma_forward_dgrad_wgrad(case):
+    k, s, p, transposed, H, W, B = case
+    C = 64
+    rng = np.random.RandomState(abs(hash(case)) % 2 ** 31)
+    x = _r16(_rand(rng, B, C, H, W))
+    w = _r16(_rand(rng, C, C, k, k) * 0.2)
+    bias = _rand(rng, C)
+    fwd, dgr, wgr, OH, OW = _geoms(B, H, W, k, s, p, transposed)
+    xd = x.double().requires_grad_(True)
+    wd = w.double().requires_grad_(True)
+    yref = F.conv_transpose2d(xd, wd, bias.double(), s, p) if transposed else F.conv2d(xd, wd, bias.double(), s, p)
+    assert tuple(yref.shape[2:]) == (OH, OW)
+    xg = nhwc(x).to(DEV).to(BF)
+    wg, bg = w.to(DEV), bias.to(DEV)
+    # forward (+ BatchNorm moment statistics)
+    y = torch.empty((B, OH, OW, C), dtype=BF, device=DEV)
+    stats = torch.zeros(2 * C, dtype=torch.float64, device=DEV)
+    ops.conv_gemm_tma(fwd, xg, ops.conv_pack_tma(fwd, wg), y, bias=bg, stats_mode=ops.STATS_MOMENTS, stats=stats)
+    torch.cuda.synchronize()
+    assert relerr(nchw(y.float()), yref) < OUT_TOL, 'fwd'
+    sref = torch.cat([yref.sum((0, 2, 3)), (yref ** 2).sum((0, 2, 3))])
+    assert relerr(stats, sref) < ACC_TOL, 'stats'
+    # data and weight gradients
+    gy = _r16(_rand(rng, *yref.shape))
+    yref.backward(gy.double())
+    gyg = nhwc(gy).to(DEV).to(BF)
+    dx = torch.empty((B, H, W, C), dtype=BF, device=DEV)
+    ops.conv_gemm_tma(dgr, gyg, ops.conv_pack_tma(dgr, wg), dx)
+    torch.cuda.synchronize()
+    assert relerr(nchw(dx.float()), xd.grad) < OUT_TOL, 'dgrad'
+    dwp = torch.zeros((k * k, C, C), dtype=torch.float32, device=DEV)
+    colsum = torch.zeros(C, dtype=torch.float32, device=DEV)
+    if transposed:
+        ops.conv_wgrad_tma(wgr, gyg, xg, dwp, q_colsum=colsum)       # P = dy, Q = x
+        cref = x.double().sum((0, 2, 3))
+    else:
+        ops.conv_wgrad_tma(wgr, xg, gyg, dwp, q_colsum=colsum)       # P = x, Q = dy
+        cref = gy.double().sum((0, 2, 3))
+    dw = torch.zeros_like(wg)
+    ops.wgrad_unpack_many([(dwp, dw, k * k, wgr.w_cin_stride, wgr.w_cout_stride)])
+    torch.cuda.synchronize()
+    assert relerr(dw, wd.grad) < ACC_TOL, 'wgrad'
+    assert relerr(colsum, cref) < ACC_TOL, 'colsum'
+    # accumulation semantics: a second call doubles the packed image
+    if transposed:
+        ops.conv_wgrad_tma(wgr, gyg, xg, dwp)
+    else:
+        ops.conv_wgrad_tma(wgr, xg, gyg, dwp)
+    dw2 = torch.zeros_like(wg)
+    ops.wgrad_unpack_many([(dwp, dw2, k * k, wgr.w_cin_stride, wgr.w_cout_stride)])
+    torch.cuda.synchronize()
+    assert relerr(dw2, 2 * wd.grad) < ACC_TOL, 'wgrad accumulate'
+
+
+def test_conv_tma_epilogue_mask_add_bnbwd_stats():
+    rng = np.random.RandomState(7)
+    B, C, H, W = 2, 64, 6, 5
+    gy = _r16(_rand(rng, B, C, H, W))
+    w = _r16(_rand(rng, C, C, 3, 3) * 0.1)
+    add = _r16(_rand(rng, B, C, H, W))
+    h = _r16(_rand(rng, B, C, H, W))
+    scale, shift = 1 + 0.2 * _rand(rng, C), 0.3 * _rand(rng, C)
+    mean, invstd = 0.1 * _rand(rng, C), 1 + 0.1 * _rand(rng, C).abs()
+    xin = torch.zeros(B, C, H, W, dtype=torch.float64, requires_grad=True)
+    F.conv2d(xin, w.double(), None, 1, 1).backward(gy.double())
+    g = xin.grad + add.double()
+    mask = (h.double() * scale.double()[None, :, None, None] + shift.double()[None, :, None, None]) > 0
+    g = g * mask
+    xhat = (h.double() - mean.double()[None, :, None, None]) * invstd.double()[None, :, None, None]
+    sref = torch.cat([g.sum((0, 2, 3)), (g * xhat).sum((0, 2, 3))])
+    _, dgr, _, _, _ = _geoms(B, H, W, 3, 1, 1, False)
+    packed = ops.conv_pack_tma(dgr, w.to(DEV))
+    stats = torch.zeros(2 * C, dtype=torch.float64, device=DEV)
+    hg = nhwc(h).to(DEV).to(BF)
+    addg = nhwc(add).to(DEV).to(BF)
+    keep = (scale.to(DEV), shift.to(DEV), mean.to(DEV), invstd.to(DEV))
+    out = torch.empty((B, H, W, C), dtype=BF, device=DEV)
+    ops.conv_gemm_tma(dgr, nhwc(gy).to(DEV).to(BF), packed, out, add_src=addg, mask_mode=ops.MASK_AFFINE, mask_src=hg,
+                      mscale=keep[0], mshift=keep[1], stats_mode=ops.STATS_BNBWD, stats=stats, xhat_src=hg,
+                      mean=keep[2], invstd=keep[3])
+    torch.cuda.synchronize()
+    assert relerr(nchw(out.float()), g) < OUT_TOL
+    assert relerr(stats, sref) < 5e-4
+    out2 = torch.empty_like(out)
+    ops.conv_gemm_tma(dgr, nhwc(gy).to(DEV).to(BF), packed, out2, mask_mode=ops.MASK_POS, mask_src=hg)
+    torch.cuda.synchronize()
+    assert relerr(nchw(out2.float()), xin.grad * (h.double() > 0)) < OUT_TOL
+
+
+def test_conv_tma_rejects_other_shapes():
+    g = ops.conv_geom(1, 4, 4, 32, 4, 4, 64, 3, 1, 1, 0, 9, 288, ops.BF16)
+    x = torch.zeros((1, 4, 4, 32), dtype=BF, device=DEV)
+    out = torch.zeros((1, 4, 4, 64), dtype=BF, device=DEV)
+    with pytest.raises(nsg._cabi.NsgError):
+        ops.conv_gemm_tma(g, x, torch.zeros(9 * 8192, dtype=torch.uint8, device=DEV), out)
+
+
+@pytest.mark.parametrize('train', [True, False])
+@pytest.mark.parametrize('res', [False, True])
+def test_bn_act64(train, res):
+    rng = np.random.RandomState(11)
+    M, C = 1000, 64
+    h = _r16(_rand(rng, M, C) * 1.5 + 0.3)
+    r = _r16(_rand(rng, M, C).abs())
+    gamma, beta = 1 + 0.1 * _rand(rng, C), 0.1 * _rand(rng, C)
+    rm, rv = 0.1 * _rand(rng, C), 1 + 0.1 * _rand(rng, C).abs()
+    hd = h.double()
+    if train:
+        mu, var = hd.mean(0), hd.var(0, unbiased=False)
+    else:
+        mu, var = rm.double(), rv.double()
+    yref = (hd - mu) / torch.sqrt(var + 1e-5) * gamma.double() + beta.double()
+    if res:
+        yref = yref + r.double()
+    yref = F.relu(yref)
+    stats = torch.cat([hd.sum(0), (hd ** 2).sum(0)]).to(DEV) if train else None
+    rmg, rvg = rm.to(DEV), rv.to(DEV)
+    nbt = torch.zeros((), dtype=torch.int64, device=DEV)
+    coef = [torch.zeros(C, device=DEV) for _ in range(4)]
+    out = torch.empty((M, C), dtype=BF, device=DEV)
+    ops.bn_act64(h.to(DEV).to(BF), out, gamma.to(DEV), beta.to(DEV), stats=stats, count=M,
+                 res=r.to(DEV).to(BF) if res else None, relu_out=True, running_mean=rmg, running_var=rvg, nbt=nbt,
+                 coef=coef)
+    torch.cuda.synchronize()
+    assert relerr(out.float(), yref) < OUT_TOL
+    assert relerr(coef[0], mu) < 1e-5 and relerr(coef[1], 1 / torch.sqrt(var + 1e-5)) < 1e-5
+    if train:
+        assert nbt.item() == 1
+        assert relerr(rmg, 0.9 * rm.double() + 0.1 * mu) < 1e-5
+        assert relerr(rvg, 0.9 * rv.double() + 0.1 * hd.var(0, unbiased=True)) < 1e-5
+    else:
+        assert nbt.item() == 0 and torch.equal(rmg.cpu(), rm)
+
+
+def test_bn_bwd64_relu64_vq_bwd_stats64():
+    rng = np.random.RandomState(12)
+    M, C = 777, 64
+    h = _r16(_rand(rng, M, C))
+    g = _r16(_rand(rng, M, C))
+    gamma = 1 + 0.1 * _rand(rng, C)
+    hd = h.double().requires_grad_(True)
+    mu, var = hd.mean(0), hd.var(0, unbiased=False)
+    y = (hd - mu) / torch.sqrt(var + 1e-5) * gamma.double()
+    y.backward(g.double())
+    mu_d, is_d = mu.detach(), (1 / torch.sqrt(var + 1e-5)).detach()
+    xhat = (h.double() - mu_d) * is_d
+    stats = torch.cat([g.double().sum(0), (g.double() * xhat).sum(0)]).to(DEV)
+    dh = torch.empty((M, C), dtype=BF, device=DEV)
+    dgamma, dbeta, dbias = (torch.zeros(C, device=DEV) for _ in range(3))
+    ops.bn_bwd64(g.to(DEV).to(BF), h.to(DEV).to(BF), dh, stats, M, mu_d.float().to(DEV), is_d.float().to(DEV),
+                 gamma.to(DEV), dgamma, dbeta, dbias)
+    torch.cuda.synchronize()
+    assert relerr(dh.float(), hd.grad) < OUT_TOL
+    assert relerr(dgamma, (g.double() * xhat).sum(0)) < 1e-5 and relerr(dbeta, g.double().sum(0)) < 1e-5
+    assert dbias.abs().max().item() < 0.05 * g.abs().sum(0).max().item()      # analytically zero
+    out = torch.empty((M, C), dtype=BF, device=DEV)
+    ops.relu64(h.to(DEV).to(BF), out)
+    assert torch.equal(out.float().cpu(), F.relu(h))
+    z, zq = _r16(_rand(rng, M, C)), _r16(_rand(rng, M, C))
+    dz = torch.empty((M, C), dtype=BF, device=DEV)
+    st = torch.zeros(2 * C, dtype=torch.float64, device=DEV)
+    ops.vq_bwd_stats64(g.to(DEV).to(BF), z.to(DEV).to(BF), zq.to(DEV).to(BF), 0.25, dz, h=h.to(DEV).to(BF),
+                       mean=mu_d.float().to(DEV), invstd=is_d.float().to(DEV), stats=st)
+    torch.cuda.synchronize()
+    dref = g.double() + 0.25 * (z.double() - zq.double())
+    assert relerr(dz.float(), dref) < OUT_TOL
+    assert relerr(st, torch.cat([dref.sum(0), (dref * xhat).sum(0)])) < ACC_TOL
