@@ -106,7 +106,7 @@ def main():
     ap.add_argument('--steps', type=int, default=20)
     ap.add_argument('--warmup', type=int, default=5)
     ap.add_argument('--impl', default='ours')
-    ap.add_argument('--mode', default=os.environ.get('NSG_BENCH_MODE', 'fp32'))
+    ap.add_argument('--mode', default=os.environ.get('NSG_BENCH_MODE', 'tma'), choices=['tma', 'bf16', 'tc32', 'fp32'])
     ap.add_argument('--no-cpu-baseline', action='store_true')
     args = ap.parse_args()
     rank = int(os.environ.get('RANK', '0'))
@@ -141,7 +141,9 @@ def main():
     with torch.no_grad():
         model.codebook.embedding.weight.normal_()                  # trained-like codebook
     model = model.to(dev)
-    if args.mode == 'bf16':        # bf16 activations, tcgen05 convolutions (bf16 x bf16), tcgen05 split-bf16 VQ search
+    if args.mode == 'tma':         # bf16 operand-ready activations, TMA-fed persistent tcgen05 convolutions (production path)
+        model.act_dtype, model.conv_impl, model.vq_mode = torch.bfloat16, 2, 1
+    elif args.mode == 'bf16':      # bf16 activations, register-staged tcgen05 convolutions, tcgen05 split-bf16 VQ search
         model.act_dtype, model.conv_impl, model.vq_mode = torch.bfloat16, 1, 1
     elif args.mode == 'tc32':      # fp32 activations, tcgen05 convolutions with split-bf16 operands (3 passes)
         model.act_dtype, model.conv_impl, model.vq_mode = torch.float32, 1, 1
@@ -208,13 +210,21 @@ def main():
     x = torch.randn(B_PER_GPU, 20, 64, DIM, device=dev).to(model.act_dtype)
     w = dict(model.named_parameters())['encoder.4.block.1.weight'].detach()
     bias = dict(model.named_parameters())['encoder.4.block.1.bias'].detach()
+    if args.mode == 'tma':
+        Pd = {n: q.detach() for n, q in model.named_parameters()}
+        kctx = eng.begin(x, True)
+        eng._pack(kctx, Pd)
+        xr = x.relu()
+        kfn = lambda i: eng._conv_fwd(kctx, Pd, 'encoder.4.block.1', xr)
+    else:
+        kfn = lambda i: eng._conv_fwd(x, w, bias, 3, 1, 1, False, ops.prologue(ops.PRO_RELU))
     for _ in range(3):
-        eng._conv_fwd(x, w, bias, 3, 1, 1, False, ops.prologue(ops.PRO_RELU))
-    kms = timed(lambda i: eng._conv_fwd(x, w, bias, 3, 1, 1, False, ops.prologue(ops.PRO_RELU)), 20)
+        kfn(0)
+    kms = timed(kfn, 20)
     kflop = 2.0 * x.numel() // DIM * DIM * DIM * 9
     achieved = kflop / (kms / 1e3) / 1e12
     roof = dict(bound='tensor', achieved=achieved, peak=pk['tf_burst'], unit='TFLOP/s', frac=achieved / pk['tf_burst'],
-                traffic=None, kernel='conv3x3 64->64 fwd (%s)' % ('tcgen05 bf16' if model.conv_impl else 'CUDA-core fp32'),
+                traffic=None, kernel='conv3x3 64->64 fwd (%s)' % ({0: 'CUDA-core fp32', 1: 'tcgen05 bf16, register-staged', 2: 'tcgen05 bf16, TMA-fed persistent'}[model.conv_impl]),
                 peak_source=pk['src'], step_frac_of_tensor_peak=TRAIN_GFLOP * world / (ms / 1e3) / 1e3 / (pk['tf_sust'] * world))
     if rank != 0:
         if world > 1:
@@ -226,7 +236,7 @@ def main():
         cpu = dict(value=r['value'], unit='mel-frames/s', cores=r['cores'], kind='port', sample=r['sample'])
     out = dict(metric='vqvae_train_mel_frames_per_sec', value=value, unit='mel-frames/s', n_gpus=world,
                steps=args.steps, warmup=max(3, args.warmup), ms_per_step=ms, higher_is_better=True, scaling='weak',
-               vs_baseline=None, dtype='bf16' if args.mode == 'bf16' else 'f32', data='synthetic',
+               vs_baseline=None, dtype='bf16' if args.mode in ('bf16', 'tma') else 'f32', data='synthetic',
                config=dict(config, l2='256 MiB flush between timed steps; 8 rotating input batches',
                            mode=args.mode, bn='local batch statistics per rank' if world > 1 else 'batch statistics'),
                e2e=dict(value=frames / (ms_e2e / 1e3), unit='mel-frames/s', ms_per_step=ms_e2e,

@@ -93,7 +93,8 @@ typedef struct {
   const void* xhat_src;     /* NSG_STATS_BNBWD: pre-BN tensor h, same shape as out */
   const float* mean;        /* [cout] */
   const float* invstd;      /* [cout] */
-  int tanh_out;             /* 1: out = tanh(v)  (models.py:183) */
+  int tanh_out;             /* output activation: 0 none, 1 tanh (models.py:183), 2 ReLU (nsg_conv_gemm_tma only:
+                             * the in-place ReLU that opens the next ResBlock, models.py:149) */
 } nsg_epilogue;
 
 /* CUDA-core fp32-accumulate kernel, any shape.  `impl` must be 0 (kept for ABI stability). */
@@ -151,7 +152,7 @@ int nsg_wgrad_unpack_many(int n, const float* const* dw_packed, float* const* dw
  *                  (NSG_STATS_BNBWD); dgamma += sum_gx; dbeta += sum_g; dbias_prev (nullable) += column sums of dh
  *   nsg_relu64     out = max(x, 0)
  *   nsg_vq_bwd_stats64  dz = g_st + coef*(z - zq)  (vq_st backward clone + commitment term, vector_quantization.py:50-52,
- *                  train.py:133) with the NSG_STATS_BNBWD reductions of the BatchNorm that produced z fused (stats nullable) */
+ *                  train.py:133) with the NSG_STATS_BNBWD reductions of the BatchNorm that produced z fused (g_st, zq, stats nullable) */
 int nsg_bn_act64(const void* h, const void* res, void* out, const double* stats, double count, const float* gamma,
                  const float* beta, float eps, float momentum, float* running_mean, float* running_var,
                  long long* num_batches_tracked, float* mean, float* invstd, float* scale, float* shift, int relu_out,

@@ -294,6 +294,10 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
             }
           }
         }
+        if (epi.tanh_out == 2) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) x[j] = fmaxf(x[j], 0.f);
+        }
         if (valid) {
 #pragma unroll
           for (int g8 = 0; g8 < 4; ++g8) st8bf(out + o + ch0 + g8 * 8, &x[g8 * 8]);
@@ -397,7 +401,8 @@ int conv_gemm_tma(const nsg_conv_geom* cg, const void* in, const void* packed, c
               "conv_gemm_tma: tensors must be 16-byte aligned");
   EpiArgs e{};
   if (int rc = make_epi(epi, &e)) return rc;
-  NSG_REQUIRE(!e.tanh_out, "conv_gemm_tma: no tanh epilogue (cout == 1 layer is served by the streaming kernel)");
+  NSG_REQUIRE(e.tanh_out == 0 || e.tanh_out == 2,
+              "conv_gemm_tma: output activation must be none (0) or ReLU (2); tanh belongs to the cout == 1 layer");
   TapGeom phases[4];
   const int np = build_phases(cg, phases);
   TmaConvParams P{};

@@ -209,12 +209,12 @@ vq_bwd_stats_kernel(const __nv_bfloat16* __restrict__ g_st, const __nv_bfloat16*
     const long long o = p * FE_C + c0;
     float gv[8], zv[8], qv[8], hv[8];
     fe_ld8(z + o, zv);
-    fe_ld8(zq + o, qv);
+    if (zq) fe_ld8(zq + o, qv);
     if (g_st) fe_ld8(g_st + o, gv);
     if (stats) fe_ld8(h + o, hv);
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-      const float d = (g_st ? gv[i] : 0.f) + coef * (zv[i] - qv[i]);
+      const float d = (g_st ? gv[i] : 0.f) + coef * (zv[i] - (zq ? qv[i] : 0.f));
       gv[i] = d;
       if (stats) {
         s1[i] += d;
@@ -286,7 +286,7 @@ int nsg_relu64(const void* x, void* out, long long n, void* stream) {
 
 int nsg_vq_bwd_stats64(const void* g_st, const void* z, const void* zq, float coef, void* dz, const void* h,
                        const float* mean, const float* invstd, double* stats, long long pixels, void* stream) {
-  NSG_REQUIRE(z && zq && dz, "vq_bwd_stats64: null tensor");
+  NSG_REQUIRE(z && dz, "vq_bwd_stats64: null tensor");
   NSG_REQUIRE(!stats || (h && mean && invstd), "vq_bwd_stats64: statistics need h, mean and invstd");
   if (pixels == 0) return NSG_OK;
   vq_bwd_stats_kernel<<<fe_grid(pixels), 256, 0, static_cast<cudaStream_t>(stream)>>>(

@@ -247,6 +247,22 @@ class Engine(object):
             return self._conv_dgrad(g_a0, P['encoder.0.weight'], 4, 2, 1, False, x.shape[1:3])
         return None
 
+    def bottleneck_bwd(self, ctx, g_st, z_e, z_q, coef):
+        """dz = g_st + coef*(z_e - z_q): straight-through clone + commitment term (vector_quantization.py:50-52)."""
+        dz = torch.empty_like(z_e)
+        ops.vq_backward_inputs(g_st, z_e, z_q, coef, dz)
+        return dz
+
+    def bottleneck_bwd_sum(self, ctx, g_st, g_ze):
+        if g_ze is None:
+            return g_st
+        dz = torch.empty_like(g_st)
+        ops.vq_backward_inputs(g_st, g_ze.to(g_st.dtype), None, 1.0, dz)
+        return dz
+
+    def finish_backward(self, ctx, G):
+        pass
+
     # ------------------------------------------------------------------ bottleneck (models.py:127-142)
     def quantize(self, z_e, codebook, want_codes=True, sqerr=None):
         n = z_e.numel() // z_e.shape[-1]

@@ -1,0 +1,317 @@
+"""bf16 train / inference schedule of the VQ-VAE over the TMA-fed tcgen05 kernels (``csrc/conv_tma.cu``).
+
+Same role and method names as ``engine.Engine`` (the host-side mirror of autograd over
+/root/reference/src/models.py:145-216), different data contract: every activation tensor that feeds a
+convolution is stored OPERAND-READY in bf16 NHWC -- BatchNorm + ReLU already applied (``bn_act64``), the
+ResBlock's in-place leading ReLU already applied by whoever produced the tensor -- so the tensor core reads
+what the TMA unit wrote, with no register staging.  Per layer the schedule is
+
+    conv (tcgen05, epilogue: bias + BN moment sums)  ->  bn_act64 (finalise statistics, normalise, ReLU, residual)
+
+and in reverse
+
+    dgrad (tcgen05, epilogue: + skip gradient, ReLU mask, BN-backward sums)  ->  bn_bwd64  ->  wgrad (tcgen05).
+
+Weight images (bf16, UMMA K-major) of all ten 64->64 layers are re-packed by ONE launch per step; their
+gradients accumulate in packed fp32 images that ONE launch folds into the reference-layout ``.grad`` tensors.
+The single-channel ends (encoder.0, decoder.6) run on the streaming CUDA-core kernels of ``conv_c1.cu``.
+"""
+import torch
+
+from . import ops
+from .ops import MASK_POS, STATS_MOMENTS, STATS_BNBWD
+from .engine import BN_EPS, BN_MOMENTUM, BN_LAYERS, BN_INDEX, RES_BLOCKS, Ctx, _out_hw
+
+BF = torch.bfloat16
+
+# (state_dict prefix, ksize, stride, pad, transposed) of the 64 -> 64 layers
+TC_LAYERS = ([('encoder.3', 4, 2, 1, False)]
+             + [(b + s, k, 1, p, False) for b in RES_BLOCKS for s, k, p in (('.block.1', 3, 1), ('.block.4', 1, 0))]
+             + [('decoder.3', 4, 2, 1, True)])
+
+
+class _Layer(object):
+    __slots__ = ('name', 'k', 's', 'p', 'tr', 'wf', 'wd', 'dwp', 'wci_f', 'wco_f', 'wci_d', 'wco_d', 'wci_g', 'wco_g')
+
+
+class EngineTMA(object):
+    """Schedule object; caches the packed weight / gradient images per model (keyed by the flat parameter buffer)."""
+
+    def __init__(self, input_dim, dim, z_dim, vq_mode=1):
+        if dim != 64:
+            raise ops.A.NsgError('the TMA engine serves dim == 64 (got %d)' % dim)
+        self.cin0, self.dim, self.k = input_dim, dim, z_dim
+        self.act_dtype = BF
+        self.vq_mode = vq_mode
+        self.layers = None
+        self._key = None
+
+    # ------------------------------------------------------------------ packed images
+    def _prepare(self, P):
+        key = tuple(P[n + '.weight'].data_ptr() for n, *_ in TC_LAYERS)
+        if self._key == key:
+            return
+        dev = P['encoder.3.weight'].device
+        D = self.dim
+        ntaps_total = sum(k * k for _, k, *_ in TC_LAYERS)
+        self.wimg = torch.empty(2 * ntaps_total * 8192, dtype=torch.uint8, device=dev)
+        self.dwp = torch.zeros(ntaps_total * D * D, dtype=torch.float32, device=dev)
+        self.layers = {}
+        self.pack_items, self.unpack_items = [], []
+        ow, og = 0, 0
+        for name, k, s, p, tr in TC_LAYERS:
+            L = _Layer()
+            L.name, L.k, L.s, L.p, L.tr = name, k, s, p, tr
+            w = P[name + '.weight']
+            kk = k * k
+            if tr:      # ConvTranspose2d weight (Cin, Cout, k, k)
+                L.wci_f, L.wco_f = D * kk, kk           # forward contracts Cin
+                L.wci_d, L.wco_d = kk, D * kk           # data gradient contracts Cout
+                L.wci_g, L.wco_g = kk, D * kk           # wgrad: a = dy channel (Cout), b = x channel (Cin)
+            else:       # Conv2d weight (Cout, Cin, k, k)
+                L.wci_f, L.wco_f = kk, D * kk
+                L.wci_d, L.wco_d = D * kk, kk
+                L.wci_g, L.wco_g = kk, D * kk           # a = x channel (Cin), b = dy channel (Cout)
+            L.wf = self.wimg[ow:ow + kk * 8192]
+            L.wd = self.wimg[ow + kk * 8192:ow + 2 * kk * 8192]
+            ow += 2 * kk * 8192
+            L.dwp = self.dwp[og:og + kk * D * D]
+            og += kk * D * D
+            self.pack_items += [(w, L.wf, kk, L.wci_f, L.wco_f), (w, L.wd, kk, L.wci_d, L.wco_d)]
+            self.layers[name] = L
+        self._key = key
+
+    def _unpack_items(self, G):
+        return [(L.dwp, G[L.name + '.weight'], L.k * L.k, L.wci_g, L.wco_g) for L in self.layers.values()]
+
+    # ------------------------------------------------------------------ helpers
+    def _bn(self, ctx, name):
+        i = BN_INDEX[name]
+        co = ctx.coef[i]
+        return dict(coef=(co[0], co[1], co[2], co[3]), mean=co[0], invstd=co[1], fstats=ctx.stats[i, 0],
+                    bstats=ctx.stats[i, 1])
+
+    def begin(self, x_nhwc, training):
+        ctx = Ctx()
+        ctx.training = training
+        ctx.saved = {}
+        dev = x_nhwc.device
+        ctx.coef = torch.empty((len(BN_LAYERS), 4, self.dim), dtype=torch.float32, device=dev)
+        ctx.stats = torch.zeros((len(BN_LAYERS), 2, 2 * self.dim), dtype=torch.float64, device=dev)
+        ctx.packed = False
+        return ctx
+
+    def _pack(self, ctx, P):
+        if not ctx.packed:
+            self._prepare(P)
+            ops.conv_pack_many(self.pack_items)
+            ctx.packed = True
+
+    def _fwd_geom(self, L, x):
+        b, h, w, c = x.shape
+        oh, ow = _out_hw(h, w, L.k, L.s, L.p, L.tr)
+        return ops.conv_geom(b, h, w, c, oh, ow, c, L.k, L.s, L.p, 1 if L.tr else 0, L.wci_f, L.wco_f, ops.BF16), oh, ow
+
+    def _conv_fwd(self, ctx, P, name, x, stats=None, relu_out=False):
+        L = self.layers[name]
+        g, oh, ow = self._fwd_geom(L, x)
+        out = torch.empty((x.shape[0], oh, ow, self.dim), dtype=BF, device=x.device)
+        ops.conv_gemm_tma(g, x, L.wf, out, bias=P[name + '.bias'],
+                          stats_mode=STATS_MOMENTS if stats is not None else 0, stats=stats, relu_out=relu_out)
+        return out
+
+    def _conv_dgrad(self, name, dy, in_hw, **epi):
+        L = self.layers[name]
+        b, oh, ow, c = dy.shape
+        ih, iw = in_hw
+        g = ops.conv_geom(b, oh, ow, c, ih, iw, c, L.k, L.s, L.p, 0 if L.tr else 1, L.wci_d, L.wco_d, ops.BF16)
+        out = torch.empty((b, ih, iw, c), dtype=BF, device=dy.device)
+        ops.conv_gemm_tma(g, dy, L.wd, out, **epi)
+        return out
+
+    def _conv_wgrad(self, name, x, dy, q_colsum=None):
+        """x = the layer's (operand-ready) forward input, dy = gradient of its output."""
+        L = self.layers[name]
+        b, h, w, c = x.shape
+        _, oh, ow, _ = dy.shape
+        if L.tr:        # P = dy gathered over x's pixels, Q = x
+            g = ops.conv_geom(b, oh, ow, c, h, w, c, L.k, L.s, L.p, 0, L.wci_g, L.wco_g, ops.BF16)
+            ops.conv_wgrad_tma(g, dy, x, L.dwp, q_colsum=q_colsum)
+        else:           # P = x gathered over dy's pixels, Q = dy
+            g = ops.conv_geom(b, h, w, c, oh, ow, c, L.k, L.s, L.p, 0, L.wci_g, L.wco_g, ops.BF16)
+            ops.conv_wgrad_tma(g, x, dy, L.dwp, q_colsum=q_colsum)
+
+    def _bn_act(self, ctx, P, Bufs, name, h, res=None, relu_out=True):
+        bn = self._bn(ctx, name)
+        out = torch.empty_like(h)
+        n = h.numel() // self.dim
+        if ctx.training:
+            ops.bn_act64(h, out, P[name + '.weight'], P[name + '.bias'], stats=bn['fstats'], count=n, res=res,
+                         relu_out=relu_out, eps=BN_EPS, momentum=BN_MOMENTUM,
+                         running_mean=Bufs[name + '.running_mean'], running_var=Bufs[name + '.running_var'],
+                         nbt=Bufs[name + '.num_batches_tracked'], coef=bn['coef'])
+        else:
+            ops.bn_act64(h, out, P[name + '.weight'], P[name + '.bias'], stats=None, res=res, relu_out=relu_out,
+                         eps=BN_EPS, running_mean=Bufs[name + '.running_mean'],
+                         running_var=Bufs[name + '.running_var'], coef=bn['coef'])
+        return out
+
+    def _bn_bwd(self, ctx, P, G, name, g, h, dbias_prev):
+        bn = self._bn(ctx, name)
+        dh = torch.empty_like(h)
+        ops.bn_bwd64(g, h, dh, bn['bstats'], h.numel() // self.dim, bn['mean'], bn['invstd'], P[name + '.weight'],
+                     dgamma=G[name + '.weight'], dbeta=G[name + '.bias'], dbias_prev=dbias_prev)
+        return dh
+
+    # ------------------------------------------------------------------ ResBlock (models.py:145-158)
+    def resblock_fwd(self, ctx, P, Bufs, name, r, relu_out):
+        """r = relu(block input) (operand-ready).  Returns relu(y) or y, with y = r + BN5(Conv1x1(relu(BN2(Conv3x3(r)))))."""
+        tr = ctx.training
+        bn2, bn5 = self._bn(ctx, name + '.block.2'), self._bn(ctx, name + '.block.5')
+        h1 = self._conv_fwd(ctx, P, name + '.block.1', r, stats=bn2['fstats'] if tr else None)
+        v1 = self._bn_act(ctx, P, Bufs, name + '.block.2', h1, relu_out=True)
+        h2 = self._conv_fwd(ctx, P, name + '.block.4', v1, stats=bn5['fstats'] if tr else None)
+        y = self._bn_act(ctx, P, Bufs, name + '.block.5', h2, res=r, relu_out=relu_out)
+        ctx.saved[name] = (r, h1, v1, h2)
+        return y
+
+    def resblock_bwd(self, ctx, P, G, name, g_y, prev_block=None):
+        """g_y: gradient wrt the block output y with this block's BN5 backward sums already accumulated by its
+        producer.  Returns the gradient wrt the block's pre-ReLU input; when ``prev_block`` names the ResBlock
+        that produced that input, its BN5 backward sums are accumulated by the same epilogue."""
+        r, h1, v1, h2 = ctx.saved[name]
+        hw = r.shape[1:3]
+        bn2 = self._bn(ctx, name + '.block.2')
+        g_h2 = self._bn_bwd(ctx, P, G, name + '.block.5', g_y, h2, G[name + '.block.4.bias'])
+        self._conv_wgrad(name + '.block.4', v1, g_h2)
+        g_v1 = self._conv_dgrad(name + '.block.4', g_h2, hw, mask_mode=MASK_POS, mask_src=v1,
+                                stats_mode=STATS_BNBWD, stats=bn2['bstats'], xhat_src=h1, mean=bn2['mean'],
+                                invstd=bn2['invstd'])
+        g_h1 = self._bn_bwd(ctx, P, G, name + '.block.2', g_v1, h1, G[name + '.block.1.bias'])
+        self._conv_wgrad(name + '.block.1', r, g_h1)
+        epi = dict(add_src=g_y, mask_mode=MASK_POS, mask_src=r)
+        if prev_block is not None:
+            pbn = self._bn(ctx, prev_block + '.block.5')
+            epi.update(stats_mode=STATS_BNBWD, stats=pbn['bstats'], xhat_src=ctx.saved[prev_block][3],
+                       mean=pbn['mean'], invstd=pbn['invstd'])
+        return self._conv_dgrad(name + '.block.1', g_h1, hw, **epi)
+
+    # ------------------------------------------------------------------ encoder / decoder (models.py:164-184)
+    def encoder_fwd(self, ctx, P, Bufs, x):
+        """x (B,H,W,Cin0) bf16 -> z_e (B,H/4,W/4,64) bf16 (raw: the quantiser's input)."""
+        self._pack(ctx, P)
+        tr = ctx.training
+        bn1 = self._bn(ctx, 'encoder.1')
+        b, h, w, cin = x.shape
+        w0 = P['encoder.0.weight']
+        oh, ow = _out_hw(h, w, 4, 2, 1, False)
+        a0 = torch.empty((b, oh, ow, self.dim), dtype=BF, device=x.device)
+        g = ops.conv_geom(b, h, w, cin, oh, ow, self.dim, 4, 2, 1, 0, 16, cin * 16, ops.BF16)
+        ops.conv_gemm(g, x, w0, a0, bias=P['encoder.0.bias'], stats_mode=STATS_MOMENTS if tr else 0,
+                      stats=bn1['fstats'] if tr else None)
+        v0 = self._bn_act(ctx, P, Bufs, 'encoder.1', a0, relu_out=True)
+        r4 = self._conv_fwd(ctx, P, 'encoder.3', v0, relu_out=True)            # relu(a1): ResBlock's in-place ReLU
+        r5 = self.resblock_fwd(ctx, P, Bufs, 'encoder.4', r4, relu_out=True)
+        z_e = self.resblock_fwd(ctx, P, Bufs, 'encoder.5', r5, relu_out=False)
+        ctx.x, ctx.a0, ctx.v0 = x, a0, v0
+        return z_e
+
+    def decoder_fwd(self, ctx, P, Bufs, z_q):
+        """z_q (B,h,w,64) bf16 -> x_tilde (B,4h,4w,Cin0) (tanh applied)."""
+        self._pack(ctx, P)
+        tr = ctx.training
+        rq = torch.empty_like(z_q)
+        ops.relu64(z_q, rq)
+        r1 = self.resblock_fwd(ctx, P, Bufs, 'decoder.0', rq, relu_out=True)
+        rd = self.resblock_fwd(ctx, P, Bufs, 'decoder.1', r1, relu_out=True)   # + decoder.2 ReLU
+        bn4 = self._bn(ctx, 'decoder.4')
+        u0 = self._conv_fwd(ctx, P, 'decoder.3', rd, stats=bn4['fstats'] if tr else None)
+        v4 = self._bn_act(ctx, P, Bufs, 'decoder.4', u0, relu_out=True)
+        b, h, w, _ = v4.shape
+        w6 = P['decoder.6.weight']
+        cout = w6.shape[1]
+        oh, ow = _out_hw(h, w, 4, 2, 1, True)
+        xt = torch.empty((b, oh, ow, cout), dtype=BF, device=v4.device)
+        g = ops.conv_geom(b, h, w, self.dim, oh, ow, cout, 4, 2, 1, 1, cout * 16, 16, ops.BF16)
+        ops.conv_gemm(g, v4, w6, xt, bias=P['decoder.6.bias'], tanh_out=True)
+        ctx.rd, ctx.u0, ctx.v4 = rd, u0, v4
+        return xt
+
+    def decoder_bwd(self, ctx, P, G, dpre):
+        """dpre (B,H',W',Cin0): gradient wrt the pre-tanh output.  Returns the gradient wrt z_q."""
+        rd, u0, v4 = ctx.rd, ctx.u0, ctx.v4
+        bn4 = self._bn(ctx, 'decoder.4')
+        if dpre.dtype != BF:
+            dpre = dpre.to(BF)
+        b, oh, ow, cout = dpre.shape
+        _, h, w, _ = v4.shape
+        w6 = P['decoder.6.weight']
+        # decoder.6 weight gradient: P = dpre gathered over v4's pixels, Q = v4
+        g = ops.conv_geom(b, oh, ow, cout, h, w, self.dim, 4, 2, 1, 0, 16, cout * 16, ops.BF16)
+        ops.conv_wgrad(g, dpre, v4, G['decoder.6.weight'])
+        ops.colsum(dpre, G['decoder.6.bias'])
+        # decoder.6 data gradient, masked by the ReLU, with decoder.4's BN-backward sums
+        g = ops.conv_geom(b, oh, ow, cout, h, w, self.dim, 4, 2, 1, 0, 16, cout * 16, ops.BF16)
+        g_v4 = torch.empty_like(v4)
+        ops.conv_gemm(g, dpre, w6, g_v4, mask_mode=MASK_POS, mask_src=v4, stats_mode=STATS_BNBWD, stats=bn4['bstats'],
+                      xhat_src=u0, mean=bn4['mean'], invstd=bn4['invstd'])
+        g_u0 = self._bn_bwd(ctx, P, G, 'decoder.4', g_v4, u0, G['decoder.3.bias'])
+        self._conv_wgrad('decoder.3', rd, g_u0)
+        pbn = self._bn(ctx, 'decoder.1.block.5')
+        g_d1 = self._conv_dgrad('decoder.3', g_u0, rd.shape[1:3], mask_mode=MASK_POS, mask_src=rd,
+                                stats_mode=STATS_BNBWD, stats=pbn['bstats'], xhat_src=ctx.saved['decoder.1'][3],
+                                mean=pbn['mean'], invstd=pbn['invstd'])
+        g_d0 = self.resblock_bwd(ctx, P, G, 'decoder.1', g_d1, prev_block='decoder.0')
+        return self.resblock_bwd(ctx, P, G, 'decoder.0', g_d0)
+
+    def bottleneck_bwd(self, ctx, g_st, z_e, z_q, coef):
+        """dz = g_st + coef*(z_e - z_q) with encoder.5's BN5 backward sums."""
+        bn = self._bn(ctx, 'encoder.5.block.5')
+        dz = torch.empty_like(z_e)
+        ops.vq_bwd_stats64(g_st, z_e, z_q, coef, dz, h=ctx.saved['encoder.5'][3], mean=bn['mean'],
+                           invstd=bn['invstd'], stats=bn['bstats'])
+        return dz
+
+    def bottleneck_bwd_sum(self, ctx, g_st, g_ze):
+        """dz = g_st + g_ze (either may be None) with encoder.5's BN5 backward sums (generic autograd path)."""
+        bn = self._bn(ctx, 'encoder.5.block.5')
+        a, b = (g_st, g_ze) if g_ze is not None else (None, g_st)
+        dz = torch.empty_like(b)
+        ops.vq_bwd_stats64(a, b, None, 1.0, dz, h=ctx.saved['encoder.5'][3], mean=bn['mean'], invstd=bn['invstd'],
+                           stats=bn['bstats'])
+        return dz
+
+    def encoder_bwd(self, ctx, P, G, g_ze, need_dx=False):
+        x, a0, v0 = ctx.x, ctx.a0, ctx.v0
+        bn1 = self._bn(ctx, 'encoder.1')
+        g_r5 = self.resblock_bwd(ctx, P, G, 'encoder.5', g_ze, prev_block='encoder.4')
+        g_a1 = self.resblock_bwd(ctx, P, G, 'encoder.4', g_r5)
+        self._conv_wgrad('encoder.3', v0, g_a1, q_colsum=G['encoder.3.bias'])
+        g_v0 = self._conv_dgrad('encoder.3', g_a1, v0.shape[1:3], mask_mode=MASK_POS, mask_src=v0,
+                                stats_mode=STATS_BNBWD, stats=bn1['bstats'], xhat_src=a0, mean=bn1['mean'],
+                                invstd=bn1['invstd'])
+        g_a0 = self._bn_bwd(ctx, P, G, 'encoder.1', g_v0, a0, G['encoder.0.bias'])
+        b, h, w, cin = x.shape
+        _, oh, ow, _ = a0.shape
+        g = ops.conv_geom(b, h, w, cin, oh, ow, self.dim, 4, 2, 1, 0, 16, cin * 16, ops.BF16)
+        ops.conv_wgrad(g, x, g_a0, G['encoder.0.weight'])
+        dx = None
+        if need_dx:
+            dx = torch.empty_like(x)
+            g = ops.conv_geom(b, oh, ow, self.dim, h, w, cin, 4, 2, 1, 1, cin * 16, 16, ops.BF16)
+            ops.conv_gemm(g, g_a0, P['encoder.0.weight'], dx)
+        return dx
+
+    def finish_backward(self, ctx, G):
+        """Fold the packed weight-gradient images into the reference-layout gradients (one launch) and clear them."""
+        ops.wgrad_unpack_many(self._unpack_items(G))
+        self.dwp.zero_()
+
+    # ------------------------------------------------------------------ bottleneck (models.py:127-142)
+    def quantize(self, z_e, codebook, want_codes=True, sqerr=None):
+        n = z_e.numel() // z_e.shape[-1]
+        idx = torch.empty((n,), dtype=torch.int64, device=z_e.device)
+        codes = torch.empty_like(z_e) if want_codes else None
+        mode = self.vq_mode if ops.vq_mode_serves(codebook.shape[0], codebook.shape[1], self.vq_mode) else 0
+        ops.vq_forward(z_e, codebook, idx, codes, sqerr, mode=mode)
+        return idx, codes

@@ -16,6 +16,7 @@ from torch.autograd import Function
 
 from . import ops
 from .engine import Engine, RES_BLOCKS
+from .engine_tma import EngineTMA
 from .vector_quantization import vq, vq_st
 
 
@@ -177,6 +178,14 @@ class VQVAE(nn.Module):
 
     # ------------------------------------------------------------------ plumbing
     def engine(self):
+        if self.conv_impl == 2:     # bf16 TMA-fed tcgen05 schedule (caches its packed weight images on the model)
+            if self.act_dtype != torch.bfloat16:
+                raise ops.A.NsgError('conv_impl = 2 (TMA engine) needs act_dtype = torch.bfloat16')
+            eng = self.__dict__.get('_eng_tma')
+            if eng is None or eng.vq_mode != self.vq_mode:
+                eng = EngineTMA(self.input_dim, self.dim, self.z_dim, self.vq_mode)
+                self.__dict__['_eng_tma'] = eng
+            return eng
         return Engine(self.input_dim, self.dim, self.z_dim, self.act_dtype, self.conv_impl, self.vq_mode)
 
     def _named(self):
@@ -285,10 +294,10 @@ class VQVAE(nn.Module):
         ops.recon_loss(xt32.view(b, h, wt), c3, sums[0:1], dpre)
         g_st = eng.decoder_bwd(ectx, P, G, dpre.view(b, h, wt, 1))
         n_lat = z_e.numel()
-        dz = torch.empty_like(z_e)
-        ops.vq_backward_inputs(g_st, z_e, z_q, 2.0 * beta / n_lat, dz)   # ST clone + beta * d commit / d z_e
+        dz = eng.bottleneck_bwd(ectx, g_st, z_e, z_q, 2.0 * beta / n_lat)  # ST clone + beta * d commit / d z_e
         ops.scatter_add(z_q, idx, G['codebook.embedding.weight'], alpha=2.0 / n_lat, sub=z_e)  # d loss_vq / d e
         eng.encoder_bwd(ectx, P, G, dz)
+        eng.finish_backward(ectx, G)
         # (python-scalar multiplies keep this CUDA-graph capturable: no host tensor is created)
         l_rec, l_vq = sums[0] * (1.0 / (b * h * w)), sums[1] * (1.0 / z_e.numel())
         losses = torch.stack([l_rec, l_vq, l_vq])
@@ -328,13 +337,10 @@ class _VQVAEFn(Function):
         dpre = torch.empty_like(ctx.xt)
         ops.tanh_bwd(_nhwc(g_xt.float()), ctx.xt, dpre)
         g_st = eng.decoder_bwd(ectx, P, G, dpre)
-        if g_ze is not None:
-            dz = torch.empty_like(g_st)
-            ops.vq_backward_inputs(g_st, _nhwc(g_ze).to(act), None, 1.0, dz)
-        else:
-            dz = g_st
+        dz = eng.bottleneck_bwd_sum(ectx, g_st, _nhwc(g_ze).to(act) if g_ze is not None else None)
         if g_zq is not None:
             ops.scatter_add(_nhwc(g_zq.float()), ctx.idx, G['codebook.embedding.weight'], alpha=1.0)
         g_x = eng.encoder_bwd(ectx, P, G, dz, need_dx=ctx.need_dx)
+        eng.finish_backward(ectx, G)
         gx = _nchw_view(g_x.float()) if g_x is not None else None
         return (None, gx) + tuple(G[n] for n in ctx.names)

@@ -320,7 +320,8 @@ def conv_pack_tma(geom, w):
 
 
 def conv_gemm_tma(geom, x, packed, out, bias=None, add_src=None, mask_mode=MASK_NONE, mask_src=None, mscale=None,
-                  mshift=None, stats_mode=STATS_NONE, stats=None, xhat_src=None, mean=None, invstd=None):
+                  mshift=None, stats_mode=STATS_NONE, stats=None, xhat_src=None, mean=None, invstd=None,
+                  relu_out=False):
     global launch_count
     A.require_device()
     _cuda(x, packed, out, bias, add_src, mask_src, stats, xhat_src)
@@ -328,7 +329,7 @@ def conv_gemm_tma(geom, x, packed, out, bias=None, add_src=None, mask_mode=MASK_
     _contig(x, 'conv input')
     _contig(out, 'conv output')
     epi = A.Epilogue(A.ptr(bias), A.ptr(add_src), mask_mode, A.ptr(mask_src), A.ptr(mscale), A.ptr(mshift),
-                     stats_mode, A.ptr(stats), A.ptr(xhat_src), A.ptr(mean), A.ptr(invstd), 0)
+                     stats_mode, A.ptr(stats), A.ptr(xhat_src), A.ptr(mean), A.ptr(invstd), 2 if relu_out else 0)
     rc = A.load().nsg_conv_gemm_tma(C.byref(geom), A.ptr(x), A.ptr(packed), C.byref(epi), A.ptr(out), A.stream_ptr())
     A.check(rc, 'nsg_conv_gemm_tma')
     launch_count += 1

@@ -7,13 +7,13 @@ nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > gp
 timeout 1200 python -m pytest tests -m gpu -q -p no:cacheprovider --timeout 300 > gpurun_out/${TAG}_pytest.log 2>&1
 echo "pytest exit $?"; grep -E "^(FAILED|ERROR)|passed|failed" gpurun_out/${TAG}_pytest.log | cut -c1-220
 timeout 300 python __graft_entry__.py smoke > gpurun_out/${TAG}_smoke.log 2>&1; echo "smoke exit $?"; tail -n 1 gpurun_out/${TAG}_smoke.log | cut -c1-300
-for MODE in fp32 tc32 bf16; do
-  EXTRA="--no-cpu-baseline"; [ $MODE = bf16 ] && EXTRA=""
+for MODE in ${MODES:-fp32 tc32 bf16 tma}; do
+  EXTRA="--no-cpu-baseline"; [ $MODE = tma ] && EXTRA=""
   timeout 600 python bench.py --steps 20 --warmup 5 --mode $MODE $EXTRA > gpurun_out/${TAG}_bench_$MODE.log 2>&1
   echo "bench $MODE exit $?"; tail -n 1 gpurun_out/${TAG}_bench_$MODE.log | cut -c1-1800
 done
 timeout 300 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/${TAG}_bench_ref.log 2>&1; echo "ref exit $?"; tail -n 1 gpurun_out/${TAG}_bench_ref.log | cut -c1-600
-M=${NCU_MODE:-bf16}
+M=${NCU_MODE:-tma}
 timeout 600 python bench.py --steps 2 --warmup 3 --no-cpu-baseline --mode $M > gpurun_out/${TAG}_plain.log 2>&1 &&
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv \
    --log-file gpurun_out/${TAG}_launches_$M.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline --mode $M > gpurun_out/${TAG}_ncu.log 2>&1
