@@ -134,6 +134,24 @@ int nsg_conv_wgrad_tc(const nsg_conv_geom* g, const void* p, const nsg_prologue*
  *   nsg_conv_wgrad_tma     dw_packed[t][a][b] (fp32, k*k*64*64, 16-byte aligned) += sum_m P[gather0(m,t),a]*Q[m,b];
  *                          q_colsum (nullable) as in nsg_conv_wgrad
  *   nsg_wgrad_unpack_many  dw[t + a*w_cin_stride + b*w_cout_stride] += dw_packed[t][a][b] for up to 24 layers */
+/* The single-channel ends of the network (models.py:165 Conv2d(1 -> 64, 4, 2, 1), models.py:182
+ * ConvTranspose2d(64 -> 1, 4, 2, 1)) on the tensor cores, bf16 tensors, geometry k4 / s2 / p1 only (else
+ * NSG_E_UNSUPPORTED; the CUDA-core nsg_conv_gemm / nsg_conv_wgrad serve every other shape).  packed_w are 8 KB images
+ * written by nsg_conv_pack_many with ntaps = -1 (rows = the 64 channels, K = the 16 taps: nsg_c1_conv_tc) or
+ * ntaps = -2 (rows = the 16 taps, K = the 64 channels: nsg_c1_convT_tc); w_cin_stride / w_cout_stride there are the
+ * element strides of w along K and along rows.
+ *   nsg_c1_conv_tc   out[m, 0..63] = epilogue(bias + sum_t in1[gather0(m, t)] * w[t, 0..63])  (encoder.0 fwd, decoder.6 dgrad)
+ *   nsg_c1_convT_tc  out1[m] = [tanh](bias + sum_{valid t} sum_c in[gather1(m, t), c] * w[c, t])   (decoder.6 fwd)
+ *   nsg_c1_wgrad_tc  dw[t + b*w_cout_stride] += sum_m p1[gather0(m, t)] * q[m, b]; q_colsum[b] += sum_m q[m, b] */
+int nsg_c1_conv_tc(const nsg_conv_geom* g, const void* in, const void* packed_w, const nsg_epilogue* epi, void* out,
+                   void* stream);
+int nsg_c1_convT_tc(const nsg_conv_geom* g, const void* in, const void* packed_w, const float* bias, int tanh_out,
+                    void* out, void* stream);
+int nsg_c1_wgrad_tc(const nsg_conv_geom* g, const void* p, const void* q, float* dw, float* q_colsum, void* stream);
+
+/* development aid: enable != 0 makes CTA 0 of every following nsg_conv_gemm_tma launch write clock64 stamps of its
+ * pipeline milestones; stamps32 (nullable, HOST pointer to 32 values) receives the last launch's stamps (synchronises). */
+int nsg_debug_timeline(int enable, unsigned long long* stamps32);
 int nsg_conv_pack_many(int n, const float* const* w, void* const* packed, const int* ntaps,
                        const long long* w_cin_stride, const long long* w_cout_stride, void* stream);
 int nsg_conv_gemm_tma(const nsg_conv_geom* g, const void* in, const void* packed_w, const nsg_epilogue* epi, void* out,

@@ -23,7 +23,8 @@ EXPORTS = [
     'nsg_adam_step', 'nsg_tanh_bwd', 'nsg_gather_rows', 'nsg_vq_workspace_bytes',
     'nsg_conv_pack_bytes', 'nsg_conv_pack_weights', 'nsg_conv_gemm_tc', 'nsg_conv_wgrad_tc',
     'nsg_conv_pack_many', 'nsg_conv_gemm_tma', 'nsg_conv_wgrad_tma', 'nsg_wgrad_unpack_many',
-    'nsg_bn_act64', 'nsg_bn_bwd64', 'nsg_relu64', 'nsg_vq_bwd_stats64',
+    'nsg_bn_act64', 'nsg_bn_bwd64', 'nsg_relu64', 'nsg_vq_bwd_stats64', 'nsg_debug_timeline',
+    'nsg_c1_conv_tc', 'nsg_c1_convT_tc', 'nsg_c1_wgrad_tc',
 ]
 
 
@@ -73,6 +74,10 @@ def load():
     lib.nsg_conv_gemm_tc.argtypes = [C.POINTER(ConvGeom), vp, vp, C.POINTER(Prologue), C.POINTER(Epilogue), vp, i, vp]
     lib.nsg_conv_wgrad_tc.argtypes = [C.POINTER(ConvGeom), vp, C.POINTER(Prologue), vp, C.POINTER(Prologue), vp, vp,
                                       i, vp]
+    lib.nsg_debug_timeline.argtypes = [i, vp]
+    lib.nsg_c1_conv_tc.argtypes = [C.POINTER(ConvGeom), vp, vp, C.POINTER(Epilogue), vp, vp]
+    lib.nsg_c1_convT_tc.argtypes = [C.POINTER(ConvGeom), vp, vp, vp, i, vp, vp]
+    lib.nsg_c1_wgrad_tc.argtypes = [C.POINTER(ConvGeom), vp, vp, vp, vp, vp]
     lib.nsg_conv_pack_many.argtypes = [i, vp, vp, vp, vp, vp, vp]
     lib.nsg_conv_gemm_tma.argtypes = [C.POINTER(ConvGeom), vp, vp, C.POINTER(Epilogue), vp, vp]
     lib.nsg_conv_wgrad_tma.argtypes = [C.POINTER(ConvGeom), vp, vp, vp, vp, vp]

@@ -45,6 +45,12 @@ int conv_wgrad_tc(const nsg_conv_geom* cg, const void* p, const nsg_prologue* pr
 
 int conv_gemm_tma(const nsg_conv_geom* cg, const void* in, const void* packed, const nsg_epilogue* epi, void* out,
                   cudaStream_t stream);
+int debug_timeline(int enable, unsigned long long* host_out);
+int conv_c1_tc(const nsg_conv_geom* cg, const void* in, const void* packed, const nsg_epilogue* epi, void* out,
+               cudaStream_t stream);
+int convT_c1_tc(const nsg_conv_geom* cg, const void* in, const void* packed, const float* bias, int tanh_out, void* out,
+                cudaStream_t stream);
+int wgrad_c1_tc(const nsg_conv_geom* cg, const void* p, const void* q, float* dw, float* q_colsum, cudaStream_t stream);
 int conv_pack_many(int n, const float* const* w, void* const* dst, const int* ntaps, const long long* in_stride,
                    const long long* out_stride, cudaStream_t stream);
 int conv_wgrad_tma(const nsg_conv_geom* cg, const void* p, const void* q, float* dwp, float* q_colsum,
@@ -144,6 +150,31 @@ int nsg_conv_gemm_tma(const nsg_conv_geom* g, const void* in, const void* packed
   NSG_REQUIRE(in && packed_w && out, "conv_gemm_tma: null pointer");
   return conv_gemm_tma(g, in, packed_w, epi, out, (cudaStream_t)stream);
 }
+
+int nsg_c1_conv_tc(const nsg_conv_geom* g, const void* in, const void* packed_w, const nsg_epilogue* epi, void* out,
+                   void* stream) {
+  int rc = check_geom(g);
+  if (rc) return rc;
+  NSG_REQUIRE(in && packed_w && out, "c1_conv_tc: null pointer");
+  return conv_c1_tc(g, in, packed_w, epi, out, (cudaStream_t)stream);
+}
+
+int nsg_c1_convT_tc(const nsg_conv_geom* g, const void* in, const void* packed_w, const float* bias, int tanh_out,
+                    void* out, void* stream) {
+  int rc = check_geom(g);
+  if (rc) return rc;
+  NSG_REQUIRE(in && packed_w && out, "c1_convT_tc: null pointer");
+  return convT_c1_tc(g, in, packed_w, bias, tanh_out, out, (cudaStream_t)stream);
+}
+
+int nsg_c1_wgrad_tc(const nsg_conv_geom* g, const void* p, const void* q, float* dw, float* q_colsum, void* stream) {
+  int rc = check_geom(g);
+  if (rc) return rc;
+  NSG_REQUIRE(p && q && dw, "c1_wgrad_tc: null pointer");
+  return wgrad_c1_tc(g, p, q, dw, q_colsum, (cudaStream_t)stream);
+}
+
+int nsg_debug_timeline(int enable, unsigned long long* stamps32) { return debug_timeline(enable, stamps32); }
 
 int nsg_conv_pack_many(int n, const float* const* w, void* const* packed, const int* ntaps,
                        const long long* w_cin_stride, const long long* w_cout_stride, void* stream) {

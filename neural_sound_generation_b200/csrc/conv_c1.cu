@@ -277,9 +277,15 @@ c1_wgrad_kernel(const T* __restrict__ P, const T* __restrict__ Q, float* __restr
 
 // ---------------------------------------------------------------------------------------------- dispatch
 // 1 when the call was served here, 0 when the shape is not one of the single-channel layers, < 0 on error
+int conv_gemm_c1_fast(const nsg_conv_geom* cg, const void* in, const float* w, const Pro& pro, const EpiArgs& e,
+                      void* out, cudaStream_t stream);
+int conv_wgrad_c1_fast(const nsg_conv_geom* cg, const void* p, const Pro& pp, const void* q, const Pro& pq, float* dw,
+                       float* q_colsum, cudaStream_t stream);
+
 int conv_gemm_c1(const nsg_conv_geom* cg, const void* in, const float* w, const Pro& pro, const EpiArgs& e, void* out,
                  cudaStream_t stream) {
   if (cg->ksize > 4) return 0;
+  if (const int served = conv_gemm_c1_fast(cg, in, w, pro, e, out, stream)) return served;
   C1Geom g{cg->batch, cg->in_h, cg->in_w, cg->out_h, cg->out_w, cg->ksize, cg->stride, cg->pad, 0};
   const long long M = (long long)cg->batch * cg->out_h * cg->out_w;
   if (cg->gather == 0 && cg->cin == 1 && cg->cout == C1_C && pro.mode == NSG_PRO_NONE && !e.tanh_out) {
@@ -309,6 +315,7 @@ int conv_gemm_c1(const nsg_conv_geom* cg, const void* in, const float* w, const 
 int conv_wgrad_c1(const nsg_conv_geom* cg, const void* p, const Pro& pp, const void* q, const Pro& pq, float* dw,
                   float* q_colsum, cudaStream_t stream) {
   if (!(cg->cin == 1 && cg->cout == C1_C && cg->ksize <= 4 && pp.mode == NSG_PRO_NONE)) return 0;
+  if (const int served = conv_wgrad_c1_fast(cg, p, pp, q, pq, dw, q_colsum, stream)) return served;
   C1Geom g{cg->batch, cg->in_h, cg->in_w, cg->out_h, cg->out_w, cg->ksize, cg->stride, cg->pad, cg->w_cout_stride};
   const long long M = (long long)cg->batch * cg->out_h * cg->out_w;
   long long blocks = (M + 31) / 32;

@@ -31,7 +31,7 @@ constexpr uint32_t TM_A_BYTES = TM_M * 128;     // one activation box
 constexpr uint32_t TM_W_BYTES = TM_C * 128;     // one tap's weight image (bf16, K-major SWIZZLE_128B)
 constexpr int TM_MAX_STAGES = 8;
 constexpr int TM_MAX_TAPS = 16;
-constexpr uint32_t TM_SMEM_LIMIT = 227 * 1024;
+constexpr uint32_t TM_SMEM_LIMIT = 224 * 1024;      // dynamic part; the kernels also hold ~2 KB of static shared memory
 
 struct TmaPhase {
   int sub_h, sub_w;              // output sub-grid of this stride phase
@@ -47,14 +47,20 @@ struct TmaConvParams {
   int in_stride;                 // 1: one tensor map; 2: four parity maps
   int box_w, box_h, log2_bw;
   int nphases, total_tiles, nw, stages;
+  unsigned long long* dbg;       // optional clock64 stamps of CTA 0 (nsg_debug_timeline), null in production
   TmaPhase ph[4];
 };
+
+__device__ __forceinline__ void tm_stamp(unsigned long long* dbg, int slot) {
+  if (dbg && blockIdx.x == 0) dbg[slot] = (unsigned long long)clock64();
+}
 
 // ---------------------------------------------------------------------------------------------- packing
 struct PackItem {
   const float* w;
   uint8_t* dst;
   int ntaps;
+  int kmax, rmax;                // K indices >= kmax and rows >= rmax are written as zeros (small operands)
   long long in_stride, out_stride;
 };
 struct PackList {
@@ -73,7 +79,9 @@ __global__ void __launch_bounds__(256) conv_pack_many_kernel(const __grid_consta
   if (t >= p.ntaps) return;
   float v[8];
 #pragma unroll
-  for (int i = 0; i < 8; ++i) v[i] = __ldg(p.w + t + (long long)(c * 8 + i) * p.in_stride + (long long)r * p.out_stride);
+  for (int i = 0; i < 8; ++i)
+    v[i] = (c * 8 + i < p.kmax && r < p.rmax)
+               ? __ldg(p.w + t + (long long)(c * 8 + i) * p.in_stride + (long long)r * p.out_stride) : 0.f;
   *reinterpret_cast<uint4*>(p.dst + (size_t)t * TM_W_BYTES + sw128_offset(r, c)) =
       make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
 }
@@ -81,6 +89,14 @@ __global__ void __launch_bounds__(256) conv_pack_many_kernel(const __grid_consta
 // ---------------------------------------------------------------------------------------------- helpers
 __device__ __forceinline__ void ld8bf(const __nv_bfloat16* p, float (&v)[8]) {
   const uint4 r = __ldg(reinterpret_cast<const uint4*>(p));
+  const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    v[2 * i] = __uint_as_float(w[i] << 16);
+    v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+  }
+}
+__device__ __forceinline__ void unpack8bf(const uint4& r, float (&v)[8]) {
   const uint32_t w[4] = {r.x, r.y, r.z, r.w};
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
@@ -108,6 +124,106 @@ __device__ __forceinline__ float transpose_sum32(float (&v)[32], int lane) {
 }
 __device__ __forceinline__ void named_bar(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+// ---------------------------------------------------------------------------------------------- shared epilogue
+// One thread = one output row (pixel) of a 128 x 64 fp32 accumulator tile: bias, residual add, ReLU mask, output
+// activation, bf16 store, and the per-channel statistics (BatchNorm forward moments or backward reductions).
+struct EpiOperands {
+  uint4 radd[4], rmask[4], rxhat[4];
+  bool use_add, use_mask, use_xhat;
+};
+// request this row's epilogue operands for channels [half*32, half*32 + 32)
+__device__ __forceinline__ void epi_request(EpiOperands& E, const EpiArgs& epi, long long o, int half) {
+  const __nv_bfloat16* add_src = static_cast<const __nv_bfloat16*>(epi.add_src);
+  const __nv_bfloat16* mask_src = static_cast<const __nv_bfloat16*>(epi.mask_src);
+  const __nv_bfloat16* xhat_src = static_cast<const __nv_bfloat16*>(epi.xhat_src);
+#pragma unroll
+  for (int g8 = 0; g8 < 4; ++g8) {
+    if (E.use_add) E.radd[g8] = __ldg(reinterpret_cast<const uint4*>(add_src + o + half * 32 + g8 * 8));
+    if (E.use_mask) E.rmask[g8] = __ldg(reinterpret_cast<const uint4*>(mask_src + o + half * 32 + g8 * 8));
+    if (E.use_xhat) E.rxhat[g8] = __ldg(reinterpret_cast<const uint4*>(xhat_src + o + half * 32 + g8 * 8));
+  }
+}
+__device__ __forceinline__ void epi_begin(EpiOperands& E, const EpiArgs& epi, long long o, bool valid) {
+  E.use_add = valid && epi.add_src != nullptr;
+  E.use_mask = valid && epi.mask_mode != NSG_MASK_NONE;
+  E.use_xhat = valid && epi.stats_mode == NSG_STATS_BNBWD;
+  epi_request(E, epi, o, 0);
+}
+__device__ __forceinline__ void epi_row(EpiOperands& E, const EpiArgs& epi, const float* sPar, float* sStat,
+                                        __nv_bfloat16* __restrict__ out, long long o, bool valid,
+                                        const uint32_t (&acc0)[32], const uint32_t (&acc1)[32], int lane) {
+  uint4 (&radd)[4] = E.radd;
+  uint4 (&rmask)[4] = E.rmask;
+  uint4 (&rxhat)[4] = E.rxhat;
+  const bool use_add = E.use_add, use_mask = E.use_mask, use_xhat = E.use_xhat;
+#pragma unroll
+      for (int chunk = 0; chunk < 2; ++chunk) {
+        const int ch0 = chunk * 32;
+        if (chunk == 1) epi_request(E, epi, o, 1);
+        float x[32], y[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          x[j] = valid ? __uint_as_float(chunk == 0 ? acc0[j] : acc1[j]) + sPar[ch0 + j] : 0.f;
+        if (use_add) {
+#pragma unroll
+          for (int g8 = 0; g8 < 4; ++g8) {
+            float a[8];
+            unpack8bf(radd[g8], a);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) x[g8 * 8 + j] += a[j];
+          }
+        }
+        if (use_mask) {
+#pragma unroll
+          for (int g8 = 0; g8 < 4; ++g8) {
+            float mk[8];
+            unpack8bf(rmask[g8], mk);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const int ch = ch0 + g8 * 8 + j;
+              const float mv = epi.mask_mode == NSG_MASK_AFFINE ? fmaf(sPar[TM_C + ch], mk[j], sPar[2 * TM_C + ch]) : mk[j];
+              x[g8 * 8 + j] = mv > 0.f ? x[g8 * 8 + j] : 0.f;
+            }
+          }
+        }
+        if (epi.tanh_out == 2) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) x[j] = fmaxf(x[j], 0.f);
+        }
+        if (valid) {
+#pragma unroll
+          for (int g8 = 0; g8 < 4; ++g8) st8bf(out + o + ch0 + g8 * 8, &x[g8 * 8]);
+        }
+        if (epi.stats_mode != NSG_STATS_NONE) {
+          if (epi.stats_mode == NSG_STATS_MOMENTS) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) y[j] = x[j] * x[j];
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) y[j] = 0.f;
+            if (use_xhat) {
+#pragma unroll
+              for (int g8 = 0; g8 < 4; ++g8) {
+                float hx[8];
+                unpack8bf(rxhat[g8], hx);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                  const int ch = ch0 + g8 * 8 + j;
+                  y[g8 * 8 + j] = x[g8 * 8 + j] * ((hx[j] - sPar[3 * TM_C + ch]) * sPar[4 * TM_C + ch]);
+                }
+              }
+            }
+          }
+        }
+        if (epi.stats_mode != NSG_STATS_NONE) {
+          const float s1 = transpose_sum32(x, lane);
+          const float s2 = transpose_sum32(y, lane);
+          atomicAdd(&sStat[ch0 + lane], s1);
+          atomicAdd(&sStat[TM_C + ch0 + lane], s2);
+        }
+      }
 }
 
 // ---------------------------------------------------------------------------------------------- conv_tma kernel
@@ -139,9 +255,9 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
   uint8_t* sW = sm;                                         // nw weight images
   uint8_t* sA = sm + (size_t)P.nw * TM_W_BYTES;             // ring of activation boxes
   uint8_t* tail = sA + (size_t)P.stages * TM_A_BYTES;
-  float* sPar = reinterpret_cast<float*>(tail);             // [5][64]: bias, mscale, mshift, mean, invstd
-  float* sStat = sPar + 5 * TM_C;                           // [2][64]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sStat + 2 * TM_C);
+  __shared__ __align__(16) float sPar[5 * TM_C];            // [5][64]: bias, mscale, mshift, mean, invstd
+  __shared__ float sStat[2 * TM_C];                         // [2][64]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(tail);
   uint64_t* full = bars;                                    // [8]
   uint64_t* empty = bars + TM_MAX_STAGES;                   // [8]
   uint64_t* wfull = bars + 2 * TM_MAX_STAGES;               // [1]
@@ -151,6 +267,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int stages = P.stages;
+  if (tid == 0) tm_stamp(P.dbg, 0);
 
   if (tid < TM_C) {
     sPar[0 * TM_C + tid] = epi.bias ? __ldg(epi.bias + tid) : 0.f;
@@ -186,6 +303,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
   const uint32_t tmem_base = *tmem_slot;
   const int ntiles_mine = ((int)blockIdx.x < P.total_tiles)
                               ? (P.total_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+  if (tid == 0) tm_stamp(P.dbg, 1);
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
@@ -212,6 +330,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
             tma::load_4d(dst, tm, 0, w0 + (dw >> 1), h0 + (dh >> 1), tl.n, &full[s]);
           }
         }
+        tm_stamp(P.dbg, 2 + (i < 3 ? i : 3));          // 2..5: producer finished issuing tile i
       }
     }
   } else if (warp == 1) {
@@ -219,6 +338,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
     if (lane == 0 && ntiles_mine > 0) {
       const uint32_t idesc = idesc_bf16(TM_M, TM_C);
       mbar_wait(wfull, 0);
+      tm_stamp(P.dbg, 6);                                // weights resident
       int it = 0;
       for (int i = 0; i < ntiles_mine; ++i) {
         const TmaTile tl = decode_tile(P, (int)blockIdx.x + i * (int)gridDim.x);
@@ -230,6 +350,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
         for (int t = 0; t < ph.ntaps; ++t, ++it) {
           const int s = it % stages, round = it / stages;
           mbar_wait(&full[s], (uint32_t)(round & 1));
+          if (it == 0) tm_stamp(P.dbg, 7);               // first activation box landed
           tc_fence_after();
           const uint64_t a = sw128_desc(smem_u32(sA + (size_t)s * TM_A_BYTES));
           const uint64_t b = sw128_desc(smem_u32(sW + (size_t)ph.wslot[t] * TM_W_BYTES));
@@ -238,6 +359,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
           umma_commit(&empty[s]);
         }
         umma_commit(&acc_full[as]);
+        tm_stamp(P.dbg, 8 + (i < 3 ? i : 3));           // 8..11: MMAs of tile i issued
       }
     }
   } else {
@@ -246,9 +368,6 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
     const int q = warp & 3;                          // TMEM lane quarter this warp may read
     const int r = q * 32 + lane;
     const int bw = r & (P.box_w - 1), bh = r >> P.log2_bw;
-    const __nv_bfloat16* add_src = static_cast<const __nv_bfloat16*>(epi.add_src);
-    const __nv_bfloat16* mask_src = static_cast<const __nv_bfloat16*>(epi.mask_src);
-    const __nv_bfloat16* xhat_src = static_cast<const __nv_bfloat16*>(epi.xhat_src);
     for (int i = grp; i < ntiles_mine; i += 2) {
       const TmaTile tl = decode_tile(P, (int)blockIdx.x + i * (int)gridDim.x);
       const TmaPhase& ph = P.ph[tl.p];
@@ -256,7 +375,10 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
       const bool valid = ohs < ph.sub_h && ows < ph.sub_w;
       const long long o = valid ? ((((long long)tl.n * P.full_h + (ohs * ph.out_stride + ph.off_h)) * P.full_w +
                                     (ows * ph.out_stride + ph.off_w)) * TM_C) : 0;
+      EpiOperands E;
+      epi_begin(E, epi, o, valid);      // operands of the first 32 channels are requested before the accumulator wait
       mbar_wait(&acc_full[grp], (uint32_t)((i >> 1) & 1));
+      if (tid == 64 + 128 * grp) tm_stamp(P.dbg, 12 + (i < 3 ? i : 3));     // 12..15: accumulator of tile i ready
       tc_fence_after();
       uint32_t acc0[32], acc1[32];
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)grp * TM_C;
@@ -265,69 +387,8 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
       tmem_ld_wait();
       tc_fence_before();
       mbar_arrive(&acc_empty[grp]);
-#pragma unroll
-      for (int chunk = 0; chunk < 2; ++chunk) {
-        const int ch0 = chunk * 32;
-        float x[32], y[32];
-#pragma unroll
-        for (int j = 0; j < 32; ++j)
-          x[j] = valid ? __uint_as_float(chunk == 0 ? acc0[j] : acc1[j]) + sPar[ch0 + j] : 0.f;
-        if (valid && add_src) {
-#pragma unroll
-          for (int g8 = 0; g8 < 4; ++g8) {
-            float a[8];
-            ld8bf(add_src + o + ch0 + g8 * 8, a);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) x[g8 * 8 + j] += a[j];
-          }
-        }
-        if (valid && epi.mask_mode != NSG_MASK_NONE) {
-#pragma unroll
-          for (int g8 = 0; g8 < 4; ++g8) {
-            float mk[8];
-            ld8bf(mask_src + o + ch0 + g8 * 8, mk);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              const int ch = ch0 + g8 * 8 + j;
-              const float mv = epi.mask_mode == NSG_MASK_AFFINE ? fmaf(sPar[TM_C + ch], mk[j], sPar[2 * TM_C + ch]) : mk[j];
-              x[g8 * 8 + j] = mv > 0.f ? x[g8 * 8 + j] : 0.f;
-            }
-          }
-        }
-        if (epi.tanh_out == 2) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) x[j] = fmaxf(x[j], 0.f);
-        }
-        if (valid) {
-#pragma unroll
-          for (int g8 = 0; g8 < 4; ++g8) st8bf(out + o + ch0 + g8 * 8, &x[g8 * 8]);
-        }
-        if (epi.stats_mode != NSG_STATS_NONE) {
-          if (epi.stats_mode == NSG_STATS_MOMENTS) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) y[j] = x[j] * x[j];
-          } else {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) y[j] = 0.f;
-            if (valid) {
-#pragma unroll
-              for (int g8 = 0; g8 < 4; ++g8) {
-                float hx[8];
-                ld8bf(xhat_src + o + ch0 + g8 * 8, hx);
-#pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                  const int ch = ch0 + g8 * 8 + j;
-                  y[g8 * 8 + j] = x[g8 * 8 + j] * ((hx[j] - sPar[3 * TM_C + ch]) * sPar[4 * TM_C + ch]);
-                }
-              }
-            }
-          }
-          const float s1 = transpose_sum32(x, lane);
-          const float s2 = transpose_sum32(y, lane);
-          atomicAdd(&sStat[ch0 + lane], s1);
-          atomicAdd(&sStat[TM_C + ch0 + lane], s2);
-        }
-      }
+      epi_row(E, epi, sPar, sStat, out, o, valid, acc0, acc1, lane);
+      if (tid == 64 + 128 * grp) tm_stamp(P.dbg, 16 + (i < 3 ? i : 3));     // 16..19: epilogue of tile i done
     }
     if (epi.stats_mode != NSG_STATS_NONE) {
       named_bar(1, 256);
@@ -338,9 +399,27 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc<128>(tmem_base);
+  if (tid == 0) tm_stamp(P.dbg, 20);
 }
 
 // ---------------------------------------------------------------------------------------------- conv_tma host side
+static unsigned long long* g_timeline = nullptr;       // device buffer of 32 stamps, set by nsg_debug_timeline(1)
+int debug_timeline(int enable, unsigned long long* host_out) {
+  if (enable && !g_timeline) {
+    cudaError_t e = cudaMalloc(&g_timeline, 32 * sizeof(unsigned long long));
+    if (e != cudaSuccess) return cuda_fail(e, "cudaMalloc(timeline)");
+    cudaMemset(g_timeline, 0, 32 * sizeof(unsigned long long));
+  }
+  if (host_out && g_timeline) {
+    cudaError_t e = cudaMemcpy(host_out, g_timeline, 32 * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaMemcpy(timeline)");
+  }
+  if (!enable && g_timeline) {
+    cudaFree(g_timeline);
+    g_timeline = nullptr;
+  }
+  return NSG_OK;
+}
 static int tma_shape_ok(const nsg_conv_geom* cg, const char* what) {
   if (cg->cin != TM_C || cg->cout != TM_C || cg->dtype != NSG_BF16) {
     set_error("%s: the TMA kernels serve bf16 tensors with cin == cout == 64 (got %d -> %d, dtype %d)", what, cg->cin,
@@ -435,11 +514,12 @@ int conv_gemm_tma(const nsg_conv_geom* cg, const void* in, const void* packed, c
   if (tiles == 0) return NSG_OK;
   P.nphases = nph;
   P.total_tiles = tiles;
-  const uint32_t tail = 7 * TM_C * 4 + (2 * TM_MAX_STAGES + 5) * 8 + 64;
+  const uint32_t tail = (2 * TM_MAX_STAGES + 5) * 8 + 64;
   int stages = (int)((TM_SMEM_LIMIT - 1024 - tail - (uint32_t)P.nw * TM_W_BYTES) / TM_A_BYTES);
   if (stages > TM_MAX_STAGES) stages = TM_MAX_STAGES;
   NSG_REQUIRE(stages >= 2, "conv_gemm_tma: weights do not leave room for the activation ring");
   P.stages = stages;
+  P.dbg = g_timeline;
   const size_t smem = 1024 + (size_t)P.nw * TM_W_BYTES + (size_t)stages * TM_A_BYTES + tail;
   CUtensorMap tm[4];
   if (int rc = encode_input_maps(tm, in, cg->batch, cg->in_h, cg->in_w, P.in_stride, P.box_w, P.box_h)) return rc;
@@ -457,6 +537,9 @@ int conv_gemm_tma(const nsg_conv_geom* cg, const void* in, const void* packed, c
   return NSG_OK;
 }
 
+// ntaps[i] > 0: a 64 -> 64 layer with ntaps images.  ntaps[i] == -1 / -2: the single-channel layers' small operands,
+// ONE image: -1 = rows are the 64 channels, K = the 16 taps (w[k + r*out_stride]); -2 = rows are the 16 taps,
+// K = the 64 channels (w[r + k*in_stride]).
 int conv_pack_many(int n, const float* const* w, void* const* dst, const int* ntaps, const long long* in_stride,
                    const long long* out_stride, cudaStream_t stream) {
   NSG_REQUIRE(n >= 0 && n <= 24, "conv_pack_many: at most 24 images per call (got %d)", n);
@@ -465,11 +548,17 @@ int conv_pack_many(int n, const float* const* w, void* const* dst, const int* nt
   L.n = n;
   int blocks = 0;
   for (int i = 0; i < n; ++i) {
-    NSG_REQUIRE(w[i] && dst[i] && ntaps[i] >= 1 && ntaps[i] <= TM_MAX_TAPS, "conv_pack_many: bad item %d", i);
+    NSG_REQUIRE(w[i] && dst[i] && ((ntaps[i] >= 1 && ntaps[i] <= TM_MAX_TAPS) || ntaps[i] == -1 || ntaps[i] == -2),
+                "conv_pack_many: bad item %d", i);
     NSG_REQUIRE((reinterpret_cast<uintptr_t>(dst[i]) & 127) == 0, "conv_pack_many: image %d must be 128-byte aligned", i);
     L.first_block[i] = blocks;
-    L.it[i] = PackItem{w[i], static_cast<uint8_t*>(dst[i]), ntaps[i], in_stride[i], out_stride[i]};
-    blocks += ntaps[i] * 2;
+    if (ntaps[i] > 0)
+      L.it[i] = PackItem{w[i], static_cast<uint8_t*>(dst[i]), ntaps[i], 64, 64, in_stride[i], out_stride[i]};
+    else if (ntaps[i] == -1)
+      L.it[i] = PackItem{w[i], static_cast<uint8_t*>(dst[i]), 1, 16, 64, in_stride[i], out_stride[i]};
+    else
+      L.it[i] = PackItem{w[i], static_cast<uint8_t*>(dst[i]), 1, 64, 16, in_stride[i], out_stride[i]};
+    blocks += (ntaps[i] > 0 ? ntaps[i] : 1) * 2;
   }
   L.first_block[n] = blocks;
   conv_pack_many_kernel<<<blocks, 256, 0, stream>>>(L);
@@ -751,6 +840,531 @@ int wgrad_unpack_many(int n, const float* const* src, float* const* dw, const in
   L.first_block[n] = blocks;
   wgrad_unpack_kernel<<<blocks, 256, 0, stream>>>(L);
   NSG_CHECK_LAUNCH("wgrad_unpack_kernel");
+  return NSG_OK;
+}
+
+
+// ============================================================================================== single-channel ends
+// The two single-channel layers (models.py:165 Conv2d(1 -> 64, 4, 2, 1); models.py:182 ConvTranspose2d(64 -> 1, 4, 2, 1))
+// on the tensor cores.  Their 64-channel side makes every per-element instruction 64x more expensive than the
+// arithmetic of the other side, so the 64-channel reduction / expansion belongs in ONE tcgen05.mma per 128 pixels:
+//   c1t_conv   out[128 px, 64] = patches[128 px, K = 16 taps] x W[64, 16]^T   (encoder.0 forward, decoder.6 dgrad)
+//   c1t_convT  p[128 px, 16 taps] = v[128 px, K = 64] x W[16, 64]^T, then every output pixel sums its <= 4 products
+//   c1t_wgrad  dW[16 taps, 64] = patches^T[16, pixels] x Q[pixels, 64]        (pixels = GEMM K, as in wgrad_tma)
+// The 16-wide operands live in the verified 128-byte-row SWIZZLE_128B layouts with only their first 32 bytes
+// (K-major: one K = 16 step) or first 16 channels (MN-major) meaningful.
+
+struct C1tConvParams {
+  int batch, in_h, in_w, out_h, out_w;
+  int box_w, box_h, log2_bw;
+  int tiles_h, tiles_w, total_tiles;
+};
+
+__global__ void __launch_bounds__(320, 1)
+c1t_conv_kernel(const __nv_bfloat16* __restrict__ in1, const uint8_t* __restrict__ wimg,
+                __nv_bfloat16* __restrict__ out, EpiArgs epi, const __grid_constant__ C1tConvParams P) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* sm = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sW = sm;                                  // one 64 x 64 image (K >= 16 zero)
+  uint8_t* sA = sm + TM_W_BYTES;                     // one patch tile per epilogue group
+  __shared__ __align__(16) float sPar[5 * TM_C];
+  __shared__ float sStat[2 * TM_C];
+  __shared__ __align__(8) uint64_t bars[5];          // wfull, full[2], acc_full[2]
+  __shared__ uint32_t tmem_slot;
+  uint64_t* wfull = bars;
+  uint64_t* full = bars + 1;
+  uint64_t* acc_full = bars + 3;
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  if (tid < TM_C) {
+    sPar[0 * TM_C + tid] = epi.bias ? __ldg(epi.bias + tid) : 0.f;
+    sPar[1 * TM_C + tid] = epi.mask_mode == NSG_MASK_AFFINE ? __ldg(epi.mscale + tid) : 1.f;
+    sPar[2 * TM_C + tid] = epi.mask_mode == NSG_MASK_AFFINE ? __ldg(epi.mshift + tid) : 0.f;
+    sPar[3 * TM_C + tid] = epi.stats_mode == NSG_STATS_BNBWD ? __ldg(epi.mean + tid) : 0.f;
+    sPar[4 * TM_C + tid] = epi.stats_mode == NSG_STATS_BNBWD ? __ldg(epi.invstd + tid) : 0.f;
+    sStat[tid] = 0.f;
+    sStat[TM_C + tid] = 0.f;
+  }
+  if (tid == 0) {
+    mbar_init(wfull, 1);
+    mbar_init(&full[0], 128); mbar_init(&full[1], 128);
+    mbar_init(&acc_full[0], 1); mbar_init(&acc_full[1], 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc<128>(&tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+  const int ntiles_mine = ((int)blockIdx.x < P.total_tiles)
+                              ? (P.total_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+
+  if (warp == 0) {
+    if (lane == 0 && ntiles_mine > 0) {
+      mbar_arrive_expect_tx(wfull, TM_W_BYTES);
+      bulk_g2s(sW, wimg, TM_W_BYTES, wfull);
+    }
+  } else if (warp == 1) {
+    if (lane == 0 && ntiles_mine > 0) {
+      const uint32_t idesc = idesc_bf16(TM_M, TM_C);
+      const uint64_t b = sw128_desc(smem_u32(sW));
+      mbar_wait(wfull, 0);
+      for (int i = 0; i < ntiles_mine; ++i) {
+        const int g = i & 1;
+        mbar_wait(&full[g], (uint32_t)((i >> 1) & 1));
+        tc_fence_after();
+        umma_bf16(tmem_base + (uint32_t)g * TM_C, sw128_desc(smem_u32(sA + (size_t)g * TM_A_BYTES)), b, idesc, 0);
+        umma_commit(&acc_full[g]);
+      }
+    }
+  } else {
+    const int grp = (warp - 2) >> 2, q = warp & 3;
+    const int r = q * 32 + lane;
+    const int bw = r & (P.box_w - 1), bh = r >> P.log2_bw;
+    uint8_t* myA = sA + (size_t)grp * TM_A_BYTES;
+    const unsigned short* in16 = reinterpret_cast<const unsigned short*>(in1);
+    for (int i = grp; i < ntiles_mine; i += 2) {
+      int t = (int)blockIdx.x + i * (int)gridDim.x;
+      const int tw = t % P.tiles_w;
+      t /= P.tiles_w;
+      const int th = t % P.tiles_h, n = t / P.tiles_h;
+      const int oh = th * P.box_h + bh, ow = tw * P.box_w + bw;
+      const bool valid = oh < P.out_h && ow < P.out_w;
+      // this row's 4 x 4 input patch (k = 4, stride 2, pad 1), taps kh*4 + kw along K
+      uint32_t pk[8];
+#pragma unroll
+      for (int kh = 0; kh < 4; ++kh) {
+        const int ih = 2 * oh - 1 + kh;
+        const bool rok = valid && ih >= 0 && ih < P.in_h;
+        const unsigned short* rowp = in16 + ((long long)n * P.in_h + ih) * P.in_w;
+        unsigned short v[4];
+#pragma unroll
+        for (int kw = 0; kw < 4; ++kw) {
+          const int iw = 2 * ow - 1 + kw;
+          v[kw] = (rok && iw >= 0 && iw < P.in_w) ? __ldg(rowp + iw) : (unsigned short)0;
+        }
+        pk[kh * 2 + 0] = (uint32_t)v[0] | ((uint32_t)v[1] << 16);
+        pk[kh * 2 + 1] = (uint32_t)v[2] | ((uint32_t)v[3] << 16);
+      }
+      const long long o = valid ? (((long long)n * P.out_h + oh) * P.out_w + ow) * TM_C : 0;
+      EpiOperands E;
+      epi_begin(E, epi, o, valid);
+      *reinterpret_cast<uint4*>(myA + sw128_offset(r, 0)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+      *reinterpret_cast<uint4*>(myA + sw128_offset(r, 1)) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+      fence_proxy_async_smem();
+      tc_fence_before();                       // orders this thread's tcgen05.ld of the previous tile before the arrive
+      mbar_arrive(&full[grp]);
+      mbar_wait(&acc_full[grp], (uint32_t)((i >> 1) & 1));
+      tc_fence_after();
+      uint32_t acc0[32], acc1[32];
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)grp * TM_C;
+      tmem_ld32(taddr, acc0);
+      tmem_ld32(taddr + 32, acc1);
+      tmem_ld_wait();
+      epi_row(E, epi, sPar, sStat, out, o, valid, acc0, acc1, lane);
+    }
+    if (epi.stats_mode != NSG_STATS_NONE) {
+      named_bar(1, 256);
+      const int e = tid - 64;
+      if (e < 2 * TM_C) atomicAdd(epi.stats + e, (double)sStat[e]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<128>(tmem_base);
+}
+
+static bool c1t_geom_ok(const nsg_conv_geom* cg) {
+  return cg->ksize == 4 && cg->stride == 2 && cg->pad == 1 && cg->dtype == NSG_BF16;
+}
+
+// Conv2d(1 -> 64) forward / ConvTranspose2d(64 -> 1) data gradient; packed = 8 KB image from conv_pack_many(ntaps = -1)
+int conv_c1_tc(const nsg_conv_geom* cg, const void* in, const void* packed, const nsg_epilogue* epi, void* out,
+               cudaStream_t stream) {
+  if (!(c1t_geom_ok(cg) && cg->gather == 0 && cg->cin == 1 && cg->cout == TM_C &&
+        cg->out_h == (cg->in_h + 2 - 4) / 2 + 1 && cg->out_w == (cg->in_w + 2 - 4) / 2 + 1)) {
+    set_error("conv_c1_tc serves bf16 Conv2d(1 -> 64, k4, s2, p1)-shaped gathers only");
+    return NSG_E_UNSUPPORTED;
+  }
+  NSG_REQUIRE((reinterpret_cast<uintptr_t>(packed) & 127) == 0, "conv_c1_tc: packed weights must be 128-byte aligned");
+  EpiArgs e{};
+  if (int rc = make_epi(epi, &e)) return rc;
+  NSG_REQUIRE(e.tanh_out == 0 || e.tanh_out == 2, "conv_c1_tc: output activation must be none or ReLU");
+  C1tConvParams P{};
+  P.batch = cg->batch; P.in_h = cg->in_h; P.in_w = cg->in_w; P.out_h = cg->out_h; P.out_w = cg->out_w;
+  pick_box(cg->out_w, TM_M, &P.box_w, &P.box_h, &P.log2_bw);
+  P.tiles_w = (cg->out_w + P.box_w - 1) / P.box_w;
+  P.tiles_h = (cg->out_h + P.box_h - 1) / P.box_h;
+  P.total_tiles = P.tiles_w * P.tiles_h * cg->batch;
+  if (P.total_tiles == 0) return NSG_OK;
+  const size_t smem = 1024 + TM_W_BYTES + 2 * TM_A_BYTES;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t err = cudaFuncSetAttribute(c1t_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (err != cudaSuccess) return cuda_fail(err, "cudaFuncSetAttribute(c1t_conv_kernel)");
+    configured = true;
+  }
+  const int grid = P.total_tiles < num_sms() ? P.total_tiles : num_sms();
+  c1t_conv_kernel<<<grid, 320, smem, stream>>>(static_cast<const __nv_bfloat16*>(in), static_cast<const uint8_t*>(packed),
+                                               static_cast<__nv_bfloat16*>(out), e, P);
+  NSG_CHECK_LAUNCH("c1t_conv_kernel");
+  return NSG_OK;
+}
+
+
+// ---------------------------------------------------------------------------------------------- 64 -> 1 transposed forward
+struct C1tConvTParams {
+  int batch, in_h, in_w, out_h, out_w;
+  int R;                 // input rows per work item (its output rows 2*r0 .. 2*(r0+R)-1)
+  int rblocks, cblocks;  // work items per image
+  int cstep;             // interior input columns per column block (in_w when cblocks == 1, else 126)
+  int stages;
+  int pstride;
+  int tanh_out;
+};
+constexpr int C1T_MAX_BOXES = 16;
+
+__device__ __forceinline__ void tmem_ld16_(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+}
+
+__global__ void __launch_bounds__(320, 1)
+c1t_convT_kernel(const __grid_constant__ CUtensorMap tm, const uint8_t* __restrict__ wimg,
+                 __nv_bfloat16* __restrict__ out, const float* __restrict__ bias,
+                 const __grid_constant__ C1tConvTParams P) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* sm = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sW = sm;                                              // 16 tap rows x 64 channels (rows >= 16 zero)
+  uint8_t* sA = sm + TM_W_BYTES;                                 // ring of 128-pixel boxes
+  float* sP = reinterpret_cast<float*>(sA + (size_t)P.stages * TM_A_BYTES);   // [boxes][16][pstride]
+  __shared__ __align__(8) uint64_t full[TM_MAX_STAGES], empty[TM_MAX_STAGES], acc_full[C1T_MAX_BOXES], wfull;
+  __shared__ uint32_t tmem_slot;
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int nboxes = P.R + 2;
+  int item = blockIdx.x;
+  const int cb = item % P.cblocks;
+  item /= P.cblocks;
+  const int rb = item % P.rblocks, n = item / P.rblocks;
+  const int r0 = rb * P.R;
+  const int ic0 = cb * P.cstep, ic1 = min(P.in_w, ic0 + P.cstep);
+  const int bx0 = P.cblocks == 1 ? 0 : ic0 - 1;
+
+  if (tid == 0) {
+    for (int s = 0; s < TM_MAX_STAGES; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);
+    }
+    for (int b = 0; b < C1T_MAX_BOXES; ++b) mbar_init(&acc_full[b], 1);
+    mbar_init(&wfull, 1);
+    fence_mbar_init();
+    tma::prefetch_desc(&tm);
+  }
+  if (warp == 1) tmem_alloc<256>(&tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_arrive_expect_tx(&wfull, TM_W_BYTES);
+      bulk_g2s(sW, wimg, TM_W_BYTES, &wfull);
+      for (int b = 0; b < nboxes; ++b) {
+        const int s = b % P.stages, round = b / P.stages;
+        if (round > 0) mbar_wait(&empty[s], (uint32_t)((round - 1) & 1));
+        mbar_arrive_expect_tx(&full[s], TM_A_BYTES);
+        tma::load_4d(sA + (size_t)s * TM_A_BYTES, &tm, 0, bx0, r0 - 1 + b, n, &full[s]);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc = idesc_bf16(TM_M, 16);
+      const uint64_t bdesc = sw128_desc(smem_u32(sW));
+      mbar_wait(&wfull, 0);
+      for (int b = 0; b < nboxes; ++b) {
+        const int s = b % P.stages, round = b / P.stages;
+        mbar_wait(&full[s], (uint32_t)(round & 1));
+        tc_fence_after();
+        const uint64_t a = sw128_desc(smem_u32(sA + (size_t)s * TM_A_BYTES));
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks) umma_bf16(tmem_base + (uint32_t)b * 16, a + 2 * ks, bdesc + 2 * ks, idesc, ks != 0);
+        umma_commit(&empty[s]);
+        umma_commit(&acc_full[b]);
+      }
+    }
+  } else {
+    if (warp < 6) {
+      // tap products of box b, pixel px = q*32 + lane: TMEM -> sP[b][t][px]
+      const int q = warp & 3;
+      const int px = q * 32 + lane;
+      for (int b = 0; b < nboxes; ++b) {
+        mbar_wait(&acc_full[b], 0);
+        tc_fence_after();
+        uint32_t v[16];
+        tmem_ld16_(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)b * 16, v);
+        tmem_ld_wait();
+        float* dst = sP + (size_t)b * 16 * P.pstride + px;
+#pragma unroll
+        for (int t = 0; t < 16; ++t) dst[(size_t)t * P.pstride] = __uint_as_float(v[t]);
+      }
+    }
+    named_bar(1, 256);
+    // every output pixel sums its (up to) four tap products: kh == (oh+1) mod 2, kw == (ow+1) mod 2
+    const float b0 = bias ? __ldg(bias) : 0.f;
+    const int oh_end = min(2 * (r0 + P.R), P.out_h);
+    const int ncols = 2 * (ic1 - ic0);
+    const int npix = (oh_end - 2 * r0) * ncols;
+    for (int i = tid - 64; i < npix; i += 256) {
+      const int oh = 2 * r0 + i / ncols, ow = 2 * ic0 + i % ncols;
+      float acc = b0;
+#pragma unroll
+      for (int a = 0; a < 2; ++a) {
+        const int kh = ((oh + 1) & 1) + 2 * a;
+        const int ih = (oh + 1 - kh) >> 1;
+        if (ih < 0 || ih >= P.in_h) continue;
+        const int lr = ih - (r0 - 1);
+#pragma unroll
+        for (int b = 0; b < 2; ++b) {
+          const int kw = ((ow + 1) & 1) + 2 * b;
+          const int iw = (ow + 1 - kw) >> 1;
+          if (iw < 0 || iw >= P.in_w) continue;
+          acc += sP[((size_t)lr * 16 + kh * 4 + kw) * P.pstride + (iw - bx0)];
+        }
+      }
+      out[((long long)n * P.out_h + oh) * P.out_w + ow] = __float2bfloat16_rn(P.tanh_out ? tanhf(acc) : acc);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<256>(tmem_base);
+}
+
+// ConvTranspose2d(64 -> 1, 4, 2, 1) forward; packed = 8 KB image from conv_pack_many(ntaps = -2)
+int convT_c1_tc(const nsg_conv_geom* cg, const void* in, const void* packed, const float* bias, int tanh_out, void* out,
+                cudaStream_t stream) {
+  if (!(c1t_geom_ok(cg) && cg->gather == 1 && cg->cin == TM_C && cg->cout == 1 && cg->out_h == 2 * cg->in_h &&
+        cg->out_w == 2 * cg->in_w)) {
+    set_error("convT_c1_tc serves bf16 ConvTranspose2d(64 -> 1, k4, s2, p1) only");
+    return NSG_E_UNSUPPORTED;
+  }
+  NSG_REQUIRE((reinterpret_cast<uintptr_t>(packed) & 127) == 0, "convT_c1_tc: packed weights must be 128-byte aligned");
+  C1tConvTParams P{};
+  P.batch = cg->batch; P.in_h = cg->in_h; P.in_w = cg->in_w; P.out_h = cg->out_h; P.out_w = cg->out_w;
+  P.tanh_out = tanh_out;
+  P.cblocks = cg->in_w <= 128 ? 1 : (cg->in_w + 125) / 126;
+  P.cstep = P.cblocks == 1 ? cg->in_w : 126;
+  P.pstride = 130;
+  long long per_img = num_sms() / ((long long)cg->batch * P.cblocks);     // row blocks per image for one wave
+  if (per_img < 1) per_img = 1;
+  if (per_img > cg->in_h) per_img = cg->in_h;
+  int R = (int)((cg->in_h + per_img - 1) / per_img);
+  if (R > 11) R = 11;                                                     // TMEM columns and shared memory
+  P.R = R;
+  P.rblocks = (cg->in_h + R - 1) / R;
+  P.stages = R + 2 < 4 ? R + 2 : 4;
+  const size_t smem = 1024 + TM_W_BYTES + (size_t)P.stages * TM_A_BYTES + (size_t)(R + 2) * 16 * P.pstride * sizeof(float);
+  CUtensorMap tm;
+  if (int rc = tma::encode_nhwc64(&tm, in, cg->in_w, cg->in_h, cg->batch, TM_C, (long long)cg->in_w * TM_C,
+                                  (long long)cg->in_h * cg->in_w * TM_C, 128, 1))
+    return rc;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t err = cudaFuncSetAttribute(c1t_convT_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           (int)TM_SMEM_LIMIT);
+    if (err != cudaSuccess) return cuda_fail(err, "cudaFuncSetAttribute(c1t_convT_kernel)");
+    configured = true;
+  }
+  const long long grid = (long long)cg->batch * P.rblocks * P.cblocks;
+  c1t_convT_kernel<<<(unsigned)grid, 320, smem, stream>>>(tm, static_cast<const uint8_t*>(packed),
+                                                          static_cast<__nv_bfloat16*>(out), bias, P);
+  NSG_CHECK_LAUNCH("c1t_convT_kernel");
+  return NSG_OK;
+}
+
+
+// ---------------------------------------------------------------------------------------------- weight gradient, one side single-channel
+struct C1tWgradParams {
+  int batch, in_h, in_w, q_h, q_w;     // single-channel grid P (in) and 64-channel grid Q
+  int box_w, box_h, log2_bw;           // 64-pixel boxes of Q
+  int tiles_h, tiles_w, total_tiles;
+  int stages;
+  long long w_tap_stride_c;            // elements between consecutive 64-side channels in dw (taps are fastest)
+};
+
+__global__ void __launch_bounds__(192, 1)
+c1t_wgrad_kernel(const __grid_constant__ CUtensorMap tq, const __nv_bfloat16* __restrict__ p1,
+                 float* __restrict__ dw, float* __restrict__ q_colsum, const __grid_constant__ C1tWgradParams P) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* sm = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  constexpr uint32_t STAGE = 3 * WG_SLOT;            // patch tile (16 taps of 64 "channels"), ones tile, Q box
+  __shared__ __align__(8) uint64_t fullQ[WG_MAX_STAGES], fullP[WG_MAX_STAGES], empty[WG_MAX_STAGES], acc_full;
+  __shared__ uint32_t tmem_slot;
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int ntiles_mine = ((int)blockIdx.x < P.total_tiles)
+                              ? (P.total_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+  // patch tiles start as zeros (taps 16..63 of the padded operand never change), ones tiles as bf16 1.0
+  for (int s = 0; s < P.stages; ++s) {
+    uint4* d0 = reinterpret_cast<uint4*>(sm + (size_t)s * STAGE);
+    for (int i = tid; i < (int)(WG_SLOT / 16); i += 192) {
+      d0[i] = make_uint4(0u, 0u, 0u, 0u);
+      d0[WG_SLOT / 16 + i] = make_uint4(0x3F803F80u, 0x3F803F80u, 0x3F803F80u, 0x3F803F80u);
+    }
+  }
+  fence_proxy_async_smem();
+  if (tid == 0) {
+    for (int s = 0; s < WG_MAX_STAGES; ++s) {
+      mbar_init(&fullQ[s], 1);
+      mbar_init(&fullP[s], 128);
+      mbar_init(&empty[s], 1);
+    }
+    mbar_init(&acc_full, 1);
+    fence_mbar_init();
+    tma::prefetch_desc(&tq);
+  }
+  if (warp == 1) tmem_alloc<64>(&tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+
+  if (ntiles_mine > 0) {
+    if (warp == 0) {
+      if (lane == 0) {
+        for (int i = 0; i < ntiles_mine; ++i) {
+          int t = (int)blockIdx.x + i * (int)gridDim.x;
+          const int tw = t % P.tiles_w;
+          t /= P.tiles_w;
+          const int th = t % P.tiles_h, n = t / P.tiles_h;
+          const int s = i % P.stages, round = i / P.stages;
+          if (round > 0) mbar_wait(&empty[s], (uint32_t)((round - 1) & 1));
+          mbar_arrive_expect_tx(&fullQ[s], WG_SLOT);
+          tma::load_4d(sm + (size_t)s * STAGE + 2 * WG_SLOT, &tq, 0, tw * P.box_w, th * P.box_h, n, &fullQ[s]);
+        }
+      }
+    } else if (warp == 1) {
+      if (lane == 0) {
+        const uint32_t idesc = idesc_bf16_mnmajor(128, TM_C);
+        for (int i = 0; i < ntiles_mine; ++i) {
+          const int s = i % P.stages, round = i / P.stages;
+          mbar_wait(&fullQ[s], (uint32_t)(round & 1));
+          mbar_wait(&fullP[s], (uint32_t)(round & 1));
+          tc_fence_after();
+          const uint32_t base = smem_u32(sm + (size_t)s * STAGE);
+#pragma unroll
+          for (int ks = 0; ks < WG_KP / 16; ++ks) {
+            const uint64_t a = sw128_desc_mnmajor(base + ks * 2048, WG_SLOT);
+            const uint64_t b = sw128_desc_mnmajor(base + 2 * WG_SLOT + ks * 2048, WG_SLOT);
+            umma_bf16(tmem_base, a, b, idesc, (i | ks) != 0);
+          }
+          umma_commit(&empty[s]);
+        }
+        umma_commit(&acc_full);
+      }
+    } else {
+      // ---------------------------------------------------------------- patch builders: thread = (pixel, tap half)
+      const int t128 = tid - 64;
+      const int px = t128 & 63, half = t128 >> 6;
+      const int bw = px & (P.box_w - 1), bh = px >> P.log2_bw;
+      const unsigned short* in16 = reinterpret_cast<const unsigned short*>(p1);
+      for (int i = 0; i < ntiles_mine; ++i) {
+        int t = (int)blockIdx.x + i * (int)gridDim.x;
+        const int tw = t % P.tiles_w;
+        t /= P.tiles_w;
+        const int th = t % P.tiles_h, n = t / P.tiles_h;
+        const int oh = th * P.box_h + bh, ow = tw * P.box_w + bw;
+        const bool valid = oh < P.q_h && ow < P.q_w;
+        uint32_t pk[4];
+#pragma unroll
+        for (int k2 = 0; k2 < 2; ++k2) {
+          const int ih = 2 * oh - 1 + half * 2 + k2;
+          const bool rok = valid && ih >= 0 && ih < P.in_h;
+          const unsigned short* rowp = in16 + ((long long)n * P.in_h + ih) * P.in_w;
+          unsigned short v[4];
+#pragma unroll
+          for (int kw = 0; kw < 4; ++kw) {
+            const int iw = 2 * ow - 1 + kw;
+            v[kw] = (rok && iw >= 0 && iw < P.in_w) ? __ldg(rowp + iw) : (unsigned short)0;
+          }
+          pk[k2 * 2 + 0] = (uint32_t)v[0] | ((uint32_t)v[1] << 16);
+          pk[k2 * 2 + 1] = (uint32_t)v[2] | ((uint32_t)v[3] << 16);
+        }
+        const int s = i % P.stages, round = i / P.stages;
+        if (round > 0) mbar_wait(&empty[s], (uint32_t)((round - 1) & 1));
+        *reinterpret_cast<uint4*>(sm + (size_t)s * STAGE + sw128_offset(px, half)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+        fence_proxy_async_smem();
+        mbar_arrive(&fullP[s]);
+      }
+      // ---------------------------------------------------------------- epilogue: rows 0..15 = taps, rows 64.. = column sums
+      mbar_wait(&acc_full, 0);
+      tc_fence_after();
+      const int q = warp & 3;
+      const int row = q * 32 + lane;
+      uint32_t acc0[32], acc1[32];
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+      tmem_ld32(taddr, acc0);
+      tmem_ld32(taddr + 32, acc1);
+      tmem_ld_wait();
+      if (row < 16) {
+#pragma unroll
+        for (int b = 0; b < 32; ++b) {
+          atomicAdd(dw + row + (long long)b * P.w_tap_stride_c, __uint_as_float(acc0[b]));
+          atomicAdd(dw + row + (long long)(b + 32) * P.w_tap_stride_c, __uint_as_float(acc1[b]));
+        }
+      } else if (row >= 64 && q_colsum) {
+        const int a = row - 64;
+        float v = 0.f;
+#pragma unroll
+        for (int c = 0; c < 32; ++c) {
+          if (a == c) v = __uint_as_float(acc0[c]);
+          if (a == 32 + c) v = __uint_as_float(acc1[c]);
+        }
+        atomicAdd(q_colsum + a, v);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<64>(tmem_base);
+}
+
+// dw[t + b*w_cout_stride] += sum_m p1[gather(m, t)] * q[m, b];  q_colsum[b] += sum_m q[m, b]   (cin == 1 side is P)
+int wgrad_c1_tc(const nsg_conv_geom* cg, const void* p, const void* q, float* dw, float* q_colsum, cudaStream_t stream) {
+  if (!(c1t_geom_ok(cg) && cg->cin == 1 && cg->cout == TM_C && cg->out_h == (cg->in_h + 2 - 4) / 2 + 1 &&
+        cg->out_w == (cg->in_w + 2 - 4) / 2 + 1)) {
+    set_error("wgrad_c1_tc serves bf16 (1-channel P, 64-channel Q, k4, s2, p1) weight gradients only");
+    return NSG_E_UNSUPPORTED;
+  }
+  C1tWgradParams P{};
+  P.batch = cg->batch; P.in_h = cg->in_h; P.in_w = cg->in_w; P.q_h = cg->out_h; P.q_w = cg->out_w;
+  P.w_tap_stride_c = cg->w_cout_stride;
+  pick_box(cg->out_w, WG_KP, &P.box_w, &P.box_h, &P.log2_bw);
+  P.tiles_w = (cg->out_w + P.box_w - 1) / P.box_w;
+  P.tiles_h = (cg->out_h + P.box_h - 1) / P.box_h;
+  P.total_tiles = P.tiles_w * P.tiles_h * cg->batch;
+  if (P.total_tiles == 0) return NSG_OK;
+  P.stages = 6;
+  const size_t smem = 1024 + (size_t)P.stages * 3 * WG_SLOT;
+  CUtensorMap tq;
+  if (int rc = tma::encode_nhwc64(&tq, q, cg->out_w, cg->out_h, cg->batch, TM_C, (long long)cg->out_w * TM_C,
+                                  (long long)cg->out_h * cg->out_w * TM_C, P.box_w, P.box_h))
+    return rc;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t err = cudaFuncSetAttribute(c1t_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (err != cudaSuccess) return cuda_fail(err, "cudaFuncSetAttribute(c1t_wgrad_kernel)");
+    configured = true;
+  }
+  const int grid = P.total_tiles < num_sms() ? P.total_tiles : num_sms();
+  c1t_wgrad_kernel<<<grid, 192, smem, stream>>>(tq, static_cast<const __nv_bfloat16*>(p), dw, q_colsum, P);
+  NSG_CHECK_LAUNCH("c1t_wgrad_kernel");
   return NSG_OK;
 }
 

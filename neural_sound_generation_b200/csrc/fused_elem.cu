@@ -25,6 +25,14 @@ __device__ __forceinline__ void fe_ld8(const __nv_bfloat16* p, float (&v)[8]) {
     v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
   }
 }
+__device__ __forceinline__ void fe_unpack(const uint4& r, float (&v)[8]) {
+  const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    v[2 * i] = __uint_as_float(w[i] << 16);
+    v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+  }
+}
 __device__ __forceinline__ uint32_t fe_pack(float a, float b) {
   __nv_bfloat162 t = __floats2bfloat162_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&t);
@@ -113,18 +121,32 @@ __global__ void __launch_bounds__(256) bn_act_kernel(const BnActArgs a) {
     sc[i] = sSc[c0 + i];
     sh[i] = sSh[c0 + i];
   }
-  for (long long p = (long long)blockIdx.x * 32 + (tid >> 3); p < a.pixels; p += (long long)gridDim.x * 32) {
-    const long long o = p * FE_C + c0;
-    float v[8], r[8];
-    fe_ld8(a.h + o, v);
-    if (a.res) fe_ld8(a.res + o, r);
+  // 4 pixels per thread and iteration: every load of the iteration is issued before the first use
+  for (long long p0 = (long long)blockIdx.x * 128 + (tid >> 3); p0 < a.pixels; p0 += (long long)gridDim.x * 128) {
+    uint4 hv[4], rv[4];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      float x = fmaf(sc[i], v[i], sh[i]);
-      if (a.res) x += r[i];
-      v[i] = a.relu_out ? fmaxf(x, 0.f) : x;
+    for (int u = 0; u < 4; ++u) {
+      const long long p = p0 + 32 * u;
+      if (p < a.pixels) {
+        hv[u] = __ldg(reinterpret_cast<const uint4*>(a.h + p * FE_C + c0));
+        if (a.res) rv[u] = __ldg(reinterpret_cast<const uint4*>(a.res + p * FE_C + c0));
+      }
     }
-    fe_st8(a.out + o, v);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const long long p = p0 + 32 * u;
+      if (p >= a.pixels) break;
+      float v[8], r[8];
+      fe_unpack(hv[u], v);
+      if (a.res) fe_unpack(rv[u], r);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        float x = fmaf(sc[i], v[i], sh[i]);
+        if (a.res) x += r[i];
+        v[i] = a.relu_out ? fmaxf(x, 0.f) : x;
+      }
+      fe_st8(a.out + p * FE_C + c0, v);
+    }
   }
 }
 
@@ -145,35 +167,55 @@ struct BnBwdArgs {
 
 __global__ void __launch_bounds__(256) bn_bwd_kernel(const BnBwdArgs a) {
   __shared__ float sred[FE_C];
+  __shared__ float sA[FE_C], sB[FE_C], sC[FE_C];     // dh = A*g + B*h + C per channel
   const int tid = threadIdx.x;
-  if (blockIdx.x == 0 && tid < FE_C) {
-    if (a.dbeta) a.dbeta[tid] += (float)a.stats[tid];
-    if (a.dgamma) a.dgamma[tid] += (float)a.stats[FE_C + tid];
+  if (tid < FE_C) {
+    const double sg = a.stats[tid] / a.count, sgx = a.stats[FE_C + tid] / a.count;
+    const float mu = a.mean[tid], is = a.invstd[tid];
+    const float k0 = a.gamma[tid] * is;
+    const float kb = k0 * is * (float)sgx;
+    sA[tid] = k0;
+    sB[tid] = -kb;
+    sC[tid] = kb * mu - k0 * (float)sg;
+    if (blockIdx.x == 0) {
+      if (a.dbeta) a.dbeta[tid] += (float)a.stats[tid];
+      if (a.dgamma) a.dgamma[tid] += (float)a.stats[FE_C + tid];
+    }
   }
+  __syncthreads();
   const int c0 = (tid & 7) * 8;
-  const float inv_count = (float)(1.0 / a.count);
-  float mu[8], is[8], k0[8], sg[8], sgx[8], col[8];
+  float ca[8], cb[8], cc[8], col[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
-    mu[i] = __ldg(a.mean + c0 + i);
-    is[i] = __ldg(a.invstd + c0 + i);
-    k0[i] = __ldg(a.gamma + c0 + i) * is[i];
-    sg[i] = (float)a.stats[c0 + i] * inv_count;
-    sgx[i] = (float)a.stats[FE_C + c0 + i] * inv_count;
+    ca[i] = sA[c0 + i];
+    cb[i] = sB[c0 + i];
+    cc[i] = sC[c0 + i];
     col[i] = 0.f;
   }
-  for (long long p = (long long)blockIdx.x * 32 + (tid >> 3); p < a.pixels; p += (long long)gridDim.x * 32) {
-    const long long o = p * FE_C + c0;
-    float gv[8], hv[8];
-    fe_ld8(a.g + o, gv);
-    fe_ld8(a.h + o, hv);
+  for (long long p0 = (long long)blockIdx.x * 128 + (tid >> 3); p0 < a.pixels; p0 += (long long)gridDim.x * 128) {
+    uint4 gr[4], hr[4];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const float xhat = (hv[i] - mu[i]) * is[i];
-      gv[i] = k0[i] * (gv[i] - sg[i] - xhat * sgx[i]);
-      col[i] += gv[i];
+    for (int u = 0; u < 4; ++u) {
+      const long long p = p0 + 32 * u;
+      if (p < a.pixels) {
+        gr[u] = __ldg(reinterpret_cast<const uint4*>(a.g + p * FE_C + c0));
+        hr[u] = __ldg(reinterpret_cast<const uint4*>(a.h + p * FE_C + c0));
+      }
     }
-    fe_st8(a.dh + o, gv);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const long long p = p0 + 32 * u;
+      if (p >= a.pixels) break;
+      float gv[8], hv[8];
+      fe_unpack(gr[u], gv);
+      fe_unpack(hr[u], hv);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        gv[i] = fmaf(ca[i], gv[i], fmaf(cb[i], hv[i], cc[i]));
+        col[i] += gv[i];
+      }
+      fe_st8(a.dh + p * FE_C + c0, gv);
+    }
   }
   if (a.dbias_prev) fe_channel_reduce<float>(col, sred, a.dbias_prev, c0);
 }
@@ -230,8 +272,8 @@ vq_bwd_stats_kernel(const __nv_bfloat16* __restrict__ g_st, const __nv_bfloat16*
 }
 
 static inline int fe_grid(long long pixels) {
-  long long blocks = (pixels + 31) / 32;
-  const long long cap = (long long)num_sms() * 8;
+  long long blocks = (pixels + 127) / 128;
+  const long long cap = (long long)num_sms() * 4;
   if (blocks > cap) blocks = cap;
   return blocks < 1 ? 1 : (int)blocks;
 }

@@ -14,7 +14,8 @@ and in reverse
 
 Weight images (bf16, UMMA K-major) of all ten 64->64 layers are re-packed by ONE launch per step; their
 gradients accumulate in packed fp32 images that ONE launch folds into the reference-layout ``.grad`` tensors.
-The single-channel ends (encoder.0, decoder.6) run on the streaming CUDA-core kernels of ``conv_c1.cu``.
+The single-channel ends (encoder.0, decoder.6) run on the tensor cores too (``c1t_*`` kernels: one
+tcgen05.mma per 128 pixels does the 64-channel expansion / reduction); other input_dim use the CUDA-core kernels.
 """
 import torch
 
@@ -45,6 +46,8 @@ class EngineTMA(object):
         self.vq_mode = vq_mode
         self.layers = None
         self._key = None
+        self.side = None            # second stream: weight gradients run beside the data-gradient chain
+        self.overlap_wgrad = True
 
     # ------------------------------------------------------------------ packed images
     def _prepare(self, P):
@@ -54,7 +57,7 @@ class EngineTMA(object):
         dev = P['encoder.3.weight'].device
         D = self.dim
         ntaps_total = sum(k * k for _, k, *_ in TC_LAYERS)
-        self.wimg = torch.empty(2 * ntaps_total * 8192, dtype=torch.uint8, device=dev)
+        self.wimg = torch.empty(2 * ntaps_total * 8192 + 3 * 8192, dtype=torch.uint8, device=dev)
         self.dwp = torch.zeros(ntaps_total * D * D, dtype=torch.float32, device=dev)
         self.layers = {}
         self.pack_items, self.unpack_items = [], []
@@ -79,6 +82,14 @@ class EngineTMA(object):
             og += kk * D * D
             self.pack_items += [(w, L.wf, kk, L.wci_f, L.wco_f), (w, L.wd, kk, L.wci_d, L.wco_d)]
             self.layers[name] = L
+        # single-channel ends on the tensor cores (input_dim == 1): 8 KB operand images
+        self.c1 = None
+        if self.cin0 == 1:
+            self.c1 = dict(enc0=self.wimg[ow:ow + 8192], dec6_fwd=self.wimg[ow + 8192:ow + 16384],
+                           dec6_dgrad=self.wimg[ow + 16384:ow + 24576])
+            self.pack_items += [(P['encoder.0.weight'], self.c1['enc0'], -1, 1, 16),
+                                (P['decoder.6.weight'], self.c1['dec6_fwd'], -2, 16, 1),
+                                (P['decoder.6.weight'], self.c1['dec6_dgrad'], -1, 1, 16)]
         self._key = key
 
     def _unpack_items(self, G):
@@ -99,7 +110,21 @@ class EngineTMA(object):
         ctx.coef = torch.empty((len(BN_LAYERS), 4, self.dim), dtype=torch.float32, device=dev)
         ctx.stats = torch.zeros((len(BN_LAYERS), 2, 2 * self.dim), dtype=torch.float64, device=dev)
         ctx.packed = False
+        ctx.keep = []               # tensors in use on the side stream (kept alive until the join)
+        ctx.forked = False
         return ctx
+
+    def _side(self, ctx, fn, *tensors):
+        """Run fn() on the side stream after everything issued so far on the current stream."""
+        if not self.overlap_wgrad:
+            return fn()
+        if self.side is None:
+            self.side = torch.cuda.Stream()
+        self.side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(self.side):
+            fn()
+        ctx.keep.extend(tensors)
+        ctx.forked = True
 
     def _pack(self, ctx, P):
         if not ctx.packed:
@@ -129,17 +154,17 @@ class EngineTMA(object):
         ops.conv_gemm_tma(g, dy, L.wd, out, **epi)
         return out
 
-    def _conv_wgrad(self, name, x, dy, q_colsum=None):
-        """x = the layer's (operand-ready) forward input, dy = gradient of its output."""
+    def _conv_wgrad(self, ctx, name, x, dy, q_colsum=None):
+        """x = the layer's (operand-ready) forward input, dy = gradient of its output.  Issued on the side stream."""
         L = self.layers[name]
         b, h, w, c = x.shape
         _, oh, ow, _ = dy.shape
         if L.tr:        # P = dy gathered over x's pixels, Q = x
             g = ops.conv_geom(b, oh, ow, c, h, w, c, L.k, L.s, L.p, 0, L.wci_g, L.wco_g, ops.BF16)
-            ops.conv_wgrad_tma(g, dy, x, L.dwp, q_colsum=q_colsum)
+            self._side(ctx, lambda: ops.conv_wgrad_tma(g, dy, x, L.dwp, q_colsum=q_colsum), x, dy)
         else:           # P = x gathered over dy's pixels, Q = dy
             g = ops.conv_geom(b, h, w, c, oh, ow, c, L.k, L.s, L.p, 0, L.wci_g, L.wco_g, ops.BF16)
-            ops.conv_wgrad_tma(g, x, dy, L.dwp, q_colsum=q_colsum)
+            self._side(ctx, lambda: ops.conv_wgrad_tma(g, x, dy, L.dwp, q_colsum=q_colsum), x, dy)
 
     def _bn_act(self, ctx, P, Bufs, name, h, res=None, relu_out=True):
         bn = self._bn(ctx, name)
@@ -183,12 +208,12 @@ class EngineTMA(object):
         hw = r.shape[1:3]
         bn2 = self._bn(ctx, name + '.block.2')
         g_h2 = self._bn_bwd(ctx, P, G, name + '.block.5', g_y, h2, G[name + '.block.4.bias'])
-        self._conv_wgrad(name + '.block.4', v1, g_h2)
+        self._conv_wgrad(ctx, name + '.block.4', v1, g_h2)
         g_v1 = self._conv_dgrad(name + '.block.4', g_h2, hw, mask_mode=MASK_POS, mask_src=v1,
                                 stats_mode=STATS_BNBWD, stats=bn2['bstats'], xhat_src=h1, mean=bn2['mean'],
                                 invstd=bn2['invstd'])
         g_h1 = self._bn_bwd(ctx, P, G, name + '.block.2', g_v1, h1, G[name + '.block.1.bias'])
-        self._conv_wgrad(name + '.block.1', r, g_h1)
+        self._conv_wgrad(ctx, name + '.block.1', r, g_h1)
         epi = dict(add_src=g_y, mask_mode=MASK_POS, mask_src=r)
         if prev_block is not None:
             pbn = self._bn(ctx, prev_block + '.block.5')
@@ -207,8 +232,12 @@ class EngineTMA(object):
         oh, ow = _out_hw(h, w, 4, 2, 1, False)
         a0 = torch.empty((b, oh, ow, self.dim), dtype=BF, device=x.device)
         g = ops.conv_geom(b, h, w, cin, oh, ow, self.dim, 4, 2, 1, 0, 16, cin * 16, ops.BF16)
-        ops.conv_gemm(g, x, w0, a0, bias=P['encoder.0.bias'], stats_mode=STATS_MOMENTS if tr else 0,
-                      stats=bn1['fstats'] if tr else None)
+        if self.c1 is not None:
+            ops.c1_conv_tc(g, x, self.c1['enc0'], a0, bias=P['encoder.0.bias'],
+                           stats_mode=STATS_MOMENTS if tr else 0, stats=bn1['fstats'] if tr else None)
+        else:
+            ops.conv_gemm(g, x, w0, a0, bias=P['encoder.0.bias'], stats_mode=STATS_MOMENTS if tr else 0,
+                          stats=bn1['fstats'] if tr else None)
         v0 = self._bn_act(ctx, P, Bufs, 'encoder.1', a0, relu_out=True)
         r4 = self._conv_fwd(ctx, P, 'encoder.3', v0, relu_out=True)            # relu(a1): ResBlock's in-place ReLU
         r5 = self.resblock_fwd(ctx, P, Bufs, 'encoder.4', r4, relu_out=True)
@@ -233,7 +262,10 @@ class EngineTMA(object):
         oh, ow = _out_hw(h, w, 4, 2, 1, True)
         xt = torch.empty((b, oh, ow, cout), dtype=BF, device=v4.device)
         g = ops.conv_geom(b, h, w, self.dim, oh, ow, cout, 4, 2, 1, 1, cout * 16, 16, ops.BF16)
-        ops.conv_gemm(g, v4, w6, xt, bias=P['decoder.6.bias'], tanh_out=True)
+        if self.c1 is not None:
+            ops.c1_convT_tc(g, v4, self.c1['dec6_fwd'], xt, bias=P['decoder.6.bias'], tanh_out=True)
+        else:
+            ops.conv_gemm(g, v4, w6, xt, bias=P['decoder.6.bias'], tanh_out=True)
         ctx.rd, ctx.u0, ctx.v4 = rd, u0, v4
         return xt
 
@@ -248,15 +280,25 @@ class EngineTMA(object):
         w6 = P['decoder.6.weight']
         # decoder.6 weight gradient: P = dpre gathered over v4's pixels, Q = v4
         g = ops.conv_geom(b, oh, ow, cout, h, w, self.dim, 4, 2, 1, 0, 16, cout * 16, ops.BF16)
-        ops.conv_wgrad(g, dpre, v4, G['decoder.6.weight'])
-        ops.colsum(dpre, G['decoder.6.bias'])
+        gw = g
+        if self.c1 is not None:
+            self._side(ctx, lambda: (ops.c1_wgrad_tc(gw, dpre, v4, G['decoder.6.weight']),
+                                     ops.colsum(dpre, G['decoder.6.bias'])), dpre, v4)
+        else:
+            self._side(ctx, lambda: (ops.conv_wgrad(gw, dpre, v4, G['decoder.6.weight']),
+                                     ops.colsum(dpre, G['decoder.6.bias'])), dpre, v4)
         # decoder.6 data gradient, masked by the ReLU, with decoder.4's BN-backward sums
         g = ops.conv_geom(b, oh, ow, cout, h, w, self.dim, 4, 2, 1, 0, 16, cout * 16, ops.BF16)
         g_v4 = torch.empty_like(v4)
-        ops.conv_gemm(g, dpre, w6, g_v4, mask_mode=MASK_POS, mask_src=v4, stats_mode=STATS_BNBWD, stats=bn4['bstats'],
-                      xhat_src=u0, mean=bn4['mean'], invstd=bn4['invstd'])
+        if self.c1 is not None:
+            ops.c1_conv_tc(g, dpre, self.c1['dec6_dgrad'], g_v4, mask_mode=MASK_POS, mask_src=v4,
+                           stats_mode=STATS_BNBWD, stats=bn4['bstats'], xhat_src=u0, mean=bn4['mean'],
+                           invstd=bn4['invstd'])
+        else:
+            ops.conv_gemm(g, dpre, w6, g_v4, mask_mode=MASK_POS, mask_src=v4, stats_mode=STATS_BNBWD,
+                          stats=bn4['bstats'], xhat_src=u0, mean=bn4['mean'], invstd=bn4['invstd'])
         g_u0 = self._bn_bwd(ctx, P, G, 'decoder.4', g_v4, u0, G['decoder.3.bias'])
-        self._conv_wgrad('decoder.3', rd, g_u0)
+        self._conv_wgrad(ctx, 'decoder.3', rd, g_u0)
         pbn = self._bn(ctx, 'decoder.1.block.5')
         g_d1 = self._conv_dgrad('decoder.3', g_u0, rd.shape[1:3], mask_mode=MASK_POS, mask_src=rd,
                                 stats_mode=STATS_BNBWD, stats=pbn['bstats'], xhat_src=ctx.saved['decoder.1'][3],
@@ -286,7 +328,7 @@ class EngineTMA(object):
         bn1 = self._bn(ctx, 'encoder.1')
         g_r5 = self.resblock_bwd(ctx, P, G, 'encoder.5', g_ze, prev_block='encoder.4')
         g_a1 = self.resblock_bwd(ctx, P, G, 'encoder.4', g_r5)
-        self._conv_wgrad('encoder.3', v0, g_a1, q_colsum=G['encoder.3.bias'])
+        self._conv_wgrad(ctx, 'encoder.3', v0, g_a1, q_colsum=G['encoder.3.bias'])
         g_v0 = self._conv_dgrad('encoder.3', g_a1, v0.shape[1:3], mask_mode=MASK_POS, mask_src=v0,
                                 stats_mode=STATS_BNBWD, stats=bn1['bstats'], xhat_src=a0, mean=bn1['mean'],
                                 invstd=bn1['invstd'])
@@ -294,7 +336,11 @@ class EngineTMA(object):
         b, h, w, cin = x.shape
         _, oh, ow, _ = a0.shape
         g = ops.conv_geom(b, h, w, cin, oh, ow, self.dim, 4, 2, 1, 0, 16, cin * 16, ops.BF16)
-        ops.conv_wgrad(g, x, g_a0, G['encoder.0.weight'])
+        gw = g
+        if self.c1 is not None:
+            self._side(ctx, lambda: ops.c1_wgrad_tc(gw, x, g_a0, G['encoder.0.weight']), x, g_a0)
+        else:
+            self._side(ctx, lambda: ops.conv_wgrad(gw, x, g_a0, G['encoder.0.weight']), x, g_a0)
         dx = None
         if need_dx:
             dx = torch.empty_like(x)
@@ -304,6 +350,10 @@ class EngineTMA(object):
 
     def finish_backward(self, ctx, G):
         """Fold the packed weight-gradient images into the reference-layout gradients (one launch) and clear them."""
+        if ctx.forked:
+            torch.cuda.current_stream().wait_stream(self.side)
+            ctx.forked = False
+        ctx.keep = []
         ops.wgrad_unpack_many(self._unpack_items(G))
         self.dwp.zero_()
 

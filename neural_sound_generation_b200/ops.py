@@ -417,3 +417,47 @@ def vq_bwd_stats64(g_st, z, zq, coef, dz, h=None, mean=None, invstd=None, stats=
     A.check(rc, 'nsg_vq_bwd_stats64')
     launch_count += 1
     return dz
+
+
+def c1_pack(w, kind):
+    """8 KB operand image of a single-channel layer's weight: kind -1 (rows = 64 channels, K = 16 taps) for
+    c1_conv_tc, kind -2 (rows = 16 taps, K = 64 channels) for c1_convT_tc.  Both weights are (64, 1, 4, 4)-shaped."""
+    packed = torch.empty(8192, dtype=torch.uint8, device=w.device)
+    conv_pack_many([(w, packed, kind, 1, 16) if kind == -1 else (w, packed, kind, 16, 1)])
+    return packed
+
+
+def c1_conv_tc(geom, x1, packed, out, bias=None, add_src=None, mask_mode=MASK_NONE, mask_src=None, mscale=None,
+               mshift=None, stats_mode=STATS_NONE, stats=None, xhat_src=None, mean=None, invstd=None):
+    global launch_count
+    A.require_device()
+    _cuda(x1, packed, out, bias, add_src, mask_src, stats, xhat_src)
+    _bf16(x1, out, add_src, mask_src, xhat_src)
+    epi = A.Epilogue(A.ptr(bias), A.ptr(add_src), mask_mode, A.ptr(mask_src), A.ptr(mscale), A.ptr(mshift),
+                     stats_mode, A.ptr(stats), A.ptr(xhat_src), A.ptr(mean), A.ptr(invstd), 0)
+    rc = A.load().nsg_c1_conv_tc(C.byref(geom), A.ptr(x1), A.ptr(packed), C.byref(epi), A.ptr(out), A.stream_ptr())
+    A.check(rc, 'nsg_c1_conv_tc')
+    launch_count += 1
+    return out
+
+
+def c1_convT_tc(geom, x, packed, out1, bias=None, tanh_out=False):
+    global launch_count
+    A.require_device()
+    _cuda(x, packed, out1, bias)
+    _bf16(x, out1)
+    rc = A.load().nsg_c1_convT_tc(C.byref(geom), A.ptr(x), A.ptr(packed), A.ptr(bias), int(bool(tanh_out)),
+                                  A.ptr(out1), A.stream_ptr())
+    A.check(rc, 'nsg_c1_convT_tc')
+    launch_count += 1
+    return out1
+
+
+def c1_wgrad_tc(geom, p1, q, dw, q_colsum=None):
+    global launch_count
+    A.require_device()
+    _cuda(p1, q, dw, q_colsum)
+    _bf16(p1, q)
+    rc = A.load().nsg_c1_wgrad_tc(C.byref(geom), A.ptr(p1), A.ptr(q), A.ptr(dw), A.ptr(q_colsum), A.stream_ptr())
+    A.check(rc, 'nsg_c1_wgrad_tc')
+    launch_count += 1

@@ -229,3 +229,67 @@ def test_bn_bwd64_relu64_vq_bwd_stats64():
     dref = g.double() + 0.25 * (z.double() - zq.double())
     assert relerr(dz.float(), dref) < OUT_TOL
     assert relerr(st, torch.cat([dref.sum(0), (dref * xhat).sum(0)])) < ACC_TOL
+
+
+C1_CASES = [(2, 16, 12), (1, 80, 256), (3, 10, 34), (1, 8, 300)]      # (B, H, W) of the single-channel grid
+
+
+@pytest.mark.parametrize('case', C1_CASES)
+def test_c1_tensor_core_kernels(case):
+    """encoder.0 / decoder.6 on the tensor cores vs fp64 on the same bf16-rounded operands."""
+    B, H, W = case
+    C, OH, OW = 64, H // 2, W // 2
+    rng = np.random.RandomState(B * 1000 + W)
+    x1 = _r16(_rand(rng, B, 1, H, W))
+    w0 = _r16(_rand(rng, C, 1, 4, 4) * 0.3)                 # Conv2d(1 -> 64) weight; also ConvT(64 -> 1) weight shape
+    bias = _rand(rng, C)
+    # ---- Conv2d(1 -> 64, 4, 2, 1) forward + moment statistics
+    xd = x1.double()
+    wd = w0.double().requires_grad_(True)
+    yref = F.conv2d(xd, wd, bias.double(), 2, 1)
+    gf = ops.conv_geom(B, H, W, 1, OH, OW, C, 4, 2, 1, 0, 16, 16, ops.BF16)
+    x1g = nhwc(x1).to(DEV).to(BF)
+    y = torch.empty((B, OH, OW, C), dtype=BF, device=DEV)
+    stats = torch.zeros(2 * C, dtype=torch.float64, device=DEV)
+    w0g = w0.to(DEV)
+    ops.c1_conv_tc(gf, x1g, ops.c1_pack(w0g, -1), y, bias=bias.to(DEV), stats_mode=ops.STATS_MOMENTS, stats=stats)
+    torch.cuda.synchronize()
+    assert relerr(nchw(y.float()), yref) < OUT_TOL, 'c1 conv fwd'
+    assert relerr(stats, torch.cat([yref.sum((0, 2, 3)), (yref ** 2).sum((0, 2, 3))])) < ACC_TOL
+    # ---- its weight gradient (+ column sums of dy)
+    gy = _r16(_rand(rng, B, C, OH, OW))
+    yref.backward(gy.double())
+    gyg = nhwc(gy).to(DEV).to(BF)
+    dw = torch.zeros_like(w0g)
+    col = torch.zeros(C, device=DEV)
+    ops.c1_wgrad_tc(gf, x1g, gyg, dw, q_colsum=col)
+    torch.cuda.synchronize()
+    assert relerr(dw, wd.grad) < ACC_TOL, 'c1 wgrad'
+    assert relerr(col, gy.double().sum((0, 2, 3))) < ACC_TOL, 'c1 colsum'
+    # ---- ConvTranspose2d(64 -> 1, 4, 2, 1) forward with tanh, on a (B, OH, OW, 64) input -> (B, H, W, 1)
+    v = _r16(_rand(rng, B, C, OH, OW))
+    b6 = _rand(rng, 1)
+    tref = torch.tanh(F.conv_transpose2d(v.double(), w0.double(), b6.double(), 2, 1))
+    gt = ops.conv_geom(B, OH, OW, C, 2 * OH, 2 * OW, 1, 4, 2, 1, 1, 16, 16, ops.BF16)
+    xt = torch.empty((B, 2 * OH, 2 * OW, 1), dtype=BF, device=DEV)
+    ops.c1_convT_tc(gt, nhwc(v).to(DEV).to(BF), ops.c1_pack(w0g, -2), xt, bias=b6.to(DEV), tanh_out=True)
+    torch.cuda.synchronize()
+    assert relerr(nchw(xt.float()), tref) < OUT_TOL, 'c1 convT fwd'
+    # ---- its data gradient: conv-like gather of the 1-channel gradient with the same weight, masked, BN-bwd sums
+    dpre = _r16(_rand(rng, B, 1, 2 * OH, 2 * OW))
+    vin = v.double().requires_grad_(True)
+    F.conv_transpose2d(vin, w0.double(), None, 2, 1).backward(dpre.double())
+    h = _r16(_rand(rng, B, C, OH, OW))
+    mean, invstd = 0.1 * _rand(rng, C), 1 + 0.1 * _rand(rng, C).abs()
+    gref = vin.grad * (v.double() > 0)
+    xhat = (h.double() - mean.double()[None, :, None, None]) * invstd.double()[None, :, None, None]
+    gd = ops.conv_geom(B, 2 * OH, 2 * OW, 1, OH, OW, C, 4, 2, 1, 0, 16, 16, ops.BF16)
+    g = torch.empty((B, OH, OW, C), dtype=BF, device=DEV)
+    st = torch.zeros(2 * C, dtype=torch.float64, device=DEV)
+    keep = (mean.to(DEV), invstd.to(DEV))
+    ops.c1_conv_tc(gd, nhwc(dpre).to(DEV).to(BF), ops.c1_pack(w0g, -1), g, mask_mode=ops.MASK_POS,
+                   mask_src=nhwc(v).to(DEV).to(BF), stats_mode=ops.STATS_BNBWD, stats=st,
+                   xhat_src=nhwc(h).to(DEV).to(BF), mean=keep[0], invstd=keep[1])
+    torch.cuda.synchronize()
+    assert relerr(nchw(g.float()), gref) < OUT_TOL, 'c1 dgrad'
+    assert relerr(st, torch.cat([gref.sum((0, 2, 3)), (gref * xhat).sum((0, 2, 3))])) < 5e-4

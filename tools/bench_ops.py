@@ -69,7 +69,7 @@ def main():
               ('conv4x4 s2 (encoder.3)', 40, 128, 4, 2, 1, False), ('convT4x4 s2 (decoder.3)', 20, 64, 4, 2, 1, True)]
     only = os.environ.get('BENCH_LAYER')
     if only is not None:
-        layers = [layers[int(only)]]
+        layers = [layers[int(only)]] if int(only) >= 0 else []
     for name, H, W, k, s, p, tr in layers:
         fwd, dgr, wgr, OH, OW = geoms(B, H, W, k, s, p, tr)
         x = torch.randn(B, H, W, C, device=DEV).to(BF)
@@ -94,6 +94,43 @@ def main():
             else:
                 t = timed(lambda: ops.conv_wgrad_tma(wgr, x, gy, dwp, q_colsum=col), flush=fl)
             print('%-26s wgrad      %s %8.1f us  %7.1f TFLOP/s' % (name, tag, t, flop / t / 1e6))
+    if only is not None and int(only) >= 0:
+        return
+    # single-channel ends (conv_c1_fast.cu): encoder.0 fwd / wgrad, decoder.6 fwd / dgrad / wgrad
+    x1 = torch.rand(B, 80, 256, 1, device=DEV).to(BF)
+    a0 = torch.empty(B, 40, 128, C, dtype=BF, device=DEV)
+    v4 = torch.randn(B, 40, 128, C, device=DEV).to(BF)
+    g64 = torch.randn(B, 40, 128, C, device=DEV).to(BF)
+    w0 = torch.randn(C, 1, 4, 4, device=DEV) * 0.1
+    w6 = torch.randn(C, 1, 4, 4, device=DEV) * 0.1
+    b0, b6 = torch.zeros(C, device=DEV), torch.zeros(1, device=DEV)
+    xt = torch.empty(B, 80, 256, 1, dtype=BF, device=DEV)
+    st = torch.zeros(2 * C, dtype=torch.float64, device=DEV)
+    mean, invstd = torch.zeros(C, device=DEV), torch.ones(C, device=DEV)
+    dw = torch.zeros(C, 1, 4, 4, device=DEV)
+    gf = ops.conv_geom(B, 80, 256, 1, 40, 128, C, 4, 2, 1, 0, 16, 16, ops.BF16)
+    gt = ops.conv_geom(B, 40, 128, C, 80, 256, 1, 4, 2, 1, 1, 16, 16, ops.BF16)
+    nb = a0.numel() * 2
+    for fl, tag in (((flush, 'cold'),) if only is not None else ((flush, 'cold'), (None, 'warm'))):
+        t = timed(lambda: ops.conv_gemm(gf, x1, w0, a0, bias=b0, stats_mode=ops.STATS_MOMENTS, stats=st), flush=fl)
+        print('c1 conv 1->64 fwd+stats     %s %8.1f us  %7.1f GB/s' % (tag, t, nb / t / 1e3))
+        t = timed(lambda: ops.conv_gemm(gf, x1, w6, a0, mask_mode=ops.MASK_POS, mask_src=v4, stats_mode=ops.STATS_BNBWD,
+                                        stats=st, xhat_src=g64, mean=mean, invstd=invstd), flush=fl)
+        print('c1 conv 1->64 dgrad+mask+bn %s %8.1f us  %7.1f GB/s' % (tag, t, 3 * nb / t / 1e3))
+        t = timed(lambda: ops.conv_gemm(gt, v4, w6, xt, bias=b6, tanh_out=True), flush=fl)
+        print('c1 convT 64->1 fwd+tanh     %s %8.1f us  %7.1f GB/s' % (tag, t, nb / t / 1e3))
+        t = timed(lambda: ops.conv_wgrad(gf, x1, g64, dw), flush=fl)
+        print('c1 wgrad                    %s %8.1f us  %7.1f GB/s' % (tag, t, nb / t / 1e3))
+        pk1, pk2 = ops.c1_pack(w0, -1), ops.c1_pack(w6, -2)
+        t = timed(lambda: ops.c1_conv_tc(gf, x1, pk1, a0, bias=b0, stats_mode=ops.STATS_MOMENTS, stats=st), flush=fl)
+        print('c1t conv 1->64 fwd+stats    %s %8.1f us  %7.1f GB/s' % (tag, t, nb / t / 1e3))
+        t = timed(lambda: ops.c1_conv_tc(gf, x1, pk1, a0, mask_mode=ops.MASK_POS, mask_src=v4, stats_mode=ops.STATS_BNBWD,
+                                         stats=st, xhat_src=g64, mean=mean, invstd=invstd), flush=fl)
+        print('c1t conv 1->64 dgrad+mask+bn %s %8.1f us  %7.1f GB/s' % (tag, t, 3 * nb / t / 1e3))
+        t = timed(lambda: ops.c1_convT_tc(gt, v4, pk2, xt, bias=b6, tanh_out=True), flush=fl)
+        print('c1t convT 64->1 fwd+tanh    %s %8.1f us  %7.1f GB/s' % (tag, t, nb / t / 1e3))
+        t = timed(lambda: ops.c1_wgrad_tc(gf, x1, g64, dw), flush=fl)
+        print('c1t wgrad                   %s %8.1f us  %7.1f GB/s' % (tag, t, nb / t / 1e3))
     if only is not None:
         return
     for name, H, W in (('20x64', 20, 64), ('40x128', 40, 128)):
