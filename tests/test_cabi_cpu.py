@@ -15,7 +15,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 def test_library_exports_every_declared_symbol():
     header = open(os.path.join(ROOT, 'include', 'nsg_b200.h')).read()
-    declared = set(re.findall(r'\b(nsg_[a-z0-9_]+)\s*\(', header))
+    declared = set(re.findall(r'\b(nsg_[A-Za-z0-9_]+)\s*\(', header))
     declared -= {'nsg_conv_geom', 'nsg_prologue', 'nsg_epilogue'}
     lib = _cabi.load()
     for name in sorted(declared):
