@@ -27,6 +27,41 @@ DIM, K_CODES = 64, 512
 TRAIN_GFLOP = 76.84                              # SURVEY.md §8d, per 32x256 step
 
 
+def ncu_traffic(kernel_key):
+    """dram read+write bytes per launch of the dominant kernel from the committed `ncu --set full` capture
+    (profiles/roofline_traffic.json, written from the .ncu-rep by tools/ncu_traffic.py); None when absent."""
+    p = os.path.join(ROOT, 'profiles', 'roofline_traffic.json')
+    try:
+        return json.load(open(p)).get(kernel_key, {}).get('dram_bytes_per_launch')
+    except Exception:
+        return None
+
+
+def stock_torch_gpu_run(dev, steps=5, warmup=2, batch=B_PER_GPU):
+    """'Stock PyTorch on the same B200' bar: the oracle restatement of the reference step --
+    the same ATen/cuDNN calls the reference modules make -- run eagerly on the GPU in fp32 (torch default TF32 settings).  Baseline
+    only: never on the product path."""
+    from oracle import vqvae_ref as R
+    p, b = R.make_state(1, DIM, K_CODES, 1, codebook='spread')
+    p = {k: v.to(dev) for k, v in p.items()}
+    b = {k: v.to(dev) for k, v in b.items()}
+    mel = R.make_mel(batch, N_MELS, FRAMES, 100).to(dev)
+    state = R.adam_init(p)
+    ts = []
+    for i in range(warmup + steps):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        r = R.step_grads(p, b, mel, 1.0)
+        p = R.adam_step(p, r['grads'], state, 1e-3)
+        b = r['buffers']
+        torch.cuda.synchronize()
+        if i >= warmup:
+            ts.append(time.perf_counter() - t0)
+    ms = 1e3 * sorted(ts)[len(ts) // 2]
+    return dict(value=batch * FRAMES / (ms / 1e3), unit='mel-frames/s', ms_per_step=ms,
+                what='oracle restatement of the reference step in eager PyTorch fp32 on this GPU (cuDNN/cuBLAS), batch %d' % batch)
+
+
 def peaks():
     p = os.path.join(ROOT, 'MEASURED_PEAKS.json')
     if os.path.exists(p):
@@ -108,6 +143,9 @@ def main():
     ap.add_argument('--impl', default='ours')
     ap.add_argument('--mode', default=os.environ.get('NSG_BENCH_MODE', 'tma'), choices=['tma', 'bf16', 'tc32', 'fp32'])
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--sync-bn', action='store_true', default=os.environ.get('NSG_BENCH_SYNC_BN', '0') == '1',
+                    help='N > 1: all-reduce BatchNorm statistics (N ranks == the reference on the global batch)')
+    ap.add_argument('--no-overlap', action='store_true', help='N > 1: one gradient all-reduce after backward')
     args = ap.parse_args()
     rank = int(os.environ.get('RANK', '0'))
     world = int(os.environ.get('WORLD_SIZE', '1'))
@@ -149,7 +187,6 @@ def main():
         model.act_dtype, model.conv_impl, model.vq_mode = torch.float32, 1, 1
     model.train()
     opt = nsg.optim.Adam(model, lr=1e-3)
-    opt.grad_scale = 1.0 / world
     flat = model.flatten_parameters()
     g = torch.Generator(device='cpu').manual_seed(1 + rank)
     n_in = 8
@@ -158,8 +195,13 @@ def main():
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)       # > 126 MB L2
 
     # the public train-step object: the train_vqvae loop body as one CUDA graph (train.py uses the same class)
-    hook = (lambda gflat: dist.all_reduce(gflat)) if world > 1 else None   # NCCL over NVLink; averaged via grad_scale
-    graphed = nsg.GraphedTrainStep(model, opt, (B_PER_GPU, 1, N_MELS, FRAMES), beta=1.0, grad_hook=hook)
+    # N > 1: dist.DataParallelStep = the same graph with the bucketed NCCL gradient all-reduce (decoder bucket beside
+    # the encoder backward), optional BatchNorm-statistic all-reduces, loss averaging; gradients averaged via grad_scale
+    if world > 1:
+        graphed = nsg.dist.DataParallelStep(model, opt, (B_PER_GPU, 1, N_MELS, FRAMES), beta=1.0,
+                                            sync_bn=args.sync_bn, overlap=not args.no_overlap)
+    else:
+        graphed = nsg.GraphedTrainStep(model, opt, (B_PER_GPU, 1, N_MELS, FRAMES), beta=1.0)
 
     def sync():
         torch.cuda.synchronize()
@@ -223,25 +265,48 @@ def main():
     kms = timed(kfn, 20)
     kflop = 2.0 * x.numel() // DIM * DIM * DIM * 9
     achieved = kflop / (kms / 1e3) / 1e12
+    # second half of BASELINE.json's metric: the VQ search alone at this workload's bottleneck size
+    nlat = B_PER_GPU * 20 * (FRAMES // 4)
+    zq_in = torch.randn(nlat, DIM, device=dev).to(model.act_dtype)
+    cbk = model.codebook.embedding.weight.detach()
+    vidx = torch.empty(nlat, dtype=torch.int64, device=dev)
+    vcodes, vsq = torch.empty_like(zq_in), torch.zeros(1, dtype=torch.float64, device=dev)
+    vmode = model.vq_mode if ops.vq_mode_serves(K_CODES, DIM, model.vq_mode) else 0
+    vfn = lambda i: ops.vq_forward(zq_in, cbk, vidx, vcodes, vsq, mode=vmode)
+    for _ in range(3):
+        vfn(0)
+    vms = timed(vfn, 20)
+    vq_tf = 2.0 * nlat * K_CODES * DIM / (vms / 1e3) / 1e12
+    vq_search = dict(value=vq_tf, unit='TFLOP/s', frac_of_peak=vq_tf / pk['tf_burst'], us=vms * 1e3, n=nlat, k=K_CODES,
+                     d=DIM, what='vq_forward (search + gather + sq-error; split-bf16 passes not counted), L2 flushed')
     roof = dict(bound='tensor', achieved=achieved, peak=pk['tf_burst'], unit='TFLOP/s', frac=achieved / pk['tf_burst'],
-                traffic=None, kernel='conv3x3 64->64 fwd (%s)' % ({0: 'CUDA-core fp32', 1: 'tcgen05 bf16, register-staged', 2: 'tcgen05 bf16, TMA-fed persistent'}[model.conv_impl]),
+                traffic=ncu_traffic('conv_tma_kernel_3x3_fwd'), kernel='conv3x3 64->64 fwd (%s)' % ({0: 'CUDA-core fp32', 1: 'tcgen05 bf16, register-staged', 2: 'tcgen05 bf16, TMA-fed persistent'}[model.conv_impl]),
                 peak_source=pk['src'], step_frac_of_tensor_peak=TRAIN_GFLOP * world / (ms / 1e3) / 1e3 / (pk['tf_sust'] * world))
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
-    cpu = None
+    cpu, stock = None, None
     if not args.no_cpu_baseline and world == 1:
         r = cpu_reference_run(2, 1, 8)
         cpu = dict(value=r['value'], unit='mel-frames/s', cores=r['cores'], kind='port', sample=r['sample'])
+        try:
+            stock = stock_torch_gpu_run(dev)
+        except Exception as e:          # a baseline must never take the bench line down
+            stock = dict(unavailable=str(e)[:200])
     out = dict(metric='vqvae_train_mel_frames_per_sec', value=value, unit='mel-frames/s', n_gpus=world,
                steps=args.steps, warmup=max(3, args.warmup), ms_per_step=ms, higher_is_better=True, scaling='weak',
                vs_baseline=None, dtype='bf16' if args.mode in ('bf16', 'tma') else 'f32', data='synthetic',
                config=dict(config, l2='256 MiB flush between timed steps; 8 rotating input batches',
-                           mode=args.mode, bn='local batch statistics per rank' if world > 1 else 'batch statistics'),
+                           mode=args.mode,
+                           bn=('batch statistics' if world == 1 else
+                               ('global-batch statistics (all-reduced, reference-equivalent)' if args.sync_bn
+                                else 'local batch statistics per rank (DDP semantics)')),
+                           collectives_per_step=(graphed.dp.collectives if world > 1 else 0)),
                e2e=dict(value=frames / (ms_e2e / 1e3), unit='mel-frames/s', ms_per_step=ms_e2e,
                         h2d_bytes_per_step=B_PER_GPU * N_MELS * FRAMES * 4, d2h_bytes_per_step=24),
-               gpu_launches=launches, clocks=clocks, roofline=roof, cpu_baseline=cpu)
+               gpu_launches=launches, clocks=clocks, roofline=roof, cpu_baseline=cpu, vq_search=vq_search,
+               stock_torch_gpu=stock)
     print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()

@@ -226,6 +226,16 @@ int nsg_vq_forward(const void* z, const float* codebook, long long n, int k, int
  * extension's statistics: table[idx[n], :] += alpha * (rows[n,:] - (sub ? sub[n,:] : 0)); counts[idx[n]] += 1. */
 int nsg_scatter_add(const void* rows, const void* sub, const long long* indices, long long n, int k, int d,
                     float alpha, float* table, float* counts, int dtype, void* stream);
+/* development aid: 0 (default) = block-aggregated scatter kernel where the shape is served (n >= 4096, d % 4 == 0,
+ * d <= 256), 1 = always the per-element atomic kernel.  Returns the previous setting; other values only query. */
+int nsg_scatter_mode(int mode);
+/* EMA codebook update (extension -- NOT in the reference; van den Oord et al. 2017, appendix A.1):
+ *   ema_count <- decay*ema_count + (1-decay)*counts;   ema_sum <- decay*ema_sum + (1-decay)*sums;
+ *   codebook[k,:] = ema_sum[k,:] / ((ema_count[k] + eps) / (sum ema_count + k*eps) * sum ema_count)
+ * counts [k] / sums [k,d] are one step's nsg_scatter_add outputs (table = sums with alpha 1, counts); every array is
+ * fp32; scratch is one caller-owned double. d % 4 == 0. */
+int nsg_ema_update(const float* counts, const float* sums, float* ema_count, float* ema_sum, float* codebook, int k,
+                   int d, float decay, float eps, double* scratch, void* stream);
 /* out[n,:] = table[indices[n],:]: nn.Embedding lookup / index_select (models.py:137-138, 194); out-of-range -> 0 */
 int nsg_gather_rows(const float* table, const long long* indices, long long n, int k, int d, void* out, int dtype,
                     void* stream);

@@ -225,7 +225,19 @@ long long vq_tc_workspace_bytes(int k, int d);
 
 using namespace nsg;
 
+namespace nsg {
+int scatter_add_agg(const void* rows, const void* sub, const long long* indices, long long n, int k, int d, float alpha,
+                    float* table, float* counts, int dtype, cudaStream_t stream);
+}
+static int g_scatter_mode = 0;
+
 extern "C" {
+
+int nsg_scatter_mode(int mode) {
+  const int old = g_scatter_mode;
+  if (mode == 0 || mode == 1) g_scatter_mode = mode;
+  return old;
+}
 
 long long nsg_vq_workspace_bytes(int k, int d, int mode) {
   if (mode == 0) return 0;
@@ -248,6 +260,10 @@ int nsg_scatter_add(const void* rows, const void* sub, const long long* indices,
                     float alpha, float* table, float* counts, int dtype, void* stream) {
   NSG_REQUIRE(rows && indices && table && n >= 0 && k >= 1 && d >= 1, "scatter_add: bad arguments");
   if (n == 0) return NSG_OK;
+  if (g_scatter_mode == 0) {      // block-aggregated kernel (scatter_ema.cu) when the shape is served
+    const int rc = scatter_add_agg(rows, sub, indices, n, k, d, alpha, table, counts, dtype, (cudaStream_t)stream);
+    if (rc != NSG_E_UNSUPPORTED) return rc;
+  }
   return NSG_DISPATCH_DTYPE(dtype, [&]() -> int {
     const int threads = 256;
     if (d % 4 == 0) {

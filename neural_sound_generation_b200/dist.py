@@ -1,0 +1,155 @@
+"""Batch-sharded data parallelism for the VQ-VAE train step (one process per GPU, NCCL over NVLink / NVSwitch).
+
+The reference is single-process (/root/reference/src/main.py:76), so the semantics are ours to define:
+
+    an N-rank run on a global batch of N*B items  ==  the reference's single process on those N*B items.
+
+Rank r trains items [r*B, (r+1)*B) (``shard_range``); model, codebook and optimiser state are replicated.  Per step:
+
+* gradients: every rank's losses are means over its shard, so the global gradient is the MEAN of the rank gradients:
+  all-reduce-sum of the flat gradient buffer, then ``optim.Adam.grad_scale = 1/N``.  The buffer is cut into two
+  buckets in reverse layer order (``bucket_slices``): the decoder bucket is reduced on a communication stream as soon
+  as the decoder's backward is complete and overlaps the bottleneck + encoder backward; codebook + encoder follow.
+* ``sync_bn=True``: BatchNorm batch statistics ([sum | sum sq] forward, [sum g | sum g*xhat] backward; 1 KB of fp64 per
+  layer and direction) are all-reduce-summed between the convolution epilogue that accumulates them and the
+  normalisation kernel that consumes them, and the element count is multiplied by N -- train-mode BatchNorm then sees
+  the global batch exactly as the reference does, and running statistics stay identical on every rank.  With
+  ``sync_bn=False`` (default; standard DDP semantics) each rank normalises with its own shard's statistics; that
+  is NOT equivalent to the reference on the global batch and is documented as such.
+* the three loss scalars are averaged across ranks for logging.
+
+All collectives are issued through ``torch.distributed`` (NCCL on GPUs; the host logic is backend-agnostic and is
+tested with gloo on CPU) and are captured into the step's CUDA graph.
+"""
+import torch
+import torch.distributed as dist
+
+from .graph import GraphedTrainStep
+
+
+def shard_range(rank, world, global_batch):
+    """Items [lo, hi) of the global batch owned by ``rank``; the batch must divide evenly (equal shards keep
+    mean-of-means == global mean)."""
+    if global_batch % world != 0:
+        raise ValueError('global batch %d does not divide over %d ranks' % (global_batch, world))
+    per = global_batch // world
+    return rank * per, (rank + 1) * per
+
+
+def bucket_slices(names, offsets, total):
+    """Cut the flat gradient buffer (parameters in ``named_parameters`` order: encoder.*, codebook.*, decoder.*) into
+    the two all-reduce buckets: {'decoder': (lo, hi), 'rest': (lo, hi)}."""
+    dec = [o for n, o in zip(names, offsets) if n.startswith('decoder.')]
+    if not dec:
+        return {'decoder': (total, total), 'rest': (0, total)}
+    lo = min(dec)
+    if any(o > lo and not n.startswith('decoder.') for n, o in zip(names, offsets)):
+        raise ValueError('decoder parameters are not contiguous at the end of the flat buffer')
+    return {'decoder': (lo, total), 'rest': (0, lo)}
+
+
+def allreduce_sum_(t, group=None):
+    """In-place all-reduce-sum on the current stream (no-op for a single rank)."""
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
+    return t
+
+
+def allreduce_buckets_(flat, slices, order=('decoder', 'rest'), group=None):
+    """All-reduce-sum every bucket of ``flat`` (1-D tensor) in ``order``; equals one all-reduce of the whole buffer."""
+    for key in order:
+        lo, hi = slices[key]
+        if hi > lo:
+            allreduce_sum_(flat[lo:hi], group)
+    return flat
+
+
+class DataParallel(object):
+    """Per-model data-parallel state; attached as ``model.dp`` and consulted by the kernel schedule
+    (``engine_tma.EngineTMA``) and by ``VQVAE.loss_and_grads``."""
+
+    def __init__(self, sync_bn=False, overlap=True, group=None):
+        if not (dist.is_available() and dist.is_initialized()):
+            raise RuntimeError('DataParallel needs an initialised torch.distributed process group')
+        self.group = group
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        self.sync_bn = bool(sync_bn)
+        self.overlap = bool(overlap)
+        self.comm = None            # communication stream (CUDA only)
+        self.collectives = 0        # issued per step (bench.py reports it)
+
+    # -- BatchNorm statistics -------------------------------------------------------------------------------
+    def reduce_stats(self, stats):
+        """stats: fp64 [2*C] sums accumulated by a convolution epilogue on the current stream."""
+        allreduce_sum_(stats, self.group)
+        self.collectives += 1
+
+    # -- gradient buckets -----------------------------------------------------------------------------------
+    def _slices(self, flat):
+        s = flat.get('buckets')
+        if s is None:
+            s = flat['buckets'] = bucket_slices(flat['names'], flat['offs'], flat['total'])
+        return s
+
+    def decoder_done(self, eng, ctx, G, flat):
+        """Called when the decoder's data-gradient chain has been issued on the current stream.  The decoder's
+        weight-gradient images are folded and its bucket is all-reduced on the communication stream."""
+        if not self.overlap:
+            return
+        main = torch.cuda.current_stream()
+        if self.comm is None:
+            self.comm = torch.cuda.Stream()
+        self.comm.wait_stream(main)
+        if ctx.forked:
+            self.comm.wait_stream(eng.side)         # decoder weight gradients issued so far on the side stream
+        lo, hi = self._slices(flat)['decoder']
+        with torch.cuda.stream(self.comm):
+            eng.unpack_part(G, 'decoder')
+            allreduce_sum_(flat['grads'][lo:hi], self.group)
+        self.collectives += 1
+
+    def finish(self, eng, ctx, G, flat):
+        """End of backward: fold the remaining gradient images, all-reduce the remaining bucket(s), join streams."""
+        sl = self._slices(flat)
+        if self.overlap:
+            eng.finish_backward(ctx, G, part='encoder')
+            lo, hi = sl['rest']
+            allreduce_sum_(flat['grads'][lo:hi], self.group)
+            torch.cuda.current_stream().wait_stream(self.comm)
+            self.collectives += 1
+        else:
+            eng.finish_backward(ctx, G)
+            allreduce_sum_(flat['grads'], self.group)
+            self.collectives += 1
+
+
+class DataParallelStep(GraphedTrainStep):
+    """``GraphedTrainStep`` for one rank of a data-parallel job: ``step = DataParallelStep(model, optimizer,
+    (B_local, n_mels, T), beta, sync_bn=False); losses = step(c_local)``.
+
+    ``losses`` are the GLOBAL-batch means [loss_recons, loss_vq, loss_commit] (averaged over ranks).  The model must
+    run the bf16 TMA engine (``conv_impl = 2``); parameters must be identical on every rank at construction (they are
+    broadcast from rank 0 to make sure)."""
+
+    def __init__(self, model, optimizer, batch_shape, beta=1.0, sync_bn=False, overlap=True, group=None):
+        self.dp = DataParallel(sync_bn=sync_bn, overlap=overlap, group=group)
+        model.__dict__['dp'] = self.dp
+        optimizer.grad_scale = 1.0 / self.dp.world
+        flat = model.flatten_parameters()
+        if self.dp.world > 1:
+            dist.broadcast(flat['params'], src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+            for _, b in model.named_buffers():
+                dist.broadcast(b, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+        super(DataParallelStep, self).__init__(model, optimizer, batch_shape, beta)
+
+    def _body(self, grad_hook):
+        self.dp.collectives = 0
+        self.optimizer.zero_grad()
+        losses, outs = self.model.loss_and_grads(self.c, beta=self.beta)
+        self.optimizer.step()
+        if self.dp.world > 1:
+            allreduce_sum_(losses, self.dp.group)
+            losses.mul_(1.0 / self.dp.world)
+            self.dp.collectives += 1
+        return losses, outs

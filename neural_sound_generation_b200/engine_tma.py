@@ -48,6 +48,7 @@ class EngineTMA(object):
         self._key = None
         self.side = None            # second stream: weight gradients run beside the data-gradient chain
         self.overlap_wgrad = True
+        self.dp = None              # dist.DataParallel: cross-rank BatchNorm statistics / bucketed gradient all-reduce
 
     # ------------------------------------------------------------------ packed images
     def _prepare(self, P):
@@ -61,8 +62,11 @@ class EngineTMA(object):
         self.dwp = torch.zeros(ntaps_total * D * D, dtype=torch.float32, device=dev)
         self.layers = {}
         self.pack_items, self.unpack_items = [], []
+        self.dwp_split = 0          # first element of the decoder layers' gradient images (they are laid out last)
         ow, og = 0, 0
         for name, k, s, p, tr in TC_LAYERS:
+            if name.startswith('decoder.') and self.dwp_split == 0:
+                self.dwp_split = og
             L = _Layer()
             L.name, L.k, L.s, L.p, L.tr = name, k, s, p, tr
             w = P[name + '.weight']
@@ -92,8 +96,10 @@ class EngineTMA(object):
                                 (P['decoder.6.weight'], self.c1['dec6_dgrad'], -1, 1, 16)]
         self._key = key
 
-    def _unpack_items(self, G):
-        return [(L.dwp, G[L.name + '.weight'], L.k * L.k, L.wci_g, L.wco_g) for L in self.layers.values()]
+    def _unpack_items(self, G, part=None):
+        """part: None = every layer, 'decoder' / 'encoder' = that half (the data-parallel gradient buckets)."""
+        return [(L.dwp, G[L.name + '.weight'], L.k * L.k, L.wci_g, L.wco_g) for L in self.layers.values()
+                if part is None or L.name.startswith(part + '.')]
 
     # ------------------------------------------------------------------ helpers
     def _bn(self, ctx, name):
@@ -170,6 +176,9 @@ class EngineTMA(object):
         bn = self._bn(ctx, name)
         out = torch.empty_like(h)
         n = h.numel() // self.dim
+        if ctx.training and self.dp is not None and self.dp.sync_bn:
+            self.dp.reduce_stats(bn['fstats'])      # statistics of the GLOBAL batch, as the single-process reference sees
+            n *= self.dp.world
         if ctx.training:
             ops.bn_act64(h, out, P[name + '.weight'], P[name + '.bias'], stats=bn['fstats'], count=n, res=res,
                          relu_out=relu_out, eps=BN_EPS, momentum=BN_MOMENTUM,
@@ -184,8 +193,16 @@ class EngineTMA(object):
     def _bn_bwd(self, ctx, P, G, name, g, h, dbias_prev):
         bn = self._bn(ctx, name)
         dh = torch.empty_like(h)
-        ops.bn_bwd64(g, h, dh, bn['bstats'], h.numel() // self.dim, bn['mean'], bn['invstd'], P[name + '.weight'],
-                     dgamma=G[name + '.weight'], dbeta=G[name + '.bias'], dbias_prev=dbias_prev)
+        n = h.numel() // self.dim
+        dgamma, dbeta = G[name + '.weight'], G[name + '.bias']
+        if self.dp is not None and self.dp.sync_bn:
+            # the reduced sums ARE the global dgamma / dbeta: only rank 0 contributes them to the gradient all-reduce
+            self.dp.reduce_stats(bn['bstats'])
+            n *= self.dp.world
+            if self.dp.rank != 0:
+                dgamma = dbeta = None
+        ops.bn_bwd64(g, h, dh, bn['bstats'], n, bn['mean'], bn['invstd'], P[name + '.weight'],
+                     dgamma=dgamma, dbeta=dbeta, dbias_prev=dbias_prev)
         return dh
 
     # ------------------------------------------------------------------ ResBlock (models.py:145-158)
@@ -348,14 +365,24 @@ class EngineTMA(object):
             ops.conv_gemm(g, g_a0, P['encoder.0.weight'], dx)
         return dx
 
-    def finish_backward(self, ctx, G):
-        """Fold the packed weight-gradient images into the reference-layout gradients (one launch) and clear them."""
+    def finish_backward(self, ctx, G, part=None):
+        """Fold the packed weight-gradient images into the reference-layout gradients (one launch) and clear them.
+        ``part`` restricts this to one half of the network (see ``unpack_part``)."""
         if ctx.forked:
             torch.cuda.current_stream().wait_stream(self.side)
             ctx.forked = False
         ctx.keep = []
-        ops.wgrad_unpack_many(self._unpack_items(G))
-        self.dwp.zero_()
+        self.unpack_part(G, part)
+
+    def unpack_part(self, G, part=None):
+        """Unpack + clear the gradient images of 'decoder', 'encoder' or (None) all layers on the current stream."""
+        ops.wgrad_unpack_many(self._unpack_items(G, part))
+        if part is None:
+            self.dwp.zero_()
+        elif part == 'decoder':
+            self.dwp[self.dwp_split:].zero_()
+        else:
+            self.dwp[:self.dwp_split].zero_()
 
     # ------------------------------------------------------------------ bottleneck (models.py:127-142)
     def quantize(self, z_e, codebook, want_codes=True, sqerr=None):

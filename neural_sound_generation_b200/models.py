@@ -70,6 +70,26 @@ class VQEmbedding(nn.Module):
         return z_q_x, z_q_x_bar
 
 
+def ema_codebook_update(embedding, z_e_x, indices, ema_count, ema_sum, decay=0.99, eps=1e-5, dp=None):
+    """EMA codebook training (extension; the reference trains the codebook by Adam through loss_vq).
+
+    ``embedding``: the ``VQEmbedding``; ``z_e_x`` (B,D,H,W) encoder output; ``indices`` flat int64 from ``vq_st``;
+    ``ema_count`` (K,) / ``ema_sum`` (K,D) fp32 state, updated in place together with ``embedding.embedding.weight``.
+    One scatter-add launch gathers counts[K] + sums[K,D]; under data parallelism (``dp``) they are all-reduce-summed
+    before the update so every rank applies the global statistics."""
+    w = embedding.embedding.weight
+    k, d = w.shape
+    z = _nhwc(z_e_x.detach())
+    stats = torch.zeros(k * d + k, dtype=torch.float32, device=w.device)
+    sums, counts = stats[:k * d].view(k, d), stats[k * d:]
+    ops.scatter_add(z, indices.reshape(-1), sums, alpha=1.0, counts=counts)
+    if dp is not None:
+        dp.reduce_stats(stats)
+    with torch.no_grad():
+        ops.ema_update(counts, sums, ema_count, ema_sum, w.data, decay, eps)
+    return counts, sums
+
+
 class _GatherRows(Function):
     """torch.index_select(weight, 0, indices) with the index_add backward (models.py:137-138)."""
 
@@ -185,7 +205,10 @@ class VQVAE(nn.Module):
             if eng is None or eng.vq_mode != self.vq_mode:
                 eng = EngineTMA(self.input_dim, self.dim, self.z_dim, self.vq_mode)
                 self.__dict__['_eng_tma'] = eng
+            eng.dp = self.__dict__.get('dp')        # dist.DataParallel (None = single process)
             return eng
+        if self.__dict__.get('dp') is not None:
+            raise ops.A.NsgError('data parallelism is implemented for the bf16 TMA engine (conv_impl = 2)')
         return Engine(self.input_dim, self.dim, self.z_dim, self.act_dtype, self.conv_impl, self.vq_mode)
 
     def _named(self):
@@ -293,11 +316,17 @@ class VQVAE(nn.Module):
         dpre = torch.empty((b, h, wt), dtype=torch.float32, device=x.device)
         ops.recon_loss(xt32.view(b, h, wt), c3, sums[0:1], dpre)
         g_st = eng.decoder_bwd(ectx, P, G, dpre.view(b, h, wt, 1))
+        dp = getattr(eng, 'dp', None)
+        if dp is not None:
+            dp.decoder_done(eng, ectx, G, self._flat)      # decoder bucket: unpack + all-reduce beside the encoder backward
         n_lat = z_e.numel()
         dz = eng.bottleneck_bwd(ectx, g_st, z_e, z_q, 2.0 * beta / n_lat)  # ST clone + beta * d commit / d z_e
         ops.scatter_add(z_q, idx, G['codebook.embedding.weight'], alpha=2.0 / n_lat, sub=z_e)  # d loss_vq / d e
         eng.encoder_bwd(ectx, P, G, dz)
-        eng.finish_backward(ectx, G)
+        if dp is not None:
+            dp.finish(eng, ectx, G, self._flat)
+        else:
+            eng.finish_backward(ectx, G)
         # (python-scalar multiplies keep this CUDA-graph capturable: no host tensor is created)
         l_rec, l_vq = sums[0] * (1.0 / (b * h * w)), sums[1] * (1.0 / z_e.numel())
         losses = torch.stack([l_rec, l_vq, l_vq])

@@ -222,6 +222,22 @@ def scatter_add(rows, indices, table, alpha=1.0, sub=None, counts=None):
     launch_count += 1
 
 
+def ema_update(counts, sums, ema_count, ema_sum, codebook, decay=0.99, eps=1e-5):
+    """EMA codebook update from one step's scatter_add statistics (extension; include/nsg_b200.h)."""
+    global launch_count
+    A.require_device()
+    _cuda(counts, sums, ema_count, ema_sum, codebook)
+    for t in (counts, sums, ema_count, ema_sum, codebook):
+        if t.dtype != torch.float32 or not t.is_contiguous():
+            raise A.NsgError('ema_update: fp32 contiguous tensors required')
+    k, d = codebook.shape
+    scratch = torch.empty(1, dtype=torch.float64, device=codebook.device)
+    rc = A.load().nsg_ema_update(A.ptr(counts), A.ptr(sums), A.ptr(ema_count), A.ptr(ema_sum), A.ptr(codebook), k, d,
+                                 float(decay), float(eps), A.ptr(scratch), A.stream_ptr())
+    A.check(rc, 'nsg_ema_update')
+    launch_count += 2
+
+
 def vq_backward_inputs(g_st, z, zq, coef, dz):
     global launch_count
     A.require_device()

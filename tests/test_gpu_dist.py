@@ -1,0 +1,140 @@
+"""Two-GPU data-parallel equivalence (needs >= 2 visible B200s; skipped otherwise).
+
+sync_bn=True : 2 ranks x B items  ==  one GPU on the 2B-item global batch (the reference's semantics)
+sync_bn=False: averaged gradients ==  mean of the two shards' single-GPU gradients (local BatchNorm statistics)
+"""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+pytestmark = pytest.mark.gpu
+
+B_LOCAL, FRAMES, STEPS = 2, 64, 2
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(('127.0.0.1', 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _model(dev, seed=5):
+    import neural_sound_generation_b200 as nsg
+    from oracle import vqvae_ref as R
+    p, b = R.make_state(1, 64, 512, seed, codebook='spread')
+    m = nsg.VQVAE(1, 64, 512)
+    sd = dict(p)
+    sd.update(b)
+    m.load_state_dict({k: v.clone() for k, v in sd.items()})
+    m = m.to(dev).train()
+    m.act_dtype, m.conv_impl, m.vq_mode = torch.bfloat16, 2, 1
+    return m
+
+
+def _rel(a, b):
+    return ((a.double() - b.double()).norm() / b.double().norm().clamp_min(1e-30)).item()
+
+
+def _worker(rank, world, port, sync_bn, out):
+    import neural_sound_generation_b200 as nsg
+    from neural_sound_generation_b200 import dist as nd
+    from oracle import vqvae_ref as R
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    torch.cuda.set_device(rank)
+    dev = torch.device('cuda', rank)
+    dist.init_process_group('nccl', rank=rank, world_size=world, device_id=dev)
+    try:
+        mels = [R.make_mel(B_LOCAL * world, 80, FRAMES, 50 + i).to(dev) for i in range(STEPS)]
+        lo, hi = nd.shard_range(rank, world, B_LOCAL * world)
+        m = _model(dev)
+        opt = nsg.optim.Adam(m, lr=1e-3)
+        step = nd.DataParallelStep(m, opt, (B_LOCAL, 1, 80, FRAMES), beta=1.0, sync_bn=sync_bn)
+        losses = []
+        for i in range(STEPS):
+            losses.append(step(mels[i][lo:hi]).clone())
+        torch.cuda.synchronize()
+        n_coll = step.dp.collectives
+        params = m._flat['params'].clone()
+        rm = dict(m.named_buffers())['encoder.1.running_mean'].clone()
+        # every rank must hold identical parameters after the update
+        other = [torch.empty_like(params) for _ in range(world)]
+        dist.all_gather(other, params)
+        assert all(torch.equal(other[0], o) for o in other), 'ranks diverged'
+        if rank == 0:
+            res = dict(n_coll=n_coll)
+            m1 = _model(dev)
+            o1 = nsg.optim.Adam(m1, lr=1e-3)
+            if sync_bn:
+                # single GPU on the global batch
+                ref_losses = []
+                g1 = nsg.GraphedTrainStep(m1, o1, (B_LOCAL * world, 1, 80, FRAMES), beta=1.0)
+                for i in range(STEPS):
+                    ref_losses.append(g1(mels[i]).clone())
+                torch.cuda.synchronize()
+                res['loss'] = max(_rel(a, b) for a, b in zip(losses, ref_losses))
+                res['params'] = _rel(params, m1._flat['params'])
+                res['running_mean'] = _rel(rm, dict(m1.named_buffers())['encoder.1.running_mean'])
+            else:
+                # mean of the two shards' single-GPU gradients (each with its own BatchNorm statistics), same Adam
+                for i in range(STEPS):
+                    gsum = None
+                    for r in range(world):
+                        a, b = nd.shard_range(r, world, B_LOCAL * world)
+                        o1.zero_grad()
+                        m1.loss_and_grads(mels[i][a:b], beta=1.0)
+                        g = m1._flat['grads'].clone()
+                        gsum = g if gsum is None else gsum + g
+                    o1.zero_grad()
+                    m1._flat['grads'].copy_(gsum)
+                    o1.grad_scale = 1.0 / world
+                    o1.step()
+                torch.cuda.synchronize()
+                res['params'] = _rel(params, m1._flat['params'])
+            out.put(res)
+    finally:
+        dist.destroy_process_group()
+
+
+def _launch(sync_bn):
+    if torch.cuda.device_count() < 2:
+        pytest.skip('needs two GPUs')
+    ctx = mp.get_context('spawn')
+    q = ctx.SimpleQueue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, sync_bn, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(240)
+    for p in procs:
+        if p.is_alive():
+            p.kill()
+            pytest.fail('data-parallel worker hung')
+        assert p.exitcode == 0
+    return q.get()
+
+
+@pytest.mark.timeout(300)
+def test_two_ranks_syncbn_equal_single_gpu_on_global_batch():
+    res = _launch(True)
+    print(res)
+    # 20 BatchNorm statistic reductions + 2 gradient buckets + the loss scalars per step
+    assert res['n_coll'] == 23
+    assert res['loss'] < 2e-3
+    assert res['running_mean'] < 1e-4
+    assert res['params'] < 2e-2         # two bf16 Adam steps; differences come from reduction order only
+
+
+@pytest.mark.timeout(300)
+def test_two_ranks_local_bn_runs_and_stays_in_sync():
+    res = _launch(False)
+    print(res)
+    assert res['n_coll'] == 3
+    assert res['params'] < 5e-3

@@ -360,6 +360,78 @@ def test_scatter_add_gather_and_bottleneck_grad():
     assert relerr(t3, torch.zeros(5, 3, dtype=torch.float64).index_add_(0, i3, r3.double())) < 1e-6
 
 
+@pytest.mark.parametrize('n,k,d,dtype,dist', [
+    (40960, 512, 64, torch.bfloat16, 'uniform'),      # config 2: 10 partitions x 30 codeword groups
+    (40960, 512, 64, torch.float32, 'skew'),          # most rows on a handful of codewords (run aggregation)
+    (5000, 37, 64, torch.float32, 'uniform'),         # ragged last partition, K not a multiple of G
+    (9001, 1000, 128, torch.bfloat16, 'uniform'),     # 32 lanes per row
+    (8192, 64, 256, torch.float32, 'one'),            # two vector groups per lane; every row on one codeword
+    (20000, 8192, 12, torch.float32, 'uniform'),      # D/4 not a power of two; mostly untouched codewords
+    (1 << 18, 512, 64, torch.bfloat16, 'uniform'),    # large-N regime: few groups, big shared table
+])
+def test_scatter_add_aggregated_kernel(n, k, d, dtype, dist):
+    """Block-aggregated scatter-add (scatter_ema.cu) == index_add_ (vector_quantization.py:58-61) == the
+    per-element kernel; counts == bincount; out-of-range indices are skipped."""
+    rng = np.random.RandomState(n % 1000 + d)
+    rows, sub = _rand(rng, n, d).to(dtype), _rand(rng, n, d).to(dtype)
+    if dist == 'uniform':
+        idx = rng.randint(0, k, n)
+    elif dist == 'skew':
+        idx = np.minimum((rng.exponential(3.0, n)).astype(np.int64), k - 1)
+    else:
+        idx = np.full(n, k // 2, np.int64)
+    idx = torch.tensor(idx)
+    idx[::997] = -1                 # ignored, like the per-element kernel
+    idx[5::1013] = k + 3
+    ok = (idx >= 0) & (idx < k)
+    ref = torch.zeros(k, d, dtype=torch.float64).index_add_(0, idx[ok], 0.25 * (rows.double() - sub.double())[ok])
+    cref = torch.bincount(idx[ok], minlength=k).float()
+    lib = nsg._cabi.load()
+    out = {}
+    for mode in (0, 1):
+        prev = lib.nsg_scatter_mode(mode)
+        try:
+            table = torch.zeros(k, d, device=DEV)
+            counts = torch.zeros(k, device=DEV)
+            ops.scatter_add(rows.to(DEV), idx.to(DEV), table, alpha=0.25, sub=sub.to(DEV), counts=counts)
+            # accumulate semantics: a second call without sub / counts adds on top
+            ops.scatter_add(rows.to(DEV), idx.to(DEV), table, alpha=-0.25)
+            ops.scatter_add(sub.to(DEV), idx.to(DEV), table, alpha=0.25)
+            torch.cuda.synchronize()
+        finally:
+            lib.nsg_scatter_mode(prev)
+        out[mode] = table
+        assert torch.equal(counts.cpu(), cref), mode
+    # three passes cancel exactly up to fp32 rounding: compare the first pass through a fresh call instead
+    for mode in (0, 1):
+        prev = lib.nsg_scatter_mode(mode)
+        try:
+            table = torch.zeros(k, d, device=DEV)
+            ops.scatter_add(rows.to(DEV), idx.to(DEV), table, alpha=0.25, sub=sub.to(DEV))
+        finally:
+            lib.nsg_scatter_mode(prev)
+        assert relerr(table, ref) < 2e-6, (mode, relerr(table, ref))
+        assert float(out[mode].abs().max()) < 1e-3 * float(ref.abs().max() + 1)
+
+
+def test_ema_update_vs_oracle_restatement():
+    """EMA codebook extension (not in the reference: parity unpinned) against oracle/vq_ref.ema_update."""
+    rng = np.random.RandomState(3)
+    n, k, d = 6000, 128, 64
+    z = _rand(rng, n, d)
+    idx = torch.tensor(rng.randint(0, k - 9, n))          # nine dead codewords
+    ema_n = torch.tensor(rng.rand(k).astype(np.float32) * 5)
+    ema_m = _rand(rng, k, d)
+    n_ref, m_ref, e_ref, c_ref, s_ref = vq_ref.ema_update(z.numpy(), idx.numpy(), ema_n.numpy(), ema_m.numpy(), 0.97, 1e-5)
+    emb = nsg.VQEmbedding(k, d).to(DEV)
+    gn, gm = ema_n.to(DEV), ema_m.to(DEV).contiguous()
+    z_nchw = z.view(n // 100, 10, 10, d).permute(0, 3, 1, 2).to(DEV)
+    counts, sums = nsg.models.ema_codebook_update(emb, z_nchw, idx.to(DEV), gn, gm, decay=0.97, eps=1e-5)
+    assert np.array_equal(counts.cpu().numpy(), c_ref) and relerr(sums, s_ref) < 1e-5
+    assert relerr(gn, n_ref) < 1e-6 and relerr(gm, m_ref) < 1e-5
+    assert relerr(emb.embedding.weight.detach(), e_ref) < 1e-5
+
+
 def test_adam_known_answer(golden_dir):
     """torch.optim.Adam KAT recorded from the reference's optimizer (tests/golden/adam_kat.npz)."""
     g = np.load(os.path.join(golden_dir, 'adam_kat.npz'))
