@@ -284,7 +284,7 @@ def main():
                 peak_source=pk['src'], step_frac_of_tensor_peak=TRAIN_GFLOP * world / (ms / 1e3) / 1e3 / (pk['tf_sust'] * world))
     if rank != 0:
         if world > 1:
-            dist.destroy_process_group()
+            nsg.dist.shutdown(graphed)
         return
     cpu, stock = None, None
     if not args.no_cpu_baseline and world == 1:
@@ -307,9 +307,9 @@ def main():
                         h2d_bytes_per_step=B_PER_GPU * N_MELS * FRAMES * 4, d2h_bytes_per_step=24),
                gpu_launches=launches, clocks=clocks, roofline=roof, cpu_baseline=cpu, vq_search=vq_search,
                stock_torch_gpu=stock)
-    print(json.dumps(out))
+    print(json.dumps(out), flush=True)
     if world > 1:
-        dist.destroy_process_group()
+        nsg.dist.shutdown(graphed)
 
 
 if __name__ == '__main__':

@@ -11,7 +11,7 @@ from .models import VQEmbedding, ResBlock, VQVAE, weights_init, to_scalar  # noq
 from .train import train_vqvae  # noqa: F401
 from .test import test_vqvae  # noqa: F401
 from . import optim  # noqa: F401
-from .graph import GraphedTrainStep  # noqa: F401
+from .graph import GraphedTrainStep, GraphedInference  # noqa: F401
 from . import dist  # noqa: F401  (DataParallelStep: batch-sharded data parallelism)
 
 VectorQuantizer = VQEmbedding   # alias for the name BASELINE.json's north_star uses

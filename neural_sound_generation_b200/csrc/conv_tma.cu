@@ -33,19 +33,26 @@ constexpr int TM_MAX_STAGES = 8;
 constexpr int TM_MAX_TAPS = 16;
 constexpr uint32_t TM_SMEM_LIMIT = 224 * 1024;      // dynamic part; the kernels also hold ~2 KB of static shared memory
 
+// Taps that differ only by a vertical shift share ONE activation box: a "group" is (tensor map, horizontal shift,
+// first row) and its box holds box_h + halo rows of box_w pixels; tap t of the group reads the 128-pixel sub-block
+// that starts roff[t] rows into the box (box_w is a multiple of 8 pixels, so every sub-block starts on a 1024-byte
+// swizzle atom).  A 3x3 tap set costs 3 boxes per tile instead of 9 -- the L2 -> SM path is what bounds these kernels.
 struct TmaPhase {
   int sub_h, sub_w;              // output sub-grid of this stride phase
   int tiles_h, tiles_w, tile0;   // tile grid and index of its first tile
-  int ntaps;
+  int ntaps, ngroups;
   int out_stride, off_h, off_w;  // oh = ohs * out_stride + off_h
-  signed char dh[TM_MAX_TAPS], dw[TM_MAX_TAPS];
-  unsigned char wslot[TM_MAX_TAPS];
+  signed char gdh[TM_MAX_TAPS], gdw[TM_MAX_TAPS];          // per group: box origin relative to the tile origin
+  unsigned char gmap[TM_MAX_TAPS], gfirst[TM_MAX_TAPS + 1];  // per group: tensor map, first tap (taps sorted by group)
+  unsigned char roff[TM_MAX_TAPS], wslot[TM_MAX_TAPS];     // per tap: row offset inside the box, weight image
 };
 
 struct TmaConvParams {
   int batch, full_h, full_w;
   int in_stride;                 // 1: one tensor map; 2: four parity maps
   int box_w, box_h, log2_bw;
+  int halo;                      // extra box rows shared by vertically shifted taps
+  uint32_t slot_bytes, row_bytes;  // one ring slot ((box_h + halo) rows); one box row (box_w pixels)
   int nphases, total_tiles, nw, stages;
   unsigned long long* dbg;       // optional clock64 stamps of CTA 0 (nsg_debug_timeline), null in production
   TmaPhase ph[4];
@@ -254,7 +261,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
   uint8_t* sm = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sW = sm;                                         // nw weight images
   uint8_t* sA = sm + (size_t)P.nw * TM_W_BYTES;             // ring of activation boxes
-  uint8_t* tail = sA + (size_t)P.stages * TM_A_BYTES;
+  uint8_t* tail = sA + (size_t)P.stages * P.slot_bytes;
   __shared__ __align__(16) float sPar[5 * TM_C];            // [5][64]: bias, mscale, mshift, mean, invstd
   __shared__ float sStat[2 * TM_C];                         // [2][64]
   uint64_t* bars = reinterpret_cast<uint64_t*>(tail);
@@ -316,19 +323,14 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
         const TmaTile tl = decode_tile(P, (int)blockIdx.x + i * (int)gridDim.x);
         const TmaPhase& ph = P.ph[tl.p];
         const int w0 = tl.tw * P.box_w, h0 = tl.th * P.box_h;
-        for (int t = 0; t < ph.ntaps; ++t, ++it) {
+        for (int g = 0; g < ph.ngroups; ++g, ++it) {
           const int s = it % stages, round = it / stages;
           if (round > 0) mbar_wait(&empty[s], (uint32_t)((round - 1) & 1));
-          mbar_arrive_expect_tx(&full[s], TM_A_BYTES);
-          const int dh = ph.dh[t], dw = ph.dw[t];
-          uint8_t* dst = sA + (size_t)s * TM_A_BYTES;
-          if (P.in_stride == 1) {
-            tma::load_4d(dst, &tm0, 0, w0 + dw, h0 + dh, tl.n, &full[s]);
-          } else {
-            const int par = (dh & 1) * 2 + (dw & 1);
-            const CUtensorMap* tm = par == 0 ? &tm0 : (par == 1 ? &tm1 : (par == 2 ? &tm2 : &tm3));
-            tma::load_4d(dst, tm, 0, w0 + (dw >> 1), h0 + (dh >> 1), tl.n, &full[s]);
-          }
+          mbar_arrive_expect_tx(&full[s], P.slot_bytes);
+          uint8_t* dst = sA + (size_t)s * P.slot_bytes;
+          const int par = ph.gmap[g];
+          const CUtensorMap* tm = par == 0 ? &tm0 : (par == 1 ? &tm1 : (par == 2 ? &tm2 : &tm3));
+          tma::load_4d(dst, tm, 0, w0 + ph.gdw[g], h0 + ph.gdh[g], tl.n, &full[s]);
         }
         tm_stamp(P.dbg, 2 + (i < 3 ? i : 3));          // 2..5: producer finished issuing tile i
       }
@@ -347,15 +349,18 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
         if (use > 0) mbar_wait(&acc_empty[as], (uint32_t)((use - 1) & 1));
         tc_fence_after();
         const uint32_t d = tmem_base + (uint32_t)as * TM_C;
-        for (int t = 0; t < ph.ntaps; ++t, ++it) {
+        for (int g = 0; g < ph.ngroups; ++g, ++it) {
           const int s = it % stages, round = it / stages;
           mbar_wait(&full[s], (uint32_t)(round & 1));
           if (it == 0) tm_stamp(P.dbg, 7);               // first activation box landed
           tc_fence_after();
-          const uint64_t a = sw128_desc(smem_u32(sA + (size_t)s * TM_A_BYTES));
-          const uint64_t b = sw128_desc(smem_u32(sW + (size_t)ph.wslot[t] * TM_W_BYTES));
+          const uint32_t box = smem_u32(sA + (size_t)s * P.slot_bytes);
+          for (int t = ph.gfirst[g]; t < ph.gfirst[g + 1]; ++t) {
+            const uint64_t a = sw128_desc(box + (uint32_t)ph.roff[t] * P.row_bytes);
+            const uint64_t b = sw128_desc(smem_u32(sW + (size_t)ph.wslot[t] * TM_W_BYTES));
 #pragma unroll
-          for (int ks = 0; ks < 4; ++ks) umma_bf16(d, a + 2 * ks, b + 2 * ks, idesc, (t | ks) != 0);
+            for (int ks = 0; ks < 4; ++ks) umma_bf16(d, a + 2 * ks, b + 2 * ks, idesc, (t | ks) != 0);
+          }
           umma_commit(&empty[s]);
         }
         umma_commit(&acc_full[as]);
@@ -433,7 +438,7 @@ static int tma_shape_ok(const nsg_conv_geom* cg, const char* what) {
   return NSG_OK;
 }
 
-static void pick_box(int sub_w, int pixels, int* box_w, int* box_h, int* log2_bw) {
+static void pick_box_w(int sub_w, int pixels, int* box_w, int* box_h, int* log2_bw) {
   int bw = 8, l2 = 3;
   while (bw < pixels && bw < sub_w) {
     bw <<= 1;
@@ -442,6 +447,63 @@ static void pick_box(int sub_w, int pixels, int* box_w, int* box_h, int* log2_bw
   *box_w = bw;
   *box_h = pixels / bw;
   *log2_bw = l2;
+}
+
+// group the taps of one phase by (tensor map, horizontal shift); returns the number of groups and the largest
+// vertical span - 1 (= halo rows).  in_stride 2 addresses the four parity views of the tensor.
+struct TapGroups {
+  int ngroups, halo;
+  int gmap[TM_MAX_TAPS], gdw[TM_MAX_TAPS], gdh[TM_MAX_TAPS], gcount[TM_MAX_TAPS];
+  int tap[TM_MAX_TAPS][TM_MAX_TAPS];       // tap indices (into TapGeom) per group
+  int edh[TM_MAX_TAPS];                    // effective vertical shift per tap
+};
+static void group_taps(const TapGeom& g, TapGroups* G) {
+  G->ngroups = 0;
+  G->halo = 0;
+  for (int t = 0; t < g.ntaps; ++t) {
+    int map = 0, dw = g.dw[t], dh = g.dh[t];
+    if (g.in_stride == 2) {
+      map = (dh & 1) * 2 + (dw & 1);
+      dw >>= 1;
+      dh >>= 1;
+    }
+    G->edh[t] = dh;
+    int gi = -1;
+    for (int i = 0; i < G->ngroups; ++i)
+      if (G->gmap[i] == map && G->gdw[i] == dw) gi = i;
+    if (gi < 0) {
+      gi = G->ngroups++;
+      G->gmap[gi] = map; G->gdw[gi] = dw; G->gdh[gi] = dh; G->gcount[gi] = 0;
+    }
+    if (dh < G->gdh[gi]) G->gdh[gi] = dh;
+    G->tap[gi][G->gcount[gi]++] = t;
+  }
+  for (int i = 0; i < G->ngroups; ++i)
+    for (int j = 0; j < G->gcount[i]; ++j) {
+      const int span = G->edh[G->tap[i][j]] - G->gdh[i];
+      if (span > G->halo) G->halo = span;
+    }
+}
+
+// 128-pixel tile shape (box_w x box_h, box_w a power of two >= 8) that minimises the bytes the TMA unit moves:
+// tiles * groups * (box_h + halo) * box_w, which accounts for ragged tiles and for the halo rows together.
+static void pick_box(const TapGeom* phases, const TapGroups* groups, int np, int batch, int pixels, int halo,
+                     int* box_w, int* box_h, int* log2_bw) {
+  long long best = -1;
+  for (int l2 = 3; (1 << l2) <= pixels; ++l2) {
+    const int bw = 1 << l2, bh = pixels / bw;
+    if (bh + halo > 256) continue;                       // TMA box dimension limit
+    long long cost = 0;
+    for (int i = 0; i < np; ++i) {
+      if (phases[i].sub_h <= 0 || phases[i].sub_w <= 0) continue;
+      const long long tiles = (long long)((phases[i].sub_w + bw - 1) / bw) * ((phases[i].sub_h + bh - 1) / bh) * batch;
+      cost += tiles * groups[i].ngroups * (bh + halo) * bw;
+    }
+    if (best < 0 || cost <= best) {                      // ties: the wider box (longer contiguous runs)
+      best = cost;
+      *box_w = bw; *box_h = bh; *log2_bw = l2;
+    }
+  }
 }
 
 // tensor maps over `in` (N, in_h, in_w, 64) bf16: plain view (in_stride 1) or the four parity views (in_stride 2)
@@ -488,9 +550,16 @@ int conv_gemm_tma(const nsg_conv_geom* cg, const void* in, const void* packed, c
   P.batch = cg->batch; P.full_h = cg->out_h; P.full_w = cg->out_w;
   P.in_stride = phases[0].in_stride;
   NSG_REQUIRE(P.in_stride == 1 || P.in_stride == 2, "conv_gemm_tma: input stride %d", P.in_stride);
-  int max_sub_w = 1;
-  for (int i = 0; i < np; ++i) max_sub_w = phases[i].sub_w > max_sub_w ? phases[i].sub_w : max_sub_w;
-  pick_box(max_sub_w, TM_M, &P.box_w, &P.box_h, &P.log2_bw);
+  static TapGroups groups[4];
+  int halo = 0;
+  for (int i = 0; i < np; ++i) {
+    group_taps(phases[i], &groups[i]);
+    if (phases[i].sub_h > 0 && phases[i].sub_w > 0 && groups[i].halo > halo) halo = groups[i].halo;
+  }
+  pick_box(phases, groups, np, cg->batch, TM_M, halo, &P.box_w, &P.box_h, &P.log2_bw);
+  P.halo = halo;
+  P.row_bytes = (uint32_t)P.box_w * 128;
+  P.slot_bytes = (uint32_t)(P.box_h + halo) * P.row_bytes;
   P.nw = cg->ksize * cg->ksize;
   int tiles = 0, nph = 0;
   for (int i = 0; i < np; ++i) {
@@ -505,24 +574,34 @@ int conv_gemm_tma(const nsg_conv_geom* cg, const void* in, const void* packed, c
     tiles += ph.tiles_w * ph.tiles_h * cg->batch;
     ph.ntaps = g.ntaps;
     ph.out_stride = g.out_stride; ph.off_h = g.off_h; ph.off_w = g.off_w;
-    for (int t = 0; t < g.ntaps; ++t) {
-      ph.dh[t] = (signed char)g.dh[t];
-      ph.dw[t] = (signed char)g.dw[t];
-      ph.wslot[t] = (unsigned char)g.woff[t];
+    const TapGroups& tg = groups[i];
+    ph.ngroups = tg.ngroups;
+    int nt = 0;
+    for (int gi = 0; gi < tg.ngroups; ++gi) {
+      ph.gmap[gi] = (unsigned char)tg.gmap[gi];
+      ph.gdw[gi] = (signed char)tg.gdw[gi];
+      ph.gdh[gi] = (signed char)tg.gdh[gi];
+      ph.gfirst[gi] = (unsigned char)nt;
+      for (int j = 0; j < tg.gcount[gi]; ++j, ++nt) {
+        const int t = tg.tap[gi][j];
+        ph.roff[nt] = (unsigned char)(tg.edh[t] - tg.gdh[gi]);
+        ph.wslot[nt] = (unsigned char)g.woff[t];
+      }
     }
+    ph.gfirst[tg.ngroups] = (unsigned char)nt;
   }
   if (tiles == 0) return NSG_OK;
   P.nphases = nph;
   P.total_tiles = tiles;
   const uint32_t tail = (2 * TM_MAX_STAGES + 5) * 8 + 64;
-  int stages = (int)((TM_SMEM_LIMIT - 1024 - tail - (uint32_t)P.nw * TM_W_BYTES) / TM_A_BYTES);
+  int stages = (int)((TM_SMEM_LIMIT - 1024 - tail - (uint32_t)P.nw * TM_W_BYTES) / P.slot_bytes);
   if (stages > TM_MAX_STAGES) stages = TM_MAX_STAGES;
   NSG_REQUIRE(stages >= 2, "conv_gemm_tma: weights do not leave room for the activation ring");
   P.stages = stages;
   P.dbg = g_timeline;
-  const size_t smem = 1024 + (size_t)P.nw * TM_W_BYTES + (size_t)stages * TM_A_BYTES + tail;
+  const size_t smem = 1024 + (size_t)P.nw * TM_W_BYTES + (size_t)stages * P.slot_bytes + tail;
   CUtensorMap tm[4];
-  if (int rc = encode_input_maps(tm, in, cg->batch, cg->in_h, cg->in_w, P.in_stride, P.box_w, P.box_h)) return rc;
+  if (int rc = encode_input_maps(tm, in, cg->batch, cg->in_h, cg->in_w, P.in_stride, P.box_w, P.box_h + halo)) return rc;
   static bool configured = false;
   if (!configured) {
     cudaError_t err = cudaFuncSetAttribute(conv_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -786,7 +865,7 @@ int conv_wgrad_tma(const nsg_conv_geom* cg, const void* p, const void* q, float*
   P.batch = cg->batch; P.q_h = cg->out_h; P.q_w = cg->out_w;
   P.in_stride = cg->stride;
   int l2;
-  pick_box(cg->out_w, WG_KP, &P.box_w, &P.box_h, &l2);
+  pick_box_w(cg->out_w, WG_KP, &P.box_w, &P.box_h, &l2);
   P.tiles_w = (cg->out_w + P.box_w - 1) / P.box_w;
   P.tiles_h = (cg->out_h + P.box_h - 1) / P.box_h;
   P.total_tiles = P.tiles_w * P.tiles_h * cg->batch;
@@ -992,7 +1071,7 @@ int conv_c1_tc(const nsg_conv_geom* cg, const void* in, const void* packed, cons
   NSG_REQUIRE(e.tanh_out == 0 || e.tanh_out == 2, "conv_c1_tc: output activation must be none or ReLU");
   C1tConvParams P{};
   P.batch = cg->batch; P.in_h = cg->in_h; P.in_w = cg->in_w; P.out_h = cg->out_h; P.out_w = cg->out_w;
-  pick_box(cg->out_w, TM_M, &P.box_w, &P.box_h, &P.log2_bw);
+  pick_box_w(cg->out_w, TM_M, &P.box_w, &P.box_h, &P.log2_bw);
   P.tiles_w = (cg->out_w + P.box_w - 1) / P.box_w;
   P.tiles_h = (cg->out_h + P.box_h - 1) / P.box_h;
   P.total_tiles = P.tiles_w * P.tiles_h * cg->batch;
@@ -1345,7 +1424,7 @@ int wgrad_c1_tc(const nsg_conv_geom* cg, const void* p, const void* q, float* dw
   C1tWgradParams P{};
   P.batch = cg->batch; P.in_h = cg->in_h; P.in_w = cg->in_w; P.q_h = cg->out_h; P.q_w = cg->out_w;
   P.w_tap_stride_c = cg->w_cout_stride;
-  pick_box(cg->out_w, WG_KP, &P.box_w, &P.box_h, &P.log2_bw);
+  pick_box_w(cg->out_w, WG_KP, &P.box_w, &P.box_h, &P.log2_bw);
   P.tiles_w = (cg->out_w + P.box_w - 1) / P.box_w;
   P.tiles_h = (cg->out_h + P.box_h - 1) / P.box_h;
   P.total_tiles = P.tiles_w * P.tiles_h * cg->batch;

@@ -55,6 +55,25 @@ def allreduce_sum_(t, group=None):
     return t
 
 
+def shutdown(step=None, timeout_s=20.0):
+    """Orderly end of a data-parallel process: release ``step``'s graph, then destroy the process group; if NCCL does
+    not return within ``timeout_s`` the process exits hard (all results must have been written by then)."""
+    import os
+    import sys
+    import threading
+    if step is not None and getattr(step, 'graph', None) is not None:
+        step.close()
+    if not (dist.is_available() and dist.is_initialized()):
+        return
+    sys.stdout.flush()
+    sys.stderr.flush()
+    t = threading.Timer(timeout_s, lambda: os._exit(0))
+    t.daemon = True
+    t.start()
+    dist.destroy_process_group()
+    t.cancel()
+
+
 def allreduce_buckets_(flat, slices, order=('decoder', 'rest'), group=None):
     """All-reduce-sum every bucket of ``flat`` (1-D tensor) in ``order``; equals one all-reduce of the whole buffer."""
     for key in order:

@@ -53,7 +53,46 @@ class GraphedTrainStep(object):
         self.optimizer.step()
         return losses, outs
 
+    def close(self):
+        """Release the CUDA graph (it holds the NCCL kernels of the captured collectives) -- call before
+        ``torch.distributed.destroy_process_group()``, which otherwise can wait on the communicator forever."""
+        dev = self.c.device
+        torch.cuda.synchronize(dev)
+        self.graph.reset()
+        self.graph = None
+        torch.cuda.synchronize(dev)
+
     def __call__(self, c):
         self.c.copy_(c.reshape(self.c.shape), non_blocking=True)
         self.graph.replay()
         return self.losses
+
+
+class GraphedInference(object):
+    """``infer = GraphedInference(model, (B, 1, n_mels, T)); latents, x_tilde = infer(x)``.
+
+    The eval-mode ``encode`` -> ``decode`` round trip of /root/reference/src/models.py:188-196 (BatchNorm running
+    statistics, no gradient) captured once as a CUDA graph: batch-1 utterances are pure launch latency
+    (SURVEY.md section 8d, config 5), so the ~25 launches replay with one ``cudaGraphLaunch``.  Returned tensors are
+    static (valid until the next call)."""
+
+    def __init__(self, model, x_shape):
+        self.model = model.eval()
+        dev = next(model.parameters()).device
+        self.x = torch.zeros(tuple(x_shape), dtype=torch.float32, device=dev)
+        with torch.no_grad():
+            self._body()                    # configures every kernel variant outside the capture
+            torch.cuda.synchronize(dev)
+            self.graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.graph):
+                self.latents, self.x_tilde = self._body()
+        torch.cuda.synchronize(dev)
+
+    def _body(self):
+        latents = self.model.encode(self.x)
+        return latents, self.model.decode(latents)
+
+    def __call__(self, x):
+        self.x.copy_(x.reshape(self.x.shape), non_blocking=True)
+        self.graph.replay()
+        return self.latents, self.x_tilde

@@ -98,8 +98,12 @@ def _worker(rank, world, port, sync_bn, out):
                 torch.cuda.synchronize()
                 res['params'] = _rel(params, m1._flat['params'])
             out.put(res)
-    finally:
-        dist.destroy_process_group()
+            print('RESULT', res, flush=True)
+        nd.shutdown(step, timeout_s=10.0)
+    except BaseException:
+        import traceback
+        traceback.print_exc()
+        os._exit(1)
 
 
 def _launch(sync_bn):
@@ -112,7 +116,7 @@ def _launch(sync_bn):
     for p in procs:
         p.start()
     for p in procs:
-        p.join(240)
+        p.join(100)
     for p in procs:
         if p.is_alive():
             p.kill()
@@ -121,7 +125,7 @@ def _launch(sync_bn):
     return q.get()
 
 
-@pytest.mark.timeout(300)
+@pytest.mark.timeout(240)
 def test_two_ranks_syncbn_equal_single_gpu_on_global_batch():
     res = _launch(True)
     print(res)
@@ -132,7 +136,7 @@ def test_two_ranks_syncbn_equal_single_gpu_on_global_batch():
     assert res['params'] < 2e-2         # two bf16 Adam steps; differences come from reduction order only
 
 
-@pytest.mark.timeout(300)
+@pytest.mark.timeout(240)
 def test_two_ranks_local_bn_runs_and_stays_in_sync():
     res = _launch(False)
     print(res)
