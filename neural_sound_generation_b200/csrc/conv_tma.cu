@@ -31,6 +31,12 @@ constexpr uint32_t TM_A_BYTES = TM_M * 128;     // one activation box
 constexpr uint32_t TM_W_BYTES = TM_C * 128;     // one tap's weight image (bf16, K-major SWIZZLE_128B)
 constexpr int TM_MAX_STAGES = 8;
 constexpr int TM_MAX_TAPS = 16;
+constexpr int TM_TILE_TABLE = 32;
+// Accumulators per tile the K = 16 steps rotate over (the epilogue adds them).  Measured (tools/microbench/mma_rate.cu):
+// back-to-back tcgen05.mma into ONE accumulator already run at the shared-memory operand rate (48 cycles for
+// M128 N64 K16), so independent chains buy nothing: 1.
+constexpr int TM_CHAINS = 1;
+constexpr int TM_ACC_COLS = TM_CHAINS * TM_C;       // TMEM columns per tile accumulator set                 // local tiles with precomputed coordinates (more: decoded on the fly)
 constexpr uint32_t TM_SMEM_LIMIT = 224 * 1024;      // dynamic part; the kernels also hold ~2 KB of static shared memory
 
 // Taps that differ only by a vertical shift share ONE activation box: a "group" is (tensor map, horizontal shift,
@@ -252,6 +258,16 @@ __device__ __forceinline__ TmaTile decode_tile(const TmaConvParams& P, int t) {
   return r;
 }
 
+__device__ __forceinline__ TmaTile fetch_tile(const TmaConvParams& P, const int4* table, int i) {
+  if (i < TM_TILE_TABLE) {
+    const int4 v = table[i];
+    TmaTile r;
+    r.p = v.x; r.n = v.y; r.th = v.z; r.tw = v.w;
+    return r;
+  }
+  return decode_tile(P, (int)blockIdx.x + i * (int)gridDim.x);
+}
+
 __global__ void __launch_bounds__(320, 1)
 conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__ CUtensorMap tm1,
                 const __grid_constant__ CUtensorMap tm2, const __grid_constant__ CUtensorMap tm3,
@@ -264,6 +280,13 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
   uint8_t* tail = sA + (size_t)P.stages * P.slot_bytes;
   __shared__ __align__(16) float sPar[5 * TM_C];            // [5][64]: bias, mscale, mshift, mean, invstd
   __shared__ float sStat[2 * TM_C];                         // [2][64]
+  // issue tables: the producer and MMA threads are single threads running dependent scalar code, so everything they
+  // would otherwise derive per tile / tap (integer divisions, byte loads from the parameter bank, descriptor
+  // packing) is computed once, in parallel, here
+  __shared__ uint32_t sTapA[4 * TM_MAX_TAPS];               // per (phase, tap): A sub-block offset, descriptor units
+  __shared__ uint32_t sTapB[4 * TM_MAX_TAPS];               // per (phase, tap): low word of the weight descriptor
+  __shared__ int sGrp[4 * TM_MAX_TAPS];                     // per (phase, group): map | dw+128 << 8 | dh+128 << 16
+  __shared__ int4 sTile[TM_TILE_TABLE];                     // per local tile: phase, image, th, tw
   uint64_t* bars = reinterpret_cast<uint64_t*>(tail);
   uint64_t* full = bars;                                    // [8]
   uint64_t* empty = bars + TM_MAX_STAGES;                   // [8]
@@ -285,6 +308,26 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
     sStat[tid] = 0.f;
     sStat[TM_C + tid] = 0.f;
   }
+  const int ntiles_mine = ((int)blockIdx.x < P.total_tiles)
+                              ? (P.total_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+  if (tid >= 64 && tid < 128) {
+    const int e = tid - 64, p = e >> 4, t = e & 15;
+    if (p < P.nphases) {
+      const TmaPhase& ph = P.ph[p];
+      sTapA[e] = ((uint32_t)ph.roff[t] * P.row_bytes) >> 4;
+      sTapB[e] = (((smem_u32(sW) + (uint32_t)ph.wslot[t] * TM_W_BYTES) >> 4) & 0x3FFFu) | (1u << 16);
+      const int gcount = t < ph.ngroups ? (int)ph.gfirst[t + 1] - (int)ph.gfirst[t] : 0;
+      sGrp[e] = (int)ph.gmap[t] | (((int)ph.gdw[t] + 128) << 8) | (((int)ph.gdh[t] + 128) << 16) |
+                ((int)ph.gfirst[t] << 24) | (gcount << 28);
+    }
+  }
+  if (tid >= 128 && tid < 128 + TM_TILE_TABLE) {
+    const int i = tid - 128;
+    if (i < ntiles_mine) {
+      const TmaTile tl = decode_tile(P, (int)blockIdx.x + i * (int)gridDim.x);
+      sTile[i] = make_int4(tl.p, tl.n, tl.th, tl.tw);
+    }
+  }
   if (tid == 0) {
     for (int s = 0; s < TM_MAX_STAGES; ++s) {
       mbar_init(&full[s], 1);
@@ -303,13 +346,11 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
       tma::prefetch_desc(&tm3);
     }
   }
-  if (warp == 1) tmem_alloc<128>(tmem_slot);
+  if (warp == 1) tmem_alloc<2 * TM_ACC_COLS>(tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const int ntiles_mine = ((int)blockIdx.x < P.total_tiles)
-                              ? (P.total_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
   if (tid == 0) tm_stamp(P.dbg, 1);
 
   if (warp == 0) {
@@ -319,18 +360,26 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
       for (int t = 0; t < P.nw; ++t)
         bulk_g2s(sW + (size_t)t * TM_W_BYTES, wimg + (size_t)t * TM_W_BYTES, TM_W_BYTES, wfull);
       int it = 0;
+      int s = 0;
+      uint32_t eparity = 1;                    // first pass over the ring: slots are free (wait on the preceding phase)
+      const uint32_t slot_bytes = P.slot_bytes;
+      const uint32_t sA_u32 = smem_u32(sA);
       for (int i = 0; i < ntiles_mine; ++i) {
-        const TmaTile tl = decode_tile(P, (int)blockIdx.x + i * (int)gridDim.x);
-        const TmaPhase& ph = P.ph[tl.p];
+        const TmaTile tl = fetch_tile(P, sTile, i);
+        const int ngroups = P.ph[tl.p].ngroups;
         const int w0 = tl.tw * P.box_w, h0 = tl.th * P.box_h;
-        for (int g = 0; g < ph.ngroups; ++g, ++it) {
-          const int s = it % stages, round = it / stages;
-          if (round > 0) mbar_wait(&empty[s], (uint32_t)((round - 1) & 1));
-          mbar_arrive_expect_tx(&full[s], P.slot_bytes);
-          uint8_t* dst = sA + (size_t)s * P.slot_bytes;
-          const int par = ph.gmap[g];
+        for (int g = 0; g < ngroups; ++g, ++it) {
+          mbar_wait(&empty[s], eparity);
+          mbar_arrive_expect_tx(&full[s], slot_bytes);
+          const int gi = sGrp[tl.p * TM_MAX_TAPS + g];
+          const int par = gi & 3;
           const CUtensorMap* tm = par == 0 ? &tm0 : (par == 1 ? &tm1 : (par == 2 ? &tm2 : &tm3));
-          tma::load_4d(dst, tm, 0, w0 + ph.gdw[g], h0 + ph.gdh[g], tl.n, &full[s]);
+          tma::load_4d_u32(sA_u32 + (uint32_t)s * slot_bytes, tm, 0, w0 + ((gi >> 8) & 255) - 128,
+                           h0 + ((gi >> 16) & 255) - 128, tl.n, &full[s]);
+          if (++s == stages) {
+            s = 0;
+            eparity ^= 1;
+          }
         }
         tm_stamp(P.dbg, 2 + (i < 3 ? i : 3));          // 2..5: producer finished issuing tile i
       }
@@ -341,27 +390,55 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
       const uint32_t idesc = idesc_bf16(TM_M, TM_C);
       mbar_wait(wfull, 0);
       tm_stamp(P.dbg, 6);                                // weights resident
-      int it = 0;
+      int it = 0, s = 0;
+      uint32_t fparity = 0;
+      const uint32_t slot_units = P.slot_bytes >> 4;
+      const uint32_t a_base = ((smem_u32(sA) >> 4) & 0x3FFFu) | (1u << 16);     // low word of sw128_desc(sA)
+      constexpr uint64_t DESC_HI = (64ull << 32) | (1ull << 46) | (2ull << 61);
       for (int i = 0; i < ntiles_mine; ++i) {
-        const TmaTile tl = decode_tile(P, (int)blockIdx.x + i * (int)gridDim.x);
+        const TmaTile tl = fetch_tile(P, sTile, i);
         const TmaPhase& ph = P.ph[tl.p];
+        const int ngroups = ph.ngroups;
         const int as = i & 1, use = i >> 1;
         if (use > 0) mbar_wait(&acc_empty[as], (uint32_t)((use - 1) & 1));
         tc_fence_after();
-        const uint32_t d = tmem_base + (uint32_t)as * TM_C;
-        for (int g = 0; g < ph.ngroups; ++g, ++it) {
-          const int s = it % stages, round = it / stages;
-          mbar_wait(&full[s], (uint32_t)(round & 1));
-          if (it == 0) tm_stamp(P.dbg, 7);               // first activation box landed
-          tc_fence_after();
-          const uint32_t box = smem_u32(sA + (size_t)s * P.slot_bytes);
-          for (int t = ph.gfirst[g]; t < ph.gfirst[g + 1]; ++t) {
-            const uint64_t a = sw128_desc(box + (uint32_t)ph.roff[t] * P.row_bytes);
-            const uint64_t b = sw128_desc(smem_u32(sW + (size_t)ph.wslot[t] * TM_W_BYTES));
+        const uint32_t d = tmem_base + (uint32_t)as * TM_ACC_COLS;
+        for (int g = 0; g < ngroups; ++g, ++it) {
+          // this group's (<= 4) tap descriptors are fetched before the box wait: the issuing thread runs dependent
+          // scalar code, so every load left between two tcgen05.mma shows up as an idle tensor pipe
+          const uint32_t gi = (uint32_t)sGrp[tl.p * TM_MAX_TAPS + g];
+          const int first = (gi >> 24) & 15, cnt = gi >> 28;
+          uint32_t ao[4], bo[4];
 #pragma unroll
-            for (int ks = 0; ks < 4; ++ks) umma_bf16(d, a + 2 * ks, b + 2 * ks, idesc, (t | ks) != 0);
+          for (int j = 0; j < 4; ++j) {
+            const int e = tl.p * TM_MAX_TAPS + ((first + j) & 15);
+            ao[j] = sTapA[e];
+            bo[j] = sTapB[e];
           }
+          mbar_wait(&full[s], fparity);
+          if (it == 0) tm_stamp(P.dbg, 7);               // first activation box landed
+          if (i == 1 && g < 3) tm_stamp(P.dbg, 21 + 3 * g);      // 21,24,27: tile 1, box of group g landed
+          tc_fence_after();
+          const uint32_t box = a_base + (uint32_t)s * slot_units;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            if (j < cnt) {
+              const uint64_t a = DESC_HI | (uint64_t)(box + ao[j]);
+              const uint64_t b = DESC_HI | (uint64_t)bo[j];
+              const uint32_t accum = (first + j) != 0;
+#pragma unroll
+              for (int ks = 0; ks < 4; ++ks)
+                umma_bf16(d + (ks % TM_CHAINS) * TM_C, a + 2 * ks, b + 2 * ks, idesc,
+                          (ks >= TM_CHAINS) ? 1u : accum);
+            }
+          }
+          if (i == 1 && g < 3) tm_stamp(P.dbg, 22 + 3 * g);      // 22,25,28: its instructions issued
           umma_commit(&empty[s]);
+          if (i == 1 && g < 3) tm_stamp(P.dbg, 23 + 3 * g);      // 23,26,29: commit issued
+          if (++s == stages) {
+            s = 0;
+            fparity ^= 1;
+          }
         }
         umma_commit(&acc_full[as]);
         tm_stamp(P.dbg, 8 + (i < 3 ? i : 3));           // 8..11: MMAs of tile i issued
@@ -374,7 +451,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
     const int r = q * 32 + lane;
     const int bw = r & (P.box_w - 1), bh = r >> P.log2_bw;
     for (int i = grp; i < ntiles_mine; i += 2) {
-      const TmaTile tl = decode_tile(P, (int)blockIdx.x + i * (int)gridDim.x);
+      const TmaTile tl = fetch_tile(P, sTile, i);
       const TmaPhase& ph = P.ph[tl.p];
       const int ohs = tl.th * P.box_h + bh, ows = tl.tw * P.box_w + bw;
       const bool valid = ohs < ph.sub_h && ows < ph.sub_w;
@@ -386,10 +463,22 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
       if (tid == 64 + 128 * grp) tm_stamp(P.dbg, 12 + (i < 3 ? i : 3));     // 12..15: accumulator of tile i ready
       tc_fence_after();
       uint32_t acc0[32], acc1[32];
-      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)grp * TM_C;
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)grp * TM_ACC_COLS;
       tmem_ld32(taddr, acc0);
       tmem_ld32(taddr + 32, acc1);
       tmem_ld_wait();
+#pragma unroll
+      for (int c = 1; c < TM_CHAINS; ++c) {
+        uint32_t part[32];
+        tmem_ld32(taddr + c * TM_C, part);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; ++j) acc0[j] = __float_as_uint(__uint_as_float(acc0[j]) + __uint_as_float(part[j]));
+        tmem_ld32(taddr + c * TM_C + 32, part);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; ++j) acc1[j] = __float_as_uint(__uint_as_float(acc1[j]) + __uint_as_float(part[j]));
+      }
       tc_fence_before();
       mbar_arrive(&acc_empty[grp]);
       epi_row(E, epi, sPar, sStat, out, o, valid, acc0, acc1, lane);
@@ -403,7 +492,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc<128>(tmem_base);
+  if (warp == 1) tmem_dealloc<2 * TM_ACC_COLS>(tmem_base);
   if (tid == 0) tm_stamp(P.dbg, 20);
 }
 
@@ -485,22 +574,27 @@ static void group_taps(const TapGeom& g, TapGroups* G) {
     }
 }
 
-// 128-pixel tile shape (box_w x box_h, box_w a power of two >= 8) that minimises the bytes the TMA unit moves:
-// tiles * groups * (box_h + halo) * box_w, which accounts for ragged tiles and for the halo rows together.
+// 128-pixel tile shape (box_w x box_h, box_w a power of two >= 8).  Measured on B200 with every SM loading
+// (profiles/r1_tma_v9_conv_timeline.txt): boxes of one CTA land one after the other at 22-30 bytes per cycle whatever
+// their shape (16 KB 64x2, 24 KB 32x6 and 32 KB 64x4 boxes all fit that line), so the cost to minimise is the bytes
+// the TMA unit moves, tiles * groups * (box_h + halo) * box_w -- ragged tiles and halo rows together; ties go to the
+// shape with fewer box rows.
 static void pick_box(const TapGeom* phases, const TapGroups* groups, int np, int batch, int pixels, int halo,
                      int* box_w, int* box_h, int* log2_bw) {
-  long long best = -1;
+  long long best_rows = -1, best_bytes = -1;
   for (int l2 = 3; (1 << l2) <= pixels; ++l2) {
     const int bw = 1 << l2, bh = pixels / bw;
     if (bh + halo > 256) continue;                       // TMA box dimension limit
-    long long cost = 0;
+    long long rows = 0, bytes = 0;
     for (int i = 0; i < np; ++i) {
       if (phases[i].sub_h <= 0 || phases[i].sub_w <= 0) continue;
       const long long tiles = (long long)((phases[i].sub_w + bw - 1) / bw) * ((phases[i].sub_h + bh - 1) / bh) * batch;
-      cost += tiles * groups[i].ngroups * (bh + halo) * bw;
+      rows += tiles * groups[i].ngroups * (bh + halo);
+      bytes += tiles * groups[i].ngroups * (bh + halo) * bw;
     }
-    if (best < 0 || cost <= best) {                      // ties: the wider box (longer contiguous runs)
-      best = cost;
+    if (best_rows < 0 || bytes < best_bytes || (bytes == best_bytes && rows <= best_rows)) {
+      best_rows = rows;
+      best_bytes = bytes;
       *box_w = bw; *box_h = bh; *log2_bw = l2;
     }
   }

@@ -65,6 +65,14 @@ __device__ __forceinline__ void load_4d(void* dst_smem, const CUtensorMap* tm, i
       "l"(reinterpret_cast<uint64_t>(tm)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(tc::smem_u32(bar))
       : "memory");
 }
+__device__ __forceinline__ void load_4d_u32(uint32_t dst_smem, const CUtensorMap* tm, int c0, int c1, int c2, int c3,
+                                            uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5}], "
+      "[%6];" ::"r"(dst_smem),
+      "l"(reinterpret_cast<uint64_t>(tm)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(tc::smem_u32(bar))
+      : "memory");
+}
 #endif
 
 }  // namespace tma
