@@ -302,7 +302,7 @@ def main():
                            bn=('batch statistics' if world == 1 else
                                ('global-batch statistics (all-reduced, reference-equivalent)' if args.sync_bn
                                 else 'local batch statistics per rank (DDP semantics)')),
-                           collectives_per_step=(graphed.dp.collectives if world > 1 else 0)),
+                           collectives_per_step=(graphed.collectives_per_step if world > 1 else 0)),
                e2e=dict(value=frames / (ms_e2e / 1e3), unit='mel-frames/s', ms_per_step=ms_e2e,
                         h2d_bytes_per_step=B_PER_GPU * N_MELS * FRAMES * 4, d2h_bytes_per_step=24),
                gpu_launches=launches, clocks=clocks, roofline=roof, cpu_baseline=cpu, vq_search=vq_search,

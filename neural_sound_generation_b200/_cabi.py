@@ -24,7 +24,7 @@ EXPORTS = [
     'nsg_conv_pack_bytes', 'nsg_conv_pack_weights', 'nsg_conv_gemm_tc', 'nsg_conv_wgrad_tc',
     'nsg_conv_pack_many', 'nsg_conv_gemm_tma', 'nsg_conv_wgrad_tma', 'nsg_wgrad_unpack_many',
     'nsg_bn_act64', 'nsg_bn_bwd64', 'nsg_relu64', 'nsg_vq_bwd_stats64', 'nsg_debug_timeline',
-    'nsg_c1_conv_tc', 'nsg_c1_convT_tc', 'nsg_c1_wgrad_tc', 'nsg_scatter_mode', 'nsg_ema_update',
+    'nsg_c1_conv_tc', 'nsg_c1_convT_tc', 'nsg_c1_wgrad_tc', 'nsg_scatter_mode', 'nsg_ema_update', 'nsg_vq_resident',
 ]
 
 
@@ -100,6 +100,7 @@ def load():
     lib.nsg_recon_loss.argtypes = [vp, vp, i, i, i, i, vp, vp, vp]
     lib.nsg_gather_rows.argtypes = [vp, vp, ll, i, i, vp, i, vp]
     lib.nsg_scatter_mode.argtypes = [i]
+    lib.nsg_vq_resident.argtypes = [i]
     lib.nsg_ema_update.argtypes = [vp, vp, vp, vp, vp, i, i, f, f, vp, vp]
     lib.nsg_tanh_bwd.argtypes = [vp, vp, vp, ll, vp]
     lib.nsg_adam_step.argtypes = [vp, vp, vp, vp, ll, f, f, f, f, f, vp, vp]

@@ -459,7 +459,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
                                     (ows * ph.out_stride + ph.off_w)) * TM_C) : 0;
       EpiOperands E;
       epi_begin(E, epi, o, valid);      // operands of the first 32 channels are requested before the accumulator wait
-      mbar_wait(&acc_full[grp], (uint32_t)((i >> 1) & 1));
+      mbar_wait_backoff(&acc_full[grp], (uint32_t)((i >> 1) & 1));
       if (tid == 64 + 128 * grp) tm_stamp(P.dbg, 12 + (i < 3 ? i : 3));     // 12..15: accumulator of tile i ready
       tc_fence_after();
       uint32_t acc0[32], acc1[32];

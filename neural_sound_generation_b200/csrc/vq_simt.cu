@@ -207,6 +207,24 @@ __global__ void gather_rows_kernel(const float* __restrict__ table, const long l
   }
 }
 
+// D % 4 == 0: one thread moves 4 channels (a 16-byte table read, an 8- or 16-byte store); the lanes of a warp cover
+// consecutive channel groups of consecutive rows, so stores are full lines and the index is read once per row group
+template <typename T>
+__global__ void __launch_bounds__(256)
+gather_rows_vec_kernel(const float* __restrict__ table, const long long* __restrict__ idx, long long N, int K, int dq,
+                       T* __restrict__ out) {
+  const long long total = N * dq;
+  const long long stride = (long long)gridDim.x * 256;
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < total; i += stride) {
+    const long long n = i / dq;
+    const int c4 = (int)(i - n * dq);
+    const long long k = __ldg(idx + n);
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (k >= 0 && k < K) v = __ldg(reinterpret_cast<const float4*>(table + (k * dq + c4) * 4));
+    Act<T>::st4(out + i * 4, v);
+  }
+}
+
 int vq_forward_simt(const void* z, const float* codebook, long long n, int k, int d, int dtype,
                     long long* indices, void* codes, double* sqerr, cudaStream_t stream) {
   return NSG_DISPATCH_DTYPE(dtype, [&]() -> int {
@@ -229,9 +247,21 @@ namespace nsg {
 int scatter_add_agg(const void* rows, const void* sub, const long long* indices, long long n, int k, int d, float alpha,
                     float* table, float* counts, int dtype, cudaStream_t stream);
 }
-static int g_scatter_mode = 0;
+// measured on B200 (profiles/r1_vq_kernels.txt): the per-element vector-atomic kernel beats the block-aggregated one at
+// every size tried (12 vs 24 us at N = 40960, 302 vs 336 us at N = 2^20; the shared-memory float atomics of the
+// aggregation are compare-and-swap loops), so it is the default; mode 0 remains for skewed assignments
+static int g_scatter_mode = 1;
+namespace nsg {
+extern int g_vq_resident;
+}
 
 extern "C" {
+
+int nsg_vq_resident(int enable) {
+  const int old = g_vq_resident;
+  if (enable == 0 || enable == 1) g_vq_resident = enable;
+  return old;
+}
 
 int nsg_scatter_mode(int mode) {
   const int old = g_scatter_mode;
@@ -260,7 +290,7 @@ int nsg_scatter_add(const void* rows, const void* sub, const long long* indices,
                     float alpha, float* table, float* counts, int dtype, void* stream) {
   NSG_REQUIRE(rows && indices && table && n >= 0 && k >= 1 && d >= 1, "scatter_add: bad arguments");
   if (n == 0) return NSG_OK;
-  if (g_scatter_mode == 0) {      // block-aggregated kernel (scatter_ema.cu) when the shape is served
+  if (g_scatter_mode == 0) {      // block-aggregated kernel (scatter_ema.cu) when the shape is served (opt-in)
     const int rc = scatter_add_agg(rows, sub, indices, n, k, d, alpha, table, counts, dtype, (cudaStream_t)stream);
     if (rc != NSG_E_UNSUPPORTED) return rc;
   }
@@ -289,6 +319,13 @@ int nsg_gather_rows(const float* table, const long long* indices, long long n, i
   NSG_REQUIRE(table && indices && out && n >= 0 && k >= 1 && d >= 1, "gather_rows: bad arguments");
   if (n == 0) return NSG_OK;
   return NSG_DISPATCH_DTYPE(dtype, [&]() -> int {
+    if (d % 4 == 0 && (reinterpret_cast<uintptr_t>(table) & 15) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0) {
+      long long blocks = (n * (d / 4) + 255) / 256;
+      if (blocks > (long long)num_sms() * 32) blocks = (long long)num_sms() * 32;
+      gather_rows_vec_kernel<T><<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(table, indices, n, k, d / 4, (T*)out);
+      NSG_CHECK_LAUNCH("gather_rows_vec_kernel");
+      return NSG_OK;
+    }
     long long blocks = (n * d + 255) / 256;
     if (blocks > (long long)num_sms() * 16) blocks = (long long)num_sms() * 16;
     gather_rows_kernel<T><<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(table, indices, n, k, d, (T*)out);

@@ -13,6 +13,8 @@
 // allocator + bulk-copy producer + MMA issuer (one elected lane).
 #include "common.cuh"
 #include "tc_common.cuh"
+#include "tma.cuh"
+#include <cstring>
 
 namespace nsg {
 
@@ -325,9 +327,344 @@ vq_search_tc_kernel(const T* __restrict__ z, const float* __restrict__ cb, const
   }
 }
 
+// ---------------------------------------------------------------------------------------------- resident-codebook search
+// K <= 512 (the reference's z_dim): the whole split codebook image (2 chunks x 64 KB) stays in shared memory for the
+// CTA's lifetime and ONE CTA per SM walks many 128-row tiles, so the 128 KB of codebook is read from L2 once per SM
+// instead of once per tile.  Two epilogue groups (4 warps each) own alternate tiles end to end -- scan the
+// 256-column accumulator of each chunk for the two best codewords, re-score them exactly in fp32, write index /
+// code / squared error -- and each owns one 256-column TMEM accumulator, so the MMA thread always has the other
+// group's tile to work on while one group is in its latency-bound tail.
+//   bf16 z (production): z tiles arrive UMMA-ready through a SWIZZLE_128B tensor map into a 4-deep ring (no thread
+//       touches them before the tensor core does); the exact re-score reads the same tile back from shared memory.
+//   fp32 z (parity mode): each group splits its own tile into hi / lo bf16 images (one 32 KB buffer per group).
+constexpr int VR_THREADS = 320;     // warps 0-3 group 0, warps 4-7 group 1, warp 8 = loader + MMA issuer, warp 9 = z producer
+constexpr int VR_STAGES = 4;        // bf16 z ring (4 x 16 KB = the two 32 KB buffers of the fp32 path)
+
+template <typename T>
+__global__ void __launch_bounds__(VR_THREADS, 1)
+vq_search_res_kernel(const __grid_constant__ CUtensorMap tmz, const T* __restrict__ z, const float* __restrict__ cb,
+                     const uint8_t* __restrict__ image, const float* __restrict__ esq_pad, long long N, int K,
+                     int nchunks, int ntiles, long long* __restrict__ indices, T* __restrict__ codes,
+                     double* __restrict__ sqerr) {
+  constexpr bool kSplitZ = sizeof(T) == 4;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* sm = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* Bres = sm;                                           // nchunks x (hi 32 KB | lo 32 KB)
+  uint8_t* Abuf = sm + (size_t)nchunks * VT_CHUNK_BYTES;        // fp32: [2 groups][hi 16 KB | lo 16 KB]; bf16: [4][16 KB]
+  float* esq_s = reinterpret_cast<float*>(Abuf + 2 * 32768);    // [nchunks * 256]
+  uint8_t* tail = reinterpret_cast<uint8_t*>(esq_s + nchunks * VT_N);
+  int* sCI = reinterpret_cast<int*>(tail);                      // [2][128][2]
+  int* sWin = reinterpret_cast<int*>(tail + 2048);              // [2][128]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(tail + 3072);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tail + 3200);
+  uint64_t* b_full = bars;                                      // [1]
+  uint64_t* a_full = bars + 1;                                  // [4]
+  uint64_t* a_empty = bars + 5;                                 // [4]
+  uint64_t* acc_full = bars + 9;                                // [2]
+  uint64_t* acc_empty = bars + 11;                              // [2]
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int ntiles_mine = ((int)blockIdx.x < ntiles) ? (ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+
+  if (tid == 0) {
+    mbar_init(b_full, 1);
+    for (int s = 0; s < VR_STAGES; ++s) {
+      mbar_init(&a_full[s], kSplitZ ? 4 : 1);
+      mbar_init(&a_empty[s], 4);
+    }
+    for (int g = 0; g < 2; ++g) {
+      mbar_init(&acc_full[g], 1);
+      mbar_init(&acc_empty[g], 4);
+    }
+    fence_mbar_init();
+    if (!kSplitZ) tma::prefetch_desc(&tmz);
+  }
+  if (warp == 8) tmem_alloc<512>(tmem_slot);
+  for (int i = tid; i < nchunks * VT_N; i += VR_THREADS) esq_s[i] = __ldg(esq_pad + i);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 9) {
+    if (!kSplitZ && lane == 0) {
+      // ---------------- z producer (bf16): one 128-row box per tile, rows past N are zero-filled by the TMA unit
+      for (int i = 0; i < ntiles_mine; ++i) {
+        const int s = i % VR_STAGES;
+        mbar_wait(&a_empty[s], (uint32_t)(((i / VR_STAGES) & 1) ^ 1));
+        mbar_arrive_expect_tx(&a_full[s], 16384);
+        const long long row0 = ((long long)blockIdx.x + (long long)i * gridDim.x) * VT_M;
+        tma::load_4d(Abuf + (size_t)s * 16384, &tmz, 0, (int)row0, 0, 0, &a_full[s]);
+      }
+    }
+  } else if (warp == 8) {
+    if (lane == 0 && ntiles_mine > 0) {
+      // ---------------- codebook loader + MMA issuer
+      mbar_arrive_expect_tx(b_full, (uint32_t)nchunks * VT_CHUNK_BYTES);
+      for (int c = 0; c < nchunks; ++c)
+        for (int h = 0; h < 2; ++h)
+          bulk_g2s(Bres + (size_t)c * VT_CHUNK_BYTES + (size_t)h * VT_IMG_HALF,
+                   image + (size_t)c * VT_CHUNK_BYTES + (size_t)h * VT_IMG_HALF, VT_IMG_HALF, b_full);
+      const uint32_t idesc = idesc_bf16(VT_M, VT_N);
+      mbar_wait(b_full, 0);
+      int used[2] = {0, 0};                 // accumulator uses so far, per group
+      for (int i0 = 0; i0 < ntiles_mine; i0 += 2) {
+        for (int c = 0; c < nchunks; ++c) {
+          for (int g = 0; g < 2; ++g) {
+            const int i = i0 + g;
+            if (i >= ntiles_mine) continue;
+            // fp32: buffer g, filled once per tile of group g; bf16: ring slot i % 4
+            const int slot = kSplitZ ? g : i % VR_STAGES;
+            const uint32_t aph = kSplitZ ? (uint32_t)((i >> 1) & 1) : (uint32_t)((i / VR_STAGES) & 1);
+            if (c == 0) mbar_wait(&a_full[slot], aph);
+            if (used[g] > 0) mbar_wait(&acc_empty[g], (uint32_t)((used[g] - 1) & 1));
+            ++used[g];
+            tc_fence_after();
+            const uint32_t d_tmem = tmem_base + (uint32_t)g * VT_N;
+            uint8_t* abase = kSplitZ ? Abuf + (size_t)slot * 32768 : Abuf + (size_t)slot * 16384;
+            const uint64_t a_hi = sw128_desc(smem_u32(abase));
+            const uint64_t a_lo = sw128_desc(smem_u32(abase + 16384));
+            const uint64_t b_hi = sw128_desc(smem_u32(Bres + (size_t)c * VT_CHUNK_BYTES));
+            const uint64_t b_lo = sw128_desc(smem_u32(Bres + (size_t)c * VT_CHUNK_BYTES + VT_IMG_HALF));
+#pragma unroll
+            for (int ks = 0; ks < VT_D / 16; ++ks) umma_bf16(d_tmem, a_hi + 2 * ks, b_hi + 2 * ks, idesc, ks > 0);
+#pragma unroll
+            for (int ks = 0; ks < VT_D / 16; ++ks) umma_bf16(d_tmem, a_hi + 2 * ks, b_lo + 2 * ks, idesc, 1);
+            if (kSplitZ) {
+#pragma unroll
+              for (int ks = 0; ks < VT_D / 16; ++ks) umma_bf16(d_tmem, a_lo + 2 * ks, b_hi + 2 * ks, idesc, 1);
+            }
+            umma_commit(&acc_full[g]);
+          }
+        }
+      }
+    }
+  } else {
+    // ---------------- epilogue group g: tiles g, g+2, ... of this CTA
+    const int g = warp >> 2, q = warp & 3;
+    const int gt = tid & 127;                         // thread within the group = TMEM lane = tile row
+    int* myCI = sCI + g * 256;
+    int* myWin = sWin + g * 128;
+    const int barid = 1 + g;
+    float err_acc = 0.f;
+    int nfull = 0;                                    // acc_full completions consumed by this group
+
+    auto stage = [&](int i) {                         // fp32 only: split this group's tile into hi / lo images
+      uint8_t* A_hi = Abuf + (size_t)g * 32768;
+      uint8_t* A_lo = A_hi + 16384;
+      const long long row0 = ((long long)blockIdx.x + (long long)i * gridDim.x) * VT_M;
+#pragma unroll
+      for (int rnd = 0; rnd < 2; ++rnd) {
+        const int row = rnd * 64 + (gt >> 1), half = gt & 1;
+        const long long grow = row0 + row;
+        float v[4][8];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          if (grow < N) {
+            load8<T>(z + grow * VT_D + (half * 4 + j) * 8, v[j]);
+          } else {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[j][e] = 0.f;
+          }
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          float hi[8], lo[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) split_bf16(v[j][e], hi[e], lo[e]);
+          const uint32_t off = sw128_offset(row, half * 4 + j);
+          *reinterpret_cast<uint4*>(A_hi + off) = make_uint4(pack_bf16(hi[0], hi[1]), pack_bf16(hi[2], hi[3]),
+                                                             pack_bf16(hi[4], hi[5]), pack_bf16(hi[6], hi[7]));
+          *reinterpret_cast<uint4*>(A_lo + off) = make_uint4(pack_bf16(lo[0], lo[1]), pack_bf16(lo[2], lo[3]),
+                                                             pack_bf16(lo[4], lo[5]), pack_bf16(lo[6], lo[7]));
+        }
+      }
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&a_full[g]);
+    };
+
+    if (kSplitZ && g < ntiles_mine) stage(g);
+    for (int i = g; i < ntiles_mine; i += 2) {
+      const long long row0 = ((long long)blockIdx.x + (long long)i * gridDim.x) * VT_M;
+      // four independent trackers (columns 4m + u): the update is a dependent compare/select chain, and with two
+      // epilogue warps per scheduler only instruction-level parallelism keeps the issue slots busy
+      Top2 tk[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) tk[u].init();
+      for (int c = 0; c < nchunks; ++c) {
+        mbar_wait_backoff(&acc_full[g], (uint32_t)(nfull & 1));
+        ++nfull;
+        tc_fence_after();
+        const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(g * VT_N);
+        uint32_t ra[32], rb[32];
+        tmem_ld32(tbase, ra);
+#pragma unroll 1
+        for (int j = 0; j < 8; j += 2) {
+          // two 32-column slices per trip: the load of the next slice is in flight while this one is scanned
+          tmem_ld_wait();
+          tmem_ld_fence(ra);
+          tmem_ld32(tbase + (uint32_t)((j + 1) * 32), rb);
+          {
+            const float4* es = reinterpret_cast<const float4*>(esq_s + c * VT_N + j * 32);
+            const int kbase = c * VT_N + j * 32;
+#pragma unroll
+            for (int e4 = 0; e4 < 8; ++e4) {
+              const float4 e = es[e4];
+              tk[0].push_ordered(fmaf(-2.f, __uint_as_float(ra[4 * e4 + 0]), e.x), kbase + 4 * e4 + 0);
+              tk[1].push_ordered(fmaf(-2.f, __uint_as_float(ra[4 * e4 + 1]), e.y), kbase + 4 * e4 + 1);
+              tk[2].push_ordered(fmaf(-2.f, __uint_as_float(ra[4 * e4 + 2]), e.z), kbase + 4 * e4 + 2);
+              tk[3].push_ordered(fmaf(-2.f, __uint_as_float(ra[4 * e4 + 3]), e.w), kbase + 4 * e4 + 3);
+            }
+          }
+          tmem_ld_wait();
+          tmem_ld_fence(rb);
+          if (j + 2 < 8) tmem_ld32(tbase + (uint32_t)((j + 2) * 32), ra);
+          {
+            const float4* es = reinterpret_cast<const float4*>(esq_s + c * VT_N + (j + 1) * 32);
+            const int kbase = c * VT_N + (j + 1) * 32;
+#pragma unroll
+            for (int e4 = 0; e4 < 8; ++e4) {
+              const float4 e = es[e4];
+              tk[0].push_ordered(fmaf(-2.f, __uint_as_float(rb[4 * e4 + 0]), e.x), kbase + 4 * e4 + 0);
+              tk[1].push_ordered(fmaf(-2.f, __uint_as_float(rb[4 * e4 + 1]), e.y), kbase + 4 * e4 + 1);
+              tk[2].push_ordered(fmaf(-2.f, __uint_as_float(rb[4 * e4 + 2]), e.z), kbase + 4 * e4 + 2);
+              tk[3].push_ordered(fmaf(-2.f, __uint_as_float(rb[4 * e4 + 3]), e.w), kbase + 4 * e4 + 3);
+            }
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&acc_empty[g]);
+      }
+      // fp32: every MMA that read this group's A buffer has retired (its last accumulator was just consumed): hand
+      // the MMA thread the next tile before the latency-bound tail of this one
+      if (kSplitZ && i + 2 < ntiles_mine) stage(i + 2);
+      Top2 t2;
+      t2.init();
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {       // lexicographic (distance, index) merge keeps the lowest index among equals
+        t2.push_any(tk[u].d1, tk[u].i1);
+        t2.push_any(tk[u].d2, tk[u].i2);
+      }
+      if (t2.i1 >= K) t2.i1 = -1;
+      if (t2.i2 >= K) t2.i2 = -1;
+      myCI[gt * 2 + 0] = t2.i1;
+      myCI[gt * 2 + 1] = t2.i2;
+      const int slot = i % VR_STAGES;
+      const uint8_t* ztile = Abuf + (size_t)slot * 16384;           // bf16 path: this tile's rows, as TMA wrote them
+      if (!kSplitZ) mbar_wait(&a_full[slot], (uint32_t)((i / VR_STAGES) & 1));   // (complete long ago: ordering only)
+      asm volatile("bar.sync %0, 128;" ::"r"(barid) : "memory");
+
+      // exact fp32 re-score of the two candidates: 8 lanes per row, 16 rows per pass, 4 passes' loads in flight
+      const int sub = gt & 7;
+#pragma unroll 1
+      for (int pb = 0; pb < 8; pb += 4) {
+        float zv[4][8], e1[4][8], e2[4][8];
+        int c1[4], c2[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int rr = (pb + u) * 16 + (gt >> 3);
+          const long long grow = row0 + rr;
+          c1[u] = myCI[rr * 2 + 0];
+          c2[u] = myCI[rr * 2 + 1];
+          const bool on = grow < N && c1[u] >= 0;
+          if (!on) c1[u] = -1;
+          if (on) {
+            if (kSplitZ) {
+              load8<T>(z + grow * VT_D + sub * 8, zv[u]);
+            } else {
+              const uint4 raw = *reinterpret_cast<const uint4*>(ztile + sw128_offset(rr, sub));
+              const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                zv[u][2 * e] = __uint_as_float(w[e] << 16);
+                zv[u][2 * e + 1] = __uint_as_float(w[e] & 0xffff0000u);
+              }
+            }
+            load8<float>(cb + (long long)c1[u] * VT_D + sub * 8, e1[u]);
+            if (c2[u] >= 0) load8<float>(cb + (long long)c2[u] * VT_D + sub * 8, e2[u]);
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int rr = (pb + u) * 16 + (gt >> 3);
+          float p1 = 0.f, p2 = 0.f;
+          if (c1[u] >= 0) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              const float df = zv[u][e] - e1[u][e];
+              p1 = fmaf(df, df, p1);
+            }
+            if (c2[u] >= 0) {
+#pragma unroll
+              for (int e = 0; e < 8; ++e) {
+                const float df = zv[u][e] - e2[u][e];
+                p2 = fmaf(df, df, p2);
+              }
+            }
+          }
+#pragma unroll
+          for (int o = 4; o > 0; o >>= 1) {
+            p1 += __shfl_xor_sync(0xffffffffu, p1, o);
+            p2 += __shfl_xor_sync(0xffffffffu, p2, o);
+          }
+          if (sub == 0) {
+            int win = c1[u] < 0 ? 0 : c1[u];
+            float dw = p1;
+            if (c1[u] >= 0 && c2[u] >= 0 && (p2 < p1 || (p2 == p1 && c2[u] < c1[u]))) {
+              win = c2[u];
+              dw = p2;
+            }
+            myWin[rr] = win;
+            const long long grow = row0 + rr;
+            if (grow < N) {
+              indices[grow] = (long long)win;
+              err_acc += dw;
+            }
+          }
+        }
+      }
+      if (!kSplitZ) {                                   // the z ring slot is free once every warp has re-scored
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&a_empty[slot]);
+      }
+      asm volatile("bar.sync %0, 128;" ::"r"(barid) : "memory");
+      if (codes) {
+#pragma unroll 4
+        for (int it = gt; it < VT_M * (VT_D / 4); it += 128) {
+          const int rr = it >> 4, c4 = it & 15;
+          const long long grow = row0 + rr;
+          if (grow < N) {
+            const float4 v = __ldg(reinterpret_cast<const float4*>(cb + (long long)myWin[rr] * VT_D + c4 * 4));
+            Act<T>::st4(codes + grow * VT_D + c4 * 4, v);
+          }
+        }
+      }
+      asm volatile("bar.sync %0, 128;" ::"r"(barid) : "memory");      // myCI / myWin are reused by the next tile
+    }
+    if (sqerr) {
+      const float e = warp_sum(err_acc);
+      if (lane == 0 && e != 0.f) atomicAdd(sqerr, (double)e);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 8) {
+    __syncwarp();
+    tmem_dealloc<512>(tmem_base);
+  }
+}
+
+static size_t vq_res_smem_bytes(int nchunks) {
+  return 1024 + (size_t)nchunks * VT_CHUNK_BYTES + 2 * 32768 + (size_t)nchunks * VT_N * 4 + 3328;
+}
+
 static size_t vq_tc_smem_bytes(int nchunks) {
   return 1024 + 32768 + 2 * (size_t)VT_CHUNK_BYTES + (size_t)nchunks * VT_N * 4 + 5376;
 }
+
+int g_vq_resident = 1;     // development switch (nsg_vq_resident): 0 = always the streaming kernel
 
 long long vq_tc_workspace_bytes(int k, int d) {
   if (d != VT_D || k < 1 || k > VT_MAX_CHUNKS * VT_N) return -1;
@@ -360,6 +697,27 @@ int vq_forward_tc(const void* z, const float* codebook, long long n, int k, int 
       configured = true;
     }
     const unsigned grid = (unsigned)((n + VT_M - 1) / VT_M);
+    if (nchunks <= 2 && g_vq_resident) {      // K <= 512: persistent CTAs with the codebook resident in shared memory
+      static bool configured_res = false;
+      if (!configured_res) {
+        cudaError_t e = cudaFuncSetAttribute(vq_search_res_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)vq_res_smem_bytes(2));
+        if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(vq_search_res_kernel)");
+        configured_res = true;
+      }
+      const unsigned pgrid = grid < (unsigned)num_sms() ? grid : (unsigned)num_sms();
+      CUtensorMap tmz;
+      memset(&tmz, 0, sizeof(tmz));
+      if (sizeof(T) == 2) {       // z (n, 64) bf16 as a 64-channel "image" one pixel high: 128-row SWIZZLE_128B boxes
+        NSG_REQUIRE((reinterpret_cast<uintptr_t>(z) & 15) == 0, "vq_forward(mode=1): z must be 16-byte aligned");
+        if (int rc = tma::encode_nhwc64(&tmz, z, n, 1, 1, VT_D, (long long)n * VT_D, (long long)n * VT_D, VT_M, 1))
+          return rc;
+      }
+      vq_search_res_kernel<T><<<pgrid, VR_THREADS, vq_res_smem_bytes(nchunks), stream>>>(
+          tmz, (const T*)z, codebook, image, esq_pad, n, k, nchunks, (int)grid, indices, (T*)codes, sqerr);
+      NSG_CHECK_LAUNCH("vq_search_res_kernel");
+      return NSG_OK;
+    }
     vq_search_tc_kernel<T><<<grid, 288, smem, stream>>>((const T*)z, codebook, image, esq_pad, n, k, nchunks,
                                                         indices, (T*)codes, sqerr);
     NSG_CHECK_LAUNCH("vq_search_tc_kernel");

@@ -97,6 +97,7 @@ class DataParallel(object):
         self.overlap = bool(overlap)
         self.comm = None            # communication stream (CUDA only)
         self.collectives = 0        # issued per step (bench.py reports it)
+        self.loss_slots = None      # view of the flat gradient buffer's tail padding that carried the loss scalars
 
     # -- BatchNorm statistics -------------------------------------------------------------------------------
     def reduce_stats(self, stats):
@@ -111,11 +112,18 @@ class DataParallel(object):
             s = flat['buckets'] = bucket_slices(flat['names'], flat['offs'], flat['total'])
         return s
 
-    def decoder_done(self, eng, ctx, G, flat):
+    def decoder_done(self, eng, ctx, G, flat, losses=None):
         """Called when the decoder's data-gradient chain has been issued on the current stream.  The decoder's
-        weight-gradient images are folded and its bucket is all-reduced on the communication stream."""
+        weight-gradient images are folded and its bucket is all-reduced on the communication stream.  ``losses``
+        (3 device scalars, already final after the forward pass) are copied into the unused padding at the end of
+        the bucket so that they are summed across ranks by the same collective."""
         if not self.overlap:
             return
+        if losses is not None:
+            last = flat['offs'][-1] + flat['last_numel']
+            if flat['total'] - last >= losses.numel():
+                self.loss_slots = flat['grads'][flat['total'] - losses.numel():]
+                self.loss_slots.copy_(losses)
         main = torch.cuda.current_stream()
         if self.comm is None:
             self.comm = torch.cuda.Stream()
@@ -163,12 +171,19 @@ class DataParallelStep(GraphedTrainStep):
         super(DataParallelStep, self).__init__(model, optimizer, batch_shape, beta)
 
     def _body(self, grad_hook):
-        self.dp.collectives = 0
+        dp = self.dp
+        dp.collectives = 0
+        dp.loss_slots = None
         self.optimizer.zero_grad()
         losses, outs = self.model.loss_and_grads(self.c, beta=self.beta)
         self.optimizer.step()
-        if self.dp.world > 1:
-            allreduce_sum_(losses, self.dp.group)
-            losses.mul_(1.0 / self.dp.world)
-            self.dp.collectives += 1
+        if dp.world > 1:
+            if dp.loss_slots is not None:
+                # the loss scalars rode in the padding at the end of the decoder gradient bucket (see decoder_done)
+                losses = dp.loss_slots.double() * (1.0 / dp.world)
+            else:
+                allreduce_sum_(losses, dp.group)
+                losses.mul_(1.0 / dp.world)
+                dp.collectives += 1
+        self.collectives_per_step = dp.collectives
         return losses, outs

@@ -236,7 +236,7 @@ class VQVAE(nn.Module):
         for p, o in zip(params, offs):
             flat[o:o + p.numel()].copy_(p.data.reshape(-1))
             p.data = flat[o:o + p.numel()].view(p.shape)
-        self._flat = dict(params=flat, grads=gflat, offs=offs, total=total, names=names)
+        self._flat = dict(params=flat, grads=gflat, offs=offs, total=total, names=names, last_numel=params[-1].numel())
         self.bind_grads()
         return self._flat
 
@@ -318,7 +318,10 @@ class VQVAE(nn.Module):
         g_st = eng.decoder_bwd(ectx, P, G, dpre.view(b, h, wt, 1))
         dp = getattr(eng, 'dp', None)
         if dp is not None:
-            dp.decoder_done(eng, ectx, G, self._flat)      # decoder bucket: unpack + all-reduce beside the encoder backward
+            # decoder bucket: unpack + all-reduce beside the encoder backward; the loss scalars ride in its padding
+            l_now = torch.stack([sums[0] * (1.0 / (b * h * w)), sums[1] * (1.0 / z_e.numel()),
+                                 sums[1] * (1.0 / z_e.numel())])
+            dp.decoder_done(eng, ectx, G, self._flat, losses=l_now)
         n_lat = z_e.numel()
         dz = eng.bottleneck_bwd(ectx, g_st, z_e, z_q, 2.0 * beta / n_lat)  # ST clone + beta * d commit / d z_e
         ops.scatter_add(z_q, idx, G['codebook.embedding.weight'], alpha=2.0 / n_lat, sub=z_e)  # d loss_vq / d e

