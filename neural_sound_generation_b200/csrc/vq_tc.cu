@@ -407,35 +407,44 @@ vq_search_res_kernel(const __grid_constant__ CUtensorMap tmz, const T* __restric
                    image + (size_t)c * VT_CHUNK_BYTES + (size_t)h * VT_IMG_HALF, VT_IMG_HALF, b_full);
       const uint32_t idesc = idesc_bf16(VT_M, VT_N);
       mbar_wait(b_full, 0);
+      // the two groups advance independently: whichever group's next (tile, chunk) has its operands in place and
+      // its accumulator drained is served first, so one group's latency-bound tail never stalls the other's scan
       int used[2] = {0, 0};                 // accumulator uses so far, per group
-      for (int i0 = 0; i0 < ntiles_mine; i0 += 2) {
-        for (int c = 0; c < nchunks; ++c) {
-          for (int g = 0; g < 2; ++g) {
-            const int i = i0 + g;
-            if (i >= ntiles_mine) continue;
-            // fp32: buffer g, filled once per tile of group g; bf16: ring slot i % 4
-            const int slot = kSplitZ ? g : i % VR_STAGES;
-            const uint32_t aph = kSplitZ ? (uint32_t)((i >> 1) & 1) : (uint32_t)((i / VR_STAGES) & 1);
-            if (c == 0) mbar_wait(&a_full[slot], aph);
-            if (used[g] > 0) mbar_wait(&acc_empty[g], (uint32_t)((used[g] - 1) & 1));
-            ++used[g];
-            tc_fence_after();
-            const uint32_t d_tmem = tmem_base + (uint32_t)g * VT_N;
-            uint8_t* abase = kSplitZ ? Abuf + (size_t)slot * 32768 : Abuf + (size_t)slot * 16384;
-            const uint64_t a_hi = sw128_desc(smem_u32(abase));
-            const uint64_t a_lo = sw128_desc(smem_u32(abase + 16384));
-            const uint64_t b_hi = sw128_desc(smem_u32(Bres + (size_t)c * VT_CHUNK_BYTES));
-            const uint64_t b_lo = sw128_desc(smem_u32(Bres + (size_t)c * VT_CHUNK_BYTES + VT_IMG_HALF));
+      int tile_g[2] = {0, 1}, chunk_g[2] = {0, 0};
+      int remaining = ntiles_mine * nchunks;
+      while (remaining > 0) {
 #pragma unroll
-            for (int ks = 0; ks < VT_D / 16; ++ks) umma_bf16(d_tmem, a_hi + 2 * ks, b_hi + 2 * ks, idesc, ks > 0);
-#pragma unroll
-            for (int ks = 0; ks < VT_D / 16; ++ks) umma_bf16(d_tmem, a_hi + 2 * ks, b_lo + 2 * ks, idesc, 1);
-            if (kSplitZ) {
-#pragma unroll
-              for (int ks = 0; ks < VT_D / 16; ++ks) umma_bf16(d_tmem, a_lo + 2 * ks, b_hi + 2 * ks, idesc, 1);
-            }
-            umma_commit(&acc_full[g]);
+        for (int g = 0; g < 2; ++g) {
+          const int i = tile_g[g];
+          if (i >= ntiles_mine) continue;
+          const int c = chunk_g[g];
+          // fp32: buffer g, filled once per tile of group g; bf16: ring slot i % 4
+          const int slot = kSplitZ ? g : i % VR_STAGES;
+          const uint32_t aph = kSplitZ ? (uint32_t)((i >> 1) & 1) : (uint32_t)((i / VR_STAGES) & 1);
+          if (c == 0 && !mbar_try_wait(&a_full[slot], aph)) continue;
+          if (used[g] > 0 && !mbar_try_wait(&acc_empty[g], (uint32_t)((used[g] - 1) & 1))) continue;
+          ++used[g];
+          --remaining;
+          if (++chunk_g[g] == nchunks) {
+            chunk_g[g] = 0;
+            tile_g[g] += 2;
           }
+          tc_fence_after();
+          const uint32_t d_tmem = tmem_base + (uint32_t)g * VT_N;
+          uint8_t* abase = kSplitZ ? Abuf + (size_t)slot * 32768 : Abuf + (size_t)slot * 16384;
+          const uint64_t a_hi = sw128_desc(smem_u32(abase));
+          const uint64_t a_lo = sw128_desc(smem_u32(abase + 16384));
+          const uint64_t b_hi = sw128_desc(smem_u32(Bres + (size_t)c * VT_CHUNK_BYTES));
+          const uint64_t b_lo = sw128_desc(smem_u32(Bres + (size_t)c * VT_CHUNK_BYTES + VT_IMG_HALF));
+#pragma unroll
+          for (int ks = 0; ks < VT_D / 16; ++ks) umma_bf16(d_tmem, a_hi + 2 * ks, b_hi + 2 * ks, idesc, ks > 0);
+#pragma unroll
+          for (int ks = 0; ks < VT_D / 16; ++ks) umma_bf16(d_tmem, a_hi + 2 * ks, b_lo + 2 * ks, idesc, 1);
+          if (kSplitZ) {
+#pragma unroll
+            for (int ks = 0; ks < VT_D / 16; ++ks) umma_bf16(d_tmem, a_lo + 2 * ks, b_hi + 2 * ks, idesc, 1);
+          }
+          umma_commit(&acc_full[g]);
         }
       }
     }

@@ -137,3 +137,26 @@ def test_tma_eval_encode_decode_and_graph():
         assert np.allclose(la, lb.tolist(), rtol=1e-3 if it == 0 else 5e-2), (it, la, lb.tolist())
     wa, wb = ma.state_dict()['encoder.3.weight'], mb.state_dict()['encoder.3.weight']
     assert relerr(wa, wb) < 5e-2
+
+
+def test_graphed_inference_config5_shape():
+    """BASELINE.json configs[4]: encode -> quantise -> decode of one ~10 s utterance (1 x 80 x 861), eval mode, as one
+    CUDA graph (models.py:188-196): replay == eager path, and both agree with the oracle up to bf16 index flips."""
+    p, b, _ = _state(seed=9, batch=1, frames=8)
+    m = _model(p, b, 2, train=False)
+    xs = [R.make_mel(1, 80, 861, 70 + i) for i in range(2)]
+    infer = nsg.GraphedInference(m, (1, 1, 80, 861))
+    for x in xs:
+        lat_g, xt_g = infer(x.to(DEV))
+        lat_g, xt_g = lat_g.clone(), xt_g.clone()
+        with torch.no_grad():
+            lat_e = m.encode(x.to(DEV).unsqueeze(1))
+            xt_e = m.decode(lat_e)
+        assert tuple(lat_g.shape) == (1, 20, 215) and lat_g.dtype == torch.int64
+        assert tuple(xt_g.shape) == (1, 1, 80, 860)
+        assert torch.equal(lat_g, lat_e) and torch.equal(xt_g, xt_e)
+        ref_lat = R.encode(p, b, x.unsqueeze(1))
+        assert (lat_g.cpu() != ref_lat).float().mean().item() < 0.05
+        xt_ref = R.decode(p, b, lat_g.cpu())
+        assert relerr(xt_g, xt_ref) < 3e-2
+    assert not torch.equal(xt_g, infer(xs[0].to(DEV))[1])
