@@ -37,29 +37,62 @@ def ncu_traffic(kernel_key):
         return None
 
 
-def stock_torch_gpu_run(dev, steps=5, warmup=2, batch=B_PER_GPU):
-    """'Stock PyTorch on the same B200' bar: the oracle restatement of the reference step --
-    the same ATen/cuDNN calls the reference modules make -- run eagerly on the GPU in fp32 (torch default TF32 settings).  Baseline
-    only: never on the product path."""
-    from oracle import vqvae_ref as R
-    p, b = R.make_state(1, DIM, K_CODES, 1, codebook='spread')
-    p = {k: v.to(dev) for k, v in p.items()}
-    b = {k: v.to(dev) for k, v in b.items()}
-    mel = R.make_mel(batch, N_MELS, FRAMES, 100).to(dev)
-    state = R.adam_init(p)
+def stock_torch_gpu_run(dev, steps=10, warmup=3, batch=B_PER_GPU):
+    """'Stock PyTorch on the same B200' bar.  /root/reference does not exist on the GPU box, so
+    the reference model is restated here with the same torch.nn layers and the same loop body (models.py:145-216,
+    vector_quantization.py:6-44, train.py:116-136) and run eagerly in fp32 with torch's default cuDNN / TF32
+    settings.  Baseline only: nothing of ours is on this path, and it is never the product."""
+    import torch.nn as nn
+    import torch.nn.functional as F
+
+    class Res(nn.Module):
+        def __init__(self, d):
+            super().__init__()
+            self.block = nn.Sequential(nn.ReLU(True), nn.Conv2d(d, d, 3, 1, 1), nn.BatchNorm2d(d), nn.ReLU(True),
+                                       nn.Conv2d(d, d, 1), nn.BatchNorm2d(d))
+
+        def forward(self, x):
+            return x + self.block(x)
+
+    d = DIM
+    enc = nn.Sequential(nn.Conv2d(1, d, 4, 2, 1), nn.BatchNorm2d(d), nn.ReLU(True), nn.Conv2d(d, d, 4, 2, 1), Res(d), Res(d))
+    dec = nn.Sequential(Res(d), Res(d), nn.ReLU(True), nn.ConvTranspose2d(d, d, 4, 2, 1), nn.BatchNorm2d(d), nn.ReLU(True),
+                        nn.ConvTranspose2d(d, 1, 4, 2, 1), nn.Tanh())
+    emb = nn.Embedding(K_CODES, d)
+    mods = nn.ModuleList([enc, dec, emb]).to(dev).train()
+    opt = torch.optim.Adam(mods.parameters(), lr=1e-3)
+    c = torch.rand(batch, 1, N_MELS, FRAMES, device=dev)
+
+    def step():
+        opt.zero_grad()
+        z_e = enc(c)
+        zf = z_e.permute(0, 2, 3, 1).contiguous()
+        flat = zf.view(-1, d)
+        with torch.no_grad():
+            cb = emb.weight
+            dist_ = torch.addmm(torch.sum(cb ** 2, dim=1) + torch.sum(flat ** 2, dim=1, keepdim=True), flat, cb.t(),
+                                alpha=-2.0, beta=1.0)
+            idx = torch.min(dist_, dim=1)[1]
+        z_q_st = zf + (torch.index_select(emb.weight.detach(), 0, idx).view_as(zf) - zf).detach()
+        z_q_bar = torch.index_select(emb.weight, 0, idx).view_as(zf).permute(0, 3, 1, 2).contiguous()
+        x_t = dec(z_q_st.permute(0, 3, 1, 2).contiguous())
+        loss = F.mse_loss(x_t, c) + F.mse_loss(z_q_bar, z_e.detach()) + F.mse_loss(z_e, z_q_bar.detach())
+        loss.backward()
+        opt.step()
+        return loss
+
     ts = []
     for i in range(warmup + steps):
         torch.cuda.synchronize()
         t0 = time.perf_counter()
-        r = R.step_grads(p, b, mel, 1.0)
-        p = R.adam_step(p, r['grads'], state, 1e-3)
-        b = r['buffers']
+        step().item()
         torch.cuda.synchronize()
         if i >= warmup:
             ts.append(time.perf_counter() - t0)
     ms = 1e3 * sorted(ts)[len(ts) // 2]
     return dict(value=batch * FRAMES / (ms / 1e3), unit='mel-frames/s', ms_per_step=ms,
-                what='oracle restatement of the reference step in eager PyTorch fp32 on this GPU (cuDNN/cuBLAS), batch %d' % batch)
+                what='torch.nn restatement of the reference step, eager PyTorch fp32 (cuDNN / cuBLAS, default TF32 '
+                     'settings) on this GPU, batch %d x %d x %d' % (batch, N_MELS, FRAMES))
 
 
 def peaks():

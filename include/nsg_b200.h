@@ -229,9 +229,9 @@ int nsg_scatter_add(const void* rows, const void* sub, const long long* indices,
 /* development aid: 1 (default) = K <= 512 uses the persistent kernel with the codebook resident in shared memory,
  * 0 = always the per-tile streaming kernel.  Returns the previous setting; other values only query. */
 int nsg_vq_resident(int enable);
-/* development aid: 1 (default) = the per-element vector-atomic kernel (the faster one on B200 at every size measured),
- * 0 = block-aggregated scatter kernel where the shape is served (n >= 4096, d % 4 == 0, d <= 256; fewer global atomics,
- * meant for heavily skewed assignments).  Returns the previous setting; other values only query. */
+/* development aid: 0 (default) = block-aggregated scatter kernel where the shape is served (n >= 4096, d % 4 == 0,
+ * d <= 256): time independent of how skewed the assignment is; 1 = always the per-element vector-atomic kernel (faster
+ * for uniform assignments, up to 12x slower for skewed ones).  Returns the previous setting; other values only query. */
 int nsg_scatter_mode(int mode);
 /* EMA codebook update (extension -- NOT in the reference; van den Oord et al. 2017, appendix A.1):
  *   ema_count <- decay*ema_count + (1-decay)*counts;   ema_sum <- decay*ema_sum + (1-decay)*sums;

@@ -108,6 +108,8 @@ def load():
         fn = getattr(lib, name)
         if name not in ('nsg_version', 'nsg_last_error'):
             fn.restype = ll if name in ('nsg_vq_workspace_bytes', 'nsg_conv_pack_bytes') else i
+    if os.environ.get('NSG_SCATTER_MODE') in ('0', '1'):      # development aid, see include/nsg_b200.h
+        lib.nsg_scatter_mode(int(os.environ['NSG_SCATTER_MODE']))
     _lib = lib
     return lib
 

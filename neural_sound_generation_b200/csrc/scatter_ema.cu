@@ -150,6 +150,21 @@ static bool plan_scatter(long long n, int k, int d, int row_bytes, ScatterPlan* 
   if (d % 4 != 0 || d > 4 * 32 * SA_MAXQ) return false;
   int lpr = 1;
   while (lpr < 32 && lpr * 2 <= d / 4) lpr *= 2;
+  // whole table in one CTA's shared memory (K = 512, D = 64: 128 KB): no codeword groups at all -- every CTA owns a
+  // slice of the rows, each index is read once, the work is balanced whatever the assignment looks like, and only
+  // the touched table rows leave through global atomics (a handful under the heavy skew of an untrained encoder)
+  const size_t whole = (size_t)k * d * 4 + (size_t)k * 4 + 2 * SA_CHUNK * 4;
+  if (whole <= 200 * 1024) {
+    long long P1 = (n + 63) / 64;
+    if (P1 > num_sms()) P1 = num_sms();
+    pl->P = (int)P1;
+    pl->G = 1;
+    pl->slots = k;
+    pl->lpr = lpr;
+    pl->rows_per_part = (n + P1 - 1) / P1;
+    pl->smem = whole;
+    return true;
+  }
   const int gmin = (int)(((long long)k * d * 4 + SA_TABLE_BYTES - 1) / SA_TABLE_BYTES);
   const int target = 2 * num_sms();
   long long P = (n + 4095) / 4096;

@@ -247,10 +247,11 @@ namespace nsg {
 int scatter_add_agg(const void* rows, const void* sub, const long long* indices, long long n, int k, int d, float alpha,
                     float* table, float* counts, int dtype, cudaStream_t stream);
 }
-// measured on B200 (profiles/r1_vq_kernels.txt): the per-element vector-atomic kernel beats the block-aggregated one at
-// every size tried (12 vs 24 us at N = 40960, 302 vs 336 us at N = 2^20; the shared-memory float atomics of the
-// aggregation are compare-and-swap loops), so it is the default; mode 0 remains for skewed assignments
-static int g_scatter_mode = 1;
+// measured on B200 (profiles/r1_final_vq_kernels.txt, N = 40960 / 2^20, K = 512, D = 64, bf16): the per-element
+// vector-atomic kernel is the faster one when the assignment is uniform (12 vs 21 us; 246 vs 493 us) but collapses when
+// a few codewords take most rows, which is exactly what an untrained encoder produces (146 us; 3461 us), while the
+// block-aggregated kernel stays at 19 us / 444 us.  The bounded one is the default; mode 1 selects the other.
+static int g_scatter_mode = 0;
 namespace nsg {
 extern int g_vq_resident;
 }
@@ -290,7 +291,7 @@ int nsg_scatter_add(const void* rows, const void* sub, const long long* indices,
                     float alpha, float* table, float* counts, int dtype, void* stream) {
   NSG_REQUIRE(rows && indices && table && n >= 0 && k >= 1 && d >= 1, "scatter_add: bad arguments");
   if (n == 0) return NSG_OK;
-  if (g_scatter_mode == 0) {      // block-aggregated kernel (scatter_ema.cu) when the shape is served (opt-in)
+  if (g_scatter_mode == 0) {      // block-aggregated kernel (scatter_ema.cu) when the shape is served
     const int rc = scatter_add_agg(rows, sub, indices, n, k, d, alpha, table, counts, dtype, (cudaStream_t)stream);
     if (rc != NSG_E_UNSUPPORTED) return rc;
   }

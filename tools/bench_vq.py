@@ -59,14 +59,17 @@ def main():
                 table = torch.zeros(k, d, device=DEV)
                 counts = torch.zeros(k, device=DEV)
                 ops.vq_forward(z, cb, idx, codes, sq, mode=0 if n * k <= (1 << 30) else 1)
-                for sm, nm in ((0, 'aggregated'), (1, 'per-element')):
-                    prev = lib.nsg_scatter_mode(sm)
-                    for fl, tag in ((flush, 'cold'), (None, 'warm')):
-                        t = timed(lambda: ops.scatter_add(codes, idx, table, alpha=0.5, sub=z, counts=counts), flush=fl, iters=10)
-                        nbytes = 2 * n * d * es + n * 8 + 2 * (k * d + k) * 4
-                        print('scatter_add N=%-8d K=%-5d D=%-3d %-5s %-11s %s %9.1f us  %7.1f GB/s  %5.1f%% of %s HBM'
-                              % (n, k, d, str(dt).split('.')[-1], nm, tag, t, nbytes / t / 1e3, 100 * nbytes / t / 1e3 / hbm, hbm))
-                    lib.nsg_scatter_mode(prev)
+                skew = (torch.rand(n, device=DEV) ** 8 * min(k, 6)).long()       # an untrained encoder: a few codewords win
+                for ix, dist_name in ((idx, 'uniform'), (skew, 'skewed')):
+                    for sm, nm in ((0, 'aggregated'), (1, 'per-element')):
+                        prev = lib.nsg_scatter_mode(sm)
+                        for fl, tag in ((flush, 'cold'), (None, 'warm')):
+                            t = timed(lambda: ops.scatter_add(codes, ix, table, alpha=0.5, sub=z, counts=counts), flush=fl, iters=10)
+                            nbytes = 2 * n * d * es + n * 8 + 2 * (k * d + k) * 4
+                            print('scatter_add N=%-8d K=%-5d D=%-3d %-5s %-11s %-7s %s %9.1f us  %7.1f GB/s  %5.1f%% of %s HBM'
+                                  % (n, k, d, str(dt).split('.')[-1], nm, dist_name, tag, t, nbytes / t / 1e3,
+                                     100 * nbytes / t / 1e3 / hbm, hbm))
+                        lib.nsg_scatter_mode(prev)
                 for fl, tag in ((flush, 'cold'), (None, 'warm')):
                     t = timed(lambda: ops.gather_rows(cb, idx, codes), flush=fl, iters=10)
                     nbytes = n * d * es + n * 8 + k * d * 4
