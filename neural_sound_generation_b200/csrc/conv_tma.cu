@@ -16,6 +16,7 @@
 //       per tap) and of Q are MN-major SWIZZLE_128B operands as they land; two taps share one M = 128 instruction;
 //       an all-ones slot yields the bias gradient; partial sums leave through 16-byte vector atomics into a packed
 //       [tap][a][b] fp32 image that wgrad_unpack folds into the reference's parameter layout.
+#include <cstdlib>
 #include "common.cuh"
 #include "conv_geom.cuh"
 #include "tc_common.cuh"
@@ -971,7 +972,16 @@ int conv_wgrad_tma(const nsg_conv_geom* cg, const void* p, const void* q, float*
       P.dw[kh * k + kw] = (signed char)(kw - cg->pad);
     }
   P.ones = q_colsum ? 1 : 0;
-  P.taps_per_group = P.ntaps + P.ones <= 10 ? P.ntaps : 8;
+  // Split-K over pixels makes every CTA add its whole [taps][64][64] partial into the packed image with vector
+  // atomics, and those, not the loads, bound the kernel: 148 CTAs x 9 taps = 1.4 M 16-byte atomics per 3x3 launch.
+  // Giving each blockIdx.y group 3 (of 9) or 4 (of 16) taps cuts the atomics 3-4x for ~20 % more operand bytes (Q is
+  // re-read once per group).  Measured warm on B200, 3x3: 24.4 us (all 9) / 17.1 (5) / 15.5 (3) / 19.0 (2) / 21.6 (1);
+  // 4x4: 24.3 (8) / 23.1 (6) / 21.2 (4) / 22.8 (3) / 26.8 (2).
+  P.taps_per_group = P.ntaps <= 4 ? P.ntaps : (P.ntaps == 9 ? 3 : 4);
+  {
+    static const int tpg_override = getenv("NSG_WGRAD_TPG") ? atoi(getenv("NSG_WGRAD_TPG")) : 0;   // tuning aid
+    if (tpg_override > 0 && tpg_override < P.taps_per_group) P.taps_per_group = tpg_override;
+  }
   const int groups = (P.ntaps + P.taps_per_group - 1) / P.taps_per_group;
   P.nslots = (P.taps_per_group + P.ones + 1) / 2 * 2;
   const uint32_t stage_bytes = (uint32_t)(P.nslots + 1) * WG_SLOT;
