@@ -132,8 +132,14 @@ int nsg_conv_wgrad_tc(const nsg_conv_geom* g, const void* p, const nsg_prologue*
  *                          to 24 (layer, orientation) pairs in one launch; strides as in nsg_conv_geom
  *   nsg_conv_gemm_tma      same contract as nsg_conv_gemm_tc with passes = 1 and no prologue
  *   nsg_conv_wgrad_tma     dw_packed[t][a][b] (fp32, k*k*64*64, 16-byte aligned) += sum_m P[gather0(m,t),a]*Q[m,b];
- *                          q_colsum (nullable) as in nsg_conv_wgrad
- *   nsg_wgrad_unpack_many  dw[t + a*w_cin_stride + b*w_cout_stride] += dw_packed[t][a][b] for up to 24 layers */
+ *                          q_colsum (nullable) as in nsg_conv_wgrad.  The split-K partials of all CTAs meet in the
+ *                          one image through vector atomics.
+ *   nsg_conv_wgrad_tma_sliced  the same sum left as S = nsg_conv_wgrad_slices(g) partial images
+ *                          dw_slices[s][t][a][b] (each OVERWRITTEN, plain stores, no atomics; q_colsum still +=):
+ *                          the form the training step uses -- faster, and the gradient no longer depends on CTA order
+ *   nsg_conv_wgrad_slices  S for that geometry on the current device (0: geometry not served)
+ *   nsg_wgrad_unpack_many  dw[t + a*w_cin_stride + b*w_cout_stride] += sum_{s < nslices[i]} dw_packed[s][t][a][b] for
+ *                          up to 24 layers; nslices null = one image each */
 /* The single-channel ends of the network (models.py:165 Conv2d(1 -> 64, 4, 2, 1), models.py:182
  * ConvTranspose2d(64 -> 1, 4, 2, 1)) on the tensor cores, bf16 tensors, geometry k4 / s2 / p1 only (else
  * NSG_E_UNSUPPORTED; the CUDA-core nsg_conv_gemm / nsg_conv_wgrad serve every other shape).  packed_w are 8 KB images
@@ -158,7 +164,10 @@ int nsg_conv_gemm_tma(const nsg_conv_geom* g, const void* in, const void* packed
                       void* stream);
 int nsg_conv_wgrad_tma(const nsg_conv_geom* g, const void* p, const void* q, float* dw_packed, float* q_colsum,
                        void* stream);
-int nsg_wgrad_unpack_many(int n, const float* const* dw_packed, float* const* dw, const int* ntaps,
+int nsg_conv_wgrad_slices(const nsg_conv_geom* g);
+int nsg_conv_wgrad_tma_sliced(const nsg_conv_geom* g, const void* p, const void* q, float* dw_slices, float* q_colsum,
+                              void* stream);
+int nsg_wgrad_unpack_many(int n, const float* const* dw_packed, float* const* dw, const int* ntaps, const int* nslices,
                           const long long* w_cin_stride, const long long* w_cout_stride, void* stream);
 
 /* Streaming companions for bf16 tensors with 64 channels (fused_elem.cu), `pixels` = N*H*W:

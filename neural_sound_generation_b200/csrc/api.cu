@@ -53,10 +53,11 @@ int convT_c1_tc(const nsg_conv_geom* cg, const void* in, const void* packed, con
 int wgrad_c1_tc(const nsg_conv_geom* cg, const void* p, const void* q, float* dw, float* q_colsum, cudaStream_t stream);
 int conv_pack_many(int n, const float* const* w, void* const* dst, const int* ntaps, const long long* in_stride,
                    const long long* out_stride, cudaStream_t stream);
-int conv_wgrad_tma(const nsg_conv_geom* cg, const void* p, const void* q, float* dwp, float* q_colsum,
+int conv_wgrad_tma(const nsg_conv_geom* cg, const void* p, const void* q, float* dwp, float* q_colsum, int sliced,
                    cudaStream_t stream);
-int wgrad_unpack_many(int n, const float* const* src, float* const* dw, const int* ntaps, const long long* a_stride,
-                      const long long* b_stride, cudaStream_t stream);
+int conv_wgrad_slices(const nsg_conv_geom* cg);
+int wgrad_unpack_many(int n, const float* const* src, float* const* dw, const int* ntaps, const int* nslices,
+                      const long long* a_stride, const long long* b_stride, cudaStream_t stream);
 
 }  // namespace nsg
 
@@ -187,13 +188,26 @@ int nsg_conv_wgrad_tma(const nsg_conv_geom* g, const void* p, const void* q, flo
   int rc = check_geom(g);
   if (rc) return rc;
   NSG_REQUIRE(p && q && dw_packed, "conv_wgrad_tma: null pointer");
-  return conv_wgrad_tma(g, p, q, dw_packed, q_colsum, (cudaStream_t)stream);
+  return conv_wgrad_tma(g, p, q, dw_packed, q_colsum, 0, (cudaStream_t)stream);
 }
 
-int nsg_wgrad_unpack_many(int n, const float* const* dw_packed, float* const* dw, const int* ntaps,
+int nsg_conv_wgrad_slices(const nsg_conv_geom* g) {
+  if (check_geom(g)) return 0;
+  return conv_wgrad_slices(g);
+}
+
+int nsg_conv_wgrad_tma_sliced(const nsg_conv_geom* g, const void* p, const void* q, float* dw_slices, float* q_colsum,
+                              void* stream) {
+  int rc = check_geom(g);
+  if (rc) return rc;
+  NSG_REQUIRE(p && q && dw_slices, "conv_wgrad_tma_sliced: null pointer");
+  return conv_wgrad_tma(g, p, q, dw_slices, q_colsum, 1, (cudaStream_t)stream);
+}
+
+int nsg_wgrad_unpack_many(int n, const float* const* dw_packed, float* const* dw, const int* ntaps, const int* nslices,
                           const long long* w_cin_stride, const long long* w_cout_stride, void* stream) {
   NSG_REQUIRE(n == 0 || (dw_packed && dw && ntaps && w_cin_stride && w_cout_stride), "wgrad_unpack_many: null pointer");
-  return wgrad_unpack_many(n, dw_packed, dw, ntaps, w_cin_stride, w_cout_stride, (cudaStream_t)stream);
+  return wgrad_unpack_many(n, dw_packed, dw, ntaps, nslices, w_cin_stride, w_cout_stride, (cudaStream_t)stream);
 }
 
 }  // extern "C"

@@ -754,6 +754,8 @@ struct TmaWgradParams {
   int nslots;                    // even number of P slots per stage (taps of the group [+ ones slot] [+ zero slot])
   int ones;                      // 1: group 0 carries an all-ones slot right after its taps (column sums of Q)
   int stages;
+  int slice_elems;               // 0: add into ONE packed image with vector atomics; else CTA x stores its partial
+                                 // image into slice x of [gridDim.x][ntaps][64][64] (no atomics, summed by the unpack)
   signed char dh[TM_MAX_TAPS], dw[TM_MAX_TAPS];
 };
 
@@ -882,7 +884,17 @@ wgrad_tma_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
         tmem_ld32(taddr, acc0);
         tmem_ld32(taddr + 32, acc1);
         tmem_ld_wait();
-        if (sl < ntaps) {
+        if (sl < ntaps && P.slice_elems) {
+          float4* dst = reinterpret_cast<float4*>(dwp + (size_t)blockIdx.x * P.slice_elems +
+                                                  ((size_t)(tap_base + sl) * TM_C + a) * TM_C);
+#pragma unroll
+          for (int v = 0; v < 8; ++v) {
+            dst[v] = make_float4(__uint_as_float(acc0[4 * v]), __uint_as_float(acc0[4 * v + 1]),
+                                 __uint_as_float(acc0[4 * v + 2]), __uint_as_float(acc0[4 * v + 3]));
+            dst[8 + v] = make_float4(__uint_as_float(acc1[4 * v]), __uint_as_float(acc1[4 * v + 1]),
+                                     __uint_as_float(acc1[4 * v + 2]), __uint_as_float(acc1[4 * v + 3]));
+          }
+        } else if (sl < ntaps) {
           float* dst = dwp + ((size_t)(tap_base + sl) * TM_C + a) * TM_C;
 #pragma unroll
           for (int v = 0; v < 8; ++v) {
@@ -909,11 +921,11 @@ wgrad_tma_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
   if (warp == 1) tmem_dealloc<TMEM_COLS>(tmem_base);
 }
 
-// dw[t + a*a_stride + b*b_stride] += packed[t][a][b]  for every listed layer, one launch
+// dw[t + a*a_stride + b*b_stride] += sum_s packed[s][t][a][b]  for every listed layer, one launch
 struct UnpackItem {
   const float* src;
   float* dw;
-  int ntaps;
+  int ntaps, nslices;
   long long a_stride, b_stride;
 };
 struct UnpackList {
@@ -925,11 +937,37 @@ __global__ void __launch_bounds__(256) wgrad_unpack_kernel(const __grid_constant
   int li = 0;
   while (li + 1 < L.n && (int)blockIdx.x >= L.first_block[li + 1]) ++li;
   const UnpackItem& u = L.it[li];
-  const int gid = ((int)blockIdx.x - L.first_block[li]) * 256 + threadIdx.x;     // (t, a, b), b fastest
-  const int b = gid & 63, a = (gid >> 6) & 63, t = gid >> 12;
-  if (t >= u.ntaps) return;
-  float* d = u.dw + t + (long long)a * u.a_stride + (long long)b * u.b_stride;
-  *d += u.src[gid];
+  // block = 256 consecutive elements of one tap image = 64 float4 columns; thread = (column, slice residue mod 4).
+  // Slices are summed in a fixed order (residue classes, then the four classes): no dependence on CTA timing.
+  __shared__ float4 part[4][64];
+  const int col = threadIdx.x & 63, sg = threadIdx.x >> 6;
+  const int e0 = ((int)blockIdx.x - L.first_block[li]) * 256 + col * 4;           // (t, a, b), b fastest
+  const size_t pitch = (size_t)u.ntaps * TM_C * TM_C;
+  const float4* src = reinterpret_cast<const float4*>(u.src + e0);
+  const size_t pitch4 = pitch / 4;
+  float4 s0 = make_float4(0.f, 0.f, 0.f, 0.f), s1 = s0;
+  int sidx = sg;
+  for (; sidx + 4 < u.nslices; sidx += 8) {
+    const float4 v0 = __ldg(src + (size_t)sidx * pitch4);
+    const float4 v1 = __ldg(src + (size_t)(sidx + 4) * pitch4);
+    s0.x += v0.x; s0.y += v0.y; s0.z += v0.z; s0.w += v0.w;
+    s1.x += v1.x; s1.y += v1.y; s1.z += v1.z; s1.w += v1.w;
+  }
+  if (sidx < u.nslices) {
+    const float4 v0 = __ldg(src + (size_t)sidx * pitch4);
+    s0.x += v0.x; s0.y += v0.y; s0.z += v0.z; s0.w += v0.w;
+  }
+  part[sg][col] = make_float4(s0.x + s1.x, s0.y + s1.y, s0.z + s1.z, s0.w + s1.w);
+  __syncthreads();
+  {
+    const int e = threadIdx.x;                       // one element per thread for the strided store
+    const int c = e >> 2, k = e & 3;
+    const float* p0 = reinterpret_cast<const float*>(&part[0][c]) + k;
+    const float v = (p0[0] + p0[256]) + (p0[512] + p0[768]);
+    const int gid = ((int)blockIdx.x - L.first_block[li]) * 256 + e;
+    const int b = gid & 63, a = (gid >> 6) & 63, t = gid >> 12;
+    if (t < u.ntaps) u.dw[t + (long long)a * u.a_stride + (long long)b * u.b_stride] += v;
+  }
 }
 
 template <int TMEM_COLS>
@@ -948,14 +986,54 @@ static int launch_wgrad_tma(dim3 grid, size_t smem, const CUtensorMap* tq, const
 }
 
 // dwp (packed fp32 [k*k][64][64], ACCUMULATED) += sum_m P[gather(m, tap), a] * Q[m, b]; q_colsum[b] += sum_m Q[m, b]
-int conv_wgrad_tma(const nsg_conv_geom* cg, const void* p, const void* q, float* dwp, float* q_colsum,
+// taps per blockIdx.y group and CTAs per group: shared by the launch and by conv_wgrad_slices
+static void wgrad_split(const nsg_conv_geom* cg, int total_tiles, int* taps_per_group, int* gx) {
+  const int ntaps = cg->ksize * cg->ksize;
+  // Split-K over pixels leaves every CTA with a whole [taps][64][64] partial, and getting those out, not the loads,
+  // bounded the first version of this kernel: 148 CTAs x 9 taps = 1.4 M 16-byte atomics per 3x3 launch.  Giving each
+  // blockIdx.y group 3 (of 9) or 4 (of 16) taps cuts the partial 3-4x for ~20 % more operand bytes (Q is re-read
+  // once per group).  Measured warm on B200 with atomics, 3x3: 24.4 us (all 9) / 17.1 (5) / 15.5 (3) / 19.0 (2) /
+  // 21.6 (1); 4x4: 24.3 (8) / 23.1 (6) / 21.2 (4) / 22.8 (3) / 26.8 (2).
+  int tpg = ntaps <= 4 ? ntaps : (ntaps == 9 ? 3 : 4);
+  static const int tpg_override = getenv("NSG_WGRAD_TPG") ? atoi(getenv("NSG_WGRAD_TPG")) : 0;   // tuning aid
+  if (tpg_override > 0 && tpg_override < tpg) tpg = tpg_override;
+  const int groups = (ntaps + tpg - 1) / tpg;
+  int x = num_sms() / groups;
+  if (x < 1) x = 1;
+  if (x > total_tiles) x = total_tiles;
+  *taps_per_group = tpg;
+  *gx = x;
+}
+
+static int wgrad_tiles(const nsg_conv_geom* cg) {
+  int bw, bh, l2;
+  pick_box_w(cg->out_w, WG_KP, &bw, &bh, &l2);
+  return ((cg->out_w + bw - 1) / bw) * ((cg->out_h + bh - 1) / bh) * cg->batch;
+}
+
+int conv_wgrad_slices(const nsg_conv_geom* cg) {
+  if (tma_shape_ok(cg, "conv_wgrad_slices")) return 0;
+  const int tiles = wgrad_tiles(cg);
+  if (tiles <= 0) return 1;
+  int tpg, gx;
+  wgrad_split(cg, tiles, &tpg, &gx);
+  return gx;
+}
+
+int conv_wgrad_tma(const nsg_conv_geom* cg, const void* p, const void* q, float* dwp, float* q_colsum, int sliced,
                    cudaStream_t stream) {
   if (int rc = tma_shape_ok(cg, "conv_wgrad_tma")) return rc;
   NSG_REQUIRE((reinterpret_cast<uintptr_t>(dwp) & 15) == 0, "conv_wgrad_tma: packed gradient image must be 16-byte aligned");
   NSG_REQUIRE((reinterpret_cast<uintptr_t>(p) & 15) == 0 && (reinterpret_cast<uintptr_t>(q) & 15) == 0,
               "conv_wgrad_tma: tensors must be 16-byte aligned");
   const long long M = (long long)cg->batch * cg->out_h * cg->out_w;
-  if (M == 0) return NSG_OK;
+  if (M == 0) {
+    if (sliced) {          // the one slice conv_wgrad_slices promised must still be defined
+      cudaError_t err = cudaMemsetAsync(dwp, 0, (size_t)cg->ksize * cg->ksize * TM_C * TM_C * sizeof(float), stream);
+      if (err != cudaSuccess) return cuda_fail(err, "cudaMemsetAsync(wgrad slice)");
+    }
+    return NSG_OK;
+  }
   TmaWgradParams P{};
   P.batch = cg->batch; P.q_h = cg->out_h; P.q_w = cg->out_w;
   P.in_stride = cg->stride;
@@ -972,16 +1050,9 @@ int conv_wgrad_tma(const nsg_conv_geom* cg, const void* p, const void* q, float*
       P.dw[kh * k + kw] = (signed char)(kw - cg->pad);
     }
   P.ones = q_colsum ? 1 : 0;
-  // Split-K over pixels makes every CTA add its whole [taps][64][64] partial into the packed image with vector
-  // atomics, and those, not the loads, bound the kernel: 148 CTAs x 9 taps = 1.4 M 16-byte atomics per 3x3 launch.
-  // Giving each blockIdx.y group 3 (of 9) or 4 (of 16) taps cuts the atomics 3-4x for ~20 % more operand bytes (Q is
-  // re-read once per group).  Measured warm on B200, 3x3: 24.4 us (all 9) / 17.1 (5) / 15.5 (3) / 19.0 (2) / 21.6 (1);
-  // 4x4: 24.3 (8) / 23.1 (6) / 21.2 (4) / 22.8 (3) / 26.8 (2).
-  P.taps_per_group = P.ntaps <= 4 ? P.ntaps : (P.ntaps == 9 ? 3 : 4);
-  {
-    static const int tpg_override = getenv("NSG_WGRAD_TPG") ? atoi(getenv("NSG_WGRAD_TPG")) : 0;   // tuning aid
-    if (tpg_override > 0 && tpg_override < P.taps_per_group) P.taps_per_group = tpg_override;
-  }
+  int gx;
+  wgrad_split(cg, P.total_tiles, &P.taps_per_group, &gx);
+  P.slice_elems = sliced ? P.ntaps * TM_C * TM_C : 0;
   const int groups = (P.ntaps + P.taps_per_group - 1) / P.taps_per_group;
   P.nslots = (P.taps_per_group + P.ones + 1) / 2 * 2;
   const uint32_t stage_bytes = (uint32_t)(P.nslots + 1) * WG_SLOT;
@@ -996,9 +1067,6 @@ int conv_wgrad_tma(const nsg_conv_geom* cg, const void* p, const void* q, float*
                                   (long long)cg->out_h * cg->out_w * TM_C, P.box_w, P.box_h))
     return rc;
   if (int rc = encode_input_maps(tp, p, cg->batch, cg->in_h, cg->in_w, P.in_stride, P.box_w, P.box_h)) return rc;
-  int gx = num_sms() / groups;
-  if (gx < 1) gx = 1;
-  if (gx > P.total_tiles) gx = P.total_tiles;
   const dim3 grid((unsigned)gx, (unsigned)groups);
   const int cols = P.nslots / 2 * TM_C;
   if (cols <= 64) return launch_wgrad_tma<64>(grid, smem, &tq, tp, dwp, q_colsum, P, stream);
@@ -1007,8 +1075,8 @@ int conv_wgrad_tma(const nsg_conv_geom* cg, const void* p, const void* q, float*
   return launch_wgrad_tma<512>(grid, smem, &tq, tp, dwp, q_colsum, P, stream);
 }
 
-int wgrad_unpack_many(int n, const float* const* src, float* const* dw, const int* ntaps, const long long* a_stride,
-                      const long long* b_stride, cudaStream_t stream) {
+int wgrad_unpack_many(int n, const float* const* src, float* const* dw, const int* ntaps, const int* nslices,
+                      const long long* a_stride, const long long* b_stride, cudaStream_t stream) {
   NSG_REQUIRE(n >= 0 && n <= 24, "wgrad_unpack_many: at most 24 layers per call (got %d)", n);
   if (n == 0) return NSG_OK;
   UnpackList L{};
@@ -1016,8 +1084,10 @@ int wgrad_unpack_many(int n, const float* const* src, float* const* dw, const in
   int blocks = 0;
   for (int i = 0; i < n; ++i) {
     NSG_REQUIRE(src[i] && dw[i] && ntaps[i] >= 1 && ntaps[i] <= TM_MAX_TAPS, "wgrad_unpack_many: bad item %d", i);
+    const int ns = nslices ? nslices[i] : 1;
+    NSG_REQUIRE(ns >= 1 && ns <= 4096, "wgrad_unpack_many: item %d has %d slices", i, ns);
     L.first_block[i] = blocks;
-    L.it[i] = UnpackItem{src[i], dw[i], ntaps[i], a_stride[i], b_stride[i]};
+    L.it[i] = UnpackItem{src[i], dw[i], ntaps[i], ns, a_stride[i], b_stride[i]};
     blocks += ntaps[i] * 16;
   }
   L.first_block[n] = blocks;

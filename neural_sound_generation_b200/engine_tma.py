@@ -17,6 +17,8 @@ gradients accumulate in packed fp32 images that ONE launch folds into the refere
 The single-channel ends (encoder.0, decoder.6) run on the tensor cores too (``c1t_*`` kernels: one
 tcgen05.mma per 128 pixels does the 64-channel expansion / reduction); other input_dim use the CUDA-core kernels.
 """
+import os
+
 import torch
 
 from . import ops
@@ -32,7 +34,7 @@ TC_LAYERS = ([('encoder.3', 4, 2, 1, False)]
 
 
 class _Layer(object):
-    __slots__ = ('name', 'k', 's', 'p', 'tr', 'wf', 'wd', 'dwp', 'wci_f', 'wco_f', 'wci_d', 'wco_d', 'wci_g', 'wco_g')
+    __slots__ = ('name', 'k', 's', 'p', 'tr', 'wf', 'wd', 'dwp', 'dwa', 'nslices', 'slice_cache', 'wci_f', 'wco_f', 'wci_d', 'wco_d', 'wci_g', 'wco_g')
 
 
 class EngineTMA(object):
@@ -48,6 +50,11 @@ class EngineTMA(object):
         self._key = None
         self.side = None            # second stream: weight gradients run beside the data-gradient chain
         self.overlap_wgrad = True
+        # Weight-gradient partials: False = CTAs meet in one packed image per layer through vector atomics; True = one
+        # slice per CTA, plain stores, summed in a fixed order by the unpack (bit-reproducible gradients).  Measured on
+        # B200 (configs[1], same box): the sliced kernels are 1-2 us faster each in isolation, but their 58 MB of
+        # partials push activations out of L2 and the step is slower, 0.824 vs 0.807 ms -- atomics stay the default.
+        self.wgrad_sliced = os.environ.get('NSG_WGRAD_SLICED', '0') == '1'
         self.dp = None              # dist.DataParallel: cross-rank BatchNorm statistics / bucketed gradient all-reduce
 
     # ------------------------------------------------------------------ packed images
@@ -59,14 +66,15 @@ class EngineTMA(object):
         D = self.dim
         ntaps_total = sum(k * k for _, k, *_ in TC_LAYERS)
         self.wimg = torch.empty(2 * ntaps_total * 8192 + 3 * 8192, dtype=torch.uint8, device=dev)
-        self.dwp = torch.zeros(ntaps_total * D * D, dtype=torch.float32, device=dev)
         self.layers = {}
         self.pack_items, self.unpack_items = [], []
-        self.dwp_split = 0          # first element of the decoder layers' gradient images (they are laid out last)
+        # wgrad_sliced = False: one packed image per layer, CTAs meet in it through vector atomics, cleared per step
+        self.dwa = torch.zeros(ntaps_total * D * D, dtype=torch.float32, device=dev)
+        self.dwa_split = 0          # first element of the decoder layers' images (they are laid out last)
         ow, og = 0, 0
         for name, k, s, p, tr in TC_LAYERS:
-            if name.startswith('decoder.') and self.dwp_split == 0:
-                self.dwp_split = og
+            if name.startswith('decoder.') and self.dwa_split == 0:
+                self.dwa_split = og
             L = _Layer()
             L.name, L.k, L.s, L.p, L.tr = name, k, s, p, tr
             w = P[name + '.weight']
@@ -82,7 +90,10 @@ class EngineTMA(object):
             L.wf = self.wimg[ow:ow + kk * 8192]
             L.wd = self.wimg[ow + kk * 8192:ow + 2 * kk * 8192]
             ow += 2 * kk * 8192
-            L.dwp = self.dwp[og:og + kk * D * D]
+            # weight-gradient partials [nslices, k*k, D, D]: one slice per CTA of the wgrad kernel (plain stores, no
+            # atomics, nothing to clear), sized at the first backward pass of a geometry and summed by unpack_part
+            L.dwp, L.nslices, L.slice_cache = None, 0, {}
+            L.dwa = self.dwa[og:og + kk * D * D]
             og += kk * D * D
             self.pack_items += [(w, L.wf, kk, L.wci_f, L.wco_f), (w, L.wd, kk, L.wci_d, L.wco_d)]
             self.layers[name] = L
@@ -98,8 +109,21 @@ class EngineTMA(object):
 
     def _unpack_items(self, G, part=None):
         """part: None = every layer, 'decoder' / 'encoder' = that half (the data-parallel gradient buckets)."""
-        return [(L.dwp, G[L.name + '.weight'], L.k * L.k, L.wci_g, L.wco_g) for L in self.layers.values()
-                if part is None or L.name.startswith(part + '.')]
+        return [(L.dwp, G[L.name + '.weight'], L.k * L.k, L.wci_g, L.wco_g, L.nslices) for L in self.layers.values()
+                if L.nslices > 0 and (part is None or L.name.startswith(part + '.'))]
+
+    def _wgrad_slices(self, L, g, key, dev):
+        if not self.wgrad_sliced:
+            L.dwp, L.nslices = L.dwa, 1
+            return L.dwa
+        ns = L.slice_cache.get(key)
+        if ns is None:
+            ns = L.slice_cache[key] = ops.conv_wgrad_slices(g)
+        need = ns * L.k * L.k * self.dim * self.dim
+        if L.dwp is None or L.dwp.numel() < need:
+            L.dwp = torch.empty(need, dtype=torch.float32, device=dev)
+        L.nslices = ns
+        return L.dwp
 
     # ------------------------------------------------------------------ helpers
     def _bn(self, ctx, name):
@@ -167,10 +191,12 @@ class EngineTMA(object):
         _, oh, ow, _ = dy.shape
         if L.tr:        # P = dy gathered over x's pixels, Q = x
             g = ops.conv_geom(b, oh, ow, c, h, w, c, L.k, L.s, L.p, 0, L.wci_g, L.wco_g, ops.BF16)
-            self._side(ctx, lambda: ops.conv_wgrad_tma(g, dy, x, L.dwp, q_colsum=q_colsum), x, dy)
+            dwp = self._wgrad_slices(L, g, (b, h, w, oh, ow), x.device)
+            self._side(ctx, lambda: ops.conv_wgrad_tma(g, dy, x, dwp, q_colsum=q_colsum, sliced=self.wgrad_sliced), x, dy)
         else:           # P = x gathered over dy's pixels, Q = dy
             g = ops.conv_geom(b, h, w, c, oh, ow, c, L.k, L.s, L.p, 0, L.wci_g, L.wco_g, ops.BF16)
-            self._side(ctx, lambda: ops.conv_wgrad_tma(g, x, dy, L.dwp, q_colsum=q_colsum), x, dy)
+            dwp = self._wgrad_slices(L, g, (b, h, w, oh, ow), x.device)
+            self._side(ctx, lambda: ops.conv_wgrad_tma(g, x, dy, dwp, q_colsum=q_colsum, sliced=self.wgrad_sliced), x, dy)
 
     def _bn_act(self, ctx, P, Bufs, name, h, res=None, relu_out=True):
         bn = self._bn(ctx, name)
@@ -366,7 +392,7 @@ class EngineTMA(object):
         return dx
 
     def finish_backward(self, ctx, G, part=None):
-        """Fold the packed weight-gradient images into the reference-layout gradients (one launch) and clear them.
+        """Sum the per-CTA weight-gradient partials into the reference-layout gradients (one launch).
         ``part`` restricts this to one half of the network (see ``unpack_part``)."""
         if ctx.forked:
             torch.cuda.current_stream().wait_stream(self.side)
@@ -375,14 +401,18 @@ class EngineTMA(object):
         self.unpack_part(G, part)
 
     def unpack_part(self, G, part=None):
-        """Unpack + clear the gradient images of 'decoder', 'encoder' or (None) all layers on the current stream."""
+        """Unpack the gradient partials of 'decoder', 'encoder' or (None) all layers on the current stream."""
         ops.wgrad_unpack_many(self._unpack_items(G, part))
-        if part is None:
-            self.dwp.zero_()
-        elif part == 'decoder':
-            self.dwp[self.dwp_split:].zero_()
-        else:
-            self.dwp[:self.dwp_split].zero_()
+        for L in self.layers.values():      # a layer's partials are consumed once
+            if part is None or L.name.startswith(part + '.'):
+                L.nslices = 0
+        if not self.wgrad_sliced:
+            if part is None:
+                self.dwa.zero_()
+            elif part == 'decoder':
+                self.dwa[self.dwa_split:].zero_()
+            else:
+                self.dwa[:self.dwa_split].zero_()
 
     # ------------------------------------------------------------------ bottleneck (models.py:127-142)
     def quantize(self, z_e, codebook, want_codes=True, sqerr=None):

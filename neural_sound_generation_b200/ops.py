@@ -352,21 +352,39 @@ def conv_gemm_tma(geom, x, packed, out, bias=None, add_src=None, mask_mode=MASK_
     return out
 
 
-def conv_wgrad_tma(geom, p, q, dw_packed, q_colsum=None):
+def conv_wgrad_slices(geom):
+    """Number of partial images conv_wgrad_tma(..., sliced=True) writes for this geometry on the current device."""
+    A.require_device()
+    s = A.load().nsg_conv_wgrad_slices(C.byref(geom))
+    if s <= 0:
+        raise RuntimeError('nsg_conv_wgrad_slices: geometry not served by the TMA weight-gradient kernel')
+    return s
+
+
+def conv_wgrad_tma(geom, p, q, dw_packed, q_colsum=None, sliced=False):
+    """sliced=False: dw_packed [k*k,64,64] += (atomics).  sliced=True: dw_packed [conv_wgrad_slices(geom),k*k,64,64]
+    is overwritten with per-CTA partials (summed by wgrad_unpack_many)."""
     global launch_count
     A.require_device()
     _cuda(p, q, dw_packed, q_colsum)
     _bf16(p, q)
     _contig(p, 'wgrad P')
     _contig(q, 'wgrad Q')
-    rc = A.load().nsg_conv_wgrad_tma(C.byref(geom), A.ptr(p), A.ptr(q), A.ptr(dw_packed), A.ptr(q_colsum),
-                                     A.stream_ptr())
-    A.check(rc, 'nsg_conv_wgrad_tma')
+    if sliced:
+        need = conv_wgrad_slices(geom) * geom.ksize * geom.ksize * 4096
+        if dw_packed.numel() < need or dw_packed.dtype != torch.float32:
+            raise ValueError('conv_wgrad_tma: sliced image needs %d fp32 elements, got %d' % (need, dw_packed.numel()))
+        fn, name = A.load().nsg_conv_wgrad_tma_sliced, 'nsg_conv_wgrad_tma_sliced'
+    else:
+        fn, name = A.load().nsg_conv_wgrad_tma, 'nsg_conv_wgrad_tma'
+    rc = fn(C.byref(geom), A.ptr(p), A.ptr(q), A.ptr(dw_packed), A.ptr(q_colsum), A.stream_ptr())
+    A.check(rc, name)
     launch_count += 1
 
 
 def wgrad_unpack_many(items):
-    """items: list of (dw_packed fp32 [k*k,64,64], dw fp32 parameter-layout gradient, ntaps, w_cin_stride, w_cout_stride)."""
+    """items: list of (dw_packed fp32 [S,k*k,64,64], dw fp32 parameter-layout gradient, ntaps, w_cin_stride,
+    w_cout_stride[, S = 1])."""
     global launch_count
     A.require_device()
     if not items:
@@ -374,8 +392,8 @@ def wgrad_unpack_many(items):
     n = len(items)
     rc = A.load().nsg_wgrad_unpack_many(
         n, _ptr_array([it[0] for it in items]), _ptr_array([it[1] for it in items]),
-        (C.c_int * n)(*[it[2] for it in items]), (C.c_longlong * n)(*[it[3] for it in items]),
-        (C.c_longlong * n)(*[it[4] for it in items]), A.stream_ptr())
+        (C.c_int * n)(*[it[2] for it in items]), (C.c_int * n)(*[(it[5] if len(it) > 5 else 1) for it in items]),
+        (C.c_longlong * n)(*[it[3] for it in items]), (C.c_longlong * n)(*[it[4] for it in items]), A.stream_ptr())
     A.check(rc, 'nsg_wgrad_unpack_many')
     launch_count += 1
 

@@ -114,6 +114,25 @@ def test_conv_tma_forward_dgrad_wgrad(case):
     ops.wgrad_unpack_many([(dwp, dw2, k * k, wgr.w_cin_stride, wgr.w_cout_stride)])
     torch.cuda.synchronize()
     assert relerr(dw2, 2 * wd.grad) < ACC_TOL, 'wgrad accumulate'
+    # sliced form (the training step's): per-CTA partial images, overwritten, summed by the unpack; stale contents
+    # of the slices must not matter and two runs must agree bit for bit (no atomics on the weight gradient)
+    ns = ops.conv_wgrad_slices(wgr)
+    assert ns >= 1
+    outs = []
+    for fill in (float('nan'), 7.0):
+        sl = torch.full((ns, k * k, C, C), fill, dtype=torch.float32, device=DEV)
+        if transposed:
+            ops.conv_wgrad_tma(wgr, gyg, xg, sl, sliced=True)
+        else:
+            ops.conv_wgrad_tma(wgr, xg, gyg, sl, sliced=True)
+        dw3 = torch.zeros_like(wg)
+        ops.wgrad_unpack_many([(sl, dw3, k * k, wgr.w_cin_stride, wgr.w_cout_stride, ns)])
+        torch.cuda.synchronize()
+        assert relerr(dw3, wd.grad) < ACC_TOL, 'wgrad sliced'
+        outs.append(dw3)
+    assert torch.equal(outs[0], outs[1]), 'sliced wgrad is not run-to-run deterministic'
+    with pytest.raises(ValueError):
+        ops.conv_wgrad_tma(wgr, xg, gyg, torch.zeros(16, device=DEV), sliced=True)
 
 
 def test_conv_tma_epilogue_mask_add_bnbwd_stats():

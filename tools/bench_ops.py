@@ -94,6 +94,13 @@ def main():
             else:
                 t = timed(lambda: ops.conv_wgrad_tma(wgr, x, gy, dwp, q_colsum=col), flush=fl)
             print('%-26s wgrad      %s %8.1f us  %7.1f TFLOP/s' % (name, tag, t, flop / t / 1e6))
+            ns = ops.conv_wgrad_slices(wgr)
+            sl = torch.empty(ns, k * k, C, C, device=DEV)
+            if tr:
+                t = timed(lambda: ops.conv_wgrad_tma(wgr, gy, x, sl, q_colsum=col, sliced=True), flush=fl)
+            else:
+                t = timed(lambda: ops.conv_wgrad_tma(wgr, x, gy, sl, q_colsum=col, sliced=True), flush=fl)
+            print('%-26s wgrad/%-3d  %s %8.1f us  %7.1f TFLOP/s' % (name, ns, tag, t, flop / t / 1e6))
     if only is not None and int(only) >= 0:
         return
     # single-channel ends (conv_c1_fast.cu): encoder.0 fwd / wgrad, decoder.6 fwd / dgrad / wgrad
