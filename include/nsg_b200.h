@@ -164,6 +164,10 @@ int nsg_conv_gemm_tma(const nsg_conv_geom* g, const void* in, const void* packed
                       void* stream);
 int nsg_conv_wgrad_tma(const nsg_conv_geom* g, const void* p, const void* q, float* dw_packed, float* q_colsum,
                        void* stream);
+/* Programmatic dependent launch for the kernels that support it (the 64-channel convolutions and their BatchNorm
+ * companions): 1 (default) lets such a kernel become resident and run its data-independent prologue while its
+ * predecessor in the stream drains; results are identical.  Returns the previous setting; any other value only reads. */
+int nsg_pdl(int enable);
 int nsg_conv_wgrad_slices(const nsg_conv_geom* g);
 int nsg_conv_wgrad_tma_sliced(const nsg_conv_geom* g, const void* p, const void* q, float* dw_slices, float* q_colsum,
                               void* stream);

@@ -1,4 +1,5 @@
 // C-ABI plumbing: error text, device check, dispatch between the CUDA-core and tcgen05 kernels.
+#include <cstdlib>
 #include <cstring>
 
 #include "common.cuh"
@@ -59,6 +60,7 @@ int conv_wgrad_slices(const nsg_conv_geom* cg);
 int wgrad_unpack_many(int n, const float* const* src, float* const* dw, const int* ntaps, const int* nslices,
                       const long long* a_stride, const long long* b_stride, cudaStream_t stream);
 
+int g_pdl = getenv("NSG_PDL") ? atoi(getenv("NSG_PDL")) : 1;     // common.cuh: programmatic dependent launch
 }  // namespace nsg
 
 using namespace nsg;
@@ -189,6 +191,12 @@ int nsg_conv_wgrad_tma(const nsg_conv_geom* g, const void* p, const void* q, flo
   if (rc) return rc;
   NSG_REQUIRE(p && q && dw_packed, "conv_wgrad_tma: null pointer");
   return conv_wgrad_tma(g, p, q, dw_packed, q_colsum, 0, (cudaStream_t)stream);
+}
+
+int nsg_pdl(int enable) {
+  const int old = g_pdl;
+  if (enable == 0 || enable == 1) g_pdl = enable;
+  return old;
 }
 
 int nsg_conv_wgrad_slices(const nsg_conv_geom* g) {

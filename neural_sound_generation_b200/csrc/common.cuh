@@ -31,6 +31,36 @@ int cuda_fail(cudaError_t e, const char* what);
 
 int num_sms();
 
+// ---- programmatic dependent launch (PDL).  A kernel launched through launch_pdl may become resident while its
+// predecessor in the stream is still running (the predecessor's CTAs have executed pdl_trigger() or exited); it must
+// execute pdl_wait() before its first access to memory an earlier kernel wrote -- pdl_wait() returns when ALL earlier
+// work in the stream has completed and is visible, so the dependency stays exact and only launch latency and the
+// prologue (barrier / TMEM set-up, layer-constant loads) move under the predecessor's tail.  Both instructions are
+// no-ops in a kernel launched without the attribute.  g_pdl = 0 (NSG_PDL=0) turns the attribute off.
+extern int g_pdl;
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = g_pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+#if defined(__CUDA_ARCH__)
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+#else
+__device__ __forceinline__ void pdl_wait() {}
+__device__ __forceinline__ void pdl_trigger() {}
+#endif
+
 // ---- activation storage types: float or bf16, always computed in fp32
 template <typename T>
 struct Act;

@@ -299,6 +299,8 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int stages = P.stages;
   if (tid == 0) tm_stamp(P.dbg, 0);
+  pdl_trigger();
+  pdl_wait();
 
   if (tid < TM_C) {
     sPar[0 * TM_C + tid] = epi.bias ? __ldg(epi.bias + tid) : 0.f;
@@ -705,8 +707,8 @@ int conv_gemm_tma(const nsg_conv_geom* cg, const void* in, const void* packed, c
     configured = true;
   }
   const int grid = tiles < num_sms() ? tiles : num_sms();
-  conv_tma_kernel<<<grid, 320, smem, stream>>>(tm[0], tm[1], tm[2], tm[3], static_cast<const uint8_t*>(packed),
-                                               static_cast<__nv_bfloat16*>(out), e, P);
+  launch_pdl(conv_tma_kernel, dim3(grid), dim3(320), smem, stream, tm[0], tm[1], tm[2], tm[3],
+             static_cast<const uint8_t*>(packed), static_cast<__nv_bfloat16*>(out), e, P);
   NSG_CHECK_LAUNCH("conv_tma_kernel");
   return NSG_OK;
 }
@@ -741,22 +743,37 @@ int conv_pack_many(int n, const float* const* w, void* const* dst, const int* nt
 }
 
 // ---------------------------------------------------------------------------------------------- weight gradient
-constexpr int WG_KP = 64;                          // pixels per box (GEMM K per stage)
-constexpr uint32_t WG_SLOT = WG_KP * 128;          // one 64-pixel x 64-channel bf16 box
+constexpr int WG_KP = 128;                         // pixels per box (GEMM K per stage)
+constexpr uint32_t WG_SLOT = WG_KP * 128;          // one WG_KP-pixel x 64-channel bf16 box
+constexpr int C1W_KP = 64;                         // the single-channel layers' weight-gradient kernel (below)
+constexpr uint32_t C1W_SLOT = C1W_KP * 128;
 constexpr int WG_MAX_STAGES = 8;
 
+// One blockIdx.y group = the taps of one kernel COLUMN (kw fixed).  Its taps differ only by a vertical shift (per
+// row-parity view when in_stride = 2), so they are served by ONE halo box per view, (box_h + halo) rows tall: tap kh's
+// operand is the box advanced by its shift * box_w pixels -- a multiple of the 1024-byte swizzle atom because
+// box_w % 8 == 0.  Operands (taps, then an all-ones block for the column sums of Q, then a zero block if the count is
+// odd) are paired in address order into M = 128 MMAs; the LBO field of the MN-major descriptor is the byte distance
+// between the two 64-channel blocks of a pair, whatever it is.
+constexpr int WG_MAX_OPS = 6;                      // 4 taps + ones + zeros
+constexpr uint32_t WG_CONST_FLAG = 0x40000000u;    // operand offset is relative to the constant region, not the stage
+struct WgGroup {
+  int nboxes, nops;
+  int bmap[2], bdw[2], bdh[2];   // per halo box: tensor map, coordinate offsets from the tile origin
+  uint32_t off[WG_MAX_OPS];      // byte offset of each operand (stage-relative, or WG_CONST_FLAG | constant-relative)
+  int tap[WG_MAX_OPS];           // tap index kh * k + kw; -2 = ones (column sums); -1 = zeros
+};
 struct TmaWgradParams {
   int batch, q_h, q_w;
-  int in_stride;                 // P gather: ip = q * in_stride + d
-  int box_w, box_h;
+  int box_w, box_h;              // Q box; P boxes are box_h + halo rows
   int tiles_h, tiles_w, total_tiles;
-  int ntaps, taps_per_group;     // all taps; taps served by one blockIdx.y group
-  int nslots;                    // even number of P slots per stage (taps of the group [+ ones slot] [+ zero slot])
-  int ones;                      // 1: group 0 carries an all-ones slot right after its taps (column sums of Q)
   int stages;
+  uint32_t box_bytes, stage_bytes;   // one P halo box; boxes + Q
   int slice_elems;               // 0: add into ONE packed image with vector atomics; else CTA x stores its partial
                                  // image into slice x of [gridDim.x][ntaps][64][64] (no atomics, summed by the unpack)
-  signed char dh[TM_MAX_TAPS], dw[TM_MAX_TAPS];
+  int dbg;
+  unsigned long long* stamps;    // optional clock64 stamps of CTA (0, 0) (nsg_debug_timeline), null in production
+  WgGroup g[4];
 };
 
 // instruction descriptor, kind::f16: D = f32, A = B = bf16, both MN-major
@@ -780,30 +797,42 @@ wgrad_tma_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
                  const __grid_constant__ TmaWgradParams P) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sm = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  const int NS = P.nslots;
-  const uint32_t stage_bytes = (uint32_t)(NS + 1) * WG_SLOT;            // P slots, then Q
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sm + (size_t)P.stages * stage_bytes);
+  const WgGroup& G = P.g[blockIdx.y];
+  uint8_t* sConst = sm + (size_t)P.stages * P.stage_bytes;               // [ones | zeros], WG_SLOT each
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sConst + 2 * WG_SLOT);
   uint64_t* full = bars;                         // [8]
   uint64_t* empty = bars + WG_MAX_STAGES;        // [8]
   uint64_t* acc_full = bars + 2 * WG_MAX_STAGES;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 1);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int tap_base = (int)blockIdx.y * P.taps_per_group;
-  const int ntaps = min(P.taps_per_group, P.ntaps - tap_base);
-  const bool ones = P.ones && blockIdx.y == 0;
+  const int npairs = G.nops / 2;
+  unsigned long long* stamps = (blockIdx.x == 0 && blockIdx.y == 0) ? P.stamps : nullptr;
+  if (tid == 0) tm_stamp(stamps, 0);
   const int ntiles_mine = ((int)blockIdx.x < P.total_tiles)
                               ? (P.total_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
 
-  // constant slots (all-ones for the bias gradient, zeros for an odd slot out) are written once per stage
-  for (int sl = ntaps; sl < NS; ++sl) {
-    const uint32_t fill = (sl == ntaps && ones) ? 0x3F803F80u : 0u;
-    for (int s = 0; s < P.stages; ++s) {
-      uint4* dst = reinterpret_cast<uint4*>(sm + (size_t)s * stage_bytes + (size_t)sl * WG_SLOT);
-      for (int i = tid; i < (int)(WG_SLOT / 16); i += 192) dst[i] = make_uint4(fill, fill, fill, fill);
-    }
+  for (int i = tid; i < (int)(2 * WG_SLOT / 16); i += 192) {
+    const uint32_t fill = i < (int)(WG_SLOT / 16) ? 0x3F803F80u : 0u;
+    reinterpret_cast<uint4*>(sConst)[i] = make_uint4(fill, fill, fill, fill);
   }
   fence_proxy_async_smem();
+  // Both single-thread loops below are bound by their own instruction latency (clock64 timeline: 1130 cycles per
+  // 3x3 tile in the MMA loop, 700 in the producer, before these tables), so everything that does not change from
+  // tile to tile is computed here, once: the A descriptor of every (stage, pair) and the B descriptor of every stage.
+  __shared__ uint64_t sDA[WG_MAX_STAGES][WG_MAX_OPS / 2];
+  __shared__ uint64_t sDB[WG_MAX_STAGES];
+  if (tid >= 64 && tid < 64 + WG_MAX_STAGES * (WG_MAX_OPS / 2)) {
+    const int s = (tid - 64) / (WG_MAX_OPS / 2), j = (tid - 64) % (WG_MAX_OPS / 2);
+    if (s < P.stages && j < npairs) {
+      const uint32_t base = smem_u32(sm + (size_t)s * P.stage_bytes), cbase = smem_u32(sConst);
+      const uint32_t o0 = G.off[2 * j], o1 = G.off[2 * j + 1];
+      const uint32_t a0 = (o0 & WG_CONST_FLAG) ? cbase + (o0 & ~WG_CONST_FLAG) : base + o0;
+      const uint32_t a1 = (o1 & WG_CONST_FLAG) ? cbase + (o1 & ~WG_CONST_FLAG) : base + o1;
+      sDA[s][j] = sw128_desc_mnmajor(a0, a1 - a0);
+      if (j == 0) sDB[s] = sw128_desc_mnmajor(base + (uint32_t)G.nboxes * P.box_bytes, WG_SLOT);
+    }
+  }
   if (tid == 0) {
     for (int s = 0; s < WG_MAX_STAGES; ++s) {
       mbar_init(&full[s], 1);
@@ -819,74 +848,95 @@ wgrad_tma_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  if (tid == 0) tm_stamp(stamps, 1);
 
   if (ntiles_mine > 0) {
     if (warp == 0) {
-      // ---------------------------------------------------------------- TMA producer
-      if (lane == 0) {
-        for (int i = 0; i < ntiles_mine; ++i) {
-          int local = (int)blockIdx.x + i * (int)gridDim.x;
-          const int tw = local % P.tiles_w;
-          local /= P.tiles_w;
-          const int th = local % P.tiles_h, n = local / P.tiles_h;
-          const int w0 = tw * P.box_w, h0 = th * P.box_h;
-          const int s = i % P.stages, round = i / P.stages;
-          if (round > 0) mbar_wait(&empty[s], (uint32_t)((round - 1) & 1));
-          uint8_t* stage = sm + (size_t)s * stage_bytes;
-          mbar_arrive_expect_tx(&full[s], (uint32_t)(ntaps + 1) * WG_SLOT);
-          tma::load_4d(stage + (size_t)NS * WG_SLOT, &tq, 0, w0, h0, n, &full[s]);
-          for (int t = 0; t < ntaps; ++t) {
-            const int dh = P.dh[tap_base + t], dw = P.dw[tap_base + t];
-            if (P.in_stride == 1) {
-              tma::load_4d(stage + (size_t)t * WG_SLOT, &tp0, 0, w0 + dw, h0 + dh, n, &full[s]);
-            } else {
-              const int par = (dh & 1) * 2 + (dw & 1);
-              const CUtensorMap* tm = par == 0 ? &tp0 : (par == 1 ? &tp1 : (par == 2 ? &tp2 : &tp3));
-              tma::load_4d(stage + (size_t)t * WG_SLOT, tm, 0, w0 + (dw >> 1), h0 + (dh >> 1), n, &full[s]);
+      // ---------------------------------------------------------------- TMA producer: the lanes decode 32 tiles'
+      // coordinates at once (the divisions), lane 0 issues them
+      const uint32_t q_off = (uint32_t)G.nboxes * P.box_bytes;
+      const CUtensorMap* m0 = G.bmap[0] == 0 ? &tp0 : (G.bmap[0] == 1 ? &tp1 : (G.bmap[0] == 2 ? &tp2 : &tp3));
+      const CUtensorMap* m1 = G.bmap[1] == 0 ? &tp0 : (G.bmap[1] == 1 ? &tp1 : (G.bmap[1] == 2 ? &tp2 : &tp3));
+      const int bdw0 = G.bdw[0], bdh0 = G.bdh[0], bdw1 = G.bdw[1], bdh1 = G.bdh[1];
+      const bool two = G.nboxes > 1, skip_p = (P.dbg & 2) != 0;
+      const uint32_t tx = skip_p ? WG_SLOT : q_off + WG_SLOT;
+      const uint32_t sm0 = smem_u32(sm);
+      int s = 0;
+      uint32_t wait_parity = 1;            // parity of the phase BEFORE the first completion: returns at once
+      for (int i0 = 0; i0 < ntiles_mine; i0 += 32) {
+        int local = (int)blockIdx.x + (i0 + lane) * (int)gridDim.x;
+        const int tw = local % P.tiles_w;
+        local /= P.tiles_w;
+        const int my_w0 = tw * P.box_w, my_h0 = (local % P.tiles_h) * P.box_h, my_n = local / P.tiles_h;
+        const int cnt = min(32, ntiles_mine - i0);
+        for (int t = 0; t < cnt; ++t) {
+          const int w0 = __shfl_sync(0xffffffffu, my_w0, t), h0 = __shfl_sync(0xffffffffu, my_h0, t);
+          const int n = __shfl_sync(0xffffffffu, my_n, t);
+          if (lane == 0) {
+            mbar_wait(&empty[s], wait_parity);
+            const uint32_t stage = sm0 + (uint32_t)s * P.stage_bytes;
+            mbar_arrive_expect_tx(&full[s], tx);
+            tma::load_4d_u32(stage + q_off, &tq, 0, w0, h0, n, &full[s]);
+            if (!skip_p) {
+              tma::load_4d_u32(stage, m0, 0, w0 + bdw0, h0 + bdh0, n, &full[s]);
+              if (two) tma::load_4d_u32(stage + P.box_bytes, m1, 0, w0 + bdw1, h0 + bdh1, n, &full[s]);
             }
+            if (i0 + t < 10) tm_stamp(stamps, 2 + i0 + t);     // 2..11: producer issued tile i
+          }
+          if (++s == P.stages) {
+            s = 0;
+            wait_parity ^= 1;
           }
         }
       }
+      if (lane == 0) tm_stamp(stamps, 12);
     } else if (warp == 1) {
       // ---------------------------------------------------------------- MMA issuer
       if (lane == 0) {
         const uint32_t idesc = idesc_bf16_mnmajor(128, TM_C);
-        const int npairs = NS / 2;
+        const int np = (P.dbg & 1) ? 0 : npairs;
+        int s = 0;
+        uint32_t parity = 0;
         for (int i = 0; i < ntiles_mine; ++i) {
-          const int s = i % P.stages, round = i / P.stages;
-          mbar_wait(&full[s], (uint32_t)(round & 1));
+          mbar_wait(&full[s], parity);
           tc_fence_after();
-          const uint32_t base = smem_u32(sm + (size_t)s * stage_bytes);
-          for (int j = 0; j < npairs; ++j) {
+          if (i < 10) tm_stamp(stamps, 13 + i);              // 13..22: tile i landed
+          const uint64_t db = sDB[s];
+          for (int j = 0; j < np; ++j) {
+            const uint64_t da = sDA[s][j];
             const uint32_t d = tmem_base + (uint32_t)j * TM_C;
+            // K steps of 16 pixels = 2048 bytes = 128 in the descriptors' 16-byte address field (no carry: < 256 KB)
+            umma_bf16(d, da, db, idesc, i != 0);
 #pragma unroll
-            for (int ks = 0; ks < WG_KP / 16; ++ks) {
-              const uint64_t a = sw128_desc_mnmajor(base + (uint32_t)(2 * j) * WG_SLOT + ks * 2048, WG_SLOT);
-              const uint64_t b = sw128_desc_mnmajor(base + (uint32_t)NS * WG_SLOT + ks * 2048, WG_SLOT);
-              umma_bf16(d, a, b, idesc, (i | ks) != 0);
-            }
+            for (int ks = 1; ks < WG_KP / 16; ++ks) umma_bf16(d, da + ks * 128, db + ks * 128, idesc, true);
           }
           umma_commit(&empty[s]);
+          if (++s == P.stages) {
+            s = 0;
+            parity ^= 1;
+          }
         }
         umma_commit(acc_full);
+        tm_stamp(stamps, 23);                                // all MMAs issued
       }
     } else {
-      // ---------------------------------------------------------------- epilogue: thread = (slot parity, channel a)
+      // ---------------------------------------------------------------- epilogue: thread = (block of the pair, channel a)
       mbar_wait(acc_full, 0);
       tc_fence_after();
+      if (tid == 64) tm_stamp(stamps, 24);                   // accumulators complete
       const int q = warp & 3;
       const int row = q * 32 + lane;
       const int a = row & 63, sp = row >> 6;
-      for (int j = 0; j < NS / 2; ++j) {
-        const int sl = 2 * j + sp;
+      for (int j = 0; j < npairs; ++j) {
+        const int tap = G.tap[2 * j + sp];
         uint32_t acc0[32], acc1[32];
         const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(j * TM_C);
         tmem_ld32(taddr, acc0);
         tmem_ld32(taddr + 32, acc1);
         tmem_ld_wait();
-        if (sl < ntaps && P.slice_elems) {
+        if (tap >= 0 && P.slice_elems) {
           float4* dst = reinterpret_cast<float4*>(dwp + (size_t)blockIdx.x * P.slice_elems +
-                                                  ((size_t)(tap_base + sl) * TM_C + a) * TM_C);
+                                                  ((size_t)tap * TM_C + a) * TM_C);
 #pragma unroll
           for (int v = 0; v < 8; ++v) {
             dst[v] = make_float4(__uint_as_float(acc0[4 * v]), __uint_as_float(acc0[4 * v + 1]),
@@ -894,8 +944,8 @@ wgrad_tma_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
             dst[8 + v] = make_float4(__uint_as_float(acc1[4 * v]), __uint_as_float(acc1[4 * v + 1]),
                                      __uint_as_float(acc1[4 * v + 2]), __uint_as_float(acc1[4 * v + 3]));
           }
-        } else if (sl < ntaps) {
-          float* dst = dwp + ((size_t)(tap_base + sl) * TM_C + a) * TM_C;
+        } else if (tap >= 0) {
+          float* dst = dwp + ((size_t)tap * TM_C + a) * TM_C;
 #pragma unroll
           for (int v = 0; v < 8; ++v) {
             red_add_v4(dst + 4 * v, __uint_as_float(acc0[4 * v]), __uint_as_float(acc0[4 * v + 1]),
@@ -903,8 +953,8 @@ wgrad_tma_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
             red_add_v4(dst + 32 + 4 * v, __uint_as_float(acc1[4 * v]), __uint_as_float(acc1[4 * v + 1]),
                        __uint_as_float(acc1[4 * v + 2]), __uint_as_float(acc1[4 * v + 3]));
           }
-        } else if (sl == ntaps && ones && colsum) {
-          // every row of the ones slot holds the column sums of Q; row a contributes column a
+        } else if (tap == -2 && colsum) {
+          // every row of the ones block holds the column sums of Q; row a contributes column a
           float v = 0.f;
 #pragma unroll
           for (int c = 0; c < 32; ++c) {
@@ -916,9 +966,11 @@ wgrad_tma_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
       }
     }
   }
+  if (tid == 64) tm_stamp(stamps, 25);                       // epilogue of warp 2 done
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc<TMEM_COLS>(tmem_base);
+  if (tid == 0) tm_stamp(stamps, 26);
 }
 
 // dw[t + a*a_stride + b*b_stride] += sum_s packed[s][t][a][b]  for every listed layer, one launch
@@ -986,38 +1038,29 @@ static int launch_wgrad_tma(dim3 grid, size_t smem, const CUtensorMap* tq, const
 }
 
 // dwp (packed fp32 [k*k][64][64], ACCUMULATED) += sum_m P[gather(m, tap), a] * Q[m, b]; q_colsum[b] += sum_m Q[m, b]
-// taps per blockIdx.y group and CTAs per group: shared by the launch and by conv_wgrad_slices
-static void wgrad_split(const nsg_conv_geom* cg, int total_tiles, int* taps_per_group, int* gx) {
-  const int ntaps = cg->ksize * cg->ksize;
-  // Split-K over pixels leaves every CTA with a whole [taps][64][64] partial, and getting those out, not the loads,
-  // bounded the first version of this kernel: 148 CTAs x 9 taps = 1.4 M 16-byte atomics per 3x3 launch.  Giving each
-  // blockIdx.y group 3 (of 9) or 4 (of 16) taps cuts the partial 3-4x for ~20 % more operand bytes (Q is re-read
-  // once per group).  Measured warm on B200 with atomics, 3x3: 24.4 us (all 9) / 17.1 (5) / 15.5 (3) / 19.0 (2) /
-  // 21.6 (1); 4x4: 24.3 (8) / 23.1 (6) / 21.2 (4) / 22.8 (3) / 26.8 (2).
-  int tpg = ntaps <= 4 ? ntaps : (ntaps == 9 ? 3 : 4);
-  static const int tpg_override = getenv("NSG_WGRAD_TPG") ? atoi(getenv("NSG_WGRAD_TPG")) : 0;   // tuning aid
-  if (tpg_override > 0 && tpg_override < tpg) tpg = tpg_override;
-  const int groups = (ntaps + tpg - 1) / tpg;
-  int x = num_sms() / groups;
-  if (x < 1) x = 1;
-  if (x > total_tiles) x = total_tiles;
-  *taps_per_group = tpg;
-  *gx = x;
-}
-
+//
+// Split: blockIdx.y = kernel column kw (k groups), blockIdx.x = num_sms / k CTAs striding over the 64-pixel tiles.
+// History of the split, measured warm on B200 (3x3, 64 x 20 x 32 pixels): every CTA serving all 9 taps from 9 separate
+// boxes left room for only 2 stages of 80 KB, 24.4 us; 3 taps per group (5 stages), 15.5 us; the 3 taps of a COLUMN
+// from one halo box (this version) cuts the P bytes by a further third.  The kernel is bound by the L2 -> SM box
+// traffic, not by its partials: replacing the atomics by plain stores gains 1-2 us (nsg_conv_wgrad_tma_sliced).
 static int wgrad_tiles(const nsg_conv_geom* cg) {
   int bw, bh, l2;
   pick_box_w(cg->out_w, WG_KP, &bw, &bh, &l2);
   return ((cg->out_w + bw - 1) / bw) * ((cg->out_h + bh - 1) / bh) * cg->batch;
+}
+static int wgrad_grid_x(const nsg_conv_geom* cg, int total_tiles) {
+  int x = num_sms() / cg->ksize;
+  if (x < 1) x = 1;
+  if (x > total_tiles) x = total_tiles;
+  return x;
 }
 
 int conv_wgrad_slices(const nsg_conv_geom* cg) {
   if (tma_shape_ok(cg, "conv_wgrad_slices")) return 0;
   const int tiles = wgrad_tiles(cg);
   if (tiles <= 0) return 1;
-  int tpg, gx;
-  wgrad_split(cg, tiles, &tpg, &gx);
-  return gx;
+  return wgrad_grid_x(cg, tiles);
 }
 
 int conv_wgrad_tma(const nsg_conv_geom* cg, const void* p, const void* q, float* dwp, float* q_colsum, int sliced,
@@ -1026,53 +1069,99 @@ int conv_wgrad_tma(const nsg_conv_geom* cg, const void* p, const void* q, float*
   NSG_REQUIRE((reinterpret_cast<uintptr_t>(dwp) & 15) == 0, "conv_wgrad_tma: packed gradient image must be 16-byte aligned");
   NSG_REQUIRE((reinterpret_cast<uintptr_t>(p) & 15) == 0 && (reinterpret_cast<uintptr_t>(q) & 15) == 0,
               "conv_wgrad_tma: tensors must be 16-byte aligned");
+  const int k = cg->ksize, stride = cg->stride;
+  NSG_REQUIRE(k >= 1 && k <= 4 && (stride == 1 || stride == 2), "conv_wgrad_tma: kernel %d stride %d not served", k, stride);
   const long long M = (long long)cg->batch * cg->out_h * cg->out_w;
   if (M == 0) {
     if (sliced) {          // the one slice conv_wgrad_slices promised must still be defined
-      cudaError_t err = cudaMemsetAsync(dwp, 0, (size_t)cg->ksize * cg->ksize * TM_C * TM_C * sizeof(float), stream);
+      cudaError_t err = cudaMemsetAsync(dwp, 0, (size_t)k * k * TM_C * TM_C * sizeof(float), stream);
       if (err != cudaSuccess) return cuda_fail(err, "cudaMemsetAsync(wgrad slice)");
     }
     return NSG_OK;
   }
   TmaWgradParams P{};
   P.batch = cg->batch; P.q_h = cg->out_h; P.q_w = cg->out_w;
-  P.in_stride = cg->stride;
   int l2;
   pick_box_w(cg->out_w, WG_KP, &P.box_w, &P.box_h, &l2);
   P.tiles_w = (cg->out_w + P.box_w - 1) / P.box_w;
   P.tiles_h = (cg->out_h + P.box_h - 1) / P.box_h;
   P.total_tiles = P.tiles_w * P.tiles_h * cg->batch;
-  const int k = cg->ksize;
-  P.ntaps = k * k;
-  for (int kh = 0; kh < k; ++kh)
-    for (int kw = 0; kw < k; ++kw) {
-      P.dh[kh * k + kw] = (signed char)(kh - cg->pad);
-      P.dw[kh * k + kw] = (signed char)(kw - cg->pad);
+  P.slice_elems = sliced ? k * k * TM_C * TM_C : 0;
+  P.dbg = getenv("NSG_WGRAD_DBG") ? atoi(getenv("NSG_WGRAD_DBG")) : 0;
+  P.stamps = g_timeline;
+
+  // vertical shift of tap kh inside its (row-parity) view, and the halo the tallest class needs
+  int sh[4], cls[4], halo = 0, nboxes_max = 0;
+  for (int kh = 0; kh < k; ++kh) {
+    const int dh = kh - cg->pad;
+    sh[kh] = stride == 1 ? dh : (dh >> 1);
+    cls[kh] = stride == 1 ? 0 : (dh & 1);
+  }
+  int cmin[2] = {1 << 20, 1 << 20}, cmax[2] = {-(1 << 20), -(1 << 20)};
+  for (int kh = 0; kh < k; ++kh) {
+    cmin[cls[kh]] = sh[kh] < cmin[cls[kh]] ? sh[kh] : cmin[cls[kh]];
+    cmax[cls[kh]] = sh[kh] > cmax[cls[kh]] ? sh[kh] : cmax[cls[kh]];
+  }
+  for (int c = 0; c < 2; ++c)
+    if (cmax[c] >= cmin[c]) {
+      ++nboxes_max;
+      if (cmax[c] - cmin[c] > halo) halo = cmax[c] - cmin[c];
     }
-  P.ones = q_colsum ? 1 : 0;
-  int gx;
-  wgrad_split(cg, P.total_tiles, &P.taps_per_group, &gx);
-  P.slice_elems = sliced ? P.ntaps * TM_C * TM_C : 0;
-  const int groups = (P.ntaps + P.taps_per_group - 1) / P.taps_per_group;
-  P.nslots = (P.taps_per_group + P.ones + 1) / 2 * 2;
-  const uint32_t stage_bytes = (uint32_t)(P.nslots + 1) * WG_SLOT;
-  const uint32_t tail = (2 * WG_MAX_STAGES + 2) * 8 + 64;
-  int stages = (int)((TM_SMEM_LIMIT - 1024 - tail) / stage_bytes);
+  const uint32_t row_bytes = (uint32_t)P.box_w * 128u;
+  P.box_bytes = (uint32_t)(P.box_h + halo) * row_bytes;
+  P.stage_bytes = (uint32_t)nboxes_max * P.box_bytes + WG_SLOT;
+  int max_ops = 0;
+  for (int kw = 0; kw < k; ++kw) {
+    WgGroup& G = P.g[kw];
+    const int dw = kw - cg->pad;
+    int box_of_cls[2] = {-1, -1};
+    G.nboxes = 0;
+    for (int c = 0; c < 2; ++c)
+      if (cmax[c] >= cmin[c]) {
+        const int b = G.nboxes++;
+        box_of_cls[c] = b;
+        G.bmap[b] = stride == 1 ? 0 : c * 2 + (dw & 1);
+        G.bdw[b] = stride == 1 ? dw : (dw >> 1);
+        G.bdh[b] = cmin[c];
+      }
+    // operands in address order: box 0's taps by shift, then box 1's, then the constant blocks
+    G.nops = 0;
+    for (int b = 0; b < G.nboxes; ++b)
+      for (int s_ = -8; s_ <= 8; ++s_)
+        for (int kh = 0; kh < k; ++kh)
+          if (box_of_cls[cls[kh]] == b && sh[kh] == s_) {
+            G.off[G.nops] = (uint32_t)b * P.box_bytes + (uint32_t)(sh[kh] - cmin[cls[kh]]) * row_bytes;
+            G.tap[G.nops] = kh * k + kw;
+            ++G.nops;
+          }
+    if (q_colsum && kw == 0) {
+      G.off[G.nops] = WG_CONST_FLAG | 0u;
+      G.tap[G.nops] = -2;
+      ++G.nops;
+    }
+    if (G.nops & 1) {
+      G.off[G.nops] = WG_CONST_FLAG | WG_SLOT;
+      G.tap[G.nops] = -1;
+      ++G.nops;
+    }
+    if (G.nops > max_ops) max_ops = G.nops;
+  }
+  const uint32_t tail = 2 * WG_SLOT + (2 * WG_MAX_STAGES + 2) * 8 + 64;
+  int stages = (int)((TM_SMEM_LIMIT - 1024 - tail) / P.stage_bytes);
   if (stages > WG_MAX_STAGES) stages = WG_MAX_STAGES;
   NSG_REQUIRE(stages >= 2, "conv_wgrad_tma: stage does not fit twice in shared memory");
   P.stages = stages;
-  const size_t smem = 1024 + (size_t)stages * stage_bytes + tail;
+  const size_t smem = 1024 + (size_t)stages * P.stage_bytes + tail;
   CUtensorMap tq, tp[4];
   if (int rc = tma::encode_nhwc64(&tq, q, cg->out_w, cg->out_h, cg->batch, TM_C, (long long)cg->out_w * TM_C,
                                   (long long)cg->out_h * cg->out_w * TM_C, P.box_w, P.box_h))
     return rc;
-  if (int rc = encode_input_maps(tp, p, cg->batch, cg->in_h, cg->in_w, P.in_stride, P.box_w, P.box_h)) return rc;
-  const dim3 grid((unsigned)gx, (unsigned)groups);
-  const int cols = P.nslots / 2 * TM_C;
+  if (int rc = encode_input_maps(tp, p, cg->batch, cg->in_h, cg->in_w, stride, P.box_w, P.box_h + halo)) return rc;
+  const dim3 grid((unsigned)wgrad_grid_x(cg, P.total_tiles), (unsigned)k);
+  const int cols = max_ops / 2 * TM_C;
   if (cols <= 64) return launch_wgrad_tma<64>(grid, smem, &tq, tp, dwp, q_colsum, P, stream);
   if (cols <= 128) return launch_wgrad_tma<128>(grid, smem, &tq, tp, dwp, q_colsum, P, stream);
-  if (cols <= 256) return launch_wgrad_tma<256>(grid, smem, &tq, tp, dwp, q_colsum, P, stream);
-  return launch_wgrad_tma<512>(grid, smem, &tq, tp, dwp, q_colsum, P, stream);
+  return launch_wgrad_tma<256>(grid, smem, &tq, tp, dwp, q_colsum, P, stream);
 }
 
 int wgrad_unpack_many(int n, const float* const* src, float* const* dw, const int* ntaps, const int* nslices,
@@ -1456,7 +1545,7 @@ c1t_wgrad_kernel(const __grid_constant__ CUtensorMap tq, const __nv_bfloat16* __
                  float* __restrict__ dw, float* __restrict__ q_colsum, const __grid_constant__ C1tWgradParams P) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sm = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  constexpr uint32_t STAGE = 3 * WG_SLOT;            // patch tile (16 taps of 64 "channels"), ones tile, Q box
+  constexpr uint32_t STAGE = 3 * C1W_SLOT;            // patch tile (16 taps of 64 "channels"), ones tile, Q box
   __shared__ __align__(8) uint64_t fullQ[WG_MAX_STAGES], fullP[WG_MAX_STAGES], empty[WG_MAX_STAGES], acc_full;
   __shared__ uint32_t tmem_slot;
 
@@ -1466,9 +1555,9 @@ c1t_wgrad_kernel(const __grid_constant__ CUtensorMap tq, const __nv_bfloat16* __
   // patch tiles start as zeros (taps 16..63 of the padded operand never change), ones tiles as bf16 1.0
   for (int s = 0; s < P.stages; ++s) {
     uint4* d0 = reinterpret_cast<uint4*>(sm + (size_t)s * STAGE);
-    for (int i = tid; i < (int)(WG_SLOT / 16); i += 192) {
+    for (int i = tid; i < (int)(C1W_SLOT / 16); i += 192) {
       d0[i] = make_uint4(0u, 0u, 0u, 0u);
-      d0[WG_SLOT / 16 + i] = make_uint4(0x3F803F80u, 0x3F803F80u, 0x3F803F80u, 0x3F803F80u);
+      d0[C1W_SLOT / 16 + i] = make_uint4(0x3F803F80u, 0x3F803F80u, 0x3F803F80u, 0x3F803F80u);
     }
   }
   fence_proxy_async_smem();
@@ -1498,8 +1587,8 @@ c1t_wgrad_kernel(const __grid_constant__ CUtensorMap tq, const __nv_bfloat16* __
           const int th = t % P.tiles_h, n = t / P.tiles_h;
           const int s = i % P.stages, round = i / P.stages;
           if (round > 0) mbar_wait(&empty[s], (uint32_t)((round - 1) & 1));
-          mbar_arrive_expect_tx(&fullQ[s], WG_SLOT);
-          tma::load_4d(sm + (size_t)s * STAGE + 2 * WG_SLOT, &tq, 0, tw * P.box_w, th * P.box_h, n, &fullQ[s]);
+          mbar_arrive_expect_tx(&fullQ[s], C1W_SLOT);
+          tma::load_4d(sm + (size_t)s * STAGE + 2 * C1W_SLOT, &tq, 0, tw * P.box_w, th * P.box_h, n, &fullQ[s]);
         }
       }
     } else if (warp == 1) {
@@ -1512,9 +1601,9 @@ c1t_wgrad_kernel(const __grid_constant__ CUtensorMap tq, const __nv_bfloat16* __
           tc_fence_after();
           const uint32_t base = smem_u32(sm + (size_t)s * STAGE);
 #pragma unroll
-          for (int ks = 0; ks < WG_KP / 16; ++ks) {
-            const uint64_t a = sw128_desc_mnmajor(base + ks * 2048, WG_SLOT);
-            const uint64_t b = sw128_desc_mnmajor(base + 2 * WG_SLOT + ks * 2048, WG_SLOT);
+          for (int ks = 0; ks < C1W_KP / 16; ++ks) {
+            const uint64_t a = sw128_desc_mnmajor(base + ks * 2048, C1W_SLOT);
+            const uint64_t b = sw128_desc_mnmajor(base + 2 * C1W_SLOT + ks * 2048, C1W_SLOT);
             umma_bf16(tmem_base, a, b, idesc, (i | ks) != 0);
           }
           umma_commit(&empty[s]);
@@ -1598,13 +1687,13 @@ int wgrad_c1_tc(const nsg_conv_geom* cg, const void* p, const void* q, float* dw
   C1tWgradParams P{};
   P.batch = cg->batch; P.in_h = cg->in_h; P.in_w = cg->in_w; P.q_h = cg->out_h; P.q_w = cg->out_w;
   P.w_tap_stride_c = cg->w_cout_stride;
-  pick_box_w(cg->out_w, WG_KP, &P.box_w, &P.box_h, &P.log2_bw);
+  pick_box_w(cg->out_w, C1W_KP, &P.box_w, &P.box_h, &P.log2_bw);
   P.tiles_w = (cg->out_w + P.box_w - 1) / P.box_w;
   P.tiles_h = (cg->out_h + P.box_h - 1) / P.box_h;
   P.total_tiles = P.tiles_w * P.tiles_h * cg->batch;
   if (P.total_tiles == 0) return NSG_OK;
   P.stages = 6;
-  const size_t smem = 1024 + (size_t)P.stages * 3 * WG_SLOT;
+  const size_t smem = 1024 + (size_t)P.stages * 3 * C1W_SLOT;
   CUtensorMap tq;
   if (int rc = tma::encode_nhwc64(&tq, q, cg->out_w, cg->out_h, cg->batch, TM_C, (long long)cg->out_w * TM_C,
                                   (long long)cg->out_h * cg->out_w * TM_C, P.box_w, P.box_h))

@@ -84,6 +84,8 @@ struct BnActArgs {
 __global__ void __launch_bounds__(256) bn_act_kernel(const BnActArgs a) {
   __shared__ float sSc[FE_C], sSh[FE_C];
   const int tid = threadIdx.x;
+  pdl_trigger();
+  pdl_wait();
   if (tid < FE_C) {
     float mu, is;
     if (a.stats) {
@@ -169,6 +171,8 @@ __global__ void __launch_bounds__(256) bn_bwd_kernel(const BnBwdArgs a) {
   __shared__ float sred[FE_C];
   __shared__ float sA[FE_C], sB[FE_C], sC[FE_C];     // dh = A*g + B*h + C per channel
   const int tid = threadIdx.x;
+  pdl_trigger();
+  pdl_wait();
   if (tid < FE_C) {
     const double sg = a.stats[tid] / a.count, sgx = a.stats[FE_C + tid] / a.count;
     const float mu = a.mean[tid], is = a.invstd[tid];
@@ -296,7 +300,7 @@ int nsg_bn_act64(const void* h, const void* res, void* out, const double* stats,
               static_cast<__nv_bfloat16*>(out), stats, count, gamma, beta, eps, momentum,
               stats ? running_mean : running_mean, stats ? running_var : running_var, num_batches_tracked,
               mean, invstd, scale, shift, relu_out, pixels};
-  bn_act_kernel<<<fe_grid(pixels), 256, 0, static_cast<cudaStream_t>(stream)>>>(a);
+  launch_pdl(bn_act_kernel, dim3(fe_grid(pixels)), dim3(256), 0, static_cast<cudaStream_t>(stream), a);
   NSG_CHECK_LAUNCH("bn_act_kernel");
   return NSG_OK;
 }
@@ -309,7 +313,7 @@ int nsg_bn_bwd64(const void* g, const void* h, void* dh, const double* stats, do
   if (pixels == 0) return NSG_OK;
   BnBwdArgs a{static_cast<const __nv_bfloat16*>(g), static_cast<const __nv_bfloat16*>(h),
               static_cast<__nv_bfloat16*>(dh), stats, count, mean, invstd, gamma, dgamma, dbeta, dbias_prev, pixels};
-  bn_bwd_kernel<<<fe_grid(pixels), 256, 0, static_cast<cudaStream_t>(stream)>>>(a);
+  launch_pdl(bn_bwd_kernel, dim3(fe_grid(pixels)), dim3(256), 0, static_cast<cudaStream_t>(stream), a);
   NSG_CHECK_LAUNCH("bn_bwd_kernel");
   return NSG_OK;
 }
