@@ -32,11 +32,15 @@ int cuda_fail(cudaError_t e, const char* what);
 int num_sms();
 
 // ---- programmatic dependent launch (PDL).  A kernel launched through launch_pdl may become resident while its
-// predecessor in the stream is still running (the predecessor's CTAs have executed pdl_trigger() or exited); it must
-// execute pdl_wait() before its first access to memory an earlier kernel wrote -- pdl_wait() returns when ALL earlier
-// work in the stream has completed and is visible, so the dependency stays exact and only launch latency and the
-// prologue (barrier / TMEM set-up, layer-constant loads) move under the predecessor's tail.  Both instructions are
-// no-ops in a kernel launched without the attribute.  g_pdl = 0 (NSG_PDL=0) turns the attribute off.
+// predecessor in the stream is still running (once every CTA of the predecessor has executed pdl_trigger() or
+// exited).  It must execute pdl_wait() before its first access to memory an earlier kernel wrote or still reads:
+// pdl_wait() returns when ALL earlier work in the stream has completed and is visible, so the dependency stays exact
+// and only the launch latency and the prologue (barrier / TMEM set-up, issue tables, layer-constant loads) move under
+// the predecessor's tail.  Discipline used by every kernel here: pdl_trigger() only AFTER pdl_wait().  Then at most
+// ONE earlier kernel (the direct predecessor) can still be running while a prologue executes, and a prologue may read
+// anything written two or more kernels back in the stream (the packed weight images of a layer: written once at the
+// start of the step).  Both instructions are no-ops in a kernel launched without the attribute.  g_pdl = 0
+// (NSG_PDL=0 / nsg_pdl(0)) turns the attribute off.
 extern int g_pdl;
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,

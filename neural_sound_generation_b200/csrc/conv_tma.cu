@@ -85,6 +85,8 @@ struct PackList {
 
 // bf16 image per tap: rows = GEMM output channel, 64 GEMM input channels along K, K-major SWIZZLE_128B
 __global__ void __launch_bounds__(256) conv_pack_many_kernel(const __grid_constant__ PackList L) {
+  pdl_wait();
+  pdl_trigger();
   int li = 0;
   while (li + 1 < L.n && (int)blockIdx.x >= L.first_block[li + 1]) ++li;
   const PackItem& p = L.it[li];
@@ -299,15 +301,10 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int stages = P.stages;
   if (tid == 0) tm_stamp(P.dbg, 0);
-  pdl_trigger();
-  pdl_wait();
 
+  // Everything up to the first pdl_wait() below is independent of the preceding kernel (common.cuh: PDL): shared-memory
+  // tables, barriers, TMEM, and the layer's weight images, which were packed at the start of the step.
   if (tid < TM_C) {
-    sPar[0 * TM_C + tid] = epi.bias ? __ldg(epi.bias + tid) : 0.f;
-    sPar[1 * TM_C + tid] = epi.mask_mode == NSG_MASK_AFFINE ? __ldg(epi.mscale + tid) : 1.f;
-    sPar[2 * TM_C + tid] = epi.mask_mode == NSG_MASK_AFFINE ? __ldg(epi.mshift + tid) : 0.f;
-    sPar[3 * TM_C + tid] = epi.stats_mode == NSG_STATS_BNBWD ? __ldg(epi.mean + tid) : 0.f;
-    sPar[4 * TM_C + tid] = epi.stats_mode == NSG_STATS_BNBWD ? __ldg(epi.invstd + tid) : 0.f;
     sStat[tid] = 0.f;
     sStat[TM_C + tid] = 0.f;
   }
@@ -362,6 +359,8 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
       mbar_arrive_expect_tx(wfull, (uint32_t)P.nw * TM_W_BYTES);
       for (int t = 0; t < P.nw; ++t)
         bulk_g2s(sW + (size_t)t * TM_W_BYTES, wimg + (size_t)t * TM_W_BYTES, TM_W_BYTES, wfull);
+      pdl_wait();                              // the activations are the preceding kernel's output
+      pdl_trigger();
       int it = 0;
       int s = 0;
       uint32_t eparity = 1;                    // first pass over the ring: slots are free (wait on the preceding phase)
@@ -453,6 +452,17 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
     const int q = warp & 3;                          // TMEM lane quarter this warp may read
     const int r = q * 32 + lane;
     const int bw = r & (P.box_w - 1), bh = r >> P.log2_bw;
+    pdl_wait();                                      // epilogue operands / coefficients come from preceding kernels
+    pdl_trigger();
+    if (tid - 64 < TM_C) {
+      const int c = tid - 64;
+      sPar[0 * TM_C + c] = epi.bias ? __ldg(epi.bias + c) : 0.f;
+      sPar[1 * TM_C + c] = epi.mask_mode == NSG_MASK_AFFINE ? __ldg(epi.mscale + c) : 1.f;
+      sPar[2 * TM_C + c] = epi.mask_mode == NSG_MASK_AFFINE ? __ldg(epi.mshift + c) : 0.f;
+      sPar[3 * TM_C + c] = epi.stats_mode == NSG_STATS_BNBWD ? __ldg(epi.mean + c) : 0.f;
+      sPar[4 * TM_C + c] = epi.stats_mode == NSG_STATS_BNBWD ? __ldg(epi.invstd + c) : 0.f;
+    }
+    named_bar(2, 256);
     for (int i = grp; i < ntiles_mine; i += 2) {
       const TmaTile tl = fetch_tile(P, sTile, i);
       const TmaPhase& ph = P.ph[tl.p];
@@ -737,7 +747,7 @@ int conv_pack_many(int n, const float* const* w, void* const* dst, const int* nt
     blocks += (ntaps[i] > 0 ? ntaps[i] : 1) * 2;
   }
   L.first_block[n] = blocks;
-  conv_pack_many_kernel<<<blocks, 256, 0, stream>>>(L);
+  launch_pdl(conv_pack_many_kernel, dim3(blocks), dim3(256), 0, stream, L);
   NSG_CHECK_LAUNCH("conv_pack_many_kernel");
   return NSG_OK;
 }
@@ -863,6 +873,8 @@ wgrad_tma_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
       const uint32_t sm0 = smem_u32(sm);
       int s = 0;
       uint32_t wait_parity = 1;            // parity of the phase BEFORE the first completion: returns at once
+      pdl_wait();                          // common.cuh (PDL): everything above is independent of earlier kernels
+      pdl_trigger();
       for (int i0 = 0; i0 < ntiles_mine; i0 += 32) {
         int local = (int)blockIdx.x + (i0 + lane) * (int)gridDim.x;
         const int tw = local % P.tiles_w;
@@ -921,6 +933,7 @@ wgrad_tma_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
       }
     } else {
       // ---------------------------------------------------------------- epilogue: thread = (block of the pair, channel a)
+      pdl_wait();
       mbar_wait(acc_full, 0);
       tc_fence_after();
       if (tid == 64) tm_stamp(stamps, 24);                   // accumulators complete
@@ -986,6 +999,8 @@ struct UnpackList {
   UnpackItem it[24];
 };
 __global__ void __launch_bounds__(256) wgrad_unpack_kernel(const __grid_constant__ UnpackList L) {
+  pdl_wait();
+  pdl_trigger();
   int li = 0;
   while (li + 1 < L.n && (int)blockIdx.x >= L.first_block[li + 1]) ++li;
   const UnpackItem& u = L.it[li];
@@ -1032,7 +1047,7 @@ static int launch_wgrad_tma(dim3 grid, size_t smem, const CUtensorMap* tq, const
     if (err != cudaSuccess) return cuda_fail(err, "cudaFuncSetAttribute(wgrad_tma_kernel)");
     configured = true;
   }
-  wgrad_tma_kernel<TMEM_COLS><<<grid, 192, smem, stream>>>(*tq, tp[0], tp[1], tp[2], tp[3], dwp, colsum, P);
+  launch_pdl(wgrad_tma_kernel<TMEM_COLS>, dim3(grid), dim3(192), smem, stream, *tq, tp[0], tp[1], tp[2], tp[3], dwp, colsum, P);
   NSG_CHECK_LAUNCH("wgrad_tma_kernel");
   return NSG_OK;
 }
@@ -1180,7 +1195,7 @@ int wgrad_unpack_many(int n, const float* const* src, float* const* dw, const in
     blocks += ntaps[i] * 16;
   }
   L.first_block[n] = blocks;
-  wgrad_unpack_kernel<<<blocks, 256, 0, stream>>>(L);
+  launch_pdl(wgrad_unpack_kernel, dim3(blocks), dim3(256), 0, stream, L);
   NSG_CHECK_LAUNCH("wgrad_unpack_kernel");
   return NSG_OK;
 }
@@ -1205,6 +1220,8 @@ struct C1tConvParams {
 __global__ void __launch_bounds__(320, 1)
 c1t_conv_kernel(const __nv_bfloat16* __restrict__ in1, const uint8_t* __restrict__ wimg,
                 __nv_bfloat16* __restrict__ out, EpiArgs epi, const __grid_constant__ C1tConvParams P) {
+  pdl_wait();
+  pdl_trigger();
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sm = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sW = sm;                                  // one 64 x 64 image (K >= 16 zero)
@@ -1347,7 +1364,7 @@ int conv_c1_tc(const nsg_conv_geom* cg, const void* in, const void* packed, cons
     configured = true;
   }
   const int grid = P.total_tiles < num_sms() ? P.total_tiles : num_sms();
-  c1t_conv_kernel<<<grid, 320, smem, stream>>>(static_cast<const __nv_bfloat16*>(in), static_cast<const uint8_t*>(packed),
+  launch_pdl(c1t_conv_kernel, dim3(grid), dim3(320), smem, stream, static_cast<const __nv_bfloat16*>(in), static_cast<const uint8_t*>(packed),
                                                static_cast<__nv_bfloat16*>(out), e, P);
   NSG_CHECK_LAUNCH("c1t_conv_kernel");
   return NSG_OK;
@@ -1380,6 +1397,8 @@ __global__ void __launch_bounds__(320, 1)
 c1t_convT_kernel(const __grid_constant__ CUtensorMap tm, const uint8_t* __restrict__ wimg,
                  __nv_bfloat16* __restrict__ out, const float* __restrict__ bias,
                  const __grid_constant__ C1tConvTParams P) {
+  pdl_wait();
+  pdl_trigger();
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sm = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sW = sm;                                              // 16 tap rows x 64 channels (rows >= 16 zero)
@@ -1524,7 +1543,7 @@ int convT_c1_tc(const nsg_conv_geom* cg, const void* in, const void* packed, con
     configured = true;
   }
   const long long grid = (long long)cg->batch * P.rblocks * P.cblocks;
-  c1t_convT_kernel<<<(unsigned)grid, 320, smem, stream>>>(tm, static_cast<const uint8_t*>(packed),
+  launch_pdl(c1t_convT_kernel, dim3((unsigned)grid), dim3(320), smem, stream, tm, static_cast<const uint8_t*>(packed),
                                                           static_cast<__nv_bfloat16*>(out), bias, P);
   NSG_CHECK_LAUNCH("c1t_convT_kernel");
   return NSG_OK;
@@ -1543,6 +1562,8 @@ struct C1tWgradParams {
 __global__ void __launch_bounds__(192, 1)
 c1t_wgrad_kernel(const __grid_constant__ CUtensorMap tq, const __nv_bfloat16* __restrict__ p1,
                  float* __restrict__ dw, float* __restrict__ q_colsum, const __grid_constant__ C1tWgradParams P) {
+  pdl_wait();
+  pdl_trigger();
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sm = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   constexpr uint32_t STAGE = 3 * C1W_SLOT;            // patch tile (16 taps of 64 "channels"), ones tile, Q box
@@ -1705,7 +1726,7 @@ int wgrad_c1_tc(const nsg_conv_geom* cg, const void* p, const void* q, float* dw
     configured = true;
   }
   const int grid = P.total_tiles < num_sms() ? P.total_tiles : num_sms();
-  c1t_wgrad_kernel<<<grid, 192, smem, stream>>>(tq, static_cast<const __nv_bfloat16*>(p), dw, q_colsum, P);
+  launch_pdl(c1t_wgrad_kernel, dim3(grid), dim3(192), smem, stream, tq, static_cast<const __nv_bfloat16*>(p), dw, q_colsum, P);
   NSG_CHECK_LAUNCH("c1t_wgrad_kernel");
   return NSG_OK;
 }

@@ -91,6 +91,8 @@ chan_reduce_kernel(const T* __restrict__ g, const T* __restrict__ h, const float
                    const float* __restrict__ invstd, const float* __restrict__ scale,
                    const float* __restrict__ shift, int relu_mask, double* __restrict__ stats,
                    float* __restrict__ out_f, long long pixels, int C) {
+  pdl_wait();
+  pdl_trigger();
   extern __shared__ float red[];  // [2][lanes][C]
   const int cq = C / VW;
   const int lanes = 256 / cq;
@@ -227,6 +229,8 @@ __global__ void relu_bwd_add_kernel(const T* __restrict__ g1, const T* __restric
 
 __global__ void tanh_bwd_kernel(const float* __restrict__ g, const float* __restrict__ y, float* __restrict__ out,
                                 long long n) {
+  pdl_wait();
+  pdl_trigger();
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
     const float t = y[i];
     out[i] = g[i] * (1.f - t * t);
@@ -237,6 +241,8 @@ __global__ void tanh_bwd_kernel(const float* __restrict__ g, const float* __rest
 __global__ void __launch_bounds__(256)
 recon_loss_kernel(const float* __restrict__ xt, const float* __restrict__ c, long long rows, int w, int wt,
                   double* loss_sum, float* __restrict__ dpre, float gscale) {
+  pdl_wait();
+  pdl_trigger();
   float acc = 0.f;
   const long long total = rows * w;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
@@ -265,6 +271,8 @@ recon_loss_kernel(const float* __restrict__ xt, const float* __restrict__ c, lon
 __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
                             float* __restrict__ v, long long n, float lr, float b1, float b2, float eps,
                             float gscale, const long long* __restrict__ step_count) {
+  pdl_wait();
+  pdl_trigger();
   __shared__ float s_step_size, s_bc2_sqrt;
   if (threadIdx.x == 0) {
     const double t = (double)(*step_count + 1);
@@ -287,7 +295,9 @@ __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, 
     v[i] = vi;
   }
 }
-__global__ void tick_kernel(long long* step_count) { *step_count += 1; }
+__global__ void tick_kernel(long long* step_count) {
+  pdl_wait();
+  pdl_trigger(); *step_count += 1; }
 
 }  // namespace nsg
 
@@ -354,10 +364,10 @@ static int launch_chan_reduce(const void* g, const void* h, const float* mean, c
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
   if (vw == 4)
-    chan_reduce_kernel<T, 4, MODE><<<(int)blocks, 256, smem, stream>>>(
+    launch_pdl(chan_reduce_kernel<T, 4, MODE>, dim3((int)blocks), dim3(256), smem, stream, 
         (const T*)g, (const T*)h, mean, invstd, scale, shift, relu_mask, stats, out_f, pixels, C);
   else
-    chan_reduce_kernel<T, 1, MODE><<<(int)blocks, 256, smem, stream>>>(
+    launch_pdl(chan_reduce_kernel<T, 1, MODE>, dim3((int)blocks), dim3(256), smem, stream, 
         (const T*)g, (const T*)h, mean, invstd, scale, shift, relu_mask, stats, out_f, pixels, C);
   NSG_CHECK_LAUNCH("chan_reduce_kernel");
   return NSG_OK;
@@ -434,7 +444,7 @@ int nsg_recon_loss(const float* x_tilde, const float* c, int batch, int h, int w
               "recon_loss: bad arguments");
   const long long rows = (long long)batch * h;
   const float gscale = (float)(2.0 / ((double)rows * w));
-  recon_loss_kernel<<<grid_for(rows * w, 256), 256, 0, (cudaStream_t)stream>>>(x_tilde, c, rows, w, wt, loss_sum,
+  launch_pdl(recon_loss_kernel, dim3(grid_for(rows * w, 256)), dim3(256), 0, (cudaStream_t)stream, x_tilde, c, rows, w, wt, loss_sum,
                                                                                  dpre, gscale);
   NSG_CHECK_LAUNCH("recon_loss_kernel");
   return NSG_OK;
@@ -443,7 +453,7 @@ int nsg_recon_loss(const float* x_tilde, const float* c, int batch, int h, int w
 int nsg_tanh_bwd(const float* g, const float* y, float* out, long long n, void* stream) {
   NSG_REQUIRE(g && y && out && n >= 0, "tanh_bwd: bad arguments");
   if (n == 0) return NSG_OK;
-  tanh_bwd_kernel<<<grid_for(n, 256), 256, 0, (cudaStream_t)stream>>>(g, y, out, n);
+  launch_pdl(tanh_bwd_kernel, dim3(grid_for(n, 256)), dim3(256), 0, (cudaStream_t)stream, g, y, out, n);
   NSG_CHECK_LAUNCH("tanh_bwd_kernel");
   return NSG_OK;
 }
@@ -452,11 +462,11 @@ int nsg_adam_step(float* params, const float* grads, float* exp_avg, float* exp_
                   float beta1, float beta2, float eps, float grad_scale, long long* step_count, void* stream) {
   NSG_REQUIRE(params && grads && exp_avg && exp_avg_sq && step_count && n >= 0, "adam_step: bad arguments");
   if (n > 0) {
-    adam_kernel<<<grid_for(n, 256), 256, 0, (cudaStream_t)stream>>>(params, grads, exp_avg, exp_avg_sq, n, lr,
+    launch_pdl(adam_kernel, dim3(grid_for(n, 256)), dim3(256), 0, (cudaStream_t)stream, params, grads, exp_avg, exp_avg_sq, n, lr,
                                                                      beta1, beta2, eps, grad_scale, step_count);
     NSG_CHECK_LAUNCH("adam_kernel");
   }
-  tick_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(step_count);
+  launch_pdl(tick_kernel, dim3(1), dim3(1), 0, (cudaStream_t)stream, step_count);
   NSG_CHECK_LAUNCH("tick_kernel");
   return NSG_OK;
 }

@@ -84,8 +84,8 @@ struct BnActArgs {
 __global__ void __launch_bounds__(256) bn_act_kernel(const BnActArgs a) {
   __shared__ float sSc[FE_C], sSh[FE_C];
   const int tid = threadIdx.x;
-  pdl_trigger();
   pdl_wait();
+  pdl_trigger();
   if (tid < FE_C) {
     float mu, is;
     if (a.stats) {
@@ -171,8 +171,8 @@ __global__ void __launch_bounds__(256) bn_bwd_kernel(const BnBwdArgs a) {
   __shared__ float sred[FE_C];
   __shared__ float sA[FE_C], sB[FE_C], sC[FE_C];     // dh = A*g + B*h + C per channel
   const int tid = threadIdx.x;
-  pdl_trigger();
   pdl_wait();
+  pdl_trigger();
   if (tid < FE_C) {
     const double sg = a.stats[tid] / a.count, sgx = a.stats[FE_C + tid] / a.count;
     const float mu = a.mean[tid], is = a.invstd[tid];
@@ -226,6 +226,8 @@ __global__ void __launch_bounds__(256) bn_bwd_kernel(const BnBwdArgs a) {
 
 __global__ void __launch_bounds__(256)
 relu_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ out, long long nvec) {
+  pdl_wait();
+  pdl_trigger();
   for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < nvec; i += (long long)gridDim.x * 256) {
     float v[8];
     fe_ld8(x + i * 8, v);
@@ -241,6 +243,8 @@ vq_bwd_stats_kernel(const __nv_bfloat16* __restrict__ g_st, const __nv_bfloat16*
                     const __nv_bfloat16* __restrict__ zq, float coef, __nv_bfloat16* __restrict__ dz,
                     const __nv_bfloat16* __restrict__ h, const float* __restrict__ mean,
                     const float* __restrict__ invstd, double* __restrict__ stats, long long pixels) {
+  pdl_wait();
+  pdl_trigger();
   __shared__ float sred[FE_C];
   const int tid = threadIdx.x;
   const int c0 = (tid & 7) * 8;
@@ -324,7 +328,7 @@ int nsg_relu64(const void* x, void* out, long long n, void* stream) {
   long long blocks = (n / 8 + 255) / 256;
   const long long cap = (long long)num_sms() * 8;
   if (blocks > cap) blocks = cap;
-  relu_kernel<<<(int)blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+  launch_pdl(relu_kernel, dim3((int)blocks), dim3(256), 0, static_cast<cudaStream_t>(stream), 
       static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(out), n / 8);
   NSG_CHECK_LAUNCH("relu_kernel");
   return NSG_OK;
@@ -335,7 +339,7 @@ int nsg_vq_bwd_stats64(const void* g_st, const void* z, const void* zq, float co
   NSG_REQUIRE(z && dz, "vq_bwd_stats64: null tensor");
   NSG_REQUIRE(!stats || (h && mean && invstd), "vq_bwd_stats64: statistics need h, mean and invstd");
   if (pixels == 0) return NSG_OK;
-  vq_bwd_stats_kernel<<<fe_grid(pixels), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+  launch_pdl(vq_bwd_stats_kernel, dim3(fe_grid(pixels)), dim3(256), 0, static_cast<cudaStream_t>(stream), 
       static_cast<const __nv_bfloat16*>(g_st), static_cast<const __nv_bfloat16*>(z),
       static_cast<const __nv_bfloat16*>(zq), coef, static_cast<__nv_bfloat16*>(dz),
       static_cast<const __nv_bfloat16*>(h), mean, invstd, stats, pixels);

@@ -34,6 +34,8 @@ __global__ void __launch_bounds__(SA_THREADS)
 scatter_agg_kernel(const T* __restrict__ rows, const T* __restrict__ sub, const long long* __restrict__ idx,
                    long long N, int K, int D, float alpha, float* __restrict__ table, float* __restrict__ counts,
                    int G, int slots, int lpr, long long rows_per_part) {
+  pdl_wait();
+  pdl_trigger();
   extern __shared__ __align__(16) uint8_t sa_smem[];
   float* tab = reinterpret_cast<float*>(sa_smem);                         // [slots][D]
   int* cnt = reinterpret_cast<int*>(tab + (size_t)slots * D);             // [slots]
@@ -200,7 +202,7 @@ int scatter_add_agg(const void* rows, const void* sub, const long long* indices,
       if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(scatter_agg_kernel)");
       configured = 200 * 1024;
     }
-    scatter_agg_kernel<T><<<pl.P * pl.G, SA_THREADS, pl.smem, stream>>>(
+    launch_pdl(scatter_agg_kernel<T>, dim3(pl.P * pl.G), dim3(SA_THREADS), pl.smem, stream, 
         (const T*)rows, (const T*)sub, indices, n, k, d, alpha, table, counts, pl.G, pl.slots, pl.lpr, pl.rows_per_part);
     NSG_CHECK_LAUNCH("scatter_agg_kernel");
     return NSG_OK;
@@ -214,6 +216,8 @@ int scatter_add_agg(const void* rows, const void* sub, const long long* indices,
 __global__ void __launch_bounds__(256)
 ema_count_kernel(const float* __restrict__ counts, float* __restrict__ ema_count, int K, float decay,
                  double* __restrict__ total) {
+  pdl_wait();
+  pdl_trigger();
   __shared__ double part[8];
   double s = 0.0;
   for (int k = threadIdx.x; k < K; k += 256) {
@@ -234,6 +238,8 @@ ema_count_kernel(const float* __restrict__ counts, float* __restrict__ ema_count
 __global__ void __launch_bounds__(256)
 ema_table_kernel(const float* __restrict__ sums, const float* __restrict__ ema_count, float* __restrict__ ema_sum,
                  float* __restrict__ codebook, int K, int D, float decay, float eps, const double* __restrict__ total) {
+  pdl_wait();
+  pdl_trigger();
   const double tot = *total;
   const long long nvec = (long long)K * D / 4;
   for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < nvec; i += (long long)gridDim.x * 256) {
@@ -261,11 +267,11 @@ extern "C" int nsg_ema_update(const float* counts, const float* sums, float* ema
   NSG_REQUIRE(k >= 1 && d >= 4 && d % 4 == 0, "ema_update: needs d %% 4 == 0 (got k=%d d=%d)", k, d);
   NSG_REQUIRE(decay >= 0.f && decay <= 1.f, "ema_update: decay %f outside [0, 1]", (double)decay);
   cudaStream_t st = (cudaStream_t)stream;
-  ema_count_kernel<<<1, 256, 0, st>>>(counts, ema_count, k, decay, scratch);
+  launch_pdl(ema_count_kernel, dim3(1), dim3(256), 0, st, counts, ema_count, k, decay, scratch);
   NSG_CHECK_LAUNCH("ema_count_kernel");
   long long blocks = ((long long)k * d / 4 + 255) / 256;
   if (blocks > (long long)num_sms() * 8) blocks = (long long)num_sms() * 8;
-  ema_table_kernel<<<(int)blocks, 256, 0, st>>>(sums, ema_count, ema_sum, codebook, k, d, decay, eps, scratch);
+  launch_pdl(ema_table_kernel, dim3((int)blocks), dim3(256), 0, st, sums, ema_count, ema_sum, codebook, k, d, decay, eps, scratch);
   NSG_CHECK_LAUNCH("ema_table_kernel");
   return NSG_OK;
 }

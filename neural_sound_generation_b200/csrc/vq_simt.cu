@@ -146,6 +146,8 @@ template <typename T, int VW>
 __global__ void scatter_add_kernel(const T* __restrict__ rows, const T* __restrict__ sub,
                                    const long long* __restrict__ idx, long long N, int K, int D, float alpha,
                                    float* __restrict__ table, float* __restrict__ counts) {
+  pdl_wait();
+  pdl_trigger();
   const int dq = D / VW;
   const long long total = N * dq;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
@@ -174,6 +176,8 @@ __global__ void scatter_add_kernel(const T* __restrict__ rows, const T* __restri
 template <typename T, int VW>
 __global__ void vq_bwd_inputs_kernel(const T* __restrict__ g, const T* __restrict__ z, const T* __restrict__ zq,
                                      float coef, T* __restrict__ dz, long long total_vec) {
+  pdl_wait();
+  pdl_trigger();
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total_vec;
        i += (long long)gridDim.x * blockDim.x) {
     const long long o = i * VW;
@@ -197,6 +201,8 @@ __global__ void vq_bwd_inputs_kernel(const T* __restrict__ g, const T* __restric
 template <typename T>
 __global__ void gather_rows_kernel(const float* __restrict__ table, const long long* __restrict__ idx, long long N,
                                    int K, int D, T* __restrict__ out) {
+  pdl_wait();
+  pdl_trigger();
   const long long total = N * D;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
@@ -213,6 +219,8 @@ template <typename T>
 __global__ void __launch_bounds__(256)
 gather_rows_vec_kernel(const float* __restrict__ table, const long long* __restrict__ idx, long long N, int K, int dq,
                        T* __restrict__ out) {
+  pdl_wait();
+  pdl_trigger();
   const long long total = N * dq;
   const long long stride = (long long)gridDim.x * 256;
   for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < total; i += stride) {
@@ -301,13 +309,13 @@ int nsg_scatter_add(const void* rows, const void* sub, const long long* indices,
       long long work = n * (d / 4);
       long long blocks = (work + threads - 1) / threads;
       if (blocks > (long long)num_sms() * 16) blocks = (long long)num_sms() * 16;
-      scatter_add_kernel<T, 4><<<(int)blocks, threads, 0, (cudaStream_t)stream>>>(
+      launch_pdl(scatter_add_kernel<T, 4>, dim3((int)blocks), dim3(threads), 0, (cudaStream_t)stream, 
           (const T*)rows, (const T*)sub, indices, n, k, d, alpha, table, counts);
     } else {
       long long work = n * d;
       long long blocks = (work + threads - 1) / threads;
       if (blocks > (long long)num_sms() * 16) blocks = (long long)num_sms() * 16;
-      scatter_add_kernel<T, 1><<<(int)blocks, threads, 0, (cudaStream_t)stream>>>(
+      launch_pdl(scatter_add_kernel<T, 1>, dim3((int)blocks), dim3(threads), 0, (cudaStream_t)stream, 
           (const T*)rows, (const T*)sub, indices, n, k, d, alpha, table, counts);
     }
     NSG_CHECK_LAUNCH("scatter_add_kernel");
@@ -323,13 +331,13 @@ int nsg_gather_rows(const float* table, const long long* indices, long long n, i
     if (d % 4 == 0 && (reinterpret_cast<uintptr_t>(table) & 15) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0) {
       long long blocks = (n * (d / 4) + 255) / 256;
       if (blocks > (long long)num_sms() * 32) blocks = (long long)num_sms() * 32;
-      gather_rows_vec_kernel<T><<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(table, indices, n, k, d / 4, (T*)out);
+      launch_pdl(gather_rows_vec_kernel<T>, dim3((int)blocks), dim3(256), 0, (cudaStream_t)stream, table, indices, n, k, d / 4, (T*)out);
       NSG_CHECK_LAUNCH("gather_rows_vec_kernel");
       return NSG_OK;
     }
     long long blocks = (n * d + 255) / 256;
     if (blocks > (long long)num_sms() * 16) blocks = (long long)num_sms() * 16;
-    gather_rows_kernel<T><<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(table, indices, n, k, d, (T*)out);
+    launch_pdl(gather_rows_kernel<T>, dim3((int)blocks), dim3(256), 0, (cudaStream_t)stream, table, indices, n, k, d, (T*)out);
     NSG_CHECK_LAUNCH("gather_rows_kernel");
     return NSG_OK;
   });
@@ -344,12 +352,12 @@ int nsg_vq_backward_inputs(const void* g_st, const void* z, const void* zq, floa
     if (n % 4 == 0) {
       long long blocks = (n / 4 + threads - 1) / threads;
       if (blocks > (long long)num_sms() * 8) blocks = (long long)num_sms() * 8;
-      vq_bwd_inputs_kernel<T, 4><<<(int)blocks, threads, 0, (cudaStream_t)stream>>>(
+      launch_pdl(vq_bwd_inputs_kernel<T, 4>, dim3((int)blocks), dim3(threads), 0, (cudaStream_t)stream, 
           (const T*)g_st, (const T*)z, (const T*)zq, coef, (T*)dz, n / 4);
     } else {
       long long blocks = (n + threads - 1) / threads;
       if (blocks > (long long)num_sms() * 8) blocks = (long long)num_sms() * 8;
-      vq_bwd_inputs_kernel<T, 1><<<(int)blocks, threads, 0, (cudaStream_t)stream>>>(
+      launch_pdl(vq_bwd_inputs_kernel<T, 1>, dim3((int)blocks), dim3(threads), 0, (cudaStream_t)stream, 
           (const T*)g_st, (const T*)z, (const T*)zq, coef, (T*)dz, n);
     }
     NSG_CHECK_LAUNCH("vq_bwd_inputs_kernel");

@@ -28,6 +28,8 @@ constexpr int VT_MAX_CHUNKS = 32;                     // K <= 8192
 // codebook fp32 (K,64) -> per chunk: swizzled bf16 hi image, swizzled bf16 lo image; |e|^2 (inf padded)
 __global__ void __launch_bounds__(256)
 vq_prep_kernel(const float* __restrict__ cb, int K, uint8_t* __restrict__ image, float* __restrict__ esq_pad) {
+  pdl_wait();
+  pdl_trigger();
   const int gid = blockIdx.x * 256 + threadIdx.x;
   const int c = gid & 7, r = (gid >> 3) & 255, ch = gid >> 11;
   const int code = ch * VT_N + r;
@@ -346,6 +348,8 @@ vq_search_res_kernel(const __grid_constant__ CUtensorMap tmz, const T* __restric
                      const uint8_t* __restrict__ image, const float* __restrict__ esq_pad, long long N, int K,
                      int nchunks, int ntiles, long long* __restrict__ indices, T* __restrict__ codes,
                      double* __restrict__ sqerr) {
+  pdl_wait();
+  pdl_trigger();
   constexpr bool kSplitZ = sizeof(T) == 4;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sm = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -694,7 +698,7 @@ int vq_forward_tc(const void* z, const float* codebook, long long n, int k, int 
   const int nchunks = (k + VT_N - 1) / VT_N;
   uint8_t* image = static_cast<uint8_t*>(ws);
   float* esq_pad = reinterpret_cast<float*>(image + (size_t)nchunks * VT_CHUNK_BYTES);
-  vq_prep_kernel<<<nchunks * 8, 256, 0, stream>>>(codebook, k, image, esq_pad);
+  launch_pdl(vq_prep_kernel, dim3(nchunks * 8), dim3(256), 0, stream, codebook, k, image, esq_pad);
   NSG_CHECK_LAUNCH("vq_prep_kernel");
   const size_t smem = vq_tc_smem_bytes(nchunks);
   return NSG_DISPATCH_DTYPE(dtype, [&]() -> int {
@@ -722,7 +726,7 @@ int vq_forward_tc(const void* z, const float* codebook, long long n, int k, int 
         if (int rc = tma::encode_nhwc64(&tmz, z, n, 1, 1, VT_D, (long long)n * VT_D, (long long)n * VT_D, VT_M, 1))
           return rc;
       }
-      vq_search_res_kernel<T><<<pgrid, VR_THREADS, vq_res_smem_bytes(nchunks), stream>>>(
+      launch_pdl(vq_search_res_kernel<T>, dim3(pgrid), dim3(VR_THREADS), vq_res_smem_bytes(nchunks), stream, 
           tmz, (const T*)z, codebook, image, esq_pad, n, k, nchunks, (int)grid, indices, (T*)codes, sqerr);
       NSG_CHECK_LAUNCH("vq_search_res_kernel");
       return NSG_OK;
