@@ -1,5 +1,6 @@
 // C-ABI plumbing: error text, device check, dispatch between the CUDA-core and tcgen05 kernels.
 #include <cstdlib>
+#include <mutex>
 #include <cstring>
 
 #include "common.cuh"
@@ -61,6 +62,48 @@ int wgrad_unpack_many(int n, const float* const* src, float* const* dw, const in
                       const long long* a_stride, const long long* b_stride, cudaStream_t stream);
 
 int g_pdl = getenv("NSG_PDL") ? atoi(getenv("NSG_PDL")) : 1;     // common.cuh: programmatic dependent launch
+
+namespace {
+bool g_notes_full = false;
+struct StreamNote {
+  cudaStream_t s;
+  bool used, packed;
+  unsigned long long since_pack;     // library launches on s after the last pack on s
+};
+StreamNote g_notes[16];
+std::mutex g_notes_mu;
+StreamNote* note_for(cudaStream_t s, bool create) {
+  for (auto& n : g_notes)
+    if (n.used && n.s == s) return &n;
+  if (!create) return nullptr;
+  for (auto& n : g_notes)
+    if (!n.used) {
+      n = StreamNote{s, true, false, 0};
+      return &n;
+    }
+  return nullptr;       // table full: callers treat the stream as never settled
+}
+}  // namespace
+void pdl_note_launch(cudaStream_t s) {
+  std::lock_guard<std::mutex> lk(g_notes_mu);
+  if (StreamNote* n = note_for(s, false)) ++n->since_pack;
+}
+void pdl_note_pack(cudaStream_t s) {
+  std::lock_guard<std::mutex> lk(g_notes_mu);
+  if (StreamNote* n = note_for(s, true)) {
+    n->packed = true;
+    n->since_pack = 0;
+  } else {
+    for (auto& m : g_notes) m.since_pack = 0, m.packed = true;     // cannot track: unsettle everything, forever safe
+    g_notes_full = true;
+  }
+}
+bool pdl_weights_settled(cudaStream_t s) {
+  std::lock_guard<std::mutex> lk(g_notes_mu);
+  if (g_notes_full) return false;
+  StreamNote* n = note_for(s, false);
+  return !n || !n->packed || n->since_pack >= 1;
+}
 }  // namespace nsg
 
 using namespace nsg;

@@ -42,6 +42,13 @@ int num_sms();
 // start of the step).  Both instructions are no-ops in a kernel launched without the attribute.  g_pdl = 0
 // (NSG_PDL=0 / nsg_pdl(0)) turns the attribute off.
 extern int g_pdl;
+// Host-side bookkeeping behind "two or more kernels back": launch_pdl notes every launch per stream, conv_pack_many
+// notes the packs; pdl_weights_settled(s) is true when at least one kernel of this library was launched on s since
+// the last pack on s (launches by anybody else are not seen, which errs on the safe side; work on other streams
+// reaches s only through events, i.e. complete).  Consumers preload their weight images above pdl_wait() only then.
+void pdl_note_launch(cudaStream_t s);
+void pdl_note_pack(cudaStream_t s);
+bool pdl_weights_settled(cudaStream_t s);
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
                               Args&&... args) {
@@ -55,6 +62,7 @@ inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
   at[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = at;
   cfg.numAttrs = g_pdl ? 1 : 0;
+  pdl_note_launch(stream);
   return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 #if defined(__CUDA_ARCH__)

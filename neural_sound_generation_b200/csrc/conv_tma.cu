@@ -62,6 +62,7 @@ struct TmaConvParams {
   uint32_t slot_bytes, row_bytes;  // one ring slot ((box_h + halo) rows); one box row (box_w pixels)
   int nphases, total_tiles, nw, stages;
   unsigned long long* dbg;       // optional clock64 stamps of CTA 0 (nsg_debug_timeline), null in production
+  int w_early;                   // 1: the weight images were written >= 2 kernels back: load them above pdl_wait()
   TmaPhase ph[4];
 };
 
@@ -356,6 +357,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
     if (lane == 0 && ntiles_mine > 0) {
+      if (!P.w_early) pdl_wait();
       mbar_arrive_expect_tx(wfull, (uint32_t)P.nw * TM_W_BYTES);
       for (int t = 0; t < P.nw; ++t)
         bulk_g2s(sW + (size_t)t * TM_W_BYTES, wimg + (size_t)t * TM_W_BYTES, TM_W_BYTES, wfull);
@@ -706,6 +708,7 @@ int conv_gemm_tma(const nsg_conv_geom* cg, const void* in, const void* packed, c
   NSG_REQUIRE(stages >= 2, "conv_gemm_tma: weights do not leave room for the activation ring");
   P.stages = stages;
   P.dbg = g_timeline;
+  P.w_early = pdl_weights_settled(stream) ? 1 : 0;
   const size_t smem = 1024 + (size_t)P.nw * TM_W_BYTES + (size_t)stages * P.slot_bytes + tail;
   CUtensorMap tm[4];
   if (int rc = encode_input_maps(tm, in, cg->batch, cg->in_h, cg->in_w, P.in_stride, P.box_w, P.box_h + halo)) return rc;
@@ -748,6 +751,7 @@ int conv_pack_many(int n, const float* const* w, void* const* dst, const int* nt
   }
   L.first_block[n] = blocks;
   launch_pdl(conv_pack_many_kernel, dim3(blocks), dim3(256), 0, stream, L);
+  pdl_note_pack(stream);
   NSG_CHECK_LAUNCH("conv_pack_many_kernel");
   return NSG_OK;
 }
@@ -1220,8 +1224,6 @@ struct C1tConvParams {
 __global__ void __launch_bounds__(320, 1)
 c1t_conv_kernel(const __nv_bfloat16* __restrict__ in1, const uint8_t* __restrict__ wimg,
                 __nv_bfloat16* __restrict__ out, EpiArgs epi, const __grid_constant__ C1tConvParams P) {
-  pdl_wait();
-  pdl_trigger();
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sm = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sW = sm;                                  // one 64 x 64 image (K >= 16 zero)
@@ -1235,12 +1237,7 @@ c1t_conv_kernel(const __nv_bfloat16* __restrict__ in1, const uint8_t* __restrict
   uint64_t* acc_full = bars + 3;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  if (tid < TM_C) {
-    sPar[0 * TM_C + tid] = epi.bias ? __ldg(epi.bias + tid) : 0.f;
-    sPar[1 * TM_C + tid] = epi.mask_mode == NSG_MASK_AFFINE ? __ldg(epi.mscale + tid) : 1.f;
-    sPar[2 * TM_C + tid] = epi.mask_mode == NSG_MASK_AFFINE ? __ldg(epi.mshift + tid) : 0.f;
-    sPar[3 * TM_C + tid] = epi.stats_mode == NSG_STATS_BNBWD ? __ldg(epi.mean + tid) : 0.f;
-    sPar[4 * TM_C + tid] = epi.stats_mode == NSG_STATS_BNBWD ? __ldg(epi.invstd + tid) : 0.f;
+  if (tid < TM_C) {          // (set-up above the first pdl_wait() touches no global memory: common.cuh, PDL)
     sStat[tid] = 0.f;
     sStat[TM_C + tid] = 0.f;
   }
@@ -1260,6 +1257,8 @@ c1t_conv_kernel(const __nv_bfloat16* __restrict__ in1, const uint8_t* __restrict
 
   if (warp == 0) {
     if (lane == 0 && ntiles_mine > 0) {
+      pdl_wait();            // encoder.0's image is written by the kernel right before this one
+      pdl_trigger();
       mbar_arrive_expect_tx(wfull, TM_W_BYTES);
       bulk_g2s(sW, wimg, TM_W_BYTES, wfull);
     }
@@ -1282,6 +1281,17 @@ c1t_conv_kernel(const __nv_bfloat16* __restrict__ in1, const uint8_t* __restrict
     const int bw = r & (P.box_w - 1), bh = r >> P.log2_bw;
     uint8_t* myA = sA + (size_t)grp * TM_A_BYTES;
     const unsigned short* in16 = reinterpret_cast<const unsigned short*>(in1);
+    pdl_wait();
+    pdl_trigger();
+    if (tid - 64 < TM_C) {
+      const int c = tid - 64;
+      sPar[0 * TM_C + c] = epi.bias ? __ldg(epi.bias + c) : 0.f;
+      sPar[1 * TM_C + c] = epi.mask_mode == NSG_MASK_AFFINE ? __ldg(epi.mscale + c) : 1.f;
+      sPar[2 * TM_C + c] = epi.mask_mode == NSG_MASK_AFFINE ? __ldg(epi.mshift + c) : 0.f;
+      sPar[3 * TM_C + c] = epi.stats_mode == NSG_STATS_BNBWD ? __ldg(epi.mean + c) : 0.f;
+      sPar[4 * TM_C + c] = epi.stats_mode == NSG_STATS_BNBWD ? __ldg(epi.invstd + c) : 0.f;
+    }
+    named_bar(2, 256);
     for (int i = grp; i < ntiles_mine; i += 2) {
       int t = (int)blockIdx.x + i * (int)gridDim.x;
       const int tw = t % P.tiles_w;
@@ -1397,8 +1407,6 @@ __global__ void __launch_bounds__(320, 1)
 c1t_convT_kernel(const __grid_constant__ CUtensorMap tm, const uint8_t* __restrict__ wimg,
                  __nv_bfloat16* __restrict__ out, const float* __restrict__ bias,
                  const __grid_constant__ C1tConvTParams P) {
-  pdl_wait();
-  pdl_trigger();
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sm = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sW = sm;                                              // 16 tap rows x 64 channels (rows >= 16 zero)
@@ -1435,6 +1443,8 @@ c1t_convT_kernel(const __grid_constant__ CUtensorMap tm, const uint8_t* __restri
 
   if (warp == 0) {
     if (lane == 0) {
+      pdl_wait();            // set-up above touches no global memory (common.cuh, PDL)
+      pdl_trigger();
       mbar_arrive_expect_tx(&wfull, TM_W_BYTES);
       bulk_g2s(sW, wimg, TM_W_BYTES, &wfull);
       for (int b = 0; b < nboxes; ++b) {
@@ -1461,6 +1471,7 @@ c1t_convT_kernel(const __grid_constant__ CUtensorMap tm, const uint8_t* __restri
       }
     }
   } else {
+    pdl_wait();              // bias read, output writes
     if (warp < 6) {
       // tap products of box b, pixel px = q*32 + lane: TMEM -> sP[b][t][px]
       const int q = warp & 3;
@@ -1562,8 +1573,6 @@ struct C1tWgradParams {
 __global__ void __launch_bounds__(192, 1)
 c1t_wgrad_kernel(const __grid_constant__ CUtensorMap tq, const __nv_bfloat16* __restrict__ p1,
                  float* __restrict__ dw, float* __restrict__ q_colsum, const __grid_constant__ C1tWgradParams P) {
-  pdl_wait();
-  pdl_trigger();
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sm = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   constexpr uint32_t STAGE = 3 * C1W_SLOT;            // patch tile (16 taps of 64 "channels"), ones tile, Q box
@@ -1601,6 +1610,8 @@ c1t_wgrad_kernel(const __grid_constant__ CUtensorMap tq, const __nv_bfloat16* __
   if (ntiles_mine > 0) {
     if (warp == 0) {
       if (lane == 0) {
+        pdl_wait();          // set-up above touches no global memory (common.cuh, PDL)
+        pdl_trigger();
         for (int i = 0; i < ntiles_mine; ++i) {
           int t = (int)blockIdx.x + i * (int)gridDim.x;
           const int tw = t % P.tiles_w;
@@ -1637,6 +1648,7 @@ c1t_wgrad_kernel(const __grid_constant__ CUtensorMap tq, const __nv_bfloat16* __
       const int px = t128 & 63, half = t128 >> 6;
       const int bw = px & (P.box_w - 1), bh = px >> P.log2_bw;
       const unsigned short* in16 = reinterpret_cast<const unsigned short*>(p1);
+      pdl_wait();
       for (int i = 0; i < ntiles_mine; ++i) {
         int t = (int)blockIdx.x + i * (int)gridDim.x;
         const int tw = t % P.tiles_w;

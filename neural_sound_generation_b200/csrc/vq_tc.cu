@@ -348,8 +348,6 @@ vq_search_res_kernel(const __grid_constant__ CUtensorMap tmz, const T* __restric
                      const uint8_t* __restrict__ image, const float* __restrict__ esq_pad, long long N, int K,
                      int nchunks, int ntiles, long long* __restrict__ indices, T* __restrict__ codes,
                      double* __restrict__ sqerr) {
-  pdl_wait();
-  pdl_trigger();
   constexpr bool kSplitZ = sizeof(T) == 4;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sm = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -384,6 +382,8 @@ vq_search_res_kernel(const __grid_constant__ CUtensorMap tmz, const T* __restric
     if (!kSplitZ) tma::prefetch_desc(&tmz);
   }
   if (warp == 8) tmem_alloc<512>(tmem_slot);
+  pdl_wait();                // barriers / TMEM above are independent of earlier kernels (common.cuh, PDL)
+  pdl_trigger();
   for (int i = tid; i < nchunks * VT_N; i += VR_THREADS) esq_s[i] = __ldg(esq_pad + i);
   tc_fence_before();
   __syncthreads();

@@ -312,3 +312,40 @@ def test_c1_tensor_core_kernels(case):
     torch.cuda.synchronize()
     assert relerr(nchw(g.float()), gref) < OUT_TOL, 'c1 dgrad'
     assert relerr(st, torch.cat([gref.sum((0, 2, 3)), (gref * xhat).sum((0, 2, 3))])) < 5e-4
+
+
+def test_programmatic_dependent_launch_keeps_results_and_orders_repacked_weights():
+    """nsg_pdl (common.cuh): kernels may start their prologue under the predecessor's tail.  Results must be identical
+    with the attribute on and off, including when a layer's weight image is re-packed by the kernel right before the
+    convolution that consumes it (the one case where the early weight load has to be suppressed), and when the
+    activations are produced by the kernel right before."""
+    from neural_sound_generation_b200 import _cabi
+    lib = _cabi.load()
+    B, C, H, W, k = 4, 64, 20, 64, 3
+    fwd, dgr, wgr, OH, OW = _geoms(B, H, W, k, 1, 1, False)
+    g = torch.Generator(device='cpu').manual_seed(3)
+    ws = [(torch.randn(C, C, k, k, generator=g) * 0.04).to(DEV) for _ in range(6)]
+    x0 = torch.randn(B, H, W, C, generator=g).to(DEV).to(BF)
+    img = torch.empty(k * k * 8192, dtype=torch.uint8, device=DEV)
+    results = {}
+    prev = lib.nsg_pdl(-1)
+    try:
+        for mode in (0, 1):
+            lib.nsg_pdl(mode)
+            outs = []
+            a, b = x0.clone(), torch.empty_like(x0)
+            for it in range(24):
+                w = ws[it % len(ws)]
+                # same image buffer re-packed every iteration, consumed by the very next launch
+                ops.conv_pack_many([(w, img, k * k, fwd.w_cin_stride, fwd.w_cout_stride)])
+                ops.conv_gemm_tma(fwd, a, img, b, relu_out=True)
+                ops.conv_gemm_tma(fwd, b, img, a)                    # chained: input written by the previous launch
+                if it % 8 == 7:
+                    outs.append(a.clone())
+            torch.cuda.synchronize()
+            results[mode] = outs
+    finally:
+        lib.nsg_pdl(prev)
+    for o0, o1 in zip(results[0], results[1]):
+        assert torch.isfinite(o0.float()).all()
+        assert torch.equal(o0, o1)
