@@ -268,6 +268,14 @@ int nsg_vq_backward_inputs(const void* g_st, const void* z, const void* zq, floa
 int nsg_recon_loss(const float* x_tilde, const float* c, int batch, int h, int w, int wt, double* loss_sum,
                    float* dpre, void* stream);
 
+/* The same for a bf16 x_tilde (the TMA engine's decoder output), with the conversions around it folded in: dpre
+ * (nullable) is written as bf16, x_tilde_f32 (nullable, (B,H,wt)) receives x_tilde widened to fp32. */
+int nsg_recon_loss_bf16(const void* x_tilde, const float* c, int batch, int h, int w, int wt, double* loss_sum,
+                        void* dpre, float* x_tilde_f32, void* stream);
+/* losses3 = [sums[0]*recon_scale, sums[1]*vq_scale, sums[1]*vq_scale]: loss_recons, loss_vq, loss_commit
+ * (train.py:129-134; the last two are the same number before beta) from the accumulated squared-error sums */
+int nsg_loss_finalize(const double* sums, double recon_scale, double vq_scale, double* losses3, void* stream);
+
 /* out = g * (1 - y^2): gradient through the decoder's final nn.Tanh (models.py:183), fp32 */
 int nsg_tanh_bwd(const float* g, const float* y, float* out, long long n, void* stream);
 

@@ -23,7 +23,7 @@ EXPORTS = [
     'nsg_adam_step', 'nsg_tanh_bwd', 'nsg_gather_rows', 'nsg_vq_workspace_bytes',
     'nsg_conv_pack_bytes', 'nsg_conv_pack_weights', 'nsg_conv_gemm_tc', 'nsg_conv_wgrad_tc',
     'nsg_conv_pack_many', 'nsg_conv_gemm_tma', 'nsg_conv_wgrad_tma', 'nsg_wgrad_unpack_many',
-    'nsg_conv_wgrad_slices', 'nsg_conv_wgrad_tma_sliced', 'nsg_pdl',
+    'nsg_conv_wgrad_slices', 'nsg_conv_wgrad_tma_sliced', 'nsg_pdl', 'nsg_recon_loss_bf16', 'nsg_loss_finalize',
     'nsg_bn_act64', 'nsg_bn_bwd64', 'nsg_relu64', 'nsg_vq_bwd_stats64', 'nsg_debug_timeline',
     'nsg_c1_conv_tc', 'nsg_c1_convT_tc', 'nsg_c1_wgrad_tc', 'nsg_scatter_mode', 'nsg_ema_update', 'nsg_vq_resident',
 ]
@@ -84,6 +84,8 @@ def load():
     lib.nsg_conv_wgrad_tma.argtypes = [C.POINTER(ConvGeom), vp, vp, vp, vp, vp]
     lib.nsg_wgrad_unpack_many.argtypes = [i, vp, vp, vp, vp, vp, vp, vp]
     lib.nsg_pdl.argtypes = [i]
+    lib.nsg_recon_loss_bf16.argtypes = [vp, vp, i, i, i, i, vp, vp, vp, vp]
+    lib.nsg_loss_finalize.argtypes = [vp, C.c_double, C.c_double, vp, vp]
     lib.nsg_conv_wgrad_slices.argtypes = [C.POINTER(ConvGeom)]
     lib.nsg_conv_wgrad_tma_sliced.argtypes = [C.POINTER(ConvGeom), vp, vp, vp, vp, vp]
     lib.nsg_bn_act64.argtypes = [vp, vp, vp, vp, d, vp, vp, f, f, vp, vp, vp, vp, vp, vp, vp, i, ll, vp]

@@ -267,6 +267,49 @@ recon_loss_kernel(const float* __restrict__ xt, const float* __restrict__ c, lon
   }
 }
 
+// bf16 decoder output: the same loss with the two dtype conversions around it folded in (x_tilde widened to fp32 for
+// the caller, dpre narrowed to the bf16 the decoder's backward kernels read) -- one pass instead of three
+__global__ void __launch_bounds__(256)
+recon_loss_bf16_kernel(const __nv_bfloat16* __restrict__ xt, const float* __restrict__ c, long long rows, int w, int wt,
+                       double* loss_sum, __nv_bfloat16* __restrict__ dpre, float* __restrict__ xt32, float gscale) {
+  pdl_wait();
+  pdl_trigger();
+  float acc = 0.f;
+  const long long total = rows * w;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / w;
+    const int wi = (int)(i % w);
+    const float t = __ldg(c + i);
+    float x = 0.f;
+    if (wi < wt) {
+      x = __bfloat162float(xt[r * wt + wi]);
+      if (xt32) xt32[r * wt + wi] = x;
+    }
+    const float d = x - t;
+    acc = fmaf(d, d, acc);
+    if (dpre && wi < wt) dpre[r * wt + wi] = __float2bfloat16_rn(gscale * d * (1.f - x * x));
+  }
+  __shared__ float part[8];
+  acc = warp_sum(acc);
+  if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double s = 0.0;
+    for (int i = 0; i < 8; ++i) s += (double)part[i];
+    atomicAdd(loss_sum, s);
+  }
+}
+
+// losses[0] = sums[0] * a, losses[1] = losses[2] = sums[1] * b   (train.py:129-134: recon, vq, commit share one sum)
+__global__ void loss_finalize_kernel(const double* __restrict__ sums, double a, double b, double* __restrict__ out) {
+  pdl_wait();
+  pdl_trigger();
+  if (threadIdx.x == 0) out[0] = sums[0] * a;
+  if (threadIdx.x == 1) out[1] = sums[1] * b;
+  if (threadIdx.x == 2) out[2] = sums[1] * b;
+}
+
 // ---------------------------------------------------------------- Adam (torch.optim.Adam single-tensor maths)
 __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
                             float* __restrict__ v, long long n, float lr, float b1, float b2, float eps,
@@ -447,6 +490,27 @@ int nsg_recon_loss(const float* x_tilde, const float* c, int batch, int h, int w
   launch_pdl(recon_loss_kernel, dim3(grid_for(rows * w, 256)), dim3(256), 0, (cudaStream_t)stream, x_tilde, c, rows, w, wt, loss_sum,
                                                                                  dpre, gscale);
   NSG_CHECK_LAUNCH("recon_loss_kernel");
+  return NSG_OK;
+}
+
+int nsg_recon_loss_bf16(const void* x_tilde, const float* c, int batch, int h, int w, int wt, double* loss_sum,
+                        void* dpre, float* x_tilde_f32, void* stream) {
+  NSG_REQUIRE(x_tilde && c && loss_sum && batch >= 0 && h >= 0 && w >= 0 && wt >= 0 && wt <= w,
+              "recon_loss_bf16: bad arguments");
+  const long long rows = (long long)batch * h;
+  if (rows * w == 0) return NSG_OK;
+  const float gscale = (float)(2.0 / ((double)rows * w));
+  launch_pdl(recon_loss_bf16_kernel, dim3(grid_for(rows * w, 256)), dim3(256), 0, (cudaStream_t)stream,
+             static_cast<const __nv_bfloat16*>(x_tilde), c, rows, w, wt, loss_sum, static_cast<__nv_bfloat16*>(dpre),
+             x_tilde_f32, gscale);
+  NSG_CHECK_LAUNCH("recon_loss_bf16_kernel");
+  return NSG_OK;
+}
+
+int nsg_loss_finalize(const double* sums, double recon_scale, double vq_scale, double* losses3, void* stream) {
+  NSG_REQUIRE(sums && losses3, "loss_finalize: null pointer");
+  launch_pdl(loss_finalize_kernel, dim3(1), dim3(32), 0, (cudaStream_t)stream, sums, recon_scale, vq_scale, losses3);
+  NSG_CHECK_LAUNCH("loss_finalize_kernel");
   return NSG_OK;
 }
 

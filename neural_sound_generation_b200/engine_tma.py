@@ -55,6 +55,8 @@ class EngineTMA(object):
         # B200 (configs[1], same box): the sliced kernels are 1-2 us faster each in isolation, but their 58 MB of
         # partials push activations out of L2 and the step is slower, 0.824 vs 0.807 ms -- atomics stay the default.
         self.wgrad_sliced = os.environ.get('NSG_WGRAD_SLICED', '0') == '1'
+        self.zbuf = None            # begin(fused=True): the step's accumulators, one allocation, one fill per step
+        self.dwa_in_zbuf = False
         self.dp = None              # dist.DataParallel: cross-rank BatchNorm statistics / bucketed gradient all-reduce
 
     # ------------------------------------------------------------------ packed images
@@ -69,7 +71,13 @@ class EngineTMA(object):
         self.layers = {}
         self.pack_items, self.unpack_items = [], []
         # wgrad_sliced = False: one packed image per layer, CTAs meet in it through vector atomics, cleared per step
-        self.dwa = torch.zeros(ntaps_total * D * D, dtype=torch.float32, device=dev)
+        if self.zbuf is not None and self.zbuf.device == dev:      # fused step: cleared with the step's other sums
+            self.dwa = self.zbuf[self.zbuf.numel() - ntaps_total * D * D * 4:].view(torch.float32)
+            self.dwa.zero_()
+            self.dwa_in_zbuf = True
+        else:
+            self.dwa = torch.zeros(ntaps_total * D * D, dtype=torch.float32, device=dev)
+            self.dwa_in_zbuf = False
         self.dwa_split = 0          # first element of the decoder layers' images (they are laid out last)
         ow, og = 0, 0
         for name, k, s, p, tr in TC_LAYERS:
@@ -132,13 +140,29 @@ class EngineTMA(object):
         return dict(coef=(co[0], co[1], co[2], co[3]), mean=co[0], invstd=co[1], fstats=ctx.stats[i, 0],
                     bstats=ctx.stats[i, 1])
 
-    def begin(self, x_nhwc, training):
+    def begin(self, x_nhwc, training, fused=False):
         ctx = Ctx()
         ctx.training = training
         ctx.saved = {}
         dev = x_nhwc.device
         ctx.coef = torch.empty((len(BN_LAYERS), 4, self.dim), dtype=torch.float32, device=dev)
-        ctx.stats = torch.zeros((len(BN_LAYERS), 2, 2 * self.dim), dtype=torch.float64, device=dev)
+        nst = len(BN_LAYERS) * 2 * 2 * self.dim
+        if fused:
+            # everything the step accumulates into lives in ONE buffer cleared by ONE fill at the start of the step:
+            # BatchNorm statistic sums (fp64), the two squared-error sums (fp64), the packed weight-gradient images
+            if self.zbuf is None or self.zbuf.device != dev:
+                nd = sum(k * k for _, k, *_ in TC_LAYERS) * self.dim * self.dim
+                self.zbuf = torch.zeros((nst + 2) * 8 + nd * 4, dtype=torch.uint8, device=dev)
+                self._key = None                    # the layers' dwa views are re-made by _prepare
+            else:
+                self.zbuf.zero_()
+            f64 = self.zbuf[:(nst + 2) * 8].view(torch.float64)
+            ctx.stats = f64[:nst].view(len(BN_LAYERS), 2, 2 * self.dim)
+            ctx.sums = f64[nst:nst + 2]
+        else:
+            ctx.stats = torch.zeros((len(BN_LAYERS), 2, 2 * self.dim), dtype=torch.float64, device=dev)
+            ctx.sums = None
+        ctx.fused = fused
         ctx.packed = False
         ctx.keep = []               # tensors in use on the side stream (kept alive until the join)
         ctx.forked = False
@@ -406,7 +430,7 @@ class EngineTMA(object):
         for L in self.layers.values():      # a layer's partials are consumed once
             if part is None or L.name.startswith(part + '.'):
                 L.nslices = 0
-        if not self.wgrad_sliced:
+        if not self.wgrad_sliced and not self.dwa_in_zbuf:
             if part is None:
                 self.dwa.zero_()
             elif part == 'decoder':

@@ -305,22 +305,31 @@ class VQVAE(nn.Module):
         b, _, h, w = c.shape
         c3 = c.detach().float().contiguous().view(b, h, w)
         x = c3.view(b, h, w, 1)
-        ectx = eng.begin(x, self.training)
+        if self.conv_impl == 2:
+            ectx = eng.begin(x, self.training, fused=True)
+            sums = ectx.sums                                                # cleared with the step's other sums
+        else:
+            ectx = eng.begin(x, self.training)
+            sums = torch.zeros(2, dtype=torch.float64, device=x.device)    # [recon sq sum, vq sq sum]
         z_e = eng.encoder_fwd(ectx, P, Bufs, x if self.act_dtype == torch.float32 else x.to(self.act_dtype))
-        sums = torch.zeros(2, dtype=torch.float64, device=x.device)        # [recon sq sum, vq sq sum]
         cb = P['codebook.embedding.weight']
         idx, z_q = eng.quantize(z_e, cb, want_codes=True, sqerr=sums[1:2])
         xt = eng.decoder_fwd(ectx, P, Bufs, z_q)
-        xt32 = xt if xt.dtype == torch.float32 else xt.float()
-        wt = xt32.shape[2]
-        dpre = torch.empty((b, h, wt), dtype=torch.float32, device=x.device)
-        ops.recon_loss(xt32.view(b, h, wt), c3, sums[0:1], dpre)
+        wt = xt.shape[2]
+        if xt.dtype == torch.bfloat16:
+            # loss + d loss / d pre-tanh (bf16, what decoder_bwd reads) + the fp32 x_tilde handed back, one kernel
+            xt32 = torch.empty(xt.shape, dtype=torch.float32, device=x.device)
+            dpre = torch.empty((b, h, wt), dtype=torch.bfloat16, device=x.device)
+            ops.recon_loss_bf16(xt.view(b, h, wt), c3, sums[0:1], dpre, xt32.view(b, h, wt))
+        else:
+            xt32 = xt if xt.dtype == torch.float32 else xt.float()
+            dpre = torch.empty((b, h, wt), dtype=torch.float32, device=x.device)
+            ops.recon_loss(xt32.view(b, h, wt), c3, sums[0:1], dpre)
         g_st = eng.decoder_bwd(ectx, P, G, dpre.view(b, h, wt, 1))
         dp = getattr(eng, 'dp', None)
         if dp is not None:
             # decoder bucket: unpack + all-reduce beside the encoder backward; the loss scalars ride in its padding
-            l_now = torch.stack([sums[0] * (1.0 / (b * h * w)), sums[1] * (1.0 / z_e.numel()),
-                                 sums[1] * (1.0 / z_e.numel())])
+            l_now = ops.loss_finalize(sums, 1.0 / (b * h * w), 1.0 / z_e.numel())
             dp.decoder_done(eng, ectx, G, self._flat, losses=l_now)
         n_lat = z_e.numel()
         dz = eng.bottleneck_bwd(ectx, g_st, z_e, z_q, 2.0 * beta / n_lat)  # ST clone + beta * d commit / d z_e
@@ -330,9 +339,7 @@ class VQVAE(nn.Module):
             dp.finish(eng, ectx, G, self._flat)
         else:
             eng.finish_backward(ectx, G)
-        # (python-scalar multiplies keep this CUDA-graph capturable: no host tensor is created)
-        l_rec, l_vq = sums[0] * (1.0 / (b * h * w)), sums[1] * (1.0 / z_e.numel())
-        losses = torch.stack([l_rec, l_vq, l_vq])
+        losses = ops.loss_finalize(sums, 1.0 / (b * h * w), 1.0 / z_e.numel())
         return losses, (_nchw_view(xt32), _nchw_view(z_e), _nchw_view(z_q), idx)
 
 

@@ -264,6 +264,41 @@ def recon_loss(x_tilde, c, loss_sum, dpre=None):
     launch_count += 1
 
 
+def recon_loss_bf16(x_tilde, c, loss_sum, dpre=None, x_tilde_f32=None):
+    """x_tilde (B, H, Wt) bf16, c (B, H, W) fp32; dpre (bf16) and x_tilde_f32 (fp32) optional outputs (B, H, Wt)."""
+    global launch_count
+    A.require_device()
+    _cuda(x_tilde, c, loss_sum, dpre, x_tilde_f32)
+    _bf16(x_tilde, dpre)
+    _contig(x_tilde, 'x_tilde')
+    _contig(c, 'target mel')
+    if c.dtype != torch.float32 or loss_sum.dtype != torch.float64:
+        raise TypeError('recon_loss_bf16: c must be fp32 and loss_sum fp64')
+    if x_tilde_f32 is not None and (x_tilde_f32.dtype != torch.float32 or not x_tilde_f32.is_contiguous()):
+        raise TypeError('recon_loss_bf16: x_tilde_f32 must be a contiguous fp32 tensor')
+    b, h, w = c.shape
+    wt = x_tilde.shape[-1]
+    rc = A.load().nsg_recon_loss_bf16(A.ptr(x_tilde), A.ptr(c), b, h, w, wt, A.ptr(loss_sum), A.ptr(dpre),
+                                      A.ptr(x_tilde_f32), A.stream_ptr())
+    A.check(rc, 'nsg_recon_loss_bf16')
+    launch_count += 1
+
+
+def loss_finalize(sums, recon_scale, vq_scale, out=None):
+    """[sums[0]*recon_scale, sums[1]*vq_scale, sums[1]*vq_scale] as one fp64 tensor (train.py:129-134)."""
+    global launch_count
+    A.require_device()
+    if out is None:
+        out = torch.empty(3, dtype=torch.float64, device=sums.device)
+    _cuda(sums, out)
+    if sums.dtype != torch.float64 or out.dtype != torch.float64 or sums.numel() < 2 or out.numel() < 3:
+        raise TypeError('loss_finalize: fp64 tensors of >= 2 and >= 3 elements')
+    rc = A.load().nsg_loss_finalize(A.ptr(sums), float(recon_scale), float(vq_scale), A.ptr(out), A.stream_ptr())
+    A.check(rc, 'nsg_loss_finalize')
+    launch_count += 1
+    return out
+
+
 def adam_step(params, grads, exp_avg, exp_avg_sq, step_count, lr, beta1=0.9, beta2=0.999, eps=1e-8,
               grad_scale=1.0):
     global launch_count
