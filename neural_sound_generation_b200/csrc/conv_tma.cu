@@ -1010,6 +1010,12 @@ __global__ void __launch_bounds__(256) wgrad_unpack_kernel(const __grid_constant
   const UnpackItem& u = L.it[li];
   // block = 256 consecutive elements of one tap image = 64 float4 columns; thread = (column, slice residue mod 4).
   // Slices are summed in a fixed order (residue classes, then the four classes): no dependence on CTA timing.
+  if (u.nslices == 1) {      // one image (the atomics form): a plain strided read-modify-write, nothing to reduce
+    const int gid = ((int)blockIdx.x - L.first_block[li]) * 256 + threadIdx.x;
+    const int b = gid & 63, a = (gid >> 6) & 63, t = gid >> 12;
+    if (t < u.ntaps) u.dw[t + (long long)a * u.a_stride + (long long)b * u.b_stride] += __ldg(u.src + gid);
+    return;
+  }
   __shared__ float4 part[4][64];
   const int col = threadIdx.x & 63, sg = threadIdx.x >> 6;
   const int e0 = ((int)blockIdx.x - L.first_block[li]) * 256 + col * 4;           // (t, a, b), b fastest

@@ -13,7 +13,7 @@ timeout 300 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/$
 timeout 200 python tools/bench_infer.py > gpurun_out/${TAG}_infer.log 2>&1; echo "infer exit $?"; tail -n 1 gpurun_out/${TAG}_infer.log | cut -c1-1200
 timeout 200 python tools/bench_vq.py --full > gpurun_out/${TAG}_vq.log 2>&1; echo "vq exit $?"
 timeout 200 python tools/bench_ops.py > gpurun_out/${TAG}_ops.log 2>&1; echo "ops exit $?"
-timeout 100 python tools/timeline_conv.py > gpurun_out/${TAG}_timeline.log 2>&1
+timeout 100 python tools/timeline_conv.py > gpurun_out/${TAG}_timeline.log 2>&1; timeout 100 python tools/timeline_wgrad.py > gpurun_out/${TAG}_timeline_wgrad.log 2>&1
 timeout 300 python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/${TAG}_plain.log 2>&1 &&
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv \
    --log-file gpurun_out/${TAG}_launches.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/${TAG}_ncu.log 2>&1
