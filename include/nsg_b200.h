@@ -280,10 +280,12 @@ int nsg_loss_finalize(const double* sums, double recon_scale, double vq_scale, d
 int nsg_tanh_bwd(const float* g, const float* y, float* out, long long n, void* stream);
 
 /* ---------------------------------------------------------------- optimiser (torch.optim.Adam, main.py:124) */
-/* one Adam step over a flat fp32 buffer.  step_count is a device scalar (incremented by the kernel grid's
- * first block AFTER use, so graphs replay correctly).  grad_scale multiplies grads (DP averaging). */
-int nsg_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, long long n, float lr,
-                  float beta1, float beta2, float eps, float grad_scale, long long* step_count, void* stream);
+/* one Adam step over a flat fp32 buffer.  step_count is a device scalar (incremented by a second one-thread launch
+ * AFTER use, so graphs replay correctly).  grad_scale multiplies grads (DP averaging).  zero_grads != 0 clears each
+ * gradient after it has been used (the next step's optimizer.zero_grad(), main.py/train.py:116, for free). */
+int nsg_adam_step(float* params, float* grads, float* exp_avg, float* exp_avg_sq, long long n, float lr,
+                  float beta1, float beta2, float eps, float grad_scale, long long* step_count, int zero_grads,
+                  void* stream);
 
 #ifdef __cplusplus
 }

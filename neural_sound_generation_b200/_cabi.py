@@ -109,7 +109,7 @@ def load():
     lib.nsg_vq_resident.argtypes = [i]
     lib.nsg_ema_update.argtypes = [vp, vp, vp, vp, vp, i, i, f, f, vp, vp]
     lib.nsg_tanh_bwd.argtypes = [vp, vp, vp, ll, vp]
-    lib.nsg_adam_step.argtypes = [vp, vp, vp, vp, ll, f, f, f, f, f, vp, vp]
+    lib.nsg_adam_step.argtypes = [vp, vp, vp, vp, ll, f, f, f, f, f, vp, i, vp]
     for name in EXPORTS:
         fn = getattr(lib, name)
         if name not in ('nsg_version', 'nsg_last_error'):

@@ -125,6 +125,16 @@ __device__ __forceinline__ void st8bf(__nv_bfloat16* p, const float* v) {
   *reinterpret_cast<uint4*>(p) =
       make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
 }
+// 16 bf16 = one whole 32-byte L2 sector per store instruction.  With 16-byte stores every sector of the output is
+// written in two partial pieces, and the L2 fetched it from DRAM to merge them: the 1 -> 64 forward read 42 MB of DRAM
+// against 2.6 MB of algorithmic input (ncu, profiles/r1_final_ncu_full_summary.txt).  p must be 32-byte aligned.
+__device__ __forceinline__ void st16bf(__nv_bfloat16* p, const float* v) {
+  asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p), "r"(pack_bf16(v[0], v[1])),
+               "r"(pack_bf16(v[2], v[3])), "r"(pack_bf16(v[4], v[5])), "r"(pack_bf16(v[6], v[7])),
+               "r"(pack_bf16(v[8], v[9])), "r"(pack_bf16(v[10], v[11])), "r"(pack_bf16(v[12], v[13])),
+               "r"(pack_bf16(v[14], v[15]))
+               : "memory");
+}
 // v[i] of lane l -> sum over lanes of v[lane] (32x32 transpose-reduce); v is destroyed
 __device__ __forceinline__ float transpose_sum32(float (&v)[32], int lane) {
 #pragma unroll
@@ -211,7 +221,7 @@ __device__ __forceinline__ void epi_row(EpiOperands& E, const EpiArgs& epi, cons
         }
         if (valid) {
 #pragma unroll
-          for (int g8 = 0; g8 < 4; ++g8) st8bf(out + o + ch0 + g8 * 8, &x[g8 * 8]);
+          for (int g16 = 0; g16 < 2; ++g16) st16bf(out + o + ch0 + g16 * 16, &x[g16 * 16]);
         }
         if (epi.stats_mode != NSG_STATS_NONE) {
           if (epi.stats_mode == NSG_STATS_MOMENTS) {
@@ -647,8 +657,8 @@ int conv_gemm_tma(const nsg_conv_geom* cg, const void* in, const void* packed, c
                   cudaStream_t stream) {
   if (int rc = tma_shape_ok(cg, "conv_gemm_tma")) return rc;
   NSG_REQUIRE((reinterpret_cast<uintptr_t>(packed) & 127) == 0, "conv_gemm_tma: packed weights must be 128-byte aligned");
-  NSG_REQUIRE((reinterpret_cast<uintptr_t>(in) & 15) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0,
-              "conv_gemm_tma: tensors must be 16-byte aligned");
+  NSG_REQUIRE((reinterpret_cast<uintptr_t>(in) & 15) == 0 && (reinterpret_cast<uintptr_t>(out) & 31) == 0,
+              "conv_gemm_tma: the input must be 16-byte and the output 32-byte aligned");
   EpiArgs e{};
   if (int rc = make_epi(epi, &e)) return rc;
   NSG_REQUIRE(e.tanh_out == 0 || e.tanh_out == 2,
@@ -1233,14 +1243,14 @@ c1t_conv_kernel(const __nv_bfloat16* __restrict__ in1, const uint8_t* __restrict
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sm = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sW = sm;                                  // one 64 x 64 image (K >= 16 zero)
-  uint8_t* sA = sm + TM_W_BYTES;                     // one patch tile per epilogue group
+  uint8_t* sA = sm + TM_W_BYTES;                     // two patch tiles per epilogue group (buffer = grp * 2 + parity)
   __shared__ __align__(16) float sPar[5 * TM_C];
   __shared__ float sStat[2 * TM_C];
-  __shared__ __align__(8) uint64_t bars[5];          // wfull, full[2], acc_full[2]
+  __shared__ __align__(8) uint64_t bars[9];          // wfull, full[4], acc_full[4]
   __shared__ uint32_t tmem_slot;
   uint64_t* wfull = bars;
   uint64_t* full = bars + 1;
-  uint64_t* acc_full = bars + 3;
+  uint64_t* acc_full = bars + 5;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   if (tid < TM_C) {          // (set-up above the first pdl_wait() touches no global memory: common.cuh, PDL)
@@ -1249,11 +1259,13 @@ c1t_conv_kernel(const __nv_bfloat16* __restrict__ in1, const uint8_t* __restrict
   }
   if (tid == 0) {
     mbar_init(wfull, 1);
-    mbar_init(&full[0], 128); mbar_init(&full[1], 128);
-    mbar_init(&acc_full[0], 1); mbar_init(&acc_full[1], 1);
+    for (int b = 0; b < 4; ++b) {
+      mbar_init(&full[b], 128);
+      mbar_init(&acc_full[b], 1);
+    }
     fence_mbar_init();
   }
-  if (warp == 1) tmem_alloc<128>(&tmem_slot);
+  if (warp == 1) tmem_alloc<256>(&tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -1271,21 +1283,20 @@ c1t_conv_kernel(const __nv_bfloat16* __restrict__ in1, const uint8_t* __restrict
   } else if (warp == 1) {
     if (lane == 0 && ntiles_mine > 0) {
       const uint32_t idesc = idesc_bf16(TM_M, TM_C);
-      const uint64_t b = sw128_desc(smem_u32(sW));
+      const uint64_t b_desc = sw128_desc(smem_u32(sW));
       mbar_wait(wfull, 0);
       for (int i = 0; i < ntiles_mine; ++i) {
-        const int g = i & 1;
-        mbar_wait(&full[g], (uint32_t)((i >> 1) & 1));
+        const int j = i >> 1, b = (i & 1) * 2 + (j & 1);
+        mbar_wait(&full[b], (uint32_t)((j >> 1) & 1));
         tc_fence_after();
-        umma_bf16(tmem_base + (uint32_t)g * TM_C, sw128_desc(smem_u32(sA + (size_t)g * TM_A_BYTES)), b, idesc, 0);
-        umma_commit(&acc_full[g]);
+        umma_bf16(tmem_base + (uint32_t)b * TM_C, sw128_desc(smem_u32(sA + (size_t)b * TM_A_BYTES)), b_desc, idesc, 0);
+        umma_commit(&acc_full[b]);
       }
     }
   } else {
     const int grp = (warp - 2) >> 2, q = warp & 3;
     const int r = q * 32 + lane;
     const int bw = r & (P.box_w - 1), bh = r >> P.log2_bw;
-    uint8_t* myA = sA + (size_t)grp * TM_A_BYTES;
     const unsigned short* in16 = reinterpret_cast<const unsigned short*>(in1);
     pdl_wait();
     pdl_trigger();
@@ -1298,41 +1309,72 @@ c1t_conv_kernel(const __nv_bfloat16* __restrict__ in1, const uint8_t* __restrict
       sPar[4 * TM_C + c] = epi.stats_mode == NSG_STATS_BNBWD ? __ldg(epi.invstd + c) : 0.f;
     }
     named_bar(2, 256);
-    for (int i = grp; i < ntiles_mine; i += 2) {
+    // The group's chain per tile is: 16 scattered 2-byte loads -> patch row into shared memory -> one MMA round trip
+    // -> epilogue.  With one buffer per group every link is exposed (9000-13700 cycles per tile measured against a
+    // 4000-cycle epilogue), so the chain is software-pipelined: the patch of tile j+2 is loaded into registers and the
+    // patch of tile j+1 is handed to the tensor core (second buffer / accumulator) BEFORE the epilogue of tile j.
+    struct TileRow {
+      int n, oh, ow;
+      bool valid;
+    };
+    auto row_of = [&](int i) {
       int t = (int)blockIdx.x + i * (int)gridDim.x;
       const int tw = t % P.tiles_w;
       t /= P.tiles_w;
-      const int th = t % P.tiles_h, n = t / P.tiles_h;
-      const int oh = th * P.box_h + bh, ow = tw * P.box_w + bw;
-      const bool valid = oh < P.out_h && ow < P.out_w;
-      // this row's 4 x 4 input patch (k = 4, stride 2, pad 1), taps kh*4 + kw along K
-      uint32_t pk[8];
+      TileRow R;
+      R.n = t / P.tiles_h;
+      R.oh = (t % P.tiles_h) * P.box_h + bh;
+      R.ow = tw * P.box_w + bw;
+      R.valid = R.oh < P.out_h && R.ow < P.out_w;
+      return R;
+    };
+    uint32_t pk[8];
+    auto load_patch = [&](int i) {        // this row's 4 x 4 input patch (k = 4, stride 2, pad 1), taps kh*4 + kw along K
+      const TileRow R = row_of(i);
 #pragma unroll
       for (int kh = 0; kh < 4; ++kh) {
-        const int ih = 2 * oh - 1 + kh;
-        const bool rok = valid && ih >= 0 && ih < P.in_h;
-        const unsigned short* rowp = in16 + ((long long)n * P.in_h + ih) * P.in_w;
+        const int ih = 2 * R.oh - 1 + kh;
+        const bool rok = R.valid && ih >= 0 && ih < P.in_h;
+        const unsigned short* rowp = in16 + ((long long)R.n * P.in_h + ih) * P.in_w;
         unsigned short v[4];
 #pragma unroll
         for (int kw = 0; kw < 4; ++kw) {
-          const int iw = 2 * ow - 1 + kw;
+          const int iw = 2 * R.ow - 1 + kw;
           v[kw] = (rok && iw >= 0 && iw < P.in_w) ? __ldg(rowp + iw) : (unsigned short)0;
         }
         pk[kh * 2 + 0] = (uint32_t)v[0] | ((uint32_t)v[1] << 16);
         pk[kh * 2 + 1] = (uint32_t)v[2] | ((uint32_t)v[3] << 16);
       }
-      const long long o = valid ? (((long long)n * P.out_h + oh) * P.out_w + ow) * TM_C : 0;
-      EpiOperands E;
-      epi_begin(E, epi, o, valid);
+    };
+    auto submit = [&](int buf) {          // patch registers -> operand tile `buf` of this group -> tensor core
+      uint8_t* myA = sA + (size_t)(grp * 2 + buf) * TM_A_BYTES;
       *reinterpret_cast<uint4*>(myA + sw128_offset(r, 0)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
       *reinterpret_cast<uint4*>(myA + sw128_offset(r, 1)) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
       fence_proxy_async_smem();
-      tc_fence_before();                       // orders this thread's tcgen05.ld of the previous tile before the arrive
-      mbar_arrive(&full[grp]);
-      mbar_wait(&acc_full[grp], (uint32_t)((i >> 1) & 1));
+      tc_fence_before();                  // orders this thread's earlier tcgen05.ld of that accumulator before the arrive
+      mbar_arrive(&full[grp * 2 + buf]);
+    };
+    if (grp < ntiles_mine) {
+      load_patch(grp);
+      submit(0);
+      if (grp + 2 < ntiles_mine) load_patch(grp + 2);
+    }
+    int j = 0;
+    for (int i = grp; i < ntiles_mine; i += 2, ++j) {
+      const int jb = j & 1;
+      if (i + 2 < ntiles_mine) {
+        submit(jb ^ 1);
+        if (i + 4 < ntiles_mine) load_patch(i + 4);
+      }
+      const TileRow R = row_of(i);
+      const bool valid = R.valid;
+      const long long o = valid ? (((long long)R.n * P.out_h + R.oh) * P.out_w + R.ow) * TM_C : 0;
+      EpiOperands E;
+      epi_begin(E, epi, o, valid);
+      mbar_wait(&acc_full[grp * 2 + jb], (uint32_t)((j >> 1) & 1));
       tc_fence_after();
       uint32_t acc0[32], acc1[32];
-      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)grp * TM_C;
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(grp * 2 + jb) * TM_C;
       tmem_ld32(taddr, acc0);
       tmem_ld32(taddr + 32, acc1);
       tmem_ld_wait();
@@ -1346,7 +1388,7 @@ c1t_conv_kernel(const __nv_bfloat16* __restrict__ in1, const uint8_t* __restrict
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc<128>(tmem_base);
+  if (warp == 1) tmem_dealloc<256>(tmem_base);
 }
 
 static bool c1t_geom_ok(const nsg_conv_geom* cg) {
@@ -1362,6 +1404,7 @@ int conv_c1_tc(const nsg_conv_geom* cg, const void* in, const void* packed, cons
     return NSG_E_UNSUPPORTED;
   }
   NSG_REQUIRE((reinterpret_cast<uintptr_t>(packed) & 127) == 0, "conv_c1_tc: packed weights must be 128-byte aligned");
+  NSG_REQUIRE((reinterpret_cast<uintptr_t>(out) & 31) == 0, "conv_c1_tc: the output must be 32-byte aligned");
   EpiArgs e{};
   if (int rc = make_epi(epi, &e)) return rc;
   NSG_REQUIRE(e.tanh_out == 0 || e.tanh_out == 2, "conv_c1_tc: output activation must be none or ReLU");
@@ -1372,7 +1415,7 @@ int conv_c1_tc(const nsg_conv_geom* cg, const void* in, const void* packed, cons
   P.tiles_h = (cg->out_h + P.box_h - 1) / P.box_h;
   P.total_tiles = P.tiles_w * P.tiles_h * cg->batch;
   if (P.total_tiles == 0) return NSG_OK;
-  const size_t smem = 1024 + TM_W_BYTES + 2 * TM_A_BYTES;
+  const size_t smem = 1024 + TM_W_BYTES + 4 * TM_A_BYTES;
   static bool configured = false;
   if (!configured) {
     cudaError_t err = cudaFuncSetAttribute(c1t_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

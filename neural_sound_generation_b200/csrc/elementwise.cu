@@ -311,9 +311,12 @@ __global__ void loss_finalize_kernel(const double* __restrict__ sums, double a, 
 }
 
 // ---------------------------------------------------------------- Adam (torch.optim.Adam single-tensor maths)
-__global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
-                            float* __restrict__ v, long long n, float lr, float b1, float b2, float eps,
-                            float gscale, const long long* __restrict__ step_count) {
+// VEC = 4: 16-byte accesses (n % 4 == 0, 16-byte aligned buffers).  zero != 0 clears each gradient after its use, which
+// replaces the next step's zero_grad fill.
+template <int VEC>
+__global__ void __launch_bounds__(256)
+adam_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m, float* __restrict__ v, long long n,
+            float lr, float b1, float b2, float eps, float gscale, const long long* __restrict__ step_count, int zero) {
   pdl_wait();
   pdl_trigger();
   __shared__ float s_step_size, s_bc2_sqrt;
@@ -326,16 +329,37 @@ __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, 
   }
   __syncthreads();
   const float step_size = s_step_size, bc2_sqrt = s_bc2_sqrt;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+  const long long nv = n / VEC;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nv;
        i += (long long)gridDim.x * blockDim.x) {
-    const float gr = g[i] * gscale;
-    float mi = m[i], vi = v[i];
-    mi = mi + (gr - mi) * (1.f - b1);             // exp_avg.lerp_(grad, 1 - beta1)
-    vi = vi * b2 + (1.f - b2) * gr * gr;          // exp_avg_sq.mul_(beta2).addcmul_(grad, grad, 1 - beta2)
-    const float denom = sqrtf(vi) / bc2_sqrt + eps;
-    p[i] = p[i] - step_size * (mi / denom);
-    m[i] = mi;
-    v[i] = vi;
+    float gr[VEC], mi[VEC], vi[VEC], pi[VEC];
+    if (VEC == 4) {
+      const float4 g4 = reinterpret_cast<const float4*>(g)[i], m4 = reinterpret_cast<const float4*>(m)[i];
+      const float4 v4 = reinterpret_cast<const float4*>(v)[i], p4 = reinterpret_cast<const float4*>(p)[i];
+      gr[0] = g4.x; gr[1 % VEC] = g4.y; gr[2 % VEC] = g4.z; gr[3 % VEC] = g4.w;
+      mi[0] = m4.x; mi[1 % VEC] = m4.y; mi[2 % VEC] = m4.z; mi[3 % VEC] = m4.w;
+      vi[0] = v4.x; vi[1 % VEC] = v4.y; vi[2 % VEC] = v4.z; vi[3 % VEC] = v4.w;
+      pi[0] = p4.x; pi[1 % VEC] = p4.y; pi[2 % VEC] = p4.z; pi[3 % VEC] = p4.w;
+    } else {
+      gr[0] = g[i]; mi[0] = m[i]; vi[0] = v[i]; pi[0] = p[i];
+    }
+#pragma unroll
+    for (int e = 0; e < VEC; ++e) {
+      const float ge = gr[e] * gscale;
+      mi[e] = mi[e] + (ge - mi[e]) * (1.f - b1);          // exp_avg.lerp_(grad, 1 - beta1)
+      vi[e] = vi[e] * b2 + (1.f - b2) * ge * ge;          // exp_avg_sq.mul_(beta2).addcmul_(grad, grad, 1 - beta2)
+      const float denom = sqrtf(vi[e]) / bc2_sqrt + eps;
+      pi[e] = pi[e] - step_size * (mi[e] / denom);
+    }
+    if (VEC == 4) {
+      reinterpret_cast<float4*>(p)[i] = make_float4(pi[0], pi[1 % VEC], pi[2 % VEC], pi[3 % VEC]);
+      reinterpret_cast<float4*>(m)[i] = make_float4(mi[0], mi[1 % VEC], mi[2 % VEC], mi[3 % VEC]);
+      reinterpret_cast<float4*>(v)[i] = make_float4(vi[0], vi[1 % VEC], vi[2 % VEC], vi[3 % VEC]);
+      if (zero) reinterpret_cast<float4*>(g)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    } else {
+      p[i] = pi[0]; m[i] = mi[0]; v[i] = vi[0];
+      if (zero) g[i] = 0.f;
+    }
   }
 }
 __global__ void tick_kernel(long long* step_count) {
@@ -522,12 +546,22 @@ int nsg_tanh_bwd(const float* g, const float* y, float* out, long long n, void* 
   return NSG_OK;
 }
 
-int nsg_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, long long n, float lr,
-                  float beta1, float beta2, float eps, float grad_scale, long long* step_count, void* stream) {
+int nsg_adam_step(float* params, float* grads, float* exp_avg, float* exp_avg_sq, long long n, float lr,
+                  float beta1, float beta2, float eps, float grad_scale, long long* step_count, int zero_grads,
+                  void* stream) {
   NSG_REQUIRE(params && grads && exp_avg && exp_avg_sq && step_count && n >= 0, "adam_step: bad arguments");
   if (n > 0) {
-    launch_pdl(adam_kernel, dim3(grid_for(n, 256)), dim3(256), 0, (cudaStream_t)stream, params, grads, exp_avg, exp_avg_sq, n, lr,
-                                                                     beta1, beta2, eps, grad_scale, step_count);
+    const bool vec = n % 4 == 0 && ((reinterpret_cast<uintptr_t>(params) | reinterpret_cast<uintptr_t>(grads) |
+                                     reinterpret_cast<uintptr_t>(exp_avg) | reinterpret_cast<uintptr_t>(exp_avg_sq)) & 15) == 0;
+    if (vec) {
+      int blocks = grid_for(n / 4, 256);
+      if (blocks > 2 * num_sms()) blocks = 2 * num_sms();
+      launch_pdl(adam_kernel<4>, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, params, grads, exp_avg, exp_avg_sq, n,
+                 lr, beta1, beta2, eps, grad_scale, step_count, zero_grads);
+    } else {
+      launch_pdl(adam_kernel<1>, dim3(grid_for(n, 256)), dim3(256), 0, (cudaStream_t)stream, params, grads, exp_avg,
+                 exp_avg_sq, n, lr, beta1, beta2, eps, grad_scale, step_count, zero_grads);
+    }
     NSG_CHECK_LAUNCH("adam_kernel");
   }
   launch_pdl(tick_kernel, dim3(1), dim3(1), 0, (cudaStream_t)stream, step_count);

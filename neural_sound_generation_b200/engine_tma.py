@@ -49,7 +49,7 @@ class EngineTMA(object):
         self.layers = None
         self._key = None
         self.side = None            # second stream: weight gradients run beside the data-gradient chain
-        self.overlap_wgrad = True
+        self.overlap_wgrad = os.environ.get('NSG_OVERLAP_WGRAD', '1') != '0'
         # Weight-gradient partials: False = CTAs meet in one packed image per layer through vector atomics; True = one
         # slice per CTA, plain stores, summed in a fixed order by the unpack (bit-reproducible gradients).  Measured on
         # B200 (configs[1], same box): the sliced kernels are 1-2 us faster each in isolation, but their 58 MB of

@@ -46,11 +46,14 @@ class GraphedTrainStep(object):
         return [f['params'], o.exp_avg, o.exp_avg_sq, o.step_count] + [b for _, b in self.model.named_buffers()]
 
     def _body(self, grad_hook):
-        self.optimizer.zero_grad()
+        # no zero_grad fill in the captured step: Adam clears every gradient right after using it; gradients written
+        # by anything else between two calls (eager loss_and_grads / backward) are cleared in __call__
+        if self.model.__dict__.get('_grads_dirty', True):
+            self.optimizer.zero_grad()
         losses, outs = self.model.loss_and_grads(self.c, beta=self.beta)
         if grad_hook is not None:
             grad_hook(self.model._flat['grads'])
-        self.optimizer.step()
+        self.optimizer.step(zero_grads=True)
         return losses, outs
 
     def close(self):
@@ -63,6 +66,8 @@ class GraphedTrainStep(object):
         torch.cuda.synchronize(dev)
 
     def __call__(self, c):
+        if self.model.__dict__.get('_grads_dirty', True):
+            self.optimizer.zero_grad()
         self.c.copy_(c.reshape(self.c.shape), non_blocking=True)
         self.graph.replay()
         return self.losses

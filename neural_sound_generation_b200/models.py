@@ -282,6 +282,8 @@ class VQVAE(nn.Module):
     def forward(self, x):
         """models.py:198-216 -> (x_tilde, z_e_x, z_q_x)"""
         names, params = self._named()
+        if torch.is_grad_enabled():
+            self.__dict__['_grads_dirty'] = True        # a backward() may follow (GraphedTrainStep clears before replay)
         return _VQVAEFn.apply(self, x, *params)
 
     # ------------------------------------------------------------------ fused train step (train.py:116-135)
@@ -299,6 +301,7 @@ class VQVAE(nn.Module):
         eng = self.engine()
         self.flatten_parameters()
         self.bind_grads()
+        self.__dict__['_grads_dirty'] = True
         P = {n: p.detach() for n, p in self.named_parameters()}
         G = grads if grads is not None else self.grad_dict()
         Bufs = self._bufs()

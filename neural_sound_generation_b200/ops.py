@@ -300,12 +300,13 @@ def loss_finalize(sums, recon_scale, vq_scale, out=None):
 
 
 def adam_step(params, grads, exp_avg, exp_avg_sq, step_count, lr, beta1=0.9, beta2=0.999, eps=1e-8,
-              grad_scale=1.0):
+              grad_scale=1.0, zero_grads=False):
     global launch_count
     A.require_device()
     _cuda(params, grads, exp_avg, exp_avg_sq, step_count)
     rc = A.load().nsg_adam_step(A.ptr(params), A.ptr(grads), A.ptr(exp_avg), A.ptr(exp_avg_sq), params.numel(),
-                                lr, beta1, beta2, eps, grad_scale, A.ptr(step_count), A.stream_ptr())
+                                lr, beta1, beta2, eps, grad_scale, A.ptr(step_count), 1 if zero_grads else 0,
+                                A.stream_ptr())
     A.check(rc, 'nsg_adam_step')
     launch_count += 2
 

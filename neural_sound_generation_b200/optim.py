@@ -26,10 +26,15 @@ class Adam(torch.optim.Optimizer):
         self.model.flatten_parameters()
         self.model._flat['grads'].zero_()
         self.model.bind_grads()
+        self.model.__dict__['_grads_dirty'] = False
 
     @torch.no_grad()
-    def step(self, closure=None):
+    def step(self, closure=None, zero_grads=False):
+        """zero_grads=True also clears the gradients (what the next iteration's zero_grad() would do) in the same
+        pass; GraphedTrainStep uses it so the captured step holds no separate fill."""
         f = self.model.flatten_parameters()
         g = self.param_groups[0]
         ops.adam_step(f['params'], f['grads'], self.exp_avg, self.exp_avg_sq, self.step_count, g['lr'],
-                      g['betas'][0], g['betas'][1], g['eps'], self.grad_scale)
+                      g['betas'][0], g['betas'][1], g['eps'], self.grad_scale, zero_grads=zero_grads)
+        if zero_grads:
+            self.model.__dict__['_grads_dirty'] = False

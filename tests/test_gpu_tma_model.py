@@ -158,6 +158,18 @@ def test_tma_eval_encode_decode_and_graph():
         assert np.allclose(la, lb.tolist(), rtol=1e-3 if it == 0 else 5e-2), (it, la, lb.tolist())
     wa, wb = ma.state_dict()['encoder.3.weight'], mb.state_dict()['encoder.3.weight']
     assert relerr(wa, wb) < 5e-2
+    # the captured step has no zero_grad fill (Adam clears each gradient after using it): gradients left behind by an
+    # eager call between two replays must not leak into the next replay
+    assert float(ma._flat['grads'].abs().max()) == 0.0
+    ma.loss_and_grads(mel2.to(DEV), beta=1.0)
+    assert float(ma._flat['grads'].abs().max()) > 0.0
+    la = step(mel2.to(DEV)).tolist()
+    ob.zero_grad()
+    lb, _ = mb.loss_and_grads(mel2.to(DEV), beta=1.0)
+    ob.step()
+    torch.cuda.synchronize()
+    assert np.allclose(la, lb.tolist(), rtol=5e-2), (la, lb.tolist())
+    assert relerr(ma.state_dict()['encoder.3.weight'], mb.state_dict()['encoder.3.weight']) < 5e-2
 
 
 def test_graphed_inference_config5_shape():
