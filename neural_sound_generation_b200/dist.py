@@ -174,16 +174,18 @@ class DataParallelStep(GraphedTrainStep):
         dp = self.dp
         dp.collectives = 0
         dp.loss_slots = None
-        self.optimizer.zero_grad()
+        if self.model.__dict__.get('_grads_dirty', True):      # as GraphedTrainStep._body: Adam clears after use
+            self.optimizer.zero_grad()
         losses, outs = self.model.loss_and_grads(self.c, beta=self.beta)
-        self.optimizer.step()
         if dp.world > 1:
             if dp.loss_slots is not None:
-                # the loss scalars rode in the padding at the end of the decoder gradient bucket (see decoder_done)
+                # the loss scalars rode in the padding at the end of the decoder gradient bucket (see decoder_done);
+                # read them before Adam clears the buffer
                 losses = dp.loss_slots.double() * (1.0 / dp.world)
             else:
                 allreduce_sum_(losses, dp.group)
                 losses.mul_(1.0 / dp.world)
                 dp.collectives += 1
+        self.optimizer.step(zero_grads=True)
         self.collectives_per_step = dp.collectives
         return losses, outs

@@ -454,3 +454,69 @@ def test_adam_known_answer(golden_dir):
     for i, s in enumerate(sizes):
         assert np.allclose(out[o:o + s].reshape(shapes[i]), g['p%d' % i], rtol=2e-6, atol=2e-7), i
         o += s
+
+
+def test_recon_loss_bf16_fused_and_loss_finalize():
+    """nsg_recon_loss_bf16 = nsg_recon_loss on the bf16-rounded x_tilde, plus the two conversions around it
+    (train.py:118-129); nsg_loss_finalize = the three loss scalars of train.py:129-134 from the two sums."""
+    rng = np.random.RandomState(18)
+    B, H, Wt, Wc = 3, 10, 8, 11
+    xt16 = torch.tensor(np.tanh(rng.standard_normal((B, H, Wt))).astype(np.float32)).to(torch.bfloat16)
+    c = torch.tensor(rng.uniform(0, 1, (B, H, Wc)).astype(np.float32))
+    x64 = xt16.double()
+    loss = F.mse_loss(F.pad(x64, (0, Wc - Wt)), c.double())
+    dref = 2.0 * (x64 - c.double()[..., :Wt]) / c.numel() * (1.0 - x64 * x64)
+    sums = torch.zeros(2, dtype=torch.float64, device=DEV)
+    dpre = torch.empty(B, H, Wt, dtype=torch.bfloat16, device=DEV)
+    x32 = torch.full((B, H, Wt), 7.0, device=DEV)
+    ops.recon_loss_bf16(xt16.to(DEV), c.to(DEV), sums[0:1], dpre, x32)
+    torch.cuda.synchronize()
+    assert abs(sums[0].item() / c.numel() - loss.item()) < 1e-6 * max(1.0, loss.item())
+    assert torch.equal(x32.cpu(), xt16.float())
+    assert torch.equal(dpre.cpu(), dref.float().to(torch.bfloat16)) or relerr(dpre, dref) < 4e-3
+    # same numbers as the fp32 kernel fed the widened tensor
+    sums2 = torch.zeros(1, dtype=torch.float64, device=DEV)
+    dpre2 = torch.empty(B, H, Wt, device=DEV)
+    ops.recon_loss(xt16.float().to(DEV), c.to(DEV), sums2, dpre2)
+    assert sums2.item() == sums[0].item() or abs(sums2.item() - sums[0].item()) < 1e-9 * abs(sums2.item())
+    assert torch.equal(dpre2.to(torch.bfloat16), dpre)
+    # optional outputs may be omitted
+    s3 = torch.zeros(1, dtype=torch.float64, device=DEV)
+    ops.recon_loss_bf16(xt16.to(DEV), c.to(DEV), s3)
+    assert abs(s3.item() - sums[0].item()) < 1e-9 * abs(s3.item())
+    with pytest.raises(Exception):
+        ops.recon_loss_bf16(xt16.float().to(DEV), c.to(DEV), s3)
+    sums[1] = 5.0
+    out = ops.loss_finalize(sums, 1.0 / c.numel(), 0.25)
+    torch.cuda.synchronize()
+    assert out.tolist() == [sums[0].item() * (1.0 / c.numel()), 1.25, 1.25]
+
+
+def test_adam_vector_path_and_gradient_clearing():
+    """16-byte path (n % 4 == 0) == scalar path bit for bit; zero_grads clears exactly the gradients, after use."""
+    rng = np.random.RandomState(5)
+    n = 4096 + 8
+    p0 = torch.tensor(rng.standard_normal(n).astype(np.float32), device=DEV)
+    res = {}
+    for tag, off in (('vec', 0), ('scalar', 1)):          # a 4-byte offset forces the scalar kernel on the same data
+        buf = [torch.zeros(n + 4, device=DEV) for _ in range(4)]
+        p, g, m, v = [b[off:off + n] for b in buf]
+        p.copy_(p0)
+        step = torch.zeros((), dtype=torch.int64, device=DEV)
+        rg = np.random.RandomState(6)
+        for it in range(3):
+            g.copy_(torch.tensor(rg.standard_normal(n).astype(np.float32)))
+            ops.adam_step(p, g, m, v, step, 1e-3, grad_scale=0.5, zero_grads=(it == 2))
+            assert (float(g.abs().max()) == 0.0) == (it == 2)
+        assert int(step) == 3
+        res[tag] = (p.clone(), m.clone(), v.clone())
+    for a, b in zip(res['vec'], res['scalar']):
+        assert torch.equal(a, b)
+    # against torch.optim.Adam
+    q = torch.nn.Parameter(p0.clone())
+    opt = torch.optim.Adam([q], lr=1e-3)
+    rg = np.random.RandomState(6)
+    for it in range(3):
+        q.grad = torch.tensor(rg.standard_normal(n).astype(np.float32), device=DEV) * 0.5
+        opt.step()
+    assert relerr(res['vec'][0], q.detach()) < 1e-6
