@@ -1122,7 +1122,9 @@ int conv_wgrad_tma(const nsg_conv_geom* cg, const void* p, const void* q, float*
   P.tiles_h = (cg->out_h + P.box_h - 1) / P.box_h;
   P.total_tiles = P.tiles_w * P.tiles_h * cg->batch;
   P.slice_elems = sliced ? k * k * TM_C * TM_C : 0;
-  P.dbg = getenv("NSG_WGRAD_DBG") ? atoi(getenv("NSG_WGRAD_DBG")) : 0;
+  // tuning aid behind profiles/r1_final_wgrad_timeline.txt: 1 = issue no MMAs, 2 = load no P boxes (results are wrong)
+  static const int wgrad_dbg = getenv("NSG_WGRAD_DBG") ? atoi(getenv("NSG_WGRAD_DBG")) : 0;
+  P.dbg = wgrad_dbg;
   P.stamps = g_timeline;
 
   // vertical shift of tap kh inside its (row-parity) view, and the halo the tallest class needs
