@@ -130,7 +130,8 @@ int nsg_conv_wgrad_tc(const nsg_conv_geom* g, const void* p, const nsg_prologue*
  * consumes exactly what the TMA unit wrote (zero padding = the unit's out-of-bounds fill).
  *   nsg_conv_pack_many     bf16 K-major SWIZZLE_128B weight images (k*k * 8192 bytes each, 128-byte aligned) of up
  *                          to 24 (layer, orientation) pairs in one launch; strides as in nsg_conv_geom
- *   nsg_conv_gemm_tma      same contract as nsg_conv_gemm_tc with passes = 1 and no prologue
+ *   nsg_conv_gemm_tma      same contract as nsg_conv_gemm_tc with passes = 1 and no prologue; `out` 32-byte aligned
+ *                          (rows leave as whole 32-byte sectors)
  *   nsg_conv_wgrad_tma     dw_packed[t][a][b] (fp32, k*k*64*64, 16-byte aligned) += sum_m P[gather0(m,t),a]*Q[m,b];
  *                          q_colsum (nullable) as in nsg_conv_wgrad.  The split-K partials of all CTAs meet in the
  *                          one image through vector atomics.
@@ -164,9 +165,14 @@ int nsg_conv_gemm_tma(const nsg_conv_geom* g, const void* in, const void* packed
                       void* stream);
 int nsg_conv_wgrad_tma(const nsg_conv_geom* g, const void* p, const void* q, float* dw_packed, float* q_colsum,
                        void* stream);
-/* Programmatic dependent launch for the kernels that support it (the 64-channel convolutions and their BatchNorm
- * companions): 1 (default) lets such a kernel become resident and run its data-independent prologue while its
- * predecessor in the stream drains; results are identical.  Returns the previous setting; any other value only reads. */
+/* Programmatic dependent launch (every kernel of this library): 1 (default) lets a kernel become resident and run its
+ * data-independent prologue while its predecessor in the stream drains; every kernel waits for ALL earlier work in
+ * the stream before its first dependent access, so results are identical.  One thing is read above that wait: the
+ * packed weight images of nsg_conv_gemm_tma, and only when the library knows they are settled -- it tracks
+ * nsg_conv_pack_many per stream and requires at least one of its own launches between the pack and the consumer.
+ * A caller that fills packed_w by other means (its own kernel) in the launch right before nsg_conv_gemm_tma on the
+ * same stream must either put any other launch / event / copy in between or call nsg_pdl(0).
+ * Returns the previous setting; any value other than 0 / 1 only reads.  Environment NSG_PDL=0 sets the default. */
 int nsg_pdl(int enable);
 int nsg_conv_wgrad_slices(const nsg_conv_geom* g);
 int nsg_conv_wgrad_tma_sliced(const nsg_conv_geom* g, const void* p, const void* q, float* dw_slices, float* q_colsum,
