@@ -1,0 +1,175 @@
+"""``main.py``-compatible driver for the VQ-VAE path of /root/reference/src/main.py:25-229.
+
+Same command-line flags and defaults (main.py:25-58), same checkpoint dict and file name (main.py:61-66, 218-227:
+``./models/<model>/checkpoint_<dataset>_<dim>_<z_dim>.pth.tar`` holding ``epoch / arch / state_dict / optimizer``, the
+optimizer state in ``torch.optim.Adam``'s own layout), same per-epoch reconstruction dump
+(main.py:155-162: ``<sampledir>/<dataset>/reconstruction_<model>_data_<dataset>_dim_<dim>_z_dim_<z_dim>_epoch_<e>.npy``).
+
+What is NOT here, and why (SURVEY.md section 8f ranks them after this row):
+  * the VAE / PixelCNN models (``--model vae``: refused -- not on the hot path);
+  * the reference's data loaders (N2).  ``--dataset ljspeech`` imports ``get_audio_data_loaders`` from a ``dataloader``
+    module on ``sys.path`` (the reference's own ``src/dataloader.py`` works unchanged: it is host code that yields the
+    5-tuples ``train_vqvae`` consumes); ``--synthetic-batches N`` substitutes N uniform-[0,1] mel batches per epoch;
+  * Griffin-Lim audio of the sample (main.py:164-197, N3): skipped with a message.
+
+    python -m neural_sound_generation_b200.main --model vqvae --dataset ljspeech --dim 64 --z-dim 512 \
+        --synthetic-batches 100 --epochs 1
+"""
+import argparse
+import os
+
+import numpy as np
+import torch
+
+from .models import VQVAE
+from .optim import Adam
+from .train import train_vqvae
+from .test import test_vqvae
+
+
+def build_parser():
+    """The reference's parser (main.py:25-58): flag names, types and defaults verbatim; our additions come last."""
+    parser = argparse.ArgumentParser(description='VQ-VAE on mel spectrograms (B200-native hot path)')
+    parser.add_argument('--batch-size', type=int, default=64, metavar='N')
+    parser.add_argument('--lr-rate', type=float, default=1e-3, metavar='N')
+    parser.add_argument('--dataset', type=str, default='MNIST', metavar='N')
+    parser.add_argument('--datadir', type=str, default='./data/', metavar='N')
+    parser.add_argument('--sampledir', type=str, default='./results/', metavar='N')
+    parser.add_argument('--epochs', type=int, default=3000, metavar='N')
+    parser.add_argument('--no-cuda', action='store_true', default=False)
+    parser.add_argument('--seed', type=int, default=1, metavar='S')
+    parser.add_argument('--log-interval', type=int, default=10, metavar='N')
+    parser.add_argument('--model', type=str, default='vae', metavar='N')
+    parser.add_argument('--beta', type=float, default=1.0)
+    parser.add_argument('--dim', type=int, default=1, metavar='S')
+    parser.add_argument('--z-dim', type=int, default=512, metavar='S')
+    # ---- not in the reference
+    parser.add_argument('--synthetic-batches', type=int, default=0, metavar='N',
+                        help='use N synthetic uniform-[0,1] mel batches (80 x --synthetic-frames) per epoch')
+    parser.add_argument('--synthetic-frames', type=int, default=256, metavar='T')
+    parser.add_argument('--resume', action='store_true', default=False,
+                        help='load ./models/<model>/checkpoint_<dataset>_<dim>_<z_dim>.pth.tar before training')
+    parser.add_argument('--fp32', action='store_true', default=False,
+                        help='fp32 parity engine instead of the bf16 TMA engine')
+    return parser
+
+
+def parse_args(argv=None):
+    args = build_parser().parse_args(argv)
+    args.cuda = not args.no_cuda and torch.cuda.is_available()
+    return args
+
+
+def checkpoint_path(args):
+    """main.py:61-65"""
+    return './models/{}/checkpoint_{}_{}_{}.pth.tar'.format(args.model, args.dataset, args.dim, args.z_dim)
+
+
+def save_checkpoint(args, state):
+    filename = checkpoint_path(args)
+    os.makedirs(os.path.dirname(filename), exist_ok=True)      # (the reference assumes the directory exists)
+    torch.save(state, filename)
+
+
+def sample_path(args, epoch):
+    """main.py:155-161"""
+    return os.path.join(args.sampledir, format(args.dataset),
+                        'reconstruction_' + str(args.model) + '_data_' + str(args.dataset) + '_dim_' + str(args.dim)
+                        + '_z_dim_' + str(args.z_dim) + '_epoch_' + str(epoch) + '.npy')
+
+
+class SyntheticMelLoader(object):
+    """Stands in for the LJSpeech loaders: yields the reference's 5-tuples ``(x, y, c, g, input_lengths)`` with only
+    ``c`` (B, 80, T) populated -- the one field the VQ-VAE loops read (train.py:108-116)."""
+
+    def __init__(self, batches, batch_size, frames, seed, pin=False):
+        g = torch.Generator().manual_seed(seed)
+        self.batches = [torch.rand(batch_size, 80, frames, generator=g) for _ in range(batches)]
+        if pin:
+            self.batches = [b.pin_memory() for b in self.batches]
+        self.dataset = range(batches * batch_size)
+        self.batch_size = batch_size
+
+    def __len__(self):
+        return len(self.batches)
+
+    def __iter__(self):
+        for c in self.batches:
+            b = c.shape[0]
+            yield (torch.zeros(b, 1, dtype=torch.long), torch.zeros(b, 1, dtype=torch.long), c, None,
+                   torch.full((b,), c.shape[2], dtype=torch.long))
+
+
+def get_loaders(args):
+    if args.synthetic_batches > 0:
+        tr = SyntheticMelLoader(args.synthetic_batches, args.batch_size, args.synthetic_frames, args.seed, args.cuda)
+        te = SyntheticMelLoader(max(1, args.synthetic_batches // 8), args.batch_size, args.synthetic_frames,
+                                args.seed + 1, args.cuda)
+        return tr, te
+    if args.dataset == 'ljspeech':
+        try:
+            from dataloader import get_audio_data_loaders        # the reference's src/dataloader.py, unchanged
+        except ImportError as e:
+            raise SystemExit('--dataset ljspeech needs the reference\'s dataloader module on sys.path (%s); '
+                             'or pass --synthetic-batches N' % e)
+        loaders = get_audio_data_loaders(os.path.join(args.datadir), None, args.batch_size, test_shuffle=True)
+        return loaders['train'], loaders['test']
+    raise SystemExit('only the LJSpeech mel path is built (--dataset ljspeech, or --synthetic-batches N); the '
+                     'torchvision branch of main.py is a later row of SURVEY.md section 8f')
+
+
+def main(argv=None):
+    args = parse_args(argv)
+    torch.manual_seed(args.seed)
+    if args.model != 'vqvae':
+        raise SystemExit('--model %s: only the VQ-VAE is on the accelerated path (SURVEY.md section 8)' % args.model)
+    if not args.cuda:
+        raise SystemExit('the B200 path has no CPU execution mode (remove --no-cuda / run on a B200)')
+    device = torch.device('cuda')
+    if args.synthetic_batches > 0 and args.dataset != 'ljspeech':
+        print('synthetic mel batches: treating --dataset %s as ljspeech-shaped input' % args.dataset)
+        args.dataset = 'ljspeech'
+    train_loader, test_loader = get_loaders(args)
+    input_dim = 3 if args.dataset == 'CIFAR10' else 1                                  # main.py:100-116
+    model = VQVAE(input_dim, args.dim, args.z_dim).to(device)
+    if not args.fp32:
+        model.act_dtype, model.conv_impl, model.vq_mode = torch.bfloat16, 2, 1
+    print(model)
+    optimizer = Adam(model, lr=args.lr_rate)                                          # main.py:124
+    last_epoch = 0
+    if args.resume:
+        ck = torch.load(checkpoint_path(args), map_location=device)
+        model.load_state_dict(ck['state_dict'])
+        optimizer.load_state_dict(ck['optimizer'])
+        last_epoch = int(ck.get('epoch', 0))
+        print('resumed %s at epoch %d' % (checkpoint_path(args), last_epoch))
+
+    def state():
+        return {'epoch': last_epoch, 'arch': args.model, 'state_dict': model.state_dict(),
+                'optimizer': optimizer.state_dict()}
+
+    try:
+        for epoch in range(last_epoch + 1, args.epochs + 1):
+            train_vqvae(args, model, optimizer, train_loader, device, epoch)
+            test_vqvae(args, model, test_loader, device, epoch)
+            with torch.no_grad():
+                x, y, c, g, input_lengths = next(iter(test_loader))
+                c = c.to(device).unsqueeze(1)
+                print("Evaluating samples")
+                reconstruction, _, _ = model(c)
+                reconstruction = reconstruction.squeeze(1).float().cpu().numpy()
+                path = sample_path(args, epoch)
+                os.makedirs(os.path.dirname(path), exist_ok=True)
+                np.save(path, reconstruction, allow_pickle=True)
+                print('audio reconstruction (Griffin-Lim, main.py:164-197) is not part of this build: skipped')
+            last_epoch = epoch
+            save_checkpoint(args, state())
+    except KeyboardInterrupt:
+        print("Interrupted!")
+    finally:
+        save_checkpoint(args, state())
+    return 0
+
+
+if __name__ == '__main__':
+    raise SystemExit(main())
