@@ -23,7 +23,8 @@ def train_vqvae(args, model, optimizer, train_loader, device, epoch):
     graphed = fused and isinstance(optimizer, _optim.Adam) and getattr(args, 'cuda_graph', True)
     if args.dataset == 'ljspeech':
         for batch_idx, (x, y, c, g, input_lengths) in tqdm(enumerate(train_loader)):
-            optimizer.zero_grad()
+            if not graphed:
+                optimizer.zero_grad()       # (the graphed step clears gradients inside Adam: no separate fill)
             # Prepare data (x, y, input_lengths are moved by the reference but never used: train.py:111-114)
             c = c.to(device, non_blocking=True) if c is not None else None
             c = c.unsqueeze(1)
