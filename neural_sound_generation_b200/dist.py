@@ -132,7 +132,7 @@ class DataParallel(object):
             self.comm.wait_stream(eng.side)         # decoder weight gradients issued so far on the side stream
         lo, hi = self._slices(flat)['decoder']
         with torch.cuda.stream(self.comm):
-            eng.unpack_part(G, 'decoder')
+            eng.unpack_part(G, 'decoder', fused=ctx.fused)
             allreduce_sum_(flat['grads'][lo:hi], self.group)
         self.collectives += 1
 

@@ -57,6 +57,7 @@ class EngineTMA(object):
         self.wgrad_sliced = os.environ.get('NSG_WGRAD_SLICED', '0') == '1'
         self.zbuf = None            # begin(fused=True): the step's accumulators, one allocation, one fill per step
         self.dwa_in_zbuf = False
+        self.dwa_dirty = False      # the images hold a consumed fused step's sums (cleared by the next fused begin)
         self.dp = None              # dist.DataParallel: cross-rank BatchNorm statistics / bucketed gradient all-reduce
 
     # ------------------------------------------------------------------ packed images
@@ -156,6 +157,7 @@ class EngineTMA(object):
                 self._key = None                    # the layers' dwa views are re-made by _prepare
             else:
                 self.zbuf.zero_()
+            self.dwa_dirty = False
             f64 = self.zbuf[:(nst + 2) * 8].view(torch.float64)
             ctx.stats = f64[:nst].view(len(BN_LAYERS), 2, 2 * self.dim)
             ctx.sums = f64[nst:nst + 2]
@@ -213,6 +215,9 @@ class EngineTMA(object):
         L = self.layers[name]
         b, h, w, c = x.shape
         _, oh, ow, _ = dy.shape
+        if not ctx.fused and self.dwa_dirty and not self.wgrad_sliced:
+            self.dwa.zero_()        # generic autograd backward after a fused step: start from clean images
+            self.dwa_dirty = False
         if L.tr:        # P = dy gathered over x's pixels, Q = x
             g = ops.conv_geom(b, oh, ow, c, h, w, c, L.k, L.s, L.p, 0, L.wci_g, L.wco_g, ops.BF16)
             dwp = self._wgrad_slices(L, g, (b, h, w, oh, ow), x.device)
@@ -422,15 +427,20 @@ class EngineTMA(object):
             torch.cuda.current_stream().wait_stream(self.side)
             ctx.forked = False
         ctx.keep = []
-        self.unpack_part(G, part)
+        self.unpack_part(G, part, fused=ctx.fused)
 
-    def unpack_part(self, G, part=None):
-        """Unpack the gradient partials of 'decoder', 'encoder' or (None) all layers on the current stream."""
+    def unpack_part(self, G, part=None, fused=False):
+        """Unpack the gradient partials of 'decoder', 'encoder' or (None) all layers on the current stream.
+        ``fused``: the caller is a ``begin(fused=True)`` step, whose next ``begin`` clears the images with the step's
+        other accumulators; any other caller (the generic autograd backward) must leave them cleared itself, or the
+        next backward would add onto this one's images."""
         ops.wgrad_unpack_many(self._unpack_items(G, part))
         for L in self.layers.values():      # a layer's partials are consumed once
             if part is None or L.name.startswith(part + '.'):
                 L.nslices = 0
-        if not self.wgrad_sliced and not self.dwa_in_zbuf:
+        if self.dwa_in_zbuf and fused:
+            self.dwa_dirty = True
+        if not self.wgrad_sliced and not (self.dwa_in_zbuf and fused):
             if part is None:
                 self.dwa.zero_()
             elif part == 'decoder':

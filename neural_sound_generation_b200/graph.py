@@ -23,6 +23,22 @@ class GraphedTrainStep(object):
         if not isinstance(optimizer, _optim.Adam):
             raise TypeError('GraphedTrainStep needs neural_sound_generation_b200.optim.Adam (device-side step count)')
         self.model, self.optimizer, self.beta = model, optimizer, float(beta)
+        self._grad_hook, self._batch_shape = grad_hook, tuple(batch_shape)
+        self._capture()
+
+    def _hyper(self):
+        g = self.optimizer.param_groups[0]
+        m = self.model
+        return (float(g['lr']), float(g['betas'][0]), float(g['betas'][1]), float(g['eps']),
+                float(self.optimizer.grad_scale), m.conv_impl, m.vq_mode, m.act_dtype)
+
+    def _capture(self):
+        """(Re)capture.  lr / betas / eps / grad_scale are by-value kernel arguments of the recorded Adam launch and the
+        engine choice fixes the recorded kernels, so ``__call__`` re-captures when any of them has changed
+        (scheduler, ``load_state_dict``) instead of silently replaying the old values."""
+        model, optimizer, grad_hook, batch_shape = self.model, self.optimizer, self._grad_hook, self._batch_shape
+        self._captured_hyper = self._hyper()
+        self.engine = model.engine() if model.conv_impl == 2 else None      # the graph writes into its buffers
         flat = model.flatten_parameters()
         dev = flat['params'].device
         self.c = torch.zeros(tuple(batch_shape), dtype=torch.float32, device=dev)
@@ -66,10 +82,54 @@ class GraphedTrainStep(object):
         torch.cuda.synchronize(dev)
 
     def __call__(self, c):
+        if self._hyper() != self._captured_hyper:
+            torch.cuda.synchronize(self.c.device)
+            self.graph.reset()
+            self._capture()
         if self.model.__dict__.get('_grads_dirty', True):
             self.optimizer.zero_grad()
         self.c.copy_(c.reshape(self.c.shape), non_blocking=True)
         self.graph.replay()
+        return self.losses
+
+
+class GraphedLossAndGrads(object):
+    """Forward + the three loss terms + backward of ``train_vqvae`` as one CUDA graph, for ANY ``torch.optim``
+    optimizer: ``fb = GraphedLossAndGrads(model, (B, 1, n_mels, T), beta); losses = fb(c); optimizer.step()``.
+
+    The replay clears and refills the model's flat gradient buffer, whose slices are the parameters' ``.grad``
+    (re-bound on every call, so ``optimizer.zero_grad(set_to_none=True)`` between calls is harmless and unnecessary).
+    The reference's own ``optim.Adam(model.parameters())`` (main.py:124) therefore trains with one graph launch plus
+    its own (foreach) update kernels per iteration."""
+
+    def __init__(self, model, batch_shape, beta=1.0):
+        self.model, self.beta = model, float(beta)
+        flat = model.flatten_parameters()
+        dev = flat['params'].device
+        self.c = torch.zeros(tuple(batch_shape), dtype=torch.float32, device=dev)
+        bufs = [b for _, b in model.named_buffers()]
+        saved = [t.clone() for t in bufs]
+        self._body()                        # configures every kernel variant outside the capture
+        torch.cuda.synchronize(dev)
+        for t, s_ in zip(bufs, saved):
+            t.copy_(s_)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.losses, self.outputs = self._body()
+        torch.cuda.synchronize(dev)
+        for t, s_ in zip(bufs, saved):
+            t.copy_(s_)
+        flat['grads'].zero_()
+
+    def _body(self):
+        self.model._flat['grads'].zero_()
+        return self.model.loss_and_grads(self.c, beta=self.beta)
+
+    def __call__(self, c):
+        self.model.bind_grads()
+        self.c.copy_(c.reshape(self.c.shape), non_blocking=True)
+        self.graph.replay()
+        self.model.__dict__['_grads_dirty'] = True
         return self.losses
 
 

@@ -50,7 +50,7 @@ def build_parser():
     parser.add_argument('--resume', action='store_true', default=False,
                         help='load ./models/<model>/checkpoint_<dataset>_<dim>_<z_dim>.pth.tar before training')
     parser.add_argument('--fp32', action='store_true', default=False,
-                        help='fp32 parity engine instead of the bf16 TMA engine')
+                        help='fp32 parity engine instead of the automatic choice (bf16 TMA engine when dim == 64)')
     return parser
 
 
@@ -132,10 +132,13 @@ def main(argv=None):
     train_loader, test_loader = get_loaders(args)
     input_dim = 3 if args.dataset == 'CIFAR10' else 1                                  # main.py:100-116
     model = VQVAE(input_dim, args.dim, args.z_dim).to(device)
-    if not args.fp32:
-        model.act_dtype, model.conv_impl, model.vq_mode = torch.bfloat16, 2, 1
+    if args.fp32:
+        model.set_precision('fp32')
+    elif model.conv_impl != 2:
+        # the reference's own default --dim 1, or any dim other than 64, is served by the general fp32 kernels
+        print('--dim %d: the bf16 tensor-core engine serves dim == 64; running the fp32 CUDA-core engine' % args.dim)
     print(model)
-    optimizer = Adam(model, lr=args.lr_rate)                                          # main.py:124
+    optimizer = Adam(model.parameters(), lr=args.lr_rate)                              # main.py:124
     last_epoch = 0
     if args.resume:
         ck = torch.load(checkpoint_path(args), map_location=device)

@@ -10,6 +10,8 @@ kernel schedule of ``engine.Engine``.
 Returned activations have the reference's logical NCHW shape over NHWC
 (channels-last) storage.
 """
+import weakref
+
 import torch
 from torch import nn
 from torch.autograd import Function
@@ -190,11 +192,73 @@ class VQVAE(nn.Module):
 
         self.apply(weights_init)
         self.input_dim, self.dim, self.z_dim = input_dim, dim, z_dim
-        # execution options (not part of the reference API)
-        self.act_dtype = torch.float32      # torch.bfloat16 selects bf16 activations
-        self.conv_impl = 0                  # 1 = tcgen05 convolutions (dim == 64, bf16)
-        self.vq_mode = 0                    # 1 = tcgen05 split-bf16 search
+        # execution options (not part of the reference API).  None = automatic: the production engine -- bf16
+        # operand-ready activations, TMA-fed tcgen05 convolutions (conv_impl 2), tcgen05 split-bf16 search (vq_mode 1)
+        # -- wherever the shape is served (dim == 64; search: D == 64, K <= 8192), the general fp32 kernels otherwise.
+        # ``set_precision('fp32')`` pins the fp32 parity engine; explicit values always win.
+        self._act_dtype = None              # torch.float32 / torch.bfloat16
+        self._conv_impl = None              # 0 = CUDA-core fp32, 1 = register-staged tcgen05, 2 = TMA-fed tcgen05 (bf16)
+        self._vq_mode = None                # 0 = exact fp32 CUDA-core search, 1 = tcgen05 split-bf16 search
         self._flat = None
+        for p in self.parameters():         # optim.Adam(model.parameters()) finds the model that owns the flat buffers
+            p._nsg_owner = weakref.ref(self)
+
+    # ------------------------------------------------------------------ execution options
+    def _auto(self):
+        """(act_dtype, conv_impl, vq_mode) of the automatic choice for this model's shape."""
+        if self.dim == 64:
+            vq = 1 if ops.vq_mode_serves(self.z_dim, self.dim, 1) else 0
+            return torch.bfloat16, 2, vq
+        return torch.float32, 0, (1 if ops.vq_mode_serves(self.z_dim, self.dim, 1) else 0)
+
+    @property
+    def conv_impl(self):
+        if self._conv_impl is not None:
+            return self._conv_impl
+        if self._act_dtype is not None:     # an explicit activation type picks the best engine that computes in it
+            return 2 if (self._act_dtype == torch.bfloat16 and self.dim == 64) else 0
+        return self._auto()[1]
+
+    @conv_impl.setter
+    def conv_impl(self, v):
+        self._conv_impl = v
+
+    @property
+    def act_dtype(self):
+        if self._act_dtype is not None:
+            return self._act_dtype
+        if self._conv_impl is not None:
+            return torch.bfloat16 if self._conv_impl == 2 else torch.float32
+        return self._auto()[0]
+
+    @act_dtype.setter
+    def act_dtype(self, v):
+        self._act_dtype = v
+
+    @property
+    def vq_mode(self):
+        if self._vq_mode is not None:
+            return self._vq_mode
+        if self._conv_impl == 0 and self._act_dtype in (None, torch.float32):
+            return 0                        # the pinned fp32 parity engine keeps the exact CUDA-core search
+        return self._auto()[2]
+
+    @vq_mode.setter
+    def vq_mode(self, v):
+        self._vq_mode = v
+
+    def set_precision(self, mode):
+        """'auto' (default: the production engine where served), 'bf16' (TMA engine; raises later if dim != 64) or
+        'fp32' (CUDA-core fp32 parity engine, exact search)."""
+        if mode == 'auto':
+            self._act_dtype = self._conv_impl = self._vq_mode = None
+        elif mode == 'bf16':
+            self._act_dtype, self._conv_impl, self._vq_mode = torch.bfloat16, 2, None
+        elif mode == 'fp32':
+            self._act_dtype, self._conv_impl, self._vq_mode = torch.float32, 0, 0
+        else:
+            raise ValueError("set_precision: 'auto', 'bf16' or 'fp32' (got %r)" % (mode,))
+        return self
 
     # ------------------------------------------------------------------ plumbing
     def engine(self):
@@ -343,7 +407,21 @@ class VQVAE(nn.Module):
         else:
             eng.finish_backward(ectx, G)
         losses = ops.loss_finalize(sums, 1.0 / (b * h * w), 1.0 / z_e.numel())
+        self.__dict__['_last_ctx'] = ectx       # saved activations of the last step (tests read the ReLU patterns)
         return losses, (_nchw_view(xt32), _nchw_view(z_e), _nchw_view(z_q), idx)
+
+    def relu_patterns(self):
+        """{ReLU name: bool (B,C,H,W)} -- the activation pattern of the last ``loss_and_grads`` on the TMA engine, in
+        the reference module naming ('encoder.1', '<block>.in', '<block>.block.3', 'decoder.2',
+        'decoder.5').  Debug / test aid: lets a reference evaluate the same piecewise-linear branch."""
+        ctx = self.__dict__.get('_last_ctx')
+        if ctx is None or not hasattr(ctx, 'v0'):
+            raise ops.A.NsgError('relu_patterns: no saved TMA-engine step')
+        pat = {'encoder.1': ctx.v0, 'decoder.2': ctx.rd, 'decoder.5': ctx.v4}
+        for blk in RES_BLOCKS:
+            r, _, v1, _ = ctx.saved[blk]
+            pat[blk + '.in'], pat[blk + '.block.3'] = r, v1
+        return {k: _nchw_view(v > 0) for k, v in pat.items()}
 
 
 class _VQVAEFn(Function):

@@ -5,14 +5,20 @@ from . import ops
 
 
 class Adam(torch.optim.Optimizer):
-    """Drop-in for ``torch.optim.Adam(model.parameters(), lr=...)`` on a ``VQVAE``.
+    """Drop-in for ``torch.optim.Adam(model.parameters(), lr=...)`` on a ``VQVAE`` (main.py:124).
 
-    Construct with ``Adam(model, lr=1e-3)``.  ``step()`` is ONE kernel over every parameter (plus a
-    one-thread step-counter tick), with defaults betas=(0.9, 0.999), eps=1e-8, no weight decay, no amsgrad --
-    the configuration the reference uses.  ``grad_scale`` is multiplied into the gradients (1/world for DP).
+    Construct exactly as the reference does, ``Adam(model.parameters(), lr=1e-3)`` (the parameters must be ALL the
+    parameters of one ``VQVAE``: the model that owns them is found through the back-reference its constructor leaves
+    on each parameter), or with the model itself, ``Adam(model, lr=1e-3)``.  ``step()`` is ONE kernel over every
+    parameter (plus a one-thread step-counter tick), with defaults betas=(0.9, 0.999), eps=1e-8, no weight decay, no
+    amsgrad -- the configuration the reference uses.  ``grad_scale`` is multiplied into the gradients (1/world for DP).
     """
 
-    def __init__(self, model, lr=1e-3, betas=(0.9, 0.999), eps=1e-8):
+    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0, amsgrad=False):
+        if weight_decay != 0 or amsgrad:
+            raise ValueError('optim.Adam: weight_decay / amsgrad are not implemented by the fused step '
+                             '(the reference uses neither, main.py:124)')
+        model = params if isinstance(params, torch.nn.Module) else self._owner(params)
         self.model = model
         flat = model.flatten_parameters()
         # the remaining keys are torch.optim.Adam's own defaults, carried so that state_dict() is interchangeable with
@@ -25,6 +31,24 @@ class Adam(torch.optim.Optimizer):
         self.exp_avg_sq = torch.zeros_like(flat['params'])
         self.step_count = torch.zeros((), dtype=torch.int64, device=dev)
         self.grad_scale = 1.0
+
+    @staticmethod
+    def _owner(params):
+        params = list(params)
+        if len(params) == 0:
+            raise ValueError('optim.Adam: empty parameter list')
+        if isinstance(params[0], dict):
+            raise ValueError('optim.Adam: one parameter group (model.parameters()) expected, as main.py:124 passes')
+        ref = getattr(params[0], '_nsg_owner', None)
+        model = ref() if ref is not None else None
+        if model is None:
+            raise TypeError('optim.Adam: these are not the parameters of a neural_sound_generation_b200.VQVAE; '
+                            'use torch.optim.Adam for other modules')
+        mine = list(model.parameters())
+        if len(mine) != len(params) or any(a is not b for a, b in zip(mine, params)):
+            raise ValueError('optim.Adam: expected ALL parameters of the model, in model.parameters() order '
+                             '(got %d of %d)' % (len(params), len(mine)))
+        return model
 
     def zero_grad(self, set_to_none=False):
         self.model.flatten_parameters()

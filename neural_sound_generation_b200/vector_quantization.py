@@ -10,8 +10,15 @@ from torch.autograd import Function
 
 from . import ops
 
-# 0 = exact fp32 CUDA-core search, 1 = tcgen05 split-bf16 tensor-core search (default once validated)
-DEFAULT_MODE = 0
+# None = automatic: the tcgen05 split-bf16 tensor-core search (mode 1: top-2 candidates re-scored exactly in fp32,
+# lowest index on ties) whenever it serves the shape, else the exact fp32 CUDA-core search (mode 0).  Set to 0 / 1 to pin.
+DEFAULT_MODE = None
+
+
+def _mode(codebook):
+    if DEFAULT_MODE is not None:
+        return DEFAULT_MODE
+    return 1 if ops.vq_mode_serves(codebook.size(0), codebook.size(1), 1) else 0
 
 
 def _prep(inputs, codebook):
@@ -39,7 +46,7 @@ class VectorQuantization(Function):
             raise RuntimeError('vq: last dim of inputs (%d) != embedding size (%d)' % (inputs.size(-1), d))
         n = inputs.numel() // d
         indices_flatten = torch.empty((n,), dtype=torch.int64, device=inputs.device)
-        ops.vq_forward(inputs.detach(), cb, indices_flatten, None, None, mode=DEFAULT_MODE)
+        ops.vq_forward(inputs.detach(), cb, indices_flatten, None, None, mode=_mode(cb))
         indices = indices_flatten.view(*inputs.size()[:-1])
         ctx.mark_non_differentiable(indices)
         return indices
@@ -62,7 +69,7 @@ class VectorQuantizationStraightThrough(Function):
         n = inputs.numel() // d
         indices_flatten = torch.empty((n,), dtype=torch.int64, device=inputs.device)
         codes = torch.empty_like(inputs)
-        ops.vq_forward(inputs.detach(), cb, indices_flatten, codes, None, mode=DEFAULT_MODE)
+        ops.vq_forward(inputs.detach(), cb, indices_flatten, codes, None, mode=_mode(cb))
         ctx.save_for_backward(indices_flatten, codebook)
         ctx.mark_non_differentiable(indices_flatten)
         return (codes, indices_flatten)

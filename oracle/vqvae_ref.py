@@ -109,9 +109,19 @@ def make_mel(batch, n_mels, frames, seed, dtype=torch.float32):
 # layers
 # ----------------------------------------------------------------------------
 _RELU_MARGINS = None     # when a list: every _relu call appends min|x| / rms(x) of its input
+_FORCED_MASKS = None     # when an iterator: every _relu call multiplies by the next mask instead of thresholding
+_RECORD_MASKS = None     # when a list: every _relu call appends its own (x > 0) decision
 
 
 def _relu(x):
+    if _FORCED_MASKS is not None:
+        # teacher-forced activation pattern (step_grads(relu_masks=...)): relu(x) -> x * mask, d/dx = mask.  Removes
+        # the ReLU discontinuity from a comparison with an implementation whose pre-activations differ by rounding.
+        m = next(_FORCED_MASKS)
+        assert m.shape == x.shape, (tuple(m.shape), tuple(x.shape))
+        return x * m.to(x.dtype)
+    if _RECORD_MASKS is not None:
+        _RECORD_MASKS.append((x.detach() > 0))
     if _RELU_MARGINS is not None:
         with torch.no_grad():
             xd = x.detach().double()
@@ -140,6 +150,8 @@ def _bn(x, p, b, name, training, new_buffers):
     """nn.BatchNorm2d forward; train mode uses biased batch variance for the output and
     updates running stats with the unbiased one (torch semantics)."""
     w, bias = p[name + '.weight'], p[name + '.bias']
+    if x.dtype == torch.bfloat16:
+        x = x.float()        # under torch.autocast nn.BatchNorm2d computes in fp32 (autocast's fp32 op list)
     if training:
         mean = x.mean(dim=(0, 2, 3))
         var = x.var(dim=(0, 2, 3), unbiased=False)
@@ -242,21 +254,44 @@ def losses(x_tilde, z_e_x, z_q_x, c4, beta):
     return loss_recons, loss_vq, loss_commit, loss_recons + loss_vq + beta * loss_commit  # :134
 
 
-def step_grads(p, b, c, beta=1.0, training=True, indices=None):
+RELU_ORDER = (['encoder.1'] + [blk + s for blk in ('encoder.4', 'encoder.5', 'decoder.0', 'decoder.1')
+                                for s in ('.in', '.block.3')] + ['decoder.2', 'decoder.5'])
+"""Names of the 11 ReLUs of one forward in call order (state_dict-style: 'encoder.4.in' = the ResBlock's in-place
+leading ReLU, models.py:149; 'encoder.4.block.3' = the ReLU after its first BatchNorm).  ``relu_masks`` follows it."""
+
+
+def step_grads(p, b, c, beta=1.0, training=True, indices=None, relu_masks=None, autocast=None):
     """One forward/backward of the train step on mel batch ``c`` (B, n_mels, T).
+
+    ``indices``: teacher-forced codebook indices (B, H, W).  ``relu_masks``: dict RELU_ORDER name -> {0,1} mask (NCHW)
+    that replaces each ReLU's own threshold decision (forward x*mask, backward mask).  ``autocast``: a dtype
+    (torch.bfloat16) to run forward + losses under ``torch.autocast('cpu', dtype)`` -- what the reference modules do
+    under autocast; it is the yardstick for a reduced-precision implementation.
 
     Returns dict(outputs, losses, grads, new_buffers).
     """
+    global _FORCED_MASKS, _RECORD_MASKS
+    import contextlib
     p = {k: v.detach().clone().requires_grad_(True) for k, v in p.items()}
     nb = dict(b)
     c4 = c.unsqueeze(1)                                                  # train.py:115
-    x_tilde, z_e_x, z_q_x, idx = forward(p, b, c4, training, nb, indices)
-    lr, lv, lc, loss = losses(x_tilde, z_e_x, z_q_x, c4, beta)
+    _FORCED_MASKS = iter([relu_masks[n] for n in RELU_ORDER]) if relu_masks is not None else None
+    _RECORD_MASKS = [] if relu_masks is None else None
+    try:
+        with (torch.autocast('cpu', dtype=autocast) if autocast is not None else contextlib.nullcontext()):
+            x_tilde, z_e_x, z_q_x, idx = forward(p, b, c4, training, nb, indices)
+            if autocast is not None:     # the reference's F.mse_loss under autocast runs in fp32
+                x_tilde, z_e_x, z_q_x = x_tilde.float(), z_e_x.float(), z_q_x.float()
+            lr, lv, lc, loss = losses(x_tilde, z_e_x, z_q_x, c4, beta)
+    finally:
+        _FORCED_MASKS = None
+        own_masks, _RECORD_MASKS = _RECORD_MASKS, None
     loss.backward()
     grads = {k: (v.grad.detach() if v.grad is not None else torch.zeros_like(v)) for k, v in p.items()}
     return dict(x_tilde=x_tilde.detach(), z_e_x=z_e_x.detach(), z_q_x=z_q_x.detach(), indices=idx,
                 loss_recons=lr.detach(), loss_vq=lv.detach(), loss_commit=lc.detach(), loss=loss.detach(),
-                grads=grads, buffers=nb)
+                grads=grads, buffers=nb,
+                relu_masks=dict(zip(RELU_ORDER, own_masks)) if own_masks is not None else relu_masks)
 
 
 def adam_init(p):

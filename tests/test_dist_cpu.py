@@ -152,7 +152,7 @@ def test_dataparallel_requires_process_group():
     with pytest.raises(RuntimeError):
         nd.DataParallel()
     # a model with a dp object but not the TMA engine refuses to run instead of silently ignoring it
-    m = nsg.VQVAE(1, 64, 512)
+    m = nsg.VQVAE(1, 64, 512).set_precision('fp32')
     m.__dict__['dp'] = object()
     with pytest.raises(Exception):
         m.engine()

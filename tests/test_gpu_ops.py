@@ -283,7 +283,7 @@ def test_vq_c1_golden(golden_dir, tag, mode):
         gi, gc = vq_ref.vq_st_backward(gout, flat.cpu().numpy(), cb.shape)
         assert np.abs(cbt.grad.cpu().numpy() - gc).max() <= 1e-5 * np.abs(gc).max()
     finally:
-        nsg.vector_quantization.DEFAULT_MODE = 0
+        nsg.vector_quantization.DEFAULT_MODE = None
 
 
 @pytest.mark.parametrize('mode', [0, 1])
@@ -298,13 +298,65 @@ def test_vq_ties_and_errors(golden_dir, mode):
     try:
         idx = _skip_if_tc_missing(lambda: nsg.vq(torch.tensor(z, device=DEV), torch.tensor(cb, device=DEV)))
     finally:
-        nsg.vector_quantization.DEFAULT_MODE = 0
+        nsg.vector_quantization.DEFAULT_MODE = None
     assert np.array_equal(idx.cpu().numpy(), g['ties/indices'].astype(np.int64))
     with pytest.raises(RuntimeError, match='VectorQuantization'):
         nsg.vector_quantization.VectorQuantization.backward(None, None)
     assert str(g['vq_backward_message']).startswith('Trying to call `.grad()`')
     with pytest.raises(RuntimeError):
         nsg.vq(torch.zeros(4, 6, device=DEV).t(), torch.zeros(3, 4, device=DEV))   # non-contiguous like .view
+
+
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize('k,dups', [
+    (512, [(3, 300, 511)]),                      # three equal codewords, both sides of the 256-column MMA boundary
+    (512, [(0, 255), (256, 257), (100, 400)]),   # pairs inside one N=256 MMA, adjacent, and straddling the boundary
+    (1024, [(7, 519), (300, 800, 1023)]),        # duplicates in different 512-codeword chunks (streaming kernel)
+    (8192, [(1, 4097, 8191), (512, 513)]),
+])
+def test_vq_tensor_core_lowest_index_ties(k, dups, dtype):
+    """Exact duplicate codewords through the tcgen05 search (vq_search_res_kernel for K <= 512, vq_search_tc_kernel
+    above): rows equal to a duplicated codeword must come back with the LOWEST index, as torch.min returns on CPU
+    (vector_quantization.py:19) -- the top-2 trackers and the fp32 re-score are where a later duplicate
+    could win."""
+    d = 64
+    rng = np.random.RandomState(k + len(dups))
+    cb = rng.standard_normal((k, d)).astype(np.float32)
+    if dtype == torch.bfloat16:
+        cb = torch.tensor(cb).bfloat16().float().numpy()          # rows of z equal to codewords stay equal in bf16
+    rows, want = [], []
+    for group in dups:
+        for j in group[1:]:
+            cb[j] = cb[group[0]]
+        for _ in range(40):                                        # spread over several 128-row tiles
+            rows.append(cb[group[0]].copy())
+            want.append(group[0])
+    filler = rng.standard_normal((700, d)).astype(np.float32)
+    order = rng.permutation(len(rows) + len(filler))
+    z = np.concatenate([np.stack(rows), filler], 0)[order]
+    want_all = np.concatenate([np.array(want), -np.ones(len(filler), dtype=np.int64)])[order]
+    zt = torch.tensor(z, device=DEV).to(dtype)
+    idx = torch.empty(z.shape[0], dtype=torch.int64, device=DEV)
+    assert ops.vq_mode_serves(k, d, 1), 'the tcgen05 search must serve D = 64, K <= 8192'
+    ops.vq_forward(zt, torch.tensor(cb, device=DEV), idx, None, None, mode=1)
+    torch.cuda.synchronize()
+    got = idx.cpu().numpy()
+    sel = want_all >= 0
+    assert np.array_equal(got[sel], want_all[sel]), (got[sel][:16], want_all[sel][:16])
+    ref = vq_ref.vq_indices(zt.float().cpu().numpy(), cb)
+    n_mis, n_viol = vq_ref.index_parity(got, ref, zt.float().cpu().numpy(), cb)
+    assert n_viol == 0, (n_mis, n_viol)
+    # near-duplicates: the later copy is closer by one ulp in one coordinate -> it must win for z equal to it
+    cb2 = cb.copy()
+    g0 = dups[0]
+    cb2[g0[1]] = cb2[g0[0]]
+    cb2[g0[1], 5] = np.nextafter(cb2[g0[1], 5], np.float32(10.0))
+    z2 = np.stack([cb2[g0[1]]] * 130).astype(np.float32)
+    if dtype == torch.float32:                                    # (bf16 inputs cannot represent the one-ulp neighbour)
+        idx2 = torch.empty(130, dtype=torch.int64, device=DEV)
+        ops.vq_forward(torch.tensor(z2, device=DEV), torch.tensor(cb2, device=DEV), idx2, None, None, mode=1)
+        n_mis, n_viol = vq_ref.index_parity(idx2.cpu().numpy(), vq_ref.vq_indices(z2, cb2), z2, cb2)
+        assert n_viol == 0
 
 
 @pytest.mark.parametrize('n,k,d', [(1, 1, 1), (5, 3, 1), (100, 17, 7), (333, 512, 64), (4096, 1024, 128), (257, 640, 256)])

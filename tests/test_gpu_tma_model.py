@@ -16,7 +16,7 @@ pytestmark = pytest.mark.gpu
 
 if torch.cuda.is_available():
     import neural_sound_generation_b200 as nsg
-    from oracle import vqvae_ref as R
+    from oracle import vq_ref, vqvae_ref as R
 
 DEV = 'cuda'
 
@@ -193,3 +193,153 @@ def test_graphed_inference_config5_shape():
         xt_ref = R.decode(p, b, lat_g.cpu())
         assert relerr(xt_g, xt_ref) < 3e-2
     assert not torch.equal(xt_g, infer(xs[0].to(DEV))[1])
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# The benchmarked configuration (BASELINE.json configs[1]: 32 x 80 x 256, bf16 TMA engine, tcgen05 search) against the
+# oracle on the same seed.  Three comparisons, each against a yardstick MEASURED IN THIS TEST on the same inputs -- the
+# oracle itself under torch.autocast(bfloat16), i.e. what the reference modules do in bf16 -- never against constants:
+#   free-running   : z_e error and index disagreement vs the fp32 oracle <= 1.5 x the autocast oracle's;
+#   teacher-forced : the fp32 oracle quantises with OUR indices and takes OUR ReLU patterns, which removes both
+#                    discontinuities (argmin, ReLU threshold); x_tilde, the three losses and every gradient are then
+#                    held to max(2e-3, the autocast oracle's error under ITS OWN forced indices + patterns);
+#   exactness      : codes == bf16(codebook[idx]) bit for bit.
+# ---------------------------------------------------------------------------------------------------------------------
+def _skip_bias(name):
+    return name.endswith('.bias') and ('block.1' in name or 'block.4' in name or name in ('encoder.0.bias', 'decoder.3.bias'))
+
+
+@pytest.mark.parametrize('codebook,batch,frames,seed', [('spread', 32, 256, 21), ('init', 2, 30, 1)])
+def test_tma_benchmarked_config_vs_oracle(codebook, batch, frames, seed):
+    torch.set_num_threads(max(1, min(16, torch.get_num_threads())))
+    p, b = R.make_state(1, 64, 512, seed, codebook=codebook)
+    mel = R.make_mel(batch, 80, frames, seed + 1)
+    m = nsg.VQVAE(1, 64, 512)
+    sd = dict(p)
+    sd.update(b)
+    m.load_state_dict({k: v.clone() for k, v in sd.items()}, strict=True)
+    m = m.to(DEV).train()
+    assert (m.conv_impl, m.act_dtype, m.vq_mode) == (2, torch.bfloat16, 1)      # the automatic choice IS the product
+    opt = nsg.optim.Adam(m.parameters(), lr=1e-3)
+    opt.zero_grad()
+    losses, (xt, ze, zq, idx) = m.loss_and_grads(mel.to(DEV), beta=1.0)
+    torch.cuda.synchronize()
+    grads = {k: v.detach().cpu().clone() for k, v in m.grad_dict().items()}
+    masks = {k: v.cpu() for k, v in m.relu_patterns().items()}
+    free = R.step_grads(p, b, mel, beta=1.0)
+    auto = R.step_grads(p, b, mel, beta=1.0, autocast=torch.bfloat16)
+    shape = free['indices'].shape
+    # ---- free-running envelope
+    e_ze, e_ze_ref = relerr(ze.float(), free['z_e_x']), relerr(auto['z_e_x'].float(), free['z_e_x'])
+    mism = (idx.cpu().view(shape) != free['indices']).float().mean().item()
+    mism_ref = (auto['indices'] != free['indices']).float().mean().item()
+    print('[%s %dx80x%d] free-running: z_e %.3e (autocast oracle %.3e), index disagreement %.2f %% (autocast %.2f %%)'
+          % (codebook, batch, frames, e_ze, e_ze_ref, 100 * mism, 100 * mism_ref))
+    assert e_ze <= 1.5 * e_ze_ref
+    if codebook == 'spread':
+        assert mism <= 1.5 * mism_ref + 1e-3
+    # the indices we chose are the argmin for OUR z_e (tie rule of SURVEY.md section 8 c4 on identical inputs)
+    zf = ze.permute(0, 2, 3, 1).reshape(-1, 64).float().cpu().numpy()
+    cbn = p['codebook.embedding.weight'].numpy()
+    n_mis, n_viol = vq_ref.index_parity(idx.cpu().numpy(), vq_ref.vq_indices(zf, cbn), zf, cbn)
+    print('indices vs oracle argmin on our own z_e: %d differ, %d outside the 1e-6 tie rule' % (n_mis, n_viol))
+    assert n_viol == 0
+    assert torch.equal(zq.permute(0, 2, 3, 1).reshape(-1, 64).float().cpu(),
+                       p['codebook.embedding.weight'][idx.cpu()].bfloat16().float())
+    # ---- teacher-forced: indices + ReLU patterns
+    r = R.step_grads(p, b, mel, beta=1.0, indices=idx.cpu().view(shape), relu_masks=masks)
+    ra = R.step_grads(p, b, mel, beta=1.0, indices=auto['indices'], relu_masks=auto['relu_masks'])   # yardstick
+    rows = []
+
+    def check(name, ours, ref, theirs, ref_theirs):
+        e, e_ref = relerr(ours, ref), relerr(theirs, ref_theirs)
+        rows.append((name, e, e_ref))
+        assert e <= max(2e-3, 1.25 * e_ref), (name, e, e_ref)
+
+    check('x_tilde', xt.float(), r['x_tilde'], auto['x_tilde'].float(), ra['x_tilde'])
+    got = losses.tolist()
+    for i, k in enumerate(('loss_recons', 'loss_vq', 'loss_commit')):
+        check(k, torch.tensor(got[i]), r[k], auto[k].float(), ra[k])
+    for name, ref in r['grads'].items():
+        if _skip_bias(name):
+            continue        # bias before a BatchNorm: analytically zero gradient, rounding noise on both sides
+        check('grad ' + name, grads[name], ref, auto['grads'][name].float(), ra['grads'][name])
+    worst = max(rows, key=lambda t: t[1])
+    print('teacher-forced (indices + ReLU patterns): worst %s %.3e (autocast oracle %.3e); x_tilde %.3e (%.3e)'
+          % (worst[0], worst[1], worst[2], rows[0][1], rows[0][2]))
+    for name, e, e_ref in rows:
+        print('   %-34s ours %.3e   autocast-bf16 oracle %.3e' % (name, e, e_ref))
+    for name in R.bn_names():
+        got_rv = dict(m.named_buffers())[name + '.running_var'].cpu()
+        assert relerr(got_rv, r['buffers'][name + '.running_var']) < 3e-2, name
+
+
+def test_tma_multi_step_loss_curve_vs_oracle():
+    """20 iterations of the train_vqvae body (GraphedTrainStep, production engine) against the oracle's train_steps on
+    the same batches: a bf16 run cannot track an fp32 run index for index, so the statement is on the
+    loss curve: every logged loss within the envelope the autocast-bf16 oracle shows against the fp32 oracle over the
+    same 20 steps (x 1.5, floor 2 %), and the final weights as close to the fp32 oracle's as the autocast run's are."""
+    p, b = R.make_state(1, 64, 512, 31, codebook='spread')
+    batches = [R.make_mel(4, 80, 64, 200 + i) for i in range(20)]
+    m = nsg.VQVAE(1, 64, 512)
+    sd = dict(p)
+    sd.update(b)
+    m.load_state_dict({k: v.clone() for k, v in sd.items()}, strict=True)
+    m = m.to(DEV).train()
+    opt = nsg.optim.Adam(m.parameters(), lr=1e-3)
+    step = nsg.GraphedTrainStep(m, opt, (4, 1, 80, 64), beta=1.0)
+    ours = [step(c.to(DEV)).tolist() for c in batches]
+    torch.cuda.synchronize()
+    pf, bf_, logf = R.train_steps(p, b, batches, beta=1.0, lr=1e-3)
+    # yardstick: the oracle with the forward/backward under autocast(bf16), fp32 master weights + Adam
+    pa, ba, st = dict(p), dict(b), R.adam_init(p)
+    loga = []
+    for c in batches:
+        ra = R.step_grads(pa, ba, c, 1.0, autocast=torch.bfloat16)
+        pa = R.adam_step(pa, {k: v.float() for k, v in ra['grads'].items()}, st, 1e-3)
+        ba = ra['buffers']
+        loga.append(ra)
+    worst, worst_ref = 0.0, 0.0
+    for i in range(20):
+        for j, k in enumerate(('loss_recons', 'loss_vq', 'loss_commit')):
+            ref = logf[i][k].item()
+            e, e_ref = abs(ours[i][j] - ref) / abs(ref), abs(loga[i][k].item() - ref) / abs(ref)
+            worst, worst_ref = max(worst, e), max(worst_ref, e_ref)
+    print('20-step loss curve: worst relative deviation from the fp32 oracle %.3e (autocast-bf16 oracle: %.3e)'
+          % (worst, worst_ref))
+    assert worst <= max(2e-2, 1.5 * worst_ref)
+    assert ours[-1][0] < ours[0][0]                                   # it trains: reconstruction loss goes down
+    sdm = m.state_dict()
+    for name in ('encoder.3.weight', 'decoder.3.weight', 'codebook.embedding.weight', 'decoder.6.weight'):
+        e, e_ref = relerr(sdm[name], pf[name]), relerr(pa[name], pf[name])
+        print('   weights after 20 steps %-28s ours %.3e   autocast-bf16 oracle %.3e' % (name, e, e_ref))
+        assert e <= max(2e-3, 1.5 * e_ref), (name, e, e_ref)
+
+
+def test_tma_generic_autograd_after_fused_step():
+    """model(c) + loss.backward() through the autograd boundary (_VQVAEFn) on the TMA engine, after fused steps have
+    left their consumed weight-gradient images behind: the gradients must equal those of a fused step on the same
+    batch (stale images were added onto), twice in a row."""
+    p, b, mel = _state(seed=17)
+    m = _model(p, b, 2)
+    opt = nsg.optim.Adam(m.parameters(), lr=1e-3)
+    c = mel.to(DEV)
+    opt.zero_grad()
+    m.loss_and_grads(c, beta=1.0)
+    torch.cuda.synchronize()
+    fused = {k: v.clone() for k, v in m.grad_dict().items()}
+    bufs = {k: v.clone() for k, v in m.named_buffers()}
+    for rep in range(2):
+        for k, v in m.named_buffers():
+            v.copy_(bufs[k])
+        opt.zero_grad()
+        x_tilde, z_e_x, z_q_x = m(c.unsqueeze(1))
+        loss = (torch.nn.functional.mse_loss(x_tilde, c.unsqueeze(1)) + torch.nn.functional.mse_loss(z_q_x, z_e_x.detach())
+                + torch.nn.functional.mse_loss(z_e_x, z_q_x.detach()))
+        loss.backward()
+        torch.cuda.synchronize()
+        for name, q in m.named_parameters():
+            if _skip_bias(name):
+                continue
+            # (the generic path hands fp32 copies of z_e / z_q / x_tilde to torch's loss: bf16-level differences)
+            assert relerr(q.grad, fused[name]) < 2e-2, (rep, name, relerr(q.grad, fused[name]))
