@@ -97,6 +97,47 @@ typedef struct {
                              * the in-place ReLU that opens the next ResBlock, models.py:149) */
 } nsg_epilogue;
 
+/* BatchNorm fused into the producing convolution (nsg_conv_bn_tma; replaces the conv -> nn.BatchNorm2d -> ReLU
+ * [-> residual add] chains of models.py:150-158 and their autograd mirror by ONE launch each):
+ *   NSG_BNF_EVAL   running statistics folded into the output affine of the ordinary (streaming) kernel:
+ *                  out = epilogue(gamma*(conv + bias - running_mean)/sqrt(running_var + eps) + beta), where epilogue =
+ *                  the nsg_epilogue add_src / mask / ReLU as usual.
+ *   NSG_BNF_TRAIN  batch statistics: every tile's fp32 accumulator stays in TMEM, the CTAs of the persistent grid sum
+ *                  their moments into epi->stats (NSG_STATS_MOMENTS, zeroed by the caller), meet at `barrier`, then
+ *                  out2 = [relu]([res +] gamma*(h - mean)*invstd + beta) with h = conv + bias; `out` (nullable) receives h
+ *                  (the backward pass reads it); running statistics / num_batches_tracked updated as torch does;
+ *                  coef (nullable, [4][64]) receives mean | invstd | scale | shift.
+ *   NSG_BNF_BWD    g = epilogue(conv) (the data gradient: + add_src, ReLU mask), epi->stats (NSG_STATS_BNBWD with
+ *                  xhat_src = h, mean, invstd of the BatchNorm being differentiated) summed over the grid, barrier, then
+ *                  out2 = gamma*invstd*(g - sum_g/count - xhat*sum_gx/count); `out` (nullable) receives g;
+ *                  dgamma += sum_gx, dbeta += sum_g (nullable).
+ * TRAIN / BWD need every tile of a CTA to keep its accumulator: at most 8 tiles of 128 pixels per CTA of the
+ * SM-count-sized grid (nsg_conv_bn_tma_fits(g) == 1), else NSG_E_UNSUPPORTED -- run nsg_conv_gemm_tma + nsg_bn_act64 /
+ * nsg_bn_bwd64.  `barrier` is ONE unsigned counter per launch, zero before the launch.  The grid barrier relies on all
+ * CTAs being resident (grid <= SM count, one CTA per SM): do not run two such launches concurrently on one device
+ * from different streams. */
+#define NSG_BNF_NONE 0
+#define NSG_BNF_TRAIN 1
+#define NSG_BNF_EVAL 2
+#define NSG_BNF_BWD 3
+typedef struct {
+  int mode;
+  int relu_out;             /* TRAIN: ReLU on out2 */
+  const float* gamma;       /* [64] */
+  const float* beta;        /* [64] (TRAIN / EVAL) */
+  float eps, momentum;
+  double count;             /* elements per channel behind the statistics (pixels, x world size for synchronised BN) */
+  float* running_mean;      /* [64]; TRAIN: updated (nullable), EVAL: read */
+  float* running_var;
+  long long* num_batches_tracked;
+  float* coef;              /* TRAIN: [4][64] published coefficients (nullable) */
+  const void* res;          /* TRAIN: residual, same shape as the output (nullable) */
+  unsigned int* barrier;    /* TRAIN / BWD */
+  float* dgamma;            /* BWD (nullable) */
+  float* dbeta;
+  void* out2;               /* TRAIN / BWD: second output, 32-byte aligned */
+} nsg_bn_fuse;
+
 /* CUDA-core fp32-accumulate kernel, any shape.  `impl` must be 0 (kept for ABI stability). */
 int nsg_conv_gemm(const nsg_conv_geom* g, const void* in, const float* w, const nsg_prologue* pro,
                   const nsg_epilogue* epi, void* out, int impl, void* stream);
@@ -163,6 +204,9 @@ int nsg_conv_pack_many(int n, const float* const* w, void* const* packed, const 
                        const long long* w_cin_stride, const long long* w_cout_stride, void* stream);
 int nsg_conv_gemm_tma(const nsg_conv_geom* g, const void* in, const void* packed_w, const nsg_epilogue* epi, void* out,
                       void* stream);
+int nsg_conv_bn_tma(const nsg_conv_geom* g, const void* in, const void* packed_w, const nsg_epilogue* epi,
+                    const nsg_bn_fuse* bn, void* out, void* stream);
+int nsg_conv_bn_tma_fits(const nsg_conv_geom* g);
 int nsg_conv_wgrad_tma(const nsg_conv_geom* g, const void* p, const void* q, float* dw_packed, float* q_colsum,
                        void* stream);
 /* Programmatic dependent launch (every kernel of this library): 1 (default) lets a kernel become resident and run its

@@ -26,6 +26,7 @@ EXPORTS = [
     'nsg_conv_wgrad_slices', 'nsg_conv_wgrad_tma_sliced', 'nsg_pdl', 'nsg_recon_loss_bf16', 'nsg_loss_finalize',
     'nsg_bn_act64', 'nsg_bn_bwd64', 'nsg_relu64', 'nsg_vq_bwd_stats64', 'nsg_debug_timeline',
     'nsg_c1_conv_tc', 'nsg_c1_convT_tc', 'nsg_c1_wgrad_tc', 'nsg_scatter_mode', 'nsg_ema_update', 'nsg_vq_resident',
+    'nsg_conv_bn_tma', 'nsg_conv_bn_tma_fits',
 ]
 
 
@@ -44,6 +45,14 @@ class Epilogue(C.Structure):
     _fields_ = [('bias', C.c_void_p), ('add_src', C.c_void_p), ('mask_mode', C.c_int), ('mask_src', C.c_void_p),
                 ('mscale', C.c_void_p), ('mshift', C.c_void_p), ('stats_mode', C.c_int), ('stats', C.c_void_p),
                 ('xhat_src', C.c_void_p), ('mean', C.c_void_p), ('invstd', C.c_void_p), ('tanh_out', C.c_int)]
+
+
+class BnFuse(C.Structure):
+    _fields_ = [('mode', C.c_int), ('relu_out', C.c_int), ('gamma', C.c_void_p), ('beta', C.c_void_p),
+                ('eps', C.c_float), ('momentum', C.c_float), ('count', C.c_double), ('running_mean', C.c_void_p),
+                ('running_var', C.c_void_p), ('num_batches_tracked', C.c_void_p), ('coef', C.c_void_p),
+                ('res', C.c_void_p), ('barrier', C.c_void_p), ('dgamma', C.c_void_p), ('dbeta', C.c_void_p),
+                ('out2', C.c_void_p)]
 
 
 class NsgError(RuntimeError):
@@ -81,6 +90,8 @@ def load():
     lib.nsg_c1_wgrad_tc.argtypes = [C.POINTER(ConvGeom), vp, vp, vp, vp, vp]
     lib.nsg_conv_pack_many.argtypes = [i, vp, vp, vp, vp, vp, vp]
     lib.nsg_conv_gemm_tma.argtypes = [C.POINTER(ConvGeom), vp, vp, C.POINTER(Epilogue), vp, vp]
+    lib.nsg_conv_bn_tma.argtypes = [C.POINTER(ConvGeom), vp, vp, C.POINTER(Epilogue), C.POINTER(BnFuse), vp, vp]
+    lib.nsg_conv_bn_tma_fits.argtypes = [C.POINTER(ConvGeom)]
     lib.nsg_conv_wgrad_tma.argtypes = [C.POINTER(ConvGeom), vp, vp, vp, vp, vp]
     lib.nsg_wgrad_unpack_many.argtypes = [i, vp, vp, vp, vp, vp, vp, vp]
     lib.nsg_pdl.argtypes = [i]

@@ -45,7 +45,9 @@ int conv_gemm_tc(const nsg_conv_geom* cg, const void* in, const void* packed, co
 int conv_wgrad_tc(const nsg_conv_geom* cg, const void* p, const nsg_prologue* pro_p, const void* q,
                   const nsg_prologue* pro_q, float* dw, float* q_colsum, int passes, cudaStream_t stream);
 
-int conv_gemm_tma(const nsg_conv_geom* cg, const void* in, const void* packed, const nsg_epilogue* epi, void* out,
+int conv_bn_tma_fits(const nsg_conv_geom* cg);
+int conv_gemm_tma(const nsg_conv_geom* cg, const void* in, const void* packed, const nsg_epilogue* epi,
+                  const nsg_bn_fuse* bnf, void* out,
                   cudaStream_t stream);
 int debug_timeline(int enable, unsigned long long* host_out);
 int conv_c1_tc(const nsg_conv_geom* cg, const void* in, const void* packed, const nsg_epilogue* epi, void* out,
@@ -194,7 +196,20 @@ int nsg_conv_gemm_tma(const nsg_conv_geom* g, const void* in, const void* packed
   int rc = check_geom(g);
   if (rc) return rc;
   NSG_REQUIRE(in && packed_w && out, "conv_gemm_tma: null pointer");
-  return conv_gemm_tma(g, in, packed_w, epi, out, (cudaStream_t)stream);
+  return conv_gemm_tma(g, in, packed_w, epi, nullptr, out, (cudaStream_t)stream);
+}
+
+int nsg_conv_bn_tma(const nsg_conv_geom* g, const void* in, const void* packed_w, const nsg_epilogue* epi,
+                    const nsg_bn_fuse* bn, void* out, void* stream) {
+  int rc = check_geom(g);
+  if (rc) return rc;
+  NSG_REQUIRE(in && packed_w, "conv_bn_tma: null pointer");
+  return conv_gemm_tma(g, in, packed_w, epi, bn, out, (cudaStream_t)stream);
+}
+
+int nsg_conv_bn_tma_fits(const nsg_conv_geom* g) {
+  if (check_geom(g)) return 0;
+  return conv_bn_tma_fits(g);
 }
 
 int nsg_c1_conv_tc(const nsg_conv_geom* g, const void* in, const void* packed_w, const nsg_epilogue* epi, void* out,

@@ -38,7 +38,7 @@ constexpr int TM_TILE_TABLE = 32;
 // M128 N64 K16), so independent chains buy nothing: 1.
 constexpr int TM_CHAINS = 1;
 constexpr int TM_ACC_COLS = TM_CHAINS * TM_C;       // TMEM columns per tile accumulator set                 // local tiles with precomputed coordinates (more: decoded on the fly)
-constexpr uint32_t TM_SMEM_LIMIT = 224 * 1024;      // dynamic part; the kernels also hold ~2 KB of static shared memory
+constexpr uint32_t TM_SMEM_LIMIT = 223 * 1024;      // dynamic part; the kernels also hold <= 4 KB of static shared memory
 
 // Taps that differ only by a vertical shift share ONE activation box: a "group" is (tensor map, horizontal shift,
 // first row) and its box holds box_h + halo rows of box_w pixels; tap t of the group reads the 128-pixel sub-block
@@ -282,17 +282,110 @@ __device__ __forceinline__ TmaTile fetch_tile(const TmaConvParams& P, const int4
   return decode_tile(P, (int)blockIdx.x + i * (int)gridDim.x);
 }
 
+// BatchNorm fused across a grid barrier (NACC > 2, "hold" launches).  A CTA of the persistent grid owns at most NACC
+// tiles; their fp32 accumulators all stay in TMEM (NACC x 64 columns).  Pass 1 (overlapping the remaining MMAs) reads
+// each accumulator once for the per-channel sums -- BatchNorm moments of the convolution output (forward) or the
+// BatchNorm-backward reductions of the masked data gradient (backward) -- the CTAs meet at a counter in global memory,
+// and pass 2 reads the accumulators again and stores the tensor the NEXT convolution reads (normalised + ReLU
+// [+ residual] forward; dh = gamma*invstd*(g - mean(g) - xhat*mean(g*xhat)) backward).  The separate bn_act / bn_bwd
+// launch of fused_elem.cu and its read + write of the whole activation disappear (models.py:151-158).
+struct BnFuse {
+  int mode;                        // NSG_BNF_*
+  int relu_out;
+  const float* gamma;
+  const float* beta;
+  float eps, momentum;
+  double count;                    // elements per channel behind the statistics
+  float* running_mean;
+  float* running_var;
+  long long* nbt;
+  float* coef;                     // TRAIN: [4][64] mean | invstd | scale | shift published by CTA 0 (nullable)
+  const __nv_bfloat16* res;        // TRAIN: residual added after the normalisation (nullable)
+  unsigned int* barrier;           // zero-initialised counter of this launch
+  float* dgamma;
+  float* dbeta;
+  __nv_bfloat16* out2;
+};
+
+// All CTAs of the grid are resident (grid <= SM count, 1 CTA per SM; kernels running beside this one on other streams
+// never wait for it), so a counter + spin is a legal grid barrier.  A lost CTA must not hang the device: the spin is
+// bounded (~1 s) and traps.
+__device__ __forceinline__ void grid_barrier(unsigned int* ctr, unsigned int expected) {
+  __threadfence();
+  atomicAdd(ctr, 1u);
+  unsigned int v = 0;
+  for (long long spins = 0; spins < (1ll << 24); ++spins) {
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
+    if (v >= expected) break;
+    __nanosleep(64);
+  }
+  if (v < expected) __trap();
+  __threadfence();
+}
+
+// operands of one (row, 32-channel half): 64 bytes each
+__device__ __forceinline__ void ld_half(const void* src, long long o, uint4 (&r)[4]) {
+  const uint4* p = reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(src) + o);
+#pragma unroll
+  for (int g8 = 0; g8 < 4; ++g8) r[g8] = __ldg(p + g8);
+}
+// x[j] (op)= operand channel j
+__device__ __forceinline__ void add_half(float (&x)[32], const uint4 (&r)[4]) {
+#pragma unroll
+  for (int g8 = 0; g8 < 4; ++g8) {
+    float a[8];
+    unpack8bf(r[g8], a);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) x[g8 * 8 + j] += a[j];
+  }
+}
+__device__ __forceinline__ void mask_half(float (&x)[32], const uint4 (&r)[4], int mask_mode, const float* sPar, int ch0) {
+#pragma unroll
+  for (int g8 = 0; g8 < 4; ++g8) {
+    float mk[8];
+    unpack8bf(r[g8], mk);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int ch = ch0 + g8 * 8 + j;
+      const float mv = mask_mode == NSG_MASK_AFFINE ? fmaf(sPar[TM_C + ch], mk[j], sPar[2 * TM_C + ch]) : mk[j];
+      x[g8 * 8 + j] = mv > 0.f ? x[g8 * 8 + j] : 0.f;
+    }
+  }
+}
+// the streaming part of the epilogue for one (row, half): x = osc*acc + osh [+ add] [masked] [ReLU]
+__device__ __forceinline__ void epi_half(float (&x)[32], const uint32_t (&acc)[32], const EpiArgs& epi, const float* sPar,
+                                         long long oh, bool valid, int ch0, bool use_add, const uint4 (&radd)[4]) {
+#pragma unroll
+  for (int j = 0; j < 32; ++j)
+    x[j] = valid ? fmaf(__uint_as_float(acc[j]), sPar[5 * TM_C + ch0 + j], sPar[ch0 + j]) : 0.f;
+  if (use_add) add_half(x, radd);
+  if (valid && epi.mask_mode != NSG_MASK_NONE) {
+    uint4 rm[4];
+    ld_half(epi.mask_src, oh, rm);
+    mask_half(x, rm, epi.mask_mode, sPar, ch0);
+  }
+  if (epi.tanh_out == 2) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) x[j] = fmaxf(x[j], 0.f);
+  }
+}
+
+// NACC = 2: streaming (two accumulators, the epilogue of tile i overlaps the MMAs of tile i+1).  NACC = 4 / 8: hold
+// (every tile of the CTA keeps its own accumulator, BnFuse above).
+template <int NACC>
 __global__ void __launch_bounds__(320, 1)
 conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__ CUtensorMap tm1,
                 const __grid_constant__ CUtensorMap tm2, const __grid_constant__ CUtensorMap tm3,
-                const uint8_t* __restrict__ wimg, __nv_bfloat16* __restrict__ out, EpiArgs epi,
+                const uint8_t* __restrict__ wimg, __nv_bfloat16* __restrict__ out, EpiArgs epi, BnFuse bn,
                 const __grid_constant__ TmaConvParams P) {
+  constexpr bool HOLD = NACC > 2;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sm = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sW = sm;                                         // nw weight images
   uint8_t* sA = sm + (size_t)P.nw * TM_W_BYTES;             // ring of activation boxes
   uint8_t* tail = sA + (size_t)P.stages * P.slot_bytes;
-  __shared__ __align__(16) float sPar[5 * TM_C];            // [5][64]: bias, mscale, mshift, mean, invstd
+  // [9][64]: 0 output shift (bias), 1 mscale, 2 mshift, 3 mean, 4 invstd, 5 output scale, 6-8 pass-2 coefficients
+  __shared__ __align__(16) float sPar[9 * TM_C];
   __shared__ float sStat[2 * TM_C];                         // [2][64]
   // issue tables: the producer and MMA threads are single threads running dependent scalar code, so everything they
   // would otherwise derive per tile / tap (integer divisions, byte loads from the parameter bank, descriptor
@@ -305,9 +398,9 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
   uint64_t* full = bars;                                    // [8]
   uint64_t* empty = bars + TM_MAX_STAGES;                   // [8]
   uint64_t* wfull = bars + 2 * TM_MAX_STAGES;               // [1]
-  uint64_t* acc_full = wfull + 1;                           // [2]
-  uint64_t* acc_empty = acc_full + 2;                       // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+  uint64_t* acc_full = wfull + 1;                           // [8]
+  uint64_t* acc_empty = acc_full + 8;                       // [8]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 8);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int stages = P.stages;
@@ -345,10 +438,8 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
       mbar_init(&empty[s], 1);
     }
     mbar_init(wfull, 1);
-    for (int a = 0; a < 2; ++a) {
-      mbar_init(&acc_full[a], 1);
-      mbar_init(&acc_empty[a], 128);
-    }
+    for (int a = 0; a < 8; ++a) mbar_init(&acc_full[a], 1);
+    for (int a = 0; a < 8; ++a) mbar_init(&acc_empty[a], 256);
     fence_mbar_init();
     tma::prefetch_desc(&tm0);
     if (P.in_stride == 2) {
@@ -357,7 +448,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
       tma::prefetch_desc(&tm3);
     }
   }
-  if (warp == 1) tmem_alloc<2 * TM_ACC_COLS>(tmem_slot);
+  if (warp == 1) tmem_alloc<NACC * TM_ACC_COLS>(tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -413,7 +504,9 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
         const TmaTile tl = fetch_tile(P, sTile, i);
         const TmaPhase& ph = P.ph[tl.p];
         const int ngroups = ph.ngroups;
-        const int as = i & 1, use = i >> 1;
+        // streaming: two accumulators in turn.  hold: tile i lives in accumulator i % NACC; with more tiles than
+        // accumulators the FIRST ntiles - NACC tiles give theirs up after pass 1 (pass 2 re-reads them from memory)
+        const int as = i % NACC, use = i / NACC;
         if (use > 0) mbar_wait(&acc_empty[as], (uint32_t)((use - 1) & 1));
         tc_fence_after();
         const uint32_t d = tmem_base + (uint32_t)as * TM_ACC_COLS;
@@ -459,65 +552,217 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
       }
     }
   } else {
-    // ------------------------------------------------------------------ epilogue groups: thread = output row
-    const int grp = (warp - 2) >> 2;                 // accumulator / tile parity served by this group
+    // ------------------------------------------------------------------ epilogue: all 8 warps work on every tile;
+    // thread = (output row, 32-channel half).  The per-channel statistics are carried in registers across the CTA's
+    // tiles and leave through ONE 32 x 32 shuffle transpose per statistic at the end (they used to cost two
+    // transposes per tile and half, 4000-4700 cycles against 1500 for the plain epilogue).
+    const int half = (warp - 2) >> 2;                // channel half
     const int q = warp & 3;                          // TMEM lane quarter this warp may read
     const int r = q * 32 + lane;
+    const int ch0 = half * 32;
     const int bw = r & (P.box_w - 1), bh = r >> P.log2_bw;
+    const int e = tid - 64;
     pdl_wait();                                      // epilogue operands / coefficients come from preceding kernels
     pdl_trigger();
-    if (tid - 64 < TM_C) {
-      const int c = tid - 64;
-      sPar[0 * TM_C + c] = epi.bias ? __ldg(epi.bias + c) : 0.f;
+    if (e < TM_C) {
+      const int c = e;
+      const float bias = epi.bias ? __ldg(epi.bias + c) : 0.f;
+      float osc = 1.f, osh = bias;
+      if (bn.mode == NSG_BNF_EVAL) {                 // BatchNorm in eval mode folds into the output affine
+        const float is = 1.0f / sqrtf(__ldg(bn.running_var + c) + bn.eps);
+        osc = __ldg(bn.gamma + c) * is;
+        osh = fmaf(bias - __ldg(bn.running_mean + c), osc, __ldg(bn.beta + c));
+      }
+      sPar[0 * TM_C + c] = osh;
       sPar[1 * TM_C + c] = epi.mask_mode == NSG_MASK_AFFINE ? __ldg(epi.mscale + c) : 1.f;
       sPar[2 * TM_C + c] = epi.mask_mode == NSG_MASK_AFFINE ? __ldg(epi.mshift + c) : 0.f;
       sPar[3 * TM_C + c] = epi.stats_mode == NSG_STATS_BNBWD ? __ldg(epi.mean + c) : 0.f;
       sPar[4 * TM_C + c] = epi.stats_mode == NSG_STATS_BNBWD ? __ldg(epi.invstd + c) : 0.f;
+      sPar[5 * TM_C + c] = osc;
     }
     named_bar(2, 256);
-    for (int i = grp; i < ntiles_mine; i += 2) {
+    const bool do_stats = epi.stats_mode != NSG_STATS_NONE;
+    const bool bwd_stats = epi.stats_mode == NSG_STATS_BNBWD;
+    float s1[32], s2[32];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) s1[j] = s2[j] = 0.f;
+    auto row_offset = [&](int i, bool& valid) -> long long {
       const TmaTile tl = fetch_tile(P, sTile, i);
       const TmaPhase& ph = P.ph[tl.p];
       const int ohs = tl.th * P.box_h + bh, ows = tl.tw * P.box_w + bw;
-      const bool valid = ohs < ph.sub_h && ows < ph.sub_w;
-      const long long o = valid ? ((((long long)tl.n * P.full_h + (ohs * ph.out_stride + ph.off_h)) * P.full_w +
-                                    (ows * ph.out_stride + ph.off_w)) * TM_C) : 0;
-      EpiOperands E;
-      epi_begin(E, epi, o, valid);      // operands of the first 32 channels are requested before the accumulator wait
-      mbar_wait_backoff(&acc_full[grp], (uint32_t)((i >> 1) & 1));
-      if (tid == 64 + 128 * grp) tm_stamp(P.dbg, 12 + (i < 3 ? i : 3));     // 12..15: accumulator of tile i ready
+      valid = ohs < ph.sub_h && ows < ph.sub_w;
+      return valid ? ((((long long)tl.n * P.full_h + (ohs * ph.out_stride + ph.off_h)) * P.full_w +
+                       (ows * ph.out_stride + ph.off_w)) * TM_C + ch0) : 0;
+    };
+    for (int i = 0; i < ntiles_mine; ++i) {
+      bool valid;
+      const long long oh = row_offset(i, valid);
+      const bool use_add = valid && epi.add_src != nullptr;
+      uint4 radd[4];
+      if (use_add) ld_half(epi.add_src, oh, radd);       // requested before the accumulator wait
+      const int as = i % NACC;
+      mbar_wait_backoff(&acc_full[as], (uint32_t)((i / NACC) & 1));
+      if (tid == 64) tm_stamp(P.dbg, 12 + (i < 3 ? i : 3));     // 12..15: accumulator of tile i ready
       tc_fence_after();
-      uint32_t acc0[32], acc1[32];
-      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)grp * TM_ACC_COLS;
-      tmem_ld32(taddr, acc0);
-      tmem_ld32(taddr + 32, acc1);
+      uint32_t acc[32];
+      tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)as * TM_ACC_COLS + (uint32_t)ch0, acc);
       tmem_ld_wait();
-#pragma unroll
-      for (int c = 1; c < TM_CHAINS; ++c) {
-        uint32_t part[32];
-        tmem_ld32(taddr + c * TM_C, part);
-        tmem_ld_wait();
-#pragma unroll
-        for (int j = 0; j < 32; ++j) acc0[j] = __float_as_uint(__uint_as_float(acc0[j]) + __uint_as_float(part[j]));
-        tmem_ld32(taddr + c * TM_C + 32, part);
-        tmem_ld_wait();
-#pragma unroll
-        for (int j = 0; j < 32; ++j) acc1[j] = __float_as_uint(__uint_as_float(acc1[j]) + __uint_as_float(part[j]));
+      if (i + NACC < ntiles_mine) {                    // a later tile of this CTA takes over the accumulator
+        tc_fence_before();
+        mbar_arrive(&acc_empty[as]);
       }
-      tc_fence_before();
-      mbar_arrive(&acc_empty[grp]);
-      epi_row(E, epi, sPar, sStat, out, o, valid, acc0, acc1, lane);
-      if (tid == 64 + 128 * grp) tm_stamp(P.dbg, 16 + (i < 3 ? i : 3));     // 16..19: epilogue of tile i done
+      float x[32];
+      epi_half(x, acc, epi, sPar, oh, valid, ch0, use_add, radd);
+      if (valid && out != nullptr) {
+        st16bf(out + oh, &x[0]);
+        st16bf(out + oh + 16, &x[16]);
+      }
+      if (do_stats) {
+        if (bwd_stats) {
+          if (valid) {
+            uint4 rx[4];
+            ld_half(epi.xhat_src, oh, rx);
+#pragma unroll
+            for (int g8 = 0; g8 < 4; ++g8) {
+              float hx[8];
+              unpack8bf(rx[g8], hx);
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                const int ch = ch0 + g8 * 8 + j;
+                s1[g8 * 8 + j] += x[g8 * 8 + j];
+                s2[g8 * 8 + j] = fmaf(x[g8 * 8 + j], (hx[j] - sPar[3 * TM_C + ch]) * sPar[4 * TM_C + ch], s2[g8 * 8 + j]);
+              }
+            }
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            s1[j] += x[j];
+            s2[j] = fmaf(x[j], x[j], s2[j]);
+          }
+        }
+      }
+      if (tid == 64) tm_stamp(P.dbg, 16 + (i < 3 ? i : 3));     // 16..19: epilogue of tile i done
     }
-    if (epi.stats_mode != NSG_STATS_NONE) {
+    if (do_stats) {
+      const float t1 = transpose_sum32(s1, lane);
+      const float t2 = transpose_sum32(s2, lane);
+      atomicAdd(&sStat[ch0 + lane], t1);
+      atomicAdd(&sStat[TM_C + ch0 + lane], t2);
       named_bar(1, 256);
-      const int e = tid - 64;
       if (e < 2 * TM_C) atomicAdd(epi.stats + e, (double)sStat[e]);
+    }
+    if (HOLD) {
+      // ---------------------------------------------------------------- grid barrier, coefficients, pass 2
+      named_bar(1, 256);                               // every statistic atomic of this CTA has been issued
+      if (tid == 64) grid_barrier(bn.barrier, gridDim.x);
+      named_bar(1, 256);
+      if (e < TM_C) {
+        const int c = e;
+        const double a0 = __ldcg(epi.stats + c), a1 = __ldcg(epi.stats + TM_C + c);
+        if (bn.mode == NSG_BNF_TRAIN) {
+          const double m = a0 / bn.count;
+          double var = a1 / bn.count - m * m;
+          if (var < 0.0) var = 0.0;
+          const float mu = (float)m;
+          const float is = (float)(1.0 / sqrt(var + (double)bn.eps));
+          const float sc = __ldg(bn.gamma + c) * is;
+          const float sh = __ldg(bn.beta + c) - mu * sc;
+          sPar[6 * TM_C + c] = sc;
+          sPar[7 * TM_C + c] = sh;
+          if (blockIdx.x == 0) {
+            if (bn.running_mean) {
+              const double unbiased = bn.count > 1.0 ? var * bn.count / (bn.count - 1.0) : var;
+              bn.running_mean[c] = (1.f - bn.momentum) * bn.running_mean[c] + bn.momentum * mu;
+              bn.running_var[c] = (1.f - bn.momentum) * bn.running_var[c] + bn.momentum * (float)unbiased;
+              if (c == 0 && bn.nbt) *bn.nbt += 1;
+            }
+            if (bn.coef) {
+              bn.coef[0 * TM_C + c] = mu;
+              bn.coef[1 * TM_C + c] = is;
+              bn.coef[2 * TM_C + c] = sc;
+              bn.coef[3 * TM_C + c] = sh;
+            }
+          }
+        } else {                                       // NSG_BNF_BWD: dh = A*g + B*h + C (fused_elem.cu: bn_bwd_kernel)
+          const double sg = a0 / bn.count, sgx = a1 / bn.count;
+          const float mu = sPar[3 * TM_C + c], is = sPar[4 * TM_C + c];
+          const float k0 = __ldg(bn.gamma + c) * is;
+          const float kb = k0 * is * (float)sgx;
+          sPar[6 * TM_C + c] = k0;
+          sPar[7 * TM_C + c] = -kb;
+          sPar[8 * TM_C + c] = kb * mu - k0 * (float)sg;
+          if (blockIdx.x == 0) {
+            if (bn.dbeta) bn.dbeta[c] += (float)a0;
+            if (bn.dgamma) bn.dgamma[c] += (float)a1;
+          }
+        }
+      }
+      named_bar(1, 256);
+      for (int i = 0; i < ntiles_mine; ++i) {
+        bool valid;
+        const long long oh = row_offset(i, valid);
+        // tiles whose accumulator was handed on read what pass 1 stored (h forward, g backward: written by this thread)
+        const bool in_tmem = i + NACC >= ntiles_mine;
+        uint32_t acc[32];
+        if (in_tmem) tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(i % NACC) * TM_ACC_COLS + (uint32_t)ch0, acc);
+        if (!valid) {
+          if (in_tmem) tmem_ld_wait();
+          continue;
+        }
+        float x[32];
+        if (!in_tmem) {
+          uint4 rs[4];
+          const uint4* p = reinterpret_cast<const uint4*>(out + oh);
+#pragma unroll
+          for (int g8 = 0; g8 < 4; ++g8) rs[g8] = p[g8];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) x[j] = 0.f;
+          add_half(x, rs);
+        }
+        if (bn.mode == NSG_BNF_TRAIN) {
+          uint4 rr[4];
+          if (bn.res) ld_half(bn.res, oh, rr);
+          if (in_tmem) {
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; ++j) x[j] = fmaf(__uint_as_float(acc[j]), sPar[5 * TM_C + ch0 + j], sPar[ch0 + j]);
+          }
+#pragma unroll
+          for (int j = 0; j < 32; ++j) x[j] = fmaf(x[j], sPar[6 * TM_C + ch0 + j], sPar[7 * TM_C + ch0 + j]);
+          if (bn.res) add_half(x, rr);
+          if (bn.relu_out) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) x[j] = fmaxf(x[j], 0.f);
+          }
+        } else {
+          const bool use_add = in_tmem && epi.add_src != nullptr;
+          uint4 radd[4], rx[4];
+          if (use_add) ld_half(epi.add_src, oh, radd);
+          ld_half(epi.xhat_src, oh, rx);
+          if (in_tmem) {
+            tmem_ld_wait();
+            epi_half(x, acc, epi, sPar, oh, true, ch0, use_add, radd);     // g, exactly as pass 1 formed it
+          }
+#pragma unroll
+          for (int g8 = 0; g8 < 4; ++g8) {
+            float hx[8];
+            unpack8bf(rx[g8], hx);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const int ch = ch0 + g8 * 8 + j;
+              x[g8 * 8 + j] = fmaf(sPar[6 * TM_C + ch], x[g8 * 8 + j], fmaf(sPar[7 * TM_C + ch], hx[j], sPar[8 * TM_C + ch]));
+            }
+          }
+        }
+        st16bf(bn.out2 + oh, &x[0]);
+        st16bf(bn.out2 + oh + 16, &x[16]);
+      }
     }
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc<2 * TM_ACC_COLS>(tmem_base);
+  if (warp == 1) tmem_dealloc<NACC * TM_ACC_COLS>(tmem_base);
   if (tid == 0) tm_stamp(P.dbg, 20);
 }
 
@@ -653,8 +898,79 @@ static int encode_input_maps(CUtensorMap* tm, const void* in, int batch, int in_
   return NSG_OK;
 }
 
-int conv_gemm_tma(const nsg_conv_geom* cg, const void* in, const void* packed, const nsg_epilogue* epi, void* out,
-                  cudaStream_t stream) {
+// validated device-side copy of the public nsg_bn_fuse
+static int make_bnfuse(const nsg_bn_fuse* b, const EpiArgs& e, BnFuse* out) {
+  BnFuse f{};
+  if (b && b->mode != NSG_BNF_NONE) {
+    NSG_REQUIRE(b->mode == NSG_BNF_TRAIN || b->mode == NSG_BNF_EVAL || b->mode == NSG_BNF_BWD, "conv_bn_tma: mode %d", b->mode);
+    f.mode = b->mode; f.relu_out = b->relu_out; f.gamma = b->gamma; f.beta = b->beta; f.eps = b->eps;
+    f.momentum = b->momentum; f.count = b->count; f.running_mean = b->running_mean; f.running_var = b->running_var;
+    f.nbt = b->num_batches_tracked; f.coef = b->coef; f.res = static_cast<const __nv_bfloat16*>(b->res);
+    f.barrier = b->barrier; f.dgamma = b->dgamma; f.dbeta = b->dbeta; f.out2 = static_cast<__nv_bfloat16*>(b->out2);
+    NSG_REQUIRE(f.gamma, "conv_bn_tma: gamma missing");
+    if (f.mode == NSG_BNF_EVAL) {
+      NSG_REQUIRE(f.beta && f.running_mean && f.running_var, "conv_bn_tma: eval mode needs beta and the running statistics");
+      NSG_REQUIRE(e.stats_mode == NSG_STATS_NONE, "conv_bn_tma: eval mode accumulates no statistics");
+    } else {
+      NSG_REQUIRE(f.barrier && f.out2 && f.count > 0, "conv_bn_tma: barrier counter, second output and count are required");
+      NSG_REQUIRE((reinterpret_cast<uintptr_t>(f.out2) & 31) == 0 && (reinterpret_cast<uintptr_t>(f.res) & 15) == 0,
+                  "conv_bn_tma: out2 must be 32-byte and res 16-byte aligned");
+      if (f.mode == NSG_BNF_TRAIN)
+        NSG_REQUIRE(f.beta && e.stats_mode == NSG_STATS_MOMENTS, "conv_bn_tma: train mode needs beta and NSG_STATS_MOMENTS");
+      else
+        NSG_REQUIRE(e.stats_mode == NSG_STATS_BNBWD, "conv_bn_tma: backward mode needs NSG_STATS_BNBWD operands");
+    }
+  }
+  *out = f;
+  return NSG_OK;
+}
+
+template <int NACC>
+static int launch_conv_tma(int grid, size_t smem, cudaStream_t stream, const CUtensorMap* tm, const void* packed, void* out,
+                           const EpiArgs& e, const BnFuse& f, const TmaConvParams& P) {
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t err = cudaFuncSetAttribute(conv_tma_kernel<NACC>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           (int)TM_SMEM_LIMIT);
+    if (err != cudaSuccess) return cuda_fail(err, "cudaFuncSetAttribute(conv_tma_kernel)");
+    configured = true;
+  }
+  launch_pdl(conv_tma_kernel<NACC>, dim3(grid), dim3(320), smem, stream, tm[0], tm[1], tm[2], tm[3],
+             static_cast<const uint8_t*>(packed), static_cast<__nv_bfloat16*>(out), e, f, P);
+  NSG_CHECK_LAUNCH("conv_tma_kernel");
+  return NSG_OK;
+}
+
+// tiles per CTA of the persistent grid for this geometry (what decides whether a hold launch fits in TMEM)
+static int conv_tma_tiles_per_cta(const nsg_conv_geom* cg) {
+  TapGeom phases[4];
+  const int np = build_phases(cg, phases);
+  static TapGroups groups[4];
+  int halo = 0;
+  for (int i = 0; i < np; ++i) {
+    group_taps(phases[i], &groups[i]);
+    if (phases[i].sub_h > 0 && phases[i].sub_w > 0 && groups[i].halo > halo) halo = groups[i].halo;
+  }
+  int bw, bh, l2;
+  pick_box(phases, groups, np, cg->batch, TM_M, halo, &bw, &bh, &l2);
+  long long tiles = 0;
+  for (int i = 0; i < np; ++i) {
+    if (phases[i].sub_h <= 0 || phases[i].sub_w <= 0) continue;
+    tiles += (long long)((phases[i].sub_w + bw - 1) / bw) * ((phases[i].sub_h + bh - 1) / bh) * cg->batch;
+  }
+  if (tiles == 0) return 0;
+  const long long grid = tiles < num_sms() ? tiles : num_sms();
+  return (int)((tiles + grid - 1) / grid);
+}
+int conv_bn_tma_fits(const nsg_conv_geom* cg) {
+  if (cg->cin != TM_C || cg->cout != TM_C || cg->dtype != NSG_BF16 || cg->ksize < 1 || cg->ksize > 4 || cg->stride < 1 ||
+      cg->stride > 2)
+    return 0;
+  return conv_tma_tiles_per_cta(cg) <= 64 ? 1 : 0;
+}
+
+int conv_gemm_tma(const nsg_conv_geom* cg, const void* in, const void* packed, const nsg_epilogue* epi,
+                  const nsg_bn_fuse* bnf, void* out, cudaStream_t stream) {
   if (int rc = tma_shape_ok(cg, "conv_gemm_tma")) return rc;
   NSG_REQUIRE((reinterpret_cast<uintptr_t>(packed) & 127) == 0, "conv_gemm_tma: packed weights must be 128-byte aligned");
   NSG_REQUIRE((reinterpret_cast<uintptr_t>(in) & 15) == 0 && (reinterpret_cast<uintptr_t>(out) & 31) == 0,
@@ -663,6 +979,10 @@ int conv_gemm_tma(const nsg_conv_geom* cg, const void* in, const void* packed, c
   if (int rc = make_epi(epi, &e)) return rc;
   NSG_REQUIRE(e.tanh_out == 0 || e.tanh_out == 2,
               "conv_gemm_tma: output activation must be none (0) or ReLU (2); tanh belongs to the cout == 1 layer");
+  BnFuse f{};
+  if (int rc = make_bnfuse(bnf, e, &f)) return rc;
+  const bool hold = f.mode == NSG_BNF_TRAIN || f.mode == NSG_BNF_BWD;
+  NSG_REQUIRE(out || hold, "conv_gemm_tma: null output");
   TapGeom phases[4];
   const int np = build_phases(cg, phases);
   TmaConvParams P{};
@@ -712,7 +1032,7 @@ int conv_gemm_tma(const nsg_conv_geom* cg, const void* in, const void* packed, c
   if (tiles == 0) return NSG_OK;
   P.nphases = nph;
   P.total_tiles = tiles;
-  const uint32_t tail = (2 * TM_MAX_STAGES + 5) * 8 + 64;
+  const uint32_t tail = (2 * TM_MAX_STAGES + 17) * 8 + 64;
   int stages = (int)((TM_SMEM_LIMIT - 1024 - tail - (uint32_t)P.nw * TM_W_BYTES) / P.slot_bytes);
   if (stages > TM_MAX_STAGES) stages = TM_MAX_STAGES;
   NSG_REQUIRE(stages >= 2, "conv_gemm_tma: weights do not leave room for the activation ring");
@@ -722,18 +1042,20 @@ int conv_gemm_tma(const nsg_conv_geom* cg, const void* in, const void* packed, c
   const size_t smem = 1024 + (size_t)P.nw * TM_W_BYTES + (size_t)stages * P.slot_bytes + tail;
   CUtensorMap tm[4];
   if (int rc = encode_input_maps(tm, in, cg->batch, cg->in_h, cg->in_w, P.in_stride, P.box_w, P.box_h + halo)) return rc;
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t err = cudaFuncSetAttribute(conv_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                           (int)TM_SMEM_LIMIT);
-    if (err != cudaSuccess) return cuda_fail(err, "cudaFuncSetAttribute(conv_tma_kernel)");
-    configured = true;
-  }
   const int grid = tiles < num_sms() ? tiles : num_sms();
-  launch_pdl(conv_tma_kernel, dim3(grid), dim3(320), smem, stream, tm[0], tm[1], tm[2], tm[3],
-             static_cast<const uint8_t*>(packed), static_cast<__nv_bfloat16*>(out), e, P);
-  NSG_CHECK_LAUNCH("conv_tma_kernel");
-  return NSG_OK;
+  if (!hold) return launch_conv_tma<2>(grid, smem, stream, tm, packed, out, e, f, P);
+  const int per_cta = (tiles + grid - 1) / grid;
+  if (per_cta > 64) {
+    set_error("conv_bn_tma: %d tiles per CTA do not fit (at most 64); run the convolution and the BatchNorm pass "
+              "separately (nsg_conv_bn_tma_fits)", per_cta);
+    return NSG_E_UNSUPPORTED;
+  }
+  // more tiles than the 8 TMEM accumulators: the surplus is read back in pass 2 from what pass 1 stored
+  NSG_REQUIRE(per_cta <= 8 || out, "conv_bn_tma: with more than 8 tiles per CTA the first output (h / g) is required");
+  // a grid barrier needs every CTA resident: one CTA per SM of THIS device
+  NSG_REQUIRE(grid <= num_sms(), "conv_bn_tma: grid %d exceeds the SM count", grid);
+  if (per_cta <= 4) return launch_conv_tma<4>(grid, smem, stream, tm, packed, out, e, f, P);
+  return launch_conv_tma<8>(grid, smem, stream, tm, packed, out, e, f, P);
 }
 
 // ntaps[i] > 0: a 64 -> 64 layer with ntaps images.  ntaps[i] == -1 / -2: the single-channel layers' small operands,

@@ -341,6 +341,8 @@ vq_search_tc_kernel(const T* __restrict__ z, const float* __restrict__ cb, const
 //   fp32 z (parity mode): each group splits its own tile into hi / lo bf16 images (one 32 KB buffer per group).
 constexpr int VR_THREADS = 320;     // warps 0-3 group 0, warps 4-7 group 1, warp 8 = loader + MMA issuer, warp 9 = z producer
 constexpr int VR_STAGES = 4;        // bf16 z ring (4 x 16 KB = the two 32 KB buffers of the fp32 path)
+constexpr int VR_CAND = 8;          // candidate list per row (4 per 256-codeword chunk)
+constexpr int VR_OVERFLOW = 255;    // candidate count marker: list too short, scan the whole codebook exactly
 
 template <typename T>
 __global__ void __launch_bounds__(VR_THREADS, 1)
@@ -355,10 +357,12 @@ vq_search_res_kernel(const __grid_constant__ CUtensorMap tmz, const T* __restric
   uint8_t* Abuf = sm + (size_t)nchunks * VT_CHUNK_BYTES;        // fp32: [2 groups][hi 16 KB | lo 16 KB]; bf16: [4][16 KB]
   float* esq_s = reinterpret_cast<float*>(Abuf + 2 * 32768);    // [nchunks * 256]
   uint8_t* tail = reinterpret_cast<uint8_t*>(esq_s + nchunks * VT_N);
-  int* sCI = reinterpret_cast<int*>(tail);                      // [2][128][2]
-  int* sWin = reinterpret_cast<int*>(tail + 2048);              // [2][128]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(tail + 3072);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tail + 3200);
+  int* sCI = reinterpret_cast<int*>(tail);                      // [2][128][VR_CAND] candidate lists
+  int* sWin = reinterpret_cast<int*>(tail + 8192);              // [2][128]
+  int* sCnt = reinterpret_cast<int*>(tail + 9216);              // [2][128]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(tail + 10240);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tail + 10368);
+  __shared__ float sEmax[VR_THREADS / 32];
   uint64_t* b_full = bars;                                      // [1]
   uint64_t* a_full = bars + 1;                                  // [4]
   uint64_t* a_empty = bars + 5;                                 // [4]
@@ -384,11 +388,23 @@ vq_search_res_kernel(const __grid_constant__ CUtensorMap tmz, const T* __restric
   if (warp == 8) tmem_alloc<512>(tmem_slot);
   pdl_wait();                // barriers / TMEM above are independent of earlier kernels (common.cuh, PDL)
   pdl_trigger();
-  for (int i = tid; i < nchunks * VT_N; i += VR_THREADS) esq_s[i] = __ldg(esq_pad + i);
+  float emx = 0.f;                 // max |e|^2 over the real codewords (the padding rows carry +inf)
+  for (int i = tid; i < nchunks * VT_N; i += VR_THREADS) {
+    const float v = __ldg(esq_pad + i);
+    esq_s[i] = v;
+    if (i < K) emx = fmaxf(emx, v);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) emx = fmaxf(emx, __shfl_xor_sync(0xffffffffu, emx, o));
+  if (lane == 0) sEmax[warp] = emx;
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  float emax = 0.f;
+#pragma unroll
+  for (int w = 0; w < VR_THREADS / 32; ++w) emax = fmaxf(emax, sEmax[w]);
+  emax = sqrtf(emax);
 
   if (warp == 9) {
     if (!kSplitZ && lane == 0) {
@@ -454,9 +470,20 @@ vq_search_res_kernel(const __grid_constant__ CUtensorMap tmz, const T* __restric
     }
   } else {
     // ---------------- epilogue group g: tiles g, g+2, ... of this CTA
+    // Exact-minimum search in two sweeps over each 256-column accumulator (it stays in TMEM between them):
+    //   sweep 1: the chunk minimum of d = |e|^2 - 2 z.e -- one FFMA and half a 3-input FMNMX per (row, codeword);
+    //   sweep 2: every codeword within `margin` of that minimum becomes a CANDIDATE (FFMA + FSETP per element; the
+    //            rare hits are appended in increasing index order).
+    // margin = 2^-14 |z| max|e| is > 2x the worst error of the split-bf16 GEMM (the dropped operand residuals are
+    // < 2^-17 |z||e| each, doubled by the factor 2), so the fp32 argmin is always among the candidates; they are then
+    // re-scored EXACTLY in fp32 in increasing index order with a strict '<' -- the lowest index wins among equal
+    // distances, however many duplicates there are (vector_quantization.py:19).  A row with more candidates than the
+    // list holds (degenerate codebooks: many identical codewords) falls back to an exact scan of all K codewords.
+    // The previous form tracked the two best codewords in one sweep at ~10 instructions per (row, codeword).
     const int g = warp >> 2, q = warp & 3;
     const int gt = tid & 127;                         // thread within the group = TMEM lane = tile row
-    int* myCI = sCI + g * 256;
+    int* myCand = sCI + g * (128 * VR_CAND);
+    int* myCnt = sCnt + g * 128;
     int* myWin = sWin + g * 128;
     const int barid = 1 + g;
     float err_acc = 0.f;
@@ -500,90 +527,168 @@ vq_search_res_kernel(const __grid_constant__ CUtensorMap tmz, const T* __restric
     if (kSplitZ && g < ntiles_mine) stage(g);
     for (int i = g; i < ntiles_mine; i += 2) {
       const long long row0 = ((long long)blockIdx.x + (long long)i * gridDim.x) * VT_M;
-      // four independent trackers (columns 4m + u): the update is a dependent compare/select chain, and with two
-      // epilogue warps per scheduler only instruction-level parallelism keeps the issue slots busy
-      Top2 tk[4];
+      const int slot = i % VR_STAGES;
+      const uint8_t* ztile = Abuf + (size_t)slot * 16384;           // bf16 path: this tile's rows, as TMA wrote them
+      float cmin[2] = {INFINITY, INFINITY};
+      int cn[2] = {0, 0};
+      int cand[2][VR_CAND / 2];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) tk[u].init();
-      for (int c = 0; c < nchunks; ++c) {
-        mbar_wait_backoff(&acc_full[g], (uint32_t)(nfull & 1));
-        ++nfull;
-        tc_fence_after();
-        const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(g * VT_N);
-        uint32_t ra[32], rb[32];
-        tmem_ld32(tbase, ra);
+      for (int c = 0; c < 2; ++c)
+#pragma unroll
+        for (int j = 0; j < VR_CAND / 2; ++j) cand[c][j] = -1;
+      float margin = 0.f;
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        if (c < nchunks) {
+          mbar_wait_backoff(&acc_full[g], (uint32_t)(nfull & 1));
+          ++nfull;
+          tc_fence_after();
+          const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(g * VT_N);
+          uint32_t ra[32], rb[32];
+          tmem_ld32(tbase, ra);
+          if (c == 0) {
+            // |z| of this row (the accumulator being complete implies its z tile has landed / been staged)
+            float zz = 0.f;
+            if (kSplitZ) {
+              const long long grow = row0 + gt;
+              if (grow < N) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                  float v[8];
+                  load8<T>(z + grow * VT_D + j * 8, v);
+#pragma unroll
+                  for (int e = 0; e < 8; ++e) zz = fmaf(v[e], v[e], zz);
+                }
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                const uint4 raw = *reinterpret_cast<const uint4*>(ztile + sw128_offset(gt, j));
+                const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                  const float lo = __uint_as_float(w[e] << 16), hi = __uint_as_float(w[e] & 0xffff0000u);
+                  zz = fmaf(lo, lo, fmaf(hi, hi, zz));
+                }
+              }
+            }
+            margin = sqrtf(zz) * emax * 6.103515625e-05f + 1e-30f;      // 2^-14 |z| max|e|
+          }
+          // ---- sweep 1: chunk minimum
+          float m0 = INFINITY, m1 = INFINITY, m2 = INFINITY, m3 = INFINITY;
 #pragma unroll 1
-        for (int j = 0; j < 8; j += 2) {
-          // two 32-column slices per trip: the load of the next slice is in flight while this one is scanned
-          tmem_ld_wait();
-          tmem_ld_fence(ra);
-          tmem_ld32(tbase + (uint32_t)((j + 1) * 32), rb);
-          {
-            const float4* es = reinterpret_cast<const float4*>(esq_s + c * VT_N + j * 32);
-            const int kbase = c * VT_N + j * 32;
+          for (int j = 0; j < 8; j += 2) {
+            tmem_ld_wait();
+            tmem_ld_fence(ra);
+            tmem_ld32(tbase + (uint32_t)((j + 1) * 32), rb);
+            {
+              const float4* es = reinterpret_cast<const float4*>(esq_s + c * VT_N + j * 32);
+#pragma unroll
+              for (int e4 = 0; e4 < 8; e4 += 2) {
+                const float4 e = es[e4], f = es[e4 + 1];
+                m0 = fminf(fminf(m0, fmaf(-2.f, __uint_as_float(ra[4 * e4 + 0]), e.x)), fmaf(-2.f, __uint_as_float(ra[4 * e4 + 1]), e.y));
+                m1 = fminf(fminf(m1, fmaf(-2.f, __uint_as_float(ra[4 * e4 + 2]), e.z)), fmaf(-2.f, __uint_as_float(ra[4 * e4 + 3]), e.w));
+                m2 = fminf(fminf(m2, fmaf(-2.f, __uint_as_float(ra[4 * e4 + 4]), f.x)), fmaf(-2.f, __uint_as_float(ra[4 * e4 + 5]), f.y));
+                m3 = fminf(fminf(m3, fmaf(-2.f, __uint_as_float(ra[4 * e4 + 6]), f.z)), fmaf(-2.f, __uint_as_float(ra[4 * e4 + 7]), f.w));
+              }
+            }
+            tmem_ld_wait();
+            tmem_ld_fence(rb);
+            tmem_ld32(tbase + (uint32_t)(((j + 2) & 7) * 32), ra);      // (wraps to slice 0: sweep 2 starts there)
+            {
+              const float4* es = reinterpret_cast<const float4*>(esq_s + c * VT_N + (j + 1) * 32);
+#pragma unroll
+              for (int e4 = 0; e4 < 8; e4 += 2) {
+                const float4 e = es[e4], f = es[e4 + 1];
+                m0 = fminf(fminf(m0, fmaf(-2.f, __uint_as_float(rb[4 * e4 + 0]), e.x)), fmaf(-2.f, __uint_as_float(rb[4 * e4 + 1]), e.y));
+                m1 = fminf(fminf(m1, fmaf(-2.f, __uint_as_float(rb[4 * e4 + 2]), e.z)), fmaf(-2.f, __uint_as_float(rb[4 * e4 + 3]), e.w));
+                m2 = fminf(fminf(m2, fmaf(-2.f, __uint_as_float(rb[4 * e4 + 4]), f.x)), fmaf(-2.f, __uint_as_float(rb[4 * e4 + 5]), f.y));
+                m3 = fminf(fminf(m3, fmaf(-2.f, __uint_as_float(rb[4 * e4 + 6]), f.z)), fmaf(-2.f, __uint_as_float(rb[4 * e4 + 7]), f.w));
+              }
+            }
+          }
+          const float mc = fminf(fminf(m0, m1), fminf(m2, m3));
+          cmin[c] = mc;
+          const float thr = mc + margin;
+          // ---- sweep 2: candidates within the margin, in increasing index order
+          int n = 0;
+          auto push = [&](int k) {
+            if (n == 0) cand[c][0] = k;
+            else if (n == 1) cand[c][1] = k;
+            else if (n == 2) cand[c][2] = k;
+            else if (n == 3) cand[c][3] = k;
+            ++n;
+          };
+          auto scan32 = [&](const uint32_t (&rr)[32], int jj) {
+            const float4* es = reinterpret_cast<const float4*>(esq_s + c * VT_N + jj * 32);
+            const int kbase = c * VT_N + jj * 32;
 #pragma unroll
             for (int e4 = 0; e4 < 8; ++e4) {
               const float4 e = es[e4];
-              tk[0].push_ordered(fmaf(-2.f, __uint_as_float(ra[4 * e4 + 0]), e.x), kbase + 4 * e4 + 0);
-              tk[1].push_ordered(fmaf(-2.f, __uint_as_float(ra[4 * e4 + 1]), e.y), kbase + 4 * e4 + 1);
-              tk[2].push_ordered(fmaf(-2.f, __uint_as_float(ra[4 * e4 + 2]), e.z), kbase + 4 * e4 + 2);
-              tk[3].push_ordered(fmaf(-2.f, __uint_as_float(ra[4 * e4 + 3]), e.w), kbase + 4 * e4 + 3);
+              const float d0 = fmaf(-2.f, __uint_as_float(rr[4 * e4 + 0]), e.x);
+              const float d1 = fmaf(-2.f, __uint_as_float(rr[4 * e4 + 1]), e.y);
+              const float d2 = fmaf(-2.f, __uint_as_float(rr[4 * e4 + 2]), e.z);
+              const float d3 = fmaf(-2.f, __uint_as_float(rr[4 * e4 + 3]), e.w);
+              if (d0 <= thr || d1 <= thr || d2 <= thr || d3 <= thr) {
+                if (d0 <= thr) push(kbase + 4 * e4 + 0);
+                if (d1 <= thr) push(kbase + 4 * e4 + 1);
+                if (d2 <= thr) push(kbase + 4 * e4 + 2);
+                if (d3 <= thr) push(kbase + 4 * e4 + 3);
+              }
             }
+          };
+#pragma unroll 1
+          for (int j = 0; j < 8; j += 2) {
+            tmem_ld_wait();
+            tmem_ld_fence(ra);
+            tmem_ld32(tbase + (uint32_t)((j + 1) * 32), rb);
+            scan32(ra, j);
+            tmem_ld_wait();
+            tmem_ld_fence(rb);
+            if (j + 2 < 8) tmem_ld32(tbase + (uint32_t)((j + 2) * 32), ra);
+            scan32(rb, j + 1);
           }
-          tmem_ld_wait();
-          tmem_ld_fence(rb);
-          if (j + 2 < 8) tmem_ld32(tbase + (uint32_t)((j + 2) * 32), ra);
-          {
-            const float4* es = reinterpret_cast<const float4*>(esq_s + c * VT_N + (j + 1) * 32);
-            const int kbase = c * VT_N + (j + 1) * 32;
-#pragma unroll
-            for (int e4 = 0; e4 < 8; ++e4) {
-              const float4 e = es[e4];
-              tk[0].push_ordered(fmaf(-2.f, __uint_as_float(rb[4 * e4 + 0]), e.x), kbase + 4 * e4 + 0);
-              tk[1].push_ordered(fmaf(-2.f, __uint_as_float(rb[4 * e4 + 1]), e.y), kbase + 4 * e4 + 1);
-              tk[2].push_ordered(fmaf(-2.f, __uint_as_float(rb[4 * e4 + 2]), e.z), kbase + 4 * e4 + 2);
-              tk[3].push_ordered(fmaf(-2.f, __uint_as_float(rb[4 * e4 + 3]), e.w), kbase + 4 * e4 + 3);
-            }
-          }
+          cn[c] = n;
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&acc_empty[g]);
         }
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&acc_empty[g]);
       }
       // fp32: every MMA that read this group's A buffer has retired (its last accumulator was just consumed): hand
       // the MMA thread the next tile before the latency-bound tail of this one
       if (kSplitZ && i + 2 < ntiles_mine) stage(i + 2);
-      Top2 t2;
-      t2.init();
+      {
+        // this row's candidate list: the chunks whose minimum is within the margin of the row minimum
+        const float gthr = fminf(cmin[0], cmin[1]) + margin;
+        int total = 0;
+        bool ovf = false;
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {       // lexicographic (distance, index) merge keeps the lowest index among equals
-        t2.push_any(tk[u].d1, tk[u].i1);
-        t2.push_any(tk[u].d2, tk[u].i2);
+        for (int c = 0; c < 2; ++c) {
+          if (cmin[c] <= gthr) {
+            if (cn[c] > VR_CAND / 2) ovf = true;
+#pragma unroll
+            for (int j = 0; j < VR_CAND / 2; ++j)
+              if (j < cn[c] && cand[c][j] < K) myCand[gt * VR_CAND + total++] = cand[c][j];
+          }
+        }
+        myCnt[gt] = ovf ? VR_OVERFLOW : total;
       }
-      if (t2.i1 >= K) t2.i1 = -1;
-      if (t2.i2 >= K) t2.i2 = -1;
-      myCI[gt * 2 + 0] = t2.i1;
-      myCI[gt * 2 + 1] = t2.i2;
-      const int slot = i % VR_STAGES;
-      const uint8_t* ztile = Abuf + (size_t)slot * 16384;           // bf16 path: this tile's rows, as TMA wrote them
       if (!kSplitZ) mbar_wait(&a_full[slot], (uint32_t)((i / VR_STAGES) & 1));   // (complete long ago: ordering only)
       asm volatile("bar.sync %0, 128;" ::"r"(barid) : "memory");
 
-      // exact fp32 re-score of the two candidates: 8 lanes per row, 16 rows per pass, 4 passes' loads in flight
+      // exact fp32 re-score: 8 lanes per row, 16 rows per pass, 4 passes' first candidates in flight
       const int sub = gt & 7;
 #pragma unroll 1
       for (int pb = 0; pb < 8; pb += 4) {
-        float zv[4][8], e1[4][8], e2[4][8];
-        int c1[4], c2[4];
+        float zv[4][8], e1[4][8];
+        int cnt[4], c1[4];
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
           const int rr = (pb + u) * 16 + (gt >> 3);
           const long long grow = row0 + rr;
-          c1[u] = myCI[rr * 2 + 0];
-          c2[u] = myCI[rr * 2 + 1];
-          const bool on = grow < N && c1[u] >= 0;
-          if (!on) c1[u] = -1;
-          if (on) {
+          cnt[u] = grow < N ? myCnt[rr] : 0;
+          c1[u] = (cnt[u] > 0 && cnt[u] != VR_OVERFLOW) ? myCand[rr * VR_CAND] : -1;
+          if (cnt[u] > 0) {
             if (kSplitZ) {
               load8<T>(z + grow * VT_D + sub * 8, zv[u]);
             } else {
@@ -595,45 +700,80 @@ vq_search_res_kernel(const __grid_constant__ CUtensorMap tmz, const T* __restric
                 zv[u][2 * e + 1] = __uint_as_float(w[e] & 0xffff0000u);
               }
             }
-            load8<float>(cb + (long long)c1[u] * VT_D + sub * 8, e1[u]);
-            if (c2[u] >= 0) load8<float>(cb + (long long)c2[u] * VT_D + sub * 8, e2[u]);
+            if (c1[u] >= 0) load8<float>(cb + (long long)c1[u] * VT_D + sub * 8, e1[u]);
           }
         }
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
           const int rr = (pb + u) * 16 + (gt >> 3);
-          float p1 = 0.f, p2 = 0.f;
-          if (c1[u] >= 0) {
-#pragma unroll
-            for (int e = 0; e < 8; ++e) {
-              const float df = zv[u][e] - e1[u][e];
-              p1 = fmaf(df, df, p1);
-            }
-            if (c2[u] >= 0) {
+          float best = INFINITY;
+          int win = 0;
+          {
+            float p1 = 0.f;
+            if (c1[u] >= 0) {
 #pragma unroll
               for (int e = 0; e < 8; ++e) {
-                const float df = zv[u][e] - e2[u][e];
-                p2 = fmaf(df, df, p2);
+                const float df = zv[u][e] - e1[u][e];
+                p1 = fmaf(df, df, p1);
+              }
+            }
+#pragma unroll
+            for (int o = 4; o > 0; o >>= 1) p1 += __shfl_xor_sync(0xffffffffu, p1, o);
+            if (c1[u] >= 0) {
+              best = p1;
+              win = c1[u];
+            }
+          }
+          // further candidates (rare): warp-uniform trip count, rows without one idle
+          const int extra = (cnt[u] != VR_OVERFLOW) ? cnt[u] : 0;
+          const int jmax = __reduce_max_sync(0xffffffffu, extra);
+          for (int j = 1; j < jmax; ++j) {
+            const int k = j < extra ? myCand[rr * VR_CAND + j] : -1;
+            float pj = 0.f;
+            if (k >= 0) {
+              float ev[8];
+              load8<float>(cb + (long long)k * VT_D + sub * 8, ev);
+#pragma unroll
+              for (int e = 0; e < 8; ++e) {
+                const float df = zv[u][e] - ev[e];
+                pj = fmaf(df, df, pj);
+              }
+            }
+#pragma unroll
+            for (int o = 4; o > 0; o >>= 1) pj += __shfl_xor_sync(0xffffffffu, pj, o);
+            if (k >= 0 && pj < best) {          // increasing index order + strict '<': lowest index among equals
+              best = pj;
+              win = k;
+            }
+          }
+          // candidate list overflow (many identical codewords): exact scan of the whole codebook for this row
+          if (__any_sync(0xffffffffu, cnt[u] == VR_OVERFLOW)) {
+            const bool mine = cnt[u] == VR_OVERFLOW;
+            for (int k = 0; k < K; ++k) {
+              float pj = 0.f;
+              if (mine) {
+                float ev[8];
+                load8<float>(cb + (long long)k * VT_D + sub * 8, ev);
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                  const float df = zv[u][e] - ev[e];
+                  pj = fmaf(df, df, pj);
+                }
+              }
+#pragma unroll
+              for (int o = 4; o > 0; o >>= 1) pj += __shfl_xor_sync(0xffffffffu, pj, o);
+              if (mine && pj < best) {
+                best = pj;
+                win = k;
               }
             }
           }
-#pragma unroll
-          for (int o = 4; o > 0; o >>= 1) {
-            p1 += __shfl_xor_sync(0xffffffffu, p1, o);
-            p2 += __shfl_xor_sync(0xffffffffu, p2, o);
-          }
           if (sub == 0) {
-            int win = c1[u] < 0 ? 0 : c1[u];
-            float dw = p1;
-            if (c1[u] >= 0 && c2[u] >= 0 && (p2 < p1 || (p2 == p1 && c2[u] < c1[u]))) {
-              win = c2[u];
-              dw = p2;
-            }
             myWin[rr] = win;
             const long long grow = row0 + rr;
             if (grow < N) {
               indices[grow] = (long long)win;
-              err_acc += dw;
+              err_acc += best;
             }
           }
         }
@@ -654,7 +794,7 @@ vq_search_res_kernel(const __grid_constant__ CUtensorMap tmz, const T* __restric
           }
         }
       }
-      asm volatile("bar.sync %0, 128;" ::"r"(barid) : "memory");      // myCI / myWin are reused by the next tile
+      asm volatile("bar.sync %0, 128;" ::"r"(barid) : "memory");      // myCand / myCnt / myWin are reused by the next tile
     }
     if (sqerr) {
       const float e = warp_sum(err_acc);
@@ -670,7 +810,7 @@ vq_search_res_kernel(const __grid_constant__ CUtensorMap tmz, const T* __restric
 }
 
 static size_t vq_res_smem_bytes(int nchunks) {
-  return 1024 + (size_t)nchunks * VT_CHUNK_BYTES + 2 * 32768 + (size_t)nchunks * VT_N * 4 + 3328;
+  return 1024 + (size_t)nchunks * VT_CHUNK_BYTES + 2 * 32768 + (size_t)nchunks * VT_N * 4 + 10752;
 }
 
 static size_t vq_tc_smem_bytes(int nchunks) {

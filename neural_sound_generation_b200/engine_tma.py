@@ -59,6 +59,9 @@ class EngineTMA(object):
         self.dwa_in_zbuf = False
         self.dwa_dirty = False      # the images hold a consumed fused step's sums (cleared by the next fused begin)
         self.dp = None              # dist.DataParallel: cross-rank BatchNorm statistics / bucketed gradient all-reduce
+        # BatchNorm fused into the producing convolution across a grid barrier (csrc/conv_tma.cu, BnFuse): the
+        # bn_act / bn_bwd passes of the latent-grid layers disappear.  NSG_FUSE_BN=0 keeps the separate passes.
+        self.fuse_bn = os.environ.get('NSG_FUSE_BN', '1') != '0'
 
     # ------------------------------------------------------------------ packed images
     def _prepare(self, P):
@@ -148,12 +151,14 @@ class EngineTMA(object):
         dev = x_nhwc.device
         ctx.coef = torch.empty((len(BN_LAYERS), 4, self.dim), dtype=torch.float32, device=dev)
         nst = len(BN_LAYERS) * 2 * 2 * self.dim
+        NBAR = 32                   # grid-barrier counters of the BatchNorm-fused launches (one each, zero at launch)
+        ctx.nbar = 0
         if fused:
             # everything the step accumulates into lives in ONE buffer cleared by ONE fill at the start of the step:
             # BatchNorm statistic sums (fp64), the two squared-error sums (fp64), the packed weight-gradient images
             if self.zbuf is None or self.zbuf.device != dev:
                 nd = sum(k * k for _, k, *_ in TC_LAYERS) * self.dim * self.dim
-                self.zbuf = torch.zeros((nst + 2) * 8 + nd * 4, dtype=torch.uint8, device=dev)
+                self.zbuf = torch.zeros((nst + 2) * 8 + NBAR * 4 + nd * 4, dtype=torch.uint8, device=dev)
                 self._key = None                    # the layers' dwa views are re-made by _prepare
             else:
                 self.zbuf.zero_()
@@ -161,9 +166,11 @@ class EngineTMA(object):
             f64 = self.zbuf[:(nst + 2) * 8].view(torch.float64)
             ctx.stats = f64[:nst].view(len(BN_LAYERS), 2, 2 * self.dim)
             ctx.sums = f64[nst:nst + 2]
+            ctx.bars = self.zbuf[(nst + 2) * 8:(nst + 2) * 8 + NBAR * 4].view(torch.int32)
         else:
             ctx.stats = torch.zeros((len(BN_LAYERS), 2, 2 * self.dim), dtype=torch.float64, device=dev)
             ctx.sums = None
+            ctx.bars = torch.zeros(NBAR, dtype=torch.int32, device=dev)
         ctx.fused = fused
         ctx.packed = False
         ctx.keep = []               # tensors in use on the side stream (kept alive until the join)
@@ -200,6 +207,62 @@ class EngineTMA(object):
         ops.conv_gemm_tma(g, x, L.wf, out, bias=P[name + '.bias'],
                           stats_mode=STATS_MOMENTS if stats is not None else 0, stats=stats, relu_out=relu_out)
         return out
+
+    def _fusable(self, g):
+        return (self.fuse_bn and not (self.dp is not None and self.dp.sync_bn) and ops.conv_bn_tma_fits(g))
+
+    def _bar(self, ctx):
+        b = ctx.bars[ctx.nbar:ctx.nbar + 1]
+        ctx.nbar += 1
+        return b
+
+    def _conv_bn_fwd(self, ctx, P, Bufs, name, bn_name, x, res=None, relu_out=True):
+        """conv `name` -> BatchNorm `bn_name` [-> + res] [-> ReLU].  Returns (h, v): the pre-normalisation tensor the
+        backward pass reads (None in eval mode when fused) and the operand-ready result.  One launch when the fused
+        kernel serves the shape, else convolution + bn_act."""
+        L = self.layers[name]
+        g, oh, ow = self._fwd_geom(L, x)
+        bn = self._bn(ctx, bn_name)
+        shape = (x.shape[0], oh, ow, self.dim)
+        if not ctx.training and self.fuse_bn:
+            v = torch.empty(shape, dtype=BF, device=x.device)
+            ops.conv_bn_tma(g, x, L.wf, v, ops.BNF_EVAL, P[bn_name + '.weight'], beta=P[bn_name + '.bias'], eps=BN_EPS,
+                            running_mean=Bufs[bn_name + '.running_mean'], running_var=Bufs[bn_name + '.running_var'],
+                            bias=P[name + '.bias'], add_src=res, relu_out=relu_out)
+            return None, v
+        if ctx.training and self._fusable(g):
+            h = torch.empty(shape, dtype=BF, device=x.device)
+            v = torch.empty(shape, dtype=BF, device=x.device)
+            ops.conv_bn_tma(g, x, L.wf, h, ops.BNF_TRAIN, P[bn_name + '.weight'], beta=P[bn_name + '.bias'], eps=BN_EPS,
+                            momentum=BN_MOMENTUM, count=h.numel() // self.dim,
+                            running_mean=Bufs[bn_name + '.running_mean'], running_var=Bufs[bn_name + '.running_var'],
+                            nbt=Bufs[bn_name + '.num_batches_tracked'], coef=ctx.coef[BN_INDEX[bn_name]], res=res,
+                            barrier=self._bar(ctx), out2=v, bn_relu=relu_out, bias=P[name + '.bias'], stats=bn['fstats'])
+            return h, v
+        h = self._conv_fwd(ctx, P, name, x, stats=bn['fstats'] if ctx.training else None)
+        return h, self._bn_act(ctx, P, Bufs, bn_name, h, res=res, relu_out=relu_out)
+
+    def _conv_dgrad_bn(self, ctx, P, G, name, dy, in_hw, bn_name, h, want_g, **epi):
+        """Data gradient of conv `name` (epilogue ``epi``: + skip gradient, ReLU mask) flowing into the backward of
+        BatchNorm `bn_name`, whose pre-normalisation tensor is ``h``.  Returns (g, dh): g = the gradient wrt the
+        BatchNorm output (None unless ``want_g``), dh = the gradient wrt ``h``."""
+        L = self.layers[name]
+        b, oh, ow, c = dy.shape
+        ih, iw = in_hw
+        g = ops.conv_geom(b, oh, ow, c, ih, iw, c, L.k, L.s, L.p, 0 if L.tr else 1, L.wci_d, L.wco_d, ops.BF16)
+        bn = self._bn(ctx, bn_name)
+        if self._fusable(g):
+            dh = torch.empty((b, ih, iw, c), dtype=BF, device=dy.device)
+            gy = torch.empty_like(dh) if want_g else None
+            ops.conv_bn_tma(g, dy, L.wd, gy, ops.BNF_BWD, P[bn_name + '.weight'], count=dh.numel() // self.dim,
+                            barrier=self._bar(ctx), dgamma=G[bn_name + '.weight'], dbeta=G[bn_name + '.bias'], out2=dh,
+                            stats=bn['bstats'], xhat_src=h, mean=bn['mean'], invstd=bn['invstd'], **epi)
+            return gy, dh
+        gy = self._conv_dgrad(name, dy, in_hw, stats_mode=STATS_BNBWD, stats=bn['bstats'], xhat_src=h, mean=bn['mean'],
+                              invstd=bn['invstd'], **epi)
+        conv_before = {'.block.2': '.block.1', '.block.5': '.block.4'}
+        pre = bn_name[:-8] + conv_before[bn_name[-8:]] + '.bias' if bn_name[-8:] in conv_before else None
+        return gy, self._bn_bwd(ctx, P, G, bn_name, gy, h, G[pre] if pre else None)
 
     def _conv_dgrad(self, name, dy, in_hw, **epi):
         L = self.layers[name]
@@ -263,35 +326,30 @@ class EngineTMA(object):
     # ------------------------------------------------------------------ ResBlock (models.py:145-158)
     def resblock_fwd(self, ctx, P, Bufs, name, r, relu_out):
         """r = relu(block input) (operand-ready).  Returns relu(y) or y, with y = r + BN5(Conv1x1(relu(BN2(Conv3x3(r)))))."""
-        tr = ctx.training
-        bn2, bn5 = self._bn(ctx, name + '.block.2'), self._bn(ctx, name + '.block.5')
-        h1 = self._conv_fwd(ctx, P, name + '.block.1', r, stats=bn2['fstats'] if tr else None)
-        v1 = self._bn_act(ctx, P, Bufs, name + '.block.2', h1, relu_out=True)
-        h2 = self._conv_fwd(ctx, P, name + '.block.4', v1, stats=bn5['fstats'] if tr else None)
-        y = self._bn_act(ctx, P, Bufs, name + '.block.5', h2, res=r, relu_out=relu_out)
+        h1, v1 = self._conv_bn_fwd(ctx, P, Bufs, name + '.block.1', name + '.block.2', r, relu_out=True)
+        h2, y = self._conv_bn_fwd(ctx, P, Bufs, name + '.block.4', name + '.block.5', v1, res=r, relu_out=relu_out)
         ctx.saved[name] = (r, h1, v1, h2)
         return y
 
-    def resblock_bwd(self, ctx, P, G, name, g_y, prev_block=None):
-        """g_y: gradient wrt the block output y with this block's BN5 backward sums already accumulated by its
-        producer.  Returns the gradient wrt the block's pre-ReLU input; when ``prev_block`` names the ResBlock
-        that produced that input, its BN5 backward sums are accumulated by the same epilogue."""
+    def resblock_bwd(self, ctx, P, G, name, g_y, g_h2=None, prev_block=None):
+        """g_y: gradient wrt the block output y.  g_h2: gradient wrt the block's second convolution output (BN5
+        backward already applied by the fused producer of g_y), or None: g_y then carries this block's BN5 backward
+        sums (accumulated by its producer) and the separate pass runs here.  Returns (g, g_h2_prev): the gradient wrt
+        the block's pre-ReLU input and, when ``prev_block`` names the ResBlock that produced that input and the fused
+        kernel serves the shape, the gradient wrt ITS second convolution output (else None, with that block's BN5
+        backward sums accumulated)."""
         r, h1, v1, h2 = ctx.saved[name]
         hw = r.shape[1:3]
-        bn2 = self._bn(ctx, name + '.block.2')
-        g_h2 = self._bn_bwd(ctx, P, G, name + '.block.5', g_y, h2, G[name + '.block.4.bias'])
+        if g_h2 is None:
+            g_h2 = self._bn_bwd(ctx, P, G, name + '.block.5', g_y, h2, G[name + '.block.4.bias'])
         self._conv_wgrad(ctx, name + '.block.4', v1, g_h2)
-        g_v1 = self._conv_dgrad(name + '.block.4', g_h2, hw, mask_mode=MASK_POS, mask_src=v1,
-                                stats_mode=STATS_BNBWD, stats=bn2['bstats'], xhat_src=h1, mean=bn2['mean'],
-                                invstd=bn2['invstd'])
-        g_h1 = self._bn_bwd(ctx, P, G, name + '.block.2', g_v1, h1, G[name + '.block.1.bias'])
+        _, g_h1 = self._conv_dgrad_bn(ctx, P, G, name + '.block.4', g_h2, hw, name + '.block.2', h1, False,
+                                      mask_mode=MASK_POS, mask_src=v1)
         self._conv_wgrad(ctx, name + '.block.1', r, g_h1)
-        epi = dict(add_src=g_y, mask_mode=MASK_POS, mask_src=r)
         if prev_block is not None:
-            pbn = self._bn(ctx, prev_block + '.block.5')
-            epi.update(stats_mode=STATS_BNBWD, stats=pbn['bstats'], xhat_src=ctx.saved[prev_block][3],
-                       mean=pbn['mean'], invstd=pbn['invstd'])
-        return self._conv_dgrad(name + '.block.1', g_h1, hw, **epi)
+            return self._conv_dgrad_bn(ctx, P, G, name + '.block.1', g_h1, hw, prev_block + '.block.5',
+                                       ctx.saved[prev_block][3], True, add_src=g_y, mask_mode=MASK_POS, mask_src=r)
+        return self._conv_dgrad(name + '.block.1', g_h1, hw, add_src=g_y, mask_mode=MASK_POS, mask_src=r), None
 
     # ------------------------------------------------------------------ encoder / decoder (models.py:164-184)
     def encoder_fwd(self, ctx, P, Bufs, x):
@@ -325,9 +383,7 @@ class EngineTMA(object):
         ops.relu64(z_q, rq)
         r1 = self.resblock_fwd(ctx, P, Bufs, 'decoder.0', rq, relu_out=True)
         rd = self.resblock_fwd(ctx, P, Bufs, 'decoder.1', r1, relu_out=True)   # + decoder.2 ReLU
-        bn4 = self._bn(ctx, 'decoder.4')
-        u0 = self._conv_fwd(ctx, P, 'decoder.3', rd, stats=bn4['fstats'] if tr else None)
-        v4 = self._bn_act(ctx, P, Bufs, 'decoder.4', u0, relu_out=True)
+        u0, v4 = self._conv_bn_fwd(ctx, P, Bufs, 'decoder.3', 'decoder.4', rd, relu_out=True)
         b, h, w, _ = v4.shape
         w6 = P['decoder.6.weight']
         cout = w6.shape[1]
@@ -371,12 +427,10 @@ class EngineTMA(object):
                           stats=bn4['bstats'], xhat_src=u0, mean=bn4['mean'], invstd=bn4['invstd'])
         g_u0 = self._bn_bwd(ctx, P, G, 'decoder.4', g_v4, u0, G['decoder.3.bias'])
         self._conv_wgrad(ctx, 'decoder.3', rd, g_u0)
-        pbn = self._bn(ctx, 'decoder.1.block.5')
-        g_d1 = self._conv_dgrad('decoder.3', g_u0, rd.shape[1:3], mask_mode=MASK_POS, mask_src=rd,
-                                stats_mode=STATS_BNBWD, stats=pbn['bstats'], xhat_src=ctx.saved['decoder.1'][3],
-                                mean=pbn['mean'], invstd=pbn['invstd'])
-        g_d0 = self.resblock_bwd(ctx, P, G, 'decoder.1', g_d1, prev_block='decoder.0')
-        return self.resblock_bwd(ctx, P, G, 'decoder.0', g_d0)
+        g_d1, g_d1h = self._conv_dgrad_bn(ctx, P, G, 'decoder.3', g_u0, rd.shape[1:3], 'decoder.1.block.5',
+                                          ctx.saved['decoder.1'][3], True, mask_mode=MASK_POS, mask_src=rd)
+        g_d0, g_d0h = self.resblock_bwd(ctx, P, G, 'decoder.1', g_d1, g_d1h, prev_block='decoder.0')
+        return self.resblock_bwd(ctx, P, G, 'decoder.0', g_d0, g_d0h)[0]
 
     def bottleneck_bwd(self, ctx, g_st, z_e, z_q, coef):
         """dz = g_st + coef*(z_e - z_q) with encoder.5's BN5 backward sums."""
@@ -398,8 +452,8 @@ class EngineTMA(object):
     def encoder_bwd(self, ctx, P, G, g_ze, need_dx=False):
         x, a0, v0 = ctx.x, ctx.a0, ctx.v0
         bn1 = self._bn(ctx, 'encoder.1')
-        g_r5 = self.resblock_bwd(ctx, P, G, 'encoder.5', g_ze, prev_block='encoder.4')
-        g_a1 = self.resblock_bwd(ctx, P, G, 'encoder.4', g_r5)
+        g_r5, g_r5h = self.resblock_bwd(ctx, P, G, 'encoder.5', g_ze, None, prev_block='encoder.4')
+        g_a1 = self.resblock_bwd(ctx, P, G, 'encoder.4', g_r5, g_r5h)[0]
         self._conv_wgrad(ctx, 'encoder.3', v0, g_a1, q_colsum=G['encoder.3.bias'])
         g_v0 = self._conv_dgrad('encoder.3', g_a1, v0.shape[1:3], mask_mode=MASK_POS, mask_src=v0,
                                 stats_mode=STATS_BNBWD, stats=bn1['bstats'], xhat_src=a0, mean=bn1['mean'],

@@ -388,6 +388,46 @@ def conv_gemm_tma(geom, x, packed, out, bias=None, add_src=None, mask_mode=MASK_
     return out
 
 
+BNF_TRAIN, BNF_EVAL, BNF_BWD = 1, 2, 3
+_fits_cache = {}
+
+
+def conv_bn_tma_fits(geom):
+    """True when a BatchNorm-fused (grid-barrier) launch of this geometry fits: <= 8 tiles per CTA on this device."""
+    A.require_device()
+    key = (torch.cuda.current_device(),) + tuple(getattr(geom, f) for f, _ in geom._fields_)
+    r = _fits_cache.get(key)
+    if r is None:
+        r = _fits_cache[key] = A.load().nsg_conv_bn_tma_fits(C.byref(geom)) == 1
+    return r
+
+
+def conv_bn_tma(geom, x, packed, out, bn_mode, gamma, beta=None, eps=1e-5, momentum=0.1, count=1.0, running_mean=None,
+                running_var=None, nbt=None, coef=None, res=None, barrier=None, dgamma=None, dbeta=None, out2=None,
+                bn_relu=False, bias=None, add_src=None, mask_mode=MASK_NONE, mask_src=None, stats=None,
+                xhat_src=None, mean=None, invstd=None, relu_out=False):
+    """nsg_conv_bn_tma: the TMA convolution with the BatchNorm that follows it (forward) / that its output gradient
+    flows into (backward) fused; see include/nsg_b200.h (nsg_bn_fuse).  ``out`` may be None for TRAIN / BWD."""
+    global launch_count
+    A.require_device()
+    _cuda(x, packed, out, out2, bias, add_src, mask_src, stats, xhat_src, res, barrier)
+    _bf16(x, out, out2, add_src, mask_src, xhat_src, res)
+    _contig(x, 'conv input')
+    for t, what in ((out, 'conv output'), (out2, 'second output'), (res, 'residual')):
+        if t is not None:
+            _contig(t, what)
+    stats_mode = {BNF_TRAIN: STATS_MOMENTS, BNF_BWD: STATS_BNBWD}.get(bn_mode, STATS_NONE)
+    epi = A.Epilogue(A.ptr(bias), A.ptr(add_src), mask_mode, A.ptr(mask_src), None, None, stats_mode, A.ptr(stats),
+                     A.ptr(xhat_src), A.ptr(mean), A.ptr(invstd), 2 if relu_out else 0)
+    bn = A.BnFuse(bn_mode, 1 if bn_relu else 0, A.ptr(gamma), A.ptr(beta), eps, momentum, float(count),
+                  A.ptr(running_mean), A.ptr(running_var), A.ptr(nbt), A.ptr(coef), A.ptr(res), A.ptr(barrier),
+                  A.ptr(dgamma), A.ptr(dbeta), A.ptr(out2))
+    rc = A.load().nsg_conv_bn_tma(C.byref(geom), A.ptr(x), A.ptr(packed), C.byref(epi), C.byref(bn), A.ptr(out),
+                                  A.stream_ptr())
+    A.check(rc, 'nsg_conv_bn_tma')
+    launch_count += 1
+
+
 def conv_wgrad_slices(geom):
     """Number of partial images conv_wgrad_tma(..., sliced=True) writes for this geometry on the current device."""
     A.require_device()

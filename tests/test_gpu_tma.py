@@ -349,3 +349,182 @@ def test_programmatic_dependent_launch_keeps_results_and_orders_repacked_weights
     for o0, o1 in zip(results[0], results[1]):
         assert torch.isfinite(o0.float()).all()
         assert torch.equal(o0, o1)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# BatchNorm fused into the producing convolution across a grid barrier (nsg_conv_bn_tma): train forward, eval fold and
+# backward, against fp64 autograd fed the same bf16-rounded operands.  Sizes cover one tile per CTA, several tiles per
+# CTA of a full 148-CTA grid (the 4- and 8-accumulator instantiations) and a shape that does not fit.
+# ---------------------------------------------------------------------------------------------------------------------
+BN_CASES = [
+    # (k, H, W, B, with residual, relu)
+    (3, 7, 9, 3, False, True),
+    (1, 5, 6, 2, True, False),
+    (3, 20, 64, 32, False, True),      # configs[1] latent grid: 320 tiles on 148 CTAs (3 per CTA, 256 TMEM columns)
+    (1, 20, 64, 32, True, True),
+    (3, 20, 64, 70, True, True),       # 700 tiles: 5 per CTA (512 TMEM columns)
+]
+
+
+def _bf(t):
+    return nhwc(t).to(DEV).to(BF)
+
+
+@pytest.mark.parametrize('case', BN_CASES)
+def test_conv_bn_tma_train_eval_backward(case):
+    k, H, W, B, with_res, relu = case
+    C, p = 64, k // 2
+    rng = np.random.RandomState(abs(hash(case)) % 2 ** 31)
+    x = _r16(_rand(rng, B, C, H, W))
+    w = _r16(_rand(rng, C, C, k, k) * 0.2)
+    bias, gamma, beta = _rand(rng, C), _rand(rng, C) * 0.5 + 1.0, _rand(rng, C) * 0.3
+    res = _r16(_rand(rng, B, C, H, W)) if with_res else None
+    rm0, rv0 = _rand(rng, C) * 0.1, torch.rand(C) + 0.5
+    fwd, dgr, _, OH, OW = _geoms(B, H, W, k, 1, p, False)
+    assert ops.conv_bn_tma_fits(fwd)
+    n = B * OH * OW
+    # ---- fp64 reference (torch semantics: biased variance normalises, unbiased updates the running statistics)
+    xd, wd = x.double(), w.double()
+    h_ref = F.conv2d(xd, wd, bias.double(), 1, p)
+    mean, var = h_ref.mean((0, 2, 3)), h_ref.var((0, 2, 3), unbiased=False)
+    invstd = 1.0 / torch.sqrt(var + 1e-5)
+    y_ref = (h_ref - mean[None, :, None, None]) * (invstd * gamma.double())[None, :, None, None] + beta.double()[None, :, None, None]
+    if with_res:
+        y_ref = y_ref + res.double()
+    v_ref = y_ref.clamp_min(0) if relu else y_ref
+    # ---- fused train forward
+    xg, wg = _bf(x), w.to(DEV)
+    packed = ops.conv_pack_tma(fwd, wg)
+    h = torch.empty((B, OH, OW, C), dtype=BF, device=DEV)
+    v = torch.empty_like(h)
+    stats = torch.zeros(2 * C, dtype=torch.float64, device=DEV)
+    bars = torch.zeros(4, dtype=torch.int32, device=DEV)
+    coef = torch.zeros((4, C), dtype=torch.float32, device=DEV)
+    rm, rv = rm0.to(DEV), rv0.to(DEV)
+    nbt = torch.zeros((), dtype=torch.int64, device=DEV)
+    ops.conv_bn_tma(fwd, xg, packed, h, ops.BNF_TRAIN, gamma.to(DEV), beta=beta.to(DEV), eps=1e-5, momentum=0.1, count=n,
+                    running_mean=rm, running_var=rv, nbt=nbt, coef=coef, res=_bf(res) if with_res else None,
+                    barrier=bars[0:1], out2=v, bn_relu=relu, bias=bias.to(DEV), stats=stats)
+    torch.cuda.synchronize()
+    assert relerr(nchw(h.float()), h_ref) < OUT_TOL, 'h'
+    assert relerr(nchw(v.float()), v_ref) < OUT_TOL, 'v'
+    assert relerr(coef[0].cpu(), mean) < ACC_TOL and relerr(coef[1].cpu(), invstd) < ACC_TOL
+    assert relerr(rm.cpu(), 0.9 * rm0.double() + 0.1 * mean) < ACC_TOL
+    assert relerr(rv.cpu(), 0.9 * rv0.double() + 0.1 * var * n / (n - 1)) < ACC_TOL
+    assert nbt.item() == 1 and 0 < bars[0].item() <= 148        # every CTA of the grid arrived once
+    # the fused result equals the two-launch form (convolution + bn_act) up to the bf16 rounding of h
+    h2 = torch.empty_like(h)
+    v2 = torch.empty_like(h)
+    stats2 = torch.zeros_like(stats)
+    ops.conv_gemm_tma(fwd, xg, packed, h2, bias=bias.to(DEV), stats_mode=ops.STATS_MOMENTS, stats=stats2)
+    ops.bn_act64(h2, v2, gamma.to(DEV), beta.to(DEV), stats=stats2, count=n, res=_bf(res) if with_res else None,
+                 relu_out=relu, eps=1e-5, momentum=0.1)
+    torch.cuda.synchronize()
+    assert torch.equal(h, h2)
+    assert relerr(stats, stats2) < 1e-5
+    assert relerr(v.float(), v2.float()) < OUT_TOL
+    # ---- eval fold
+    ve = torch.empty_like(h)
+    ops.conv_bn_tma(fwd, xg, packed, ve, ops.BNF_EVAL, gamma.to(DEV), beta=beta.to(DEV), eps=1e-5,
+                    running_mean=rm0.to(DEV), running_var=rv0.to(DEV), bias=bias.to(DEV),
+                    add_src=_bf(res) if with_res else None, relu_out=relu)
+    torch.cuda.synchronize()
+    ye = (h_ref - rm0.double()[None, :, None, None]) * (gamma.double() / torch.sqrt(rv0.double() + 1e-5))[None, :, None, None] \
+        + beta.double()[None, :, None, None]
+    if with_res:
+        ye = ye + res.double()
+    assert relerr(nchw(ve.float()), ye.clamp_min(0) if relu else ye) < OUT_TOL, 'eval'
+    # ---- backward: g = mask(dgrad(dy) [+ skip]) flows into the backward of a BatchNorm whose input was hb
+    dy = _r16(_rand(rng, B, C, OH, OW))
+    hb = _r16(_rand(rng, B, C, H, W) * 1.5 + 0.2)                   # pre-normalisation tensor of the BN being differentiated
+    maskt = _r16(_rand(rng, B, C, H, W))
+    skip = _r16(_rand(rng, B, C, H, W)) if with_res else None
+    mu_b = hb.double().mean((0, 2, 3))
+    is_b = 1.0 / torch.sqrt(hb.double().var((0, 2, 3), unbiased=False) + 1e-5)
+    g_ref = F.conv_transpose2d(dy.double(), wd, None, 1, p)
+    if with_res:
+        g_ref = g_ref + skip.double()
+    g_ref = g_ref * (maskt.double() > 0)
+    xhat = (hb.double() - mu_b[None, :, None, None]) * is_b[None, :, None, None]
+    nb = B * H * W
+    sg, sgx = g_ref.sum((0, 2, 3)), (g_ref * xhat).sum((0, 2, 3))
+    dh_ref = (gamma.double() * is_b)[None, :, None, None] * (g_ref - sg[None, :, None, None] / nb
+                                                             - xhat * sgx[None, :, None, None] / nb)
+    gout = torch.empty((B, H, W, C), dtype=BF, device=DEV)
+    dh = torch.empty_like(gout)
+    bst = torch.zeros(2 * C, dtype=torch.float64, device=DEV)
+    dgamma = torch.full((C,), 0.5, dtype=torch.float32, device=DEV)
+    dbeta = torch.full((C,), -0.25, dtype=torch.float32, device=DEV)
+    ops.conv_bn_tma(dgr, _bf(dy), ops.conv_pack_tma(dgr, wg), gout, ops.BNF_BWD, gamma.to(DEV), count=nb,
+                    barrier=bars[1:2], dgamma=dgamma, dbeta=dbeta, out2=dh, stats=bst, xhat_src=_bf(hb),
+                    mean=mu_b.float().to(DEV), invstd=is_b.float().to(DEV), add_src=_bf(skip) if with_res else None,
+                    mask_mode=ops.MASK_POS, mask_src=_bf(maskt))
+    torch.cuda.synchronize()
+    assert relerr(nchw(gout.float()), g_ref) < OUT_TOL, 'g'
+    assert relerr(nchw(dh.float()), dh_ref) < 2 * OUT_TOL, 'dh'
+    assert relerr(dgamma.cpu() - 0.5, sgx) < ACC_TOL * 5 and relerr(dbeta.cpu() + 0.25, sg) < ACC_TOL * 5
+    # g not wanted: same dh
+    dh2 = torch.empty_like(dh)
+    bst.zero_()
+    ops.conv_bn_tma(dgr, _bf(dy), ops.conv_pack_tma(dgr, wg), None, ops.BNF_BWD, gamma.to(DEV), count=nb,
+                    barrier=bars[2:3], out2=dh2, stats=bst, xhat_src=_bf(hb), mean=mu_b.float().to(DEV),
+                    invstd=is_b.float().to(DEV), add_src=_bf(skip) if with_res else None, mask_mode=ops.MASK_POS,
+                    mask_src=_bf(maskt))
+    torch.cuda.synchronize()
+    assert relerr(dh2.float(), dh.float()) < 1e-3
+
+
+def test_conv_bn_tma_more_tiles_than_accumulators():
+    """The 40 x 128 grid at batch 32 is 1280 tiles = 9 per CTA, one more than the 8 TMEM accumulators: the first tile
+    of each CTA is read back in pass 2 from the h / g that pass 1 stored.  Fused launches against the two-launch form
+    (convolution + bn_act64 / bn_bwd64) on decoder.3's forward and encoder.3's data gradient."""
+    rng = np.random.RandomState(11)
+    B, C = 32, 64
+    gamma, beta = (_rand(rng, C) * 0.5 + 1.0).to(DEV), (_rand(rng, C) * 0.3).to(DEV)
+    bias = _rand(rng, C).to(DEV)
+    # ---- decoder.3 forward: ConvTranspose2d(64, 64, 4, 2, 1) 20 x 64 -> 40 x 128, BatchNorm, ReLU
+    fwd, _, _, OH, OW = _geoms(B, 20, 64, 4, 2, 1, True)
+    assert ops.conv_bn_tma_fits(fwd)
+    x = _rand(rng, B, 20, 64, C).to(DEV).to(BF)
+    w = (_rand(rng, C, C, 4, 4) * 0.1).to(DEV)
+    packed = ops.conv_pack_tma(fwd, w)
+    n = B * OH * OW
+    h, v = (torch.empty((B, OH, OW, C), dtype=BF, device=DEV) for _ in range(2))
+    st = torch.zeros(2 * C, dtype=torch.float64, device=DEV)
+    bars = torch.zeros(4, dtype=torch.int32, device=DEV)
+    ops.conv_bn_tma(fwd, x, packed, h, ops.BNF_TRAIN, gamma, beta=beta, count=n, barrier=bars[0:1], out2=v, bn_relu=True,
+                    bias=bias, stats=st)
+    h2, v2 = torch.empty_like(h), torch.empty_like(h)
+    st2 = torch.zeros_like(st)
+    ops.conv_gemm_tma(fwd, x, packed, h2, bias=bias, stats_mode=ops.STATS_MOMENTS, stats=st2)
+    ops.bn_act64(h2, v2, gamma, beta, stats=st2, count=n, relu_out=True)
+    torch.cuda.synchronize()
+    assert torch.equal(h, h2) and relerr(st, st2) < 1e-5
+    assert relerr(v.float(), v2.float()) < OUT_TOL
+    # ---- encoder.3 data gradient: Conv2d(64, 64, 4, 2, 1) 40 x 128 -> 20 x 64, gradient back on the 40 x 128 grid
+    _, dgr, _, _, _ = _geoms(B, 40, 128, 4, 2, 1, False)
+    dy = _rand(rng, B, 20, 64, C).to(DEV).to(BF)
+    hb = (_rand(rng, B, 40, 128, C) * 1.5 + 0.2).to(DEV).to(BF)
+    maskt = _rand(rng, B, 40, 128, C).to(DEV).to(BF)
+    mu = hb.float().mean((0, 1, 2))
+    istd = 1.0 / torch.sqrt(hb.float().var((0, 1, 2), unbiased=False) + 1e-5)
+    pk = ops.conv_pack_tma(dgr, w)
+    nb = B * 40 * 128
+    g, dh = torch.empty_like(hb), torch.empty_like(hb)
+    bst = torch.zeros(2 * C, dtype=torch.float64, device=DEV)
+    dgam, dbet = torch.zeros(C, device=DEV), torch.zeros(C, device=DEV)
+    ops.conv_bn_tma(dgr, dy, pk, g, ops.BNF_BWD, gamma, count=nb, barrier=bars[1:2], dgamma=dgam, dbeta=dbet, out2=dh,
+                    stats=bst, xhat_src=hb, mean=mu, invstd=istd, mask_mode=ops.MASK_POS, mask_src=maskt)
+    g2, dh2 = torch.empty_like(hb), torch.empty_like(hb)
+    bst2 = torch.zeros_like(bst)
+    dgam2, dbet2 = torch.zeros(C, device=DEV), torch.zeros(C, device=DEV)
+    ops.conv_gemm_tma(dgr, dy, pk, g2, mask_mode=ops.MASK_POS, mask_src=maskt, stats_mode=ops.STATS_BNBWD, stats=bst2,
+                      xhat_src=hb, mean=mu, invstd=istd)
+    ops.bn_bwd64(g2, hb, dh2, bst2, nb, mu, istd, gamma, dgamma=dgam2, dbeta=dbet2)
+    torch.cuda.synchronize()
+    assert torch.equal(g, g2) and relerr(bst, bst2) < 1e-4
+    assert relerr(dh.float(), dh2.float()) < OUT_TOL
+    assert relerr(dgam, dgam2) < 1e-4 and relerr(dbet, dbet2) < 1e-4
+    with pytest.raises(Exception, match='first output'):
+        ops.conv_bn_tma(fwd, x, packed, None, ops.BNF_TRAIN, gamma, beta=beta, count=n, barrier=bars[2:3], out2=v,
+                        bias=bias, stats=st)

@@ -1,0 +1,12 @@
+#!/bin/bash
+# round-2 GPU visit: suite, smoke, bench (ours + reference arm)
+TAG=${1:-r2a}; shift
+mkdir -p gpurun_out
+nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm --format=csv > gpurun_out/${TAG}_smi.txt
+timeout 1500 python -m pytest tests -m gpu -q -p no:cacheprovider --timeout 600 -s > gpurun_out/${TAG}_pytest.log 2>&1
+echo "pytest exit $?"; grep -E "^(FAILED|ERROR)|passed|failed" gpurun_out/${TAG}_pytest.log | cut -c1-300
+timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/${TAG}_smoke.log 2>&1; echo "smoke exit $?"; tail -n 3 gpurun_out/${TAG}_smoke.log
+timeout 600 python bench.py --steps 20 --warmup 5 "$@" > gpurun_out/${TAG}_bench.log 2>&1
+echo "bench exit $?"; tail -n 2 gpurun_out/${TAG}_bench.log | cut -c1-1500
+timeout 600 python bench.py --impl reference --steps 5 --warmup 2 > gpurun_out/${TAG}_bench_ref.log 2>&1
+echo "ref exit $?"; tail -n 1 gpurun_out/${TAG}_bench_ref.log | cut -c1-600
