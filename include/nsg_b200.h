@@ -319,9 +319,10 @@ int nsg_recon_loss(const float* x_tilde, const float* c, int batch, int h, int w
                    float* dpre, void* stream);
 
 /* The same for a bf16 x_tilde (the TMA engine's decoder output), with the conversions around it folded in: dpre
- * (nullable) is written as bf16, x_tilde_f32 (nullable, (B,H,wt)) receives x_tilde widened to fp32. */
+ * (nullable) is written as bf16, x_tilde_f32 (nullable, (B,H,wt)) receives x_tilde widened to fp32, dpre_sum (nullable,
+ * one float) += the sum of the written dpre values = the gradient of the output layer's bias (models.py:182). */
 int nsg_recon_loss_bf16(const void* x_tilde, const float* c, int batch, int h, int w, int wt, double* loss_sum,
-                        void* dpre, float* x_tilde_f32, void* stream);
+                        void* dpre, float* x_tilde_f32, float* dpre_sum, void* stream);
 /* losses3 = [sums[0]*recon_scale, sums[1]*vq_scale, sums[1]*vq_scale]: loss_recons, loss_vq, loss_commit
  * (train.py:129-134; the last two are the same number before beta) from the accumulated squared-error sums */
 int nsg_loss_finalize(const double* sums, double recon_scale, double vq_scale, double* losses3, void* stream);
@@ -330,12 +331,14 @@ int nsg_loss_finalize(const double* sums, double recon_scale, double vq_scale, d
 int nsg_tanh_bwd(const float* g, const float* y, float* out, long long n, void* stream);
 
 /* ---------------------------------------------------------------- optimiser (torch.optim.Adam, main.py:124) */
-/* one Adam step over a flat fp32 buffer.  step_count is a device scalar (incremented by a second one-thread launch
- * AFTER use, so graphs replay correctly).  grad_scale multiplies grads (DP averaging).  zero_grads != 0 clears each
- * gradient after it has been used (the next step's optimizer.zero_grad(), main.py/train.py:116, for free). */
+/* one Adam step over a flat fp32 buffer.  step_count is a device scalar incremented AFTER use (graphs replay
+ * correctly): by the last block of the same launch when `ticket` (one zero-initialised unsigned counter owned by this
+ * optimiser, zero again afterwards) is given, else by a second one-thread launch.  grad_scale multiplies grads (DP
+ * averaging).  zero_grads != 0 clears each gradient after it has been used (the next step's optimizer.zero_grad(),
+ * main.py/train.py:116, for free). */
 int nsg_adam_step(float* params, float* grads, float* exp_avg, float* exp_avg_sq, long long n, float lr,
                   float beta1, float beta2, float eps, float grad_scale, long long* step_count, int zero_grads,
-                  void* stream);
+                  unsigned int* ticket, void* stream);
 
 #ifdef __cplusplus
 }

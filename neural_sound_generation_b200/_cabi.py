@@ -95,7 +95,7 @@ def load():
     lib.nsg_conv_wgrad_tma.argtypes = [C.POINTER(ConvGeom), vp, vp, vp, vp, vp]
     lib.nsg_wgrad_unpack_many.argtypes = [i, vp, vp, vp, vp, vp, vp, vp]
     lib.nsg_pdl.argtypes = [i]
-    lib.nsg_recon_loss_bf16.argtypes = [vp, vp, i, i, i, i, vp, vp, vp, vp]
+    lib.nsg_recon_loss_bf16.argtypes = [vp, vp, i, i, i, i, vp, vp, vp, vp, vp]
     lib.nsg_loss_finalize.argtypes = [vp, C.c_double, C.c_double, vp, vp]
     lib.nsg_conv_wgrad_slices.argtypes = [C.POINTER(ConvGeom)]
     lib.nsg_conv_wgrad_tma_sliced.argtypes = [C.POINTER(ConvGeom), vp, vp, vp, vp, vp]
@@ -120,7 +120,7 @@ def load():
     lib.nsg_vq_resident.argtypes = [i]
     lib.nsg_ema_update.argtypes = [vp, vp, vp, vp, vp, i, i, f, f, vp, vp]
     lib.nsg_tanh_bwd.argtypes = [vp, vp, vp, ll, vp]
-    lib.nsg_adam_step.argtypes = [vp, vp, vp, vp, ll, f, f, f, f, f, vp, i, vp]
+    lib.nsg_adam_step.argtypes = [vp, vp, vp, vp, ll, f, f, f, f, f, vp, i, vp, vp]
     for name in EXPORTS:
         fn = getattr(lib, name)
         if name not in ('nsg_version', 'nsg_last_error'):

@@ -271,10 +271,11 @@ recon_loss_kernel(const float* __restrict__ xt, const float* __restrict__ c, lon
 // the caller, dpre narrowed to the bf16 the decoder's backward kernels read) -- one pass instead of three
 __global__ void __launch_bounds__(256)
 recon_loss_bf16_kernel(const __nv_bfloat16* __restrict__ xt, const float* __restrict__ c, long long rows, int w, int wt,
-                       double* loss_sum, __nv_bfloat16* __restrict__ dpre, float* __restrict__ xt32, float gscale) {
+                       double* loss_sum, __nv_bfloat16* __restrict__ dpre, float* __restrict__ xt32, float gscale,
+                       float* __restrict__ dpre_sum) {
   pdl_wait();
   pdl_trigger();
-  float acc = 0.f;
+  float acc = 0.f, dsum = 0.f;
   const long long total = rows * w;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
@@ -288,16 +289,29 @@ recon_loss_bf16_kernel(const __nv_bfloat16* __restrict__ xt, const float* __rest
     }
     const float d = x - t;
     acc = fmaf(d, d, acc);
-    if (dpre && wi < wt) dpre[r * wt + wi] = __float2bfloat16_rn(gscale * d * (1.f - x * x));
+    if (dpre && wi < wt) {
+      const __nv_bfloat16 dv = __float2bfloat16_rn(gscale * d * (1.f - x * x));
+      dpre[r * wt + wi] = dv;
+      dsum += __bfloat162float(dv);        // (the rounded value: what the decoder's backward kernels read)
+    }
   }
-  __shared__ float part[8];
+  __shared__ float part[8], part2[8];
   acc = warp_sum(acc);
-  if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = acc;
+  dsum = warp_sum(dsum);
+  if ((threadIdx.x & 31) == 0) {
+    part[threadIdx.x >> 5] = acc;
+    part2[threadIdx.x >> 5] = dsum;
+  }
   __syncthreads();
   if (threadIdx.x == 0) {
     double s = 0.0;
-    for (int i = 0; i < 8; ++i) s += (double)part[i];
+    float s2 = 0.f;
+    for (int i = 0; i < 8; ++i) {
+      s += (double)part[i];
+      s2 += part2[i];
+    }
     atomicAdd(loss_sum, s);
+    if (dpre_sum) atomicAdd(dpre_sum, s2);   // gradient of the output layer's single bias (models.py:182)
   }
 }
 
@@ -316,7 +330,8 @@ __global__ void loss_finalize_kernel(const double* __restrict__ sums, double a, 
 template <int VEC>
 __global__ void __launch_bounds__(256)
 adam_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m, float* __restrict__ v, long long n,
-            float lr, float b1, float b2, float eps, float gscale, const long long* __restrict__ step_count, int zero) {
+            float lr, float b1, float b2, float eps, float gscale, long long* step_count, int zero,
+            unsigned int* ticket) {
   pdl_wait();
   pdl_trigger();
   __shared__ float s_step_size, s_bc2_sqrt;
@@ -359,6 +374,18 @@ adam_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m,
     } else {
       p[i] = pi[0]; m[i] = mi[0]; v[i] = vi[0];
       if (zero) g[i] = 0.f;
+    }
+  }
+  // step counter: advanced by the LAST block to finish (every block read it at its start), so the optimiser step
+  // is one launch; `ticket` is a zero-initialised counter owned by the caller, left at zero again
+  if (ticket) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence();
+      if (atomicAdd(ticket, 1u) == gridDim.x - 1) {
+        *ticket = 0u;
+        *step_count += 1;
+      }
     }
   }
 }
@@ -518,7 +545,7 @@ int nsg_recon_loss(const float* x_tilde, const float* c, int batch, int h, int w
 }
 
 int nsg_recon_loss_bf16(const void* x_tilde, const float* c, int batch, int h, int w, int wt, double* loss_sum,
-                        void* dpre, float* x_tilde_f32, void* stream) {
+                        void* dpre, float* x_tilde_f32, float* dpre_sum, void* stream) {
   NSG_REQUIRE(x_tilde && c && loss_sum && batch >= 0 && h >= 0 && w >= 0 && wt >= 0 && wt <= w,
               "recon_loss_bf16: bad arguments");
   const long long rows = (long long)batch * h;
@@ -526,7 +553,7 @@ int nsg_recon_loss_bf16(const void* x_tilde, const float* c, int batch, int h, i
   const float gscale = (float)(2.0 / ((double)rows * w));
   launch_pdl(recon_loss_bf16_kernel, dim3(grid_for(rows * w, 256)), dim3(256), 0, (cudaStream_t)stream,
              static_cast<const __nv_bfloat16*>(x_tilde), c, rows, w, wt, loss_sum, static_cast<__nv_bfloat16*>(dpre),
-             x_tilde_f32, gscale);
+             x_tilde_f32, gscale, dpre_sum);
   NSG_CHECK_LAUNCH("recon_loss_bf16_kernel");
   return NSG_OK;
 }
@@ -548,7 +575,7 @@ int nsg_tanh_bwd(const float* g, const float* y, float* out, long long n, void* 
 
 int nsg_adam_step(float* params, float* grads, float* exp_avg, float* exp_avg_sq, long long n, float lr,
                   float beta1, float beta2, float eps, float grad_scale, long long* step_count, int zero_grads,
-                  void* stream) {
+                  unsigned int* ticket, void* stream) {
   NSG_REQUIRE(params && grads && exp_avg && exp_avg_sq && step_count && n >= 0, "adam_step: bad arguments");
   if (n > 0) {
     const bool vec = n % 4 == 0 && ((reinterpret_cast<uintptr_t>(params) | reinterpret_cast<uintptr_t>(grads) |
@@ -557,12 +584,13 @@ int nsg_adam_step(float* params, float* grads, float* exp_avg, float* exp_avg_sq
       int blocks = grid_for(n / 4, 256);
       if (blocks > 2 * num_sms()) blocks = 2 * num_sms();
       launch_pdl(adam_kernel<4>, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, params, grads, exp_avg, exp_avg_sq, n,
-                 lr, beta1, beta2, eps, grad_scale, step_count, zero_grads);
+                 lr, beta1, beta2, eps, grad_scale, step_count, zero_grads, ticket);
     } else {
       launch_pdl(adam_kernel<1>, dim3(grid_for(n, 256)), dim3(256), 0, (cudaStream_t)stream, params, grads, exp_avg,
-                 exp_avg_sq, n, lr, beta1, beta2, eps, grad_scale, step_count, zero_grads);
+                 exp_avg_sq, n, lr, beta1, beta2, eps, grad_scale, step_count, zero_grads, ticket);
     }
     NSG_CHECK_LAUNCH("adam_kernel");
+    if (ticket) return NSG_OK;
   }
   launch_pdl(tick_kernel, dim3(1), dim3(1), 0, (cudaStream_t)stream, step_count);
   NSG_CHECK_LAUNCH("tick_kernel");

@@ -410,8 +410,11 @@ class EngineTMA(object):
         g = ops.conv_geom(b, oh, ow, cout, h, w, self.dim, 4, 2, 1, 0, 16, cout * 16, ops.BF16)
         gw = g
         if self.c1 is not None:
-            self._side(ctx, lambda: (ops.c1_wgrad_tc(gw, dpre, v4, G['decoder.6.weight']),
-                                     ops.colsum(dpre, G['decoder.6.bias'])), dpre, v4)
+            if getattr(ctx, 'dbias6_done', False):      # the fused loss kernel already summed dpre into the bias gradient
+                self._side(ctx, lambda: ops.c1_wgrad_tc(gw, dpre, v4, G['decoder.6.weight']), dpre, v4)
+            else:
+                self._side(ctx, lambda: (ops.c1_wgrad_tc(gw, dpre, v4, G['decoder.6.weight']),
+                                         ops.colsum(dpre, G['decoder.6.bias'])), dpre, v4)
         else:
             self._side(ctx, lambda: (ops.conv_wgrad(gw, dpre, v4, G['decoder.6.weight']),
                                      ops.colsum(dpre, G['decoder.6.bias'])), dpre, v4)

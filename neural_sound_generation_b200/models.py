@@ -387,7 +387,9 @@ class VQVAE(nn.Module):
             # loss + d loss / d pre-tanh (bf16, what decoder_bwd reads) + the fp32 x_tilde handed back, one kernel
             xt32 = torch.empty(xt.shape, dtype=torch.float32, device=x.device)
             dpre = torch.empty((b, h, wt), dtype=torch.bfloat16, device=x.device)
-            ops.recon_loss_bf16(xt.view(b, h, wt), c3, sums[0:1], dpre, xt32.view(b, h, wt))
+            ops.recon_loss_bf16(xt.view(b, h, wt), c3, sums[0:1], dpre, xt32.view(b, h, wt),
+                                dpre_sum=G['decoder.6.bias'] if getattr(eng, 'c1', None) is not None else None)
+            ectx.dbias6_done = getattr(eng, 'c1', None) is not None
         else:
             xt32 = xt if xt.dtype == torch.float32 else xt.float()
             dpre = torch.empty((b, h, wt), dtype=torch.float32, device=x.device)

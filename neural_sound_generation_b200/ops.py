@@ -264,11 +264,14 @@ def recon_loss(x_tilde, c, loss_sum, dpre=None):
     launch_count += 1
 
 
-def recon_loss_bf16(x_tilde, c, loss_sum, dpre=None, x_tilde_f32=None):
-    """x_tilde (B, H, Wt) bf16, c (B, H, W) fp32; dpre (bf16) and x_tilde_f32 (fp32) optional outputs (B, H, Wt)."""
+def recon_loss_bf16(x_tilde, c, loss_sum, dpre=None, x_tilde_f32=None, dpre_sum=None):
+    """x_tilde (B, H, Wt) bf16, c (B, H, W) fp32; dpre (bf16) and x_tilde_f32 (fp32) optional outputs (B, H, Wt);
+    dpre_sum (fp32, one element) += sum of dpre (the output layer's bias gradient)."""
     global launch_count
     A.require_device()
-    _cuda(x_tilde, c, loss_sum, dpre, x_tilde_f32)
+    _cuda(x_tilde, c, loss_sum, dpre, x_tilde_f32, dpre_sum)
+    if dpre_sum is not None and dpre_sum.dtype != torch.float32:
+        raise TypeError('recon_loss_bf16: dpre_sum must be fp32')
     _bf16(x_tilde, dpre)
     _contig(x_tilde, 'x_tilde')
     _contig(c, 'target mel')
@@ -279,7 +282,7 @@ def recon_loss_bf16(x_tilde, c, loss_sum, dpre=None, x_tilde_f32=None):
     b, h, w = c.shape
     wt = x_tilde.shape[-1]
     rc = A.load().nsg_recon_loss_bf16(A.ptr(x_tilde), A.ptr(c), b, h, w, wt, A.ptr(loss_sum), A.ptr(dpre),
-                                      A.ptr(x_tilde_f32), A.stream_ptr())
+                                      A.ptr(x_tilde_f32), A.ptr(dpre_sum), A.stream_ptr())
     A.check(rc, 'nsg_recon_loss_bf16')
     launch_count += 1
 
@@ -300,15 +303,16 @@ def loss_finalize(sums, recon_scale, vq_scale, out=None):
 
 
 def adam_step(params, grads, exp_avg, exp_avg_sq, step_count, lr, beta1=0.9, beta2=0.999, eps=1e-8,
-              grad_scale=1.0, zero_grads=False):
+              grad_scale=1.0, zero_grads=False, ticket=None):
+    """ticket: a zeroed int32 scalar owned by the optimiser -> the step counter advances inside the same launch."""
     global launch_count
     A.require_device()
-    _cuda(params, grads, exp_avg, exp_avg_sq, step_count)
+    _cuda(params, grads, exp_avg, exp_avg_sq, step_count, ticket)
     rc = A.load().nsg_adam_step(A.ptr(params), A.ptr(grads), A.ptr(exp_avg), A.ptr(exp_avg_sq), params.numel(),
                                 lr, beta1, beta2, eps, grad_scale, A.ptr(step_count), 1 if zero_grads else 0,
-                                A.stream_ptr())
+                                A.ptr(ticket), A.stream_ptr())
     A.check(rc, 'nsg_adam_step')
-    launch_count += 2
+    launch_count += 1 if (ticket is not None and params.numel() > 0) else 2
 
 
 def tanh_bwd(g, y, out):

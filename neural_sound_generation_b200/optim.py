@@ -30,6 +30,7 @@ class Adam(torch.optim.Optimizer):
         self.exp_avg = torch.zeros_like(flat['params'])
         self.exp_avg_sq = torch.zeros_like(flat['params'])
         self.step_count = torch.zeros((), dtype=torch.int64, device=dev)
+        self.ticket = torch.zeros((), dtype=torch.int32, device=dev)    # last-block election inside the Adam kernel
         self.grad_scale = 1.0
 
     @staticmethod
@@ -63,7 +64,7 @@ class Adam(torch.optim.Optimizer):
         f = self.model.flatten_parameters()
         g = self.param_groups[0]
         ops.adam_step(f['params'], f['grads'], self.exp_avg, self.exp_avg_sq, self.step_count, g['lr'],
-                      g['betas'][0], g['betas'][1], g['eps'], self.grad_scale, zero_grads=zero_grads)
+                      g['betas'][0], g['betas'][1], g['eps'], self.grad_scale, zero_grads=zero_grads, ticket=self.ticket)
         if zero_grads:
             self.model.__dict__['_grads_dirty'] = False
 

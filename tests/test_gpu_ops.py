@@ -521,9 +521,12 @@ def test_recon_loss_bf16_fused_and_loss_finalize():
     sums = torch.zeros(2, dtype=torch.float64, device=DEV)
     dpre = torch.empty(B, H, Wt, dtype=torch.bfloat16, device=DEV)
     x32 = torch.full((B, H, Wt), 7.0, device=DEV)
-    ops.recon_loss_bf16(xt16.to(DEV), c.to(DEV), sums[0:1], dpre, x32)
+    dsum = torch.full((1,), 0.125, device=DEV)
+    ops.recon_loss_bf16(xt16.to(DEV), c.to(DEV), sums[0:1], dpre, x32, dpre_sum=dsum)
     torch.cuda.synchronize()
     assert abs(sums[0].item() / c.numel() - loss.item()) < 1e-6 * max(1.0, loss.item())
+    # the output layer's bias gradient: += the sum of the ROUNDED dpre values (what ops.colsum(dpre) would return)
+    assert abs(dsum.item() - 0.125 - dpre.double().sum().item()) < 1e-5 * dpre.double().abs().sum().item()
     assert torch.equal(x32.cpu(), xt16.float())
     assert torch.equal(dpre.cpu(), dref.float().to(torch.bfloat16)) or relerr(dpre, dref) < 4e-3
     # same numbers as the fp32 kernel fed the widened tensor
@@ -562,6 +565,17 @@ def test_adam_vector_path_and_gradient_clearing():
             assert (float(g.abs().max()) == 0.0) == (it == 2)
         assert int(step) == 3
         res[tag] = (p.clone(), m.clone(), v.clone())
+        # one-launch form: the last block advances the step counter (ticket left at zero) -- same numbers
+        p2, g2, m2, v2 = [torch.zeros(n + 4, device=DEV)[off:off + n] for _ in range(4)]
+        p2.copy_(p0)
+        step2, ticket = torch.zeros((), dtype=torch.int64, device=DEV), torch.zeros((), dtype=torch.int32, device=DEV)
+        rg = np.random.RandomState(6)
+        for it in range(3):
+            g2.copy_(torch.tensor(rg.standard_normal(n).astype(np.float32)))
+            l0 = ops.launch_count
+            ops.adam_step(p2, g2, m2, v2, step2, 1e-3, grad_scale=0.5, zero_grads=(it == 2), ticket=ticket)
+            assert ops.launch_count - l0 == 1 and int(step2) == it + 1 and int(ticket) == 0
+        assert torch.equal(p2, res[tag][0]) and torch.equal(m2, res[tag][1]) and torch.equal(v2, res[tag][2])
     for a, b in zip(res['vec'], res['scalar']):
         assert torch.equal(a, b)
     # against torch.optim.Adam
