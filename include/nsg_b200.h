@@ -193,6 +193,10 @@ int nsg_conv_wgrad_tc(const nsg_conv_geom* g, const void* p, const nsg_prologue*
  *   nsg_c1_wgrad_tc  dw[t + b*w_cout_stride] += sum_m p1[gather0(m, t)] * q[m, b]; q_colsum[b] += sum_m q[m, b] */
 int nsg_c1_conv_tc(const nsg_conv_geom* g, const void* in, const void* packed_w, const nsg_epilogue* epi, void* out,
                    void* stream);
+/* nsg_c1_conv_tc with an eval-mode BatchNorm (bn->mode == NSG_BNF_EVAL) folded into its output affine (models.py:165-167
+ * in eval mode: one launch instead of two) */
+int nsg_c1_conv_bn_tc(const nsg_conv_geom* g, const void* in, const void* packed_w, const nsg_epilogue* epi,
+                      const nsg_bn_fuse* bn, void* out, void* stream);
 int nsg_c1_convT_tc(const nsg_conv_geom* g, const void* in, const void* packed_w, const float* bias, int tanh_out,
                     void* out, void* stream);
 int nsg_c1_wgrad_tc(const nsg_conv_geom* g, const void* p, const void* q, float* dw, float* q_colsum, void* stream);

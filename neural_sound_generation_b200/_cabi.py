@@ -26,7 +26,7 @@ EXPORTS = [
     'nsg_conv_wgrad_slices', 'nsg_conv_wgrad_tma_sliced', 'nsg_pdl', 'nsg_recon_loss_bf16', 'nsg_loss_finalize',
     'nsg_bn_act64', 'nsg_bn_bwd64', 'nsg_relu64', 'nsg_vq_bwd_stats64', 'nsg_debug_timeline',
     'nsg_c1_conv_tc', 'nsg_c1_convT_tc', 'nsg_c1_wgrad_tc', 'nsg_scatter_mode', 'nsg_ema_update', 'nsg_vq_resident',
-    'nsg_conv_bn_tma', 'nsg_conv_bn_tma_fits',
+    'nsg_conv_bn_tma', 'nsg_conv_bn_tma_fits', 'nsg_c1_conv_bn_tc',
 ]
 
 
@@ -86,6 +86,7 @@ def load():
                                       i, vp]
     lib.nsg_debug_timeline.argtypes = [i, vp]
     lib.nsg_c1_conv_tc.argtypes = [C.POINTER(ConvGeom), vp, vp, C.POINTER(Epilogue), vp, vp]
+    lib.nsg_c1_conv_bn_tc.argtypes = [C.POINTER(ConvGeom), vp, vp, C.POINTER(Epilogue), C.POINTER(BnFuse), vp, vp]
     lib.nsg_c1_convT_tc.argtypes = [C.POINTER(ConvGeom), vp, vp, vp, i, vp, vp]
     lib.nsg_c1_wgrad_tc.argtypes = [C.POINTER(ConvGeom), vp, vp, vp, vp, vp]
     lib.nsg_conv_pack_many.argtypes = [i, vp, vp, vp, vp, vp, vp]

@@ -50,8 +50,8 @@ int conv_gemm_tma(const nsg_conv_geom* cg, const void* in, const void* packed, c
                   const nsg_bn_fuse* bnf, void* out,
                   cudaStream_t stream);
 int debug_timeline(int enable, unsigned long long* host_out);
-int conv_c1_tc(const nsg_conv_geom* cg, const void* in, const void* packed, const nsg_epilogue* epi, void* out,
-               cudaStream_t stream);
+int conv_c1_tc(const nsg_conv_geom* cg, const void* in, const void* packed, const nsg_epilogue* epi,
+               const nsg_bn_fuse* bnf, void* out, cudaStream_t stream);
 int convT_c1_tc(const nsg_conv_geom* cg, const void* in, const void* packed, const float* bias, int tanh_out, void* out,
                 cudaStream_t stream);
 int wgrad_c1_tc(const nsg_conv_geom* cg, const void* p, const void* q, float* dw, float* q_colsum, cudaStream_t stream);
@@ -217,7 +217,15 @@ int nsg_c1_conv_tc(const nsg_conv_geom* g, const void* in, const void* packed_w,
   int rc = check_geom(g);
   if (rc) return rc;
   NSG_REQUIRE(in && packed_w && out, "c1_conv_tc: null pointer");
-  return conv_c1_tc(g, in, packed_w, epi, out, (cudaStream_t)stream);
+  return conv_c1_tc(g, in, packed_w, epi, nullptr, out, (cudaStream_t)stream);
+}
+
+int nsg_c1_conv_bn_tc(const nsg_conv_geom* g, const void* in, const void* packed_w, const nsg_epilogue* epi,
+                      const nsg_bn_fuse* bn, void* out, void* stream) {
+  int rc = check_geom(g);
+  if (rc) return rc;
+  NSG_REQUIRE(in && packed_w && out, "c1_conv_bn_tc: null pointer");
+  return conv_c1_tc(g, in, packed_w, epi, bn, out, (cudaStream_t)stream);
 }
 
 int nsg_c1_convT_tc(const nsg_conv_geom* g, const void* in, const void* packed_w, const float* bias, int tanh_out,

@@ -1563,12 +1563,12 @@ struct C1tConvParams {
 
 __global__ void __launch_bounds__(320, 1)
 c1t_conv_kernel(const __nv_bfloat16* __restrict__ in1, const uint8_t* __restrict__ wimg,
-                __nv_bfloat16* __restrict__ out, EpiArgs epi, const __grid_constant__ C1tConvParams P) {
+                __nv_bfloat16* __restrict__ out, EpiArgs epi, BnFuse bn, const __grid_constant__ C1tConvParams P) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sm = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sW = sm;                                  // one 64 x 64 image (K >= 16 zero)
-  uint8_t* sA = sm + TM_W_BYTES;                     // two patch tiles per epilogue group (buffer = grp * 2 + parity)
-  __shared__ __align__(16) float sPar[5 * TM_C];
+  uint8_t* sA = sm + TM_W_BYTES;                     // four patch tiles (tile i uses buffer i & 3)
+  __shared__ __align__(16) float sPar[6 * TM_C];
   __shared__ float sStat[2 * TM_C];
   __shared__ __align__(8) uint64_t bars[9];          // wfull, full[4], acc_full[4]
   __shared__ uint32_t tmem_slot;
@@ -1584,7 +1584,7 @@ c1t_conv_kernel(const __nv_bfloat16* __restrict__ in1, const uint8_t* __restrict
   if (tid == 0) {
     mbar_init(wfull, 1);
     for (int b = 0; b < 4; ++b) {
-      mbar_init(&full[b], 128);
+      mbar_init(&full[b], 256);
       mbar_init(&acc_full[b], 1);
     }
     fence_mbar_init();
@@ -1610,33 +1610,45 @@ c1t_conv_kernel(const __nv_bfloat16* __restrict__ in1, const uint8_t* __restrict
       const uint64_t b_desc = sw128_desc(smem_u32(sW));
       mbar_wait(wfull, 0);
       for (int i = 0; i < ntiles_mine; ++i) {
-        const int j = i >> 1, b = (i & 1) * 2 + (j & 1);
-        mbar_wait(&full[b], (uint32_t)((j >> 1) & 1));
+        const int b = i & 3;
+        mbar_wait(&full[b], (uint32_t)((i >> 2) & 1));
         tc_fence_after();
         umma_bf16(tmem_base + (uint32_t)b * TM_C, sw128_desc(smem_u32(sA + (size_t)b * TM_A_BYTES)), b_desc, idesc, 0);
         umma_commit(&acc_full[b]);
       }
     }
   } else {
-    const int grp = (warp - 2) >> 2, q = warp & 3;
+    // all 8 warps work on every tile: thread = (output pixel, 32-channel half).  The per-channel statistics are carried
+    // in registers across the CTA's ~9 tiles and reduced once at the end (they used to cost two 32 x 32 shuffle
+    // transposes per tile and half -- this kernel is bound by its epilogue's instruction count).
+    const int half = (warp - 2) >> 2, q = warp & 3;
     const int r = q * 32 + lane;
+    const int ch0 = half * 32;
     const int bw = r & (P.box_w - 1), bh = r >> P.log2_bw;
+    const int e = tid - 64;
     const unsigned short* in16 = reinterpret_cast<const unsigned short*>(in1);
     pdl_wait();
     pdl_trigger();
-    if (tid - 64 < TM_C) {
-      const int c = tid - 64;
-      sPar[0 * TM_C + c] = epi.bias ? __ldg(epi.bias + c) : 0.f;
+    if (e < TM_C) {
+      const int c = e;
+      const float bias = epi.bias ? __ldg(epi.bias + c) : 0.f;
+      float osc = 1.f, osh = bias;
+      if (bn.mode == NSG_BNF_EVAL) {                 // BatchNorm in eval mode folds into the output affine
+        const float is = 1.0f / sqrtf(__ldg(bn.running_var + c) + bn.eps);
+        osc = __ldg(bn.gamma + c) * is;
+        osh = fmaf(bias - __ldg(bn.running_mean + c), osc, __ldg(bn.beta + c));
+      }
+      sPar[0 * TM_C + c] = osh;
       sPar[1 * TM_C + c] = epi.mask_mode == NSG_MASK_AFFINE ? __ldg(epi.mscale + c) : 1.f;
       sPar[2 * TM_C + c] = epi.mask_mode == NSG_MASK_AFFINE ? __ldg(epi.mshift + c) : 0.f;
       sPar[3 * TM_C + c] = epi.stats_mode == NSG_STATS_BNBWD ? __ldg(epi.mean + c) : 0.f;
       sPar[4 * TM_C + c] = epi.stats_mode == NSG_STATS_BNBWD ? __ldg(epi.invstd + c) : 0.f;
+      sPar[5 * TM_C + c] = osc;
     }
     named_bar(2, 256);
-    // The group's chain per tile is: 16 scattered 2-byte loads -> patch row into shared memory -> one MMA round trip
-    // -> epilogue.  With one buffer per group every link is exposed (9000-13700 cycles per tile measured against a
-    // 4000-cycle epilogue), so the chain is software-pipelined: the patch of tile j+2 is loaded into registers and the
-    // patch of tile j+1 is handed to the tensor core (second buffer / accumulator) BEFORE the epilogue of tile j.
+    // Per tile the chain is: 8 scattered 2-byte loads -> half a patch row into shared memory -> one MMA round trip ->
+    // epilogue.  It is software-pipelined over the four buffers: the patch of tile i+2 is loaded into registers and
+    // the patch of tile i+1 is handed to the tensor core BEFORE the epilogue of tile i.
     struct TileRow {
       int n, oh, ow;
       bool valid;
@@ -1652,11 +1664,12 @@ c1t_conv_kernel(const __nv_bfloat16* __restrict__ in1, const uint8_t* __restrict
       R.valid = R.oh < P.out_h && R.ow < P.out_w;
       return R;
     };
-    uint32_t pk[8];
-    auto load_patch = [&](int i) {        // this row's 4 x 4 input patch (k = 4, stride 2, pad 1), taps kh*4 + kw along K
+    uint32_t pk[4];
+    auto load_patch = [&](int i) {        // this thread's half (kernel rows 2*half, 2*half + 1) of the 4 x 4 input patch
       const TileRow R = row_of(i);
 #pragma unroll
-      for (int kh = 0; kh < 4; ++kh) {
+      for (int kk = 0; kk < 2; ++kk) {
+        const int kh = half * 2 + kk;
         const int ih = 2 * R.oh - 1 + kh;
         const bool rok = R.valid && ih >= 0 && ih < P.in_h;
         const unsigned short* rowp = in16 + ((long long)R.n * P.in_h + ih) * P.in_w;
@@ -1666,47 +1679,81 @@ c1t_conv_kernel(const __nv_bfloat16* __restrict__ in1, const uint8_t* __restrict
           const int iw = 2 * R.ow - 1 + kw;
           v[kw] = (rok && iw >= 0 && iw < P.in_w) ? __ldg(rowp + iw) : (unsigned short)0;
         }
-        pk[kh * 2 + 0] = (uint32_t)v[0] | ((uint32_t)v[1] << 16);
-        pk[kh * 2 + 1] = (uint32_t)v[2] | ((uint32_t)v[3] << 16);
+        pk[kk * 2 + 0] = (uint32_t)v[0] | ((uint32_t)v[1] << 16);
+        pk[kk * 2 + 1] = (uint32_t)v[2] | ((uint32_t)v[3] << 16);
       }
     };
-    auto submit = [&](int buf) {          // patch registers -> operand tile `buf` of this group -> tensor core
-      uint8_t* myA = sA + (size_t)(grp * 2 + buf) * TM_A_BYTES;
-      *reinterpret_cast<uint4*>(myA + sw128_offset(r, 0)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-      *reinterpret_cast<uint4*>(myA + sw128_offset(r, 1)) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+    auto submit = [&](int buf) {          // patch registers -> operand tile `buf` -> tensor core (taps kh*4 + kw along K)
+      uint8_t* myA = sA + (size_t)buf * TM_A_BYTES;
+      *reinterpret_cast<uint4*>(myA + sw128_offset(r, half)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
       fence_proxy_async_smem();
       tc_fence_before();                  // orders this thread's earlier tcgen05.ld of that accumulator before the arrive
-      mbar_arrive(&full[grp * 2 + buf]);
+      mbar_arrive(&full[buf]);
     };
-    if (grp < ntiles_mine) {
-      load_patch(grp);
+    if (ntiles_mine > 0) {
+      load_patch(0);
       submit(0);
-      if (grp + 2 < ntiles_mine) load_patch(grp + 2);
+      if (1 < ntiles_mine) load_patch(1);
     }
-    int j = 0;
-    for (int i = grp; i < ntiles_mine; i += 2, ++j) {
-      const int jb = j & 1;
-      if (i + 2 < ntiles_mine) {
-        submit(jb ^ 1);
-        if (i + 4 < ntiles_mine) load_patch(i + 4);
+    const bool do_stats = epi.stats_mode != NSG_STATS_NONE;
+    const bool bwd_stats = epi.stats_mode == NSG_STATS_BNBWD;
+    float s1[32], s2[32];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) s1[j] = s2[j] = 0.f;
+    for (int i = 0; i < ntiles_mine; ++i) {
+      if (i + 1 < ntiles_mine) {
+        submit((i + 1) & 3);
+        if (i + 2 < ntiles_mine) load_patch(i + 2);
       }
       const TileRow R = row_of(i);
       const bool valid = R.valid;
-      const long long o = valid ? (((long long)R.n * P.out_h + R.oh) * P.out_w + R.ow) * TM_C : 0;
-      EpiOperands E;
-      epi_begin(E, epi, o, valid);
-      mbar_wait(&acc_full[grp * 2 + jb], (uint32_t)((j >> 1) & 1));
+      const long long oh = valid ? (((long long)R.n * P.out_h + R.oh) * P.out_w + R.ow) * TM_C + ch0 : 0;
+      const bool use_add = valid && epi.add_src != nullptr;
+      uint4 radd[4];
+      if (use_add) ld_half(epi.add_src, oh, radd);
+      mbar_wait(&acc_full[i & 3], (uint32_t)((i >> 2) & 1));
       tc_fence_after();
-      uint32_t acc0[32], acc1[32];
-      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(grp * 2 + jb) * TM_C;
-      tmem_ld32(taddr, acc0);
-      tmem_ld32(taddr + 32, acc1);
+      uint32_t acc[32];
+      tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(i & 3) * TM_C + (uint32_t)ch0, acc);
       tmem_ld_wait();
-      epi_row(E, epi, sPar, sStat, out, o, valid, acc0, acc1, lane);
+      float x[32];
+      epi_half(x, acc, epi, sPar, oh, valid, ch0, use_add, radd);
+      if (valid) {
+        st16bf(out + oh, &x[0]);
+        st16bf(out + oh + 16, &x[16]);
+      }
+      if (do_stats) {
+        if (bwd_stats) {
+          if (valid) {
+            uint4 rx[4];
+            ld_half(epi.xhat_src, oh, rx);
+#pragma unroll
+            for (int g8 = 0; g8 < 4; ++g8) {
+              float hx[8];
+              unpack8bf(rx[g8], hx);
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                const int ch = ch0 + g8 * 8 + j;
+                s1[g8 * 8 + j] += x[g8 * 8 + j];
+                s2[g8 * 8 + j] = fmaf(x[g8 * 8 + j], (hx[j] - sPar[3 * TM_C + ch]) * sPar[4 * TM_C + ch], s2[g8 * 8 + j]);
+              }
+            }
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            s1[j] += x[j];
+            s2[j] = fmaf(x[j], x[j], s2[j]);
+          }
+        }
+      }
     }
-    if (epi.stats_mode != NSG_STATS_NONE) {
+    if (do_stats) {
+      const float t1 = transpose_sum32(s1, lane);
+      const float t2 = transpose_sum32(s2, lane);
+      atomicAdd(&sStat[ch0 + lane], t1);
+      atomicAdd(&sStat[TM_C + ch0 + lane], t2);
       named_bar(1, 256);
-      const int e = tid - 64;
       if (e < 2 * TM_C) atomicAdd(epi.stats + e, (double)sStat[e]);
     }
   }
@@ -1720,8 +1767,8 @@ static bool c1t_geom_ok(const nsg_conv_geom* cg) {
 }
 
 // Conv2d(1 -> 64) forward / ConvTranspose2d(64 -> 1) data gradient; packed = 8 KB image from conv_pack_many(ntaps = -1)
-int conv_c1_tc(const nsg_conv_geom* cg, const void* in, const void* packed, const nsg_epilogue* epi, void* out,
-               cudaStream_t stream) {
+int conv_c1_tc(const nsg_conv_geom* cg, const void* in, const void* packed, const nsg_epilogue* epi,
+               const nsg_bn_fuse* bnf, void* out, cudaStream_t stream) {
   if (!(c1t_geom_ok(cg) && cg->gather == 0 && cg->cin == 1 && cg->cout == TM_C &&
         cg->out_h == (cg->in_h + 2 - 4) / 2 + 1 && cg->out_w == (cg->in_w + 2 - 4) / 2 + 1)) {
     set_error("conv_c1_tc serves bf16 Conv2d(1 -> 64, k4, s2, p1)-shaped gathers only");
@@ -1732,6 +1779,9 @@ int conv_c1_tc(const nsg_conv_geom* cg, const void* in, const void* packed, cons
   EpiArgs e{};
   if (int rc = make_epi(epi, &e)) return rc;
   NSG_REQUIRE(e.tanh_out == 0 || e.tanh_out == 2, "conv_c1_tc: output activation must be none or ReLU");
+  BnFuse f{};
+  if (int rc = make_bnfuse(bnf, e, &f)) return rc;
+  NSG_REQUIRE(f.mode == NSG_BNF_NONE || f.mode == NSG_BNF_EVAL, "conv_c1_tc: only the eval-mode BatchNorm fold is fused here");
   C1tConvParams P{};
   P.batch = cg->batch; P.in_h = cg->in_h; P.in_w = cg->in_w; P.out_h = cg->out_h; P.out_w = cg->out_w;
   pick_box_w(cg->out_w, TM_M, &P.box_w, &P.box_h, &P.log2_bw);
@@ -1748,7 +1798,7 @@ int conv_c1_tc(const nsg_conv_geom* cg, const void* in, const void* packed, cons
   }
   const int grid = P.total_tiles < num_sms() ? P.total_tiles : num_sms();
   launch_pdl(c1t_conv_kernel, dim3(grid), dim3(320), smem, stream, static_cast<const __nv_bfloat16*>(in), static_cast<const uint8_t*>(packed),
-                                               static_cast<__nv_bfloat16*>(out), e, P);
+                                               static_cast<__nv_bfloat16*>(out), e, f, P);
   NSG_CHECK_LAUNCH("c1t_conv_kernel");
   return NSG_OK;
 }

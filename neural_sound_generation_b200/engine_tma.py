@@ -362,13 +362,20 @@ class EngineTMA(object):
         oh, ow = _out_hw(h, w, 4, 2, 1, False)
         a0 = torch.empty((b, oh, ow, self.dim), dtype=BF, device=x.device)
         g = ops.conv_geom(b, h, w, cin, oh, ow, self.dim, 4, 2, 1, 0, 16, cin * 16, ops.BF16)
-        if self.c1 is not None:
-            ops.c1_conv_tc(g, x, self.c1['enc0'], a0, bias=P['encoder.0.bias'],
-                           stats_mode=STATS_MOMENTS if tr else 0, stats=bn1['fstats'] if tr else None)
+        if self.c1 is not None and not tr and self.fuse_bn:
+            # eval: encoder.1's running statistics fold into the convolution's output affine, one launch
+            v0 = ops.c1_conv_bn_eval_tc(g, x, self.c1['enc0'], a0, P['encoder.1.weight'], P['encoder.1.bias'],
+                                        Bufs['encoder.1.running_mean'], Bufs['encoder.1.running_var'], eps=BN_EPS,
+                                        bias=P['encoder.0.bias'], relu_out=True)
+            a0 = None
         else:
-            ops.conv_gemm(g, x, w0, a0, bias=P['encoder.0.bias'], stats_mode=STATS_MOMENTS if tr else 0,
-                          stats=bn1['fstats'] if tr else None)
-        v0 = self._bn_act(ctx, P, Bufs, 'encoder.1', a0, relu_out=True)
+            if self.c1 is not None:
+                ops.c1_conv_tc(g, x, self.c1['enc0'], a0, bias=P['encoder.0.bias'],
+                               stats_mode=STATS_MOMENTS if tr else 0, stats=bn1['fstats'] if tr else None)
+            else:
+                ops.conv_gemm(g, x, w0, a0, bias=P['encoder.0.bias'], stats_mode=STATS_MOMENTS if tr else 0,
+                              stats=bn1['fstats'] if tr else None)
+            v0 = self._bn_act(ctx, P, Bufs, 'encoder.1', a0, relu_out=True)
         r4 = self._conv_fwd(ctx, P, 'encoder.3', v0, relu_out=True)            # relu(a1): ResBlock's in-place ReLU
         r5 = self.resblock_fwd(ctx, P, Bufs, 'encoder.4', r4, relu_out=True)
         z_e = self.resblock_fwd(ctx, P, Bufs, 'encoder.5', r5, relu_out=False)

@@ -555,6 +555,23 @@ def c1_conv_tc(geom, x1, packed, out, bias=None, add_src=None, mask_mode=MASK_NO
     return out
 
 
+def c1_conv_bn_eval_tc(geom, x1, packed, out, gamma, beta, running_mean, running_var, eps=1e-5, bias=None, relu_out=True):
+    """nsg_c1_conv_bn_tc: Conv2d(1 -> 64, 4, 2, 1) + eval-mode BatchNorm [+ ReLU] in one launch (models.py:165-167)."""
+    global launch_count
+    A.require_device()
+    _cuda(x1, packed, out, bias, gamma, beta, running_mean, running_var)
+    _bf16(x1, out)
+    epi = A.Epilogue(A.ptr(bias), None, MASK_NONE, None, None, None, STATS_NONE, None, None, None, None,
+                     2 if relu_out else 0)
+    bn = A.BnFuse(BNF_EVAL, 0, A.ptr(gamma), A.ptr(beta), eps, 0.0, 1.0, A.ptr(running_mean), A.ptr(running_var), None,
+                  None, None, None, None, None, None)
+    rc = A.load().nsg_c1_conv_bn_tc(C.byref(geom), A.ptr(x1), A.ptr(packed), C.byref(epi), C.byref(bn), A.ptr(out),
+                                    A.stream_ptr())
+    A.check(rc, 'nsg_c1_conv_bn_tc')
+    launch_count += 1
+    return out
+
+
 def c1_convT_tc(geom, x, packed, out1, bias=None, tanh_out=False):
     global launch_count
     A.require_device()
