@@ -334,6 +334,15 @@ int nsg_loss_finalize(const double* sums, double recon_scale, double vq_scale, d
 /* out = g * (1 - y^2): gradient through the decoder's final nn.Tanh (models.py:183), fp32 */
 int nsg_tanh_bwd(const float* g, const float* y, float* out, long long n, void* stream);
 
+/* ---------------------------------------------------------------- input pipeline (dataloader.py:410-415) */
+/* Device half of collate_fn for the mel conditioning features: `frames` holds the kept frames of the batch's utterances
+ * back to back, time-major ((sum of lengths) x n_mels fp32, cropped on the host as dataloader.py:356-362 prescribes);
+ * offsets[b] .. offsets[b+1] (batch + 1 ints, in frames) delimit item b.  Writes the zero-padded, transposed batch
+ * (batch, n_mels, t_out) as fp32 (out_f32, nullable) and as bf16 (out_bf16, nullable; = the (B, n_mels, T, 1) NHWC
+ * tensor the bf16 encoder reads).  Frames beyond t_out are dropped, items shorter than t_out are zero-padded. */
+int nsg_mel_collate(const float* frames, const int* offsets, int batch, int n_mels, int t_out, float* out_f32,
+                    void* out_bf16, void* stream);
+
 /* ---------------------------------------------------------------- optimiser (torch.optim.Adam, main.py:124) */
 /* one Adam step over a flat fp32 buffer.  step_count is a device scalar incremented AFTER use (graphs replay
  * correctly): by the last block of the same launch when `ticket` (one zero-initialised unsigned counter owned by this

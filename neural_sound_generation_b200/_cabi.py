@@ -26,7 +26,7 @@ EXPORTS = [
     'nsg_conv_wgrad_slices', 'nsg_conv_wgrad_tma_sliced', 'nsg_pdl', 'nsg_recon_loss_bf16', 'nsg_loss_finalize',
     'nsg_bn_act64', 'nsg_bn_bwd64', 'nsg_relu64', 'nsg_vq_bwd_stats64', 'nsg_debug_timeline',
     'nsg_c1_conv_tc', 'nsg_c1_convT_tc', 'nsg_c1_wgrad_tc', 'nsg_scatter_mode', 'nsg_ema_update', 'nsg_vq_resident',
-    'nsg_conv_bn_tma', 'nsg_conv_bn_tma_fits', 'nsg_c1_conv_bn_tc',
+    'nsg_conv_bn_tma', 'nsg_conv_bn_tma_fits', 'nsg_c1_conv_bn_tc', 'nsg_mel_collate',
 ]
 
 
@@ -121,6 +121,7 @@ def load():
     lib.nsg_vq_resident.argtypes = [i]
     lib.nsg_ema_update.argtypes = [vp, vp, vp, vp, vp, i, i, f, f, vp, vp]
     lib.nsg_tanh_bwd.argtypes = [vp, vp, vp, ll, vp]
+    lib.nsg_mel_collate.argtypes = [vp, vp, i, i, i, vp, vp, vp]
     lib.nsg_adam_step.argtypes = [vp, vp, vp, vp, ll, f, f, f, f, f, vp, i, vp, vp]
     for name in EXPORTS:
         fn = getattr(lib, name)

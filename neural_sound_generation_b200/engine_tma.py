@@ -262,6 +262,8 @@ class EngineTMA(object):
                               invstd=bn['invstd'], **epi)
         conv_before = {'.block.2': '.block.1', '.block.5': '.block.4'}
         pre = bn_name[:-8] + conv_before[bn_name[-8:]] + '.bias' if bn_name[-8:] in conv_before else None
+        if bn_name == 'encoder.1':
+            pre = 'encoder.0.bias'
         return gy, self._bn_bwd(ctx, P, G, bn_name, gy, h, G[pre] if pre else None)
 
     def _conv_dgrad(self, name, dy, in_hw, **epi):
@@ -465,10 +467,10 @@ class EngineTMA(object):
         g_r5, g_r5h = self.resblock_bwd(ctx, P, G, 'encoder.5', g_ze, None, prev_block='encoder.4')
         g_a1 = self.resblock_bwd(ctx, P, G, 'encoder.4', g_r5, g_r5h)[0]
         self._conv_wgrad(ctx, 'encoder.3', v0, g_a1, q_colsum=G['encoder.3.bias'])
-        g_v0 = self._conv_dgrad('encoder.3', g_a1, v0.shape[1:3], mask_mode=MASK_POS, mask_src=v0,
-                                stats_mode=STATS_BNBWD, stats=bn1['bstats'], xhat_src=a0, mean=bn1['mean'],
-                                invstd=bn1['invstd'])
-        g_a0 = self._bn_bwd(ctx, P, G, 'encoder.1', g_v0, a0, G['encoder.0.bias'])
+        # encoder.3's data gradient flows through encoder.2's ReLU into encoder.1's BatchNorm backward: one launch
+        # (the 40 x 128 grid is 9 tiles per CTA at batch 32: the surplus tile is re-read from the stored g)
+        _, g_a0 = self._conv_dgrad_bn(ctx, P, G, 'encoder.3', g_a1, v0.shape[1:3], 'encoder.1', a0, True,
+                                      mask_mode=MASK_POS, mask_src=v0)
         b, h, w, cin = x.shape
         _, oh, ow, _ = a0.shape
         g = ops.conv_geom(b, h, w, cin, oh, ow, self.dim, 4, 2, 1, 0, 16, cin * 16, ops.BF16)

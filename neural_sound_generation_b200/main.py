@@ -107,13 +107,14 @@ def get_loaders(args):
                                 args.seed + 1, args.cuda)
         return tr, te
     if args.dataset == 'ljspeech':
-        try:
-            from dataloader import get_audio_data_loaders        # the reference's src/dataloader.py, unchanged
-        except ImportError as e:
-            raise SystemExit('--dataset ljspeech needs the reference\'s dataloader module on sys.path (%s); '
-                             'or pass --synthetic-batches N' % e)
-        loaders = get_audio_data_loaders(os.path.join(args.datadir), None, args.batch_size, test_shuffle=True)
-        return loaders['train'], loaders['test']
+        # the reference's get_audio_data_loaders (dataloader.py:437-489): train.txt under --datadir, 95 / 5 split,
+        # length-bucketed batches cropped to hparams.max_time_steps -- assembled on the device (data.py)
+        from . import data as D
+        tr_set, te_set = D.MelNpyDataset(args.datadir, train=True), D.MelNpyDataset(args.datadir, train=False)
+        frames = D.max_time_frames()
+        tr = D.DeviceMelLoader(tr_set, args.batch_size, max_frames=frames, seed=args.seed, bucket=True)
+        te = D.DeviceMelLoader(te_set, args.batch_size, max_frames=frames, seed=args.seed + 1, bucket=False, shuffle=True)
+        return tr, te
     raise SystemExit('only the LJSpeech mel path is built (--dataset ljspeech, or --synthetic-batches N); the '
                      'torchvision branch of main.py is a later row of SURVEY.md section 8f')
 

@@ -592,3 +592,19 @@ def c1_wgrad_tc(geom, p1, q, dw, q_colsum=None):
     rc = A.load().nsg_c1_wgrad_tc(C.byref(geom), A.ptr(p1), A.ptr(q), A.ptr(dw), A.ptr(q_colsum), A.stream_ptr())
     A.check(rc, 'nsg_c1_wgrad_tc')
     launch_count += 1
+
+
+def mel_collate(frames, offsets, n_mels, t_out, out_f32=None, out_bf16=None):
+    """nsg_mel_collate: frames fp32 (sum_len, n_mels) device tensor, offsets int32 (B + 1) device tensor (in frames)."""
+    global launch_count
+    A.require_device()
+    _cuda(frames, offsets, out_f32, out_bf16)
+    if frames.dtype != torch.float32 or offsets.dtype != torch.int32:
+        raise TypeError('mel_collate: frames must be fp32 and offsets int32')
+    if out_bf16 is not None:
+        _bf16(out_bf16)
+    _contig(frames, 'frames')
+    rc = A.load().nsg_mel_collate(A.ptr(frames), A.ptr(offsets), offsets.numel() - 1, n_mels, t_out, A.ptr(out_f32),
+                                  A.ptr(out_bf16), A.stream_ptr())
+    A.check(rc, 'nsg_mel_collate')
+    launch_count += 1
