@@ -5,12 +5,20 @@ Same command-line flags and defaults (main.py:25-58), same checkpoint dict and f
 optimizer state in ``torch.optim.Adam``'s own layout), same per-epoch reconstruction dump
 (main.py:155-162: ``<sampledir>/<dataset>/reconstruction_<model>_data_<dataset>_dim_<dim>_z_dim_<z_dim>_epoch_<e>.npy``).
 
+Data (main.py:77-99):
+  * ``--dataset ljspeech``: ``train.txt`` + mel ``.npy`` files under ``--datadir``, read, length-bucketed, cropped and
+    padded as the reference's dataloader.py does, with the batch assembled on the device (``data.py``, row N2);
+  * any other name is a ``torchvision.datasets`` class as in the reference (``MNIST`` / ``FashionMNIST``: one channel;
+    ``CIFAR10``: ``input_dim = 3``, main.py:100-116), read from ``--datadir/<dataset>/`` -- the files must already be
+    there (the reference passes ``download=True``; this build never touches the network);
+  * ``--synthetic-batches N`` substitutes N uniform-[0,1] batches per epoch of the dataset's shape (mel 80 x
+    ``--synthetic-frames``, 1 x 28 x 28, 3 x 32 x 32).
+
 What is NOT here, and why (SURVEY.md section 8f ranks them after this row):
   * the VAE / PixelCNN models (``--model vae``: refused -- not on the hot path);
-  * the reference's data loaders (N2).  ``--dataset ljspeech`` imports ``get_audio_data_loaders`` from a ``dataloader``
-    module on ``sys.path`` (the reference's own ``src/dataloader.py`` works unchanged: it is host code that yields the
-    5-tuples ``train_vqvae`` consumes); ``--synthetic-batches N`` substitutes N uniform-[0,1] mel batches per epoch;
-  * Griffin-Lim audio of the sample (main.py:164-197, N3): skipped with a message.
+  * Griffin-Lim audio of the sample (main.py:164-197, N3): skipped with a message.  For image datasets the whole
+    per-epoch sample block is skipped: the reference's own block unpacks 5-tuples (main.py:138-139) and cannot run on
+    ``(data, label)`` loaders.
 
     python -m neural_sound_generation_b200.main --model vqvae --dataset ljspeech --dim 64 --z-dim 512 \
         --synthetic-batches 100 --epochs 1
@@ -100,7 +108,32 @@ class SyntheticMelLoader(object):
                    torch.full((b,), c.shape[2], dtype=torch.long))
 
 
+IMAGE_SHAPES = {'MNIST': (1, 28, 28), 'FashionMNIST': (1, 28, 28), 'KMNIST': (1, 28, 28), 'CIFAR10': (3, 32, 32),
+                'CIFAR100': (3, 32, 32)}
+
+
+class SyntheticImageLoader(object):
+    """Stands in for the torchvision loaders of main.py:84-99: yields ``(data, label)`` with data (B, C, H, W) in [0, 1]."""
+
+    def __init__(self, batches, batch_size, shape, seed):
+        g = torch.Generator().manual_seed(seed)
+        self.batches = [torch.rand((batch_size,) + tuple(shape), generator=g) for _ in range(batches)]
+        self.dataset = range(batches * batch_size)
+        self.batch_size = batch_size
+
+    def __len__(self):
+        return len(self.batches)
+
+    def __iter__(self):
+        for d in self.batches:
+            yield d, torch.zeros(d.shape[0], dtype=torch.long)
+
+
 def get_loaders(args):
+    if args.synthetic_batches > 0 and args.dataset != 'ljspeech':
+        shape = IMAGE_SHAPES.get(args.dataset, (1, 28, 28))
+        return (SyntheticImageLoader(args.synthetic_batches, args.batch_size, shape, args.seed),
+                SyntheticImageLoader(max(1, args.synthetic_batches // 8), args.batch_size, shape, args.seed + 1))
     if args.synthetic_batches > 0:
         tr = SyntheticMelLoader(args.synthetic_batches, args.batch_size, args.synthetic_frames, args.seed, args.cuda)
         te = SyntheticMelLoader(max(1, args.synthetic_batches // 8), args.batch_size, args.synthetic_frames,
@@ -115,8 +148,23 @@ def get_loaders(args):
         tr = D.DeviceMelLoader(tr_set, args.batch_size, max_frames=frames, seed=args.seed, bucket=True)
         te = D.DeviceMelLoader(te_set, args.batch_size, max_frames=frames, seed=args.seed + 1, bucket=False, shuffle=True)
         return tr, te
-    raise SystemExit('only the LJSpeech mel path is built (--dataset ljspeech, or --synthetic-batches N); the '
-                     'torchvision branch of main.py is a later row of SURVEY.md section 8f')
+    # main.py:84-99 / dataloader.py:45-60: a torchvision dataset under <datadir>/<dataset>/, ToTensor() images
+    try:
+        from torchvision import datasets, transforms
+        cls = getattr(datasets, args.dataset)
+    except (ImportError, AttributeError) as e:
+        raise SystemExit('--dataset %s: not a torchvision dataset (%s)' % (args.dataset, e))
+    root = './{}/{}/'.format(args.datadir, args.dataset)
+    kwargs = {'num_workers': 1, 'pin_memory': True}
+    try:
+        tr = torch.utils.data.DataLoader(cls(root, train=True, download=False, transform=transforms.ToTensor()),
+                                         batch_size=args.batch_size, shuffle=True, **kwargs)
+        te = torch.utils.data.DataLoader(cls(root, train=False, download=False, transform=transforms.ToTensor()),
+                                         batch_size=args.batch_size, shuffle=True, **kwargs)
+    except RuntimeError as e:
+        raise SystemExit('--dataset %s: files not found under %s and this build does not download (%s); '
+                         'use --synthetic-batches N for a smoke run' % (args.dataset, root, e))
+    return tr, te
 
 
 def main(argv=None):
@@ -127,9 +175,6 @@ def main(argv=None):
     if not args.cuda:
         raise SystemExit('the B200 path has no CPU execution mode (remove --no-cuda / run on a B200)')
     device = torch.device('cuda')
-    if args.synthetic_batches > 0 and args.dataset != 'ljspeech':
-        print('synthetic mel batches: treating --dataset %s as ljspeech-shaped input' % args.dataset)
-        args.dataset = 'ljspeech'
     train_loader, test_loader = get_loaders(args)
     input_dim = 3 if args.dataset == 'CIFAR10' else 1                                  # main.py:100-116
     model = VQVAE(input_dim, args.dim, args.z_dim).to(device)
@@ -157,6 +202,10 @@ def main(argv=None):
             train_vqvae(args, model, optimizer, train_loader, device, epoch)
             test_vqvae(args, model, test_loader, device, epoch)
             with torch.no_grad():
+                if args.dataset != 'ljspeech':      # (the reference's sample block unpacks mel 5-tuples, main.py:138)
+                    last_epoch = epoch
+                    save_checkpoint(args, state())
+                    continue
                 x, y, c, g, input_lengths = next(iter(test_loader))
                 c = c.to(device).unsqueeze(1)
                 print("Evaluating samples")

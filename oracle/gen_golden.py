@@ -195,6 +195,57 @@ def gen_step(ref_models, ref_train, ref_test, tag, codebook, frames, seed, batch
     print('vqvae_step_%s.npz' % tag, 'losses', out['losses'], buf.getvalue().strip())
 
 
+class _ImageLoader(list):
+    """In-memory stand-in for the torchvision DataLoader of main.py:84-99: yields (data, label), exposes ``.dataset``."""
+    def __init__(self, items):
+        super().__init__(items)
+        self.dataset = list(range(sum(int(i[0].shape[0]) for i in items)))
+
+
+def gen_step_images(ref_models, ref_train, tag, input_dim, hw, seed, batch=4, steps=2):
+    """The torchvision branch (main.py:100-116 picks input_dim 1 or 3; train.py:150-179 is the loop): one fp64
+    forward/backward of the reference modules on an image batch + ``steps`` verbatim train_vqvae iterations."""
+    import torch.nn.functional as F
+    out = {}
+    dim, k = 64, 512
+    params, buffers = R.make_state(input_dim, dim, k, seed, codebook='spread')
+    imgs = [R.make_images(batch, input_dim, hw, hw, seed + 100 + i) for i in range(steps)]
+    out['meta'] = np.array([input_dim, dim, k, batch, hw, seed, steps], dtype=np.int64)
+    model = ref_models.VQVAE(input_dim, dim, k)
+    load_into(model, params, buffers)
+    model = model.double().train()
+    data = imgs[0].double()
+    x_tilde, z_e_x, z_q_x = model(data)
+    with torch.no_grad():
+        latents = ref_models.vq(z_e_x.permute(0, 2, 3, 1).contiguous(), model.codebook.embedding.weight)
+    lr_ = F.mse_loss(x_tilde, data)                                  # train.py:160
+    lv = F.mse_loss(z_q_x, z_e_x.detach())
+    lc = F.mse_loss(z_e_x, z_q_x.detach())
+    loss = lr_ + lv + 1.0 * lc
+    model.zero_grad()
+    loss.backward()
+    out['x_tilde'] = x_tilde.detach().float().numpy()
+    out['z_e_x'] = z_e_x.detach().float().numpy()
+    out['indices'] = latents.numpy().astype(np.int16)
+    out['losses'] = np.array([lr_.item(), lv.item(), lc.item(), loss.item()], dtype=np.float64)
+    for name, prm in model.named_parameters():
+        put(out, 'grad/' + name, prm.grad)
+    # ---- verbatim torchvision-branch loop from a fresh copy of the same state
+    model = ref_models.VQVAE(input_dim, dim, k)
+    load_into(model, params, buffers)
+    opt = torch.optim.Adam(model.parameters(), lr=1e-3)              # main.py:124
+    args = argparse.Namespace(dataset='CIFAR10' if input_dim == 3 else 'MNIST', beta=1.0, log_interval=1)
+    buf = io.StringIO()
+    loader = _ImageLoader([(im, torch.zeros(batch, dtype=torch.long)) for im in imgs])
+    with contextlib.redirect_stdout(buf), contextlib.redirect_stderr(io.StringIO()):
+        ref_train.train_vqvae(args, model, opt, loader, torch.device('cpu'), 1)
+    out['train_stdout'] = np.array(buf.getvalue())
+    for name, prm in model.named_parameters():
+        put(out, 'after/' + name, prm)
+    np.savez_compressed(os.path.join(OUT, 'vqvae_step_%s.npz' % tag), **out)
+    print('vqvae_step_%s.npz' % tag, 'losses', out['losses'], buf.getvalue().strip().splitlines()[-1])
+
+
 def gen_eval(ref_models):
     """Config C5-shaped (small): eval-mode encode -> decode with non-trivial running stats."""
     out = {}
@@ -241,10 +292,17 @@ def gen_adam():
 
 
 def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--only', default=None, help="'images': just the torchvision-branch fixtures")
+    only = ap.parse_args().only
     torch.manual_seed(1)
     torch.set_num_threads(1)          # fixed summation order for the fixtures
     os.makedirs(OUT, exist_ok=True)
     ref_vq, ref_models, ref_train, ref_test = import_reference()
+    gen_step_images(ref_models, ref_train, 'img3_32', 3, 32, 71)     # CIFAR10-shaped (main.py:109-116: input_dim = 3)
+    gen_step_images(ref_models, ref_train, 'img1_28', 1, 28, 72)     # MNIST / FashionMNIST-shaped (28 x 28, one channel)
+    if only == 'images':
+        return
     gen_vq(ref_vq)
     # seeds chosen (search over 200 seeds each) for the largest ReLU margin of the first batch, see
     # oracle.vqvae_ref.relu_margins: >= 1.8e-5 relative, i.e. ~20x fp32 rounding of a pre-activation

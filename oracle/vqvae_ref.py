@@ -105,6 +105,12 @@ def make_mel(batch, n_mels, frames, seed, dtype=torch.float32):
     return torch.tensor(rng.uniform(0.0, 1.0, size=(batch, n_mels, frames)).astype(np.float32)).to(dtype)
 
 
+def make_images(batch, channels, height, width, seed, dtype=torch.float32):
+    """Deterministic image batch in [0, 1] (what transforms.ToTensor() yields, dataloader.py:45-49): (B, C, H, W)."""
+    rng = np.random.RandomState(seed)
+    return torch.tensor(rng.uniform(0.0, 1.0, size=(batch, channels, height, width)).astype(np.float32)).to(dtype)
+
+
 # ----------------------------------------------------------------------------
 # layers
 # ----------------------------------------------------------------------------
@@ -274,7 +280,7 @@ def step_grads(p, b, c, beta=1.0, training=True, indices=None, relu_masks=None, 
     import contextlib
     p = {k: v.detach().clone().requires_grad_(True) for k, v in p.items()}
     nb = dict(b)
-    c4 = c.unsqueeze(1)                                                  # train.py:115
+    c4 = c.unsqueeze(1) if c.dim() == 3 else c                           # train.py:115 (mel) / :151 (image batches)
     _FORCED_MASKS = iter([relu_masks[n] for n in RELU_ORDER]) if relu_masks is not None else None
     _RECORD_MASKS = [] if relu_masks is None else None
     try:

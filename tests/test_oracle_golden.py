@@ -8,6 +8,7 @@ import pytest
 import torch
 
 from oracle import vq_ref, vqvae_ref as R
+from helpers import relerr
 
 
 PRE_BN_BIAS = (['encoder.0.bias', 'decoder.3.bias']
@@ -177,3 +178,33 @@ def test_ema_extension_self_consistent():
     n, m, e, counts, sums = vq_ref.ema_update(z, idx, np.ones(16, np.float32), np.zeros((16, 8), np.float32))
     assert counts.sum() == 100 and np.allclose(sums.sum(0), z.sum(0), atol=1e-4)
     assert n.shape == (16,) and m.shape == (16, 8) and e.shape == (16, 8)
+
+
+@pytest.mark.parametrize('tag', ['img3_32', 'img1_28'])
+def test_image_branch_against_reference(golden_dir, tag):
+    """The torchvision branch (main.py:100-116, train.py:150-179): the oracle on (B, C, H, W) image batches vs the
+    reference modules evaluated in fp64, and its loop vs the reference's printed losses / weights."""
+    g = _load(golden_dir, 'vqvae_step_%s.npz' % tag)
+    input_dim, dim, k, batch, hw, seed, steps = [int(v) for v in g['meta']]
+    p, b = R.make_state(input_dim, dim, k, seed, codebook='spread', dtype=torch.float64)
+    imgs = [R.make_images(batch, input_dim, hw, hw, seed + 100 + i) for i in range(steps)]
+    r = R.step_grads(p, b, imgs[0].double(), beta=1.0)
+    assert np.array_equal(r['indices'].numpy(), g['indices'].astype(np.int64))
+    for name in ('x_tilde', 'z_e_x'):
+        assert tuple(r[name].shape) == g[name].shape
+        assert relerr(r[name], g[name]) < 2e-6, name
+    got = np.array([r['loss_recons'].item(), r['loss_vq'].item(), r['loss_commit'].item(), r['loss'].item()])
+    assert np.allclose(got, g['losses'], rtol=1e-6)
+    for name in p:
+        if name in PRE_BN_BIAS:
+            continue
+        _check_summary(g, 'grad/' + name, r['grads'][name], rtol=2e-6, atol=1e-9)
+    p32, b32 = R.make_state(input_dim, dim, k, seed, codebook='spread')
+    p2, b2, log = R.train_steps(p32, b32, imgs, beta=1.0, lr=1e-3)
+    printed = [float(v) for v in re.findall(r'Loss: ([0-9.]+)', str(g['train_stdout']))]
+    assert len(printed) == steps
+    for pr, lg in zip(printed, log):
+        assert abs(pr - (lg['loss_recons'].item() + lg['loss_vq'].item())) < 5e-4 * max(1.0, pr)
+    for name in p2:
+        if name not in PRE_BN_BIAS:
+            _check_summary(g, 'after/' + name, p2[name], rtol=1e-2, atol=steps * 1.5e-3)

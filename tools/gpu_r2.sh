@@ -5,7 +5,7 @@ TAG=${1:-r2a}; shift
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm --format=csv > gpurun_out/${TAG}_smi.txt
 : > gpurun_out/${TAG}_pytest.log
-for f in tests/test_gpu_tma.py tests/test_gpu_ops.py tests/test_gpu_tma_model.py tests/test_gpu_model.py tests/test_gpu_main.py tests/test_gpu_data.py tests/test_gpu_dist.py; do
+for f in tests/test_gpu_tma.py tests/test_gpu_ops.py tests/test_gpu_tma_model.py tests/test_gpu_model.py tests/test_gpu_main.py tests/test_gpu_data.py tests/test_gpu_images.py tests/test_gpu_dist.py; do
   echo "=== $f" >> gpurun_out/${TAG}_pytest.log
   timeout 900 python -m pytest $f -m gpu -q -p no:cacheprovider --timeout 600 -s >> gpurun_out/${TAG}_pytest.log 2>&1
   echo "pytest $f exit $?"
