@@ -63,6 +63,15 @@ int conv_wgrad_slices(const nsg_conv_geom* cg);
 int wgrad_unpack_many(int n, const float* const* src, float* const* dw, const int* ntaps, const int* nslices,
                       const long long* a_stride, const long long* b_stride, cudaStream_t stream);
 
+int greatest_priority() {
+  static int cached = 1;
+  if (cached == 1) {
+    int least = 0, greatest = 0;
+    cached = cudaDeviceGetStreamPriorityRange(&least, &greatest) == cudaSuccess ? greatest : 0;
+  }
+  return cached;
+}
+
 int g_pdl = getenv("NSG_PDL") ? atoi(getenv("NSG_PDL")) : 1;     // common.cuh: programmatic dependent launch
 
 namespace {

@@ -49,21 +49,40 @@ extern int g_pdl;
 void pdl_note_launch(cudaStream_t s);
 void pdl_note_pack(cudaStream_t s);
 bool pdl_weights_settled(cudaStream_t s);
+// `urgent`: the launch carries the device's greatest priority.  Used by the grid-barrier kernels (conv_tma.cu, BnFuse):
+// their resident CTAs spin until the LAST CTA of the grid has arrived, so when an SM frees up next to a kernel of
+// another stream (the weight gradients run beside the data-gradient chain) the pending CTA of the barrier kernel
+// must be the one that gets it.
+int greatest_priority();
 template <typename... KArgs, typename... Args>
-inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
-                              Args&&... args) {
+inline cudaError_t launch_pdl_ex(bool urgent, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                                 cudaStream_t stream, Args&&... args) {
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = grid;
   cfg.blockDim = block;
   cfg.dynamicSmemBytes = smem;
   cfg.stream = stream;
-  cudaLaunchAttribute at[1];
-  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cudaLaunchAttribute at[2];
+  int n = 0;
+  if (g_pdl) {
+    at[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[n].val.programmaticStreamSerializationAllowed = 1;
+    ++n;
+  }
+  if (urgent) {
+    at[n].id = cudaLaunchAttributePriority;
+    at[n].val.priority = greatest_priority();
+    ++n;
+  }
   cfg.attrs = at;
-  cfg.numAttrs = g_pdl ? 1 : 0;
+  cfg.numAttrs = n;
   pdl_note_launch(stream);
   return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              Args&&... args) {
+  return launch_pdl_ex(false, kernel, grid, block, smem, stream, static_cast<Args&&>(args)...);
 }
 #if defined(__CUDA_ARCH__)
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }

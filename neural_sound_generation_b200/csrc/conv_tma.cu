@@ -935,8 +935,8 @@ static int launch_conv_tma(int grid, size_t smem, cudaStream_t stream, const CUt
     if (err != cudaSuccess) return cuda_fail(err, "cudaFuncSetAttribute(conv_tma_kernel)");
     configured = true;
   }
-  launch_pdl(conv_tma_kernel<NACC>, dim3(grid), dim3(320), smem, stream, tm[0], tm[1], tm[2], tm[3],
-             static_cast<const uint8_t*>(packed), static_cast<__nv_bfloat16*>(out), e, f, P);
+  launch_pdl_ex(NACC > 2, conv_tma_kernel<NACC>, dim3(grid), dim3(320), smem, stream, tm[0], tm[1], tm[2], tm[3],
+                static_cast<const uint8_t*>(packed), static_cast<__nv_bfloat16*>(out), e, f, P);
   NSG_CHECK_LAUNCH("conv_tma_kernel");
   return NSG_OK;
 }

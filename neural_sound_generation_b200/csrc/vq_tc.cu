@@ -561,6 +561,7 @@ vq_search_res_kernel(const __grid_constant__ CUtensorMap tmz, const T* __restric
                 }
               }
             } else {
+              mbar_wait(&a_full[slot], (uint32_t)((i / VR_STAGES) & 1));     // (complete long ago: acquires the TMA write)
 #pragma unroll
               for (int j = 0; j < 8; ++j) {
                 const uint4 raw = *reinterpret_cast<const uint4*>(ztile + sw128_offset(gt, j));
