@@ -24,6 +24,7 @@ class GraphedTrainStep(object):
             raise TypeError('GraphedTrainStep needs neural_sound_generation_b200.optim.Adam (device-side step count)')
         self.model, self.optimizer, self.beta = model, optimizer, float(beta)
         self._grad_hook, self._batch_shape = grad_hook, tuple(batch_shape)
+        self._copy, self._stage, self._stage_free, self._pending, self._k = None, None, [None, None], None, 0
         self._capture()
 
     def _hyper(self):
@@ -81,6 +82,23 @@ class GraphedTrainStep(object):
         self.graph = None
         torch.cuda.synchronize(dev)
 
+    def prefetch(self, c):
+        """Start copying the NEXT batch (pinned host tensor) into a staging buffer on a private copy stream, so the
+        transfer runs under the step in flight; the following ``step(c)`` with the same tensor object then only waits
+        for that copy and moves the batch device-to-device.  Two staging buffers alternate."""
+        dev = self.c.device
+        if self._copy is None:
+            self._copy = torch.cuda.Stream(device=dev)
+            self._stage = [torch.empty_like(self.c) for _ in range(2)]
+        k = self._k ^ 1
+        if self._stage_free[k] is not None:                 # the step that last read this staging buffer
+            self._copy.wait_event(self._stage_free[k])
+        with torch.cuda.stream(self._copy):
+            self._stage[k].copy_(c.reshape(self.c.shape), non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(self._copy)
+        self._pending, self._k = (c, k, ev), k
+
     def __call__(self, c):
         if self._hyper() != self._captured_hyper:
             torch.cuda.synchronize(self.c.device)
@@ -88,7 +106,17 @@ class GraphedTrainStep(object):
             self._capture()
         if self.model.__dict__.get('_grads_dirty', True):
             self.optimizer.zero_grad()
-        self.c.copy_(c.reshape(self.c.shape), non_blocking=True)
+        if self._pending is not None and self._pending[0] is c:
+            _, k, ev = self._pending
+            self._pending = None
+            cur = torch.cuda.current_stream(self.c.device)
+            cur.wait_event(ev)
+            self.c.copy_(self._stage[k])
+            free = torch.cuda.Event()
+            free.record(cur)
+            self._stage_free[k] = free
+        else:
+            self.c.copy_(c.reshape(self.c.shape), non_blocking=True)
         self.graph.replay()
         return self.losses
 

@@ -343,3 +343,29 @@ def test_tma_generic_autograd_after_fused_step():
                 continue
             # (the generic path hands fp32 copies of z_e / z_q / x_tilde to torch's loss: bf16-level differences)
             assert relerr(q.grad, fused[name]) < 2e-2, (rep, name, relerr(q.grad, fused[name]))
+
+
+def test_graphed_step_prefetch_is_the_same_step():
+    """GraphedTrainStep.prefetch (double-buffered host -> device copy on a private stream): the step that consumes a
+    prefetched pinned batch is the step fed directly; a batch that was not the prefetched one falls back to the direct
+    copy."""
+    p, b, _ = _state(seed=23)
+    host = [R.make_mel(4, 80, 64, 700 + i).pin_memory() for i in range(5)]
+    runs = []
+    for use_prefetch in (False, True):
+        m = _model(p, b, 2)
+        opt = nsg.optim.Adam(m.parameters(), lr=1e-3)
+        step = nsg.GraphedTrainStep(m, opt, (4, 1, 80, 64), beta=1.0)
+        out = []
+        for i in range(5):
+            losses = step(host[i])
+            if use_prefetch and i + 1 < 5:
+                step.prefetch(host[i + 1] if i != 2 else host[0])      # (i == 2: a prefetch that is then NOT consumed)
+            out.append(losses.tolist())
+        torch.cuda.synchronize()
+        runs.append((out, {k: v.clone() for k, v in m.state_dict().items()}))
+    # (the weight gradients meet through fp32 atomics: two runs agree to rounding, not bit for bit)
+    assert np.allclose(np.array(runs[0][0]), np.array(runs[1][0]), rtol=2e-3)
+    for k in runs[0][1]:
+        if runs[0][1][k].dtype.is_floating_point:
+            assert relerr(runs[1][1][k], runs[0][1][k]) < 5e-3, k
