@@ -116,6 +116,23 @@ typedef struct {
  * nsg_bn_bwd64.  `barrier` is ONE unsigned counter per launch, zero before the launch.  The grid barrier relies on all
  * CTAs being resident (grid <= SM count, one CTA per SM): do not run two such launches concurrently on one device
  * from different streams. */
+/* Cross-GPU statistics for synchronised BatchNorm (one process per GPU of ONE node): every rank owns an exchange
+ * area of NSG_PEER_AREA_BYTES in peer-mapped memory (torch.distributed._symmetric_memory / cuMemCreate + cuMemMap),
+ * zero-initialised, whose address AS MAPPED ON THIS GPU is areas[rank].  A launch that carries an nsg_peer_sync sums
+ * its 128 fp64 statistics over the ranks through those areas (direct NVLink stores + flags, ranks added in rank order:
+ * identical bits everywhere) -- no collective launch.  `slot` selects one of NSG_PEER_SLOTS exchange slots; a slot may
+ * be used once between two points at which all ranks synchronise (the step's gradient all-reduce), by the same launch
+ * on every rank.  A rank that never arrives traps the waiting kernels after ~1 s instead of hanging the device. */
+#define NSG_PEER_MAX 8
+#define NSG_PEER_SLOTS 32
+#define NSG_PEER_AREA_BYTES (NSG_PEER_SLOTS * NSG_PEER_MAX * 128 * 8 + NSG_PEER_SLOTS * NSG_PEER_MAX * 4)
+typedef struct {
+  int world, rank, slot;
+  void* areas[NSG_PEER_MAX];
+} nsg_peer_sync;
+/* sums[0..127] (fp64, device) := sum over ranks; one small launch (the stand-alone form of the exchange) */
+int nsg_peer_allreduce_stats(double* sums, const nsg_peer_sync* peer, void* stream);
+
 #define NSG_BNF_NONE 0
 #define NSG_BNF_TRAIN 1
 #define NSG_BNF_EVAL 2
@@ -136,6 +153,8 @@ typedef struct {
   float* dgamma;            /* BWD (nullable) */
   float* dbeta;
   void* out2;               /* TRAIN / BWD: second output, 32-byte aligned */
+  const nsg_peer_sync* peer; /* TRAIN / BWD, nullable: sum the statistics over the GPUs of the node inside the barrier
+                              * (`count` must then be the GLOBAL element count and `barrier` TWO zeroed counters) */
 } nsg_bn_fuse;
 
 /* CUDA-core fp32-accumulate kernel, any shape.  `impl` must be 0 (kept for ABI stability). */

@@ -26,7 +26,7 @@ EXPORTS = [
     'nsg_conv_wgrad_slices', 'nsg_conv_wgrad_tma_sliced', 'nsg_pdl', 'nsg_recon_loss_bf16', 'nsg_loss_finalize',
     'nsg_bn_act64', 'nsg_bn_bwd64', 'nsg_relu64', 'nsg_vq_bwd_stats64', 'nsg_debug_timeline',
     'nsg_c1_conv_tc', 'nsg_c1_convT_tc', 'nsg_c1_wgrad_tc', 'nsg_scatter_mode', 'nsg_ema_update', 'nsg_vq_resident',
-    'nsg_conv_bn_tma', 'nsg_conv_bn_tma_fits', 'nsg_c1_conv_bn_tc', 'nsg_mel_collate',
+    'nsg_conv_bn_tma', 'nsg_conv_bn_tma_fits', 'nsg_c1_conv_bn_tc', 'nsg_mel_collate', 'nsg_peer_allreduce_stats',
 ]
 
 
@@ -47,12 +47,20 @@ class Epilogue(C.Structure):
                 ('xhat_src', C.c_void_p), ('mean', C.c_void_p), ('invstd', C.c_void_p), ('tanh_out', C.c_int)]
 
 
+PEER_MAX, PEER_SLOTS = 8, 32
+PEER_AREA_BYTES = PEER_SLOTS * PEER_MAX * 128 * 8 + PEER_SLOTS * PEER_MAX * 4
+
+
+class PeerSync(C.Structure):
+    _fields_ = [('world', C.c_int), ('rank', C.c_int), ('slot', C.c_int), ('areas', C.c_void_p * PEER_MAX)]
+
+
 class BnFuse(C.Structure):
     _fields_ = [('mode', C.c_int), ('relu_out', C.c_int), ('gamma', C.c_void_p), ('beta', C.c_void_p),
                 ('eps', C.c_float), ('momentum', C.c_float), ('count', C.c_double), ('running_mean', C.c_void_p),
                 ('running_var', C.c_void_p), ('num_batches_tracked', C.c_void_p), ('coef', C.c_void_p),
                 ('res', C.c_void_p), ('barrier', C.c_void_p), ('dgamma', C.c_void_p), ('dbeta', C.c_void_p),
-                ('out2', C.c_void_p)]
+                ('out2', C.c_void_p), ('peer', C.POINTER(PeerSync))]
 
 
 class NsgError(RuntimeError):
@@ -122,6 +130,7 @@ def load():
     lib.nsg_ema_update.argtypes = [vp, vp, vp, vp, vp, i, i, f, f, vp, vp]
     lib.nsg_tanh_bwd.argtypes = [vp, vp, vp, ll, vp]
     lib.nsg_mel_collate.argtypes = [vp, vp, i, i, i, vp, vp, vp]
+    lib.nsg_peer_allreduce_stats.argtypes = [vp, C.POINTER(PeerSync), vp]
     lib.nsg_adam_step.argtypes = [vp, vp, vp, vp, ll, f, f, f, f, f, vp, i, vp, vp]
     for name in EXPORTS:
         fn = getattr(lib, name)

@@ -46,6 +46,7 @@ int conv_wgrad_tc(const nsg_conv_geom* cg, const void* p, const nsg_prologue* pr
                   const nsg_prologue* pro_q, float* dw, float* q_colsum, int passes, cudaStream_t stream);
 
 int conv_bn_tma_fits(const nsg_conv_geom* cg);
+int peer_allreduce_stats(double* sums, const nsg_peer_sync* p, cudaStream_t stream);
 int conv_gemm_tma(const nsg_conv_geom* cg, const void* in, const void* packed, const nsg_epilogue* epi,
                   const nsg_bn_fuse* bnf, void* out,
                   cudaStream_t stream);
@@ -214,6 +215,10 @@ int nsg_conv_bn_tma(const nsg_conv_geom* g, const void* in, const void* packed_w
   if (rc) return rc;
   NSG_REQUIRE(in && packed_w, "conv_bn_tma: null pointer");
   return conv_gemm_tma(g, in, packed_w, epi, bn, out, (cudaStream_t)stream);
+}
+
+int nsg_peer_allreduce_stats(double* sums, const nsg_peer_sync* peer, void* stream) {
+  return peer_allreduce_stats(sums, peer, (cudaStream_t)stream);
 }
 
 int nsg_conv_bn_tma_fits(const nsg_conv_geom* g) {

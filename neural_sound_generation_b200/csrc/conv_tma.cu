@@ -282,6 +282,70 @@ __device__ __forceinline__ TmaTile fetch_tile(const TmaConvParams& P, const int4
   return decode_tile(P, (int)blockIdx.x + i * (int)gridDim.x);
 }
 
+// ---------------------------------------------------------------------------------------------- cross-GPU statistics
+// Synchronised BatchNorm (one process per GPU; every rank must normalise with the statistics of the GLOBAL batch to
+// equal the single-process reference): the 128 fp64 partial sums of a layer are exchanged through peer-mapped
+// ("symmetric") memory over NVLink inside the kernel that needs them, instead of a 1 KB ncclAllReduce launch per
+// layer and direction (~26 us each, 20 per step).  Every rank owns an area
+//     slots [NSG_PEER_SLOTS][8 ranks][128] fp64   |   flags [NSG_PEER_SLOTS][8 ranks] u32
+// mapped on all ranks.  One exchange (slot s) on rank r:  write my sums into slot (s, r) of EVERY rank; fence; raise
+// flag (s, r) on every rank; wait until my flags (s, 0..world-1) are up; sum my slots (s, 0..world-1) in rank order
+// (every rank adds the same numbers in the same order: bit-identical results everywhere); lower my flags.  A slot is
+// used once per step, and a rank can only reach it again after the step's gradient all-reduce, which every rank enters
+// after its own last exchange -- so lowering the flags after the read cannot race with the next step's writers.
+struct PeerSync {
+  int world, rank, slot;
+  double* slots[NSG_PEER_MAX];
+  unsigned int* flags[NSG_PEER_MAX];
+};
+constexpr size_t kPeerSlotDoubles = (size_t)NSG_PEER_MAX * 2 * TM_C;
+
+// executed by 128+ threads of ONE CTA (thread index e = 0.. within the group, `bar` = their named barrier id / count);
+// sums[0..127] in global memory is replaced by the sum over ranks
+__device__ __forceinline__ void peer_exchange(const PeerSync& ps, double* sums, int e, int bar_id, int bar_threads) {
+  const size_t base = (size_t)ps.slot * kPeerSlotDoubles;
+  if (e < 2 * TM_C) {
+    const double v = __ldcg(sums + e);
+    for (int p = 0; p < ps.world; ++p)
+      asm volatile("st.relaxed.sys.global.f64 [%0], %1;" ::"l"(ps.slots[p] + base + (size_t)ps.rank * 2 * TM_C + e), "d"(v) : "memory");
+  }
+  __threadfence_system();
+  named_bar(bar_id, bar_threads);
+  if (e < ps.world) {
+    unsigned int* mine_on_peer = ps.flags[e] + (size_t)ps.slot * NSG_PEER_MAX + ps.rank;
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(mine_on_peer), "r"(1u) : "memory");
+    const unsigned int* theirs = ps.flags[ps.rank] + (size_t)ps.slot * NSG_PEER_MAX + e;
+    unsigned int v = 0;
+    for (long long spins = 0; spins < (1ll << 28); ++spins) {      // ranks may be seconds apart (first steps): ~20 s
+      asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(theirs) : "memory");
+      if (v != 0) break;
+      __nanosleep(64);
+    }
+    if (v == 0) __trap();                  // a rank that never arrives must not hang the device
+  }
+  named_bar(bar_id, bar_threads);
+  if (e < 2 * TM_C) {
+    double acc = 0.0;
+    for (int r = 0; r < ps.world; ++r) {
+      double v;
+      asm volatile("ld.relaxed.sys.global.f64 %0, [%1];" : "=d"(v) : "l"(ps.slots[ps.rank] + base + (size_t)r * 2 * TM_C + e) : "memory");
+      acc += v;
+    }
+    __stcg(sums + e, acc);
+  }
+  __threadfence();
+  named_bar(bar_id, bar_threads);
+  if (e < ps.world) ps.flags[ps.rank][(size_t)ps.slot * NSG_PEER_MAX + e] = 0u;
+}
+
+// stand-alone form for the statistics that are not produced by a grid-barrier launch (encoder.1 forward, the two
+// backward reductions fed by the single-channel / bottleneck kernels): one CTA, replaces ncclAllReduce of 1 KB
+__global__ void __launch_bounds__(128) peer_allreduce_kernel(double* sums, PeerSync ps) {
+  pdl_wait();
+  pdl_trigger();
+  peer_exchange(ps, sums, threadIdx.x, 3, 128);
+}
+
 // BatchNorm fused across a grid barrier (NACC > 2, "hold" launches).  A CTA of the persistent grid owns at most NACC
 // tiles; their fp32 accumulators all stay in TMEM (NACC x 64 columns).  Pass 1 (overlapping the remaining MMAs) reads
 // each accumulator once for the per-channel sums -- BatchNorm moments of the convolution output (forward) or the
@@ -305,6 +369,7 @@ struct BnFuse {
   float* dgamma;
   float* dbeta;
   __nv_bfloat16* out2;
+  PeerSync peer;                   // world > 1: the statistics are summed over the GPUs of the node inside the barrier
 };
 
 // All CTAs of the grid are resident (grid <= SM count, 1 CTA per SM; kernels running beside this one on other streams
@@ -315,6 +380,17 @@ __device__ __forceinline__ void grid_barrier(unsigned int* ctr, unsigned int exp
   atomicAdd(ctr, 1u);
   unsigned int v = 0;
   for (long long spins = 0; spins < (1ll << 24); ++spins) {
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
+    if (v >= expected) break;
+    __nanosleep(64);
+  }
+  if (v < expected) __trap();
+  __threadfence();
+}
+
+__device__ __forceinline__ void grid_barrier_wait(unsigned int* ctr, unsigned int expected, long long max_spins = 1ll << 24) {
+  unsigned int v = 0;
+  for (long long spins = 0; spins < max_spins; ++spins) {
     asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
     if (v >= expected) break;
     __nanosleep(64);
@@ -655,7 +731,23 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
     if (HOLD) {
       // ---------------------------------------------------------------- grid barrier, coefficients, pass 2
       named_bar(1, 256);                               // every statistic atomic of this CTA has been issued
-      if (tid == 64) grid_barrier(bn.barrier, gridDim.x);
+      if (bn.peer.world > 1) {
+        // synchronised BatchNorm: CTA 0 waits for the grid, swaps the sums with the other GPUs, then opens a second gate
+        if (tid == 64) grid_barrier(bn.barrier, gridDim.x);
+        if (blockIdx.x == 0) {
+          named_bar(1, 256);
+          peer_exchange(bn.peer, epi.stats, e, 1, 256);
+          named_bar(1, 256);
+          if (tid == 64) {
+            __threadfence();
+            atomicExch(bn.barrier + 1, 1u);
+          }
+        } else if (tid == 64) {
+          grid_barrier_wait(bn.barrier + 1, 1u, 1ll << 29);
+        }
+      } else if (tid == 64) {
+        grid_barrier(bn.barrier, gridDim.x);
+      }
       named_bar(1, 256);
       if (e < TM_C) {
         const int c = e;
@@ -898,6 +990,31 @@ static int encode_input_maps(CUtensorMap* tm, const void* in, int batch, int in_
   return NSG_OK;
 }
 
+static int make_peer(const nsg_peer_sync* p, PeerSync* out) {
+  NSG_REQUIRE(p->world >= 2 && p->world <= NSG_PEER_MAX && p->rank >= 0 && p->rank < p->world,
+              "peer sync: world %d / rank %d (at most %d GPUs of one node)", p->world, p->rank, NSG_PEER_MAX);
+  NSG_REQUIRE(p->slot >= 0 && p->slot < NSG_PEER_SLOTS, "peer sync: slot %d out of range", p->slot);
+  PeerSync s{};
+  s.world = p->world; s.rank = p->rank; s.slot = p->slot;
+  for (int i = 0; i < p->world; ++i) {
+    NSG_REQUIRE(p->areas[i], "peer sync: area of rank %d missing", i);
+    s.slots[i] = static_cast<double*>(p->areas[i]);
+    s.flags[i] = reinterpret_cast<unsigned int*>(static_cast<char*>(p->areas[i]) +
+                                                 (size_t)NSG_PEER_SLOTS * kPeerSlotDoubles * sizeof(double));
+  }
+  *out = s;
+  return NSG_OK;
+}
+
+int peer_allreduce_stats(double* sums, const nsg_peer_sync* p, cudaStream_t stream) {
+  NSG_REQUIRE(sums && p, "peer_allreduce_stats: null pointer");
+  PeerSync s{};
+  if (int rc = make_peer(p, &s)) return rc;
+  launch_pdl(peer_allreduce_kernel, dim3(1), dim3(128), 0, stream, sums, s);
+  NSG_CHECK_LAUNCH("peer_allreduce_kernel");
+  return NSG_OK;
+}
+
 // validated device-side copy of the public nsg_bn_fuse
 static int make_bnfuse(const nsg_bn_fuse* b, const EpiArgs& e, BnFuse* out) {
   BnFuse f{};
@@ -907,6 +1024,12 @@ static int make_bnfuse(const nsg_bn_fuse* b, const EpiArgs& e, BnFuse* out) {
     f.momentum = b->momentum; f.count = b->count; f.running_mean = b->running_mean; f.running_var = b->running_var;
     f.nbt = b->num_batches_tracked; f.coef = b->coef; f.res = static_cast<const __nv_bfloat16*>(b->res);
     f.barrier = b->barrier; f.dgamma = b->dgamma; f.dbeta = b->dbeta; f.out2 = static_cast<__nv_bfloat16*>(b->out2);
+    if (b->peer && b->peer->world > 1) {
+      if (int rc = make_peer(b->peer, &f.peer)) return rc;
+      NSG_REQUIRE(f.mode != NSG_BNF_EVAL, "conv_bn_tma: eval mode exchanges nothing");
+    } else {
+      f.peer.world = 1;
+    }
     NSG_REQUIRE(f.gamma, "conv_bn_tma: gamma missing");
     if (f.mode == NSG_BNF_EVAL) {
       NSG_REQUIRE(f.beta && f.running_mean && f.running_var, "conv_bn_tma: eval mode needs beta and the running statistics");

@@ -87,7 +87,7 @@ class DataParallel(object):
     """Per-model data-parallel state; attached as ``model.dp`` and consulted by the kernel schedule
     (``engine_tma.EngineTMA``) and by ``VQVAE.loss_and_grads``."""
 
-    def __init__(self, sync_bn=False, overlap=True, group=None):
+    def __init__(self, sync_bn=False, overlap=True, group=None, peer_ok=True):
         if not (dist.is_available() and dist.is_initialized()):
             raise RuntimeError('DataParallel needs an initialised torch.distributed process group')
         self.group = group
@@ -98,10 +98,51 @@ class DataParallel(object):
         self.comm = None            # communication stream (CUDA only)
         self.collectives = 0        # issued per step (bench.py reports it)
         self.loss_slots = None      # view of the flat gradient buffer's tail padding that carried the loss scalars
+        # sync_bn over peer memory: the statistics are exchanged INSIDE the kernels that need them (csrc/conv_tma.cu,
+        # PeerSync) instead of one 1 KB ncclAllReduce launch per layer and direction
+        self.peer_areas = None      # every rank's exchange area as mapped on this GPU, or None (-> NCCL)
+        self.peer_exchanges = 0     # exchange slots used so far in the current step
+        if self.sync_bn and self.world > 1 and torch.cuda.is_available() and peer_ok and self.world <= 8:
+            self._setup_peer_memory()
+
+    def _setup_peer_memory(self):
+        import os
+        if os.environ.get('NSG_PEER_SYNC', '1') == '0':
+            return
+        try:
+            import torch.distributed._symmetric_memory as symm
+            from ._cabi import PEER_AREA_BYTES
+            dev = torch.device('cuda', torch.cuda.current_device())
+            area = symm.empty(PEER_AREA_BYTES, dtype=torch.uint8, device=dev)
+            hdl = symm.rendezvous(area, self.group if self.group is not None else dist.group.WORLD)
+            area.zero_()
+            torch.cuda.synchronize(dev)
+            dist.barrier(group=self.group)
+            self._peer_keep = (area, hdl)
+            self.peer_areas = [int(p) for p in hdl.buffer_ptrs]
+        except Exception as e:              # no peer access between these GPUs: fall back to NCCL, loudly
+            print('[nsg dist] peer-memory statistics unavailable (%s): sync-BN uses ncclAllReduce' % str(e)[:200])
+            self.peer_areas = None
+
+    def begin_step(self):
+        self.peer_exchanges = 0
+
+    def next_peer(self):
+        """nsg_peer_sync of the next exchange of this step (all ranks issue the same sequence)."""
+        from . import ops
+        if self.peer_exchanges >= 32:
+            raise RuntimeError('more than 32 statistic exchanges in one step')
+        ps = ops.peer_sync(self.world, self.rank, self.peer_exchanges, self.peer_areas)
+        self.peer_exchanges += 1
+        return ps
 
     # -- BatchNorm statistics -------------------------------------------------------------------------------
     def reduce_stats(self, stats):
         """stats: fp64 [2*C] sums accumulated by a convolution epilogue on the current stream."""
+        if self.peer_areas is not None:
+            from . import ops
+            ops.peer_allreduce_stats(stats, self.next_peer())
+            return
         allreduce_sum_(stats, self.group)
         self.collectives += 1
 
@@ -168,6 +209,9 @@ class DataParallelStep(GraphedTrainStep):
             dist.broadcast(flat['params'], src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
             for _, b in model.named_buffers():
                 dist.broadcast(b, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+            # the in-kernel statistic exchange has a bounded wait: start the first (eager) iteration together
+            torch.cuda.synchronize()
+            dist.barrier(group=group)
         super(DataParallelStep, self).__init__(model, optimizer, batch_shape, beta)
 
     def _body(self, grad_hook):

@@ -151,8 +151,10 @@ class EngineTMA(object):
         dev = x_nhwc.device
         ctx.coef = torch.empty((len(BN_LAYERS), 4, self.dim), dtype=torch.float32, device=dev)
         nst = len(BN_LAYERS) * 2 * 2 * self.dim
-        NBAR = 32                   # grid-barrier counters of the BatchNorm-fused launches (one each, zero at launch)
+        NBAR = 64                   # grid-barrier counters of the BatchNorm-fused launches (two each, zero at launch)
         ctx.nbar = 0
+        if self.dp is not None:
+            self.dp.begin_step()
         if fused:
             # everything the step accumulates into lives in ONE buffer cleared by ONE fill at the start of the step:
             # BatchNorm statistic sums (fp64), the two squared-error sums (fp64), the packed weight-gradient images
@@ -208,12 +210,17 @@ class EngineTMA(object):
                           stats_mode=STATS_MOMENTS if stats is not None else 0, stats=stats, relu_out=relu_out)
         return out
 
+    def _sync(self):
+        """True when BatchNorm statistics span the ranks (dist.DataParallel(sync_bn=True))."""
+        return self.dp is not None and self.dp.sync_bn and self.dp.world > 1
+
     def _fusable(self, g):
-        return (self.fuse_bn and not (self.dp is not None and self.dp.sync_bn) and ops.conv_bn_tma_fits(g))
+        # synchronised BatchNorm fuses only when the statistics can be exchanged inside the kernel (peer memory)
+        return (self.fuse_bn and (not self._sync() or self.dp.peer_areas is not None) and ops.conv_bn_tma_fits(g))
 
     def _bar(self, ctx):
-        b = ctx.bars[ctx.nbar:ctx.nbar + 1]
-        ctx.nbar += 1
+        b = ctx.bars[ctx.nbar:ctx.nbar + 2]
+        ctx.nbar += 2
         return b
 
     def _conv_bn_fwd(self, ctx, P, Bufs, name, bn_name, x, res=None, relu_out=True):
@@ -233,8 +240,10 @@ class EngineTMA(object):
         if ctx.training and self._fusable(g):
             h = torch.empty(shape, dtype=BF, device=x.device)
             v = torch.empty(shape, dtype=BF, device=x.device)
+            sync = self._sync()
             ops.conv_bn_tma(g, x, L.wf, h, ops.BNF_TRAIN, P[bn_name + '.weight'], beta=P[bn_name + '.bias'], eps=BN_EPS,
-                            momentum=BN_MOMENTUM, count=h.numel() // self.dim,
+                            momentum=BN_MOMENTUM, count=h.numel() // self.dim * (self.dp.world if sync else 1),
+                            peer=self.dp.next_peer() if sync else None,
                             running_mean=Bufs[bn_name + '.running_mean'], running_var=Bufs[bn_name + '.running_var'],
                             nbt=Bufs[bn_name + '.num_batches_tracked'], coef=ctx.coef[BN_INDEX[bn_name]], res=res,
                             barrier=self._bar(ctx), out2=v, bn_relu=relu_out, bias=P[name + '.bias'], stats=bn['fstats'])
@@ -254,8 +263,13 @@ class EngineTMA(object):
         if self._fusable(g):
             dh = torch.empty((b, ih, iw, c), dtype=BF, device=dy.device)
             gy = torch.empty_like(dh) if want_g else None
-            ops.conv_bn_tma(g, dy, L.wd, gy, ops.BNF_BWD, P[bn_name + '.weight'], count=dh.numel() // self.dim,
-                            barrier=self._bar(ctx), dgamma=G[bn_name + '.weight'], dbeta=G[bn_name + '.bias'], out2=dh,
+            sync = self._sync()
+            lead = not sync or self.dp.rank == 0    # the exchanged sums ARE the global dgamma / dbeta: one rank adds them
+            ops.conv_bn_tma(g, dy, L.wd, gy, ops.BNF_BWD, P[bn_name + '.weight'],
+                            count=dh.numel() // self.dim * (self.dp.world if sync else 1),
+                            peer=self.dp.next_peer() if sync else None, barrier=self._bar(ctx),
+                            dgamma=G[bn_name + '.weight'] if lead else None,
+                            dbeta=G[bn_name + '.bias'] if lead else None, out2=dh,
                             stats=bn['bstats'], xhat_src=h, mean=bn['mean'], invstd=bn['invstd'], **epi)
             return gy, dh
         gy = self._conv_dgrad(name, dy, in_hw, stats_mode=STATS_BNBWD, stats=bn['bstats'], xhat_src=h, mean=bn['mean'],

@@ -409,7 +409,7 @@ def conv_bn_tma_fits(geom):
 def conv_bn_tma(geom, x, packed, out, bn_mode, gamma, beta=None, eps=1e-5, momentum=0.1, count=1.0, running_mean=None,
                 running_var=None, nbt=None, coef=None, res=None, barrier=None, dgamma=None, dbeta=None, out2=None,
                 bn_relu=False, bias=None, add_src=None, mask_mode=MASK_NONE, mask_src=None, stats=None,
-                xhat_src=None, mean=None, invstd=None, relu_out=False):
+                xhat_src=None, mean=None, invstd=None, relu_out=False, peer=None):
     """nsg_conv_bn_tma: the TMA convolution with the BatchNorm that follows it (forward) / that its output gradient
     flows into (backward) fused; see include/nsg_b200.h (nsg_bn_fuse).  ``out`` may be None for TRAIN / BWD."""
     global launch_count
@@ -425,7 +425,7 @@ def conv_bn_tma(geom, x, packed, out, bn_mode, gamma, beta=None, eps=1e-5, momen
                      A.ptr(xhat_src), A.ptr(mean), A.ptr(invstd), 2 if relu_out else 0)
     bn = A.BnFuse(bn_mode, 1 if bn_relu else 0, A.ptr(gamma), A.ptr(beta), eps, momentum, float(count),
                   A.ptr(running_mean), A.ptr(running_var), A.ptr(nbt), A.ptr(coef), A.ptr(res), A.ptr(barrier),
-                  A.ptr(dgamma), A.ptr(dbeta), A.ptr(out2))
+                  A.ptr(dgamma), A.ptr(dbeta), A.ptr(out2), C.pointer(peer) if peer is not None else None)
     rc = A.load().nsg_conv_bn_tma(C.byref(geom), A.ptr(x), A.ptr(packed), C.byref(epi), C.byref(bn), A.ptr(out),
                                   A.stream_ptr())
     A.check(rc, 'nsg_conv_bn_tma')
@@ -564,7 +564,7 @@ def c1_conv_bn_eval_tc(geom, x1, packed, out, gamma, beta, running_mean, running
     epi = A.Epilogue(A.ptr(bias), None, MASK_NONE, None, None, None, STATS_NONE, None, None, None, None,
                      2 if relu_out else 0)
     bn = A.BnFuse(BNF_EVAL, 0, A.ptr(gamma), A.ptr(beta), eps, 0.0, 1.0, A.ptr(running_mean), A.ptr(running_var), None,
-                  None, None, None, None, None, None)
+                  None, None, None, None, None, None, None)
     rc = A.load().nsg_c1_conv_bn_tc(C.byref(geom), A.ptr(x1), A.ptr(packed), C.byref(epi), C.byref(bn), A.ptr(out),
                                     A.stream_ptr())
     A.check(rc, 'nsg_c1_conv_bn_tc')
@@ -607,4 +607,25 @@ def mel_collate(frames, offsets, n_mels, t_out, out_f32=None, out_bf16=None):
     rc = A.load().nsg_mel_collate(A.ptr(frames), A.ptr(offsets), offsets.numel() - 1, n_mels, t_out, A.ptr(out_f32),
                                   A.ptr(out_bf16), A.stream_ptr())
     A.check(rc, 'nsg_mel_collate')
+    launch_count += 1
+
+
+def peer_sync(world, rank, slot, area_ptrs):
+    """nsg_peer_sync for one exchange: ``area_ptrs`` = every rank's exchange area as mapped on this GPU (ints)."""
+    ps = A.PeerSync()
+    ps.world, ps.rank, ps.slot = world, rank, slot
+    for i, a in enumerate(area_ptrs):
+        ps.areas[i] = a
+    return ps
+
+
+def peer_allreduce_stats(sums, peer):
+    """sums (128 fp64, device) := sum over the ranks of the node through peer memory (no NCCL launch)."""
+    global launch_count
+    A.require_device()
+    _cuda(sums)
+    if sums.dtype != torch.float64 or sums.numel() != 128:
+        raise TypeError('peer_allreduce_stats: 128 fp64 sums expected')
+    rc = A.load().nsg_peer_allreduce_stats(A.ptr(sums), C.byref(peer), A.stream_ptr())
+    A.check(rc, 'nsg_peer_allreduce_stats')
     launch_count += 1

@@ -129,8 +129,9 @@ def _launch(sync_bn):
 def test_two_ranks_syncbn_equal_single_gpu_on_global_batch():
     res = _launch(True)
     print(res)
-    # 20 BatchNorm statistic reductions + 2 gradient buckets (the loss scalars ride in the first) per step
-    assert res['n_coll'] == 22
+    # NCCL collectives per step: the 2 gradient buckets (the loss scalars ride in the first); the 20 BatchNorm statistic
+    # reductions go through peer memory inside the kernels (22 collectives when NSG_PEER_SYNC=0 / no peer access)
+    assert res['n_coll'] in (2, 22)
     assert res['loss'] < 2e-3
     assert res['running_mean'] < 2e-2   # second step's statistics see weights that took one sign-like Adam update
     assert res['params'] < 2e-2         # two bf16 Adam steps; differences come from reduction order only
