@@ -303,7 +303,8 @@ int nsg_colsum(const void* g, float* out, long long pixels, int channels, int dt
  *   codes   : [N,D] [dtype] = codebook[indices]                              (nullable)
  *   sqerr   : double[1] += sum (z - e)^2                                     (nullable)
  * mode 0 = exact fp32 CUDA-core search; 1 = tcgen05 split-bf16 tensor-core search with exact fp32 re-scoring of
- * the two best candidates (D == 64, K <= 8192).  mode 1 needs a caller-owned scratch buffer `ws` of
+ * the candidates (D in {64, 128, 256}; K <= 8192, 7168 at D = 256; fp32 z whose hi + lo tile images no longer fit in
+ * shared memory -- D = 256, or D = 128 with K > 7168 -- runs the exact CUDA-core search inside the same call).  mode 1 needs a caller-owned scratch buffer `ws` of
  * nsg_vq_workspace_bytes(k, d, 1) bytes (negative = shape not served by that mode); mode 0 needs none. */
 long long nsg_vq_workspace_bytes(int k, int d, int mode);
 int nsg_vq_forward(const void* z, const float* codebook, long long n, int k, int d, int dtype, int mode,

@@ -25,34 +25,39 @@ constexpr uint32_t VT_IMG_HALF = VT_N * 128;          // one 256-row bf16 K-majo
 constexpr uint32_t VT_CHUNK_BYTES = 2 * VT_IMG_HALF;  // hi + lo
 constexpr int VT_MAX_CHUNKS = 32;                     // K <= 8192
 
-// codebook fp32 (K,64) -> per chunk: swizzled bf16 hi image, swizzled bf16 lo image; |e|^2 (inf padded)
+// codebook fp32 (K, D = 64 * nd) -> per (chunk of 256 codewords, block of 64 dims): swizzled bf16 hi image, swizzled bf16
+// lo image (unit u = chunk * nd + dblock at image + u * VT_CHUNK_BYTES); |e|^2 over all D (inf padded)
 __global__ void __launch_bounds__(256)
-vq_prep_kernel(const float* __restrict__ cb, int K, uint8_t* __restrict__ image, float* __restrict__ esq_pad) {
+vq_prep_kernel(const float* __restrict__ cb, int K, int nd, uint8_t* __restrict__ image, float* __restrict__ esq_pad) {
   pdl_wait();
   pdl_trigger();
   const int gid = blockIdx.x * 256 + threadIdx.x;
   const int c = gid & 7, r = (gid >> 3) & 255, ch = gid >> 11;
   const int code = ch * VT_N + r;
-  float v[8];
-  if (code < K) {
-    const float4 a = __ldg(reinterpret_cast<const float4*>(cb + (long long)code * VT_D + c * 8));
-    const float4 b = __ldg(reinterpret_cast<const float4*>(cb + (long long)code * VT_D + c * 8 + 4));
-    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
-  } else {
+  const int D = nd * VT_D;
+  float sq = 0.f;
+  for (int db = 0; db < nd; ++db) {
+    float v[8];
+    if (code < K) {
+      const float4 a = __ldg(reinterpret_cast<const float4*>(cb + (long long)code * D + db * VT_D + c * 8));
+      const float4 b = __ldg(reinterpret_cast<const float4*>(cb + (long long)code * D + db * VT_D + c * 8 + 4));
+      v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+    } else {
 #pragma unroll
-    for (int i = 0; i < 8; ++i) v[i] = 0.f;
-  }
-  float hi[8], lo[8], sq = 0.f;
+      for (int i = 0; i < 8; ++i) v[i] = 0.f;
+    }
+    float hi[8], lo[8];
 #pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    split_bf16(v[i], hi[i], lo[i]);
-    sq = fmaf(v[i], v[i], sq);
+    for (int i = 0; i < 8; ++i) {
+      split_bf16(v[i], hi[i], lo[i]);
+      sq = fmaf(v[i], v[i], sq);
+    }
+    uint8_t* dst = image + (size_t)(ch * nd + db) * VT_CHUNK_BYTES + sw128_offset(r, c);
+    *reinterpret_cast<uint4*>(dst) =
+        make_uint4(pack_bf16(hi[0], hi[1]), pack_bf16(hi[2], hi[3]), pack_bf16(hi[4], hi[5]), pack_bf16(hi[6], hi[7]));
+    *reinterpret_cast<uint4*>(dst + VT_IMG_HALF) =
+        make_uint4(pack_bf16(lo[0], lo[1]), pack_bf16(lo[2], lo[3]), pack_bf16(lo[4], lo[5]), pack_bf16(lo[6], lo[7]));
   }
-  uint8_t* dst = image + (size_t)ch * VT_CHUNK_BYTES + sw128_offset(r, c);
-  *reinterpret_cast<uint4*>(dst) =
-      make_uint4(pack_bf16(hi[0], hi[1]), pack_bf16(hi[2], hi[3]), pack_bf16(hi[4], hi[5]), pack_bf16(hi[6], hi[7]));
-  *reinterpret_cast<uint4*>(dst + VT_IMG_HALF) =
-      make_uint4(pack_bf16(lo[0], lo[1]), pack_bf16(lo[2], lo[3]), pack_bf16(lo[4], lo[5]), pack_bf16(lo[6], lo[7]));
   sq += __shfl_xor_sync(0xffffffffu, sq, 4);
   sq += __shfl_xor_sync(0xffffffffu, sq, 2);
   sq += __shfl_xor_sync(0xffffffffu, sq, 1);
@@ -106,18 +111,24 @@ __device__ __forceinline__ void load8<__nv_bfloat16>(const __nv_bfloat16* p, flo
   }
 }
 
-template <typename T>
+// Streaming search, D = 64 * ND (ND = 1, 2, 4): the codebook streams through the two 64 KB buffers in units of
+// (256 codewords, 64 dims) and the ND units of a chunk accumulate into the same 256-column TMEM accumulator, so the
+// pipeline and the epilogue are those of D = 64; only the z tile (ND K-blocks of 16 KB per image) and the exact
+// re-score / gather (D dims per row) grow.
+template <typename T, int ND>
 __global__ void __launch_bounds__(288, 1)
 vq_search_tc_kernel(const T* __restrict__ z, const float* __restrict__ cb, const uint8_t* __restrict__ image,
                     const float* __restrict__ esq_pad, long long N, int K, int nchunks,
                     long long* __restrict__ indices, T* __restrict__ codes, double* __restrict__ sqerr) {
   constexpr bool kSplitZ = sizeof(T) == 4;   // bf16 activations have no low part
+  constexpr int D = ND * VT_D;
+  constexpr uint32_t A_IMG = ND * 16384;     // one image of the z tile: ND K-blocks of 128 rows x 64 bf16
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sm = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* A_hi = sm;
-  uint8_t* A_lo = sm + 16384;
-  uint8_t* Bbuf = sm + 32768;                                   // 2 x 64 KB
-  float* esq_s = reinterpret_cast<float*>(sm + 32768 + 2 * VT_CHUNK_BYTES);
+  uint8_t* A_lo = sm + A_IMG;                                   // (fp32 z only)
+  uint8_t* Bbuf = sm + (kSplitZ ? 2 : 1) * A_IMG;               // 2 x 64 KB
+  float* esq_s = reinterpret_cast<float*>(Bbuf + 2 * VT_CHUNK_BYTES);
   uint8_t* tail = reinterpret_cast<uint8_t*>(esq_s + nchunks * VT_N);
   float* sCD = reinterpret_cast<float*>(tail);                  // [2][128][2]
   int* sCI = reinterpret_cast<int*>(tail + 2048);               // [2][128][2]
@@ -143,28 +154,31 @@ vq_search_tc_kernel(const T* __restrict__ z, const float* __restrict__ cb, const
   }
   if (warp == 8) tmem_alloc<512>(tmem_slot);
   if (tid < 256) {
-    // stage the z tile: thread = (row, half); 4 x 16-byte chunks of bf16 hi (and lo)
+    // stage the z tile: thread = (row, half); per 64-dim block 4 x 16-byte chunks of bf16 hi (and lo)
     const int row = tid >> 1, half = tid & 1;
     const long long grow = row0 + row;
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const int c = half * 4 + j;
-      float v[8];
-      if (grow < N) {
-        load8<T>(z + grow * VT_D + c * 8, v);
-      } else {
+    for (int db = 0; db < ND; ++db) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) v[i] = 0.f;
+      for (int j = 0; j < 4; ++j) {
+        const int c = half * 4 + j;
+        float v[8];
+        if (grow < N) {
+          load8<T>(z + grow * D + db * VT_D + c * 8, v);
+        } else {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) v[i] = 0.f;
+        }
+        float hi[8], lo[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) split_bf16(v[i], hi[i], lo[i]);
+        const uint32_t off = (uint32_t)db * 16384 + sw128_offset(row, c);
+        *reinterpret_cast<uint4*>(A_hi + off) = make_uint4(pack_bf16(hi[0], hi[1]), pack_bf16(hi[2], hi[3]),
+                                                           pack_bf16(hi[4], hi[5]), pack_bf16(hi[6], hi[7]));
+        if (kSplitZ)
+          *reinterpret_cast<uint4*>(A_lo + off) = make_uint4(pack_bf16(lo[0], lo[1]), pack_bf16(lo[2], lo[3]),
+                                                             pack_bf16(lo[4], lo[5]), pack_bf16(lo[6], lo[7]));
       }
-      float hi[8], lo[8];
-#pragma unroll
-      for (int i = 0; i < 8; ++i) split_bf16(v[i], hi[i], lo[i]);
-      const uint32_t off = sw128_offset(row, c);
-      *reinterpret_cast<uint4*>(A_hi + off) = make_uint4(pack_bf16(hi[0], hi[1]), pack_bf16(hi[2], hi[3]),
-                                                         pack_bf16(hi[4], hi[5]), pack_bf16(hi[6], hi[7]));
-      if (kSplitZ)
-        *reinterpret_cast<uint4*>(A_lo + off) = make_uint4(pack_bf16(lo[0], lo[1]), pack_bf16(lo[2], lo[3]),
-                                                           pack_bf16(lo[4], lo[5]), pack_bf16(lo[6], lo[7]));
     }
     for (int i = tid; i < nchunks * VT_N; i += 256) esq_s[i] = __ldg(esq_pad + i);
     fence_proxy_async_smem();
@@ -176,39 +190,42 @@ vq_search_tc_kernel(const T* __restrict__ z, const float* __restrict__ cb, const
 
   if (warp == 8) {
     if (lane == 0) {
-      // ---------------- producer + MMA issuer
+      // ---------------- producer + MMA issuer: unit u = chunk * ND + dblock streams through buffer u & 1
       const uint32_t idesc = idesc_bf16(VT_M, VT_N);
-      const uint64_t a_hi = sw128_desc(smem_u32(A_hi)), a_lo = sw128_desc(smem_u32(A_lo));
-      auto load_chunk = [&](int c) {
-        const int b = c & 1;
+      const int nunits = nchunks * ND;
+      auto load_unit = [&](int u) {
+        const int b = u & 1;
         mbar_arrive_expect_tx(&b_full[b], VT_CHUNK_BYTES);
-        bulk_g2s(Bbuf + (size_t)b * VT_CHUNK_BYTES, image + (size_t)c * VT_CHUNK_BYTES, VT_CHUNK_BYTES, &b_full[b]);
+        bulk_g2s(Bbuf + (size_t)b * VT_CHUNK_BYTES, image + (size_t)u * VT_CHUNK_BYTES, VT_CHUNK_BYTES, &b_full[b]);
       };
-      load_chunk(0);
-      if (nchunks > 1) load_chunk(1);
-      for (int c = 0; c < nchunks; ++c) {
-        const int b = c & 1;
-        const uint32_t ph = (c >> 1) & 1;
-        mbar_wait(&b_full[b], ph);
-        if (c >= 2) mbar_wait(&acc_empty[b], ph ^ 1);
+      load_unit(0);
+      if (nunits > 1) load_unit(1);
+      for (int u = 0; u < nunits; ++u) {
+        const int b = u & 1;
+        const int c = u / ND, db = u - c * ND;
+        const int ab = c & 1;                               // accumulator of this chunk
+        mbar_wait(&b_full[b], (uint32_t)((u >> 1) & 1));
+        if (db == 0 && c >= 2) mbar_wait(&acc_empty[ab], (uint32_t)(((c >> 1) & 1) ^ 1));
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + (uint32_t)b * VT_N;
+        const uint32_t d_tmem = tmem_base + (uint32_t)ab * VT_N;
+        const uint64_t a_hi = sw128_desc(smem_u32(A_hi + (size_t)db * 16384));
+        const uint64_t a_lo = sw128_desc(smem_u32(A_lo + (size_t)db * 16384));
         const uint64_t b_hi = sw128_desc(smem_u32(Bbuf + (size_t)b * VT_CHUNK_BYTES));
         const uint64_t b_lo = sw128_desc(smem_u32(Bbuf + (size_t)b * VT_CHUNK_BYTES + VT_IMG_HALF));
 #pragma unroll
-        for (int ks = 0; ks < VT_D / 16; ++ks) umma_bf16(d_tmem, a_hi + 2 * ks, b_hi + 2 * ks, idesc, ks > 0);
+        for (int ks = 0; ks < VT_D / 16; ++ks) umma_bf16(d_tmem, a_hi + 2 * ks, b_hi + 2 * ks, idesc, (db > 0 || ks > 0) ? 1u : 0u);
 #pragma unroll
         for (int ks = 0; ks < VT_D / 16; ++ks) umma_bf16(d_tmem, a_hi + 2 * ks, b_lo + 2 * ks, idesc, 1);
         if (kSplitZ) {
 #pragma unroll
           for (int ks = 0; ks < VT_D / 16; ++ks) umma_bf16(d_tmem, a_lo + 2 * ks, b_hi + 2 * ks, idesc, 1);
         }
-        umma_commit(&acc_full[b]);
+        if (db == ND - 1) umma_commit(&acc_full[ab]);
         umma_commit(&b_empty[b]);
-        if (c >= 1 && c + 1 < nchunks) {      // refill the buffer chunk c-1 used, now that its MMAs retired
-          const int pb = (c - 1) & 1;
-          mbar_wait(&b_empty[pb], ((c - 1) >> 1) & 1);
-          load_chunk(c + 1);
+        if (u >= 1 && u + 1 < nunits) {       // refill the buffer unit u-1 used, now that its MMAs retired
+          const int pb = (u - 1) & 1;
+          mbar_wait(&b_empty[pb], (uint32_t)(((u - 1) >> 1) & 1));
+          load_unit(u + 1);
         }
       }
     }
@@ -250,7 +267,7 @@ vq_search_tc_kernel(const T* __restrict__ z, const float* __restrict__ cb, const
     sCD[(g * VT_M + row) * 2 + 1] = t2.d2; sCI[(g * VT_M + row) * 2 + 1] = t2.i2;
     asm volatile("bar.sync 1, 256;" ::: "memory");
 
-    // ---------------- exact fp32 re-score of the two best candidates: 8 lanes per row
+    // ---------------- exact fp32 re-score of the two best candidates: 8 lanes per row, D / 8 dims per lane
     const int sub = tid & 7;
 #pragma unroll 1
     for (int pass = 0; pass < 4; ++pass) {
@@ -264,20 +281,23 @@ vq_search_tc_kernel(const T* __restrict__ z, const float* __restrict__ cb, const
         for (int s = 0; s < 2; ++s) m.push_any(sCD[(gg * VT_M + rr) * 2 + s], sCI[(gg * VT_M + rr) * 2 + s]);
       float p1 = 0.f, p2 = 0.f;
       if (grow < N && m.i1 >= 0) {
-        float zv[8], ev[8];
-        load8<T>(z + grow * VT_D + sub * 8, zv);
-        load8<float>(cb + (long long)m.i1 * VT_D + sub * 8, ev);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const float df = zv[i] - ev[i];
-          p1 = fmaf(df, df, p1);
-        }
-        if (m.i2 >= 0) {
-          load8<float>(cb + (long long)m.i2 * VT_D + sub * 8, ev);
+        for (int db = 0; db < ND; ++db) {
+          float zv[8], ev[8];
+          load8<T>(z + grow * D + db * VT_D + sub * 8, zv);
+          load8<float>(cb + (long long)m.i1 * D + db * VT_D + sub * 8, ev);
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
             const float df = zv[i] - ev[i];
-            p2 = fmaf(df, df, p2);
+            p1 = fmaf(df, df, p1);
+          }
+          if (m.i2 >= 0) {
+            load8<float>(cb + (long long)m.i2 * D + db * VT_D + sub * 8, ev);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const float df = zv[i] - ev[i];
+              p2 = fmaf(df, df, p2);
+            }
           }
         }
       }
@@ -307,12 +327,12 @@ vq_search_tc_kernel(const T* __restrict__ z, const float* __restrict__ cb, const
       }
     }
     if (codes) {
-      for (int i = tid; i < VT_M * (VT_D / 4); i += 256) {
-        const int rr = i >> 4, c4 = i & 15;
+      for (int i = tid; i < VT_M * (D / 4); i += 256) {
+        const int rr = i / (D / 4), c4 = i % (D / 4);
         const long long grow = row0 + rr;
         if (grow < N) {
-          const float4 v = __ldg(reinterpret_cast<const float4*>(cb + (long long)sWin[rr] * VT_D + c4 * 4));
-          Act<T>::st4(codes + grow * VT_D + c4 * 4, v);
+          const float4 v = __ldg(reinterpret_cast<const float4*>(cb + (long long)sWin[rr] * D + c4 * 4));
+          Act<T>::st4(codes + grow * D + c4 * 4, v);
         }
       }
     }
@@ -814,44 +834,67 @@ static size_t vq_res_smem_bytes(int nchunks) {
   return 1024 + (size_t)nchunks * VT_CHUNK_BYTES + 2 * 32768 + (size_t)nchunks * VT_N * 4 + 10752;
 }
 
-static size_t vq_tc_smem_bytes(int nchunks) {
-  return 1024 + 32768 + 2 * (size_t)VT_CHUNK_BYTES + (size_t)nchunks * VT_N * 4 + 5376;
+// dynamic shared memory of the streaming kernel: z tile images (hi, + lo for fp32 z), two codebook units, |e|^2, tail
+static size_t vq_tc_smem_bytes(int nchunks, int nd, bool split_z) {
+  return 1024 + (size_t)(split_z ? 2 : 1) * nd * 16384 + 2 * (size_t)VT_CHUNK_BYTES + (size_t)nchunks * VT_N * 4 + 5376;
 }
+constexpr size_t VT_SMEM_MAX = 227 * 1024;
 
 int g_vq_resident = 1;     // development switch (nsg_vq_resident): 0 = always the streaming kernel
 
+// D = 64, 128 or 256 and as many codewords as the kernel's shared memory holds |e|^2 for beside a bf16 z tile
+// (K <= 8192 at D = 64 / 128, 7168 at D = 256).  fp32 z needs a second z image: where that no longer fits (D = 256, or
+// D = 128 with K > 7168) vq_forward_tc runs the exact CUDA-core search instead -- same indices, no tensor cores.
 long long vq_tc_workspace_bytes(int k, int d) {
-  if (d != VT_D || k < 1 || k > VT_MAX_CHUNKS * VT_N) return -1;
+  if ((d != 64 && d != 128 && d != 256) || k < 1 || k > VT_MAX_CHUNKS * VT_N) return -1;
   const long long nchunks = (k + VT_N - 1) / VT_N;
-  return nchunks * (long long)VT_CHUNK_BYTES + nchunks * VT_N * 4;
+  const int nd = d / VT_D;
+  if (vq_tc_smem_bytes((int)nchunks, nd, false) > VT_SMEM_MAX) return -1;
+  return nchunks * nd * (long long)VT_CHUNK_BYTES + nchunks * VT_N * 4;
+}
+
+int vq_forward_simt(const void* z, const float* codebook, long long n, int k, int d, int dtype, long long* indices,
+                    void* codes, double* sqerr, cudaStream_t stream);
+
+template <typename T, int ND>
+static int launch_vq_tc(unsigned grid, size_t smem, cudaStream_t stream, const void* z, const float* codebook,
+                        const uint8_t* image, const float* esq_pad, long long n, int k, int nchunks, long long* indices,
+                        void* codes, double* sqerr) {
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(vq_search_tc_kernel<T, ND>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)VT_SMEM_MAX);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(vq_search_tc_kernel)");
+    configured = true;
+  }
+  vq_search_tc_kernel<T, ND><<<grid, 288, smem, stream>>>((const T*)z, codebook, image, esq_pad, n, k, nchunks, indices,
+                                                          (T*)codes, sqerr);
+  NSG_CHECK_LAUNCH("vq_search_tc_kernel");
+  return NSG_OK;
 }
 
 int vq_forward_tc(const void* z, const float* codebook, long long n, int k, int d, int dtype, long long* indices,
                   void* codes, double* sqerr, void* ws, long long ws_bytes, cudaStream_t stream) {
   const long long need = vq_tc_workspace_bytes(k, d);
   if (need < 0) {
-    set_error("vq_forward(mode=1): tensor-core search supports D == 64 and K <= %d (got K=%d, D=%d)",
-              VT_MAX_CHUNKS * VT_N, k, d);
+    set_error("vq_forward(mode=1): tensor-core search supports D in {64, 128, 256} and K <= %d (7168 at D = 256) "
+              "(got K=%d, D=%d)", VT_MAX_CHUNKS * VT_N, k, d);
     return NSG_E_UNSUPPORTED;
   }
   NSG_REQUIRE(ws && ws_bytes >= need, "vq_forward(mode=1): workspace of %lld bytes required (got %lld)", need, ws_bytes);
   NSG_REQUIRE((reinterpret_cast<uintptr_t>(ws) & 15) == 0, "vq_forward(mode=1): workspace must be 16-byte aligned");
   const int nchunks = (k + VT_N - 1) / VT_N;
+  const int nd = d / VT_D;
+  const size_t smem = vq_tc_smem_bytes(nchunks, nd, dtype == NSG_F32);
+  if (smem > VT_SMEM_MAX)      // fp32 z whose hi + lo images do not fit: the exact CUDA-core search (see above)
+    return vq_forward_simt(z, codebook, n, k, d, dtype, indices, codes, sqerr, stream);
   uint8_t* image = static_cast<uint8_t*>(ws);
-  float* esq_pad = reinterpret_cast<float*>(image + (size_t)nchunks * VT_CHUNK_BYTES);
-  launch_pdl(vq_prep_kernel, dim3(nchunks * 8), dim3(256), 0, stream, codebook, k, image, esq_pad);
+  float* esq_pad = reinterpret_cast<float*>(image + (size_t)nchunks * nd * VT_CHUNK_BYTES);
+  launch_pdl(vq_prep_kernel, dim3(nchunks * 8), dim3(256), 0, stream, codebook, k, nd, image, esq_pad);
   NSG_CHECK_LAUNCH("vq_prep_kernel");
-  const size_t smem = vq_tc_smem_bytes(nchunks);
   return NSG_DISPATCH_DTYPE(dtype, [&]() -> int {
-    static bool configured = false;
-    if (!configured) {
-      cudaError_t e = cudaFuncSetAttribute(vq_search_tc_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                           (int)vq_tc_smem_bytes(VT_MAX_CHUNKS));
-      if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(vq_search_tc_kernel)");
-      configured = true;
-    }
     const unsigned grid = (unsigned)((n + VT_M - 1) / VT_M);
-    if (nchunks <= 2 && g_vq_resident) {      // K <= 512: persistent CTAs with the codebook resident in shared memory
+    if (nd == 1 && nchunks <= 2 && g_vq_resident) {      // D = 64, K <= 512: persistent CTAs, codebook resident in shared memory
       static bool configured_res = false;
       if (!configured_res) {
         cudaError_t e = cudaFuncSetAttribute(vq_search_res_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -872,10 +915,9 @@ int vq_forward_tc(const void* z, const float* codebook, long long n, int k, int 
       NSG_CHECK_LAUNCH("vq_search_res_kernel");
       return NSG_OK;
     }
-    vq_search_tc_kernel<T><<<grid, 288, smem, stream>>>((const T*)z, codebook, image, esq_pad, n, k, nchunks,
-                                                        indices, (T*)codes, sqerr);
-    NSG_CHECK_LAUNCH("vq_search_tc_kernel");
-    return NSG_OK;
+    if (nd == 1) return launch_vq_tc<T, 1>(grid, smem, stream, z, codebook, image, esq_pad, n, k, nchunks, indices, codes, sqerr);
+    if (nd == 2) return launch_vq_tc<T, 2>(grid, smem, stream, z, codebook, image, esq_pad, n, k, nchunks, indices, codes, sqerr);
+    return launch_vq_tc<T, 4>(grid, smem, stream, z, codebook, image, esq_pad, n, k, nchunks, indices, codes, sqerr);
   });
 }
 

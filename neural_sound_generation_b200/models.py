@@ -194,7 +194,7 @@ class VQVAE(nn.Module):
         self.input_dim, self.dim, self.z_dim = input_dim, dim, z_dim
         # execution options (not part of the reference API).  None = automatic: the production engine -- bf16
         # operand-ready activations, TMA-fed tcgen05 convolutions (conv_impl 2), tcgen05 split-bf16 search (vq_mode 1)
-        # -- wherever the shape is served (dim == 64; search: D == 64, K <= 8192), the general fp32 kernels otherwise.
+        # -- wherever the shape is served (dim == 64; search: D in {64, 128, 256}, K <= 8192), the general fp32 kernels otherwise.
         # ``set_precision('fp32')`` pins the fp32 parity engine; explicit values always win.
         self._act_dtype = None              # torch.float32 / torch.bfloat16
         self._conv_impl = None              # 0 = CUDA-core fp32, 1 = register-staged tcgen05, 2 = TMA-fed tcgen05 (bf16)
