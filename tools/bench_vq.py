@@ -37,6 +37,7 @@ def main():
     cases = [(2048, 512, 64), (40960, 512, 64), (1 << 20, 512, 64)]
     if full:
         cases += [(1 << 20, k, 64) for k in (1024, 2048, 4096, 8192)]
+        cases += [(1 << 20, k, d) for d in (128, 256) for k in (512, 4096)]      # configs[3]: D = 64-256
     for n, k, d in cases:
         for dt in (torch.bfloat16, torch.float32):
             z = torch.randn(n, d, device=DEV).to(dt)
