@@ -363,6 +363,48 @@ int nsg_tanh_bwd(const float* g, const float* y, float* out, long long n, void* 
 int nsg_mel_collate(const float* frames, const int* offsets, int batch, int n_mels, int t_out, float* out_f32,
                     void* out_bf16, void* stream);
 
+/* ---------------------------------------------------------------- mel <-> audio (audio_tacotron.py) */
+/* All fp32, frame-major device buffers: a spectrum is [n_frames][n_fft/2 + 1] (complex64 = interleaved re, im), a mel
+ * spectrogram handed OUT is [n_frames][n_mels]; a mel spectrogram handed IN (nsg_mel_to_linear) keeps the layout the
+ * reference passes around, (n_mels, n_frames) row-major (main.py:152-181).  n_fft: a power of two in [16, 4096]. */
+
+/* librosa.stft(y, n_fft, hop) as audio_tacotron.py:154-158 calls it: centred frames over the reflect-padded signal,
+ * periodic Hann window, n_frames = 1 + n_samples / hop.  preemph != 0: the transform of lfilter([1, -preemph], [1], y)
+ * (audio_tacotron.py:22-25) without materialising it.  spec: [n_frames][n_fft/2 + 1][2]. */
+int nsg_stft(const float* y, long long n_samples, int n_fft, int hop, float preemph, float* spec, void* stream);
+
+/* audio_tacotron.py:70-78 melspectrogram with the signal-normalisation branch the reference's hparams select
+ * (allow_clipping_in_normalization, not symmetric): pre-emphasis, STFT, |.|, basis_t ([n_fft/2 + 1][n_mels] =
+ * librosa.filters.mel transposed), 20 log10(max(10^(min_level_db/20), .)) - ref_level_db, scaled into [0, max_abs] and
+ * clipped.  mel: [n_frames][n_mels]. */
+int nsg_melspectrogram(const float* wav, long long n_samples, int n_fft, int hop, float preemph, const float* basis_t,
+                       int n_mels, float min_level_db, float ref_level_db, float max_abs, float* mel, void* stream);
+
+/* librosa.istft(D, hop) as audio_tacotron.py:160-161 calls it: irfft, synthesis window, overlap-add, division by the
+ * window sum-of-squares envelope (where > tiny(float32)), n_fft/2 trimmed at both ends -> hop * (n_frames - 1) samples.
+ * workspace: nsg_istft_workspace_bytes(n_frames, n_fft) bytes, caller-owned. */
+long long nsg_istft_workspace_bytes(int n_frames, int n_fft);
+int nsg_istft(const float* spec, int n_frames, int n_fft, int hop, void* workspace, float* y, void* stream);
+
+/* audio_tacotron.py:142-152 _griffin_lim: y = istft(mag * exp(2 pi i angles0)); `iters` times { angles =
+ * exp(1j * angle(stft(y))); y = istft(mag * angles) }.  mag: [n_frames][n_fft/2 + 1] target magnitudes (the reference
+ * passes S ** power); angles0: same shape, the np.random.rand(*S.shape) of :146 (fractions of a turn) -- explicit so
+ * that a caller (and the parity tests) own the randomness.  ONE launch: a persistent grid of <= one CTA per SM with a
+ * grid barrier per iteration (launched with the device's greatest priority, see "Launch policy" in INTEGRATION.md).
+ * workspace: nsg_griffin_lim_workspace_bytes() bytes, 256-byte aligned, caller-owned.  y: hop * (n_frames - 1). */
+long long nsg_griffin_lim_workspace_bytes(int n_frames, int n_fft);
+int nsg_griffin_lim(const float* mag, const float* angles0, int n_frames, int n_fft, int hop, int iters, void* workspace,
+                    float* y, void* stream);
+
+/* audio_tacotron.py:101-107 + the `** hparams.power` of :115: mag[t][k] = max(1e-10, sum_m inv_basis_t[m][k] *
+ * 10^((clip(mel[m][t], 0, max_abs) * -min_level_db / max_abs + min_level_db + ref_level_db) / 20)) ^ power.
+ * mel: (n_mels, n_frames) row-major; inv_basis_t: [n_mels][n_bins] = pinv(mel basis) transposed. */
+int nsg_mel_to_linear(const float* mel, int n_mels, int n_frames, const float* inv_basis_t, int n_bins,
+                      float min_level_db, float ref_level_db, float max_abs, float power, float* mag, void* stream);
+
+/* scipy.signal.lfilter([1], [1, -k], x) (audio_tacotron.py:27-30): y[i] = x[i] + k y[i-1]; x and y must not overlap */
+int nsg_inv_preemphasis(const float* x, long long n_samples, float k, float* y, void* stream);
+
 /* ---------------------------------------------------------------- optimiser (torch.optim.Adam, main.py:124) */
 /* one Adam step over a flat fp32 buffer.  step_count is a device scalar incremented AFTER use (graphs replay
  * correctly): by the last block of the same launch when `ticket` (one zero-initialised unsigned counter owned by this

@@ -17,3 +17,4 @@ from . import dist  # noqa: F401  (DataParallelStep: batch-sharded data parallel
 VectorQuantizer = VQEmbedding   # alias for the name BASELINE.json's north_star uses
 __version__ = '0.1'
 from . import data  # noqa: F401  (device-side mel batch assembly: MelNpyDataset, DeviceMelLoader)
+from . import audio  # noqa: F401  (mel <-> audio: STFT / ISTFT / Griffin-Lim kernels, audio_tacotron.py names)

@@ -27,6 +27,8 @@ EXPORTS = [
     'nsg_bn_act64', 'nsg_bn_bwd64', 'nsg_relu64', 'nsg_vq_bwd_stats64', 'nsg_debug_timeline',
     'nsg_c1_conv_tc', 'nsg_c1_convT_tc', 'nsg_c1_wgrad_tc', 'nsg_scatter_mode', 'nsg_ema_update', 'nsg_vq_resident',
     'nsg_conv_bn_tma', 'nsg_conv_bn_tma_fits', 'nsg_c1_conv_bn_tc', 'nsg_mel_collate', 'nsg_peer_allreduce_stats',
+    'nsg_stft', 'nsg_melspectrogram', 'nsg_istft', 'nsg_istft_workspace_bytes', 'nsg_griffin_lim',
+    'nsg_griffin_lim_workspace_bytes', 'nsg_mel_to_linear', 'nsg_inv_preemphasis',
 ]
 
 
@@ -131,11 +133,20 @@ def load():
     lib.nsg_tanh_bwd.argtypes = [vp, vp, vp, ll, vp]
     lib.nsg_mel_collate.argtypes = [vp, vp, i, i, i, vp, vp, vp]
     lib.nsg_peer_allreduce_stats.argtypes = [vp, C.POINTER(PeerSync), vp]
+    lib.nsg_stft.argtypes = [vp, ll, i, i, f, vp, vp]
+    lib.nsg_melspectrogram.argtypes = [vp, ll, i, i, f, vp, i, f, f, f, vp, vp]
+    lib.nsg_istft_workspace_bytes.argtypes = [i, i]
+    lib.nsg_istft.argtypes = [vp, i, i, i, vp, vp, vp]
+    lib.nsg_griffin_lim_workspace_bytes.argtypes = [i, i]
+    lib.nsg_griffin_lim.argtypes = [vp, vp, i, i, i, i, vp, vp, vp]
+    lib.nsg_mel_to_linear.argtypes = [vp, i, i, vp, i, f, f, f, f, vp, vp]
+    lib.nsg_inv_preemphasis.argtypes = [vp, ll, f, vp, vp]
     lib.nsg_adam_step.argtypes = [vp, vp, vp, vp, ll, f, f, f, f, f, vp, i, vp, vp]
     for name in EXPORTS:
         fn = getattr(lib, name)
         if name not in ('nsg_version', 'nsg_last_error'):
-            fn.restype = ll if name in ('nsg_vq_workspace_bytes', 'nsg_conv_pack_bytes') else i
+            fn.restype = ll if name in ('nsg_vq_workspace_bytes', 'nsg_conv_pack_bytes', 'nsg_istft_workspace_bytes',
+                                        'nsg_griffin_lim_workspace_bytes') else i
     if os.environ.get('NSG_SCATTER_MODE') in ('0', '1'):      # development aid, see include/nsg_b200.h
         lib.nsg_scatter_mode(int(os.environ['NSG_SCATTER_MODE']))
     _lib = lib

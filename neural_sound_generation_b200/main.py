@@ -16,9 +16,10 @@ Data (main.py:77-99):
 
 What is NOT here, and why (SURVEY.md section 8f ranks them after this row):
   * the VAE / PixelCNN models (``--model vae``: refused -- not on the hot path);
-  * Griffin-Lim audio of the sample (main.py:164-197, N3): skipped with a message.  For image datasets the whole
-    per-epoch sample block is skipped: the reference's own block unpacks 5-tuples (main.py:138-139) and cannot run on
-    ``(data, label)`` loaders.
+  * for image datasets the whole per-epoch sample block is skipped: the reference's own block unpacks 5-tuples
+    (main.py:138-139) and cannot run on ``(data, label)`` loaders.
+The Griffin-Lim audio of the per-epoch sample (main.py:164-197, row N3) runs on the device (``audio.py``) and is written
+next to the ``.npy`` dump under the reference's file name.
 
     python -m neural_sound_generation_b200.main --model vqvae --dataset ljspeech --dim 64 --z-dim 512 \
         --synthetic-batches 100 --epochs 1
@@ -29,6 +30,7 @@ import os
 import numpy as np
 import torch
 
+from . import audio
 from .models import VQVAE
 from .optim import Adam
 from .train import train_vqvae
@@ -84,6 +86,14 @@ def sample_path(args, epoch):
     return os.path.join(args.sampledir, format(args.dataset),
                         'reconstruction_' + str(args.model) + '_data_' + str(args.dataset) + '_dim_' + str(args.dim)
                         + '_z_dim_' + str(args.z_dim) + '_epoch_' + str(epoch) + '.npy')
+
+
+def audio_path(args, epoch, fft_size, hop_size):
+    """main.py:183-191"""
+    return os.path.join(args.sampledir, format(args.dataset),
+                        'audio_recon_' + str(args.model) + '_data_' + str(args.dataset) + '_dim_' + str(args.dim)
+                        + '_z_dim_' + str(args.z_dim) + '_epoch_' + str(epoch) + '_fftsize_' + str(fft_size)
+                        + '_hopsize_' + str(hop_size) + '.wav')
 
 
 class SyntheticMelLoader(object):
@@ -214,7 +224,15 @@ def main(argv=None):
                 path = sample_path(args, epoch)
                 os.makedirs(os.path.dirname(path), exist_ok=True)
                 np.save(path, reconstruction, allow_pickle=True)
-                print('audio reconstruction (Griffin-Lim, main.py:164-197) is not part of this build: skipped')
+                # main.py:164-197: Griffin-Lim audio of the sample, on the device (audio.py / csrc/audio.cu, row N3).
+                # As in the reference, the concatenation of the batch is only printed; the waveform is made from the
+                # loop variable, i.e. the LAST item of the batch (main.py:168-181).
+                print("Trying audio reconstruction on test set..")
+                print((reconstruction.shape[1], reconstruction.shape[0] * reconstruction.shape[2]))
+                sampling_rate, fft_size, hop_size, n_mels = 22050, 1024, 256, 80
+                assert reconstruction.shape[1] == n_mels
+                signal = audio.inv_mel_spectrogram(reconstruction[-1], sampling_rate, fft_size, hop_size, n_mels)
+                audio.save_wav(signal, audio_path(args, epoch, fft_size, hop_size))
             last_epoch = epoch
             save_checkpoint(args, state())
     except KeyboardInterrupt:

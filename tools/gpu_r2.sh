@@ -7,7 +7,7 @@ nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm --format=csv > gpurun_out/${
 : > gpurun_out/${TAG}_pytest.log
 for f in tests/test_gpu_tma.py tests/test_gpu_ops.py tests/test_gpu_tma_model.py tests/test_gpu_model.py tests/test_gpu_main.py tests/test_gpu_data.py tests/test_gpu_images.py tests/test_gpu_dist.py; do
   echo "=== $f" >> gpurun_out/${TAG}_pytest.log
-  timeout 900 python -m pytest $f -m gpu -q -p no:cacheprovider --timeout 600 -s >> gpurun_out/${TAG}_pytest.log 2>&1
+  timeout 600 python -m pytest $f -m gpu -q -p no:cacheprovider --timeout 300 -s >> gpurun_out/${TAG}_pytest.log 2>&1
   echo "pytest $f exit $?"
 done
 grep -E "^(FAILED|ERROR)|passed|failed|=== " gpurun_out/${TAG}_pytest.log | cut -c1-300
