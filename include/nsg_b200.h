@@ -51,8 +51,15 @@ extern "C" {
 
 const char* nsg_version(void);
 const char* nsg_last_error(void);
-/* 1 when the current device is sm_100 (B200); fills name (<= 127 chars) when not null. */
+/* 1 when the current device is sm_100 (B200); fills name (<= 127 chars) when not null.  Also the library's one-time
+ * set-up (the pinned report words below): call it once per process and device before the first launch. */
 int nsg_device_ok(char* name, int name_len);
+/* Every wait inside the tensor-core kernels (mbarrier, grid barrier, peer flags) is bounded: after ~2 s without
+ * progress the waiting thread records where it was stuck in pinned host memory and traps, so a lost pipeline stage
+ * surfaces as a CUDA launch failure with a location instead of a hung device.  out: 8 words -- out[0] != 0 when a
+ * report is present; out[1] translation unit (1 conv_tc.cu, 2 conv_tma.cu, 3 vq_tc.cu), out[2] source line, out[3]
+ * block (x | y << 20), out[4] thread, out[5] barrier parity / counter value, out[6] grid size.  clear != 0 resets. */
+int nsg_hang_report(unsigned int* out, int clear);
 
 /* ---------------------------------------------------------------- convolution (models.py:150,153,165,168,179,182)
  * One implicit-GEMM-over-taps entry point serves nn.Conv2d forward, nn.ConvTranspose2d forward and both
@@ -122,7 +129,7 @@ typedef struct {
  * its 128 fp64 statistics over the ranks through those areas (direct NVLink stores + flags, ranks added in rank order:
  * identical bits everywhere) -- no collective launch.  `slot` selects one of NSG_PEER_SLOTS exchange slots; a slot may
  * be used once between two points at which all ranks synchronise (the step's gradient all-reduce), by the same launch
- * on every rank.  A rank that never arrives traps the waiting kernels after ~1 s instead of hanging the device. */
+ * on every rank.  A rank that never arrives traps the waiting kernels after ~40 s instead of hanging the device. */
 #define NSG_PEER_MAX 8
 #define NSG_PEER_SLOTS 32
 #define NSG_PEER_AREA_BYTES (NSG_PEER_SLOTS * NSG_PEER_MAX * 128 * 8 + NSG_PEER_SLOTS * NSG_PEER_MAX * 4)

@@ -27,7 +27,7 @@ EXPORTS = [
     'nsg_bn_act64', 'nsg_bn_bwd64', 'nsg_relu64', 'nsg_vq_bwd_stats64', 'nsg_debug_timeline',
     'nsg_c1_conv_tc', 'nsg_c1_convT_tc', 'nsg_c1_wgrad_tc', 'nsg_scatter_mode', 'nsg_ema_update', 'nsg_vq_resident',
     'nsg_conv_bn_tma', 'nsg_conv_bn_tma_fits', 'nsg_c1_conv_bn_tc', 'nsg_mel_collate', 'nsg_peer_allreduce_stats',
-    'nsg_stft', 'nsg_melspectrogram', 'nsg_istft', 'nsg_istft_workspace_bytes', 'nsg_griffin_lim',
+    'nsg_hang_report', 'nsg_stft', 'nsg_melspectrogram', 'nsg_istft', 'nsg_istft_workspace_bytes', 'nsg_griffin_lim',
     'nsg_griffin_lim_workspace_bytes', 'nsg_mel_to_linear', 'nsg_inv_preemphasis',
 ]
 
@@ -133,6 +133,7 @@ def load():
     lib.nsg_tanh_bwd.argtypes = [vp, vp, vp, ll, vp]
     lib.nsg_mel_collate.argtypes = [vp, vp, i, i, i, vp, vp, vp]
     lib.nsg_peer_allreduce_stats.argtypes = [vp, C.POINTER(PeerSync), vp]
+    lib.nsg_hang_report.argtypes = [vp, i]
     lib.nsg_stft.argtypes = [vp, ll, i, i, f, vp, vp]
     lib.nsg_melspectrogram.argtypes = [vp, ll, i, i, f, vp, i, f, f, f, vp, vp]
     lib.nsg_istft_workspace_bytes.argtypes = [i, i]
@@ -172,6 +173,17 @@ def require_device():
     if load().nsg_device_ok(name, 128) != 1:
         raise NsgError(load().nsg_last_error().decode())
     _device_checked = True
+
+
+def hang_report(clear=False):
+    """Where a kernel's bounded wait gave up (include/nsg_b200.h: nsg_hang_report), or None."""
+    w = (C.c_uint * 8)()
+    load().nsg_hang_report(w, 1 if clear else 0)
+    if w[0] == 0:
+        return None
+    unit = {1: 'conv_tc.cu', 2: 'conv_tma.cu', 3: 'vq_tc.cu'}.get(w[1], '?')
+    return ('kernel wait timed out at %s:%d, block (%d, %d) of %d, thread %d, parity/value %#x'
+            % (unit, w[2], w[3] & 0xFFFFF, w[3] >> 20, w[6], w[4], w[5]))
 
 
 def stream_ptr():

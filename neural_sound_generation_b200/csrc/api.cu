@@ -118,6 +118,29 @@ bool pdl_weights_settled(cudaStream_t s) {
 }
 }  // namespace nsg
 
+// pinned, device-mapped words the kernels' bounded waits report into before trapping (one buffer per process)
+static volatile unsigned int* g_hang_host = nullptr;
+namespace nsg {
+int conv_tc_hang_init(unsigned int*);
+int conv_tma_hang_init(unsigned int*);
+int vq_tc_hang_init(unsigned int*);
+}
+static int hang_init() {
+  if (g_hang_host) return NSG_OK;
+  unsigned int* h = nullptr;
+  cudaError_t e = cudaHostAlloc(reinterpret_cast<void**>(&h), 8 * sizeof(unsigned int), cudaHostAllocMapped);
+  if (e != cudaSuccess) return nsg::cuda_fail(e, "cudaHostAlloc(hang report)");
+  memset(h, 0, 8 * sizeof(unsigned int));
+  unsigned int* d = nullptr;
+  e = cudaHostGetDevicePointer(reinterpret_cast<void**>(&d), h, 0);
+  if (e != cudaSuccess) return nsg::cuda_fail(e, "cudaHostGetDevicePointer(hang report)");
+  if (int rc = nsg::conv_tc_hang_init(d)) return rc;
+  if (int rc = nsg::conv_tma_hang_init(d)) return rc;
+  if (int rc = nsg::vq_tc_hang_init(d)) return rc;
+  g_hang_host = h;
+  return NSG_OK;
+}
+
 using namespace nsg;
 
 extern "C" {
@@ -146,7 +169,21 @@ int nsg_device_ok(char* name, int name_len) {
     set_error("device '%s' is sm_%d%d; this library contains sm_100a code only", prop.name, prop.major, prop.minor);
     return 0;
   }
+  if (hang_init() != NSG_OK) return 0;
   return 1;
+}
+
+/* Where a kernel gave up waiting (see tc_common.cuh "bounded waits"): out[0] != 0 when a report is present, then
+ * out[1] = translation unit (1 conv_tc.cu, 2 conv_tma.cu, 3 vq_tc.cu), out[2] = source line, out[3] = block
+ * (x | y << 20), out[4] = thread, out[5] = barrier parity / counter value, out[6] = grid size.  clear != 0 resets it. */
+int nsg_hang_report(unsigned int* out, int clear) {
+  if (!g_hang_host) {
+    if (out) memset(out, 0, 8 * sizeof(unsigned int));
+    return NSG_OK;
+  }
+  if (out) memcpy(out, (const void*)g_hang_host, 8 * sizeof(unsigned int));
+  if (clear) memset((void*)g_hang_host, 0, 8 * sizeof(unsigned int));
+  return NSG_OK;
 }
 
 static int check_geom(const nsg_conv_geom* g) {

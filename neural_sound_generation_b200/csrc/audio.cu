@@ -135,7 +135,7 @@ __device__ __forceinline__ float au_ola(const float* F, const float* win, long l
 }
 
 // a counter in global memory as a grid barrier: legal because the grid is at most one CTA per SM and every CTA is
-// resident (launch below); bounded (~1 s) and trapping rather than hanging.  `epoch` = barriers passed so far.
+// resident (launch below); bounded (2 s) and trapping rather than hanging.  `epoch` = barriers passed so far.
 __device__ __forceinline__ void au_grid_barrier(unsigned int* ctr, unsigned int epoch) {
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -143,12 +143,15 @@ __device__ __forceinline__ void au_grid_barrier(unsigned int* ctr, unsigned int 
     __threadfence();
     atomicAdd(ctr, 1u);
     unsigned int v = 0;
-    for (long long spins = 0; spins < (1ll << 24); ++spins) {
+    unsigned long long t0, t1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    for (;;) {
       asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
       if (v >= expected) break;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+      if (t1 - t0 > 2000000000ull) __trap();
       __nanosleep(32);
     }
-    if (v < expected) __trap();
     __threadfence();
   }
   __syncthreads();

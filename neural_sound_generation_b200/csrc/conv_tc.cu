@@ -18,6 +18,7 @@
 // used as MN-major SWIZZLE_128B tiles, which is byte-for-byte the pixel-major image the forward kernel builds.
 #include "common.cuh"
 #include "conv_geom.cuh"
+#define NSG_TU_ID 1
 #include "tc_common.cuh"
 
 namespace nsg {
@@ -776,4 +777,11 @@ int conv_wgrad_tc(const nsg_conv_geom* cg, const void* p, const nsg_prologue* pr
   return NSG_E_INVALID;
 }
 
+}  // namespace nsg
+
+namespace nsg {
+int conv_tc_hang_init(unsigned int* host_mapped_words) {
+  cudaError_t e = cudaMemcpyToSymbol(tc::g_hang_words, &host_mapped_words, sizeof(host_mapped_words));
+  return e == cudaSuccess ? NSG_OK : cuda_fail(e, "cudaMemcpyToSymbol(g_hang_words)");
+}
 }  // namespace nsg

@@ -19,6 +19,7 @@
 #include <cstdlib>
 #include "common.cuh"
 #include "conv_geom.cuh"
+#define NSG_TU_ID 2
 #include "tc_common.cuh"
 #include "tma.cuh"
 
@@ -316,12 +317,13 @@ __device__ __forceinline__ void peer_exchange(const PeerSync& ps, double* sums, 
     asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(mine_on_peer), "r"(1u) : "memory");
     const unsigned int* theirs = ps.flags[ps.rank] + (size_t)ps.slot * NSG_PEER_MAX + e;
     unsigned int v = 0;
-    for (long long spins = 0; spins < (1ll << 28); ++spins) {      // ranks may be seconds apart (first steps): ~20 s
+    const unsigned long long t0 = global_ns();
+    for (;;) {                                         // ranks may be seconds apart (first steps): ~40 s
       asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(theirs) : "memory");
-      if (v != 0) break;
+      if (v != 0 || global_ns() - t0 > 20 * kHangNs) break;
       __nanosleep(64);
     }
-    if (v == 0) __trap();                  // a rank that never arrives must not hang the device
+    if (v == 0) hang_trap(__LINE__, (uint32_t)e);   // a rank that never arrives must not hang the device
   }
   named_bar(bar_id, bar_threads);
   if (e < 2 * TM_C) {
@@ -374,29 +376,23 @@ struct BnFuse {
 
 // All CTAs of the grid are resident (grid <= SM count, 1 CTA per SM; kernels running beside this one on other streams
 // never wait for it), so a counter + spin is a legal grid barrier.  A lost CTA must not hang the device: the spin is
-// bounded (~1 s) and traps.
+// bounded (2 s) and traps with a report (tc_common.cuh).
+__device__ __forceinline__ void grid_barrier_wait(unsigned int* ctr, unsigned int expected,
+                                                  unsigned long long limit_ns = kHangNs) {
+  unsigned int v = 0;
+  const unsigned long long t0 = global_ns();
+  for (;;) {
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
+    if (v >= expected) break;
+    if (global_ns() - t0 > limit_ns) hang_trap(__LINE__, v);
+    __nanosleep(64);
+  }
+  __threadfence();
+}
 __device__ __forceinline__ void grid_barrier(unsigned int* ctr, unsigned int expected) {
   __threadfence();
   atomicAdd(ctr, 1u);
-  unsigned int v = 0;
-  for (long long spins = 0; spins < (1ll << 24); ++spins) {
-    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
-    if (v >= expected) break;
-    __nanosleep(64);
-  }
-  if (v < expected) __trap();
-  __threadfence();
-}
-
-__device__ __forceinline__ void grid_barrier_wait(unsigned int* ctr, unsigned int expected, long long max_spins = 1ll << 24) {
-  unsigned int v = 0;
-  for (long long spins = 0; spins < max_spins; ++spins) {
-    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
-    if (v >= expected) break;
-    __nanosleep(64);
-  }
-  if (v < expected) __trap();
-  __threadfence();
+  grid_barrier_wait(ctr, expected);
 }
 
 // operands of one (row, 32-channel half): 64 bytes each
@@ -743,7 +739,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
             atomicExch(bn.barrier + 1, 1u);
           }
         } else if (tid == 64) {
-          grid_barrier_wait(bn.barrier + 1, 1u, 1ll << 29);
+          grid_barrier_wait(bn.barrier + 1, 1u, 30 * kHangNs);    // the other GPUs may be seconds away
         }
       } else if (tid == 64) {
         grid_barrier(bn.barrier, gridDim.x);
@@ -2289,4 +2285,11 @@ int wgrad_c1_tc(const nsg_conv_geom* cg, const void* p, const void* q, float* dw
   return NSG_OK;
 }
 
+}  // namespace nsg
+
+namespace nsg {
+int conv_tma_hang_init(unsigned int* host_mapped_words) {
+  cudaError_t e = cudaMemcpyToSymbol(tc::g_hang_words, &host_mapped_words, sizeof(host_mapped_words));
+  return e == cudaSuccess ? NSG_OK : cuda_fail(e, "cudaMemcpyToSymbol(g_hang_words)");
+}
 }  // namespace nsg

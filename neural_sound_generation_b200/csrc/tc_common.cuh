@@ -36,15 +36,59 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-  while (!mbar_try_wait(bar, parity)) {
+// ---------------------------------------------------------------- bounded waits
+// Every wait in these kernels is bounded: a pipeline that can never advance (a lost TMA box, a miscounted arrival)
+// must not hang the device.  After ~2 s without progress the waiting thread writes WHERE it was stuck -- translation
+// unit, source line, block, thread, barrier parity -- into a few words of pinned HOST memory (they survive the dead
+// context; nsg_hang_report() reads them) and traps.  The words are per translation unit (no relocatable device code
+// in this build); nsg_device_ok() hands every unit the same host buffer before the first launch.
+#ifndef NSG_TU_ID
+#define NSG_TU_ID 0
+#endif
+static __device__ unsigned int* g_hang_words = nullptr;
+static __device__ unsigned int g_hang_once = 0;     // first reporter of this translation unit wins
+static __device__ __noinline__ void hang_trap(uint32_t line, uint32_t aux) {
+  unsigned int* w = g_hang_words;
+  if (w != nullptr && atomicCAS(&g_hang_once, 0u, 1u) == 0u) {
+    volatile unsigned int* v = w;
+    v[0] = 1u;
+    v[1] = (uint32_t)NSG_TU_ID;
+    v[2] = line;
+    v[3] = blockIdx.x | (blockIdx.y << 20);
+    v[4] = threadIdx.x;
+    v[5] = aux;
+    v[6] = gridDim.x;
+    __threadfence_system();
+  }
+  __trap();
+}
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+constexpr unsigned long long kHangNs = 2000000000ull;
+__device__ __forceinline__ void mbar_wait_tagged(uint64_t* bar, uint32_t parity, uint32_t line) {
+  if (mbar_try_wait(bar, parity)) return;
+  const unsigned long long t0 = global_ns();
+  for (uint32_t spins = 1;; ++spins) {
+    if (mbar_try_wait(bar, parity)) return;
+    if ((spins & 1023u) == 0 && global_ns() - t0 > kHangNs) hang_trap(line, parity);
   }
 }
 // for whole warps that wait on a tile-granular event: a polling warp is always eligible and takes issue slots from
 // the working warps of its scheduler (measured: 25 % of all issued instructions in the VQ search were the poll loop)
-__device__ __forceinline__ void mbar_wait_backoff(uint64_t* bar, uint32_t parity) {
-  while (!mbar_try_wait(bar, parity)) __nanosleep(128);
+__device__ __forceinline__ void mbar_wait_backoff_tagged(uint64_t* bar, uint32_t parity, uint32_t line) {
+  if (mbar_try_wait(bar, parity)) return;
+  const unsigned long long t0 = global_ns();
+  for (uint32_t spins = 1;; ++spins) {
+    __nanosleep(128);
+    if (mbar_try_wait(bar, parity)) return;
+    if ((spins & 255u) == 0 && global_ns() - t0 > kHangNs) hang_trap(line, parity | 0x100u);
+  }
 }
+#define mbar_wait(bar, parity) mbar_wait_tagged(bar, parity, __LINE__)
+#define mbar_wait_backoff(bar, parity) mbar_wait_backoff_tagged(bar, parity, __LINE__)
 
 // ---------------------------------------------------------------- bulk async copy global -> shared (TMA engine, 1-D)
 __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {

@@ -12,6 +12,7 @@
 // warp roles: 0-7 operand staging + epilogue (one TMEM row per thread, two column halves), 8 = TMEM
 // allocator + bulk-copy producer + MMA issuer (one elected lane).
 #include "common.cuh"
+#define NSG_TU_ID 3
 #include "tc_common.cuh"
 #include "tma.cuh"
 #include <cstring>
@@ -921,4 +922,11 @@ int vq_forward_tc(const void* z, const float* codebook, long long n, int k, int 
   });
 }
 
+}  // namespace nsg
+
+namespace nsg {
+int vq_tc_hang_init(unsigned int* host_mapped_words) {
+  cudaError_t e = cudaMemcpyToSymbol(tc::g_hang_words, &host_mapped_words, sizeof(host_mapped_words));
+  return e == cudaSuccess ? NSG_OK : cuda_fail(e, "cudaMemcpyToSymbol(g_hang_words)");
+}
 }  // namespace nsg

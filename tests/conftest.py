@@ -27,3 +27,20 @@ def pytest_collection_modifyitems(config, items):
 @pytest.fixture(scope='session')
 def golden_dir():
     return GOLDEN
+
+
+@pytest.hookimpl(hookwrapper=True)
+def pytest_runtest_makereport(item, call):
+    """A GPU test that dies on a CUDA launch failure: attach where the kernel's bounded wait gave up
+    (include/nsg_b200.h: nsg_hang_report) to the report."""
+    outcome = yield
+    rep = outcome.get_result()
+    if rep.when == 'call' and rep.failed and 'gpu' in item.keywords:
+        try:
+            from neural_sound_generation_b200 import _cabi
+            r = _cabi.hang_report()
+            if r:
+                rep.sections.append(('nsg hang report', r))
+                print('\n[nsg hang report] ' + r)
+        except Exception:
+            pass

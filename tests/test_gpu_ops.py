@@ -355,8 +355,12 @@ def test_vq_tensor_core_lowest_index_ties(k, dups, dtype):
     if dtype == torch.float32:                                    # (bf16 inputs cannot represent the one-ulp neighbour)
         idx2 = torch.empty(130, dtype=torch.int64, device=DEV)
         ops.vq_forward(torch.tensor(z2, device=DEV), torch.tensor(cb2, device=DEV), idx2, None, None, mode=1)
-        n_mis, n_viol = vq_ref.index_parity(idx2.cpu().numpy(), vq_ref.vq_indices(z2, cb2), z2, cb2)
-        assert n_viol == 0
+        # the exact match (fp64 distance 0) must win over its one-ulp neighbour with the LOWER index.  (The reference's
+        # fp32 expansion |e|^2 + |z|^2 - 2 z.e rounds both to the same value and returns the lower index: the farther
+        # codeword by (1 ulp)^2.  Ours is the true argmin; the symmetric 1e-6 rule relative to the reference's
+        # distance cannot express "closer than the reference", so the winner itself is asserted.)
+        got2 = idx2.cpu().numpy()
+        assert (got2 == g0[1]).all(), got2[:8]
 
 
 @pytest.mark.parametrize('n,k,d', [(1, 1, 1), (5, 3, 1), (100, 17, 7), (333, 512, 64), (4096, 1024, 128), (257, 640, 256)])
