@@ -370,6 +370,56 @@ int nsg_tanh_bwd(const float* g, const float* y, float* out, long long n, void* 
 int nsg_mel_collate(const float* frames, const int* offsets, int batch, int n_mels, int t_out, float* out_f32,
                     void* out_bf16, void* stream);
 
+/* ---------------------------------------------------------------- other model families (models.py:64-118, 218-341; row N4) */
+/* Stride-1 convolution with a RECTANGULAR kernel, any channel counts, any zero padding, fp32 NHWC: the layers of the
+ * reference's VAE (5 x 5, models.py:74,85) and GatedPixelCNN (vertical (k/2+1) x k and horizontal 1 x (k/2+1) stacks,
+ * models.py:241-253) that the square <= 4 x 4 entry points above do not cover.
+ *   gather 0: out[n,oh,ow,co] = bias[co] + sum in[n, oh - pad_h + kh, ow - pad_w + kw, ci] * w[kh*kw_n + kw + ci*w_cin_stride + co*w_cout_stride]
+ *   gather 1: the same with ih = oh + pad_h - kh, iw = ow + pad_w - kw  (ConvTranspose2d forward / Conv2d data gradient)
+ * out_h / out_w may be SMALLER than the full result: only the leading rows / columns are computed (the crop of
+ * models.py:264,268).  add_src (nullable, same shape as out) is added before the activation; act: 0 none, 1 tanh,
+ * 2 ReLU; stats (nullable, act == 0): double[2*cout] += per-channel sum and sum of squares (BatchNorm moments). */
+typedef struct {
+  int batch, in_h, in_w, cin;
+  int out_h, out_w, cout;
+  int kh, kw, pad_h, pad_w;
+  int gather;
+  long long w_cin_stride, w_cout_stride;
+} nsg_rect_geom;
+int nsg_conv_rect(const nsg_rect_geom* geom, const float* in, const float* w, const float* bias, const float* add_src,
+                  int act, double* stats, float* out, void* stream);
+/* dw[tap + a*w_cin_stride + b*w_cout_stride] += sum over q's pixels of p[gather-0 tap pixel, a] * q[pixel, b]; geom:
+ * in_* / cin describe p, out_* / cout describe q (swap the operands for a transposed convolution, as nsg_conv_wgrad);
+ * q_colsum (nullable) += per-channel sums of q (the bias gradient). */
+int nsg_conv_rect_wgrad(const nsg_rect_geom* geom, const float* p, const float* q, float* dw, float* q_colsum,
+                        void* stream);
+
+/* out[m][c] = tanh(a) * sigmoid(b), (a | b) = the two channel halves of x[m][2C] + add2[m][2C] + cond[item(m)][2C]
+ * (GatedActivation, models.py:218-225, with the class-conditional bias of :262-270); add2 / cond nullable;
+ * item(m) = m / pixels_per_item. */
+int nsg_gated_act(const float* x, const float* add2, const float* cond, long long pixels, int channels,
+                  long long pixels_per_item, float* out, void* stream);
+
+/* Reparameterisation + KL term of the convolutional VAE (models.py:103-110): stats[m][2Z] = (mu | logvar) channel halves;
+ * z[m][c] = mu + exp(logvar / 2) * eps[m][c];  kl_sum[0] += sum over m, c of KL(N(mu, std) || N(0, 1))
+ * = 0.5 (std^2 + mu^2 - 1 - logvar).  Backward: dstats = (dz + kl_scale mu | dz eps std / 2 + kl_scale (std^2 - 1) / 2). */
+int nsg_vae_reparam_kl(const float* stats, const float* eps, long long pixels, int z_channels, float* z, double* kl_sum,
+                       void* stream);
+int nsg_vae_reparam_kl_bwd(const float* stats, const float* eps, const float* dz, float kl_scale, long long pixels,
+                           int z_channels, float* dstats, void* stream);
+
+/* sum[0] += sum (a - b)^2; grad (nullable) = grad_scale * 2 (a - b) (* (1 - a^2) when through_tanh: a = tanh(pre),
+ * grad is then with respect to pre)   -- loss.py:22-24 mse_loss(size_average=False) and its backward */
+int nsg_sqerr_sum(const float* a, const float* b, long long n, double* sum, float grad_scale, int through_tanh,
+                  float* grad, void* stream);
+
+/* One categorical draw per row by inverse CDF: p = softmax(logits[row]) over `classes` contiguous floats at
+ * logits + row * row_stride + offset; out[row * out_stride] = the first class whose cumulative probability exceeds
+ * u[row] (u in [0, 1); the last class when rounding leaves the total below u)  -- GatedPixelCNN.generate,
+ * models.py:334-339, with the uniform draws supplied by the caller. */
+int nsg_softmax_sample(const float* logits, long long rows, int classes, long long row_stride, long long offset,
+                       const float* u, long long* out, long long out_stride, void* stream);
+
 /* ---------------------------------------------------------------- mel <-> audio (audio_tacotron.py) */
 /* All fp32, frame-major device buffers: a spectrum is [n_frames][n_fft/2 + 1] (complex64 = interleaved re, im), a mel
  * spectrogram handed OUT is [n_frames][n_mels]; a mel spectrogram handed IN (nsg_mel_to_linear) keeps the layout the

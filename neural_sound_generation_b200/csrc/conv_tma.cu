@@ -154,106 +154,6 @@ __device__ __forceinline__ void named_bar(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 
-// ---------------------------------------------------------------------------------------------- shared epilogue
-// One thread = one output row (pixel) of a 128 x 64 fp32 accumulator tile: bias, residual add, ReLU mask, output
-// activation, bf16 store, and the per-channel statistics (BatchNorm forward moments or backward reductions).
-struct EpiOperands {
-  uint4 radd[4], rmask[4], rxhat[4];
-  bool use_add, use_mask, use_xhat;
-};
-// request this row's epilogue operands for channels [half*32, half*32 + 32)
-__device__ __forceinline__ void epi_request(EpiOperands& E, const EpiArgs& epi, long long o, int half) {
-  const __nv_bfloat16* add_src = static_cast<const __nv_bfloat16*>(epi.add_src);
-  const __nv_bfloat16* mask_src = static_cast<const __nv_bfloat16*>(epi.mask_src);
-  const __nv_bfloat16* xhat_src = static_cast<const __nv_bfloat16*>(epi.xhat_src);
-#pragma unroll
-  for (int g8 = 0; g8 < 4; ++g8) {
-    if (E.use_add) E.radd[g8] = __ldg(reinterpret_cast<const uint4*>(add_src + o + half * 32 + g8 * 8));
-    if (E.use_mask) E.rmask[g8] = __ldg(reinterpret_cast<const uint4*>(mask_src + o + half * 32 + g8 * 8));
-    if (E.use_xhat) E.rxhat[g8] = __ldg(reinterpret_cast<const uint4*>(xhat_src + o + half * 32 + g8 * 8));
-  }
-}
-__device__ __forceinline__ void epi_begin(EpiOperands& E, const EpiArgs& epi, long long o, bool valid) {
-  E.use_add = valid && epi.add_src != nullptr;
-  E.use_mask = valid && epi.mask_mode != NSG_MASK_NONE;
-  E.use_xhat = valid && epi.stats_mode == NSG_STATS_BNBWD;
-  epi_request(E, epi, o, 0);
-}
-__device__ __forceinline__ void epi_row(EpiOperands& E, const EpiArgs& epi, const float* sPar, float* sStat,
-                                        __nv_bfloat16* __restrict__ out, long long o, bool valid,
-                                        const uint32_t (&acc0)[32], const uint32_t (&acc1)[32], int lane) {
-  uint4 (&radd)[4] = E.radd;
-  uint4 (&rmask)[4] = E.rmask;
-  uint4 (&rxhat)[4] = E.rxhat;
-  const bool use_add = E.use_add, use_mask = E.use_mask, use_xhat = E.use_xhat;
-#pragma unroll
-      for (int chunk = 0; chunk < 2; ++chunk) {
-        const int ch0 = chunk * 32;
-        if (chunk == 1) epi_request(E, epi, o, 1);
-        float x[32], y[32];
-#pragma unroll
-        for (int j = 0; j < 32; ++j)
-          x[j] = valid ? __uint_as_float(chunk == 0 ? acc0[j] : acc1[j]) + sPar[ch0 + j] : 0.f;
-        if (use_add) {
-#pragma unroll
-          for (int g8 = 0; g8 < 4; ++g8) {
-            float a[8];
-            unpack8bf(radd[g8], a);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) x[g8 * 8 + j] += a[j];
-          }
-        }
-        if (use_mask) {
-#pragma unroll
-          for (int g8 = 0; g8 < 4; ++g8) {
-            float mk[8];
-            unpack8bf(rmask[g8], mk);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              const int ch = ch0 + g8 * 8 + j;
-              const float mv = epi.mask_mode == NSG_MASK_AFFINE ? fmaf(sPar[TM_C + ch], mk[j], sPar[2 * TM_C + ch]) : mk[j];
-              x[g8 * 8 + j] = mv > 0.f ? x[g8 * 8 + j] : 0.f;
-            }
-          }
-        }
-        if (epi.tanh_out == 2) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) x[j] = fmaxf(x[j], 0.f);
-        }
-        if (valid) {
-#pragma unroll
-          for (int g16 = 0; g16 < 2; ++g16) st16bf(out + o + ch0 + g16 * 16, &x[g16 * 16]);
-        }
-        if (epi.stats_mode != NSG_STATS_NONE) {
-          if (epi.stats_mode == NSG_STATS_MOMENTS) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) y[j] = x[j] * x[j];
-          } else {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) y[j] = 0.f;
-            if (use_xhat) {
-#pragma unroll
-              for (int g8 = 0; g8 < 4; ++g8) {
-                float hx[8];
-                unpack8bf(rxhat[g8], hx);
-#pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                  const int ch = ch0 + g8 * 8 + j;
-                  y[g8 * 8 + j] = x[g8 * 8 + j] * ((hx[j] - sPar[3 * TM_C + ch]) * sPar[4 * TM_C + ch]);
-                }
-              }
-            }
-          }
-        }
-        if (epi.stats_mode != NSG_STATS_NONE) {
-          const float s1 = transpose_sum32(x, lane);
-          const float s2 = transpose_sum32(y, lane);
-          atomicAdd(&sStat[ch0 + lane], s1);
-          atomicAdd(&sStat[TM_C + ch0 + lane], s2);
-        }
-      }
-}
-
 // ---------------------------------------------------------------------------------------------- conv_tma kernel
 struct TmaTile {
   int p, n, th, tw;
@@ -458,7 +358,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
   uint8_t* tail = sA + (size_t)P.stages * P.slot_bytes;
   // [9][64]: 0 output shift (bias), 1 mscale, 2 mshift, 3 mean, 4 invstd, 5 output scale, 6-8 pass-2 coefficients
   __shared__ __align__(16) float sPar[9 * TM_C];
-  __shared__ float sStat[2 * TM_C];                         // [2][64]
+  __shared__ float sStat[4 * 2 * TM_C];                     // [lane quarter][2][64]
   // issue tables: the producer and MMA threads are single threads running dependent scalar code, so everything they
   // would otherwise derive per tile / tap (integer divisions, byte loads from the parameter bank, descriptor
   // packing) is computed once, in parallel, here
@@ -480,10 +380,6 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
 
   // Everything up to the first pdl_wait() below is independent of the preceding kernel (common.cuh: PDL): shared-memory
   // tables, barriers, TMEM, and the layer's weight images, which were packed at the start of the step.
-  if (tid < TM_C) {
-    sStat[tid] = 0.f;
-    sStat[TM_C + tid] = 0.f;
-  }
   const int ntiles_mine = ((int)blockIdx.x < P.total_tiles)
                               ? (P.total_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
   if (tid >= 64 && tid < 128) {
@@ -719,10 +615,14 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
     if (do_stats) {
       const float t1 = transpose_sum32(s1, lane);
       const float t2 = transpose_sum32(s2, lane);
-      atomicAdd(&sStat[ch0 + lane], t1);
-      atomicAdd(&sStat[TM_C + ch0 + lane], t2);
+      // one slot per (TMEM lane quarter, statistic, channel), summed in a FIXED order: the CTA's contribution does not
+      // depend on which warp finishes first, so the forward pass is reproducible run to run (the fp64 atomics across
+      // CTAs differ at 1e-16, far below the fp32 coefficients derived from them)
+      sStat[q * 2 * TM_C + ch0 + lane] = t1;
+      sStat[q * 2 * TM_C + TM_C + ch0 + lane] = t2;
       named_bar(1, 256);
-      if (e < 2 * TM_C) atomicAdd(epi.stats + e, (double)sStat[e]);
+      if (e < 2 * TM_C)
+        atomicAdd(epi.stats + e, (double)((sStat[e] + sStat[2 * TM_C + e]) + (sStat[4 * TM_C + e] + sStat[6 * TM_C + e])));
     }
     if (HOLD) {
       // ---------------------------------------------------------------- grid barrier, coefficients, pass 2
@@ -792,46 +692,45 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
         const long long oh = row_offset(i, valid);
         // tiles whose accumulator was handed on read what pass 1 stored (h forward, g backward: written by this thread)
         const bool in_tmem = i + NACC >= ntiles_mine;
+        // tcgen05.ld / tcgen05.wait::ld are .sync.aligned: the WHOLE warp executes them, converged -- rows outside a
+        // ragged tile (box wider than the tensor) take part and only skip the arithmetic and the store.  The row's
+        // global operands are requested in between so that they travel under the TMEM read.
         uint32_t acc[32];
         if (in_tmem) tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(i % NACC) * TM_ACC_COLS + (uint32_t)ch0, acc);
-        if (!valid) {
-          if (in_tmem) tmem_ld_wait();
-          continue;
-        }
-        float x[32];
-        if (!in_tmem) {
-          uint4 rs[4];
+        const bool train = bn.mode == NSG_BNF_TRAIN;
+        const bool use_res = valid && train && bn.res != nullptr;
+        const bool use_add = valid && !train && in_tmem && epi.add_src != nullptr;
+        uint4 rs[4], rr[4], radd[4], rx[4];
+        if (valid && !in_tmem) {
           const uint4* p = reinterpret_cast<const uint4*>(out + oh);
 #pragma unroll
           for (int g8 = 0; g8 < 4; ++g8) rs[g8] = p[g8];
+        }
+        if (use_res) ld_half(bn.res, oh, rr);
+        if (use_add) ld_half(epi.add_src, oh, radd);
+        if (valid && !train) ld_half(epi.xhat_src, oh, rx);
+        if (in_tmem) tmem_ld_wait();
+        if (!valid) continue;
+        float x[32];
+        if (!in_tmem) {
 #pragma unroll
           for (int j = 0; j < 32; ++j) x[j] = 0.f;
           add_half(x, rs);
         }
-        if (bn.mode == NSG_BNF_TRAIN) {
-          uint4 rr[4];
-          if (bn.res) ld_half(bn.res, oh, rr);
+        if (train) {
           if (in_tmem) {
-            tmem_ld_wait();
 #pragma unroll
             for (int j = 0; j < 32; ++j) x[j] = fmaf(__uint_as_float(acc[j]), sPar[5 * TM_C + ch0 + j], sPar[ch0 + j]);
           }
 #pragma unroll
           for (int j = 0; j < 32; ++j) x[j] = fmaf(x[j], sPar[6 * TM_C + ch0 + j], sPar[7 * TM_C + ch0 + j]);
-          if (bn.res) add_half(x, rr);
+          if (use_res) add_half(x, rr);
           if (bn.relu_out) {
 #pragma unroll
             for (int j = 0; j < 32; ++j) x[j] = fmaxf(x[j], 0.f);
           }
         } else {
-          const bool use_add = in_tmem && epi.add_src != nullptr;
-          uint4 radd[4], rx[4];
-          if (use_add) ld_half(epi.add_src, oh, radd);
-          ld_half(epi.xhat_src, oh, rx);
-          if (in_tmem) {
-            tmem_ld_wait();
-            epi_half(x, acc, epi, sPar, oh, true, ch0, use_add, radd);     // g, exactly as pass 1 formed it
-          }
+          if (in_tmem) epi_half(x, acc, epi, sPar, oh, true, ch0, use_add, radd);     // g, exactly as pass 1 formed it
 #pragma unroll
           for (int g8 = 0; g8 < 4; ++g8) {
             float hx[8];
@@ -1688,7 +1587,7 @@ c1t_conv_kernel(const __nv_bfloat16* __restrict__ in1, const uint8_t* __restrict
   uint8_t* sW = sm;                                  // one 64 x 64 image (K >= 16 zero)
   uint8_t* sA = sm + TM_W_BYTES;                     // four patch tiles (tile i uses buffer i & 3)
   __shared__ __align__(16) float sPar[6 * TM_C];
-  __shared__ float sStat[2 * TM_C];
+  __shared__ float sStat[4 * 2 * TM_C];
   __shared__ __align__(8) uint64_t bars[9];          // wfull, full[4], acc_full[4]
   __shared__ uint32_t tmem_slot;
   uint64_t* wfull = bars;
@@ -1696,10 +1595,6 @@ c1t_conv_kernel(const __nv_bfloat16* __restrict__ in1, const uint8_t* __restrict
   uint64_t* acc_full = bars + 5;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  if (tid < TM_C) {          // (set-up above the first pdl_wait() touches no global memory: common.cuh, PDL)
-    sStat[tid] = 0.f;
-    sStat[TM_C + tid] = 0.f;
-  }
   if (tid == 0) {
     mbar_init(wfull, 1);
     for (int b = 0; b < 4; ++b) {
@@ -1870,10 +1765,14 @@ c1t_conv_kernel(const __nv_bfloat16* __restrict__ in1, const uint8_t* __restrict
     if (do_stats) {
       const float t1 = transpose_sum32(s1, lane);
       const float t2 = transpose_sum32(s2, lane);
-      atomicAdd(&sStat[ch0 + lane], t1);
-      atomicAdd(&sStat[TM_C + ch0 + lane], t2);
+      // one slot per (TMEM lane quarter, statistic, channel), summed in a FIXED order: the CTA's contribution does not
+      // depend on which warp finishes first, so the forward pass is reproducible run to run (the fp64 atomics across
+      // CTAs differ at 1e-16, far below the fp32 coefficients derived from them)
+      sStat[q * 2 * TM_C + ch0 + lane] = t1;
+      sStat[q * 2 * TM_C + TM_C + ch0 + lane] = t2;
       named_bar(1, 256);
-      if (e < 2 * TM_C) atomicAdd(epi.stats + e, (double)sStat[e]);
+      if (e < 2 * TM_C)
+        atomicAdd(epi.stats + e, (double)((sStat[e] + sStat[2 * TM_C + e]) + (sStat[4 * TM_C + e] + sStat[6 * TM_C + e])));
     }
   }
   tc_fence_before();
