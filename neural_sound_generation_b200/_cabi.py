@@ -27,7 +27,8 @@ EXPORTS = [
     'nsg_bn_act64', 'nsg_bn_bwd64', 'nsg_relu64', 'nsg_vq_bwd_stats64', 'nsg_debug_timeline',
     'nsg_c1_conv_tc', 'nsg_c1_convT_tc', 'nsg_c1_wgrad_tc', 'nsg_scatter_mode', 'nsg_ema_update', 'nsg_vq_resident',
     'nsg_conv_bn_tma', 'nsg_conv_bn_tma_fits', 'nsg_c1_conv_bn_tc', 'nsg_mel_collate', 'nsg_peer_allreduce_stats',
-    'nsg_hang_report', 'nsg_stft', 'nsg_melspectrogram', 'nsg_istft', 'nsg_istft_workspace_bytes', 'nsg_griffin_lim',
+    'nsg_hang_report', 'nsg_conv_rect', 'nsg_conv_rect_wgrad', 'nsg_gated_act', 'nsg_vae_reparam_kl',
+    'nsg_vae_reparam_kl_bwd', 'nsg_sqerr_sum', 'nsg_softmax_sample', 'nsg_stft', 'nsg_melspectrogram', 'nsg_istft', 'nsg_istft_workspace_bytes', 'nsg_griffin_lim',
     'nsg_griffin_lim_workspace_bytes', 'nsg_mel_to_linear', 'nsg_inv_preemphasis',
 ]
 
@@ -63,6 +64,13 @@ class BnFuse(C.Structure):
                 ('running_var', C.c_void_p), ('num_batches_tracked', C.c_void_p), ('coef', C.c_void_p),
                 ('res', C.c_void_p), ('barrier', C.c_void_p), ('dgamma', C.c_void_p), ('dbeta', C.c_void_p),
                 ('out2', C.c_void_p), ('peer', C.POINTER(PeerSync))]
+
+
+class RectGeom(C.Structure):
+    _fields_ = [('batch', C.c_int), ('in_h', C.c_int), ('in_w', C.c_int), ('cin', C.c_int),
+                ('out_h', C.c_int), ('out_w', C.c_int), ('cout', C.c_int),
+                ('kh', C.c_int), ('kw', C.c_int), ('pad_h', C.c_int), ('pad_w', C.c_int), ('gather', C.c_int),
+                ('w_cin_stride', C.c_longlong), ('w_cout_stride', C.c_longlong)]
 
 
 class NsgError(RuntimeError):
@@ -134,6 +142,13 @@ def load():
     lib.nsg_mel_collate.argtypes = [vp, vp, i, i, i, vp, vp, vp]
     lib.nsg_peer_allreduce_stats.argtypes = [vp, C.POINTER(PeerSync), vp]
     lib.nsg_hang_report.argtypes = [vp, i]
+    lib.nsg_conv_rect.argtypes = [C.POINTER(RectGeom), vp, vp, vp, vp, i, vp, vp, vp]
+    lib.nsg_conv_rect_wgrad.argtypes = [C.POINTER(RectGeom), vp, vp, vp, vp, vp]
+    lib.nsg_gated_act.argtypes = [vp, vp, vp, ll, i, ll, vp, vp]
+    lib.nsg_vae_reparam_kl.argtypes = [vp, vp, ll, i, vp, vp, vp]
+    lib.nsg_vae_reparam_kl_bwd.argtypes = [vp, vp, vp, f, ll, i, vp, vp]
+    lib.nsg_sqerr_sum.argtypes = [vp, vp, ll, vp, f, i, vp, vp]
+    lib.nsg_softmax_sample.argtypes = [vp, ll, i, ll, ll, vp, vp, ll, vp]
     lib.nsg_stft.argtypes = [vp, ll, i, i, f, vp, vp]
     lib.nsg_melspectrogram.argtypes = [vp, ll, i, i, f, vp, i, f, f, f, vp, vp]
     lib.nsg_istft_workspace_bytes.argtypes = [i, i]

@@ -358,7 +358,10 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
   uint8_t* tail = sA + (size_t)P.stages * P.slot_bytes;
   // [9][64]: 0 output shift (bias), 1 mscale, 2 mshift, 3 mean, 4 invstd, 5 output scale, 6-8 pass-2 coefficients
   __shared__ __align__(16) float sPar[9 * TM_C];
-  __shared__ float sStat[4 * 2 * TM_C];                     // [lane quarter][2][64]
+  // [lane quarter][2][64] partial statistic sums: written once, after the CTA's last tile, when every TMA load has been
+  // consumed -- the first 4 KB of the (then idle) activation ring serve (static shared memory is full: 223 KB dynamic
+  // + 4 KB static is the 227 KB limit)
+  float* sStat = reinterpret_cast<float*>(sA);
   // issue tables: the producer and MMA threads are single threads running dependent scalar code, so everything they
   // would otherwise derive per tile / tap (integer divisions, byte loads from the parameter bank, descriptor
   // packing) is computed once, in parallel, here

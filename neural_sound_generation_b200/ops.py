@@ -629,3 +629,112 @@ def peer_allreduce_stats(sums, peer):
     rc = A.load().nsg_peer_allreduce_stats(A.ptr(sums), C.byref(peer), A.stream_ptr())
     A.check(rc, 'nsg_peer_allreduce_stats')
     launch_count += 1
+
+
+# ---------------------------------------------------------------------------------------------- row N4 (VAE / PixelCNN)
+def _f32(*ts):
+    for t in ts:
+        if t is not None and t.dtype != torch.float32:
+            raise A.NsgError('this entry point takes float32 tensors (got %s)' % t.dtype)
+
+
+def conv_rect(x, w, out, kh, kw, pad_h, pad_w, gather, w_cin_stride, w_cout_stride, bias=None, add_src=None, act=0,
+              stats=None):
+    """nsg_conv_rect: stride-1 convolution with a (kh, kw) kernel over NHWC fp32 ``x`` into ``out`` (whose height / width
+    may be the cropped leading part of the full result).  gather 0 = Conv2d-like, 1 = ConvTranspose2d-like."""
+    global launch_count
+    A.require_device()
+    _cuda(x, w, out, bias, add_src, stats)
+    _f32(x, w, out, bias, add_src)
+    for t, what in ((x, 'conv input'), (w, 'conv weight'), (out, 'conv output'), (add_src, 'add_src')):
+        _contig(t, what)
+    b, ih, iw, cin = x.shape
+    _, oh, ow, cout = out.shape
+    g = A.RectGeom(b, ih, iw, cin, oh, ow, cout, kh, kw, pad_h, pad_w, gather, w_cin_stride, w_cout_stride)
+    rc = A.load().nsg_conv_rect(C.byref(g), A.ptr(x), A.ptr(w), A.ptr(bias), A.ptr(add_src), act, A.ptr(stats), A.ptr(out),
+                                A.stream_ptr())
+    A.check(rc, 'nsg_conv_rect')
+    launch_count += 1
+    return out
+
+
+def conv_rect_wgrad(p, q, dw, kh, kw, pad_h, pad_w, w_cin_stride, w_cout_stride, q_colsum=None):
+    """dw[tap + a*w_cin_stride + b*w_cout_stride] += sum over q's pixels of p[tap-shifted pixel, a] * q[pixel, b]."""
+    global launch_count
+    A.require_device()
+    _cuda(p, q, dw, q_colsum)
+    _f32(p, q, dw, q_colsum)
+    _contig(p, 'wgrad P')
+    _contig(q, 'wgrad Q')
+    b, ih, iw, ca = p.shape
+    _, oh, ow, cb = q.shape
+    g = A.RectGeom(b, ih, iw, ca, oh, ow, cb, kh, kw, pad_h, pad_w, 0, w_cin_stride, w_cout_stride)
+    rc = A.load().nsg_conv_rect_wgrad(C.byref(g), A.ptr(p), A.ptr(q), A.ptr(dw), A.ptr(q_colsum), A.stream_ptr())
+    A.check(rc, 'nsg_conv_rect_wgrad')
+    launch_count += 1
+
+
+def gated_act(x, out, add2=None, cond=None):
+    """out[..., c] = tanh(a) * sigmoid(b) with (a | b) = halves of x + add2 + cond[item]; x (B, H, W, 2C), cond (B, 2C)."""
+    global launch_count
+    A.require_device()
+    _cuda(x, out, add2, cond)
+    _f32(x, out, add2, cond)
+    for t, what in ((x, 'gate input'), (out, 'gate output'), (add2, 'add2'), (cond, 'cond')):
+        _contig(t, what)
+    c = out.shape[-1]
+    pixels = out.numel() // c
+    rc = A.load().nsg_gated_act(A.ptr(x), A.ptr(add2), A.ptr(cond), pixels, c, pixels // x.shape[0], A.ptr(out),
+                                A.stream_ptr())
+    A.check(rc, 'nsg_gated_act')
+    launch_count += 1
+    return out
+
+
+def vae_reparam_kl(stats, eps, z, kl_sum):
+    global launch_count
+    A.require_device()
+    _cuda(stats, eps, z, kl_sum)
+    _f32(stats, eps, z)
+    zc = z.shape[-1]
+    rc = A.load().nsg_vae_reparam_kl(A.ptr(stats), A.ptr(eps), z.numel() // zc, zc, A.ptr(z), A.ptr(kl_sum), A.stream_ptr())
+    A.check(rc, 'nsg_vae_reparam_kl')
+    launch_count += 1
+
+
+def vae_reparam_kl_bwd(stats, eps, dz, kl_scale, dstats):
+    global launch_count
+    A.require_device()
+    _cuda(stats, eps, dz, dstats)
+    _f32(stats, eps, dz, dstats)
+    zc = eps.shape[-1]
+    rc = A.load().nsg_vae_reparam_kl_bwd(A.ptr(stats), A.ptr(eps), A.ptr(dz), float(kl_scale), eps.numel() // zc, zc,
+                                         A.ptr(dstats), A.stream_ptr())
+    A.check(rc, 'nsg_vae_reparam_kl_bwd')
+    launch_count += 1
+
+
+def sqerr_sum(a, b, total=None, grad=None, grad_scale=1.0, through_tanh=False):
+    global launch_count
+    A.require_device()
+    _cuda(a, b, total, grad)
+    _f32(a, b, grad)
+    _contig(a, 'sqerr a')
+    _contig(b, 'sqerr b')
+    rc = A.load().nsg_sqerr_sum(A.ptr(a), A.ptr(b), a.numel(), A.ptr(total), float(grad_scale), int(through_tanh),
+                                A.ptr(grad), A.stream_ptr())
+    A.check(rc, 'nsg_sqerr_sum')
+    launch_count += 1
+
+
+def softmax_sample(logits, row_stride, offset, rows, classes, u, out, out_stride):
+    global launch_count
+    A.require_device()
+    _cuda(logits, u, out)
+    _f32(logits, u)
+    if out.dtype != torch.int64:
+        raise A.NsgError('softmax_sample: int64 output expected')
+    rc = A.load().nsg_softmax_sample(A.ptr(logits), rows, classes, row_stride, offset, A.ptr(u), A.ptr(out), out_stride,
+                                     A.stream_ptr())
+    A.check(rc, 'nsg_softmax_sample')
+    launch_count += 1

@@ -74,3 +74,23 @@ def test_product_does_not_import_oracle():
             if f.endswith(('.py', '.cu', '.cuh', '.h')):
                 src = open(os.path.join(dirpath, f)).read()
                 assert 'oracle' not in src.replace('oracle of record', ''), os.path.join(dirpath, f)
+
+
+def test_persistent_kernels_fit_in_shared_memory():
+    """conv_tma_kernel asks for 223 KB of dynamic shared memory (TM_SMEM_LIMIT) on top of its static tables; the sum
+    must stay within the 227 KB a CTA may own on sm_100, or cudaFuncSetAttribute fails at the first launch -- a build
+    property that can be checked without a GPU (cuobjdump counts the 1 KB the driver reserves per CTA as SHARED)."""
+    import shutil
+    import subprocess
+    from neural_sound_generation_b200 import _cabi
+    if shutil.which('cuobjdump') is None:
+        import pytest
+        pytest.skip('cuobjdump not on PATH')
+    out = subprocess.run(['cuobjdump', '-res-usage', _cabi.LIB_PATH], capture_output=True, text=True).stdout.splitlines()
+    seen = 0
+    for i, line in enumerate(out):
+        if 'conv_tma_kernel' in line and i + 1 < len(out) and 'SHARED:' in out[i + 1]:
+            static = int(out[i + 1].split('SHARED:')[1].split()[0])
+            assert static - 1024 + 223 * 1024 <= 227 * 1024, (line.strip()[:80], static)
+            seen += 1
+    assert seen >= 3            # the streaming and the two accumulator-holding instantiations
