@@ -15,7 +15,6 @@ Data (main.py:77-99):
     ``--synthetic-frames``, 1 x 28 x 28, 3 x 32 x 32).
 
 What is NOT here, and why (SURVEY.md section 8f ranks them after this row):
-  * the VAE / PixelCNN models (``--model vae``: refused -- not on the hot path);
   * for image datasets the whole per-epoch sample block is skipped: the reference's own block unpacks 5-tuples
     (main.py:138-139) and cannot run on ``(data, label)`` loaders.
 The Griffin-Lim audio of the per-epoch sample (main.py:164-197, row N3) runs on the device (``audio.py``) and is written
@@ -33,8 +32,9 @@ import torch
 from . import audio
 from .models import VQVAE
 from .optim import Adam
-from .train import train_vqvae
-from .test import test_vqvae
+from .models_n4 import VAE
+from .train import train_vqvae, train_vae
+from .test import test_vqvae, test_vae
 
 
 def build_parser():
@@ -180,21 +180,25 @@ def get_loaders(args):
 def main(argv=None):
     args = parse_args(argv)
     torch.manual_seed(args.seed)
-    if args.model != 'vqvae':
-        raise SystemExit('--model %s: only the VQ-VAE is on the accelerated path (SURVEY.md section 8)' % args.model)
+    if args.model not in ('vqvae', 'vae'):
+        raise SystemExit('--model %s: vqvae or vae (main.py:117-121)' % args.model)
     if not args.cuda:
         raise SystemExit('the B200 path has no CPU execution mode (remove --no-cuda / run on a B200)')
     device = torch.device('cuda')
     train_loader, test_loader = get_loaders(args)
     input_dim = 3 if args.dataset == 'CIFAR10' else 1                                  # main.py:100-116
-    model = VQVAE(input_dim, args.dim, args.z_dim).to(device)
-    if args.fp32:
-        model.set_precision('fp32')
-    elif model.conv_impl != 2:
-        # the reference's own default --dim 1, or any dim other than 64, is served by the general fp32 kernels
-        print('--dim %d: the bf16 tensor-core engine serves dim == 64; running the fp32 CUDA-core engine' % args.dim)
+    vae = args.model == 'vae'
+    if vae:         # main.py:117-118 (row N4): the convolutional VAE on the general fp32 kernels, torch's own Adam
+        model = VAE(input_dim, args.dim, args.z_dim).to(device)
+    else:
+        model = VQVAE(input_dim, args.dim, args.z_dim).to(device)
+        if args.fp32:
+            model.set_precision('fp32')
+        elif model.conv_impl != 2:
+            # the reference's own default --dim 1, or any dim other than 64, is served by the general fp32 kernels
+            print('--dim %d: the bf16 tensor-core engine serves dim == 64; running the fp32 CUDA-core engine' % args.dim)
     print(model)
-    optimizer = Adam(model.parameters(), lr=args.lr_rate)                              # main.py:124
+    optimizer = (torch.optim.Adam if vae else Adam)(model.parameters(), lr=args.lr_rate)   # main.py:124
     last_epoch = 0
     if args.resume:
         ck = torch.load(checkpoint_path(args), map_location=device)
@@ -209,8 +213,12 @@ def main(argv=None):
 
     try:
         for epoch in range(last_epoch + 1, args.epochs + 1):
-            train_vqvae(args, model, optimizer, train_loader, device, epoch)
-            test_vqvae(args, model, test_loader, device, epoch)
+            if vae:                                                                    # main.py:130-135
+                train_vae(args, model, optimizer, train_loader, device, epoch)
+                test_vae(args, model, test_loader, device, epoch)
+            else:
+                train_vqvae(args, model, optimizer, train_loader, device, epoch)
+                test_vqvae(args, model, test_loader, device, epoch)
             with torch.no_grad():
                 if args.dataset != 'ljspeech':      # (the reference's sample block unpacks mel 5-tuples, main.py:138)
                     last_epoch = epoch
@@ -219,7 +227,7 @@ def main(argv=None):
                 x, y, c, g, input_lengths = next(iter(test_loader))
                 c = c.to(device).unsqueeze(1)
                 print("Evaluating samples")
-                reconstruction, _, _ = model(c)
+                reconstruction = model(c)[0]                                           # main.py:148-151
                 reconstruction = reconstruction.squeeze(1).float().cpu().numpy()
                 path = sample_path(args, epoch)
                 os.makedirs(os.path.dirname(path), exist_ok=True)

@@ -32,3 +32,21 @@ def test_vqvae(args, model, test_loader, device, epoch):
         test_loss = loss_recons + loss_vq
         print('====> Test set loss: {:.4f}'.format(test_loss))
     return test_loss
+
+
+def test_vae(args, model, test_loader, device, epoch):
+    """test.py:32-70: evaluation loop of the convolutional VAE (row N4); returns the printed mean loss."""
+    from .models_n4 import mse_loss
+    model.eval()
+    test_loss = 0
+    mel = args.dataset == 'ljspeech'
+    with torch.no_grad():
+        for item in test_loader:
+            c = (item[2].unsqueeze(1) if mel else item[0]).to(device)
+            x_tilde, kl_d = model(c)
+            if x_tilde.size(3) != c.size(3):
+                x_tilde = F.pad(x_tilde, (0, c.size(3) - x_tilde.size(3)))
+            test_loss += mse_loss(x_tilde, c, kl_d).item()
+        test_loss /= len(test_loader.dataset)
+        print('====> Test set loss: {:.4f}'.format(test_loss))
+    return test_loss

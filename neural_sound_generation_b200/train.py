@@ -97,3 +97,29 @@ def train_vqvae(args, model, optimizer, train_loader, device, epoch):
                 epoch, batch_idx * len(c), len(train_loader.dataset),
                 args.log_interval * batch_idx / len(train_loader), train_loss))
     print('====> Epoch: {} Average loss: {:.4f}'.format(epoch, train_loss / len(train_loader.dataset)))
+
+
+def train_vae(args, model, optimizer, train_loader, device, epoch):
+    """train.py:41-101: the convolutional VAE loop (row N4).  ``model(c) -> (x_tilde, kl_d)``,
+    ``loss = mse_loss(pad(x_tilde), c, kl_d)`` (loss.py:22-24; the zero-pad of train.py:58-60 without its CPU round
+    trip), same printed formats.  Eager: one explicit kernel schedule forward, its reverse backward (models_n4.py)."""
+    from .models_n4 import mse_loss
+    model.train()
+    train_loss = 0
+    mel = args.dataset == 'ljspeech'
+    batches = tqdm(enumerate(train_loader)) if mel else enumerate(train_loader)
+    for batch_idx, item in batches:
+        optimizer.zero_grad()
+        c = (item[2].unsqueeze(1) if mel else item[0]).to(device, non_blocking=True)
+        x_tilde, kl_d = model(c)
+        if x_tilde.size(3) != c.size(3):
+            x_tilde = F.pad(x_tilde, (0, c.size(3) - x_tilde.size(3)))
+        loss = mse_loss(x_tilde, c, kl_d)
+        loss.backward()
+        train_loss += loss.item()
+        optimizer.step()
+        if batch_idx % args.log_interval == 0:
+            print('Train Epoch: {} [{}/{} ({:.0f}%)]\tLoss: {:.6f}'.format(
+                epoch, batch_idx * len(c), len(train_loader.dataset),
+                100. * batch_idx / len(train_loader), loss.item() / len(c)))
+    print('====> Epoch: {} Average loss: {:.4f}'.format(epoch, train_loss / len(train_loader.dataset)))

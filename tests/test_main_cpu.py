@@ -38,7 +38,7 @@ def test_checkpoint_and_sample_names_match_the_reference():
 
 def test_refusals_are_loud():
     with pytest.raises(SystemExit):
-        M.main(['--model', 'vae', '--dataset', 'ljspeech', '--synthetic-batches', '1'])
+        M.main(['--model', 'pixelrnn', '--dataset', 'ljspeech', '--synthetic-batches', '1'])
     with pytest.raises(SystemExit):
         M.main(['--model', 'vqvae', '--dataset', 'ljspeech', '--no-cuda', '--synthetic-batches', '1'])
 
