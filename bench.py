@@ -292,8 +292,9 @@ def main():
         kctx = eng.begin(x, True)
         eng._pack(kctx, Pd)
         Bd = dict(model.named_buffers())
-        for _ in range(6):          # the launch the step makes for this layer: convolution + BatchNorm + ReLU, fused
-            eng._conv_bn_fwd(kctx, Pd, Bd, 'encoder.4.block.1', 'encoder.4.block.2', x, relu_out=True)
+        kst = torch.zeros(2 * DIM, dtype=torch.float64, device=dev)
+        for _ in range(6):          # the launch the step makes for this layer: convolution + BatchNorm moment sums
+            eng._conv_fwd(kctx, Pd, 'encoder.4.block.1', x, stats=kst)
         torch.cuda.synchronize()
         print(json.dumps(dict(kernel_only=True, launches=6)))
         return
@@ -393,12 +394,21 @@ def main():
         xr = x.relu()
         Bd = {n: q.clone() for n, q in model.named_buffers()}      # (the running statistics of the model stay untouched)
 
-        def kfn(i):                 # the launch the step makes for this layer: convolution + BatchNorm + ReLU in one kernel
+        kstats = torch.zeros(2 * DIM, dtype=torch.float64, device=dev)
+
+        def kfn(i):                 # the launch the step makes for this layer: convolution + BatchNorm moment sums
+            return eng._conv_fwd(kctx, Pd, 'encoder.4.block.1', xr, stats=kstats)
+
+        def kfused(i):              # the BatchNorm-fused form of the same layer (NSG_FUSE_BN=1), timed for the record
             if kctx.nbar >= 30:     # (one zeroed grid-barrier counter per launch)
                 kctx.bars.zero_()
                 kctx.nbar = 0
-            return eng._conv_bn_fwd(kctx, Pd, Bd, 'encoder.4.block.1', 'encoder.4.block.2', xr, relu_out=True)
-        kplain = lambda i: eng._conv_fwd(kctx, Pd, 'encoder.4.block.1', xr)
+            fb, eng.fuse_bn = eng.fuse_bn, True
+            try:
+                return eng._conv_bn_fwd(kctx, Pd, Bd, 'encoder.4.block.1', 'encoder.4.block.2', xr, relu_out=True)
+            finally:
+                eng.fuse_bn = fb
+        kplain = kfused
     else:
         kfn = lambda i: eng._conv_fwd(x, w, bias, 3, 1, 1, False, ops.prologue(ops.PRO_RELU))
     for _ in range(3):
@@ -426,8 +436,8 @@ def main():
     vq_search = dict(value=vq_tf, unit='TFLOP/s', frac_of_peak=vq_tf / pk['tf_burst'], us=vms * 1e3, n=nlat, k=K_CODES,
                      d=DIM, what='vq_forward (search + gather + sq-error; split-bf16 passes not counted), L2 flushed')
     roof = dict(bound='tensor', achieved=achieved, peak=pk['tf_burst'], unit='TFLOP/s', frac=achieved / pk['tf_burst'],
-                traffic=ncu_traffic('conv_tma_kernel_3x3_fwd'), kernel='conv3x3 64->64 fwd (%s)' % ({0: 'CUDA-core fp32', 1: 'tcgen05 bf16, register-staged', 2: 'tcgen05 bf16, TMA-fed persistent, BatchNorm + ReLU fused across a grid barrier (two outputs)'}[model.conv_impl]),
-                us=kms * 1e3, us_conv_only=(kms_plain * 1e3 if kms_plain else None),
+                traffic=ncu_traffic('conv_tma_kernel_3x3_fwd'), kernel='conv3x3 64->64 fwd (%s)' % ({0: 'CUDA-core fp32', 1: 'tcgen05 bf16, register-staged', 2: 'tcgen05 bf16, TMA-fed persistent, BatchNorm moment sums in the epilogue'}[model.conv_impl]),
+                us=kms * 1e3, us_fused_conv_bn_relu=(kms_plain * 1e3 if kms_plain else None),
                 peak_source=pk['src'], step_frac_of_tensor_peak=TRAIN_GFLOP * world / (ms / 1e3) / 1e3 / (pk['tf_sust'] * world))
     if rank != 0:
         if world > 1:

@@ -86,6 +86,23 @@ __global__ void __launch_bounds__(256) bn_act_kernel(const BnActArgs a) {
   const int tid = threadIdx.x;
   pdl_wait();
   pdl_trigger();
+  const int c0 = (tid & 7) * 8;
+  // The first 4 pixels of this thread are requested BEFORE the coefficients are derived: the statistics load, the
+  // fp64 arithmetic behind mean / invstd and the CTA barrier then run under the latency of the tensor loads instead
+  // of in front of it (at configs[1] every CTA has exactly one such batch: the kernel is one memory round trip).
+  long long p0 = (long long)blockIdx.x * 128 + (tid >> 3);
+  uint4 hv[4], rv[4];
+  auto request = [&](long long q0) {
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const long long p = q0 + 32 * u;
+      if (p < a.pixels) {
+        hv[u] = __ldg(reinterpret_cast<const uint4*>(a.h + p * FE_C + c0));
+        if (a.res) rv[u] = __ldg(reinterpret_cast<const uint4*>(a.res + p * FE_C + c0));
+      }
+    }
+  };
+  request(p0);
   if (tid < FE_C) {
     float mu, is;
     if (a.stats) {
@@ -116,24 +133,13 @@ __global__ void __launch_bounds__(256) bn_act_kernel(const BnActArgs a) {
     }
   }
   __syncthreads();
-  const int c0 = (tid & 7) * 8;
   float sc[8], sh[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     sc[i] = sSc[c0 + i];
     sh[i] = sSh[c0 + i];
   }
-  // 4 pixels per thread and iteration: every load of the iteration is issued before the first use
-  for (long long p0 = (long long)blockIdx.x * 128 + (tid >> 3); p0 < a.pixels; p0 += (long long)gridDim.x * 128) {
-    uint4 hv[4], rv[4];
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const long long p = p0 + 32 * u;
-      if (p < a.pixels) {
-        hv[u] = __ldg(reinterpret_cast<const uint4*>(a.h + p * FE_C + c0));
-        if (a.res) rv[u] = __ldg(reinterpret_cast<const uint4*>(a.res + p * FE_C + c0));
-      }
-    }
+  for (; p0 < a.pixels; p0 += (long long)gridDim.x * 128) {
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
       const long long p = p0 + 32 * u;
@@ -149,6 +155,7 @@ __global__ void __launch_bounds__(256) bn_act_kernel(const BnActArgs a) {
       }
       fe_st8(a.out + p * FE_C + c0, v);
     }
+    request(p0 + (long long)gridDim.x * 128);          // next batch (none at configs[1])
   }
 }
 
@@ -173,6 +180,21 @@ __global__ void __launch_bounds__(256) bn_bwd_kernel(const BnBwdArgs a) {
   const int tid = threadIdx.x;
   pdl_wait();
   pdl_trigger();
+  const int c0 = (tid & 7) * 8;
+  // (first batch of tensor loads in flight before the coefficients are derived: see bn_act_kernel)
+  long long p0 = (long long)blockIdx.x * 128 + (tid >> 3);
+  uint4 gr[4], hr[4];
+  auto request = [&](long long q0) {
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const long long p = q0 + 32 * u;
+      if (p < a.pixels) {
+        gr[u] = __ldg(reinterpret_cast<const uint4*>(a.g + p * FE_C + c0));
+        hr[u] = __ldg(reinterpret_cast<const uint4*>(a.h + p * FE_C + c0));
+      }
+    }
+  };
+  request(p0);
   if (tid < FE_C) {
     const double sg = a.stats[tid] / a.count, sgx = a.stats[FE_C + tid] / a.count;
     const float mu = a.mean[tid], is = a.invstd[tid];
@@ -187,7 +209,6 @@ __global__ void __launch_bounds__(256) bn_bwd_kernel(const BnBwdArgs a) {
     }
   }
   __syncthreads();
-  const int c0 = (tid & 7) * 8;
   float ca[8], cb[8], cc[8], col[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
@@ -196,16 +217,7 @@ __global__ void __launch_bounds__(256) bn_bwd_kernel(const BnBwdArgs a) {
     cc[i] = sC[c0 + i];
     col[i] = 0.f;
   }
-  for (long long p0 = (long long)blockIdx.x * 128 + (tid >> 3); p0 < a.pixels; p0 += (long long)gridDim.x * 128) {
-    uint4 gr[4], hr[4];
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const long long p = p0 + 32 * u;
-      if (p < a.pixels) {
-        gr[u] = __ldg(reinterpret_cast<const uint4*>(a.g + p * FE_C + c0));
-        hr[u] = __ldg(reinterpret_cast<const uint4*>(a.h + p * FE_C + c0));
-      }
-    }
+  for (; p0 < a.pixels; p0 += (long long)gridDim.x * 128) {
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
       const long long p = p0 + 32 * u;
@@ -220,6 +232,7 @@ __global__ void __launch_bounds__(256) bn_bwd_kernel(const BnBwdArgs a) {
       }
       fe_st8(a.dh + p * FE_C + c0, gv);
     }
+    request(p0 + (long long)gridDim.x * 128);
   }
   if (a.dbias_prev) fe_channel_reduce<float>(col, sred, a.dbias_prev, c0);
 }

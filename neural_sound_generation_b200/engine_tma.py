@@ -59,9 +59,17 @@ class EngineTMA(object):
         self.dwa_in_zbuf = False
         self.dwa_dirty = False      # the images hold a consumed fused step's sums (cleared by the next fused begin)
         self.dp = None              # dist.DataParallel: cross-rank BatchNorm statistics / bucketed gradient all-reduce
-        # BatchNorm fused into the producing convolution across a grid barrier (csrc/conv_tma.cu, BnFuse): the
-        # bn_act / bn_bwd passes of the latent-grid layers disappear.  NSG_FUSE_BN=0 keeps the separate passes.
-        self.fuse_bn = os.environ.get('NSG_FUSE_BN', '1') != '0'
+        # BatchNorm fused into the producing convolution across a grid barrier (csrc/conv_tma.cu, BnFuse): one launch
+        # instead of conv + bn_act / dgrad + bn_bwd.  MEASURED on B200 (profiles/r2_fuse_bn_ab.txt, configs[1]): the
+        # fused step is SLOWER, 0.816 vs 0.667 ms -- after the barrier every CTA re-reads its 2-3 accumulators and
+        # stores them with nothing left to overlap (26.7 us against 16.5 + 7.6 us for the 3x3 forward), while the
+        # separate streaming pass spreads the same stores over the whole machine under programmatic dependent launch.
+        # So training keeps the two-kernel form by default; NSG_FUSE_BN=1 selects the fused launches (they remain the
+        # place where synchronised BatchNorm exchanges its statistics between GPUs without a collective, see dist.py).
+        # Eval mode needs no barrier -- the running statistics fold into the convolution's output affine -- and is
+        # always fused (config 5: 0.111 ms against 0.123 ms per utterance).
+        self.fuse_bn = os.environ.get('NSG_FUSE_BN', '0') == '1'
+        self.fuse_bn_eval = os.environ.get('NSG_FUSE_BN_EVAL', '1') != '0'
 
     # ------------------------------------------------------------------ packed images
     def _prepare(self, P):
@@ -231,7 +239,7 @@ class EngineTMA(object):
         g, oh, ow = self._fwd_geom(L, x)
         bn = self._bn(ctx, bn_name)
         shape = (x.shape[0], oh, ow, self.dim)
-        if not ctx.training and self.fuse_bn:
+        if not ctx.training and self.fuse_bn_eval:
             v = torch.empty(shape, dtype=BF, device=x.device)
             ops.conv_bn_tma(g, x, L.wf, v, ops.BNF_EVAL, P[bn_name + '.weight'], beta=P[bn_name + '.bias'], eps=BN_EPS,
                             running_mean=Bufs[bn_name + '.running_mean'], running_var=Bufs[bn_name + '.running_var'],
@@ -378,7 +386,7 @@ class EngineTMA(object):
         oh, ow = _out_hw(h, w, 4, 2, 1, False)
         a0 = torch.empty((b, oh, ow, self.dim), dtype=BF, device=x.device)
         g = ops.conv_geom(b, h, w, cin, oh, ow, self.dim, 4, 2, 1, 0, 16, cin * 16, ops.BF16)
-        if self.c1 is not None and not tr and self.fuse_bn:
+        if self.c1 is not None and not tr and self.fuse_bn_eval:
             # eval: encoder.1's running statistics fold into the convolution's output affine, one launch
             v0 = ops.c1_conv_bn_eval_tc(g, x, self.c1['enc0'], a0, P['encoder.1.weight'], P['encoder.1.bias'],
                                         Bufs['encoder.1.running_mean'], Bufs['encoder.1.running_var'], eps=BN_EPS,
