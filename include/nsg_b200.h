@@ -57,7 +57,7 @@ int nsg_device_ok(char* name, int name_len);
 /* Every wait inside the tensor-core kernels (mbarrier, grid barrier, peer flags) is bounded: after ~2 s without
  * progress the waiting thread records where it was stuck in pinned host memory and traps, so a lost pipeline stage
  * surfaces as a CUDA launch failure with a location instead of a hung device.  out: 8 words -- out[0] != 0 when a
- * report is present; out[1] translation unit (1 conv_tc.cu, 2 conv_tma.cu, 3 vq_tc.cu), out[2] source line, out[3]
+ * report is present; out[1] translation unit (1 conv_tc.cu, 2 conv_tma.cu, 3 vq_tc.cu, 4 fused_elem.cu), out[2] source line, out[3]
  * block (x | y << 20), out[4] thread, out[5] barrier parity / counter value, out[6] grid size.  clear != 0 resets. */
 int nsg_hang_report(unsigned int* out, int clear);
 
@@ -271,6 +271,17 @@ int nsg_bn_act64(const void* h, const void* res, void* out, const double* stats,
 int nsg_bn_bwd64(const void* g, const void* h, void* dh, const double* stats, double count, const float* mean,
                  const float* invstd, const float* gamma, float* dgamma, float* dbeta, float* dbias_prev,
                  long long pixels, void* stream);
+/* The same two kernels with the cross-GPU statistic exchange INSIDE them (synchronised BatchNorm, one process per GPU):
+ * CTA 0 swaps `stats` with the other ranks over peer memory (nsg_peer_sync above) while the tensor loads of every CTA
+ * are in flight, writes the global sums back into `stats` and opens `gate` (one zeroed unsigned counter per launch);
+ * `count` must be the GLOBAL element count.  peer == null or world <= 1: exactly nsg_bn_act64 / nsg_bn_bwd64. */
+int nsg_bn_act64_sync(const void* h, const void* res, void* out, double* stats, double count, const float* gamma,
+                      const float* beta, float eps, float momentum, float* running_mean, float* running_var,
+                      long long* num_batches_tracked, float* mean, float* invstd, float* scale, float* shift,
+                      int relu_out, long long pixels, const nsg_peer_sync* peer, unsigned int* gate, void* stream);
+int nsg_bn_bwd64_sync(const void* g, const void* h, void* dh, double* stats, double count, const float* mean,
+                      const float* invstd, const float* gamma, float* dgamma, float* dbeta, float* dbias_prev,
+                      long long pixels, const nsg_peer_sync* peer, unsigned int* gate, void* stream);
 int nsg_relu64(const void* x, void* out, long long n, void* stream);
 int nsg_vq_bwd_stats64(const void* g_st, const void* z, const void* zq, float coef, void* dz, const void* h,
                        const float* mean, const float* invstd, double* stats, long long pixels, void* stream);

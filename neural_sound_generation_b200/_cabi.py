@@ -27,7 +27,7 @@ EXPORTS = [
     'nsg_bn_act64', 'nsg_bn_bwd64', 'nsg_relu64', 'nsg_vq_bwd_stats64', 'nsg_debug_timeline',
     'nsg_c1_conv_tc', 'nsg_c1_convT_tc', 'nsg_c1_wgrad_tc', 'nsg_scatter_mode', 'nsg_ema_update', 'nsg_vq_resident',
     'nsg_conv_bn_tma', 'nsg_conv_bn_tma_fits', 'nsg_c1_conv_bn_tc', 'nsg_mel_collate', 'nsg_peer_allreduce_stats',
-    'nsg_hang_report', 'nsg_conv_rect', 'nsg_conv_rect_wgrad', 'nsg_gated_act', 'nsg_vae_reparam_kl',
+    'nsg_hang_report', 'nsg_bn_act64_sync', 'nsg_bn_bwd64_sync', 'nsg_conv_rect', 'nsg_conv_rect_wgrad', 'nsg_gated_act', 'nsg_vae_reparam_kl',
     'nsg_vae_reparam_kl_bwd', 'nsg_sqerr_sum', 'nsg_softmax_sample', 'nsg_stft', 'nsg_melspectrogram', 'nsg_istft', 'nsg_istft_workspace_bytes', 'nsg_griffin_lim',
     'nsg_griffin_lim_workspace_bytes', 'nsg_mel_to_linear', 'nsg_inv_preemphasis',
 ]
@@ -120,6 +120,9 @@ def load():
     lib.nsg_conv_wgrad_tma_sliced.argtypes = [C.POINTER(ConvGeom), vp, vp, vp, vp, vp]
     lib.nsg_bn_act64.argtypes = [vp, vp, vp, vp, d, vp, vp, f, f, vp, vp, vp, vp, vp, vp, vp, i, ll, vp]
     lib.nsg_bn_bwd64.argtypes = [vp, vp, vp, vp, d, vp, vp, vp, vp, vp, vp, ll, vp]
+    lib.nsg_bn_act64_sync.argtypes = [vp, vp, vp, vp, d, vp, vp, f, f, vp, vp, vp, vp, vp, vp, vp, i, ll,
+                                      C.POINTER(PeerSync), vp, vp]
+    lib.nsg_bn_bwd64_sync.argtypes = [vp, vp, vp, vp, d, vp, vp, vp, vp, vp, vp, ll, C.POINTER(PeerSync), vp, vp]
     lib.nsg_relu64.argtypes = [vp, vp, ll, vp]
     lib.nsg_vq_bwd_stats64.argtypes = [vp, vp, vp, f, vp, vp, vp, vp, vp, ll, vp]
     lib.nsg_bn_finalize.argtypes = [vp, i, d, vp, vp, f, f, vp, vp, vp, vp, vp, vp, vp, vp]
@@ -196,7 +199,7 @@ def hang_report(clear=False):
     load().nsg_hang_report(w, 1 if clear else 0)
     if w[0] == 0:
         return None
-    unit = {1: 'conv_tc.cu', 2: 'conv_tma.cu', 3: 'vq_tc.cu'}.get(w[1], '?')
+    unit = {1: 'conv_tc.cu', 2: 'conv_tma.cu', 3: 'vq_tc.cu', 4: 'fused_elem.cu'}.get(w[1], '?')
     return ('kernel wait timed out at %s:%d, block (%d, %d) of %d, thread %d, parity/value %#x'
             % (unit, w[2], w[3] & 0xFFFFF, w[3] >> 20, w[6], w[4], w[5]))
 

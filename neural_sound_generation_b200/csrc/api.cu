@@ -124,6 +124,7 @@ namespace nsg {
 int conv_tc_hang_init(unsigned int*);
 int conv_tma_hang_init(unsigned int*);
 int vq_tc_hang_init(unsigned int*);
+int fused_elem_hang_init(unsigned int*);
 }
 static int hang_init() {
   if (g_hang_host) return NSG_OK;
@@ -137,6 +138,7 @@ static int hang_init() {
   if (int rc = nsg::conv_tc_hang_init(d)) return rc;
   if (int rc = nsg::conv_tma_hang_init(d)) return rc;
   if (int rc = nsg::vq_tc_hang_init(d)) return rc;
+  if (int rc = nsg::fused_elem_hang_init(d)) return rc;
   g_hang_host = h;
   return NSG_OK;
 }
@@ -174,7 +176,7 @@ int nsg_device_ok(char* name, int name_len) {
 }
 
 /* Where a kernel gave up waiting (see tc_common.cuh "bounded waits"): out[0] != 0 when a report is present, then
- * out[1] = translation unit (1 conv_tc.cu, 2 conv_tma.cu, 3 vq_tc.cu), out[2] = source line, out[3] = block
+ * out[1] = translation unit (1 conv_tc.cu, 2 conv_tma.cu, 3 vq_tc.cu, 4 fused_elem.cu), out[2] = source line, out[3] = block
  * (x | y << 20), out[4] = thread, out[5] = barrier parity / counter value, out[6] = grid size.  clear != 0 resets it. */
 int nsg_hang_report(unsigned int* out, int clear) {
   if (!g_hang_host) {

@@ -22,6 +22,7 @@
 #define NSG_TU_ID 2
 #include "tc_common.cuh"
 #include "tma.cuh"
+#include "peer.cuh"
 
 namespace nsg {
 
@@ -183,63 +184,7 @@ __device__ __forceinline__ TmaTile fetch_tile(const TmaConvParams& P, const int4
   return decode_tile(P, (int)blockIdx.x + i * (int)gridDim.x);
 }
 
-// ---------------------------------------------------------------------------------------------- cross-GPU statistics
-// Synchronised BatchNorm (one process per GPU; every rank must normalise with the statistics of the GLOBAL batch to
-// equal the single-process reference): the 128 fp64 partial sums of a layer are exchanged through peer-mapped
-// ("symmetric") memory over NVLink inside the kernel that needs them, instead of a 1 KB ncclAllReduce launch per
-// layer and direction (~26 us each, 20 per step).  Every rank owns an area
-//     slots [NSG_PEER_SLOTS][8 ranks][128] fp64   |   flags [NSG_PEER_SLOTS][8 ranks] u32
-// mapped on all ranks.  One exchange (slot s) on rank r:  write my sums into slot (s, r) of EVERY rank; fence; raise
-// flag (s, r) on every rank; wait until my flags (s, 0..world-1) are up; sum my slots (s, 0..world-1) in rank order
-// (every rank adds the same numbers in the same order: bit-identical results everywhere); lower my flags.  A slot is
-// used once per step, and a rank can only reach it again after the step's gradient all-reduce, which every rank enters
-// after its own last exchange -- so lowering the flags after the read cannot race with the next step's writers.
-struct PeerSync {
-  int world, rank, slot;
-  double* slots[NSG_PEER_MAX];
-  unsigned int* flags[NSG_PEER_MAX];
-};
-constexpr size_t kPeerSlotDoubles = (size_t)NSG_PEER_MAX * 2 * TM_C;
-
-// executed by 128+ threads of ONE CTA (thread index e = 0.. within the group, `bar` = their named barrier id / count);
-// sums[0..127] in global memory is replaced by the sum over ranks
-__device__ __forceinline__ void peer_exchange(const PeerSync& ps, double* sums, int e, int bar_id, int bar_threads) {
-  const size_t base = (size_t)ps.slot * kPeerSlotDoubles;
-  if (e < 2 * TM_C) {
-    const double v = __ldcg(sums + e);
-    for (int p = 0; p < ps.world; ++p)
-      asm volatile("st.relaxed.sys.global.f64 [%0], %1;" ::"l"(ps.slots[p] + base + (size_t)ps.rank * 2 * TM_C + e), "d"(v) : "memory");
-  }
-  __threadfence_system();
-  named_bar(bar_id, bar_threads);
-  if (e < ps.world) {
-    unsigned int* mine_on_peer = ps.flags[e] + (size_t)ps.slot * NSG_PEER_MAX + ps.rank;
-    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(mine_on_peer), "r"(1u) : "memory");
-    const unsigned int* theirs = ps.flags[ps.rank] + (size_t)ps.slot * NSG_PEER_MAX + e;
-    unsigned int v = 0;
-    const unsigned long long t0 = global_ns();
-    for (;;) {                                         // ranks may be seconds apart (first steps): ~40 s
-      asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(theirs) : "memory");
-      if (v != 0 || global_ns() - t0 > 20 * kHangNs) break;
-      __nanosleep(64);
-    }
-    if (v == 0) hang_trap(__LINE__, (uint32_t)e);   // a rank that never arrives must not hang the device
-  }
-  named_bar(bar_id, bar_threads);
-  if (e < 2 * TM_C) {
-    double acc = 0.0;
-    for (int r = 0; r < ps.world; ++r) {
-      double v;
-      asm volatile("ld.relaxed.sys.global.f64 %0, [%1];" : "=d"(v) : "l"(ps.slots[ps.rank] + base + (size_t)r * 2 * TM_C + e) : "memory");
-      acc += v;
-    }
-    __stcg(sums + e, acc);
-  }
-  __threadfence();
-  named_bar(bar_id, bar_threads);
-  if (e < ps.world) ps.flags[ps.rank][(size_t)ps.slot * NSG_PEER_MAX + e] = 0u;
-}
-
+// (PeerSync / peer_exchange: the cross-GPU statistic exchange over peer-mapped memory lives in peer.cuh)
 // stand-alone form for the statistics that are not produced by a grid-barrier launch (encoder.1 forward, the two
 // backward reductions fed by the single-channel / bottleneck kernels): one CTA, replaces ncclAllReduce of 1 KB
 __global__ void __launch_bounds__(128) peer_allreduce_kernel(double* sums, PeerSync ps) {
@@ -888,7 +833,7 @@ static int encode_input_maps(CUtensorMap* tm, const void* in, int batch, int in_
   return NSG_OK;
 }
 
-static int make_peer(const nsg_peer_sync* p, PeerSync* out) {
+int make_peer(const nsg_peer_sync* p, PeerSync* out) {
   NSG_REQUIRE(p->world >= 2 && p->world <= NSG_PEER_MAX && p->rank >= 0 && p->rank < p->world,
               "peer sync: world %d / rank %d (at most %d GPUs of one node)", p->world, p->rank, NSG_PEER_MAX);
   NSG_REQUIRE(p->slot >= 0 && p->slot < NSG_PEER_SLOTS, "peer sync: slot %d out of range", p->slot);

@@ -11,10 +11,40 @@
 // One thread owns 8 consecutive channels (16-byte accesses) of a grid-strided set of pixels, so per-channel
 // coefficients live in registers and per-channel reductions need two shuffles, one shared-memory and one global atomic.
 #include "common.cuh"
+#define NSG_TU_ID 4
+#include "peer.cuh"
 
 namespace nsg {
 
 constexpr int FE_C = 64;
+
+// Synchronised BatchNorm without a collective and without an extra launch: CTA 0 swaps the layer's 128 partial sums
+// with the other GPUs over peer memory (peer.cuh) while every CTA's tensor loads are already in flight, then opens
+// `gate` (one zeroed counter per launch); the other CTAs wait at it before deriving their coefficients.  CTA 0 is
+// dispatched first, so the waiters cannot keep it from becoming resident.
+__device__ __forceinline__ void fe_global_stats(const PeerSync& peer, double* stats, unsigned int* gate) {
+  if (peer.world <= 1) return;
+  if (blockIdx.x == 0) {
+    peer_exchange(peer, stats, (int)threadIdx.x, 1, (int)blockDim.x);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence();
+      asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(gate), "r"(1u) : "memory");
+    }
+  } else {
+    if (threadIdx.x == 0) {
+      unsigned int v = 0;
+      const unsigned long long t0 = global_ns();
+      for (;;) {
+        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(gate) : "memory");
+        if (v != 0) break;
+        if (global_ns() - t0 > 30 * kHangNs) hang_trap(__LINE__, 0u);
+        __nanosleep(64);
+      }
+    }
+    __syncthreads();
+  }
+}
 
 __device__ __forceinline__ void fe_ld8(const __nv_bfloat16* p, float (&v)[8]) {
   const uint4 r = __ldg(reinterpret_cast<const uint4*>(p));
@@ -79,6 +109,8 @@ struct BnActArgs {
   float* shift;
   int relu_out;
   long long pixels;
+  PeerSync peer;                 // world > 1: the statistics are summed over the GPUs inside this launch
+  unsigned int* gate;
 };
 
 __global__ void __launch_bounds__(256) bn_act_kernel(const BnActArgs a) {
@@ -103,11 +135,12 @@ __global__ void __launch_bounds__(256) bn_act_kernel(const BnActArgs a) {
     }
   };
   request(p0);
+  if (a.stats) fe_global_stats(a.peer, const_cast<double*>(a.stats), a.gate);
   if (tid < FE_C) {
     float mu, is;
     if (a.stats) {
-      const double m = a.stats[tid] / a.count;
-      double var = a.stats[FE_C + tid] / a.count - m * m;
+      const double m = __ldcg(a.stats + tid) / a.count;
+      double var = __ldcg(a.stats + FE_C + tid) / a.count - m * m;
       if (var < 0.0) var = 0.0;
       mu = (float)m;
       is = (float)(1.0 / sqrt(var + (double)a.eps));
@@ -172,6 +205,8 @@ struct BnBwdArgs {
   float* dbeta;
   float* dbias_prev;             // nullable
   long long pixels;
+  PeerSync peer;
+  unsigned int* gate;
 };
 
 __global__ void __launch_bounds__(256) bn_bwd_kernel(const BnBwdArgs a) {
@@ -195,8 +230,9 @@ __global__ void __launch_bounds__(256) bn_bwd_kernel(const BnBwdArgs a) {
     }
   };
   request(p0);
+  fe_global_stats(a.peer, const_cast<double*>(a.stats), a.gate);
   if (tid < FE_C) {
-    const double sg = a.stats[tid] / a.count, sgx = a.stats[FE_C + tid] / a.count;
+    const double sg = __ldcg(a.stats + tid) / a.count, sgx = __ldcg(a.stats + FE_C + tid) / a.count;
     const float mu = a.mean[tid], is = a.invstd[tid];
     const float k0 = a.gamma[tid] * is;
     const float kb = k0 * is * (float)sgx;
@@ -204,8 +240,8 @@ __global__ void __launch_bounds__(256) bn_bwd_kernel(const BnBwdArgs a) {
     sB[tid] = -kb;
     sC[tid] = kb * mu - k0 * (float)sg;
     if (blockIdx.x == 0) {
-      if (a.dbeta) a.dbeta[tid] += (float)a.stats[tid];
-      if (a.dgamma) a.dgamma[tid] += (float)a.stats[FE_C + tid];
+      if (a.dbeta) a.dbeta[tid] += (float)__ldcg(a.stats + tid);
+      if (a.dgamma) a.dgamma[tid] += (float)__ldcg(a.stats + FE_C + tid);
     }
   }
   __syncthreads();
@@ -301,14 +337,35 @@ static inline int fe_grid(long long pixels) {
 
 }  // namespace nsg
 
+namespace nsg {
+int fused_elem_hang_init(unsigned int* host_mapped_words) {
+  cudaError_t e = cudaMemcpyToSymbol(tc::g_hang_words, &host_mapped_words, sizeof(host_mapped_words));
+  return e == cudaSuccess ? NSG_OK : cuda_fail(e, "cudaMemcpyToSymbol(g_hang_words)");
+}
+}  // namespace nsg
+
 using namespace nsg;
 
 extern "C" {
+
+int nsg_bn_act64_sync(const void* h, const void* res, void* out, double* stats, double count, const float* gamma,
+                      const float* beta, float eps, float momentum, float* running_mean, float* running_var,
+                      long long* num_batches_tracked, float* mean, float* invstd, float* scale, float* shift,
+                      int relu_out, long long pixels, const nsg_peer_sync* peer, unsigned int* gate, void* stream);
 
 int nsg_bn_act64(const void* h, const void* res, void* out, const double* stats, double count, const float* gamma,
                  const float* beta, float eps, float momentum, float* running_mean, float* running_var,
                  long long* num_batches_tracked, float* mean, float* invstd, float* scale, float* shift, int relu_out,
                  long long pixels, void* stream) {
+  return nsg_bn_act64_sync(h, res, out, const_cast<double*>(stats), count, gamma, beta, eps, momentum, running_mean,
+                           running_var, num_batches_tracked, mean, invstd, scale, shift, relu_out, pixels, nullptr,
+                           nullptr, stream);
+}
+
+int nsg_bn_act64_sync(const void* h, const void* res, void* out, double* stats, double count, const float* gamma,
+                      const float* beta, float eps, float momentum, float* running_mean, float* running_var,
+                      long long* num_batches_tracked, float* mean, float* invstd, float* scale, float* shift,
+                      int relu_out, long long pixels, const nsg_peer_sync* peer, unsigned int* gate, void* stream) {
   NSG_REQUIRE(h && out && gamma && beta, "bn_act64: null tensor");
   NSG_REQUIRE(stats || (running_mean && running_var), "bn_act64: eval mode needs the running statistics");
   NSG_REQUIRE(!stats || count > 0, "bn_act64: count must be positive");
@@ -316,20 +373,42 @@ int nsg_bn_act64(const void* h, const void* res, void* out, const double* stats,
   BnActArgs a{static_cast<const __nv_bfloat16*>(h), static_cast<const __nv_bfloat16*>(res),
               static_cast<__nv_bfloat16*>(out), stats, count, gamma, beta, eps, momentum,
               stats ? running_mean : running_mean, stats ? running_var : running_var, num_batches_tracked,
-              mean, invstd, scale, shift, relu_out, pixels};
+              mean, invstd, scale, shift, relu_out, pixels, PeerSync{}, gate};
+  a.peer.world = 1;
+  if (peer && peer->world > 1) {
+    NSG_REQUIRE(stats && gate, "bn_act64_sync: the exchange needs the statistics and a zeroed gate counter");
+    if (int rc = make_peer(peer, &a.peer)) return rc;
+  }
   launch_pdl(bn_act_kernel, dim3(fe_grid(pixels)), dim3(256), 0, static_cast<cudaStream_t>(stream), a);
   NSG_CHECK_LAUNCH("bn_act_kernel");
   return NSG_OK;
 }
 
+int nsg_bn_bwd64_sync(const void* g, const void* h, void* dh, double* stats, double count, const float* mean,
+                      const float* invstd, const float* gamma, float* dgamma, float* dbeta, float* dbias_prev,
+                      long long pixels, const nsg_peer_sync* peer, unsigned int* gate, void* stream);
+
 int nsg_bn_bwd64(const void* g, const void* h, void* dh, const double* stats, double count, const float* mean,
                  const float* invstd, const float* gamma, float* dgamma, float* dbeta, float* dbias_prev,
                  long long pixels, void* stream) {
+  return nsg_bn_bwd64_sync(g, h, dh, const_cast<double*>(stats), count, mean, invstd, gamma, dgamma, dbeta, dbias_prev,
+                           pixels, nullptr, nullptr, stream);
+}
+
+int nsg_bn_bwd64_sync(const void* g, const void* h, void* dh, double* stats, double count, const float* mean,
+                      const float* invstd, const float* gamma, float* dgamma, float* dbeta, float* dbias_prev,
+                      long long pixels, const nsg_peer_sync* peer, unsigned int* gate, void* stream) {
   NSG_REQUIRE(g && h && dh && stats && mean && invstd && gamma, "bn_bwd64: null tensor");
   NSG_REQUIRE(count > 0, "bn_bwd64: count must be positive");
   if (pixels == 0) return NSG_OK;
   BnBwdArgs a{static_cast<const __nv_bfloat16*>(g), static_cast<const __nv_bfloat16*>(h),
-              static_cast<__nv_bfloat16*>(dh), stats, count, mean, invstd, gamma, dgamma, dbeta, dbias_prev, pixels};
+              static_cast<__nv_bfloat16*>(dh), stats, count, mean, invstd, gamma, dgamma, dbeta, dbias_prev, pixels,
+              PeerSync{}, gate};
+  a.peer.world = 1;
+  if (peer && peer->world > 1) {
+    NSG_REQUIRE(gate, "bn_bwd64_sync: the exchange needs a zeroed gate counter");
+    if (int rc = make_peer(peer, &a.peer)) return rc;
+  }
   launch_pdl(bn_bwd_kernel, dim3(fe_grid(pixels)), dim3(256), 0, static_cast<cudaStream_t>(stream), a);
   NSG_CHECK_LAUNCH("bn_bwd_kernel");
   return NSG_OK;

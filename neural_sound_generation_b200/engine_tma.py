@@ -70,6 +70,9 @@ class EngineTMA(object):
         # always fused (config 5: 0.111 ms against 0.123 ms per utterance).
         self.fuse_bn = os.environ.get('NSG_FUSE_BN', '0') == '1'
         self.fuse_bn_eval = os.environ.get('NSG_FUSE_BN_EVAL', '1') != '0'
+        # synchronised BatchNorm over peer memory: the exchange runs INSIDE bn_act / bn_bwd (CTA 0, under the other CTAs'
+        # tensor loads) rather than as a one-CTA kernel of its own in front of them (NSG_PEER_IN_KERNEL=0)
+        self.peer_in_kernel = os.environ.get('NSG_PEER_IN_KERNEL', '1') != '0'
 
     # ------------------------------------------------------------------ packed images
     def _prepare(self, P):
@@ -314,18 +317,29 @@ class EngineTMA(object):
             dwp = self._wgrad_slices(L, g, (b, h, w, oh, ow), x.device)
             self._side(ctx, lambda: ops.conv_wgrad_tma(g, x, dy, dwp, q_colsum=q_colsum, sliced=self.wgrad_sliced), x, dy)
 
+    def _stat_exchange(self, ctx, stats):
+        """Synchronised BatchNorm: (peer, gate) for a kernel that exchanges ``stats`` itself over peer memory, or
+        (None, None) after an ncclAllReduce of them (no peer access) / when nothing is to be exchanged."""
+        if not self._sync():
+            return None, None
+        if self.dp.peer_areas is not None and self.peer_in_kernel:
+            return self.dp.next_peer(), self._bar(ctx)[0:1]
+        self.dp.reduce_stats(stats)         # one-CTA peer kernel, or ncclAllReduce
+        return None, None
+
     def _bn_act(self, ctx, P, Bufs, name, h, res=None, relu_out=True):
         bn = self._bn(ctx, name)
         out = torch.empty_like(h)
         n = h.numel() // self.dim
-        if ctx.training and self.dp is not None and self.dp.sync_bn:
-            self.dp.reduce_stats(bn['fstats'])      # statistics of the GLOBAL batch, as the single-process reference sees
-            n *= self.dp.world
         if ctx.training:
+            # statistics of the GLOBAL batch, as the single-process reference sees them
+            peer, gate = self._stat_exchange(ctx, bn['fstats'])
+            if self._sync():
+                n *= self.dp.world
             ops.bn_act64(h, out, P[name + '.weight'], P[name + '.bias'], stats=bn['fstats'], count=n, res=res,
                          relu_out=relu_out, eps=BN_EPS, momentum=BN_MOMENTUM,
                          running_mean=Bufs[name + '.running_mean'], running_var=Bufs[name + '.running_var'],
-                         nbt=Bufs[name + '.num_batches_tracked'], coef=bn['coef'])
+                         nbt=Bufs[name + '.num_batches_tracked'], coef=bn['coef'], peer=peer, gate=gate)
         else:
             ops.bn_act64(h, out, P[name + '.weight'], P[name + '.bias'], stats=None, res=res, relu_out=relu_out,
                          eps=BN_EPS, running_mean=Bufs[name + '.running_mean'],
@@ -337,14 +351,14 @@ class EngineTMA(object):
         dh = torch.empty_like(h)
         n = h.numel() // self.dim
         dgamma, dbeta = G[name + '.weight'], G[name + '.bias']
-        if self.dp is not None and self.dp.sync_bn:
+        peer, gate = self._stat_exchange(ctx, bn['bstats'])
+        if self._sync():
             # the reduced sums ARE the global dgamma / dbeta: only rank 0 contributes them to the gradient all-reduce
-            self.dp.reduce_stats(bn['bstats'])
             n *= self.dp.world
             if self.dp.rank != 0:
                 dgamma = dbeta = None
         ops.bn_bwd64(g, h, dh, bn['bstats'], n, bn['mean'], bn['invstd'], P[name + '.weight'],
-                     dgamma=dgamma, dbeta=dbeta, dbias_prev=dbias_prev)
+                     dgamma=dgamma, dbeta=dbeta, dbias_prev=dbias_prev, peer=peer, gate=gate)
         return dh
 
     # ------------------------------------------------------------------ ResBlock (models.py:145-158)

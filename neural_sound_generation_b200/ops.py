@@ -479,8 +479,9 @@ def wgrad_unpack_many(items):
 
 
 def bn_act64(h, out, gamma, beta, stats=None, count=1.0, res=None, relu_out=True, eps=1e-5, momentum=0.1,
-             running_mean=None, running_var=None, nbt=None, coef=None):
-    """coef: optional (mean, invstd, scale, shift) fp32 [64] tensors to publish."""
+             running_mean=None, running_var=None, nbt=None, coef=None, peer=None, gate=None):
+    """coef: optional (mean, invstd, scale, shift) fp32 [64] tensors to publish.  peer (ops.peer_sync) + gate (one
+    zeroed int32 counter): the statistics are summed over the GPUs inside the launch (``count`` = global count)."""
     global launch_count
     A.require_device()
     _cuda(h, out, gamma, beta, stats, res, running_mean, running_var)
@@ -488,23 +489,26 @@ def bn_act64(h, out, gamma, beta, stats=None, count=1.0, res=None, relu_out=True
     if h.shape[-1] != 64:
         raise A.NsgError('bn_act64 serves 64-channel tensors')
     cf = coef if coef is not None else (None, None, None, None)
-    rc = A.load().nsg_bn_act64(A.ptr(h), A.ptr(res), A.ptr(out), A.ptr(stats), float(count), A.ptr(gamma),
-                               A.ptr(beta), eps, momentum, A.ptr(running_mean), A.ptr(running_var), A.ptr(nbt),
-                               A.ptr(cf[0]), A.ptr(cf[1]), A.ptr(cf[2]), A.ptr(cf[3]), int(bool(relu_out)),
-                               h.numel() // 64, A.stream_ptr())
+    rc = A.load().nsg_bn_act64_sync(A.ptr(h), A.ptr(res), A.ptr(out), A.ptr(stats), float(count), A.ptr(gamma),
+                                    A.ptr(beta), eps, momentum, A.ptr(running_mean), A.ptr(running_var), A.ptr(nbt),
+                                    A.ptr(cf[0]), A.ptr(cf[1]), A.ptr(cf[2]), A.ptr(cf[3]), int(bool(relu_out)),
+                                    h.numel() // 64, C.pointer(peer) if peer is not None else None, A.ptr(gate),
+                                    A.stream_ptr())
     A.check(rc, 'nsg_bn_act64')
     launch_count += 1
     return out
 
 
-def bn_bwd64(g, h, dh, stats, count, mean, invstd, gamma, dgamma=None, dbeta=None, dbias_prev=None):
+def bn_bwd64(g, h, dh, stats, count, mean, invstd, gamma, dgamma=None, dbeta=None, dbias_prev=None, peer=None,
+             gate=None):
     global launch_count
     A.require_device()
     _cuda(g, h, dh, stats, mean, invstd, gamma)
     _bf16(g, h, dh)
-    rc = A.load().nsg_bn_bwd64(A.ptr(g), A.ptr(h), A.ptr(dh), A.ptr(stats), float(count), A.ptr(mean),
-                               A.ptr(invstd), A.ptr(gamma), A.ptr(dgamma), A.ptr(dbeta), A.ptr(dbias_prev),
-                               h.numel() // 64, A.stream_ptr())
+    rc = A.load().nsg_bn_bwd64_sync(A.ptr(g), A.ptr(h), A.ptr(dh), A.ptr(stats), float(count), A.ptr(mean),
+                                    A.ptr(invstd), A.ptr(gamma), A.ptr(dgamma), A.ptr(dbeta), A.ptr(dbias_prev),
+                                    h.numel() // 64, C.pointer(peer) if peer is not None else None, A.ptr(gate),
+                                    A.stream_ptr())
     A.check(rc, 'nsg_bn_bwd64')
     launch_count += 1
     return dh
