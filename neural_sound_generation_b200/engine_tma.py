@@ -70,9 +70,12 @@ class EngineTMA(object):
         # always fused (config 5: 0.111 ms against 0.123 ms per utterance).
         self.fuse_bn = os.environ.get('NSG_FUSE_BN', '0') == '1'
         self.fuse_bn_eval = os.environ.get('NSG_FUSE_BN_EVAL', '1') != '0'
-        # synchronised BatchNorm over peer memory: the exchange runs INSIDE bn_act / bn_bwd (CTA 0, under the other CTAs'
-        # tensor loads) rather than as a one-CTA kernel of its own in front of them (NSG_PEER_IN_KERNEL=0)
-        self.peer_in_kernel = os.environ.get('NSG_PEER_IN_KERNEL', '1') != '0'
+        # Synchronised BatchNorm over peer memory: the exchange is a one-CTA kernel in front of bn_act / bn_bwd by default;
+        # NSG_PEER_IN_KERNEL=1 runs it INSIDE them (CTA 0 under the other CTAs' tensor loads, a gate for the rest: no
+        # extra launch).  MEASURED (profiles/r2_scale_*): the separate kernel wins -- 0.870 against 0.924 ms at 8 GPUs,
+        # 0.82 against 0.86 ms at 2 -- because the gate holds ALL CTAs of the consumer for the NVLink round trip, while
+        # the separate kernel's round trip overlaps the consumer's launch under programmatic dependent launch.
+        self.peer_in_kernel = os.environ.get('NSG_PEER_IN_KERNEL', '0') == '1'
 
     # ------------------------------------------------------------------ packed images
     def _prepare(self, P):
