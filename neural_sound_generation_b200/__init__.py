@@ -19,3 +19,4 @@ __version__ = '0.1'
 from . import data  # noqa: F401  (device-side mel batch assembly: MelNpyDataset, DeviceMelLoader)
 from . import audio  # noqa: F401  (mel <-> audio: STFT / ISTFT / Griffin-Lim kernels, audio_tacotron.py names)
 from .models_n4 import VAE, GatedActivation, GatedMaskedConv2d, GatedPixelCNN  # noqa: F401  (row N4: the other model families)
+from . import tiled  # noqa: F401  (W-tiled inference of one long utterance, one tile per GPU)

@@ -157,3 +157,78 @@ def test_dataparallel_requires_process_group():
     with pytest.raises(Exception):
         m.engine()
     assert np.isfinite(1.0)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# W-tiled inference of one long utterance (tiled.py): partition logic on CPU with a stand-in model whose encode /
+# decode have the real model's strides and receptive fields (two 4/2/1 convolutions + two 3x3 at latent resolution;
+# two 3x3 + two 4/2/1 transposed convolutions), single process and world-size-2 gloo
+# ---------------------------------------------------------------------------------------------------------------------
+class _StandIn(object):
+    def __init__(self):
+        g = torch.Generator().manual_seed(0)
+        self.w = [torch.randn(4, 1, 4, 4, generator=g, dtype=torch.float64), torch.randn(4, 4, 4, 4, generator=g, dtype=torch.float64),
+                  torch.randn(4, 4, 3, 3, generator=g, dtype=torch.float64), torch.randn(1, 4, 3, 3, generator=g, dtype=torch.float64)]
+        self.d = [torch.randn(4, 1, 3, 3, generator=g, dtype=torch.float64), torch.randn(4, 4, 3, 3, generator=g, dtype=torch.float64),
+                  torch.randn(4, 4, 4, 4, generator=g, dtype=torch.float64), torch.randn(4, 1, 4, 4, generator=g, dtype=torch.float64)]
+
+    def encode(self, x):
+        import torch.nn.functional as F
+        h = F.conv2d(x.double(), self.w[0], None, 2, 1)
+        h = F.conv2d(torch.tanh(h), self.w[1], None, 2, 1)
+        h = F.conv2d(torch.tanh(h), self.w[2], None, 1, 1)
+        h = F.conv2d(torch.tanh(h), self.w[3], None, 1, 1)
+        return (h[:, 0] * 37.0).round().long()
+
+    def decode(self, lat):
+        import torch.nn.functional as F
+        h = F.conv2d(lat.double().unsqueeze(1) / 37.0, self.d[0], None, 1, 1)
+        h = F.conv2d(torch.tanh(h), self.d[1], None, 1, 1)
+        h = F.conv_transpose2d(torch.tanh(h), self.d[2], None, 2, 1)
+        return torch.tanh(F.conv_transpose2d(torch.tanh(h), self.d[3], None, 2, 1)).float()
+
+
+def test_tile_bounds_and_single_process_tiling():
+    from neural_sound_generation_b200 import tiled as T
+    assert T.tile_bounds(10, 3) == [(0, 4), (4, 7), (7, 10)] and T.tile_bounds(2, 5) == [(0, 1), (1, 2)]
+    assert T.halo_range(4, 7, 10, 3) == (1, 10, 3, 3) and T.halo_range(0, 4, 10, 3) == (0, 7, 0, 4)
+    assert T.my_tiles(5, 1, 2) == [1, 3]
+    m = _StandIn()
+    x = torch.rand(1, 1, 16, 163, generator=torch.Generator().manual_seed(1))
+    want_lat = m.encode(x)
+    for n in (1, 2, 3, 7):
+        lat, bounds = T.encode_tiled(m, x, n)
+        assert torch.equal(lat, want_lat), n
+        xt, _ = T.decode_tiled(m, want_lat, n)
+        assert torch.allclose(xt, m.decode(want_lat), atol=1e-6), n
+
+
+def _tiled_worker(rank, world, port, out):
+    import os
+    import torch.distributed as dist
+    from neural_sound_generation_b200 import tiled as T
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    try:
+        m = _StandIn()
+        x = torch.rand(1, 1, 16, 120, generator=torch.Generator().manual_seed(2))
+        lat, xt = T.encode_decode_sharded(m, x, n_tiles=3)
+        ok = torch.equal(lat, m.encode(x)) and torch.allclose(xt, m.decode(m.encode(x)), atol=1e-6)
+        out.put((rank, bool(ok)))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_tiled_inference_sharded_over_two_ranks_gloo():
+    import torch.multiprocessing as mp
+    ctx = mp.get_context('spawn')
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_tiled_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in range(2))
+    for p in procs:
+        p.join(60)
+    assert res == [(0, True), (1, True)]
