@@ -1008,7 +1008,15 @@ int conv_gemm_tma(const nsg_conv_geom* cg, const void* in, const void* packed, c
   const size_t smem = 1024 + (size_t)P.nw * TM_W_BYTES + (size_t)stages * P.slot_bytes + tail;
   CUtensorMap tm[4];
   if (int rc = encode_input_maps(tm, in, cg->batch, cg->in_h, cg->in_w, P.in_stride, P.box_w, P.box_h + halo)) return rc;
-  const int grid = tiles < num_sms() ? tiles : num_sms();
+  int grid = tiles < num_sms() ? tiles : num_sms();
+  // NSG_CONV_BALANCE=1 (experiment): as many CTAs as give every CTA the SAME number of tiles (320 tiles: 107 CTAs x 3
+  // instead of 124 x 2 + 24 x 3) -- the kernel lasts as long as its 3-tile CTAs either way, and fewer CTAs share the
+  // L2 -> shared-memory path that bounds the tile period
+  static const bool balance = [] { const char* v = getenv("NSG_CONV_BALANCE"); return v && v[0] == '1'; }();
+  if (balance && !hold && tiles > grid) {
+    const int per = (tiles + grid - 1) / grid;
+    grid = (tiles + per - 1) / per;
+  }
   if (!hold) return launch_conv_tma<2>(grid, smem, stream, tm, packed, out, e, f, P);
   const int per_cta = (tiles + grid - 1) / grid;
   if (per_cta > 64) {

@@ -76,6 +76,11 @@ class EngineTMA(object):
         # 0.82 against 0.86 ms at 2 -- because the gate holds ALL CTAs of the consumer for the NVLink round trip, while
         # the separate kernel's round trip overlaps the consumer's launch under programmatic dependent launch.
         self.peer_in_kernel = os.environ.get('NSG_PEER_IN_KERNEL', '0') == '1'
+        # The bias of a convolution that feeds a BatchNorm has an analytically ZERO gradient (the normalisation removes any
+        # per-channel constant); the reference computes rounding noise there (1e-9 of the weight gradients).  bn_bwd can
+        # form that noise (column sums of dh, one shared-memory reduction per CTA) or skip it and leave an exact zero:
+        # NSG_PREBN_DBIAS=0 skips.
+        self.prebn_dbias = os.environ.get('NSG_PREBN_DBIAS', '1') != '0'
 
     # ------------------------------------------------------------------ packed images
     def _prepare(self, P):
@@ -361,7 +366,7 @@ class EngineTMA(object):
             if self.dp.rank != 0:
                 dgamma = dbeta = None
         ops.bn_bwd64(g, h, dh, bn['bstats'], n, bn['mean'], bn['invstd'], P[name + '.weight'],
-                     dgamma=dgamma, dbeta=dbeta, dbias_prev=dbias_prev, peer=peer, gate=gate)
+                     dgamma=dgamma, dbeta=dbeta, dbias_prev=dbias_prev if self.prebn_dbias else None, peer=peer, gate=gate)
         return dh
 
     # ------------------------------------------------------------------ ResBlock (models.py:145-158)
