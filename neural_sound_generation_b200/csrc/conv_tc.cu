@@ -161,7 +161,7 @@ tapgemm_tc_kernel(const T* __restrict__ in, const uint8_t* __restrict__ wpacked,
   using Cfg = TcCfg<PASSES>;
   constexpr int STAGES = Cfg::STAGES;
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* sm = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sm = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);    // (pointer arithmetic on the __shared__ array: the compiler keeps the address space -- LDS / STS instead of generic loads)
   uint8_t* tail = sm + STAGES * Cfg::STAGE_BYTES;
   int* rowN = reinterpret_cast<int*>(tail);
   int* rowH = rowN + CT_M;
@@ -515,7 +515,7 @@ wgrad_tc_kernel(const T* __restrict__ P, const T* __restrict__ Q, float* __restr
   constexpr uint32_t SLOT = KP * 128;                 // one bf16 tile: KP pixels x 64 channels
   constexpr int STAGES = 2;
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* sm = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sm = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);    // (pointer arithmetic on the __shared__ array: the compiler keeps the address space -- LDS / STS instead of generic loads)
   const int NS = g.nslots;
   const uint32_t half_bytes = (uint32_t)(NS + 1) * SLOT;                 // P slots + Q, one precision half
   const uint32_t stage_bytes = half_bytes * (SPLIT ? 2 : 1);

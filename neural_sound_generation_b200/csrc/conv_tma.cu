@@ -297,7 +297,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
                 const __grid_constant__ TmaConvParams P) {
   constexpr bool HOLD = NACC > 2;
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* sm = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sm = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);    // (pointer arithmetic on the __shared__ array: the compiler keeps the address space -- LDS / STS instead of generic loads)
   uint8_t* sW = sm;                                         // nw weight images
   uint8_t* sA = sm + (size_t)P.nw * TM_W_BYTES;             // ring of activation boxes
   uint8_t* tail = sA + (size_t)P.stages * P.slot_bytes;
@@ -1008,15 +1008,9 @@ int conv_gemm_tma(const nsg_conv_geom* cg, const void* in, const void* packed, c
   const size_t smem = 1024 + (size_t)P.nw * TM_W_BYTES + (size_t)stages * P.slot_bytes + tail;
   CUtensorMap tm[4];
   if (int rc = encode_input_maps(tm, in, cg->batch, cg->in_h, cg->in_w, P.in_stride, P.box_w, P.box_h + halo)) return rc;
-  int grid = tiles < num_sms() ? tiles : num_sms();
-  // NSG_CONV_BALANCE=1 (experiment): as many CTAs as give every CTA the SAME number of tiles (320 tiles: 107 CTAs x 3
-  // instead of 124 x 2 + 24 x 3) -- the kernel lasts as long as its 3-tile CTAs either way, and fewer CTAs share the
-  // L2 -> shared-memory path that bounds the tile period
-  static const bool balance = [] { const char* v = getenv("NSG_CONV_BALANCE"); return v && v[0] == '1'; }();
-  if (balance && !hold && tiles > grid) {
-    const int per = (tiles + grid - 1) / grid;
-    grid = (tiles + per - 1) / per;
-  }
+  // (one CTA per SM even when that leaves 124 CTAs with 2 tiles and 24 with 3: giving every CTA 3 tiles on 107 CTAs
+  // was measured and is no faster -- 19.0 against 17.5 us for the 3x3 forward, profiles/r2_toggles_ab.txt)
+  const int grid = tiles < num_sms() ? tiles : num_sms();
   if (!hold) return launch_conv_tma<2>(grid, smem, stream, tm, packed, out, e, f, P);
   const int per_cta = (tiles + grid - 1) / grid;
   if (per_cta > 64) {
@@ -1116,7 +1110,7 @@ wgrad_tma_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
                  const __grid_constant__ CUtensorMap tp3, float* __restrict__ dwp, float* __restrict__ colsum,
                  const __grid_constant__ TmaWgradParams P) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* sm = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sm = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);    // (pointer arithmetic on the __shared__ array: the compiler keeps the address space -- LDS / STS instead of generic loads)
   const WgGroup& G = P.g[blockIdx.y];
   uint8_t* sConst = sm + (size_t)P.stages * P.stage_bytes;               // [ones | zeros], WG_SLOT each
   uint64_t* bars = reinterpret_cast<uint64_t*>(sConst + 2 * WG_SLOT);
@@ -1539,7 +1533,7 @@ __global__ void __launch_bounds__(320, 1)
 c1t_conv_kernel(const __nv_bfloat16* __restrict__ in1, const uint8_t* __restrict__ wimg,
                 __nv_bfloat16* __restrict__ out, EpiArgs epi, BnFuse bn, const __grid_constant__ C1tConvParams P) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* sm = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sm = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);    // (pointer arithmetic on the __shared__ array: the compiler keeps the address space -- LDS / STS instead of generic loads)
   uint8_t* sW = sm;                                  // one 64 x 64 image (K >= 16 zero)
   uint8_t* sA = sm + TM_W_BYTES;                     // four patch tiles (tile i uses buffer i & 3)
   __shared__ __align__(16) float sPar[6 * TM_C];
@@ -1805,7 +1799,7 @@ c1t_convT_kernel(const __grid_constant__ CUtensorMap tm, const uint8_t* __restri
                  __nv_bfloat16* __restrict__ out, const float* __restrict__ bias,
                  const __grid_constant__ C1tConvTParams P) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* sm = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sm = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);    // (pointer arithmetic on the __shared__ array: the compiler keeps the address space -- LDS / STS instead of generic loads)
   uint8_t* sW = sm;                                              // 16 tap rows x 64 channels (rows >= 16 zero)
   uint8_t* sA = sm + TM_W_BYTES;                                 // ring of 128-pixel boxes
   float* sP = reinterpret_cast<float*>(sA + (size_t)P.stages * TM_A_BYTES);   // [boxes][16][pstride]
@@ -1971,7 +1965,7 @@ __global__ void __launch_bounds__(192, 1)
 c1t_wgrad_kernel(const __grid_constant__ CUtensorMap tq, const __nv_bfloat16* __restrict__ p1,
                  float* __restrict__ dw, float* __restrict__ q_colsum, const __grid_constant__ C1tWgradParams P) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* sm = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sm = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);    // (pointer arithmetic on the __shared__ array: the compiler keeps the address space -- LDS / STS instead of generic loads)
   constexpr uint32_t STAGE = 3 * C1W_SLOT;            // patch tile (16 taps of 64 "channels"), ones tile, Q box
   __shared__ __align__(8) uint64_t fullQ[WG_MAX_STAGES], fullP[WG_MAX_STAGES], empty[WG_MAX_STAGES], acc_full;
   __shared__ uint32_t tmem_slot;

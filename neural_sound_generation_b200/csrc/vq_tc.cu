@@ -125,7 +125,7 @@ vq_search_tc_kernel(const T* __restrict__ z, const float* __restrict__ cb, const
   constexpr int D = ND * VT_D;
   constexpr uint32_t A_IMG = ND * 16384;     // one image of the z tile: ND K-blocks of 128 rows x 64 bf16
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* sm = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sm = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);    // (pointer arithmetic on the __shared__ array: the compiler keeps the address space -- LDS / STS instead of generic loads)
   uint8_t* A_hi = sm;
   uint8_t* A_lo = sm + A_IMG;                                   // (fp32 z only)
   uint8_t* Bbuf = sm + (kSplitZ ? 2 : 1) * A_IMG;               // 2 x 64 KB
@@ -373,7 +373,7 @@ vq_search_res_kernel(const __grid_constant__ CUtensorMap tmz, const T* __restric
                      double* __restrict__ sqerr) {
   constexpr bool kSplitZ = sizeof(T) == 4;
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* sm = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sm = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);    // (pointer arithmetic on the __shared__ array: the compiler keeps the address space -- LDS / STS instead of generic loads)
   uint8_t* Bres = sm;                                           // nchunks x (hi 32 KB | lo 32 KB)
   uint8_t* Abuf = sm + (size_t)nchunks * VT_CHUNK_BYTES;        // fp32: [2 groups][hi 16 KB | lo 16 KB]; bf16: [4][16 KB]
   float* esq_s = reinterpret_cast<float*>(Abuf + 2 * 32768);    // [nchunks * 256]

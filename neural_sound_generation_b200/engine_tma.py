@@ -77,10 +77,11 @@ class EngineTMA(object):
         # the separate kernel's round trip overlaps the consumer's launch under programmatic dependent launch.
         self.peer_in_kernel = os.environ.get('NSG_PEER_IN_KERNEL', '0') == '1'
         # The bias of a convolution that feeds a BatchNorm has an analytically ZERO gradient (the normalisation removes any
-        # per-channel constant); the reference computes rounding noise there (1e-9 of the weight gradients).  bn_bwd can
-        # form that noise (column sums of dh, one shared-memory reduction per CTA) or skip it and leave an exact zero:
-        # NSG_PREBN_DBIAS=0 skips.
-        self.prebn_dbias = os.environ.get('NSG_PREBN_DBIAS', '1') != '0'
+        # per-channel constant); the reference computes rounding noise there (~1e-9 of the weight gradients), which Adam
+        # then normalises into +-lr steps of a parameter that cannot influence the output.  bn_bwd can form that noise
+        # (column sums of dh: one shared-memory reduction per CTA) or leave the exact zero: skipping is the default
+        # (MEASURED 0.652 against 0.668 ms per step, profiles/r2_toggles_ab.txt); NSG_PREBN_DBIAS=1 computes it.
+        self.prebn_dbias = os.environ.get('NSG_PREBN_DBIAS', '0') == '1'
 
     # ------------------------------------------------------------------ packed images
     def _prepare(self, P):
