@@ -270,11 +270,32 @@ __device__ __forceinline__ void mask_half(float (&x)[32], const uint4 (&r)[4], i
   }
 }
 // the streaming part of the epilogue for one (row, half): x = osc*acc + osh [+ add] [masked] [ReLU]
-__device__ __forceinline__ void epi_half(float (&x)[32], const uint32_t (&acc)[32], const EpiArgs& epi, const float* sPar,
-                                         long long oh, bool valid, int ch0, bool use_add, const uint4 (&radd)[4]) {
+// (per-channel coefficients come from shared memory 4 at a time: 8 LDS.128 per 32 channels instead of 32 LDS.32; the
+// output scale differs from 1 only when eval-mode BatchNorm is folded in -- `scaled` -- and is not even loaded otherwise)
+__device__ __forceinline__ void ld32s(const float* p, float (&v)[32]) {
+  const float4* q = reinterpret_cast<const float4*>(p);
 #pragma unroll
-  for (int j = 0; j < 32; ++j)
-    x[j] = valid ? fmaf(__uint_as_float(acc[j]), sPar[5 * TM_C + ch0 + j], sPar[ch0 + j]) : 0.f;
+  for (int i = 0; i < 8; ++i) {
+    const float4 t = q[i];
+    v[4 * i] = t.x; v[4 * i + 1] = t.y; v[4 * i + 2] = t.z; v[4 * i + 3] = t.w;
+  }
+}
+__device__ __forceinline__ void epi_half(float (&x)[32], const uint32_t (&acc)[32], const EpiArgs& epi, const float* sPar,
+                                         long long oh, bool valid, int ch0, bool use_add, const uint4 (&radd)[4],
+                                         bool scaled) {
+  {
+    float sh[32];
+    ld32s(sPar + ch0, sh);
+    if (scaled) {
+      float sc[32];
+      ld32s(sPar + 5 * TM_C + ch0, sc);
+#pragma unroll
+      for (int j = 0; j < 32; ++j) x[j] = valid ? fmaf(__uint_as_float(acc[j]), sc[j], sh[j]) : 0.f;
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) x[j] = valid ? __uint_as_float(acc[j]) + sh[j] : 0.f;
+    }
+  }
   if (use_add) add_half(x, radd);
   if (valid && epi.mask_mode != NSG_MASK_NONE) {
     uint4 rm[4];
@@ -528,7 +549,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
         mbar_arrive(&acc_empty[as]);
       }
       float x[32];
-      epi_half(x, acc, epi, sPar, oh, valid, ch0, use_add, radd);
+      epi_half(x, acc, epi, sPar, oh, valid, ch0, use_add, radd, bn.mode == NSG_BNF_EVAL);
       if (valid && out != nullptr) {
         st16bf(out + oh, &x[0]);
         st16bf(out + oh + 16, &x[16]);
@@ -538,15 +559,17 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
           if (valid) {
             uint4 rx[4];
             ld_half(epi.xhat_src, oh, rx);
+            float mu[32], is[32];
+            ld32s(sPar + 3 * TM_C + ch0, mu);
+            ld32s(sPar + 4 * TM_C + ch0, is);
 #pragma unroll
             for (int g8 = 0; g8 < 4; ++g8) {
               float hx[8];
               unpack8bf(rx[g8], hx);
 #pragma unroll
               for (int j = 0; j < 8; ++j) {
-                const int ch = ch0 + g8 * 8 + j;
                 s1[g8 * 8 + j] += x[g8 * 8 + j];
-                s2[g8 * 8 + j] = fmaf(x[g8 * 8 + j], (hx[j] - sPar[3 * TM_C + ch]) * sPar[4 * TM_C + ch], s2[g8 * 8 + j]);
+                s2[g8 * 8 + j] = fmaf(x[g8 * 8 + j], (hx[j] - mu[g8 * 8 + j]) * is[g8 * 8 + j], s2[g8 * 8 + j]);
               }
             }
           }
@@ -668,7 +691,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
         if (train) {
           if (in_tmem) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) x[j] = fmaf(__uint_as_float(acc[j]), sPar[5 * TM_C + ch0 + j], sPar[ch0 + j]);
+            for (int j = 0; j < 32; ++j) x[j] = __uint_as_float(acc[j]) + sPar[ch0 + j];       // (TRAIN: output scale 1)
           }
 #pragma unroll
           for (int j = 0; j < 32; ++j) x[j] = fmaf(x[j], sPar[6 * TM_C + ch0 + j], sPar[7 * TM_C + ch0 + j]);
@@ -678,7 +701,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
             for (int j = 0; j < 32; ++j) x[j] = fmaxf(x[j], 0.f);
           }
         } else {
-          if (in_tmem) epi_half(x, acc, epi, sPar, oh, true, ch0, use_add, radd);     // g, exactly as pass 1 formed it
+          if (in_tmem) epi_half(x, acc, epi, sPar, oh, true, ch0, use_add, radd, false);     // g, exactly as pass 1 formed it
 #pragma unroll
           for (int g8 = 0; g8 < 4; ++g8) {
             float hx[8];
@@ -1681,7 +1704,7 @@ c1t_conv_kernel(const __nv_bfloat16* __restrict__ in1, const uint8_t* __restrict
       tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(i & 3) * TM_C + (uint32_t)ch0, acc);
       tmem_ld_wait();
       float x[32];
-      epi_half(x, acc, epi, sPar, oh, valid, ch0, use_add, radd);
+      epi_half(x, acc, epi, sPar, oh, valid, ch0, use_add, radd, bn.mode == NSG_BNF_EVAL);
       if (valid) {
         st16bf(out + oh, &x[0]);
         st16bf(out + oh + 16, &x[16]);
@@ -1691,15 +1714,17 @@ c1t_conv_kernel(const __nv_bfloat16* __restrict__ in1, const uint8_t* __restrict
           if (valid) {
             uint4 rx[4];
             ld_half(epi.xhat_src, oh, rx);
+            float mu[32], is[32];
+            ld32s(sPar + 3 * TM_C + ch0, mu);
+            ld32s(sPar + 4 * TM_C + ch0, is);
 #pragma unroll
             for (int g8 = 0; g8 < 4; ++g8) {
               float hx[8];
               unpack8bf(rx[g8], hx);
 #pragma unroll
               for (int j = 0; j < 8; ++j) {
-                const int ch = ch0 + g8 * 8 + j;
                 s1[g8 * 8 + j] += x[g8 * 8 + j];
-                s2[g8 * 8 + j] = fmaf(x[g8 * 8 + j], (hx[j] - sPar[3 * TM_C + ch]) * sPar[4 * TM_C + ch], s2[g8 * 8 + j]);
+                s2[g8 * 8 + j] = fmaf(x[g8 * 8 + j], (hx[j] - mu[g8 * 8 + j]) * is[g8 * 8 + j], s2[g8 * 8 + j]);
               }
             }
           }
