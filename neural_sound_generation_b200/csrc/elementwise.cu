@@ -335,6 +335,23 @@ adam_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m,
   pdl_wait();
   pdl_trigger();
   __shared__ float s_step_size, s_bc2_sqrt;
+  const long long nv = n / VEC;
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  // The first (at this model's size: the only) batch of loads is requested BEFORE the bias corrections are derived:
+  // two double-precision pow() calls by one thread and the barrier behind them are several microseconds during which
+  // the tensors would otherwise not even have been asked for.
+  float4 g4 = make_float4(0.f, 0.f, 0.f, 0.f), m4 = g4, v4 = g4, p4 = g4;
+  float g1 = 0.f, m1 = 0.f, v1 = 0.f, p1 = 0.f;
+  auto request = [&](long long j) {
+    if (j >= nv) return;
+    if (VEC == 4) {
+      g4 = reinterpret_cast<const float4*>(g)[j]; m4 = reinterpret_cast<const float4*>(m)[j];
+      v4 = reinterpret_cast<const float4*>(v)[j]; p4 = reinterpret_cast<const float4*>(p)[j];
+    } else {
+      g1 = g[j]; m1 = m[j]; v1 = v[j]; p1 = p[j];
+    }
+  };
+  request(i);
   if (threadIdx.x == 0) {
     const double t = (double)(*step_count + 1);
     const double bc1 = 1.0 - pow((double)b1, t);
@@ -344,20 +361,17 @@ adam_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m,
   }
   __syncthreads();
   const float step_size = s_step_size, bc2_sqrt = s_bc2_sqrt;
-  const long long nv = n / VEC;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nv;
-       i += (long long)gridDim.x * blockDim.x) {
+  for (; i < nv; i += (long long)gridDim.x * blockDim.x) {
     float gr[VEC], mi[VEC], vi[VEC], pi[VEC];
     if (VEC == 4) {
-      const float4 g4 = reinterpret_cast<const float4*>(g)[i], m4 = reinterpret_cast<const float4*>(m)[i];
-      const float4 v4 = reinterpret_cast<const float4*>(v)[i], p4 = reinterpret_cast<const float4*>(p)[i];
       gr[0] = g4.x; gr[1 % VEC] = g4.y; gr[2 % VEC] = g4.z; gr[3 % VEC] = g4.w;
       mi[0] = m4.x; mi[1 % VEC] = m4.y; mi[2 % VEC] = m4.z; mi[3 % VEC] = m4.w;
       vi[0] = v4.x; vi[1 % VEC] = v4.y; vi[2 % VEC] = v4.z; vi[3 % VEC] = v4.w;
       pi[0] = p4.x; pi[1 % VEC] = p4.y; pi[2 % VEC] = p4.z; pi[3 % VEC] = p4.w;
     } else {
-      gr[0] = g[i]; mi[0] = m[i]; vi[0] = v[i]; pi[0] = p[i];
+      gr[0] = g1; mi[0] = m1; vi[0] = v1; pi[0] = p1;
     }
+    request(i + (long long)gridDim.x * blockDim.x);
 #pragma unroll
     for (int e = 0; e < VEC; ++e) {
       const float ge = gr[e] * gscale;

@@ -304,23 +304,42 @@ vq_bwd_stats_kernel(const __nv_bfloat16* __restrict__ g_st, const __nv_bfloat16*
     is[i] = stats ? __ldg(invstd + c0 + i) : 0.f;
     s1[i] = s2[i] = 0.f;
   }
-  for (long long p = (long long)blockIdx.x * 32 + (tid >> 3); p < pixels; p += (long long)gridDim.x * 32) {
-    const long long o = p * FE_C + c0;
-    float gv[8], zv[8], qv[8], hv[8];
-    fe_ld8(z + o, zv);
-    if (zq) fe_ld8(zq + o, qv);
-    if (g_st) fe_ld8(g_st + o, gv);
-    if (stats) fe_ld8(h + o, hv);
+  // 4 pixels per thread and iteration, every load of the iteration requested before the first use (one memory round
+  // trip per 128 pixels of a CTA instead of four)
+  for (long long p0 = (long long)blockIdx.x * 128 + (tid >> 3); p0 < pixels; p0 += (long long)gridDim.x * 128) {
+    uint4 rz[4], rq[4], rg[4], rh[4];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const float d = (g_st ? gv[i] : 0.f) + coef * (zv[i] - (zq ? qv[i] : 0.f));
-      gv[i] = d;
-      if (stats) {
-        s1[i] += d;
-        s2[i] = fmaf(d, (hv[i] - mu[i]) * is[i], s2[i]);
+    for (int u = 0; u < 4; ++u) {
+      const long long p = p0 + 32 * u;
+      if (p < pixels) {
+        const long long o = p * FE_C + c0;
+        rz[u] = __ldg(reinterpret_cast<const uint4*>(z + o));
+        if (zq) rq[u] = __ldg(reinterpret_cast<const uint4*>(zq + o));
+        if (g_st) rg[u] = __ldg(reinterpret_cast<const uint4*>(g_st + o));
+        if (stats) rh[u] = __ldg(reinterpret_cast<const uint4*>(h + o));
       }
     }
-    fe_st8(dz + o, gv);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const long long p = p0 + 32 * u;
+      if (p >= pixels) break;
+      const long long o = p * FE_C + c0;
+      float gv[8], zv[8], qv[8], hv[8];
+      fe_unpack(rz[u], zv);
+      if (zq) fe_unpack(rq[u], qv);
+      if (g_st) fe_unpack(rg[u], gv);
+      if (stats) fe_unpack(rh[u], hv);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float d = (g_st ? gv[i] : 0.f) + coef * (zv[i] - (zq ? qv[i] : 0.f));
+        gv[i] = d;
+        if (stats) {
+          s1[i] += d;
+          s2[i] = fmaf(d, (hv[i] - mu[i]) * is[i], s2[i]);
+        }
+      }
+      fe_st8(dz + o, gv);
+    }
   }
   if (stats) {
     fe_channel_reduce<double>(s1, sred, stats, c0);
