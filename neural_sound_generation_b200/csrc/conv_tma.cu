@@ -53,7 +53,8 @@ struct TmaPhase {
   int out_stride, off_h, off_w;  // oh = ohs * out_stride + off_h
   signed char gdh[TM_MAX_TAPS], gdw[TM_MAX_TAPS];          // per group: box origin relative to the tile origin
   unsigned char gmap[TM_MAX_TAPS], gfirst[TM_MAX_TAPS + 1];  // per group: tensor map, first tap (taps sorted by group)
-  unsigned char roff[TM_MAX_TAPS], wslot[TM_MAX_TAPS];     // per tap: row offset inside the box, weight image
+  unsigned short aoff[TM_MAX_TAPS];                        // per tap: offset of its sub-block inside the box, 16-byte units
+  unsigned char wslot[TM_MAX_TAPS];                        // per tap: weight image
 };
 
 struct TmaConvParams {
@@ -61,7 +62,10 @@ struct TmaConvParams {
   int in_stride;                 // 1: one tensor map; 2: four parity maps
   int box_w, box_h, log2_bw;
   int halo;                      // extra box rows shared by vertically shifted taps
-  uint32_t slot_bytes, row_bytes;  // one ring slot ((box_h + halo) rows); one box row (box_w pixels)
+  uint32_t slot_bytes, row_bytes;  // one ring slot; one box row (pixels per box line x 128 bytes)
+  uint32_t box_bytes;            // bytes one TMA box delivers (<= slot_bytes: slots are 1024-byte multiples)
+  uint32_t sbo16;                // byte distance between the 8-pixel groups of the A operand, 16-byte units
+  int swap;                      // 1: the box's fast pixel axis is H ("w" quantities of the tile grid run along H)
   int nphases, total_tiles, nw, stages;
   unsigned long long* dbg;       // optional clock64 stamps of CTA 0 (nsg_debug_timeline), null in production
   int w_early;                   // 1: the weight images were written >= 2 kernels back: load them above pdl_wait()
@@ -355,11 +359,11 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
     const int e = tid - 64, p = e >> 4, t = e & 15;
     if (p < P.nphases) {
       const TmaPhase& ph = P.ph[p];
-      sTapA[e] = ((uint32_t)ph.roff[t] * P.row_bytes) >> 4;
+      sTapA[e] = (uint32_t)ph.aoff[t];
       sTapB[e] = (((smem_u32(sW) + (uint32_t)ph.wslot[t] * TM_W_BYTES) >> 4) & 0x3FFFu) | (1u << 16);
       const int gcount = t < ph.ngroups ? (int)ph.gfirst[t + 1] - (int)ph.gfirst[t] : 0;
       sGrp[e] = (int)ph.gmap[t] | (((int)ph.gdw[t] + 128) << 8) | (((int)ph.gdh[t] + 128) << 16) |
-                ((int)ph.gfirst[t] << 24) | (gcount << 28);
+                ((int)ph.gfirst[t] << 24) | ((gcount > 0 ? gcount - 1 : 0) << 28);       // (count - 1: up to 16 taps)
     }
   }
   if (tid >= 128 && tid < 128 + TM_TILE_TABLE) {
@@ -412,7 +416,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
         const int w0 = tl.tw * P.box_w, h0 = tl.th * P.box_h;
         for (int g = 0; g < ngroups; ++g, ++it) {
           mbar_wait(&empty[s], eparity);
-          mbar_arrive_expect_tx(&full[s], slot_bytes);
+          mbar_arrive_expect_tx(&full[s], P.box_bytes);
           const int gi = sGrp[tl.p * TM_MAX_TAPS + g];
           const int par = gi & 3;
           const CUtensorMap* tm = par == 0 ? &tm0 : (par == 1 ? &tm1 : (par == 2 ? &tm2 : &tm3));
@@ -436,7 +440,12 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
       uint32_t fparity = 0;
       const uint32_t slot_units = P.slot_bytes >> 4;
       const uint32_t a_base = ((smem_u32(sA) >> 4) & 0x3FFFu) | (1u << 16);     // low word of sw128_desc(sA)
-      constexpr uint64_t DESC_HI = (64ull << 32) | (1ull << 46) | (2ull << 61);
+      // SWIZZLE_128B K-major descriptors.  A: 8-pixel groups P.sbo16 * 16 bytes apart (1024 when a tile line is a whole
+      // number of groups; the box line pitch in the one-box form, where a group is ONE box line of 8 pixels and the
+      // +-1-pixel taps start 128 bytes off the swizzle atom -- the hardware applies the swizzle to the absolute
+      // shared-memory address, exactly as the TMA unit wrote it: tools/microbench/desc_probe.cu).  B: the weight images.
+      const uint64_t DESC_A_HI = ((uint64_t)P.sbo16 << 32) | (1ull << 46) | (2ull << 61);
+      constexpr uint64_t DESC_B_HI = (64ull << 32) | (1ull << 46) | (2ull << 61);
       for (int i = 0; i < ntiles_mine; ++i) {
         const TmaTile tl = fetch_tile(P, sTile, i);
         const TmaPhase& ph = P.ph[tl.p];
@@ -448,10 +457,10 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
         tc_fence_after();
         const uint32_t d = tmem_base + (uint32_t)as * TM_ACC_COLS;
         for (int g = 0; g < ngroups; ++g, ++it) {
-          // this group's (<= 4) tap descriptors are fetched before the box wait: the issuing thread runs dependent
-          // scalar code, so every load left between two tcgen05.mma shows up as an idle tensor pipe
+          // the group's tap descriptors are fetched four at a time before they are needed: the issuing thread runs
+          // dependent scalar code, so every load left between two tcgen05.mma shows up as an idle tensor pipe
           const uint32_t gi = (uint32_t)sGrp[tl.p * TM_MAX_TAPS + g];
-          const int first = (gi >> 24) & 15, cnt = gi >> 28;
+          const int first = (gi >> 24) & 15, cnt = (int)(gi >> 28) + 1;
           uint32_t ao[4], bo[4];
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
@@ -464,16 +473,30 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
           if (i == 1 && g < 3) tm_stamp(P.dbg, 21 + 3 * g);      // 21,24,27: tile 1, box of group g landed
           tc_fence_after();
           const uint32_t box = a_base + (uint32_t)s * slot_units;
+          for (int j0 = 0; j0 < cnt; j0 += 4) {
+            uint32_t an[4], bn_[4];
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            if (j < cnt) {
-              const uint64_t a = DESC_HI | (uint64_t)(box + ao[j]);
-              const uint64_t b = DESC_HI | (uint64_t)bo[j];
-              const uint32_t accum = (first + j) != 0;
+            for (int j = 0; j < 4; ++j) {                // (the next four, for groups of more than four taps)
+              const int e = tl.p * TM_MAX_TAPS + ((first + j0 + 4 + j) & 15);
+              an[j] = sTapA[e];
+              bn_[j] = sTapB[e];
+            }
 #pragma unroll
-              for (int ks = 0; ks < 4; ++ks)
-                umma_bf16(d + (ks % TM_CHAINS) * TM_C, a + 2 * ks, b + 2 * ks, idesc,
-                          (ks >= TM_CHAINS) ? 1u : accum);
+            for (int j = 0; j < 4; ++j) {
+              if (j0 + j < cnt) {
+                const uint64_t a = DESC_A_HI | (uint64_t)(box + ao[j]);
+                const uint64_t b = DESC_B_HI | (uint64_t)bo[j];
+                const uint32_t accum = (first + j0 + j) != 0;
+#pragma unroll
+                for (int ks = 0; ks < 4; ++ks)
+                  umma_bf16(d + (ks % TM_CHAINS) * TM_C, a + 2 * ks, b + 2 * ks, idesc,
+                            (ks >= TM_CHAINS) ? 1u : accum);
+              }
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              ao[j] = an[j];
+              bo[j] = bn_[j];
             }
           }
           if (i == 1 && g < 3) tm_stamp(P.dbg, 22 + 3 * g);      // 22,25,28: its instructions issued
@@ -526,7 +549,9 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
     auto row_offset = [&](int i, bool& valid) -> long long {
       const TmaTile tl = fetch_tile(P, sTile, i);
       const TmaPhase& ph = P.ph[tl.p];
-      const int ohs = tl.th * P.box_h + bh, ows = tl.tw * P.box_w + bw;
+      // (tile grid "w" / "h" = the box's fast / slow pixel axis: W / H, or H / W when P.swap)
+      const int fi = tl.tw * P.box_w + bw, si = tl.th * P.box_h + bh;
+      const int ohs = P.swap ? fi : si, ows = P.swap ? si : fi;
       valid = ohs < ph.sub_h && ows < ph.sub_w;
       return valid ? ((((long long)tl.n * P.full_h + (ohs * ph.out_stride + ph.off_h)) * P.full_w +
                        (ows * ph.out_stride + ph.off_w)) * TM_C + ch0) : 0;
@@ -830,12 +855,16 @@ static void pick_box(const TapGeom* phases, const TapGroups* groups, int np, int
 
 // tensor maps over `in` (N, in_h, in_w, 64) bf16: plain view (in_stride 1) or the four parity views (in_stride 2)
 static int encode_input_maps(CUtensorMap* tm, const void* in, int batch, int in_h, int in_w, int in_stride, int box_w,
-                             int box_h) {
+                             int box_h, int swap = 0) {
+  // swap: the box's fast pixel axis (tensor-map dimension 1) is H instead of W
   const long long C = TM_C;
+  auto enc = [&](CUtensorMap* t, const void* base, long long dw_, long long dh_, long long ws, long long hs) -> int {
+    if (swap)
+      return tma::encode_nhwc64(t, base, dh_, dw_, batch, hs, ws, (long long)in_h * in_w * C, box_w, box_h);
+    return tma::encode_nhwc64(t, base, dw_, dh_, batch, ws, hs, (long long)in_h * in_w * C, box_w, box_h);
+  };
   if (in_stride == 1) {
-    if (int rc = tma::encode_nhwc64(&tm[0], in, in_w, in_h, batch, C, (long long)in_w * C, (long long)in_h * in_w * C,
-                                    box_w, box_h))
-      return rc;
+    if (int rc = enc(&tm[0], in, in_w, in_h, C, (long long)in_w * C)) return rc;
     tm[1] = tm[2] = tm[3] = tm[0];
     return NSG_OK;
   }
@@ -844,14 +873,10 @@ static int encode_input_maps(CUtensorMap* tm, const void* in, int batch, int in_
       const __nv_bfloat16* base = static_cast<const __nv_bfloat16*>(in) + ((long long)ph * in_w + pw) * C;
       const long long dw_ = (in_w - pw + 1) / 2, dh_ = (in_h - ph + 1) / 2;
       if (dw_ < 1 || dh_ < 1) {       // degenerate parity view (1-pixel-wide tensor): never addressed in range
-        if (int rc = tma::encode_nhwc64(&tm[ph * 2 + pw], in, 1, 1, batch, 2 * C, 2LL * in_w * C,
-                                        (long long)in_h * in_w * C, box_w, box_h))
-          return rc;
+        if (int rc = enc(&tm[ph * 2 + pw], in, 1, 1, 2 * C, 2LL * in_w * C)) return rc;
         continue;
       }
-      if (int rc = tma::encode_nhwc64(&tm[ph * 2 + pw], base, dw_, dh_, batch, 2 * C, 2LL * in_w * C,
-                                      (long long)in_h * in_w * C, box_w, box_h))
-        return rc;
+      if (int rc = enc(&tm[ph * 2 + pw], base, dw_, dh_, 2 * C, 2LL * in_w * C)) return rc;
     }
   return NSG_OK;
 }
@@ -984,10 +1009,63 @@ int conv_gemm_tma(const nsg_conv_geom* cg, const void* in, const void* packed, c
     group_taps(phases[i], &groups[i]);
     if (phases[i].sub_h > 0 && phases[i].sub_w > 0 && groups[i].halo > halo) halo = groups[i].halo;
   }
-  pick_box(phases, groups, np, cg->batch, TM_M, halo, &P.box_w, &P.box_h, &P.log2_bw);
-  P.halo = halo;
-  P.row_bytes = (uint32_t)P.box_w * 128;
-  P.slot_bytes = (uint32_t)(P.box_h + halo) * P.row_bytes;
+  // ONE box per (tile, tensor map) for kernels wider than one pixel.  The tile is 8 pixels along the box's fast pixel
+  // axis x 16 lines; the box carries the halo pixels of BOTH axes, and tap (dh, dw) reads the sub-block that starts
+  // (its line shift x line pitch + its pixel shift) x 128 bytes into the box: a group of 8 A rows is one box line, the
+  // descriptor's group stride (SBO) is the line pitch, and a start 128 bytes off the 1024-byte swizzle atom is legal
+  // because the tensor core swizzles on the absolute shared-memory address, as the TMA unit does when it writes
+  // (tools/microbench/desc_probe.cu: every tap of a 3 x 3 kernel from one 10 x 18-pixel box).  A 3 x 3 tile then loads
+  // 23 KB instead of three 24 KB boxes -- the L2 -> shared-memory path is what bounds these kernels.  The fast axis is
+  // whichever of W / H leaves fewer ragged tiles (20 x 64 latent grid: H, 3 x 4 tiles per image).
+  static const bool one_box_enabled = [] { const char* v = getenv("NSG_CONV_ONE_BOX"); return !(v && v[0] == '0'); }();
+  bool one_box = one_box_enabled && cg->ksize > 1;
+  int hf[2] = {0, 0}, hs[2] = {0, 0};                   // halo along the fast / slow axis, per orientation
+  long long ntile[2] = {0, 0};
+  if (one_box) {
+    for (int sw = 0; sw < 2; ++sw)
+      for (int i = 0; i < np; ++i) {
+        const TapGeom& g = phases[i];
+        if (g.sub_h <= 0 || g.sub_w <= 0) continue;
+        const int ef = sw ? g.sub_h : g.sub_w, es = sw ? g.sub_w : g.sub_h;
+        ntile[sw] += (long long)((ef + 7) / 8) * ((es + 15) / 16) * cg->batch;
+        for (int m = 0; m < 4; ++m) {                   // per tensor map: the span of its taps on either axis
+          int lo_f = 1 << 20, hi_f = -(1 << 20), lo_s = 1 << 20, hi_s = -(1 << 20);
+          for (int t = 0; t < g.ntaps; ++t) {
+            int map = 0, dw = g.dw[t], dh = g.dh[t];
+            if (g.in_stride == 2) {
+              map = (dh & 1) * 2 + (dw & 1);
+              dw >>= 1;
+              dh >>= 1;
+            }
+            if (map != m) continue;
+            const int df = sw ? dh : dw, ds = sw ? dw : dh;
+            if (df < lo_f) lo_f = df;
+            if (df > hi_f) hi_f = df;
+            if (ds < lo_s) lo_s = ds;
+            if (ds > hi_s) hi_s = ds;
+          }
+          if (hi_f >= lo_f && hi_f - lo_f > hf[sw]) hf[sw] = hi_f - lo_f;
+          if (hi_s >= lo_s && hi_s - lo_s > hs[sw]) hs[sw] = hi_s - lo_s;
+        }
+      }
+  }
+  P.swap = 0;
+  if (one_box) {
+    P.swap = ntile[1] < ntile[0] ? 1 : 0;
+    P.box_w = 8; P.box_h = 16; P.log2_bw = 3;
+    P.halo = hs[P.swap];
+    P.row_bytes = (uint32_t)(8 + hf[P.swap]) * 128;                       // one box line
+    P.box_bytes = (uint32_t)(16 + hs[P.swap]) * P.row_bytes;
+    P.slot_bytes = (P.box_bytes + 1023u) & ~1023u;
+    P.sbo16 = P.row_bytes >> 4;
+  } else {
+    pick_box(phases, groups, np, cg->batch, TM_M, halo, &P.box_w, &P.box_h, &P.log2_bw);
+    P.halo = halo;
+    P.row_bytes = (uint32_t)P.box_w * 128;
+    P.slot_bytes = (uint32_t)(P.box_h + halo) * P.row_bytes;
+    P.box_bytes = P.slot_bytes;
+    P.sbo16 = 1024 >> 4;
+  }
   P.nw = cg->ksize * cg->ksize;
   int tiles = 0, nph = 0;
   for (int i = 0; i < np; ++i) {
@@ -996,27 +1074,64 @@ int conv_gemm_tma(const nsg_conv_geom* cg, const void* in, const void* packed, c
     NSG_REQUIRE(g.ntaps > 0, "conv_gemm_tma: a stride phase without taps (ksize < stride) is not supported");
     TmaPhase& ph = P.ph[nph++];
     ph.sub_h = g.sub_h; ph.sub_w = g.sub_w;
-    ph.tiles_w = (g.sub_w + P.box_w - 1) / P.box_w;
-    ph.tiles_h = (g.sub_h + P.box_h - 1) / P.box_h;
+    const int ef = P.swap ? g.sub_h : g.sub_w, es = P.swap ? g.sub_w : g.sub_h;
+    ph.tiles_w = (ef + P.box_w - 1) / P.box_w;
+    ph.tiles_h = (es + P.box_h - 1) / P.box_h;
     ph.tile0 = tiles;
     tiles += ph.tiles_w * ph.tiles_h * cg->batch;
     ph.ntaps = g.ntaps;
     ph.out_stride = g.out_stride; ph.off_h = g.off_h; ph.off_w = g.off_w;
-    const TapGroups& tg = groups[i];
-    ph.ngroups = tg.ngroups;
     int nt = 0;
-    for (int gi = 0; gi < tg.ngroups; ++gi) {
-      ph.gmap[gi] = (unsigned char)tg.gmap[gi];
-      ph.gdw[gi] = (signed char)tg.gdw[gi];
-      ph.gdh[gi] = (signed char)tg.gdh[gi];
-      ph.gfirst[gi] = (unsigned char)nt;
-      for (int j = 0; j < tg.gcount[gi]; ++j, ++nt) {
-        const int t = tg.tap[gi][j];
-        ph.roff[nt] = (unsigned char)(tg.edh[t] - tg.gdh[gi]);
-        ph.wslot[nt] = (unsigned char)g.woff[t];
+    if (one_box) {
+      // groups = the tensor maps that have taps; box origin = the least shift on either axis
+      int ng = 0;
+      for (int m = 0; m < 4; ++m) {
+        int lo_f = 1 << 20, lo_s = 1 << 20, cnt = 0;
+        int df[TM_MAX_TAPS], ds[TM_MAX_TAPS], ti[TM_MAX_TAPS];
+        for (int t = 0; t < g.ntaps; ++t) {
+          int map = 0, dw = g.dw[t], dh = g.dh[t];
+          if (g.in_stride == 2) {
+            map = (dh & 1) * 2 + (dw & 1);
+            dw >>= 1;
+            dh >>= 1;
+          }
+          if (map != m) continue;
+          df[cnt] = P.swap ? dh : dw;
+          ds[cnt] = P.swap ? dw : dh;
+          ti[cnt] = t;
+          if (df[cnt] < lo_f) lo_f = df[cnt];
+          if (ds[cnt] < lo_s) lo_s = ds[cnt];
+          ++cnt;
+        }
+        if (cnt == 0) continue;
+        ph.gmap[ng] = (unsigned char)m;
+        ph.gdw[ng] = (signed char)lo_f;
+        ph.gdh[ng] = (signed char)lo_s;
+        ph.gfirst[ng] = (unsigned char)nt;
+        for (int j = 0; j < cnt; ++j, ++nt) {
+          ph.aoff[nt] = (unsigned short)((((uint32_t)(ds[j] - lo_s) * P.row_bytes) + (uint32_t)(df[j] - lo_f) * 128u) >> 4);
+          ph.wslot[nt] = (unsigned char)g.woff[ti[j]];
+        }
+        ++ng;
       }
+      ph.ngroups = ng;
+      ph.gfirst[ng] = (unsigned char)nt;
+    } else {
+      const TapGroups& tg = groups[i];
+      ph.ngroups = tg.ngroups;
+      for (int gi = 0; gi < tg.ngroups; ++gi) {
+        ph.gmap[gi] = (unsigned char)tg.gmap[gi];
+        ph.gdw[gi] = (signed char)tg.gdw[gi];
+        ph.gdh[gi] = (signed char)tg.gdh[gi];
+        ph.gfirst[gi] = (unsigned char)nt;
+        for (int j = 0; j < tg.gcount[gi]; ++j, ++nt) {
+          const int t = tg.tap[gi][j];
+          ph.aoff[nt] = (unsigned short)(((uint32_t)(tg.edh[t] - tg.gdh[gi]) * P.row_bytes) >> 4);
+          ph.wslot[nt] = (unsigned char)g.woff[t];
+        }
+      }
+      ph.gfirst[tg.ngroups] = (unsigned char)nt;
     }
-    ph.gfirst[tg.ngroups] = (unsigned char)nt;
   }
   if (tiles == 0) return NSG_OK;
   P.nphases = nph;
@@ -1030,7 +1145,9 @@ int conv_gemm_tma(const nsg_conv_geom* cg, const void* in, const void* packed, c
   P.w_early = pdl_weights_settled(stream) ? 1 : 0;
   const size_t smem = 1024 + (size_t)P.nw * TM_W_BYTES + (size_t)stages * P.slot_bytes + tail;
   CUtensorMap tm[4];
-  if (int rc = encode_input_maps(tm, in, cg->batch, cg->in_h, cg->in_w, P.in_stride, P.box_w, P.box_h + halo)) return rc;
+  if (int rc = encode_input_maps(tm, in, cg->batch, cg->in_h, cg->in_w, P.in_stride,
+                                 one_box ? 8 + hf[P.swap] : P.box_w, one_box ? 16 + hs[P.swap] : P.box_h + halo, P.swap))
+    return rc;
   // (one CTA per SM even when that leaves 124 CTAs with 2 tiles and 24 with 3: giving every CTA 3 tiles on 107 CTAs
   // was measured and is no faster -- 19.0 against 17.5 us for the 3x3 forward, profiles/r2_toggles_ab.txt)
   const int grid = tiles < num_sms() ? tiles : num_sms();
