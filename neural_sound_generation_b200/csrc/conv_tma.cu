@@ -29,6 +29,7 @@ namespace nsg {
 using namespace tc;
 
 constexpr int TM_M = 128;                       // pixels per tile
+constexpr int TM_THREADS = 352;                 // conv_tma_kernel: producer warp, 2 MMA-issuing warps, 8 epilogue warps
 constexpr int TM_C = 64;                        // channels
 constexpr uint32_t TM_A_BYTES = TM_M * 128;     // one activation box
 constexpr uint32_t TM_W_BYTES = TM_C * 128;     // one tap's weight image (bf16, K-major SWIZZLE_128B)
@@ -66,6 +67,7 @@ struct TmaConvParams {
   uint32_t box_bytes;            // bytes one TMA box delivers (<= slot_bytes: slots are 1024-byte multiples)
   uint32_t sbo16;                // byte distance between the 8-pixel groups of the A operand, 16-byte units
   int swap;                      // 1: the box's fast pixel axis is H ("w" quantities of the tile grid run along H)
+  int issuers;                   // 1 / 2 MMA-issuing threads (2: local tiles alternate between warps 1 and 10)
   int nphases, total_tiles, nw, stages;
   unsigned long long* dbg;       // optional clock64 stamps of CTA 0 (nsg_debug_timeline), null in production
   int w_early;                   // 1: the weight images were written >= 2 kernels back: load them above pdl_wait()
@@ -312,15 +314,18 @@ __device__ __forceinline__ void epi_half(float (&x)[32], const uint32_t (&acc)[3
   }
 }
 
-// NACC = 2: streaming (two accumulators, the epilogue of tile i overlaps the MMAs of tile i+1).  NACC = 4 / 8: hold
-// (every tile of the CTA keeps its own accumulator, BnFuse above).
-template <int NACC>
-__global__ void __launch_bounds__(320, 1)
+// HOLD = false: streaming (NACC accumulators in turn, the epilogue of tile i overlaps the MMAs of the following tiles).
+// HOLD = true: every tile of the CTA keeps its own accumulator for the second pass (BnFuse above).
+// Warps: 0 = TMA producer, 1 and 10 = MMA issuers (even / odd local tiles when P.issuers == 2), 2-9 = epilogue.
+// Two issuers because ONE thread cannot keep the tensor pipe busy at N = 64: the uniform-datapath sequence around each
+// tcgen05.mma (elect, descriptor adds, branch) costs 75-85 cycles in this kernel against the instruction's 48, and the
+// hand-over between two tiles 700-1400 more.
+template <int NACC, bool HOLD>
+__global__ void __launch_bounds__(TM_THREADS, 1)
 conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__ CUtensorMap tm1,
                 const __grid_constant__ CUtensorMap tm2, const __grid_constant__ CUtensorMap tm3,
                 const uint8_t* __restrict__ wimg, __nv_bfloat16* __restrict__ out, EpiArgs epi, BnFuse bn,
                 const __grid_constant__ TmaConvParams P) {
-  constexpr bool HOLD = NACC > 2;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* sm = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);    // (pointer arithmetic on the __shared__ array: the compiler keeps the address space -- LDS / STS instead of generic loads)
   uint8_t* sW = sm;                                         // nw weight images
@@ -405,52 +410,70 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
         bulk_g2s(sW + (size_t)t * TM_W_BYTES, wimg + (size_t)t * TM_W_BYTES, TM_W_BYTES, wfull);
       pdl_wait();                              // the activations are the preceding kernel's output
       pdl_trigger();
-      int it = 0;
-      int s = 0;
-      uint32_t eparity = 1;                    // first pass over the ring: slots are free (wait on the preceding phase)
+      // the ring of activation slots: ONE ring for a single MMA issuer; with two, each issuer owns a part of it (its
+      // full / empty barriers then have exactly one waiter on either side -- a thread that skipped the other issuer's
+      // phases of a shared barrier could not tell phase u from phase u - 2 by parity)
+      const bool split = P.issuers == 2;
+      const int size0 = split ? stages >> 1 : stages, size1 = stages - (stages >> 1);
+      int s0 = 0, s1 = 0;
+      uint32_t ep0 = 1, ep1 = 1;               // first pass over a ring: slots are free (wait on the preceding phase)
       const uint32_t slot_bytes = P.slot_bytes;
       const uint32_t sA_u32 = smem_u32(sA);
       for (int i = 0; i < ntiles_mine; ++i) {
         const TmaTile tl = fetch_tile(P, sTile, i);
         const int ngroups = P.ph[tl.p].ngroups;
         const int w0 = tl.tw * P.box_w, h0 = tl.th * P.box_h;
-        for (int g = 0; g < ngroups; ++g, ++it) {
-          mbar_wait(&empty[s], eparity);
+        const bool second = split && (i & 1);
+        for (int g = 0; g < ngroups; ++g) {
+          const int s = second ? size0 + s1 : s0;
+          mbar_wait(&empty[s], second ? ep1 : ep0);
           mbar_arrive_expect_tx(&full[s], P.box_bytes);
           const int gi = sGrp[tl.p * TM_MAX_TAPS + g];
           const int par = gi & 3;
           const CUtensorMap* tm = par == 0 ? &tm0 : (par == 1 ? &tm1 : (par == 2 ? &tm2 : &tm3));
           tma::load_4d_u32(sA_u32 + (uint32_t)s * slot_bytes, tm, 0, w0 + ((gi >> 8) & 255) - 128,
                            h0 + ((gi >> 16) & 255) - 128, tl.n, &full[s]);
-          if (++s == stages) {
-            s = 0;
-            eparity ^= 1;
+          if (second) {
+            if (++s1 == size1) {
+              s1 = 0;
+              ep1 ^= 1;
+            }
+          } else if (++s0 == size0) {
+            s0 = 0;
+            ep0 ^= 1;
           }
         }
         tm_stamp(P.dbg, 2 + (i < 3 ? i : 3));          // 2..5: producer finished issuing tile i
       }
     }
-  } else if (warp == 1) {
-    // ------------------------------------------------------------------ MMA issuer
-    if (lane == 0 && ntiles_mine > 0) {
+  } else if (warp == 1 || warp == 10) {
+    // ------------------------------------------------------------------ MMA issuers
+    const int me = warp == 1 ? 0 : 1;
+    const bool split = P.issuers == 2;                   // tile i belongs to issuer i & 1
+    if (lane == 0 && ntiles_mine > me && (me == 0 || split)) {
       const uint32_t idesc = idesc_bf16(TM_M, TM_C);
       mbar_wait(wfull, 0);
-      tm_stamp(P.dbg, 6);                                // weights resident
+      if (me == 0) tm_stamp(P.dbg, 6);                   // weights resident
+      // this issuer's part of the slot ring (the producer above)
+      const int ring0 = split && me ? stages >> 1 : 0;
+      const int ring_size = split ? (me ? stages - (stages >> 1) : stages >> 1) : stages;
       int it = 0, s = 0;
       uint32_t fparity = 0;
       const uint32_t slot_units = P.slot_bytes >> 4;
-      const uint32_t a_base = ((smem_u32(sA) >> 4) & 0x3FFFu) | (1u << 16);     // low word of sw128_desc(sA)
+      const uint32_t a_base = (((smem_u32(sA) >> 4) + (uint32_t)ring0 * slot_units) & 0x3FFFu) | (1u << 16);     // low word of sw128_desc(first slot)
+      uint64_t* const rfull = full + ring0;
+      uint64_t* const rempty = empty + ring0;
       // SWIZZLE_128B K-major descriptors.  A: 8-pixel groups P.sbo16 * 16 bytes apart (1024 when a tile line is a whole
       // number of groups; the box line pitch in the one-box form, where a group is ONE box line of 8 pixels and the
       // +-1-pixel taps start 128 bytes off the swizzle atom -- the hardware applies the swizzle to the absolute
       // shared-memory address, exactly as the TMA unit wrote it: tools/microbench/desc_probe.cu).  B: the weight images.
       const uint64_t DESC_A_HI = ((uint64_t)P.sbo16 << 32) | (1ull << 46) | (2ull << 61);
       constexpr uint64_t DESC_B_HI = (64ull << 32) | (1ull << 46) | (2ull << 61);
-      for (int i = 0; i < ntiles_mine; ++i) {
+      for (int i = me; i < ntiles_mine; i += split ? 2 : 1) {
         const TmaTile tl = fetch_tile(P, sTile, i);
         const TmaPhase& ph = P.ph[tl.p];
         const int ngroups = ph.ngroups;
-        // streaming: two accumulators in turn.  hold: tile i lives in accumulator i % NACC; with more tiles than
+        // streaming: the accumulators in turn.  hold: tile i lives in accumulator i % NACC; with more tiles than
         // accumulators the FIRST ntiles - NACC tiles give theirs up after pass 1 (pass 2 re-reads them from memory)
         const int as = i % NACC, use = i / NACC;
         if (use > 0) mbar_wait(&acc_empty[as], (uint32_t)((use - 1) & 1));
@@ -468,8 +491,8 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
             ao[j] = sTapA[e];
             bo[j] = sTapB[e];
           }
-          mbar_wait(&full[s], fparity);
-          if (it == 0) tm_stamp(P.dbg, 7);               // first activation box landed
+          mbar_wait(&rfull[s], fparity);
+          if (it == 0 && me == 0) tm_stamp(P.dbg, 7);               // first activation box landed
           if (i == 1 && g < 3) tm_stamp(P.dbg, 21 + 3 * g);      // 21,24,27: tile 1, box of group g landed
           tc_fence_after();
           const uint32_t box = a_base + (uint32_t)s * slot_units;
@@ -500,9 +523,9 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
             }
           }
           if (i == 1 && g < 3) tm_stamp(P.dbg, 22 + 3 * g);      // 22,25,28: its instructions issued
-          umma_commit(&empty[s]);
+          umma_commit(&rempty[s]);
           if (i == 1 && g < 3) tm_stamp(P.dbg, 23 + 3 * g);      // 23,26,29: commit issued
-          if (++s == stages) {
+          if (++s == ring_size) {
             s = 0;
             fparity ^= 1;
           }
@@ -939,17 +962,17 @@ static int make_bnfuse(const nsg_bn_fuse* b, const EpiArgs& e, BnFuse* out) {
   return NSG_OK;
 }
 
-template <int NACC>
+template <int NACC, bool HOLD>
 static int launch_conv_tma(int grid, size_t smem, cudaStream_t stream, const CUtensorMap* tm, const void* packed, void* out,
                            const EpiArgs& e, const BnFuse& f, const TmaConvParams& P) {
   static bool configured = false;
   if (!configured) {
-    cudaError_t err = cudaFuncSetAttribute(conv_tma_kernel<NACC>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t err = cudaFuncSetAttribute(conv_tma_kernel<NACC, HOLD>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                            (int)TM_SMEM_LIMIT);
     if (err != cudaSuccess) return cuda_fail(err, "cudaFuncSetAttribute(conv_tma_kernel)");
     configured = true;
   }
-  launch_pdl_ex(NACC > 2, conv_tma_kernel<NACC>, dim3(grid), dim3(320), smem, stream, tm[0], tm[1], tm[2], tm[3],
+  launch_pdl_ex(HOLD, conv_tma_kernel<NACC, HOLD>, dim3(grid), dim3(TM_THREADS), smem, stream, tm[0], tm[1], tm[2], tm[3],
                 static_cast<const uint8_t*>(packed), static_cast<__nv_bfloat16*>(out), e, f, P);
   NSG_CHECK_LAUNCH("conv_tma_kernel");
   return NSG_OK;
@@ -1141,6 +1164,9 @@ int conv_gemm_tma(const nsg_conv_geom* cg, const void* in, const void* packed, c
   if (stages > TM_MAX_STAGES) stages = TM_MAX_STAGES;
   NSG_REQUIRE(stages >= 2, "conv_gemm_tma: weights do not leave room for the activation ring");
   P.stages = stages;
+  // two MMA-issuing threads when each can own at least two slots of the ring (NSG_CONV_ISSUERS=1: one, for A/B runs)
+  static const int issuers = [] { const char* v = getenv("NSG_CONV_ISSUERS"); return v && v[0] == '1' ? 1 : 2; }();
+  P.issuers = stages >= 4 ? issuers : 1;
   P.dbg = g_timeline;
   P.w_early = pdl_weights_settled(stream) ? 1 : 0;
   const size_t smem = 1024 + (size_t)P.nw * TM_W_BYTES + (size_t)stages * P.slot_bytes + tail;
@@ -1151,7 +1177,8 @@ int conv_gemm_tma(const nsg_conv_geom* cg, const void* in, const void* packed, c
   // (one CTA per SM even when that leaves 124 CTAs with 2 tiles and 24 with 3: giving every CTA 3 tiles on 107 CTAs
   // was measured and is no faster -- 19.0 against 17.5 us for the 3x3 forward, profiles/r2_toggles_ab.txt)
   const int grid = tiles < num_sms() ? tiles : num_sms();
-  if (!hold) return launch_conv_tma<2>(grid, smem, stream, tm, packed, out, e, f, P);
+  // streaming: 4 accumulators, so that neither issuer waits for an epilogue before the CTA's fifth tile
+  if (!hold) return launch_conv_tma<4, false>(grid, smem, stream, tm, packed, out, e, f, P);
   const int per_cta = (tiles + grid - 1) / grid;
   if (per_cta > 64) {
     set_error("conv_bn_tma: %d tiles per CTA do not fit (at most 64); run the convolution and the BatchNorm pass "
@@ -1162,8 +1189,8 @@ int conv_gemm_tma(const nsg_conv_geom* cg, const void* in, const void* packed, c
   NSG_REQUIRE(per_cta <= 8 || out, "conv_bn_tma: with more than 8 tiles per CTA the first output (h / g) is required");
   // a grid barrier needs every CTA resident: one CTA per SM of THIS device
   NSG_REQUIRE(grid <= num_sms(), "conv_bn_tma: grid %d exceeds the SM count", grid);
-  if (per_cta <= 4) return launch_conv_tma<4>(grid, smem, stream, tm, packed, out, e, f, P);
-  return launch_conv_tma<8>(grid, smem, stream, tm, packed, out, e, f, P);
+  if (per_cta <= 4) return launch_conv_tma<4, true>(grid, smem, stream, tm, packed, out, e, f, P);
+  return launch_conv_tma<8, true>(grid, smem, stream, tm, packed, out, e, f, P);
 }
 
 // ntaps[i] > 0: a 64 -> 64 layer with ntaps images.  ntaps[i] == -1 / -2: the single-channel layers' small operands,
