@@ -454,6 +454,17 @@ int nsg_melspectrogram(const float* wav, long long n_samples, int n_fft, int hop
 long long nsg_istft_workspace_bytes(int n_frames, int n_fft);
 int nsg_istft(const float* spec, int n_frames, int n_fft, int hop, void* workspace, float* y, void* stream);
 
+/* nsg_istft without any allocation: the frame scratch lives in a file-scope device array inside the library.  (No
+ * counterpart in the reference: added for callers that may not call cudaMalloc
+ * -- code under CUDA graph capture, serving loops, harnesses that forbid it.)  Limit: n_frames * n_fft <=
+ * nsg_istft_static_max_floats() = 2^20 (4 MiB held by every GPU that loads the library, until exit); larger inputs
+ * are rejected with NSG_E_INVALID and a message naming nsg_istft.  The entry point calls no cudaMalloc / cudaFree or
+ * allocating library routine.  Every call on a device shares the array: calls that overlap on the GPU (different
+ * streams) race -- serialise them.  Nothing in the scratch has to start at zero (each call overwrites what it reads).
+ * Same results as nsg_istft, bit for bit. */
+long long nsg_istft_static_max_floats(void);
+int nsg_istft_static(const float* spec, int n_frames, int n_fft, int hop, float* y, void* stream);
+
 /* audio_tacotron.py:142-152 _griffin_lim: y = istft(mag * exp(2 pi i angles0)); `iters` times { angles =
  * exp(1j * angle(stft(y))); y = istft(mag * angles) }.  mag: [n_frames][n_fft/2 + 1] target magnitudes (the reference
  * passes S ** power); angles0: same shape, the np.random.rand(*S.shape) of :146 (fractions of a turn) -- explicit so

@@ -28,7 +28,7 @@ EXPORTS = [
     'nsg_c1_conv_tc', 'nsg_c1_convT_tc', 'nsg_c1_wgrad_tc', 'nsg_scatter_mode', 'nsg_ema_update', 'nsg_vq_resident',
     'nsg_conv_bn_tma', 'nsg_conv_bn_tma_fits', 'nsg_c1_conv_bn_tc', 'nsg_mel_collate', 'nsg_peer_allreduce_stats',
     'nsg_hang_report', 'nsg_bn_act64_sync', 'nsg_bn_bwd64_sync', 'nsg_conv_rect', 'nsg_conv_rect_wgrad', 'nsg_gated_act', 'nsg_vae_reparam_kl',
-    'nsg_vae_reparam_kl_bwd', 'nsg_sqerr_sum', 'nsg_softmax_sample', 'nsg_stft', 'nsg_melspectrogram', 'nsg_istft', 'nsg_istft_workspace_bytes', 'nsg_griffin_lim',
+    'nsg_vae_reparam_kl_bwd', 'nsg_sqerr_sum', 'nsg_softmax_sample', 'nsg_stft', 'nsg_melspectrogram', 'nsg_istft', 'nsg_istft_workspace_bytes', 'nsg_istft_static', 'nsg_istft_static_max_floats', 'nsg_griffin_lim',
     'nsg_griffin_lim_workspace_bytes', 'nsg_mel_to_linear', 'nsg_inv_preemphasis',
 ]
 
@@ -156,6 +156,8 @@ def load():
     lib.nsg_melspectrogram.argtypes = [vp, ll, i, i, f, vp, i, f, f, f, vp, vp]
     lib.nsg_istft_workspace_bytes.argtypes = [i, i]
     lib.nsg_istft.argtypes = [vp, i, i, i, vp, vp, vp]
+    lib.nsg_istft_static.argtypes = [vp, i, i, i, vp, vp]
+    lib.nsg_istft_static_max_floats.argtypes = []
     lib.nsg_griffin_lim_workspace_bytes.argtypes = [i, i]
     lib.nsg_griffin_lim.argtypes = [vp, vp, i, i, i, i, vp, vp, vp]
     lib.nsg_mel_to_linear.argtypes = [vp, i, i, vp, i, f, f, f, f, vp, vp]
@@ -164,7 +166,7 @@ def load():
     for name in EXPORTS:
         fn = getattr(lib, name)
         if name not in ('nsg_version', 'nsg_last_error'):
-            fn.restype = ll if name in ('nsg_vq_workspace_bytes', 'nsg_conv_pack_bytes', 'nsg_istft_workspace_bytes',
+            fn.restype = ll if name in ('nsg_vq_workspace_bytes', 'nsg_conv_pack_bytes', 'nsg_istft_workspace_bytes', 'nsg_istft_static_max_floats',
                                         'nsg_griffin_lim_workspace_bytes') else i
     if os.environ.get('NSG_SCATTER_MODE') in ('0', '1'):      # development aid, see include/nsg_b200.h
         lib.nsg_scatter_mode(int(os.environ['NSG_SCATTER_MODE']))

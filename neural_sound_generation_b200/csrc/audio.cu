@@ -16,6 +16,7 @@
 //   * pre-emphasis is folded into the STFT's frame load; its inverse (a one-pole IIR) is a block-wide scan of affine
 //     maps with the carry handed from chunk to chunk, exact for any coefficient.
 // Arithmetic: fp32 (the reference: float32 mel algebra, complex128 Griffin-Lim); parity bars in tests/test_gpu_audio.py.
+#include <mutex>
 #include "common.cuh"
 
 namespace nsg {
@@ -520,6 +521,52 @@ extern "C" int nsg_istft(const float* spec, int n_frames, int n_fft, int hop, vo
              static_cast<const float*>(F), n_fft, hop, n_frames, y);
   NSG_CHECK_LAUNCH("istft_ola_kernel");
   return NSG_OK;
+}
+
+// ---------------------------------------------------------------------------------------------- ISTFT without allocation
+// nsg_istft with its frame scratch (the windowed inverse transforms, n_frames * n_fft floats) in a file-scope device
+// array instead of a caller-owned workspace: for callers that may not call cudaMalloc (code under CUDA graph capture,
+// serving loops, harnesses that forbid it).  No counterpart in the reference.
+// Every GPU that loads the library holds the array (4 MiB) until exit; every call on a device shares it, so
+// calls that overlap on the GPU (different streams) race.  The array keeps the last call's contents; nothing in it has to
+// start at zero: istft_frames_kernel overwrites every element that istft_ola_kernel reads in the same call.
+constexpr long long AU_STATIC_SCRATCH_FLOATS = 1ll << 20;       // n_frames * n_fft <= 2^20 (e.g. 1024 frames of n_fft 1024)
+static __device__ __align__(256) float g_istft_scratch[AU_STATIC_SCRATCH_FLOATS];
+
+// In host code `g_istft_scratch` is a host-side stand-in, not a device address: the address a kernel may use comes
+// from cudaGetSymbolAddress, once per device, with that device current.
+static int au_static_scratch(float** out) {
+  constexpr int kMaxDevices = 64;
+  static float* ptr[kMaxDevices] = {};
+  static std::mutex mu;
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return cuda_fail(e, "cudaGetDevice(istft_static)");
+  NSG_REQUIRE(dev >= 0 && dev < kMaxDevices, "istft_static: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ptr[dev]) {
+    float* p = nullptr;
+    e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_istft_scratch);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetSymbolAddress(g_istft_scratch)");
+    NSG_REQUIRE(p != nullptr, "istft_static: cudaGetSymbolAddress returned a null address");
+    ptr[dev] = p;
+  }
+  *out = ptr[dev];
+  return NSG_OK;
+}
+
+extern "C" long long nsg_istft_static_max_floats(void) { return AU_STATIC_SCRATCH_FLOATS; }
+
+extern "C" int nsg_istft_static(const float* spec, int n_frames, int n_fft, int hop, float* y, void* stream) {
+  if (int rc = au_check_fft(n_fft, hop, "istft_static")) return rc;
+  NSG_REQUIRE(spec && y, "istft_static: null pointer");
+  NSG_REQUIRE(n_frames >= 2, "istft_static: at least two frames (got %d)", n_frames);
+  NSG_REQUIRE((long long)n_frames * n_fft <= AU_STATIC_SCRATCH_FLOATS,
+              "istft_static: n_frames * n_fft = %lld exceeds the built-in scratch of %lld floats; use nsg_istft with a "
+              "caller-owned workspace", (long long)n_frames * n_fft, AU_STATIC_SCRATCH_FLOATS);
+  float* F = nullptr;
+  if (int rc = au_static_scratch(&F)) return rc;
+  return nsg_istft(spec, n_frames, n_fft, hop, F, y, stream);
 }
 
 extern "C" long long nsg_griffin_lim_workspace_bytes(int n_frames, int n_fft) {
