@@ -29,6 +29,7 @@ namespace nsg {
 using namespace tc;
 
 constexpr int TM_M = 128;                       // pixels per tile
+constexpr int WG_THREADS = 224;                 // wgrad_tma_kernel: producer warp, 2 MMA-issuing warps, 4 epilogue warps
 constexpr int TM_THREADS = 352;                 // conv_tma_kernel: producer warp, 2 MMA-issuing warps, 8 epilogue warps
 constexpr int TM_C = 64;                        // channels
 constexpr uint32_t TM_A_BYTES = TM_M * 128;     // one activation box
@@ -1253,6 +1254,7 @@ struct TmaWgradParams {
   int slice_elems;               // 0: add into ONE packed image with vector atomics; else CTA x stores its partial
                                  // image into slice x of [gridDim.x][ntaps][64][64] (no atomics, summed by the unpack)
   int dbg;
+  int issuers;                   // 1 / 2 MMA-issuing threads (2: the operand pairs of a tile alternate between warps 1 and 6)
   unsigned long long* stamps;    // optional clock64 stamps of CTA (0, 0) (nsg_debug_timeline), null in production
   WgGroup g[4];
 };
@@ -1270,8 +1272,10 @@ __device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, 
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
+// Warps: 0 = TMA producer, 1 and 6 = MMA issuers, 2-5 = epilogue.  With two issuers each takes every other operand
+// pair (= accumulator) of every tile: both wait on the stage's full barrier and both commit to its empty barrier.
 template <int TMEM_COLS>
-__global__ void __launch_bounds__(192, 1)
+__global__ void __launch_bounds__(WG_THREADS, 1)
 wgrad_tma_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ CUtensorMap tp0,
                  const __grid_constant__ CUtensorMap tp1, const __grid_constant__ CUtensorMap tp2,
                  const __grid_constant__ CUtensorMap tp3, float* __restrict__ dwp, float* __restrict__ colsum,
@@ -1288,12 +1292,13 @@ wgrad_tma_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int npairs = G.nops / 2;
+  const int nissuers = (P.issuers == 2 && npairs >= 2) ? 2 : 1;
   unsigned long long* stamps = (blockIdx.x == 0 && blockIdx.y == 0) ? P.stamps : nullptr;
   if (tid == 0) tm_stamp(stamps, 0);
   const int ntiles_mine = ((int)blockIdx.x < P.total_tiles)
                               ? (P.total_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
 
-  for (int i = tid; i < (int)(2 * WG_SLOT / 16); i += 192) {
+  for (int i = tid; i < (int)(2 * WG_SLOT / 16); i += WG_THREADS) {
     const uint32_t fill = i < (int)(WG_SLOT / 16) ? 0x3F803F80u : 0u;
     reinterpret_cast<uint4*>(sConst)[i] = make_uint4(fill, fill, fill, fill);
   }
@@ -1317,9 +1322,9 @@ wgrad_tma_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
   if (tid == 0) {
     for (int s = 0; s < WG_MAX_STAGES; ++s) {
       mbar_init(&full[s], 1);
-      mbar_init(&empty[s], 1);
+      mbar_init(&empty[s], (uint32_t)nissuers);
     }
-    mbar_init(acc_full, 1);
+    mbar_init(acc_full, (uint32_t)nissuers);
     fence_mbar_init();
     tma::prefetch_desc(&tq);
     tma::prefetch_desc(&tp0);
@@ -1373,9 +1378,10 @@ wgrad_tma_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
         }
       }
       if (lane == 0) tm_stamp(stamps, 12);
-    } else if (warp == 1) {
-      // ---------------------------------------------------------------- MMA issuer
-      if (lane == 0) {
+    } else if (warp == 1 || warp == 6) {
+      // ---------------------------------------------------------------- MMA issuers
+      const int me = warp == 1 ? 0 : 1;
+      if (lane == 0 && me < nissuers) {
         const uint32_t idesc = idesc_bf16_mnmajor(128, TM_C);
         const int np = (P.dbg & 1) ? 0 : npairs;
         int s = 0;
@@ -1383,9 +1389,9 @@ wgrad_tma_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
         for (int i = 0; i < ntiles_mine; ++i) {
           mbar_wait(&full[s], parity);
           tc_fence_after();
-          if (i < 10) tm_stamp(stamps, 13 + i);              // 13..22: tile i landed
+          if (i < 10 && me == 0) tm_stamp(stamps, 13 + i);   // 13..22: tile i landed
           const uint64_t db = sDB[s];
-          for (int j = 0; j < np; ++j) {
+          for (int j = me; j < np; j += nissuers) {
             const uint64_t da = sDA[s][j];
             const uint32_t d = tmem_base + (uint32_t)j * TM_C;
             // K steps of 16 pixels = 2048 bytes = 128 in the descriptors' 16-byte address field (no carry: < 256 KB)
@@ -1400,9 +1406,9 @@ wgrad_tma_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__
           }
         }
         umma_commit(acc_full);
-        tm_stamp(stamps, 23);                                // all MMAs issued
+        if (me == 0) tm_stamp(stamps, 23);                   // all MMAs issued
       }
-    } else {
+    } else if (warp < 6) {
       // ---------------------------------------------------------------- epilogue: thread = (block of the pair, channel a)
       pdl_wait();
       mbar_wait(acc_full, 0);
@@ -1524,7 +1530,7 @@ static int launch_wgrad_tma(dim3 grid, size_t smem, const CUtensorMap* tq, const
     if (err != cudaSuccess) return cuda_fail(err, "cudaFuncSetAttribute(wgrad_tma_kernel)");
     configured = true;
   }
-  launch_pdl(wgrad_tma_kernel<TMEM_COLS>, dim3(grid), dim3(192), smem, stream, *tq, tp[0], tp[1], tp[2], tp[3], dwp, colsum, P);
+  launch_pdl(wgrad_tma_kernel<TMEM_COLS>, dim3(grid), dim3(WG_THREADS), smem, stream, *tq, tp[0], tp[1], tp[2], tp[3], dwp, colsum, P);
   NSG_CHECK_LAUNCH("wgrad_tma_kernel");
   return NSG_OK;
 }
@@ -1582,6 +1588,8 @@ int conv_wgrad_tma(const nsg_conv_geom* cg, const void* p, const void* q, float*
   // tuning aid behind profiles/r1_final_wgrad_timeline.txt: 1 = issue no MMAs, 2 = load no P boxes (results are wrong)
   static const int wgrad_dbg = getenv("NSG_WGRAD_DBG") ? atoi(getenv("NSG_WGRAD_DBG")) : 0;
   P.dbg = wgrad_dbg;
+  static const int wg_issuers = [] { const char* v = getenv("NSG_WGRAD_ISSUERS"); return v && v[0] == '1' ? 1 : 2; }();
+  P.issuers = wg_issuers;
   P.stamps = g_timeline;
 
   // vertical shift of tap kh inside its (row-parity) view, and the halo the tallest class needs
