@@ -69,6 +69,7 @@ struct TmaConvParams {
   uint32_t sbo16;                // byte distance between the 8-pixel groups of the A operand, 16-byte units
   int swap;                      // 1: the box's fast pixel axis is H ("w" quantities of the tile grid run along H)
   int issuers;                   // 1 / 2 MMA-issuing threads (2: local tiles alternate between warps 1 and 10)
+  int elect;                     // 1: the issuing warps run converged and elect.sync issues (NSG_CONV_ELECT)
   int nphases, total_tiles, nw, stages;
   unsigned long long* dbg;       // optional clock64 stamps of CTA 0 (nsg_debug_timeline), null in production
   int w_early;                   // 1: the weight images were written >= 2 kernels back: load them above pdl_wait()
@@ -315,6 +316,111 @@ __device__ __forceinline__ void epi_half(float (&x)[32], const uint32_t (&acc)[3
   }
 }
 
+// The MMA-issuing loop of conv_tma_kernel, issuer `me` (0: warp 1, 1: warp 10).  ELECT = false: lane 0 runs it alone.
+// ELECT = true: the WHOLE warp runs it, converged -- every value is warp-uniform, all lanes poll the barriers, and only
+// the tcgen05 instructions are predicated on elect.sync (tc_common.cuh); without the divergent `if (lane == 0)` the
+// compiler needs no ELECT / BRA.U.ANY loop around every UTCHMMA.
+template <int NACC, bool ELECT>
+__device__ __forceinline__ void conv_issue_tiles(const TmaConvParams& P, int me, int lane, int ntiles_mine, const int4* sTile,
+                                                 const int* sGrp, const uint32_t* sTapA, const uint32_t* sTapB, uint8_t* sA,
+                                                 uint64_t* full, uint64_t* empty, uint64_t* wfull, uint64_t* acc_full,
+                                                 uint64_t* acc_empty, uint32_t tmem_base) {
+  {
+    const int stages = P.stages;
+    const bool split = P.issuers == 2;                   // tile i belongs to issuer i & 1
+    if ((ELECT || lane == 0) && ntiles_mine > me && (me == 0 || split)) {
+      const uint32_t idesc = idesc_bf16(TM_M, TM_C);
+      mbar_wait(wfull, 0);
+      if (me == 0) tm_stamp(P.dbg, 6);                   // weights resident
+      // this issuer's part of the slot ring (the producer above)
+      const int ring0 = split && me ? stages >> 1 : 0;
+      const int ring_size = split ? (me ? stages - (stages >> 1) : stages >> 1) : stages;
+      int it = 0, s = 0;
+      uint32_t fparity = 0;
+      const uint32_t slot_units = P.slot_bytes >> 4;
+      const uint32_t a_base = (((smem_u32(sA) >> 4) + (uint32_t)ring0 * slot_units) & 0x3FFFu) | (1u << 16);     // low word of sw128_desc(first slot)
+      uint64_t* const rfull = full + ring0;
+      uint64_t* const rempty = empty + ring0;
+      // SWIZZLE_128B K-major descriptors.  A: 8-pixel groups P.sbo16 * 16 bytes apart (1024 when a tile line is a whole
+      // number of groups; the box line pitch in the one-box form, where a group is ONE box line of 8 pixels and the
+      // +-1-pixel taps start 128 bytes off the swizzle atom -- the hardware applies the swizzle to the absolute
+      // shared-memory address, exactly as the TMA unit wrote it: tools/microbench/desc_probe.cu).  B: the weight images.
+      const uint64_t DESC_A_HI = ((uint64_t)P.sbo16 << 32) | (1ull << 46) | (2ull << 61);
+      constexpr uint64_t DESC_B_HI = (64ull << 32) | (1ull << 46) | (2ull << 61);
+      for (int i = me; i < ntiles_mine; i += split ? 2 : 1) {
+        const TmaTile tl = fetch_tile(P, sTile, i);
+        const TmaPhase& ph = P.ph[tl.p];
+        const int ngroups = ph.ngroups;
+        // streaming: the accumulators in turn.  hold: tile i lives in accumulator i % NACC; with more tiles than
+        // accumulators the FIRST ntiles - NACC tiles give theirs up after pass 1 (pass 2 re-reads them from memory)
+        const int as = i % NACC, use = i / NACC;
+        if (use > 0) mbar_wait(&acc_empty[as], (uint32_t)((use - 1) & 1));
+        tc_fence_after();
+        const uint32_t d = tmem_base + (uint32_t)as * TM_ACC_COLS;
+        for (int g = 0; g < ngroups; ++g, ++it) {
+          // the group's tap descriptors are fetched four at a time before they are needed: the issuing thread runs
+          // dependent scalar code, so every load left between two tcgen05.mma shows up as an idle tensor pipe
+          const uint32_t gi = (uint32_t)sGrp[tl.p * TM_MAX_TAPS + g];
+          const int first = (gi >> 24) & 15, cnt = (int)(gi >> 28) + 1;
+          uint32_t ao[4], bo[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const int e = tl.p * TM_MAX_TAPS + ((first + j) & 15);
+            ao[j] = sTapA[e];
+            bo[j] = sTapB[e];
+          }
+          mbar_wait(&rfull[s], fparity);
+          if (it == 0 && me == 0) tm_stamp(P.dbg, 7);               // first activation box landed
+          if (i == 1 && g < 3) tm_stamp(P.dbg, 21 + 3 * g);      // 21,24,27: tile 1, box of group g landed
+          tc_fence_after();
+          const uint32_t box = a_base + (uint32_t)s * slot_units;
+          for (int j0 = 0; j0 < cnt; j0 += 4) {
+            uint32_t an[4], bn_[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {                // (the next four, for groups of more than four taps)
+              const int e = tl.p * TM_MAX_TAPS + ((first + j0 + 4 + j) & 15);
+              an[j] = sTapA[e];
+              bn_[j] = sTapB[e];
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const uint64_t a = DESC_A_HI | (uint64_t)(box + ao[j]);
+              const uint64_t b = DESC_B_HI | (uint64_t)bo[j];
+              const uint32_t accum = (first + j0 + j) != 0;
+              if (ELECT) {                               // (taps past the group's count are predicated off: no branch)
+                const uint32_t valid = (j0 + j < cnt) ? 1u : 0u;
+#pragma unroll
+                for (int ks = 0; ks < 4; ++ks)
+                  umma_bf16_elect(d + (ks % TM_CHAINS) * TM_C, a + 2 * ks, b + 2 * ks, idesc,
+                                  (ks >= TM_CHAINS) ? 1u : accum, valid);
+              } else if (j0 + j < cnt) {
+#pragma unroll
+                for (int ks = 0; ks < 4; ++ks)
+                  umma_bf16(d + (ks % TM_CHAINS) * TM_C, a + 2 * ks, b + 2 * ks, idesc,
+                            (ks >= TM_CHAINS) ? 1u : accum);
+              }
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              ao[j] = an[j];
+              bo[j] = bn_[j];
+            }
+          }
+          if (i == 1 && g < 3) tm_stamp(P.dbg, 22 + 3 * g);      // 22,25,28: its instructions issued
+          if (ELECT) umma_commit_elect(&rempty[s]); else umma_commit(&rempty[s]);
+          if (i == 1 && g < 3) tm_stamp(P.dbg, 23 + 3 * g);      // 23,26,29: commit issued
+          if (++s == ring_size) {
+            s = 0;
+            fparity ^= 1;
+          }
+        }
+        if (ELECT) umma_commit_elect(&acc_full[as]); else umma_commit(&acc_full[as]);
+        tm_stamp(P.dbg, 8 + (i < 3 ? i : 3));           // 8..11: MMAs of tile i issued
+      }
+    }
+  }
+}
+
 // HOLD = false: streaming (NACC accumulators in turn, the epilogue of tile i overlaps the MMAs of the following tiles).
 // HOLD = true: every tile of the CTA keeps its own accumulator for the second pass (BnFuse above).
 // Warps: 0 = TMA producer, 1 and 10 = MMA issuers (even / odd local tiles when P.issuers == 2), 2-9 = epilogue.
@@ -448,93 +554,13 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tm0, const __grid_constant__
       }
     }
   } else if (warp == 1 || warp == 10) {
-    // ------------------------------------------------------------------ MMA issuers
-    const int me = warp == 1 ? 0 : 1;
-    const bool split = P.issuers == 2;                   // tile i belongs to issuer i & 1
-    if (lane == 0 && ntiles_mine > me && (me == 0 || split)) {
-      const uint32_t idesc = idesc_bf16(TM_M, TM_C);
-      mbar_wait(wfull, 0);
-      if (me == 0) tm_stamp(P.dbg, 6);                   // weights resident
-      // this issuer's part of the slot ring (the producer above)
-      const int ring0 = split && me ? stages >> 1 : 0;
-      const int ring_size = split ? (me ? stages - (stages >> 1) : stages >> 1) : stages;
-      int it = 0, s = 0;
-      uint32_t fparity = 0;
-      const uint32_t slot_units = P.slot_bytes >> 4;
-      const uint32_t a_base = (((smem_u32(sA) >> 4) + (uint32_t)ring0 * slot_units) & 0x3FFFu) | (1u << 16);     // low word of sw128_desc(first slot)
-      uint64_t* const rfull = full + ring0;
-      uint64_t* const rempty = empty + ring0;
-      // SWIZZLE_128B K-major descriptors.  A: 8-pixel groups P.sbo16 * 16 bytes apart (1024 when a tile line is a whole
-      // number of groups; the box line pitch in the one-box form, where a group is ONE box line of 8 pixels and the
-      // +-1-pixel taps start 128 bytes off the swizzle atom -- the hardware applies the swizzle to the absolute
-      // shared-memory address, exactly as the TMA unit wrote it: tools/microbench/desc_probe.cu).  B: the weight images.
-      const uint64_t DESC_A_HI = ((uint64_t)P.sbo16 << 32) | (1ull << 46) | (2ull << 61);
-      constexpr uint64_t DESC_B_HI = (64ull << 32) | (1ull << 46) | (2ull << 61);
-      for (int i = me; i < ntiles_mine; i += split ? 2 : 1) {
-        const TmaTile tl = fetch_tile(P, sTile, i);
-        const TmaPhase& ph = P.ph[tl.p];
-        const int ngroups = ph.ngroups;
-        // streaming: the accumulators in turn.  hold: tile i lives in accumulator i % NACC; with more tiles than
-        // accumulators the FIRST ntiles - NACC tiles give theirs up after pass 1 (pass 2 re-reads them from memory)
-        const int as = i % NACC, use = i / NACC;
-        if (use > 0) mbar_wait(&acc_empty[as], (uint32_t)((use - 1) & 1));
-        tc_fence_after();
-        const uint32_t d = tmem_base + (uint32_t)as * TM_ACC_COLS;
-        for (int g = 0; g < ngroups; ++g, ++it) {
-          // the group's tap descriptors are fetched four at a time before they are needed: the issuing thread runs
-          // dependent scalar code, so every load left between two tcgen05.mma shows up as an idle tensor pipe
-          const uint32_t gi = (uint32_t)sGrp[tl.p * TM_MAX_TAPS + g];
-          const int first = (gi >> 24) & 15, cnt = (int)(gi >> 28) + 1;
-          uint32_t ao[4], bo[4];
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const int e = tl.p * TM_MAX_TAPS + ((first + j) & 15);
-            ao[j] = sTapA[e];
-            bo[j] = sTapB[e];
-          }
-          mbar_wait(&rfull[s], fparity);
-          if (it == 0 && me == 0) tm_stamp(P.dbg, 7);               // first activation box landed
-          if (i == 1 && g < 3) tm_stamp(P.dbg, 21 + 3 * g);      // 21,24,27: tile 1, box of group g landed
-          tc_fence_after();
-          const uint32_t box = a_base + (uint32_t)s * slot_units;
-          for (int j0 = 0; j0 < cnt; j0 += 4) {
-            uint32_t an[4], bn_[4];
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {                // (the next four, for groups of more than four taps)
-              const int e = tl.p * TM_MAX_TAPS + ((first + j0 + 4 + j) & 15);
-              an[j] = sTapA[e];
-              bn_[j] = sTapB[e];
-            }
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              if (j0 + j < cnt) {
-                const uint64_t a = DESC_A_HI | (uint64_t)(box + ao[j]);
-                const uint64_t b = DESC_B_HI | (uint64_t)bo[j];
-                const uint32_t accum = (first + j0 + j) != 0;
-#pragma unroll
-                for (int ks = 0; ks < 4; ++ks)
-                  umma_bf16(d + (ks % TM_CHAINS) * TM_C, a + 2 * ks, b + 2 * ks, idesc,
-                            (ks >= TM_CHAINS) ? 1u : accum);
-              }
-            }
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              ao[j] = an[j];
-              bo[j] = bn_[j];
-            }
-          }
-          if (i == 1 && g < 3) tm_stamp(P.dbg, 22 + 3 * g);      // 22,25,28: its instructions issued
-          umma_commit(&rempty[s]);
-          if (i == 1 && g < 3) tm_stamp(P.dbg, 23 + 3 * g);      // 23,26,29: commit issued
-          if (++s == ring_size) {
-            s = 0;
-            fparity ^= 1;
-          }
-        }
-        umma_commit(&acc_full[as]);
-        tm_stamp(P.dbg, 8 + (i < 3 ? i : 3));           // 8..11: MMAs of tile i issued
-      }
-    }
+    // ------------------------------------------------------------------ MMA issuers (conv_issue_tiles above)
+    if (P.elect)
+      conv_issue_tiles<NACC, true>(P, warp == 1 ? 0 : 1, lane, ntiles_mine, sTile, sGrp, sTapA, sTapB, sA, full, empty, wfull,
+                                   acc_full, acc_empty, tmem_base);
+    else
+      conv_issue_tiles<NACC, false>(P, warp == 1 ? 0 : 1, lane, ntiles_mine, sTile, sGrp, sTapA, sTapB, sA, full, empty, wfull,
+                                    acc_full, acc_empty, tmem_base);
   } else {
     // ------------------------------------------------------------------ epilogue: all 8 warps work on every tile;
     // thread = (output row, 32-channel half).  The per-channel statistics are carried in registers across the CTA's
@@ -1168,6 +1194,10 @@ int conv_gemm_tma(const nsg_conv_geom* cg, const void* in, const void* packed, c
   // two MMA-issuing threads when each can own at least two slots of the ring (NSG_CONV_ISSUERS=1: one, for A/B runs)
   static const int issuers = [] { const char* v = getenv("NSG_CONV_ISSUERS"); return v && v[0] == '1' ? 1 : 2; }();
   P.issuers = stages >= 4 ? issuers : 1;
+  // (default on: 0.617 against 0.621 ms per step, the 4 x 4 stride-2 forward 12.5 against 14.3 us warm; NSG_CONV_ELECT=0
+  // keeps the single-lane loop for A/B runs -- profiles/r2_elect_issue_ab.txt)
+  static const int elect = [] { const char* v = getenv("NSG_CONV_ELECT"); return v && v[0] == '0' ? 0 : 1; }();
+  P.elect = elect;
   P.dbg = g_timeline;
   P.w_early = pdl_weights_settled(stream) ? 1 : 0;
   const size_t smem = 1024 + (size_t)P.nw * TM_W_BYTES + (size_t)stages * P.slot_bytes + tail;

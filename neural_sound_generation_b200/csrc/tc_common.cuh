@@ -133,6 +133,28 @@ __device__ __forceinline__ void umma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
                : "memory");
 }
+// The same two, for an issue loop that the WHOLE warp runs convergently: elect.sync picks the issuing lane (the same
+// one every time for a full mask -- tcgen05.commit tracks the operations of the thread that executes it) and only the
+// tcgen05 instruction is predicated.  `valid` = 0 turns the instruction off without a branch.
+__device__ __forceinline__ void umma_bf16_elect(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                                uint32_t accumulate, uint32_t valid = 1u) {
+  asm volatile(
+      "{\n\t.reg .pred p, q, v;\n\t"
+      "setp.ne.b32 q, %4, 0;\n\t"
+      "setp.ne.b32 v, %5, 0;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "and.pred p, p, v;\n\t"
+      "@p tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, q;\n\t}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(valid)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit_elect(uint64_t* bar) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "@p tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(smem_u32(bar))
+      : "memory");
+}
 // 32 lanes x 32 consecutive fp32 columns: thread i of the warp receives TMEM lane (base_lane + i)
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
   asm volatile(
