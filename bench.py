@@ -337,6 +337,20 @@ def main():
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return t.item() / steps
 
+    def timed_back_to_back(fn, steps):
+        """Average duration of `steps` launches issued back to back between ONE pair of events (no flush kernel in
+        between: the caller rotates inputs larger than L2, or wants the warm figure).  The host gets a head start -- a
+        ~1 ms spin kernel without memory traffic -- so that the launches are queued when their turn comes and the events
+        bracket GPU time, not the host's launch latency."""
+        torch.cuda._sleep(2000000)
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        for i in range(steps):
+            fn(i)
+        e.record()
+        sync()
+        return s.elapsed_time(e) / steps
+
     for i in range(max(3, args.warmup)):
         graphed(devin[i % n_in])
     sync()
@@ -413,7 +427,29 @@ def main():
         kfn = lambda i: eng._conv_fwd(x, w, bias, 3, 1, 1, False, ops.prologue(ops.PRO_RELU))
     for _ in range(3):
         kfn(0)
-    kms = timed(kfn, 20)
+    kms_flushed = timed(kfn, 20)
+    kms_warm = timed_back_to_back(kfn, 20)
+    kms = kms_flushed
+    kl2 = '256 MiB write-flush before every launch'
+    if args.mode == 'tma':
+        # The roofline figure: inputs larger than L2 instead of the write-flush.  The flush leaves 126 MB of DIRTY lines
+        # whose write-back is charged to the ~10 us kernel that follows, and bracketing ONE launch with events adds the
+        # event / launch gaps to it (a step-sized region amortises both, a single kernel does not).  Here 64 distinct
+        # inputs = 336 MB cycle through the L2 -- launch i reads a tensor last touched 64 launches (>= 336 MB of traffic)
+        # ago, i.e. from DRAM; weights and the allocator-reused output stay hot, as they do inside the step -- and the
+        # figure is the average of 20 launches issued back to back with programmatic dependent launch, as the step
+        # issues them.  The flushed single-launch figure and the warm figure are reported beside it.
+        nrot = 64
+        xs = [xr.clone() for _ in range(nrot)]
+
+        def kfn_rot(i):
+            return eng._conv_fwd(kctx, Pd, 'encoder.4.block.1', xs[i % nrot], stats=kstats)
+        for i in range(nrot):
+            kfn_rot(i)
+        kms = timed_back_to_back(kfn_rot, 20)
+        kl2 = ('average of 20 back-to-back launches on 64 rotating inputs (336 MB > 126 MB L2), no flush: every launch '
+               'reads its input from DRAM')
+        del xs
     kms_plain = None
     if args.mode == 'tma':
         for _ in range(3):
@@ -437,7 +473,8 @@ def main():
                      d=DIM, what='vq_forward (search + gather + sq-error; split-bf16 passes not counted), L2 flushed')
     roof = dict(bound='tensor', achieved=achieved, peak=pk['tf_burst'], unit='TFLOP/s', frac=achieved / pk['tf_burst'],
                 traffic=ncu_traffic('conv_tma_kernel_3x3_fwd'), kernel='conv3x3 64->64 fwd (%s)' % ({0: 'CUDA-core fp32', 1: 'tcgen05 bf16, register-staged', 2: 'tcgen05 bf16, TMA-fed persistent, BatchNorm moment sums in the epilogue'}[model.conv_impl]),
-                us=kms * 1e3, us_fused_conv_bn_relu=(kms_plain * 1e3 if kms_plain else None),
+                us=kms * 1e3, l2=kl2, us_l2_write_flushed=kms_flushed * 1e3, us_warm=kms_warm * 1e3,
+                us_fused_conv_bn_relu=(kms_plain * 1e3 if kms_plain else None),
                 peak_source=pk['src'], step_frac_of_tensor_peak=TRAIN_GFLOP * world / (ms / 1e3) / 1e3 / (pk['tf_sust'] * world))
     if rank != 0:
         if world > 1:
