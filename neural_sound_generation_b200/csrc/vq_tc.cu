@@ -454,6 +454,7 @@ vq_search_res_kernel(const __grid_constant__ CUtensorMap tmz, const T* __restric
       int tile_g[2] = {0, 1}, chunk_g[2] = {0, 0};
       int remaining = ntiles_mine * nchunks;
       while (remaining > 0) {
+        bool progressed = false;
 #pragma unroll
         for (int g = 0; g < 2; ++g) {
           const int i = tile_g[g];
@@ -466,6 +467,7 @@ vq_search_res_kernel(const __grid_constant__ CUtensorMap tmz, const T* __restric
           if (used[g] > 0 && !mbar_try_wait(&acc_empty[g], (uint32_t)((used[g] - 1) & 1))) continue;
           ++used[g];
           --remaining;
+          progressed = true;
           if (++chunk_g[g] == nchunks) {
             chunk_g[g] = 0;
             tile_g[g] += 2;
@@ -487,6 +489,9 @@ vq_search_res_kernel(const __grid_constant__ CUtensorMap tmz, const T* __restric
           }
           umma_commit(&acc_full[g]);
         }
+        // nothing to issue: both groups are scanning.  This thread shares its scheduler with two scanning warps and a
+        // polling warp is always eligible (ncu: 6 % of the kernel's instructions were this loop) -- back off
+        if (!progressed) __nanosleep(64);
       }
     }
   } else {
@@ -641,9 +646,14 @@ vq_search_res_kernel(const __grid_constant__ CUtensorMap tmz, const T* __restric
             else if (n == 3) cand[c][3] = k;
             ++n;
           };
+          // (branch-free per element: the hits of a 32-column slice are collected in a bit mask -- FFMA + FSETP +
+          // predicated OR -- and the rare set bits are walked once per slice; a branch per 4 columns made the warp run
+          // the divergent push path for every group in which ANY of its 32 rows had a candidate: as many instructions
+          // again as the scan itself, at 16-21 active threads per warp)
           auto scan32 = [&](const uint32_t (&rr)[32], int jj) {
             const float4* es = reinterpret_cast<const float4*>(esq_s + c * VT_N + jj * 32);
             const int kbase = c * VT_N + jj * 32;
+            uint32_t hit = 0;
 #pragma unroll
             for (int e4 = 0; e4 < 8; ++e4) {
               const float4 e = es[e4];
@@ -651,12 +661,14 @@ vq_search_res_kernel(const __grid_constant__ CUtensorMap tmz, const T* __restric
               const float d1 = fmaf(-2.f, __uint_as_float(rr[4 * e4 + 1]), e.y);
               const float d2 = fmaf(-2.f, __uint_as_float(rr[4 * e4 + 2]), e.z);
               const float d3 = fmaf(-2.f, __uint_as_float(rr[4 * e4 + 3]), e.w);
-              if (d0 <= thr || d1 <= thr || d2 <= thr || d3 <= thr) {
-                if (d0 <= thr) push(kbase + 4 * e4 + 0);
-                if (d1 <= thr) push(kbase + 4 * e4 + 1);
-                if (d2 <= thr) push(kbase + 4 * e4 + 2);
-                if (d3 <= thr) push(kbase + 4 * e4 + 3);
-              }
+              if (d0 <= thr) hit |= 1u << (4 * e4 + 0);
+              if (d1 <= thr) hit |= 1u << (4 * e4 + 1);
+              if (d2 <= thr) hit |= 1u << (4 * e4 + 2);
+              if (d3 <= thr) hit |= 1u << (4 * e4 + 3);
+            }
+            while (hit) {                                  // increasing index order
+              push(kbase + __ffs((int)hit) - 1);
+              hit &= hit - 1;
             }
           };
 #pragma unroll 1
