@@ -386,9 +386,21 @@ adam_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m,
   };
   request(i);
   if (threadIdx.x == 0) {
-    const double t = (double)(*step_count + 1);
-    const double bc1 = 1.0 - pow((double)b1, t);
-    const double bc2 = 1.0 - pow((double)b2, t);
+    // beta ** step by binary exponentiation (the step is an integer: ~20 dependent double multiplications for both
+    // powers together, against two calls of the general pow(), a few thousand cycles in front of the CTA's barrier)
+    long long t = *step_count + 1;
+    double q1 = (double)b1, q2 = (double)b2, r1 = 1.0, r2 = 1.0;
+    while (t > 0) {
+      if (t & 1) {
+        r1 *= q1;
+        r2 *= q2;
+      }
+      q1 *= q1;
+      q2 *= q2;
+      t >>= 1;
+    }
+    const double bc1 = 1.0 - r1;
+    const double bc2 = 1.0 - r2;
     s_step_size = (float)((double)lr / bc1);
     s_bc2_sqrt = (float)sqrt(bc2);
   }

@@ -111,6 +111,9 @@ struct BnActArgs {
   long long pixels;
   PeerSync peer;                 // world > 1: the statistics are summed over the GPUs inside this launch
   unsigned int* gate;
+  double inv_count;              // 1 / count from the host: a double-precision division is a ~100-instruction sequence, and
+                                 // the whole CTA waits at a barrier for the 64 threads that derive the coefficients
+  double unbias;                 // count / (count - 1), or 1
 };
 
 __global__ void __launch_bounds__(256) bn_act_kernel(const BnActArgs a) {
@@ -139,13 +142,15 @@ __global__ void __launch_bounds__(256) bn_act_kernel(const BnActArgs a) {
   if (tid < FE_C) {
     float mu, is;
     if (a.stats) {
-      const double m = __ldcg(a.stats + tid) / a.count;
-      double var = __ldcg(a.stats + FE_C + tid) / a.count - m * m;
+      const double m = __ldcg(a.stats + tid) * a.inv_count;
+      double var = __ldcg(a.stats + FE_C + tid) * a.inv_count - m * m;
       if (var < 0.0) var = 0.0;
       mu = (float)m;
-      is = (float)(1.0 / sqrt(var + (double)a.eps));
+      // (the moments and their difference in double -- cancellation --, the reciprocal square root in single precision:
+      // a double sqrt + division is a few hundred dependent instructions in front of the CTA's barrier)
+      is = 1.0f / sqrtf((float)(var + (double)a.eps));
       if (blockIdx.x == 0 && a.running_mean) {
-        const double unbiased = a.count > 1.0 ? var * a.count / (a.count - 1.0) : var;
+        const double unbiased = var * a.unbias;
         a.running_mean[tid] = (1.f - a.momentum) * a.running_mean[tid] + a.momentum * mu;
         a.running_var[tid] = (1.f - a.momentum) * a.running_var[tid] + a.momentum * (float)unbiased;
         if (tid == 0 && a.nbt) *a.nbt += 1;
@@ -207,6 +212,7 @@ struct BnBwdArgs {
   long long pixels;
   PeerSync peer;
   unsigned int* gate;
+  double inv_count;              // 1 / count (see BnActArgs)
 };
 
 __global__ void __launch_bounds__(256) bn_bwd_kernel(const BnBwdArgs a) {
@@ -232,7 +238,7 @@ __global__ void __launch_bounds__(256) bn_bwd_kernel(const BnBwdArgs a) {
   request(p0);
   fe_global_stats(a.peer, const_cast<double*>(a.stats), a.gate);
   if (tid < FE_C) {
-    const double sg = __ldcg(a.stats + tid) / a.count, sgx = __ldcg(a.stats + FE_C + tid) / a.count;
+    const double sg = __ldcg(a.stats + tid) * a.inv_count, sgx = __ldcg(a.stats + FE_C + tid) * a.inv_count;
     const float mu = a.mean[tid], is = a.invstd[tid];
     const float k0 = a.gamma[tid] * is;
     const float kb = k0 * is * (float)sgx;
@@ -392,7 +398,9 @@ int nsg_bn_act64_sync(const void* h, const void* res, void* out, double* stats, 
   BnActArgs a{static_cast<const __nv_bfloat16*>(h), static_cast<const __nv_bfloat16*>(res),
               static_cast<__nv_bfloat16*>(out), stats, count, gamma, beta, eps, momentum,
               stats ? running_mean : running_mean, stats ? running_var : running_var, num_batches_tracked,
-              mean, invstd, scale, shift, relu_out, pixels, PeerSync{}, gate};
+              mean, invstd, scale, shift, relu_out, pixels, PeerSync{}, gate, 0.0, 1.0};
+  a.inv_count = count > 0 ? 1.0 / count : 0.0;
+  a.unbias = count > 1.0 ? count / (count - 1.0) : 1.0;
   a.peer.world = 1;
   if (peer && peer->world > 1) {
     NSG_REQUIRE(stats && gate, "bn_act64_sync: the exchange needs the statistics and a zeroed gate counter");
@@ -422,7 +430,7 @@ int nsg_bn_bwd64_sync(const void* g, const void* h, void* dh, double* stats, dou
   if (pixels == 0) return NSG_OK;
   BnBwdArgs a{static_cast<const __nv_bfloat16*>(g), static_cast<const __nv_bfloat16*>(h),
               static_cast<__nv_bfloat16*>(dh), stats, count, mean, invstd, gamma, dgamma, dbeta, dbias_prev, pixels,
-              PeerSync{}, gate};
+              PeerSync{}, gate, 1.0 / count};
   a.peer.world = 1;
   if (peer && peer->world > 1) {
     NSG_REQUIRE(gate, "bn_bwd64_sync: the exchange needs a zeroed gate counter");
