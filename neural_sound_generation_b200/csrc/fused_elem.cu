@@ -91,6 +91,37 @@ __device__ __forceinline__ void fe_channel_reduce(float (&s)[8], float* sred, Ou
   __syncthreads();
 }
 
+// two statistics at once, without shared-memory atomics: lanes 0-7 of every warp hold the warp's sums of 8 channels
+// each after two shuffles; they go to [statistic][warp][channel] and 128 threads add the 8 warps in a FIXED order
+// (one barrier instead of six, and the CTA's contribution no longer depends on the order in which its warps arrive)
+template <typename OutT>
+__device__ __forceinline__ void fe_channel_reduce2(float (&a)[8], float (&b)[8], float* sred2 /* [2][8][FE_C] */,
+                                                   OutT* dst /* [2 * FE_C] */, int c0) {
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    a[i] += __shfl_xor_sync(0xffffffffu, a[i], 8);
+    a[i] += __shfl_xor_sync(0xffffffffu, a[i], 16);
+    b[i] += __shfl_xor_sync(0xffffffffu, b[i], 8);
+    b[i] += __shfl_xor_sync(0xffffffffu, b[i], 16);
+  }
+  const int tid = threadIdx.x, warp = tid >> 5;
+  if ((tid & 31) < 8) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      sred2[(0 * 8 + warp) * FE_C + c0 + i] = a[i];
+      sred2[(1 * 8 + warp) * FE_C + c0 + i] = b[i];
+    }
+  }
+  __syncthreads();
+  if (tid < 2 * FE_C) {
+    const int which = tid >> 6, c = tid & (FE_C - 1);
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) t += sred2[(which * 8 + w) * FE_C + c];
+    atomicAdd(dst + which * FE_C + c, (OutT)t);
+  }
+}
+
 struct BnActArgs {
   const __nv_bfloat16* h;
   const __nv_bfloat16* res;
@@ -300,7 +331,7 @@ vq_bwd_stats_kernel(const __nv_bfloat16* __restrict__ g_st, const __nv_bfloat16*
                     const float* __restrict__ invstd, double* __restrict__ stats, long long pixels) {
   pdl_wait();
   pdl_trigger();
-  __shared__ float sred[FE_C];
+  __shared__ float sred2[2 * 8 * FE_C];
   const int tid = threadIdx.x;
   const int c0 = (tid & 7) * 8;
   float mu[8], is[8], s1[8], s2[8];
@@ -347,10 +378,7 @@ vq_bwd_stats_kernel(const __nv_bfloat16* __restrict__ g_st, const __nv_bfloat16*
       fe_st8(dz + o, gv);
     }
   }
-  if (stats) {
-    fe_channel_reduce<double>(s1, sred, stats, c0);
-    fe_channel_reduce<double>(s2, sred, stats + FE_C, c0);
-  }
+  if (stats) fe_channel_reduce2<double>(s1, s2, sred2, stats, c0);
 }
 
 static inline int fe_grid(long long pixels) {
