@@ -368,9 +368,9 @@ def main():
     # (double-buffered: the copy of batch i+1 is issued before the host waits for step i's losses, so it runs under
     # the step; every timed step still moves one whole batch host -> device and its three losses device -> host)
     def e2e_step(i):
-        losses = graphed(host[i % n_in])
+        graphed(host[i % n_in])
         graphed.prefetch(host[(i + 1) % n_in])
-        return losses.tolist()
+        return graphed.read_losses()        # (device -> pinned host copy queued behind the replay + one stream sync)
     e2e_step(n_in - 1)
     sync()
     ms_e2e = timed(e2e_step, args.steps)

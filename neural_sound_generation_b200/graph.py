@@ -46,16 +46,26 @@ class GraphedTrainStep(object):
         # one eager iteration configures every kernel variant (cudaFuncSetAttribute is not capturable); the
         # model / optimizer state it touches is restored afterwards
         saved = [t.clone() for t in self._state()]
-        self._body(grad_hook)
+        l0, _ = self._body(grad_hook)
         torch.cuda.synchronize(dev)
         for t, s in zip(self._state(), saved):
             t.copy_(s)
+        self._losses_host = torch.empty(l0.shape, dtype=l0.dtype).pin_memory()      # read_losses()
         self.graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self.graph):
             self.losses, self.outputs = self._body(grad_hook)
         torch.cuda.synchronize(dev)
         for t, s in zip(self._state(), saved):
             t.copy_(s)
+
+    def read_losses(self):
+        """[loss_recons, loss_vq, loss_commit] of the last replay as Python floats (waits for the step).  The copy goes
+        into PINNED host memory and is queued behind the replay while it is still running, so what is left after the
+        step is one stream synchronisation -- ``losses.tolist()`` copies into pageable memory through the driver's
+        staging buffer, ~10 us more per step on the boxes measured."""
+        self._losses_host.copy_(self.losses, non_blocking=True)
+        torch.cuda.current_stream(self.c.device).synchronize()
+        return self._losses_host.tolist()
 
     def _state(self):
         f = self.model._flat

@@ -52,7 +52,9 @@ def _step_fn(args, model, optimizer):
     if graph_ok and isinstance(optimizer, _optim.Adam):
         def step(c):
             key = ('step', tuple(c.shape), beta, id(optimizer))
-            lv = _cached(model, key, limit, lambda: GraphedTrainStep(model, optimizer, c.shape, beta))(c).tolist()
+            g = _cached(model, key, limit, lambda: GraphedTrainStep(model, optimizer, c.shape, beta))
+            g(c)
+            lv = g.read_losses()                        # one host sync (reference: two .item())
             return lv[0], lv[1]
     elif graph_ok:
         def step(c):

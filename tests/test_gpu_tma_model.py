@@ -382,7 +382,10 @@ def test_graphed_step_prefetch_is_the_same_step():
             losses = step(host[i])
             if use_prefetch and i + 1 < 5:
                 step.prefetch(host[i + 1] if i != 2 else host[0])      # (i == 2: a prefetch that is then NOT consumed)
-            out.append(losses.tolist())
+            # read_losses(): the copy into pinned host memory queued behind the replay == the device tensor
+            host_read = step.read_losses()
+            assert host_read == losses.tolist()
+            out.append(host_read)
         torch.cuda.synchronize()
         runs.append((out, {k: v.clone() for k, v in m.state_dict().items()}))
     # The forward pass is reproducible (fixed-order statistic sums), so the FIRST step's losses agree to fp64-atomic
