@@ -429,3 +429,26 @@ def test_tma_fused_batchnorm_matches_two_kernel_form(batch, frames):
     for k, v in ba.items():
         if 'running' in k:
             assert relerr(bb[k], v) < 2e-2, k
+
+
+def test_codebook_gradient_is_the_same_on_the_side_stream(monkeypatch):
+    """The codebook's index_add_ gradient runs on the engine's side stream beside the decoder forward by default
+    (NSG_SCATTER_SIDE=2); placed beside the encoder backward (1) or inline (0) it is the same sum -- fp32 atomics in a
+    different order, and nothing else of the step changes."""
+    p, b, mel = _state(seed=31)
+    got = {}
+    for mode in ('0', '1', '2'):
+        monkeypatch.setenv('NSG_SCATTER_SIDE', mode)
+        m = _model(p, b, 2)
+        opt = nsg.optim.Adam(m, lr=1e-3)
+        opt.zero_grad()
+        losses, (xt, ze, zq, idx) = m.loss_and_grads(mel.to(DEV), beta=1.0)
+        torch.cuda.synchronize()
+        g = {k: q.grad.detach().clone() for k, q in m.named_parameters()}
+        got[mode] = (losses.tolist(), idx.clone(), g)
+    for mode in ('1', '2'):
+        assert got[mode][0] == got['0'][0]                                   # same forward, same losses
+        assert torch.equal(got[mode][1], got['0'][1])
+        e = relerr(got[mode][2]['codebook.embedding.weight'], got['0'][2]['codebook.embedding.weight'])
+        assert e < 1e-5, (mode, e)
+        assert float(got[mode][2]['codebook.embedding.weight'].abs().sum()) > 0
